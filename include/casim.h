@@ -1,0 +1,240 @@
+/*
+ * casim -- B200-native batched simulator for the CollisionAvoidanceEnv stepping path
+ * of mlodel/gym-exploration-2d.  C ABI of libcasim.so.
+ *
+ * This is the drop-in boundary: every entry point below is
+ * what a binding of the reference's stepping path would call instead of the Python
+ * implementation cited next to it (paths relative to the reference tree,
+ * gym_collision_avoidance/envs/...).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no torch types.
+ *   - Unless a function name ends in _host, every pointer is a DEVICE pointer owned by the
+ *     caller; the library never frees caller memory.  Calls are asynchronous on the passed
+ *     stream (a cudaStream_t passed as void*; NULL = legacy default stream).
+ *   - Return value: 0 = ok, otherwise a cudaError_t-compatible code (or CASIM_EINVAL);
+ *     casim_last_error() returns a human-readable message for the calling thread.
+ *   - One handle per GPU; calls on one stream are ordered; no host threads inside.
+ */
+#ifndef CASIM_H
+#define CASIM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CASIM_ABI_VERSION 1
+#define CASIM_EINVAL 10001
+
+/* ------------------------------------------------------------------------------------ */
+/* State record: 24 four-byte words per agent, stored as 6 planes of float4 ("packs"),   */
+/* plane p = state + p*E*A float4's, element (e*A + a).  Mirrors the attributes of       */
+/* envs/agent.py:9-112 that the stepping path reads or writes.                           */
+/* ------------------------------------------------------------------------------------ */
+#define CASIM_NUM_PACKS 6
+#define CASIM_STATE_WORDS 24
+enum casim_state_word {
+  /* pack 0 */ CASIM_PX = 0, CASIM_PY, CASIM_HEADING, CASIM_SPEED,
+  /* pack 1 */ CASIM_VX, CASIM_VY, CASIM_DELTA_HEADING, CASIM_TURNING_DIR,
+  /* pack 2 */ CASIM_GX, CASIM_GY, CASIM_RADIUS, CASIM_PREF_SPEED,           /* constant in an episode */
+  /* pack 3 */ CASIM_T, CASIM_TIME_REMAINING, CASIM_DIST_TO_GOAL, CASIM_PAST_DIST_TO_GOAL,
+  /* pack 4 */ CASIM_PAST_ACT0_V, CASIM_PAST_ACT0_W, CASIM_PAST_ACT1_V, CASIM_PAST_ACT1_W,
+  /* pack 5 */ CASIM_HEADING_EGO, CASIM_STEP_NUM /*i32*/, CASIM_FLAGS /*i32*/, CASIM_TYPE /*i32*/
+};
+
+/* CASIM_FLAGS bits (envs/agent.py:67-72, collision_avoidance_env.py:720) */
+enum casim_flag {
+  CASIM_F_IS_AT_GOAL = 1, CASIM_F_WAS_AT_GOAL_ALREADY = 2, CASIM_F_IN_COLLISION = 4,
+  CASIM_F_WAS_IN_COLLISION_ALREADY = 8, CASIM_F_RAN_OUT_OF_TIME = 16, CASIM_F_IS_DONE = 32,
+  CASIM_F_IS_INFEASIBLE = 64
+};
+
+/* CASIM_TYPE = policy | dynamics<<8 | sensor_mask<<16 */
+enum casim_policy {            /* envs/policies/ */
+  CASIM_POLICY_STATIC = 0,         /* StaticPolicy.py:9-12            */
+  CASIM_POLICY_NONCOOPERATIVE = 1, /* NonCooperativePolicy.py:10-13   */
+  CASIM_POLICY_EXTERNAL = 2,       /* ExternalPolicy.py: action = caller's [speed, dheading] */
+  CASIM_POLICY_LEARNING = 3,       /* LearningPolicy.py:11-16         */
+  CASIM_POLICY_CARRL = 4,          /* CARRLPolicy.py:14-15 (11-entry table) */
+  CASIM_POLICY_IG_GREEDY = 5,      /* ig_greedy.py:31-43 (action from casim_explore_step) */
+  CASIM_POLICY_GA3C_CADRL = 6,     /* GA3CCADRLPolicy.py:34-43 (action from casim_ga3c_forward) */
+  CASIM_POLICY_PEDESTRIAN = 7      /* PedestrianDatasetPolicy.py:15-16 (zeros) */
+};
+enum casim_dynamics {          /* envs/dynamics/ */
+  CASIM_DYN_UNICYCLE = 0,          /* UnicycleDynamics.py:10-31       */
+  CASIM_DYN_FIRST_ORDER = 1,       /* FirstOrderDynamics.py:10-23     */
+  CASIM_DYN_EXTERNAL = 2,          /* ExternalDynamics.py:8-23 + agent.py:125-145 */
+  CASIM_DYN_UNICYCLE_MAX_TURN_RATE = 3 /* UnicycleDynamicsMaxTurnRate.py:11-26 */
+};
+enum casim_sensor {            /* envs/sensors/ */
+  CASIM_SENSOR_OTHER_AGENTS = 1,   /* OtherAgentsStatesSensor.py:11-77 */
+  CASIM_SENSOR_LASERSCAN = 2,      /* LaserScanSensor.py:27-58         */
+  CASIM_SENSOR_OCCUPANCY_GRID = 4  /* OccupancyGridSensor.py:70-98     */
+};
+
+enum casim_game_over_mode {    /* collision_avoidance_env.py:722-736 */
+  CASIM_GAME_OVER_AGENT0 = 0,      /* TRAIN_SINGLE_AGENT, or EVALUATE_MODE and not HOMOGENEOUS_TESTING */
+  CASIM_GAME_OVER_ALL = 1,         /* EVALUATE_MODE and HOMOGENEOUS_TESTING */
+  CASIM_GAME_OVER_ALL_LEARNING = 2 /* otherwise: all agents whose policy is_still_learning */
+};
+
+#define CASIM_MAX_BEAMS 32
+#define CASIM_MAX_RANGES 32
+#define CASIM_MAX_AGENTS 32      /* one warp lane per agent of an environment */
+#define CASIM_MAP_DIM 300        /* Map(30 m, 30 m, 0.1 m): collision_avoidance_env.py:497 */
+#define CASIM_MAP_WORDS 10       /* 32-bit words per bit-packed map row (ceil(300/32)) */
+#define CASIM_NUM_STATS 8
+#define CASIM_GA3C_NUM_ACTIONS 11
+#define CASIM_GA3C_INPUT 75      /* GA3C_CADRL/network.py:148-151 NN_INPUT_SIZE */
+#define CASIM_GA3C_NUM_PARAMS 170764
+
+/* Snapshot of the reference's global Config (envs/config.py:3-221) plus the env members the
+ * path reads (collision_avoidance_env.py:97, 755-774).  All thresholds are doubles because the
+ * kernels evaluate the decision predicates in fp64, like the reference. */
+typedef struct casim_config {
+  double dt;                          /* Config.DT                      config.py:29 */
+  double reward_at_goal;              /* config.py:30 */
+  double reward_collision_with_agent; /* config.py:31 */
+  double reward_timeout;              /* config.py:32 */
+  double reward_infeasible;           /* config.py:33 */
+  double reward_collision_with_wall;  /* config.py:34 */
+  double reward_time_step;            /* config.py:37 */
+  double reward_distance_to_goal;     /* config.py:38 */
+  double reward_wiggly_behavior;      /* config.py:39 */
+  double wiggly_behavior_threshold;   /* config.py:40 */
+  double reward_min;                  /* collision_avoidance_env.py:773 */
+  double reward_max;                  /* collision_avoidance_env.py:774 */
+  double getting_close_range;         /* config.py:43 */
+  double near_goal_threshold;         /* config.py:60 */
+  double max_time_ratio;              /* config.py:61 */
+  double sensing_horizon;             /* config.py:63 (inf) */
+  double max_heading_change;          /* collision_avoidance_env.py:97 (LearningPolicy) */
+  double map_width, map_height;       /* config.py:88-89 (metres) */
+  double map_cell;                    /* config.py:85 SUBMAP_RESOLUTION */
+  double laser_max_range;             /* LaserScanSensor.py:15 */
+  double laser_norm_range;            /* config.py:95 MAX_RANGE */
+  double laser_angles[CASIM_MAX_BEAMS];  /* np.linspace(-pi, pi, num_beams)      LaserScanSensor.py:19 */
+  double laser_ranges[CASIM_MAX_RANGES]; /* np.arange(0, max_range, 2*pi/slices)  LaserScanSensor.py:20 */
+  /* exploration belief (ig_greedy.py:18-29, targetMap.py:7-24, experiments/src/dmcts.py:73-78) */
+  double ig_sens_fov;                 /* radians (targetMap.sensFOV) */
+  double ig_detect_fov;               /* the number ig_greedy compares against an angle in radians (degrees, sic) */
+  double ig_range;
+  double ig_cell;                     /* target-map cell size (map_res*5 = 0.5) */
+  double ig_rocc, ig_remp, ig_tolerance, ig_p_false_neg, ig_p_false_pos, ig_prior;
+  double ig_dt;
+  int32_t laser_num_beams;            /* config.py:55 */
+  int32_t laser_num_ranges;
+  int32_t collision_av_w_static_agent;/* config.py:49 */
+  int32_t max_other_agents_observed;  /* config.py:72 (sort clip)      */
+  int32_t max_other_agents_rows;      /* config.py:71 (rows of other_agents_states) */
+  int32_t submap_w, submap_h;         /* config.py:83-84 */
+  int32_t game_over_mode;             /* enum casim_game_over_mode */
+  int32_t auto_reset;                 /* batched-env extension: a game_over env restarts from its
+                                         initial condition at the beginning of the next step */
+  int32_t ig_map_dim;                 /* cells per side of the target map (60) */
+  int32_t reserved[6];
+} casim_config;
+
+/* Observation / result buffers written by casim_reset and casim_step.  NULL = not wanted
+ * (a sensor buffer must be non-NULL if any agent carries that sensor). */
+typedef struct casim_obs {
+  float*   obs_misc;            /* [E,A,4]  rel_goal_x, rel_goal_y, num_other_agents, use_ppo
+                                   (dynamics/Dynamics.py:28, OtherAgentsStatesSensor.py:75, config.py:208-213) */
+  float*   other_agents_states; /* [E,A,rows,10]  OtherAgentsStatesSensor.py:35-77 */
+  float*   laserscan;           /* [E,A,num_beams] LaserScanSensor.py:58 */
+  uint8_t* local_grid;          /* [E,A,submap_w,submap_h] bool (rows = map rows)  OccupancyGridSensor.py:98 */
+  float*   rewards;             /* [E,A]  collision_avoidance_env.py:502-567 (per-agent; agent 0's is the
+                                   TRAIN_SINGLE_AGENT scalar) */
+  uint8_t* done;                /* [E,A]  which_agents_done, :711-720 */
+  uint8_t* game_over;           /* [E]    :722-736 */
+  uint8_t* collision_flags;     /* [E,A]  bit0 collision_with_agent, bit1 collision_with_wall (:630-671); may be NULL */
+  float*   nearest_dist;        /* [E,A]  dist_btwn_nearest_agent (:649), +inf if none; may be NULL */
+  float*   stats;               /* [CASIM_NUM_STATS] per-step sums over the shard: n_new_collisions, n_new_at_goal,
+                                   n_new_timeouts, n_game_over_envs, reward_sum, n_active_agents, n_agents, 0; may be NULL */
+} casim_obs;
+
+typedef struct casim_handle casim_handle;
+
+const char* casim_last_error(void);
+int casim_abi_version(void);
+
+/* Fill a config with the reference defaults (envs/config.py, LaserScanSensor.py:13-20,
+ * experiments/src/dmcts.py:73-78).  Host-only, no GPU needed. */
+void casim_default_config(casim_config* cfg);
+
+/* Replaces CollisionAvoidanceEnv.__init__ (collision_avoidance_env.py:60-160) for E environments of
+ * at most A agents.  Allocates only internal scratch (bit-packed maps, per-step partial sums). */
+int casim_create(const casim_config* cfg, int E, int A, casim_handle** out);
+int casim_destroy(casim_handle* h);
+int casim_set_config(casim_handle* h, const casim_config* cfg);
+
+/* Replaces _init_static_map + Map.__init__/get_occupancy_grid (collision_avoidance_env.py:481-500,
+ * Map.py:10-36,107-123).  rects: [n_maps, max_rects, 4] = (x of corner 1, y of corner 1, x of corner 3,
+ * y of corner 3) in metres; n_rects: [n_maps].  n_maps is 1 (shared by all envs) or E.  n_maps = 0 clears
+ * the map ("no obstacles": the wall check of collision_avoidance_env.py:656 is skipped).
+ * Also (re)builds the squared Euclidean distance field used by the exploration kernels
+ * (information_models/edfMap.py:11-12).  map_out (optional): [n_maps,300,300] uint8 copy of static_map. */
+int casim_set_obstacles(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps,
+                        int max_rects, uint8_t* map_out, void* stream);
+/* Same, from a ready-made occupancy raster [n_maps,300,300] uint8 (Map.static_map). */
+int casim_set_map(casim_handle* h, const uint8_t* static_map, int n_maps, void* stream);
+
+/* Trajectory tables for ExternalDynamics (dynamics/ExternalDynamics.py:11-20): traj [E,A,T,4] =
+ * (pose_x, pose_y, vel_x, vel_y).  The pointer is borrowed until replaced. */
+int casim_set_trajectories(casim_handle* h, const float* traj, int T);
+
+/* Replaces Agent.__init__ for every agent + the first _get_obs (agent.py:9-112,
+ * collision_avoidance_env.py:257-266).  init: [E,A,7] = start_x, start_y, goal_x, goal_y, radius,
+ * pref_speed, initial_heading (NaN = None -> atan2(goal-start), agent.py:29-33); type: [E,A] CASIM_TYPE words;
+ * n_agents: [E].  Writes state [6,E,A,4] and the observation buffers.  The library keeps the three
+ * input pointers (borrowed) for auto_reset. */
+int casim_reset(casim_handle* h, float* state, const float* init, const int32_t* type,
+                const int32_t* n_agents, const casim_obs* obs, void* stream);
+
+/* Recompute sensors/observations from a caller-modified state without stepping (_get_obs, :740-753). */
+int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, void* stream);
+
+/* Replaces CollisionAvoidanceEnv.step (collision_avoidance_env.py:162-232): _take_action (in-kernel policies,
+ * fp32 action rounding :289, Agent.take_action agent.py:147-190, dynamics), _compute_rewards +
+ * _check_for_collisions (:502-567, :630-671), _get_obs (sensors), _check_which_agents_done (:711-738).
+ * ext_actions: [E,A,2] caller-supplied actions (external / learning / CARRL agents); may be NULL if none.
+ * policy_actions: [E,A,2] actions chosen by casim_explore_step / casim_ga3c_forward; may be NULL if none. */
+int casim_step(casim_handle* h, float* state, const float* ext_actions, const float* policy_actions,
+               float dt, const casim_obs* obs, void* stream);
+
+/* Host-buffer variant: ext_actions_host (pinned, may be NULL) is copied H2D, the step runs, and rewards, done and
+ * game_over (and obs_misc/sensor buffers if the host pointers are non-NULL) are copied D2H into `host`; blocks until
+ * the results are in host memory.  `dev` holds the device buffers used for the step. */
+int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
+                    const float* policy_actions, float dt, const casim_obs* dev, const casim_obs* host,
+                    void* stream);
+
+/* Replaces ig_greedy.find_next_action for every ig_greedy agent (policies/ig_greedy.py:31-93,
+ * information_models/targetMap.py:43-147, edfMap.py:14-47): detector emulation from other_agents_states,
+ * target-map odds update over the visible cells, one-step greedy information-gain argmax over 9 candidate
+ * actions.  belief: [E,A,ig_map_dim,ig_map_dim] fp32 odds (row j = y cell, col i = x cell), RMW.
+ * policy_actions [E,A,2] receives the chosen action; best_mi [E,A] (optional) the winning score;
+ * cand_mi [E,A,9] (optional) every candidate's score (-1 = infeasible);
+ * counters [4] (optional, uint64): cells tested, EDF samples, visible cells, clamped samples. */
+int casim_explore_step(casim_handle* h, const float* state, const float* other_agents_states, float* belief,
+                       float* policy_actions, float* best_mi, float* cand_mi, unsigned long long* counters,
+                       void* stream);
+
+/* Replaces GA3CCADRLPolicy.find_next_action for every GA3C agent (policies/GA3CCADRLPolicy.py:34-106,
+ * GA3C_CADRL/network.py:45-98).  weights: fp32 parameter blob, order kernel/bias of lstm [71,256],[256];
+ * layer1 [68,256],[256]; layer2 [256,256],[256]; fullyconnected1 [256,256],[256]; logits_p [256,11],[11]
+ * (row-major [in,out] like TF).  Writes policy_actions [E,A,2]; optionally action_idx [E,A] (int32, -1 for
+ * non-GA3C agents), probs [E,A,11] and nn_input [E,A,75]. */
+int casim_ga3c_set_weights(casim_handle* h, const float* weights_host, int n_params, void* stream);
+int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_actions, int32_t* action_idx,
+                       float* probs, float* nn_input, int use_tensor_cores, void* stream);
+
+/* Introspection for benchmarks: number of kernel launches issued through this handle so far. */
+unsigned long long casim_launch_count(const casim_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CASIM_H */

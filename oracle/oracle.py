@@ -1,0 +1,175 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes wrapper around oracle/libcasim_oracle.so.
+
+The oracle is the CPU restatement (plain C, fp64) of the reference stepping path.  It may be
+imported only by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs, as the checker or the timed CPU baseline -- never by the product package.
+"""
+import ctypes
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+_PKG = os.path.join(_ROOT, "gym-exploration-2d_b200")
+if _PKG not in sys.path:
+    sys.path.insert(0, _PKG)
+
+from casim.config import SimConfig, MAP_DIM, NUM_STATS  # noqa: E402  (struct layout only)
+from casim import layout as L  # noqa: E402
+
+_LIB_PATH = os.path.join(_HERE, "libcasim_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    if force or not os.path.exists(_LIB_PATH) or \
+            os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, "casim_oracle.c")):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "libcasim_oracle.so"])
+    return _LIB_PATH
+
+
+class _Obs(ctypes.Structure):
+    _fields_ = [("obs_misc", ctypes.c_void_p), ("other_agents_states", ctypes.c_void_p),
+                ("laserscan", ctypes.c_void_p), ("local_grid", ctypes.c_void_p),
+                ("rewards", ctypes.c_void_p), ("done", ctypes.c_void_p), ("game_over", ctypes.c_void_p),
+                ("collision_flags", ctypes.c_void_p), ("nearest_dist", ctypes.c_void_p),
+                ("stats", ctypes.c_void_p)]
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.casim_oracle_default_config.argtypes = [ctypes.POINTER(SimConfig)]
+        _lib.casim_oracle_default_config.restype = None
+    return _lib
+
+
+def default_config():
+    c = SimConfig()
+    lib().casim_oracle_default_config(ctypes.byref(c))
+    return c
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def rasterize(cfg, rects):
+    """Map.get_occupancy_grid: rects [n,4] (x1,y1,x3,y3) -> [300,300] uint8."""
+    rects = np.ascontiguousarray(rects, dtype=np.float64).reshape(-1, 4)
+    out = np.zeros((MAP_DIM, MAP_DIM), np.uint8)
+    lib().casim_oracle_rasterize(ctypes.byref(cfg), _p(rects), ctypes.c_int(len(rects)), _p(out))
+    return out
+
+
+class ObsBuffers:
+    """Output arrays of one oracle step (doubles / uint8)."""
+
+    def __init__(self, cfg, E, A):
+        rows = cfg.max_other_agents_rows
+        self.obs_misc = np.zeros((E, A, 4))
+        self.other_agents_states = np.zeros((E, A, rows, 10))
+        self.laserscan = np.zeros((E, A, cfg.laser_num_beams))
+        self.local_grid = np.zeros((E, A, cfg.submap_w, cfg.submap_h), np.uint8)
+        self.rewards = np.zeros((E, A))
+        self.done = np.zeros((E, A), np.uint8)
+        self.game_over = np.zeros((E,), np.uint8)
+        self.collision_flags = np.zeros((E, A), np.uint8)
+        self.nearest_dist = np.zeros((E, A))
+        self.stats = np.zeros((NUM_STATS,))
+
+    def struct(self):
+        s = _Obs()
+        for name, _ in _Obs._fields_:
+            setattr(s, name, _p(getattr(self, name)))
+        return s
+
+
+def maps_arg(maps):
+    if maps is None:
+        return None, 0
+    maps = np.ascontiguousarray(maps, dtype=np.uint8).reshape(-1, MAP_DIM, MAP_DIM)
+    return maps, maps.shape[0]
+
+
+def reset(cfg, init, types, n_agents=None, maps=None, obs=None):
+    """Agent.__init__ for every agent + first _get_obs.  init [E,A,7] f64, types [E,A] i32.
+    Returns (state [E,A,24] f64, ObsBuffers)."""
+    init = np.ascontiguousarray(init, dtype=np.float64)
+    E, A = init.shape[:2]
+    types = np.ascontiguousarray(types, dtype=np.int32).reshape(E, A)
+    n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
+    state = np.zeros((E, A, L.STATE_WORDS))
+    obs = obs or ObsBuffers(cfg, E, A)
+    maps, n_maps = maps_arg(maps)
+    o = obs.struct()
+    rc = lib().casim_oracle_reset(ctypes.byref(cfg), E, A, _p(n_agents), _p(state), _p(init), _p(types),
+                                  _p(maps), n_maps, ctypes.byref(o))
+    assert rc == 0
+    return state, obs
+
+
+def observe(cfg, state, n_agents=None, maps=None, obs=None):
+    state = np.ascontiguousarray(state, dtype=np.float64)
+    E, A = state.shape[:2]
+    n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
+    obs = obs or ObsBuffers(cfg, E, A)
+    maps, n_maps = maps_arg(maps)
+    o = obs.struct()
+    rc = lib().casim_oracle_observe(ctypes.byref(cfg), E, A, _p(n_agents), _p(state), _p(maps), n_maps,
+                                    ctypes.byref(o))
+    assert rc == 0
+    return obs
+
+
+def step(cfg, state, ext_actions=None, policy_actions=None, dt=None, n_agents=None, maps=None,
+         traj=None, init=None, types0=None, prev_game_over=None, obs=None, n_threads=1):
+    """One CollisionAvoidanceEnv.step per environment, in place on ``state`` [E,A,24] f64."""
+    assert state.dtype == np.float64 and state.flags.c_contiguous
+    E, A = state.shape[:2]
+    dt = cfg.dt if dt is None else float(dt)
+    f64 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)  # noqa: E731
+    ext_actions, policy_actions, traj, init = f64(ext_actions), f64(policy_actions), f64(traj), f64(init)
+    T = 0 if traj is None else traj.shape[2]
+    n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
+    types0 = None if types0 is None else np.ascontiguousarray(types0, dtype=np.int32)
+    prev_game_over = None if prev_game_over is None else np.ascontiguousarray(prev_game_over, dtype=np.uint8)
+    obs = obs or ObsBuffers(cfg, E, A)
+    maps, n_maps = maps_arg(maps)
+    o = obs.struct()
+    rc = lib().casim_oracle_step(ctypes.byref(cfg), E, A, _p(n_agents), _p(state), _p(ext_actions),
+                                 _p(policy_actions), ctypes.c_double(dt), _p(maps), n_maps, _p(traj), T,
+                                 _p(init), _p(types0), _p(prev_game_over), ctypes.byref(o), int(n_threads))
+    assert rc == 0, rc
+    return obs
+
+
+# ------------------------------------------------------------------------------------------
+# conversions between the GPU layout (state [6,E,A,4] fp32 with int32 words) and the oracle's
+# [E,A,24] doubles
+def state_from_packs(packs):
+    """packs: numpy float32 [6,E,A,4] (int words bit-cast) -> float64 [E,A,24]."""
+    packs = np.ascontiguousarray(packs, dtype=np.float32)
+    P, E, A, _ = packs.shape
+    w = packs.transpose(1, 2, 0, 3).reshape(E, A, P * 4)
+    out = w.astype(np.float64)
+    iw = np.ascontiguousarray(w).view(np.int32)
+    for k in L.INT_WORDS:
+        out[..., k] = iw[..., k]
+    return np.ascontiguousarray(out)
+
+
+def packs_from_state(state):
+    """float64 [E,A,24] -> float32 [6,E,A,4] with int32 words bit-cast (values rounded to fp32)."""
+    E, A, W = state.shape
+    w = state.astype(np.float32)
+    iw = w.view(np.int32)
+    for k in L.INT_WORDS:
+        iw[..., k] = state[..., k].astype(np.int32)
+    return np.ascontiguousarray(w.reshape(E, A, W // 4, 4).transpose(2, 0, 1, 3))

@@ -1,0 +1,146 @@
+"""CPU: the C oracle (oracle/casim_oracle.c) against golden vectors produced by the real reference
+(oracle/gen_golden.py).  Flags / ordering / grid cells exact, continuous values 1e-5."""
+import numpy as np
+import pytest
+
+import helpers as H
+from casim import layout as L
+
+
+def cfg_for(oracle, mode):
+    c = oracle.default_config()
+    c.game_over_mode = int(mode)
+    return c
+
+
+def run_single_step(oracle, z, k, maps):
+    n = int(z["n_agents"][k])
+    cfg = cfg_for(oracle, z["game_over_mode"][k])
+    state = np.ascontiguousarray(z["state_in"][k:k + 1]).copy()
+    mid = int(z["map_id"][k])
+    obs = oracle.step(cfg, state, ext_actions=z["ext_actions"][k:k + 1], dt=0.1,
+                      n_agents=z["n_agents"][k:k + 1], maps=maps[mid], traj=z["traj"][k:k + 1])
+    return n, state, obs
+
+
+@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz"])
+def test_single_step_vs_reference(oracle_lib, name):
+    oracle = oracle_lib
+    z = H.load(name)
+    maps, _ = H.unpack_maps()
+    ncases = z["state_in"].shape[0]
+    for k in range(ncases):
+        n, state, obs = run_single_step(oracle, z, k, maps)
+        what = "%s case %d" % (name, k)
+        H.assert_state_close(state, z["state_out"][k:k + 1], [n], what)
+        assert np.array_equal(obs.done[0, :n], z["done"][k, :n]), what
+        assert obs.game_over[0] == z["game_over"][k], what
+        assert np.array_equal(obs.collision_flags[0, :n], z["collision_flags"][k, :n]), what
+        H.assert_close(obs.rewards[0, :n], z["rewards"][k, :n], what + " rewards")
+        H.assert_close(obs.nearest_dist[0, :n], z["nearest_dist"][k, :n], what + " nearest")
+        H.assert_close(obs.obs_misc[0, :n, :3], z["obs_misc"][k, :n, :3], what + " obs_misc")
+        H.assert_close(obs.other_agents_states[0, :n], z["other_agents_states"][k, :n], what + " other_agents")
+        # closest-N ordering: the type / radius columns pin the row order exactly
+        assert np.array_equal(obs.other_agents_states[0, :n, :, 9], z["other_agents_states"][k, :n, :, 9]), what
+        H.assert_close(obs.laserscan[0, :n], z["laserscan"][k, :n], what + " laserscan", rtol=0, atol=1e-12)
+        assert np.array_equal(obs.local_grid[0, :n], z["local_grid"][k, :n]), what + " local_grid"
+
+
+def test_reset_vs_reference(oracle_lib):
+    oracle = oracle_lib
+    z = H.load("reset.npz")
+    maps, _ = H.unpack_maps()
+    cfg = oracle.default_config()
+    for k in range(z["init"].shape[0]):
+        n = int(z["n_agents"][k])
+        state, obs = oracle.reset(cfg, z["init"][k:k + 1], z["types"][k:k + 1], n_agents=z["n_agents"][k:k + 1],
+                                  maps=maps[int(z["map_id"][k])])
+        what = "reset case %d" % k
+        H.assert_state_close(state, z["state_out"][k:k + 1], [n], what)
+        H.assert_close(obs.other_agents_states[0, :n], z["other_agents_states"][k, :n], what)
+        H.assert_close(obs.laserscan[0, :n], z["laserscan"][k, :n], what, rtol=0, atol=1e-12)
+        assert np.array_equal(obs.local_grid[0, :n], z["local_grid"][k, :n]), what
+        H.assert_close(obs.obs_misc[0, :n, :3], z["obs_misc"][k, :n, :3], what)
+
+
+@pytest.mark.parametrize("name,tol", [("c1_two_agents.npz", 1e-9), ("c1_two_agents_nep50.npz", 1e-5)])
+def test_c1_trajectory_vs_reference(oracle_lib, name, tol):
+    """Config C1: 100 free-running steps of the 2-agent example.  The nep50 variant is the reference
+    executed with Python-float headings under numpy 2 (float32 dynamics): it must agree
+    within the 1e-5 tolerance with identical flags."""
+    oracle = oracle_lib
+    z = H.load(name)
+    cfg = oracle.default_config()
+    cfg.game_over_mode = 2
+    state, obs = oracle.reset(cfg, z["init"][None], z["types"][None])
+    H.assert_close(state[0][:, H.CONT_WORDS], z["states"][0][:, H.CONT_WORDS], "t0", rtol=tol, atol=tol)
+    first_done = None
+    for t in range(z["rewards"].shape[0]):
+        obs = oracle.step(cfg, state, dt=0.1)
+        ref = z["states"][t + 1]
+        for k in L.INT_WORDS:
+            assert np.array_equal(state[0, :, k], ref[:, k]), (t, k)
+        H.assert_close(state[0][:, H.CONT_WORDS], ref[:, H.CONT_WORDS], "t=%d" % t, rtol=tol, atol=tol)
+        H.assert_close(obs.rewards[0], z["rewards"][t], "rew t=%d" % t, rtol=tol, atol=tol)
+        assert np.array_equal(obs.done[0], z["done"][t])
+        assert obs.game_over[0] == z["game_over"][t]
+        H.assert_close(obs.other_agents_states[0], z["other_agents_states"][t + 1], "oas t=%d" % t, rtol=tol, atol=tol)
+        if first_done is None and obs.done[0].any():
+            first_done = t
+    assert first_done == 37            # first done at step index 37
+
+
+def test_appendix_b_known_answers(oracle_lib):
+    """SURVEY.md Appendix B values (reference run with float headings -> 1e-5 tolerance on positions)."""
+    oracle = oracle_lib
+    cfg = oracle.default_config()
+    cfg.game_over_mode = 2
+    t = L.encode_type(L.POLICY_NONCOOPERATIVE, L.DYN_UNICYCLE, L.SENSOR_OTHER_AGENTS)
+    init = np.array([[[-3, -3, 3, 3, 0.5, 1.0, 0.5], [3, 3, -3, -3, 0.5, 1.0, 0.5]]], dtype=np.float64)
+    state, _ = oracle.reset(cfg, init, np.array([[t, t]], np.int32))
+    assert abs(state[0, 0, L.TIME_REMAINING] / 3.0 - 7.7352813742385695) < 1e-12
+    obs = oracle.step(cfg, state)
+    assert abs(state[0, 0, L.PX] - (-2.9292893186211586)) < 1e-7
+    assert abs(obs.rewards[0, 0] - (-0.00076923076923077)) < 1e-15
+    assert abs(state[0, 0, L.DIST_TO_GOAL] - 8.38528136962797) < 1e-7
+    row = obs.other_agents_states[0, 0, 0]
+    np.testing.assert_allclose(row, [5.8585786372423172, 5.8585786372423172, 8.2852813650173704, 0,
+                                     -0.999999982885729, 0, 0.5, 1.0, 7.2852813650173704, 2.0], atol=1e-7)
+    # ordering check: host at the origin, others at (3,0), (0,2) Static, (0,-2), (-1,0), all r = 0.2
+    ts = L.encode_type(L.POLICY_STATIC, L.DYN_UNICYCLE, 0)
+    tn = L.encode_type(L.POLICY_NONCOOPERATIVE, L.DYN_UNICYCLE, L.SENSOR_OTHER_AGENTS)
+    init = np.array([[[0, 0, 5, 0, 0.2, 1, 0], [3, 0, 5, 5, 0.2, 1, 0], [0, 2, 5, 5, 0.2, 1, 0],
+                      [0, -2, 5, 5, 0.2, 1, 0], [-1, 0, 5, 5, 0.2, 1, 0]]], dtype=np.float64)
+    state, obs = oracle.reset(cfg, init, np.array([[tn, tn, ts, tn, tn]], np.int32))
+    rows = obs.other_agents_states[0, 0]
+    np.testing.assert_allclose(rows[:4, 8], [2.6, 1.6, 1.6, 0.6], atol=1e-12)
+    assert list(rows[:4, 9]) == [2, 2, 1, 2]          # agents 1, 3, 2, 4: the tie is won by the higher index
+    np.testing.assert_allclose(rows[:4, 0:2], [[3, 0], [0, -2], [0, 2], [-1, 0]], atol=1e-12)
+
+
+def test_map_raster_vs_reference(oracle_lib):
+    oracle = oracle_lib
+    maps, rects = H.unpack_maps()
+    cfg = oracle.default_config()
+    for mid in (1, 2):
+        m = oracle.rasterize(cfg, rects[mid])
+        assert np.array_equal(m, maps[mid])
+
+
+def test_occupancy_grid_vs_cv2(oracle_lib):
+    """OccupancyGridSensor restatement vs the reference sensor (cv2.warpAffine) on 400 random poses."""
+    oracle = oracle_lib
+    z = H.load("occgrid.npz")
+    maps, _ = H.unpack_maps()
+    cfg = oracle.default_config()
+    grids = np.unpackbits(z["grids"], axis=-1)[..., :60]
+    t = L.encode_type(L.POLICY_STATIC, L.DYN_UNICYCLE, L.SENSOR_OCCUPANCY_GRID)
+    mism = 0
+    for k in range(z["poses"].shape[0]):
+        st = np.zeros((1, 1, L.STATE_WORDS))
+        st[0, 0, L.PX], st[0, 0, L.PY], st[0, 0, L.HEADING] = z["poses"][k]
+        st[0, 0, L.TYPE] = t
+        st[0, 0, L.RADIUS] = 0.5
+        obs = oracle.observe(cfg, st, maps=maps[int(z["map_id"][k])])
+        mism += int((obs.local_grid[0, 0] != grids[k]).sum())
+    assert mism == 0
