@@ -1,0 +1,391 @@
+/*
+ * casim_api.cu -- the C ABI of libcasim.so (include/casim.h): handle management, configuration
+ * snapshot, and the entry points that launch the kernels.  No torch types, no host threads, no
+ * host synchronisation except in the *_host variant and in create/destroy.
+ */
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "casim_internal.h"
+
+static thread_local char g_err[512] = "";
+
+void casim_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+#define CK(call)                                                                      \
+  do {                                                                                \
+    cudaError_t _e = (call);                                                          \
+    if (_e != cudaSuccess) {                                                          \
+      casim_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return (int)_e;                                                                 \
+    }                                                                                 \
+  } while (0)
+
+#define REQUIRE(cond, msg)                     \
+  do {                                         \
+    if (!(cond)) {                             \
+      casim_set_error("casim: %s", msg);       \
+      return CASIM_EINVAL;                     \
+    }                                          \
+  } while (0)
+
+extern "C" {
+
+const char* casim_last_error(void) { return g_err; }
+int casim_abi_version(void) { return CASIM_ABI_VERSION; }
+
+/* Reference defaults: config.py:29-95, LaserScanSensor.py:13-20, collision_avoidance_env.py:97,755-774,
+ * ig_greedy.py:18-29, experiments/src/dmcts.py:73-78. */
+void casim_default_config(casim_config* c) {
+  memset(c, 0, sizeof(*c));
+  c->dt = 0.1;
+  c->reward_at_goal = 3.0;
+  c->reward_collision_with_agent = -10.0;
+  c->reward_timeout = -10.0;
+  c->reward_infeasible = 0.0;
+  c->reward_collision_with_wall = -0.25;
+  c->reward_time_step = -0.01;
+  c->reward_distance_to_goal = 0.0;
+  c->reward_wiggly_behavior = 0.0;
+  c->wiggly_behavior_threshold = 0.0;
+  c->reward_min = -10.0;
+  c->reward_max = 3.0;
+  c->getting_close_range = 0.2;
+  c->near_goal_threshold = 0.75;
+  c->max_time_ratio = 3.0;
+  c->sensing_horizon = INFINITY;
+  c->max_heading_change = 4.0;
+  c->map_width = 30.0;
+  c->map_height = 30.0;
+  c->map_cell = 0.1;
+  c->laser_max_range = 6.0;
+  c->laser_norm_range = 6.0;
+  c->laser_num_beams = 16;
+  {
+    /* np.linspace(-pi, pi, 16) and np.arange(0, 6, 2*pi/16) */
+    const double PI = 3.14159265358979323846;
+    int n = c->laser_num_beams;
+    double start = -PI, stop = PI, step = (stop - start) / (double)(n - 1);
+    for (int i = 0; i < n; i++) c->laser_angles[i] = (double)i * step + start;
+    c->laser_angles[n - 1] = stop;
+    double rstep = 2 * PI / 16.0;
+    int nr = (int)ceil((6.0 - 0.0) / rstep);
+    c->laser_num_ranges = nr;
+    for (int i = 0; i < nr; i++) c->laser_ranges[i] = 0.0 + (double)i * rstep;
+    c->ig_sens_fov = 60.0 * PI / 180.0;
+  }
+  c->ig_detect_fov = 60.0;
+  c->ig_range = 5.0;
+  c->ig_cell = 0.1 * 5;
+  c->ig_rocc = 1.5;
+  c->ig_remp = 0.66;
+  c->ig_tolerance = 0.01;
+  c->ig_p_false_neg = 0.1;
+  c->ig_p_false_pos = 0.05;
+  c->ig_prior = 1.0;
+  c->ig_dt = 0.1;
+  c->collision_av_w_static_agent = 0;
+  c->max_other_agents_observed = 9;
+  c->max_other_agents_rows = 9;
+  c->submap_w = 60;
+  c->submap_h = 60;
+  c->game_over_mode = CASIM_GAME_OVER_AGENT0;
+  c->auto_reset = 0;
+  c->ig_map_dim = 60;
+}
+
+static int derive(const casim_config* c, DevCfg* d) {
+  memset(d, 0, sizeof(*d));
+  REQUIRE(c->laser_num_beams >= 0 && c->laser_num_beams <= CASIM_MAX_BEAMS, "laser_num_beams out of range");
+  REQUIRE(c->laser_num_ranges >= 0 && c->laser_num_ranges <= CASIM_MAX_RANGES, "laser_num_ranges out of range");
+  REQUIRE(c->map_cell > 0, "map_cell must be positive");
+  REQUIRE((int)(c->map_width / c->map_cell) == CASIM_MAP_DIM && (int)(c->map_height / c->map_cell) == CASIM_MAP_DIM,
+          "the static map must be 300x300 cells");
+  REQUIRE(c->max_other_agents_rows >= 1 && c->max_other_agents_rows <= CASIM_MAX_AGENTS, "max_other_agents_rows");
+  REQUIRE(c->submap_w >= 1 && c->submap_w <= 64 && c->submap_h >= 1 && c->submap_h <= 64, "submap must be <= 64x64");
+  d->dt = c->dt;
+  d->dt_nominal = c->dt;
+  d->r_at_goal = c->reward_at_goal;
+  d->r_coll_agent = c->reward_collision_with_agent;
+  d->r_timeout = c->reward_timeout;
+  d->r_infeasible = c->reward_infeasible;
+  d->r_coll_wall = c->reward_collision_with_wall;
+  d->r_time_step = c->reward_time_step;
+  d->r_dist_goal = c->reward_distance_to_goal;
+  d->r_wiggly = c->reward_wiggly_behavior;
+  d->wiggly_thr = c->wiggly_behavior_threshold;
+  d->r_min = c->reward_min;
+  d->r_max = c->reward_max;
+  d->close_range = c->getting_close_range;
+  d->near_goal = c->near_goal_threshold;
+  d->max_time_ratio = c->max_time_ratio;
+  d->sensing_horizon = c->sensing_horizon;
+  d->max_heading_change = c->max_heading_change;
+  d->map_ox = (c->map_width / 2.) / c->map_cell;
+  d->map_oy = (c->map_height / 2.) / c->map_cell;
+  d->cell = c->map_cell;
+  d->inv_cell = 1.0 / c->map_cell;
+  d->laser_max_range = c->laser_max_range;
+  d->laser_norm = c->laser_norm_range;
+  d->nb = c->laser_num_beams;
+  d->nr = c->laser_num_ranges;
+  for (int i = 0; i < d->nb; i++) {
+    d->laser_ang[i] = c->laser_angles[i];
+    d->laser_cos[i] = cos(c->laser_angles[i]);
+    d->laser_sin[i] = sin(c->laser_angles[i]);
+  }
+  for (int i = 0; i < d->nr; i++) d->laser_r[i] = c->laser_ranges[i];
+  d->ig_fov_half = c->ig_sens_fov / 2;
+  d->ig_detect_fov_half = c->ig_detect_fov / 2.0;
+  d->ig_range = c->ig_range;
+  d->ig_cell = c->ig_cell;
+  d->ig_rocc = c->ig_rocc;
+  d->ig_remp = c->ig_remp;
+  d->ig_tol = c->ig_tolerance;
+  d->ig_pfn = c->ig_p_false_neg;
+  d->ig_pfp = c->ig_p_false_pos;
+  d->ig_dt = c->ig_dt;
+  d->ig_det_thresh = sqrt(0.5) * c->ig_cell + c->ig_tolerance;
+  d->coll_w_static = c->collision_av_w_static_agent;
+  d->max_obs = c->max_other_agents_observed;
+  d->rows = c->max_other_agents_rows;
+  d->submap_w = c->submap_w;
+  d->submap_h = c->submap_h;
+  d->game_over_mode = c->game_over_mode;
+  d->auto_reset = c->auto_reset;
+  d->ig_dim = c->ig_map_dim;
+  return 0;
+}
+
+int casim_create(const casim_config* cfg, int E, int A, casim_handle** out) {
+  REQUIRE(cfg && out, "null argument");
+  REQUIRE(E >= 1, "E must be >= 1");
+  REQUIRE(A >= 1 && A <= CASIM_MAX_AGENTS, "A must be in 1..32");
+  casim_handle* h = (casim_handle*)calloc(1, sizeof(casim_handle));
+  REQUIRE(h, "out of host memory");
+  h->cfg = *cfg;
+  int rc = derive(cfg, &h->dc);
+  if (rc) {
+    free(h);
+    return rc;
+  }
+  h->E = E;
+  h->A = A;
+  cudaError_t e = cudaGetDevice(&h->device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device);
+  int epw = 32 / A;
+  h->max_ctas = (E + epw - 1) / epw;
+  size_t N = (size_t)E * A;
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->pose64, N * 4 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->prev_game_over, (size_t)E);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->partials, (size_t)h->max_ctas * CASIM_NUM_STATS * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->ticket, sizeof(unsigned int));
+  if (e == cudaSuccess) e = cudaMemset(h->prev_game_over, 0, (size_t)E);
+  if (e == cudaSuccess) e = cudaMemset(h->ticket, 0, sizeof(unsigned int));
+  if (e == cudaSuccess) e = cudaMemset(h->pose64, 0, N * 4 * sizeof(double));
+  if (e != cudaSuccess) {
+    casim_set_error("casim_create: %s", cudaGetErrorString(e));
+    casim_destroy(h);
+    return (int)e;
+  }
+  *out = h;
+  return 0;
+}
+
+int casim_destroy(casim_handle* h) {
+  if (!h) return 0;
+  cudaFree(h->pose64);
+  cudaFree(h->prev_game_over);
+  cudaFree(h->partials);
+  cudaFree(h->ticket);
+  cudaFree(h->map_planes);
+  cudaFree(h->edf_d2);
+  cudaFree(h->edf_scratch);
+  cudaFree(h->ga3c_w);
+  cudaFree(h->ga3c_wb);
+  free(h);
+  return 0;
+}
+
+int casim_set_config(casim_handle* h, const casim_config* cfg) {
+  REQUIRE(h && cfg, "null argument");
+  DevCfg d;
+  int rc = derive(cfg, &d);
+  if (rc) return rc;
+  h->cfg = *cfg;
+  h->dc = d;
+  return 0;
+}
+
+static int ensure_maps(casim_handle* h, int n_maps) {
+  if (n_maps <= h->n_maps_alloc) return 0;
+  cudaFree(h->map_planes);
+  cudaFree(h->edf_d2);
+  cudaFree(h->edf_scratch);
+  h->map_planes = nullptr;
+  h->edf_d2 = h->edf_scratch = nullptr;
+  h->n_maps_alloc = 0;
+  CK(cudaMalloc((void**)&h->map_planes, (size_t)n_maps * CASIM_NUM_PLANES * CASIM_PLANE_WORDS * sizeof(uint32_t)));
+  CK(cudaMalloc((void**)&h->edf_d2, (size_t)n_maps * CASIM_MAP_DIM * CASIM_MAP_DIM * sizeof(int32_t)));
+  CK(cudaMalloc((void**)&h->edf_scratch, (size_t)n_maps * CASIM_MAP_DIM * CASIM_MAP_DIM * sizeof(int32_t)));
+  h->n_maps_alloc = n_maps;
+  return 0;
+}
+
+int casim_set_obstacles(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps, int max_rects,
+                        uint8_t* map_out, void* stream) {
+  REQUIRE(h, "null handle");
+  REQUIRE(n_maps == 0 || n_maps == 1 || n_maps == h->E, "n_maps must be 0, 1 or E");
+  if (n_maps == 0) {
+    h->n_maps = 0;
+    return 0;
+  }
+  REQUIRE(rects && n_rects && max_rects >= 0, "null rectangles");
+  int rc = ensure_maps(h, n_maps);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(casim_launch_raster(h, rects, n_rects, n_maps, max_rects, s));
+  CK(casim_launch_map_derive(h, n_maps, map_out, s));
+  h->n_maps = n_maps;
+  return 0;
+}
+
+int casim_set_map(casim_handle* h, const uint8_t* static_map, int n_maps, void* stream) {
+  REQUIRE(h, "null handle");
+  REQUIRE(n_maps == 0 || n_maps == 1 || n_maps == h->E, "n_maps must be 0, 1 or E");
+  if (n_maps == 0) {
+    h->n_maps = 0;
+    return 0;
+  }
+  REQUIRE(static_map, "null map");
+  int rc = ensure_maps(h, n_maps);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(casim_launch_pack_map(h, static_map, n_maps, s));
+  CK(casim_launch_map_derive(h, n_maps, nullptr, s));
+  h->n_maps = n_maps;
+  return 0;
+}
+
+int casim_set_trajectories(casim_handle* h, const float* traj, int T) {
+  REQUIRE(h, "null handle");
+  REQUIRE((traj == nullptr) == (T == 0), "traj and T must both be set or both be empty");
+  h->traj = traj;
+  h->T = T;
+  return 0;
+}
+
+static int check_obs(const casim_handle* h, const casim_obs* obs) {
+  REQUIRE(obs, "null casim_obs");
+  (void)h;
+  return 0;
+}
+
+static int run_sensors(casim_handle* h, const float* state, const casim_obs* obs, cudaStream_t s) {
+  if (obs->laserscan) CK(casim_launch_laser(h, state, obs->laserscan, s));
+  if (obs->local_grid) CK(casim_launch_grid(h, state, obs->local_grid, s));
+  return 0;
+}
+
+int casim_reset(casim_handle* h, float* state, const float* init, const int32_t* type, const int32_t* n_agents,
+                const casim_obs* obs, void* stream) {
+  REQUIRE(h && state && init && type, "null argument");
+  int rc = check_obs(h, obs);
+  if (rc) return rc;
+  h->init = init;
+  h->type0 = type;
+  h->n_agents = n_agents;
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(casim_launch_core(h, CASIM_MODE_RESET, state, nullptr, nullptr, h->cfg.dt, obs, s));
+  return run_sensors(h, state, obs, s);
+}
+
+int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, void* stream) {
+  REQUIRE(h && state, "null argument");
+  int rc = check_obs(h, obs);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(casim_launch_core(h, CASIM_MODE_OBSERVE, const_cast<float*>(state), nullptr, nullptr, h->cfg.dt, obs, s));
+  return run_sensors(h, state, obs, s);
+}
+
+int casim_step(casim_handle* h, float* state, const float* ext_actions, const float* policy_actions, double dt,
+               const casim_obs* obs, void* stream) {
+  REQUIRE(h && state, "null argument");
+  int rc = check_obs(h, obs);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  double dtd = dt > 0 ? dt : h->cfg.dt;
+  CK(casim_launch_core(h, CASIM_MODE_STEP, state, ext_actions, policy_actions, dtd, obs, s));
+  return run_sensors(h, state, obs, s);
+}
+
+int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
+                    const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
+                    void* stream) {
+  REQUIRE(h && state && dev && host, "null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  size_t N = (size_t)h->E * h->A;
+  if (ext_actions_host) {
+    REQUIRE(ext_actions_dev, "ext_actions_dev required with ext_actions_host");
+    CK(cudaMemcpyAsync(ext_actions_dev, ext_actions_host, N * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
+  }
+  int rc = casim_step(h, state, ext_actions_host ? ext_actions_dev : nullptr, policy_actions, dt, dev, s);
+  if (rc) return rc;
+#define D2H(field, bytes)                                                                        \
+  if (host->field) {                                                                             \
+    REQUIRE(dev->field, "host buffer given without its device buffer: " #field);                 \
+    CK(cudaMemcpyAsync(host->field, dev->field, (bytes), cudaMemcpyDeviceToHost, s));            \
+  }
+  D2H(rewards, N * sizeof(float))
+  D2H(done, N)
+  D2H(game_over, (size_t)h->E)
+  D2H(collision_flags, N)
+  D2H(nearest_dist, N * sizeof(float))
+  D2H(stats, CASIM_NUM_STATS * sizeof(float))
+  D2H(obs_misc, N * 4 * sizeof(float))
+  D2H(other_agents_states, N * (size_t)h->dc.rows * 10 * sizeof(float))
+  D2H(laserscan, N * (size_t)h->dc.nb * sizeof(float))
+  D2H(local_grid, N * (size_t)h->dc.submap_w * h->dc.submap_h)
+#undef D2H
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+int casim_explore_step(casim_handle* h, const float* state, const float* other_agents_states, float* belief,
+                       float* policy_actions, float* best_mi, float* cand_mi, unsigned long long* counters,
+                       void* stream) {
+  REQUIRE(h && state && other_agents_states && belief && policy_actions, "null argument");
+  REQUIRE(h->n_maps > 0, "casim_explore_step needs a static map (casim_set_obstacles / casim_set_map)");
+  CK(casim_launch_explore(h, state, other_agents_states, belief, policy_actions, best_mi, cand_mi, counters,
+                          (cudaStream_t)stream));
+  return 0;
+}
+
+int casim_ga3c_set_weights(casim_handle* h, const float* weights_host, int n_params, void* stream) {
+  REQUIRE(h && weights_host, "null argument");
+  REQUIRE(n_params == CASIM_GA3C_NUM_PARAMS, "GA3C-CADRL parameter blob must hold 170764 floats");
+  CK(casim_ga3c_upload(h, weights_host, n_params, (cudaStream_t)stream));
+  return 0;
+}
+
+int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_actions, int32_t* action_idx, float* probs,
+                       float* nn_input, int use_tensor_cores, void* stream) {
+  REQUIRE(h && state && policy_actions, "null argument");
+  REQUIRE(h->ga3c_w, "casim_ga3c_set_weights has not been called");
+  CK(casim_launch_ga3c(h, state, policy_actions, action_idx, probs, nn_input, use_tensor_cores,
+                       (cudaStream_t)stream));
+  return 0;
+}
+
+unsigned long long casim_launch_count(const casim_handle* h) { return h ? h->launches : 0ull; }
+
+} /* extern "C" */

@@ -1,0 +1,89 @@
+/*
+ * casim_internal.h -- shared between the translation units of libcasim.so (not part of the ABI).
+ *
+ * Every kernel receives the derived configuration `DevCfg` BY VALUE (kernel parameter space =
+ * constant bank), so no __constant__ symbol has to be shared across translation units and no
+ * relocatable device code is needed.
+ */
+#ifndef CASIM_INTERNAL_H
+#define CASIM_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../../include/casim.h"
+
+#define CASIM_NUM_SMS_FALLBACK 148
+#define CASIM_PLANE_WORDS (CASIM_MAP_DIM * CASIM_MAP_WORDS) /* 3000 words = 12 000 B per bit plane */
+#define CASIM_NUM_PLANES 4 /* S, S|right, S|down, S|right|down|diag  (OccupancyGrid bilinear footprint) */
+
+/* Derived, device-side view of casim_config (thresholds stay doubles: predicates are fp64). */
+struct DevCfg {
+  double dt, dt_nominal;
+  double r_at_goal, r_coll_agent, r_timeout, r_infeasible, r_coll_wall, r_time_step, r_dist_goal;
+  double r_wiggly, wiggly_thr, r_min, r_max;
+  double close_range, near_goal, max_time_ratio, sensing_horizon, max_heading_change;
+  double map_ox, map_oy; /* (width/2)/cell, (height/2)/cell : Map.py:31-32 */
+  double cell, inv_cell;
+  double laser_max_range, laser_norm;
+  double laser_cos[CASIM_MAX_BEAMS], laser_sin[CASIM_MAX_BEAMS], laser_ang[CASIM_MAX_BEAMS];
+  double laser_r[CASIM_MAX_RANGES];
+  /* exploration */
+  double ig_fov_half, ig_detect_fov_half, ig_range, ig_cell, ig_rocc, ig_remp, ig_tol, ig_pfn, ig_pfp, ig_dt;
+  double ig_det_thresh; /* sqrt(0.5)*cell + tolerance */
+  int nb, nr;
+  int coll_w_static, max_obs, rows, submap_w, submap_h, game_over_mode, auto_reset, ig_dim;
+};
+
+struct casim_handle {
+  casim_config cfg;
+  DevCfg dc;
+  int E, A;
+  int device;
+  int num_sms;
+  /* maps */
+  int n_maps;              /* 0 = no obstacles */
+  uint32_t* map_planes;    /* [n_maps_alloc][4][300][10] bit planes (plane 0 = static_map) */
+  int32_t* edf_d2;         /* [n_maps_alloc][300][300] squared distance (cells^2) to the nearest occupied cell;
+                              edfMap.map[r][c] == sqrt(edf_d2) * cell exactly (information_models/edfMap.py:11-12) */
+  int32_t* edf_scratch;    /* [n_maps_alloc][300][300] column pass */
+  int n_maps_alloc;
+  /* borrowed from the caller (casim_reset / casim_set_trajectories) */
+  const float* init;
+  const int32_t* type0;
+  const int32_t* n_agents;
+  const float* traj;
+  int T;
+  /* scratch */
+  double* pose64;          /* [E*A][4] post-move px, py, heading, radius in fp64 for the sensor kernels */
+  uint8_t* prev_game_over; /* [E] */
+  double* partials;        /* [max_ctas][8] */
+  unsigned int* ticket;    /* last-block counter */
+  int max_ctas;
+  /* GA3C */
+  float* ga3c_w;           /* fp32 parameter blob on the device */
+  void* ga3c_wb;           /* bf16 tiles for the tensor-core path */
+  unsigned long long launches;
+};
+
+/* ---- launchers (host functions defined in the .cu files) ---- */
+enum { CASIM_MODE_STEP = 0, CASIM_MODE_RESET = 1, CASIM_MODE_OBSERVE = 2 };
+
+cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const float* ext_actions,
+                              const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s);
+cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laserscan, cudaStream_t s);
+cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s);
+cudaError_t casim_launch_raster(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps,
+                                int max_rects, cudaStream_t s);
+cudaError_t casim_launch_pack_map(casim_handle* h, const uint8_t* static_map, int n_maps, cudaStream_t s);
+cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_out, cudaStream_t s);
+cudaError_t casim_launch_explore(casim_handle* h, const float* state, const float* oas, float* belief,
+                                 float* policy_actions, float* best_mi, float* cand_mi,
+                                 unsigned long long* counters, cudaStream_t s);
+cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy_actions, int32_t* action_idx,
+                              float* probs, float* nn_input, int use_tc, cudaStream_t s);
+cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_params, cudaStream_t s);
+
+void casim_set_error(const char* fmt, ...);
+
+#endif

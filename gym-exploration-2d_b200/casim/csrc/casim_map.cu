@@ -1,0 +1,158 @@
+/*
+ * casim_map.cu -- static map construction (once per reset, not on the per-step path).
+ *
+ *   k_raster      Map.get_occupancy_grid (Map.py:107-123) + world_coordinates_to_map_indices (Map.py:40-47):
+ *                 axis-aligned rectangles (corner 1 = top-left, corner 3 = bottom-right) -> 300x300 bits.
+ *   k_pack        a ready-made bool raster [n,300,300] -> bits.
+ *   k_derive      the three OR-dilated planes used by the OccupancyGrid kernel (bilinear footprints
+ *                 {S}, {S, right}, {S, down}, {S, right, down, diagonal}) and the optional uint8 copy.
+ *   k_edt_cols / k_edt_rows   edfMap.update (information_models/edfMap.py:11-12): exact Euclidean distance
+ *                 transform of the free space, kept as exact integer squared distances (the kernels take sqrt * cell size in
+ *                 fp64 on the fly, which is what scipy.ndimage.distance_transform_edt * cellSize yields).
+ */
+#include "casim_device.cuh"
+
+namespace {
+
+__global__ void k_raster(DevCfg c, const float* rects, const int32_t* n_rects, int n_maps, int max_rects,
+                         uint32_t* planes) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_maps * CASIM_PLANE_WORDS) return;
+  int m = i / CASIM_PLANE_WORDS, w = i - m * CASIM_PLANE_WORDS;
+  int row = w / CASIM_MAP_WORDS, wc = w - row * CASIM_MAP_WORDS;
+  uint32_t bits = 0;
+  int nrect = min(n_rects[m], max_rects);
+  for (int k = 0; k < nrect; k++) {
+    const float* r = rects + ((size_t)m * max_rects + k) * 4;
+    int r0, c0, r1, c1;
+    world_to_map_div(c, (double)r[0], (double)r[1], r0, c0);
+    world_to_map_div(c, (double)r[2], (double)r[3], r1, c1);
+    if (row < r0 || row > r1) continue;
+    int lo = max(c0, wc * 32), hi = min(min(c1, wc * 32 + 31), CASIM_MAP_DIM - 1);
+    for (int col = lo; col <= hi; col++) bits |= 1u << (col & 31);
+  }
+  planes[(size_t)m * CASIM_NUM_PLANES * CASIM_PLANE_WORDS + w] = bits;
+}
+
+__global__ void k_pack(const uint8_t* maps, int n_maps, uint32_t* planes) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_maps * CASIM_PLANE_WORDS) return;
+  int m = i / CASIM_PLANE_WORDS, w = i - m * CASIM_PLANE_WORDS;
+  int row = w / CASIM_MAP_WORDS, wc = w - row * CASIM_MAP_WORDS;
+  const uint8_t* src = maps + ((size_t)m * CASIM_MAP_DIM + row) * CASIM_MAP_DIM;
+  uint32_t bits = 0;
+  for (int b = 0; b < 32; b++) {
+    int col = wc * 32 + b;
+    if (col < CASIM_MAP_DIM && src[col]) bits |= 1u << b;
+  }
+  planes[(size_t)m * CASIM_NUM_PLANES * CASIM_PLANE_WORDS + w] = bits;
+}
+
+__device__ __forceinline__ uint32_t plane_word(const uint32_t* p0, int row, int wc) {
+  if (row < 0 || row >= CASIM_MAP_DIM || wc < 0 || wc >= CASIM_MAP_WORDS) return 0u;
+  return p0[row * CASIM_MAP_WORDS + wc];
+}
+
+/* word of "S shifted so that bit c holds S(row, c+1)" */
+__device__ __forceinline__ uint32_t right_word(const uint32_t* p0, int row, int wc) {
+  return (plane_word(p0, row, wc) >> 1) | (plane_word(p0, row, wc + 1) << 31);
+}
+
+__global__ void k_derive(int n_maps, uint32_t* planes, uint8_t* map_out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_maps * CASIM_PLANE_WORDS) return;
+  int m = i / CASIM_PLANE_WORDS, w = i - m * CASIM_PLANE_WORDS;
+  int row = w / CASIM_MAP_WORDS, wc = w - row * CASIM_MAP_WORDS;
+  uint32_t* base = planes + (size_t)m * CASIM_NUM_PLANES * CASIM_PLANE_WORDS;
+  const uint32_t* p0 = base;
+  uint32_t colmask = (wc == CASIM_MAP_WORDS - 1) ? ((1u << (CASIM_MAP_DIM - 32 * (CASIM_MAP_WORDS - 1))) - 1u) : 0xffffffffu;
+  uint32_t s = plane_word(p0, row, wc);
+  uint32_t r = right_word(p0, row, wc);
+  uint32_t d = plane_word(p0, row + 1, wc);
+  uint32_t dr = right_word(p0, row + 1, wc);
+  base[1 * CASIM_PLANE_WORDS + w] = (s | r) & colmask;
+  base[2 * CASIM_PLANE_WORDS + w] = (s | d) & colmask;
+  base[3 * CASIM_PLANE_WORDS + w] = (s | r | d | dr) & colmask;
+  if (map_out) {
+    uint8_t* dst = map_out + ((size_t)m * CASIM_MAP_DIM + row) * CASIM_MAP_DIM;
+    for (int b = 0; b < 32; b++) {
+      int col = wc * 32 + b;
+      if (col < CASIM_MAP_DIM) dst[col] = (s >> b) & 1u;
+    }
+  }
+}
+
+/* pass 1: per column, distance (in cells) to the nearest occupied cell in that column (big = none) */
+__global__ void k_edt_cols(int n_maps, const uint32_t* planes, int* gdist) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_maps * CASIM_MAP_DIM) return;
+  int m = i / CASIM_MAP_DIM, col = i - m * CASIM_MAP_DIM;
+  const uint32_t* p0 = planes + (size_t)m * CASIM_NUM_PLANES * CASIM_PLANE_WORDS;
+  int* g = gdist + (size_t)m * CASIM_MAP_DIM * CASIM_MAP_DIM;
+  const int BIG = 1 << 20;
+  int d = BIG;
+  for (int row = 0; row < CASIM_MAP_DIM; row++) {
+    bool occ = (p0[row * CASIM_MAP_WORDS + (col >> 5)] >> (col & 31)) & 1u;
+    d = occ ? 0 : min(d + 1, BIG);
+    g[row * CASIM_MAP_DIM + col] = d;
+  }
+  d = BIG;
+  for (int row = CASIM_MAP_DIM - 1; row >= 0; row--) {
+    bool occ = (p0[row * CASIM_MAP_WORDS + (col >> 5)] >> (col & 31)) & 1u;
+    d = occ ? 0 : min(d + 1, BIG);
+    g[row * CASIM_MAP_DIM + col] = min(g[row * CASIM_MAP_DIM + col], d);
+  }
+}
+
+/* pass 2: exact minimum over the row of dx^2 + g^2 (300 candidates per cell), sqrt, * cell */
+__global__ void k_edt_rows(int n_maps, const int* gdist, int32_t* edf_d2) {
+  __shared__ int sg[CASIM_MAP_DIM];
+  int m = blockIdx.x / CASIM_MAP_DIM, row = blockIdx.x - m * CASIM_MAP_DIM;
+  const int* g = gdist + ((size_t)m * CASIM_MAP_DIM + row) * CASIM_MAP_DIM;
+  for (int k = threadIdx.x; k < CASIM_MAP_DIM; k += blockDim.x) sg[k] = g[k];
+  __syncthreads();
+  const int BIG = 1 << 20;
+  for (int col = threadIdx.x; col < CASIM_MAP_DIM; col += blockDim.x) {
+    long long best = -1;
+    for (int k = 0; k < CASIM_MAP_DIM; k++) {
+      int gv = sg[k];
+      if (gv >= BIG) continue;
+      long long dx = col - k;
+      long long v = dx * dx + (long long)gv * gv;
+      if (best < 0 || v < best) best = v;
+    }
+    /* no obstacle anywhere: scipy returns the distance to a non-existent background; the exploration
+     * kernels are only used with obstacles, keep a large finite value */
+    size_t o = ((size_t)m * CASIM_MAP_DIM + row) * CASIM_MAP_DIM + col;
+    edf_d2[o] = best < 0 ? (1 << 30) : (int32_t)best;
+  }
+}
+
+}  // namespace
+
+cudaError_t casim_launch_raster(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps,
+                                int max_rects, cudaStream_t s) {
+  int total = n_maps * CASIM_PLANE_WORDS;
+  h->launches++;
+  k_raster<<<(total + 255) / 256, 256, 0, s>>>(h->dc, rects, n_rects, n_maps, max_rects, h->map_planes);
+  return cudaGetLastError();
+}
+
+cudaError_t casim_launch_pack_map(casim_handle* h, const uint8_t* static_map, int n_maps, cudaStream_t s) {
+  int total = n_maps * CASIM_PLANE_WORDS;
+  h->launches++;
+  k_pack<<<(total + 255) / 256, 256, 0, s>>>(static_map, n_maps, h->map_planes);
+  return cudaGetLastError();
+}
+
+cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_out, cudaStream_t s) {
+  int total = n_maps * CASIM_PLANE_WORDS;
+  h->launches += 3;
+  k_derive<<<(total + 255) / 256, 256, 0, s>>>(n_maps, h->map_planes, map_out);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return err;
+  int* gdist = h->edf_scratch;
+  k_edt_cols<<<(n_maps * CASIM_MAP_DIM + 127) / 128, 128, 0, s>>>(n_maps, h->map_planes, gdist);
+  k_edt_rows<<<n_maps * CASIM_MAP_DIM, 128, 0, s>>>(n_maps, gdist, h->edf_d2);
+  return cudaGetLastError();
+}

@@ -1,0 +1,245 @@
+/*
+ * casim_sensors.cu -- LaserScanSensor and OccupancyGridSensor kernels.
+ *
+ *   k_laser : sensors/LaserScanSensor.py:27-58 (+ Map.py:49-59 lattice -> cell indices, Map.py:73-79 ego disc).
+ *             One warp per agent ("ray fan"): lanes split the beams x range-samples lattice, each lane builds
+ *             a hit bit-mask for its part of a beam, masks are OR-combined with shuffles, and the
+ *             "last sample whose running hit count is 1" rule is evaluated with bit tricks.
+ *   k_grid  : sensors/OccupancyGridSensor.py:70-98,131-143 + Map.py:81-105 + cv2.getRotationMatrix2D /
+ *             cv2.warpAffine (bilinear, zero border) restated in OpenCV's fixed point (AB_BITS 10, INTER_BITS 5).
+ *             Because the result is cast to bool, a destination cell is the OR of the source cells with a
+ *             non-zero bilinear weight; the four possible footprints are precomputed as bit planes
+ *             (casim_map.cu), so a cell is ONE bit lookup.
+ *
+ * Both read the fp64 post-move pose scratch written by the step kernel (pose64), so that their cell
+ * indices are computed from the same float64 numbers the reference would use inside one step.
+ */
+#include "casim_device.cuh"
+
+namespace {
+
+struct LaserArgs {
+  DevCfg c;
+  const float4* state;
+  const double* pose64;
+  const int32_t* n_agents;
+  const uint32_t* map_planes;
+  float* out;
+  int E, A, n_maps;
+};
+
+__global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
+  const DevCfg& c = p.c;
+  const int lane = threadIdx.x & 31;
+  const long long g = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long N = (long long)p.E * p.A;
+  if (g >= N) return;
+  const int e = (int)(g / p.A), ai = (int)(g - (long long)e * p.A);
+  const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+  const int nb = c.nb, nr = c.nr;
+  float* out = p.out + g * nb;
+  const int type = __float_as_int(p.state[5 * N + g].w);
+  const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_LASERSCAN);
+  if (!on) {
+    for (int b = lane; b < nb; b += 32) out[b] = 0.f;
+    return;
+  }
+  const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[0];
+  const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[1];
+  const double px = q0.x, py = q0.y, heading = q1.x, radius = q1.y;
+  const uint32_t* pl =
+      p.n_maps > 0 ? p.map_planes + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_NUM_PLANES * CASIM_PLANE_WORDS : nullptr;
+  int r0, c0;
+  const bool ego_in = world_to_map_div(c, px, py, r0, c0);
+  const double rc = radius / c.cell, rc2 = rc * rc;
+  /* lanes per beam: 32 / next_pow2(nb) */
+  int nbp = 1;
+  while (nbp < nb) nbp <<= 1;
+  const int P = 32 / nbp; /* nb <= 32 */
+  const int b = lane / P, part = lane - b * P;
+  unsigned mask = 0;
+  if (b < nb && pl) {
+    double sn, cs;
+    sincos(c.laser_ang[b] + heading, &sn, &cs);
+    for (int k = part; k < nr; k += P) {
+      double x = px + c.laser_r[k] * cs, y = py + c.laser_r[k] * sn;
+      int row, col;
+      if (world_to_map_mul(c, x, y, row, col) && map_bit(pl, row, col)) {
+        bool ego = ego_in && in_disc(row, col, r0, c0, rc2);
+        if (!ego) mask |= 1u << k;
+      }
+    }
+  }
+  for (int o = 1; o < P; o <<= 1) mask |= __shfl_xor_sync(FULL_MASK, mask, o);
+  if (b < nb && part == 0) {
+    double range = c.laser_max_range;
+    if (mask) {
+      unsigned rest = mask & (mask - 1); /* drop the first hit */
+      int idx = rest ? (__ffs(rest) - 2) : (nr - 1);
+      range = c.laser_r[idx];
+    }
+    out[b] = (float)(1.0 - range / c.laser_norm);
+  }
+}
+
+/* ------------------------------------------------------------------------------------------------ */
+struct GridArgs {
+  DevCfg c;
+  const float4* state;
+  const double* pose64;
+  const int32_t* n_agents;
+  const uint32_t* map_planes;
+  uint8_t* out;
+  int E, A, n_maps;
+};
+
+/* One CTA per agent: warps 0-1 build the per-row / per-column fixed-point tables in fp64, then every thread
+ * produces 4-cell output words with integer arithmetic and one bit lookup per cell. */
+__global__ void __launch_bounds__(256) k_grid(const GridArgs p) {
+  const DevCfg& c = p.c;
+  const long long g = blockIdx.x;
+  const long long N = (long long)p.E * p.A;
+  const int e = (int)(g / p.A), ai = (int)(g - (long long)e * p.A);
+  const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+  const int H = c.submap_h, W = c.submap_w; /* out[oy*H + ox], oy < W rows, ox < H cols */
+  const int cells = H * W;
+  uint8_t* out = p.out + g * cells;
+  const int type = __float_as_int(p.state[5 * N + g].w);
+  const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_OCCUPANCY_GRID) && p.n_maps > 0;
+  __shared__ int sX0[128], sY0[128], sAd[128], sBd[128];
+  __shared__ int s_geom[4];
+  if (!on) {
+    if ((cells & 3) == 0 && (((uintptr_t)out) & 3) == 0)
+      for (int i = threadIdx.x; i < (cells >> 2); i += blockDim.x) reinterpret_cast<uint32_t*>(out)[i] = 0u;
+    else
+      for (int i = threadIdx.x; i < cells; i += blockDim.x) out[i] = 0;
+    return;
+  }
+  const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[0];
+  const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[1];
+  const double px = q0.x, py = q0.y, heading = q1.x;
+  int row0, col0;
+  world_to_map_div(c, px, py, row0, col0);
+  /* Map.getSubmapByIndices (Map.py:81-105) */
+  int sx = max(row0 - W / 2, 0), sy = max(col0 - H / 2, 0);
+  int ex = sx + W, ey = sy + H;
+  if (ex > CASIM_MAP_DIM - 1) {
+    ex = CASIM_MAP_DIM - 1;
+    sx = ex - W;
+  }
+  if (ey > CASIM_MAP_DIM - 1) {
+    ey = CASIM_MAP_DIM - 1;
+    sy = ey - H;
+  }
+  const int nrows = min(ex - sx, W), ncols = min(ey - sy, H);
+  if (threadIdx.x < 128) {
+    /* cv2.getRotationMatrix2D(center=(col0,row0), angle=-heading*180/pi, 1) then warpAffine's inversion */
+    double angle_deg = -heading * 180 / CASIM_PI;
+    double ang = angle_deg * (CASIM_PI / 180);
+    double beta, alpha;
+    sincos(ang, &beta, &alpha);
+    double cx = (double)(float)col0, cy = (double)(float)row0;
+    double M0 = alpha, M1 = beta, M2 = (1 - alpha) * cx - beta * cy;
+    double M3 = -beta, M4 = alpha, M5 = beta * cx + (1 - alpha) * cy;
+    double D = M0 * M4 - M1 * M3;
+    D = D != 0 ? 1. / D : 0;
+    double A11 = M4 * D, A22 = M0 * D;
+    M0 = A11;
+    M1 *= -D;
+    M3 *= -D;
+    M4 = A22;
+    double b1 = -M0 * M2 - M1 * M5;
+    double b2 = -M3 * M2 - M4 * M5;
+    M2 = b1;
+    M5 = b2;
+    int t = threadIdx.x;
+    if (t < 64) {
+      if (t < nrows) {
+        int y = sx + t;
+        sX0[t] = __double2int_rn((M1 * y + M2) * 1024) + 16;
+        sY0[t] = __double2int_rn((M4 * y + M5) * 1024) + 16;
+      }
+    } else {
+      t -= 64;
+      if (t < ncols) {
+        int x = sy + t;
+        sAd[t] = __double2int_rn(M0 * x * 1024);
+        sBd[t] = __double2int_rn(M3 * x * 1024);
+      }
+    }
+  }
+  __syncthreads();
+  const uint32_t* pl = p.map_planes + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_NUM_PLANES * CASIM_PLANE_WORDS;
+  const bool vec = (H & 3) == 0 && (((uintptr_t)out) & 3) == 0;
+  const int wpr = vec ? (H >> 2) : H; /* output words (or bytes) per row */
+  const int step = vec ? 4 : 1;
+  for (int i = threadIdx.x; i < W * wpr; i += blockDim.x) {
+    int oy = i / wpr, ox0 = (i - oy * wpr) * step;
+    uint32_t word = 0;
+#pragma unroll 4
+    for (int k = 0; k < step; k++) {
+      int ox = ox0 + k;
+      int v = 0;
+      if (oy < nrows && ox < ncols) {
+        int X = (sX0[oy] + sAd[ox]) >> 5, Y = (sY0[oy] + sBd[ox]) >> 5;
+        int sxi = X >> 5, syi = Y >> 5, fx = X & 31, fy = Y & 31;
+        if (sxi >= 0 && sxi < CASIM_MAP_DIM && syi >= 0 && syi < CASIM_MAP_DIM) {
+          int plane = (fx > 0 ? 1 : 0) + (fy > 0 ? 2 : 0);
+          v = map_bit(pl + plane * CASIM_PLANE_WORDS, syi, sxi);
+        } else { /* border: the footprint may still reach into the map from outside */
+          auto S = [&](int r, int cc) -> int {
+            return (r >= 0 && r < CASIM_MAP_DIM && cc >= 0 && cc < CASIM_MAP_DIM) ? map_bit(pl, r, cc) : 0;
+          };
+          v = S(syi, sxi);
+          if (fx > 0) v |= S(syi, sxi + 1);
+          if (fy > 0) v |= S(syi + 1, sxi);
+          if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
+        }
+      }
+      word |= (uint32_t)v << (8 * k);
+    }
+    if (vec)
+      reinterpret_cast<uint32_t*>(out)[i] = word;
+    else
+      out[i] = (uint8_t)word;
+  }
+}
+
+}  // namespace
+
+cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laserscan, cudaStream_t s) {
+  LaserArgs a;
+  a.c = h->dc;
+  a.state = reinterpret_cast<const float4*>(state);
+  a.pose64 = h->pose64;
+  a.n_agents = h->n_agents;
+  a.map_planes = h->map_planes;
+  a.n_maps = h->n_maps;
+  a.out = laserscan;
+  a.E = h->E;
+  a.A = h->A;
+  long long N = (long long)h->E * h->A;
+  int wpc = 8;
+  dim3 grid((unsigned)((N + wpc - 1) / wpc)), block(32 * wpc);
+  h->launches++;
+  k_laser<<<grid, block, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s) {
+  if (h->dc.submap_w > 64 || h->dc.submap_h > 64) return cudaErrorInvalidValue;
+  GridArgs a;
+  a.c = h->dc;
+  a.state = reinterpret_cast<const float4*>(state);
+  a.pose64 = h->pose64;
+  a.n_agents = h->n_agents;
+  a.map_planes = h->map_planes;
+  a.n_maps = h->n_maps;
+  a.out = local_grid;
+  a.E = h->E;
+  a.A = h->A;
+  long long N = (long long)h->E * h->A;
+  h->launches++;
+  k_grid<<<(unsigned)N, 256, 0, s>>>(a);
+  return cudaGetLastError();
+}

@@ -1,0 +1,613 @@
+/*
+ * casim_step.cu -- the fused environment-step kernel.
+ *
+ * One launch does, for every environment of the shard (citations relative to
+ * gym_collision_avoidance/envs/ of mlodel/gym-exploration-2d):
+ *   _take_action            collision_avoidance_env.py:287-340   in-kernel policies, fp32 action rounding
+ *   Agent.take_action       agent.py:147-190                     finished branch, dynamics, goal/time budget
+ *   Dynamics.step           dynamics/{Unicycle,FirstOrder,UnicycleDynamicsMaxTurnRate,External}Dynamics.py
+ *   update_ego_frame        dynamics/Dynamics.py:14-28 + agent.py:250-269
+ *   _check_for_collisions   collision_avoidance_env.py:630-671   all pairs + wall disc
+ *   _compute_rewards        collision_avoidance_env.py:502-567
+ *   OtherAgentsStatesSensor sensors/OtherAgentsStatesSensor.py:11-77   ego transform + closest-N ordering
+ *   _check_which_agents_done collision_avoidance_env.py:711-738
+ *   + per-step episode statistics for the shard (last-block reduction, no atomics on the data path).
+ *
+ * Thread mapping: one lane per agent; a warp holds floor(32/A) whole environments, so lane L of warp w
+ * is element (w*epw*A + L) of every [E,A] array: all state loads/stores are contiguous float4 per warp.
+ * Agents of an environment exchange their post-move pose with warp shuffles (no shared memory, no
+ * barrier).  Every decision predicate is evaluated in fp64 on the fp32 state, like the float64
+ * reference; state is stored back as fp32.  The observation rows are staged in shared memory and
+ * written out as contiguous 16-byte stores.
+ */
+#include <stdio.h>
+
+#include "casim_device.cuh"
+
+namespace {
+
+struct CoreArgs {
+  DevCfg c;
+  float4* state;               /* [6][E*A] float4 */
+  const float* ext_actions;    /* [E*A][2] or NULL */
+  const float* policy_actions; /* [E*A][2] or NULL */
+  const float* traj;           /* [E*A][T][4] or NULL */
+  const float* init;           /* [E*A][7] */
+  const int32_t* type0;        /* [E*A] */
+  const int32_t* n_agents;     /* [E] or NULL */
+  const uint32_t* map_planes;  /* [n_maps][4][300][10] or NULL */
+  uint8_t* prev_game_over;     /* [E] */
+  double* pose64;              /* [E*A][4] or NULL */
+  double* partials;            /* [ctas][8] */
+  unsigned int* ticket;
+  casim_obs o;
+  double dt;
+  int E, A, T, n_maps, epw, write_pose;
+};
+
+struct Agent {
+  double px, py, heading, speed;
+  double vx, vy, dheading, turning;
+  double gx, gy, radius, pref;
+  double t, trem, dgoal, pdgoal;
+  double a0v, a0w, a1v, a1w;
+  double hego;
+  int step_num, flags, type;
+};
+
+__device__ __forceinline__ void load_agent(const float4* st, size_t plane, size_t g, Agent& a) {
+  float4 p0 = st[g], p1 = st[plane + g], p2 = st[2 * plane + g], p3 = st[3 * plane + g],
+         p4 = st[4 * plane + g], p5 = st[5 * plane + g];
+  a.px = p0.x; a.py = p0.y; a.heading = p0.z; a.speed = p0.w;
+  a.vx = p1.x; a.vy = p1.y; a.dheading = p1.z; a.turning = p1.w;
+  a.gx = p2.x; a.gy = p2.y; a.radius = p2.z; a.pref = p2.w;
+  a.t = p3.x; a.trem = p3.y; a.dgoal = p3.z; a.pdgoal = p3.w;
+  a.a0v = p4.x; a.a0w = p4.y; a.a1v = p4.z; a.a1w = p4.w;
+  a.hego = p5.x;
+  a.step_num = __float_as_int(p5.y);
+  a.flags = __float_as_int(p5.z);
+  a.type = __float_as_int(p5.w);
+}
+
+__device__ __forceinline__ void store_agent(float4* st, size_t plane, size_t g, const Agent& a, bool all) {
+  st[g] = make_float4((float)a.px, (float)a.py, (float)a.heading, (float)a.speed);
+  st[plane + g] = make_float4((float)a.vx, (float)a.vy, (float)a.dheading, (float)a.turning);
+  if (all) st[2 * plane + g] = make_float4((float)a.gx, (float)a.gy, (float)a.radius, (float)a.pref);
+  st[3 * plane + g] = make_float4((float)a.t, (float)a.trem, (float)a.dgoal, (float)a.pdgoal);
+  st[4 * plane + g] = make_float4((float)a.a0v, (float)a.a0w, (float)a.a1v, (float)a.a1w);
+  st[5 * plane + g] = make_float4((float)a.hego, __int_as_float(a.step_num), __int_as_float(a.flags),
+                                  __int_as_float(a.type));
+}
+
+/* agent.py:250-269 get_ref */
+__device__ __forceinline__ void ref_axes(const Agent& a, double& p0, double& p1, double& dist) {
+  double gdx = a.gx - a.px, gdy = a.gy - a.py;
+  dist = sqrt(gdx * gdx + gdy * gdy);
+  if (dist > 1e-8) {
+    p0 = gdx / dist;
+    p1 = gdy / dist;
+  } else {
+    p0 = gdx;
+    p1 = gdy;
+  }
+}
+
+/* dynamics/Dynamics.py:14-28 update_ego_frame */
+__device__ __forceinline__ void update_ego_frame(Agent& a) {
+  double p0, p1, dist;
+  ref_axes(a, p0, p1, dist);
+  a.pdgoal = a.dgoal;
+  a.dgoal = dist;
+  if (a.t == 0.0) a.pdgoal = dist;
+  a.hego = wrap_pi(a.heading - atan2(p1, p0));
+}
+
+/* agent.py:9-112 Agent.__init__ */
+__device__ __forceinline__ void agent_init(const DevCfg& c, const float* in, int type, Agent& a) {
+  double sx = in[0], sy = in[1], gx = in[2], gy = in[3], radius = in[4], pref = in[5];
+  float h = in[6];
+  a.px = sx; a.py = sy; a.gx = gx; a.gy = gy; a.radius = radius; a.pref = pref;
+  a.heading = isnan(h) ? atan2(gy - sy, gx - sx) : (double)h;
+  a.speed = 0; a.vx = 0; a.vy = 0; a.dheading = 0; a.turning = 0;
+  a.t = 0; a.dgoal = 0; a.pdgoal = 0; a.a0v = a.a0w = a.a1v = a.a1w = 0; a.hego = 0;
+  a.step_num = 0; a.flags = 0; a.type = type;
+  double dx = sx - gx, dy = sy - gy;
+  double straight = (sqrt(dx * dx + dy * dy) - c.near_goal) / pref;
+  a.trem = c.max_time_ratio * straight;
+  update_ego_frame(a);
+}
+
+/* collision_avoidance_env.py:298-320: the action each policy contributes, rounded to fp32 (:289) */
+__device__ __forceinline__ void choose_action(const DevCfg& c, const Agent& a, const float* ext, const float* pol,
+                                              size_t g, float& a0, float& a1) {
+  a0 = 0.f;
+  a1 = 0.f;
+  if (a.flags & CASIM_F_IS_DONE) return;
+  switch (a.type & 0xff) {
+    case CASIM_POLICY_NONCOOPERATIVE: /* NonCooperativePolicy.py:10-13 */
+      a0 = (float)a.pref;
+      a1 = (float)(-a.hego);
+      break;
+    case CASIM_POLICY_EXTERNAL:
+      if (ext) {
+        a0 = ext[2 * g];
+        a1 = ext[2 * g + 1];
+      }
+      break;
+    case CASIM_POLICY_LEARNING: /* LearningPolicy.py:11-16 */
+      if (ext) {
+        double heading = c.max_heading_change * (2. * (double)ext[2 * g + 1] - 1.);
+        double speed = a.pref * (double)ext[2 * g];
+        a0 = (float)speed;
+        a1 = (float)heading;
+      }
+      break;
+    case CASIM_POLICY_CARRL: /* CARRLPolicy.py:7-15 */
+      if (ext) {
+        int k = (int)ext[2 * g];
+        if (k < 0) k += 11;
+        k = min(max(k, 0), 10);
+        const double mh = CASIM_PI / 6;
+        double step = (mh - (-mh)) / 10.0;
+        double w = (k == 10) ? mh : (double)k * step + (-mh);
+        a0 = 1.0f;
+        a1 = (float)w;
+      }
+      break;
+    case CASIM_POLICY_IG_GREEDY:
+    case CASIM_POLICY_GA3C_CADRL:
+      if (pol) {
+        a0 = pol[2 * g];
+        a1 = pol[2 * g + 1];
+      }
+      break;
+    default: /* Static, PedestrianDataset: zeros */
+      break;
+  }
+}
+
+__device__ __forceinline__ void dynamics_step(const DevCfg& c, Agent& a, float a0, float a1, double dt,
+                                              const float* traj, int T, size_t g) {
+  int dyn = (a.type >> 8) & 0xff;
+  if (dyn == CASIM_DYN_EXTERNAL) { /* ExternalDynamics.py:8-23 + agent.py:125-145 */
+    if (!traj || T <= 0) return;
+    int k = a.step_num < T - 1 ? a.step_num : T - 1;
+    float4 row = *reinterpret_cast<const float4*>(traj + (g * (size_t)T + k) * 4);
+    double heading = atan2((double)row.z, (double)row.w) - a.heading; /* x/y swapped, sic */
+    double px = row.x, py = row.y;
+    if (a.step_num == 0) {
+      a.vx = 0;
+      a.vy = 0;
+    } else {
+      a.vx = (px - a.px) / c.dt_nominal;
+      a.vy = (py - a.py) / c.dt_nominal;
+    }
+    a.dheading = wrap_pi(heading - a.heading);
+    a.px = px;
+    a.py = py;
+    a.speed = sqrt(a.vx * a.vx + a.vy * a.vy);
+    a.heading = heading;
+    return;
+  }
+  double speed = (double)a0, sel;
+  if (dyn == CASIM_DYN_FIRST_ORDER) /* FirstOrderDynamics.py:10-23 */
+    sel = wrap_pi((double)a1 * dt + a.heading);
+  else if (dyn == CASIM_DYN_UNICYCLE_MAX_TURN_RATE) { /* UnicycleDynamicsMaxTurnRate.py:11-26 */
+    double rate = (double)a1 / dt;
+    rate = fmin(fmax(rate, -3.0), 3.0);
+    sel = wrap_pi(rate * dt + a.heading);
+  } else /* UnicycleDynamics.py:10-31 */
+    sel = wrap_pi((double)a1 + a.heading);
+  double sn, cs;
+  sincos(sel, &sn, &cs);
+  a.px += speed * cs * dt;
+  a.py += speed * sn * dt;
+  a.vx = speed * cs;
+  a.vy = speed * sn;
+  a.speed = speed;
+  a.dheading = wrap_pi(sel - a.heading);
+  a.heading = sel;
+  if (dyn == CASIM_DYN_UNICYCLE) {
+    double td = a.turning;
+    if (fabs(td) < 1e-5)
+      td = 0.11 * sgn_d(sel);
+    else if (td * sel < 0)
+      td = fmax(-CASIM_PI, fmin(CASIM_PI, -td + sel));
+    else
+      td = sgn_d(td) * fmax(0.0, fabs(td) - 0.1);
+    a.turning = td;
+  }
+}
+
+/* agent.py:147-190 */
+__device__ __forceinline__ void take_action(const DevCfg& c, Agent& a, float a0, float a1, double dt,
+                                            const float* traj, int T, size_t g) {
+  int flags = a.flags;
+  if (flags & (CASIM_F_IS_AT_GOAL | CASIM_F_RAN_OUT_OF_TIME | CASIM_F_IN_COLLISION)) {
+    if (flags & CASIM_F_IS_AT_GOAL) flags |= CASIM_F_WAS_AT_GOAL_ALREADY;
+    if (flags & CASIM_F_IN_COLLISION) flags |= CASIM_F_WAS_IN_COLLISION_ALREADY;
+    if (!(flags & CASIM_F_IS_AT_GOAL)) a.t += dt;
+    a.vx = 0;
+    a.vy = 0;
+    a.flags = flags;
+    return;
+  }
+  a.a1v = a.a0v;
+  a.a1w = a.a0w;
+  a.a0v = (double)a0;
+  a.a0w = (double)a1;
+  dynamics_step(c, a, a0, a1, dt, traj, T, g);
+  update_ego_frame(a);
+  double ex = a.px - a.gx, ey = a.py - a.gy;
+  if (ex * ex + ey * ey <= c.near_goal * c.near_goal)
+    flags |= CASIM_F_IS_AT_GOAL;
+  else
+    flags &= ~CASIM_F_IS_AT_GOAL;
+  a.trem -= dt;
+  a.t += dt;
+  a.step_num += 1;
+  if (a.trem <= 0.0) flags |= CASIM_F_RAN_OUT_OF_TIME;
+  a.flags = flags;
+}
+
+template <int MODE, int AP>
+__global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
+  extern __shared__ __align__(16) float s_stage[];
+  __shared__ double s_part[4][CASIM_NUM_STATS];
+  __shared__ bool s_last;
+  const DevCfg& c = p.c;
+  const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
+  const int warps_per_cta = blockDim.x >> 5;
+  const int w = blockIdx.x * warps_per_cta + warp_in_cta;
+  const int A = p.A, epw = p.epw;
+  const int le = lane / A, ai = lane - le * A;
+  const int env0 = w * epw;
+  const int e = env0 + le;
+  const bool slot = le < epw && e < p.E; /* lane maps to an [E,A] element */
+  const int n = slot ? (p.n_agents ? min(p.n_agents[e], A) : A) : 0;
+  const bool valid = slot && ai < n;
+  const int base = le * A; /* first lane of my environment */
+  const size_t plane = (size_t)p.E * A;
+  const size_t g = (size_t)env0 * A + lane;
+
+  Agent a;
+  int old_flags = 0;
+  bool wrote_all = false;
+  if (valid) {
+    if (MODE == CASIM_MODE_RESET) {
+      agent_init(c, p.init + g * 7, p.type0[g], a);
+      wrote_all = true;
+    } else {
+      load_agent(p.state, plane, g, a);
+      if (MODE == CASIM_MODE_STEP && c.auto_reset && p.init && p.prev_game_over[e]) {
+        agent_init(c, p.init + g * 7, p.type0[g], a);
+        wrote_all = true;
+      }
+    }
+  } else {
+    a = Agent();
+    a.px = a.py = a.heading = a.speed = a.vx = a.vy = a.dheading = a.turning = a.gx = a.gy = a.radius = a.pref =
+        a.t = a.trem = a.dgoal = a.pdgoal = a.a0v = a.a0w = a.a1v = a.a1w = a.hego = 0;
+    a.step_num = a.flags = a.type = 0;
+  }
+
+  if (MODE == CASIM_MODE_STEP && valid) {
+    old_flags = a.flags;
+    float a0, a1;
+    choose_action(c, a, p.ext_actions, p.policy_actions, g, a0, a1);
+    take_action(c, a, a0, a1, p.dt, p.traj, p.T, g);
+  }
+
+  /* ---- all pairs of my environment: distances to every other agent (registers, static indexing) ---- */
+  const bool me_static = (a.type & 0xff) == CASIM_POLICY_STATIC;
+  const int sensors = (a.type >> 16) & 0xff;
+  const bool want_oas = p.o.other_agents_states != nullptr;
+  double dist[AP];
+  bool coll_agent = false;
+  double nearest = INFINITY;
+#pragma unroll
+  for (int j = 0; j < AP; j++) {
+    int src = (base + j) & 31;
+    double ox = __shfl_sync(FULL_MASK, a.px, src), oy = __shfl_sync(FULL_MASK, a.py, src);
+    float orad = __shfl_sync(FULL_MASK, (float)a.radius, src);
+    int ostatic = __shfl_sync(FULL_MASK, (int)me_static, src);
+    double dx = a.px - ox, dy = a.py - oy;
+    double d = sqrt(dx * dx + dy * dy);
+    dist[j] = d;
+    if (MODE == CASIM_MODE_STEP && valid && j < n && j != ai) {
+      /* pair (lo, hi): skipped when the HIGHER index is Static (collision_avoidance_env.py:643-644) */
+      bool hi_static = j > ai ? (ostatic != 0) : me_static;
+      if (!(hi_static && !c.coll_w_static)) {
+        double cr = j > ai ? a.radius + (double)orad : (double)orad + a.radius;
+        if (j > ai) nearest = fmin(nearest, d - cr); /* :649 lower index only */
+        if (d <= cr) coll_agent = true;
+      }
+    }
+  }
+
+  bool coll_wall = false;
+  float reward = 0.f;
+  bool done = false;
+  double st_new_coll = 0, st_new_goal = 0, st_new_to = 0, st_rew = 0, st_active = 0, st_agents = 0, st_go = 0;
+  if (MODE == CASIM_MODE_STEP) {
+    if (valid && p.n_maps > 0) { /* :656-666 */
+      const uint32_t* pl = p.map_planes + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_NUM_PLANES * CASIM_PLANE_WORDS;
+      int r0, c0;
+      if (world_to_map_div(c, a.px, a.py, r0, c0)) coll_wall = disc_hits_map(c, pl, r0, c0, a.radius);
+    }
+    if (valid) { /* _compute_rewards :502-567 */
+      int flags = a.flags;
+      double r = c.r_time_step;
+      if (flags & CASIM_F_IS_AT_GOAL) {
+        if (!(flags & CASIM_F_WAS_AT_GOAL_ALREADY)) r = c.r_at_goal;
+      } else {
+        if (!(flags & CASIM_F_WAS_IN_COLLISION_ALREADY)) {
+          if (coll_agent) {
+            r = c.r_coll_agent;
+            flags |= CASIM_F_IN_COLLISION;
+          } else if (coll_wall) {
+            r = c.r_coll_wall;
+            flags |= CASIM_F_IN_COLLISION;
+          } else {
+            if (nearest <= c.close_range) r += -0.1 - nearest / 2.;
+            double wv = a.a1v - a.a0v, ww = a.a1w - a.a0w;
+            if (sqrt(wv * wv + ww * ww) > c.wiggly_thr) r += c.r_wiggly;
+          }
+        } else if (flags & CASIM_F_RAN_OUT_OF_TIME)
+          r += c.r_timeout;
+        if (flags & CASIM_F_IS_INFEASIBLE) r += c.r_infeasible;
+        r += c.r_dist_goal * (a.pdgoal - a.dgoal);
+      }
+      r = fmin(fmax(r, c.r_min), c.r_max);
+      r = r / (c.r_max - c.r_min);
+      /* _check_which_agents_done :711-720 */
+      done = (flags & (CASIM_F_IS_AT_GOAL | CASIM_F_RAN_OUT_OF_TIME | CASIM_F_IN_COLLISION)) != 0;
+      if (done)
+        flags |= CASIM_F_IS_DONE;
+      else
+        flags &= ~CASIM_F_IS_DONE;
+      a.flags = flags;
+      reward = (float)r;
+      int nf = flags & ~old_flags;
+      st_new_coll = (nf & CASIM_F_IN_COLLISION) != 0;
+      st_new_goal = (nf & CASIM_F_IS_AT_GOAL) != 0;
+      st_new_to = (nf & CASIM_F_RAN_OUT_OF_TIME) != 0;
+      st_rew = r;
+      st_active = !(old_flags & CASIM_F_IS_DONE);
+      st_agents = 1;
+    }
+    /* game over :722-736 */
+    unsigned envmask = (A == 32 ? 0xffffffffu : ((1u << A) - 1u)) << base;
+    bool learning = (a.type & 0xff) == CASIM_POLICY_LEARNING;
+    unsigned b_all = __ballot_sync(FULL_MASK, done || !valid);
+    unsigned b_learn = __ballot_sync(FULL_MASK, done || !valid || !learning);
+    unsigned b_done = __ballot_sync(FULL_MASK, done);
+    if (slot && ai == 0) {
+      bool go;
+      if (c.game_over_mode == CASIM_GAME_OVER_ALL)
+        go = (b_all & envmask) == envmask;
+      else if (c.game_over_mode == CASIM_GAME_OVER_ALL_LEARNING)
+        go = (b_learn & envmask) == envmask;
+      else
+        go = n > 0 ? ((b_done >> base) & 1u) != 0 : true;
+      if (p.o.game_over) p.o.game_over[e] = (uint8_t)go;
+      p.prev_game_over[e] = (uint8_t)go;
+      st_go = go;
+    }
+    if (slot) {
+      if (p.o.rewards) p.o.rewards[g] = reward;
+      if (p.o.done) p.o.done[g] = (uint8_t)done;
+      if (p.o.collision_flags) p.o.collision_flags[g] = (uint8_t)((coll_agent ? 1 : 0) | (coll_wall ? 2 : 0));
+      if (p.o.nearest_dist) p.o.nearest_dist[g] = valid ? (float)nearest : 0.f;
+    }
+  } else if (MODE == CASIM_MODE_RESET) {
+    if (slot && ai == 0) p.prev_game_over[e] = 0;
+  }
+
+  /* ---- state write-back ---- */
+  if (MODE == CASIM_MODE_STEP) {
+    if (valid) store_agent(p.state, plane, g, a, wrote_all);
+  } else if (MODE == CASIM_MODE_RESET) {
+    if (slot) store_agent(p.state, plane, g, a, true);
+  }
+  if (p.write_pose && slot) {
+    double2* q = reinterpret_cast<double2*>(p.pose64 + 4 * g);
+    q[0] = make_double2(a.px, a.py);
+    q[1] = make_double2(a.heading, a.radius);
+  }
+
+  /* ---- OtherAgentsStatesSensor (OtherAgentsStatesSensor.py:11-77) ---- */
+  int nobs = 0;
+  if (want_oas) {
+    const int rows = c.rows;
+    const int rowlen = rows * 10;
+    float* stage = s_stage + (size_t)warp_in_cta * 32 * rowlen;
+    float* mine = stage + lane * rowlen;
+    const bool sense = valid && (sensors & CASIM_SENSOR_OTHER_AGENTS);
+    /* keys + ranks: ascending stable order of (dist - r_h - r_o), ties -> lower index first */
+    double key[AP];
+    int rank[AP];
+    int m = 0;
+#pragma unroll
+    for (int j = 0; j < AP; j++) {
+      float orad = __shfl_sync(FULL_MASK, (float)a.radius, (base + j) & 31);
+      bool ok = sense && j < n && j != ai && !(dist[j] > c.sensing_horizon);
+      key[j] = ok ? dist[j] - a.radius - (double)orad : INFINITY;
+      rank[j] = 0;
+      m += ok;
+    }
+#pragma unroll
+    for (int j = 0; j < AP; j++)
+#pragma unroll
+      for (int k = j + 1; k < AP; k++) {
+        bool kfirst = key[k] < key[j];
+        rank[j] += kfirst;
+        rank[k] += !kfirst;
+      }
+    const int K = min(m, c.max_obs);
+    nobs = min(K, rows);
+    double p0 = 0, p1 = 0, dgoal;
+    ref_axes(a, p0, p1, dgoal);
+    const double q0 = -p1, q1 = p0;
+    if (slot)
+      for (int r = nobs; r < rows; r++)
+#pragma unroll
+        for (int k = 0; k < 10; k++) mine[r * 10 + k] = 0.f;
+#pragma unroll
+    for (int j = 0; j < AP; j++) {
+      int src = (base + j) & 31;
+      double ox = __shfl_sync(FULL_MASK, a.px, src), oy = __shfl_sync(FULL_MASK, a.py, src);
+      double ovx = __shfl_sync(FULL_MASK, a.vx, src), ovy = __shfl_sync(FULL_MASK, a.vy, src);
+      float orad = __shfl_sync(FULL_MASK, (float)a.radius, src);
+      int ostatic = __shfl_sync(FULL_MASK, (int)me_static, src);
+      bool ok = sense && j < n && j != ai && !(dist[j] > c.sensing_horizon);
+      int row = K - 1 - rank[j];
+      if (ok && rank[j] < K && row < rows) {
+        double rx = ox - a.px, ry = oy - a.py;
+        float* wr = mine + row * 10;
+        wr[0] = (float)rx;
+        wr[1] = (float)ry;
+        wr[2] = (float)(rx * p0 + ry * p1);
+        wr[3] = (float)(rx * q0 + ry * q1);
+        wr[4] = (float)(ovx * p0 + ovy * p1);
+        wr[5] = (float)(ovx * q0 + ovy * q1);
+        wr[6] = orad;
+        wr[7] = (float)(a.radius + (double)orad);
+        wr[8] = (float)(sqrt(rx * rx + ry * ry) - a.radius - (double)orad);
+        wr[9] = ostatic ? 1.f : 2.f;
+      }
+    }
+    __syncwarp();
+    /* coalesced copy-out of the warp's contiguous [agents][rows][10] block */
+    int nslots = min(epw, max(p.E - env0, 0)) * A;
+    int total = nslots * rowlen;
+    float* dst = p.o.other_agents_states + (size_t)env0 * A * rowlen;
+    if (total > 0) {
+      if ((((uintptr_t)dst) & 15) == 0 && (total & 3) == 0) {
+        const float4* s4 = reinterpret_cast<const float4*>(stage);
+        float4* d4 = reinterpret_cast<float4*>(dst);
+        for (int i = lane; i < (total >> 2); i += 32) d4[i] = s4[i];
+      } else {
+        for (int i = lane; i < total; i += 32) dst[i] = stage[i];
+      }
+    }
+  }
+  if (p.o.obs_misc && slot) { /* rel_goal (Dynamics.py:28), num_other_agents, use_ppo (config.py:208-213) */
+    float4 mo = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid)
+      mo = make_float4((float)(a.gx - a.px), (float)(a.gy - a.py), (float)nobs,
+                       (a.type & 0xff) == CASIM_POLICY_LEARNING ? 1.f : 0.f);
+    reinterpret_cast<float4*>(p.o.obs_misc)[g] = mo;
+  }
+
+  /* ---- per-step statistics: warp -> CTA -> last block (deterministic, atomic-free on the data) ---- */
+  if (MODE == CASIM_MODE_STEP && p.o.stats) {
+    double v[CASIM_NUM_STATS] = {st_new_coll, st_new_goal, st_new_to, st_go, st_rew, st_active, st_agents, 0.0};
+#pragma unroll
+    for (int k = 0; k < 7; k++) v[k] = warp_sum(v[k]);
+    if (lane == 0)
+#pragma unroll
+      for (int k = 0; k < CASIM_NUM_STATS; k++) s_part[warp_in_cta][k] = v[k];
+    __syncthreads();
+    if (threadIdx.x < CASIM_NUM_STATS) {
+      double s = 0;
+      for (int q = 0; q < warps_per_cta; q++) s += s_part[q][threadIdx.x];
+      p.partials[(size_t)blockIdx.x * CASIM_NUM_STATS + threadIdx.x] = s;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned int t = atomicInc(p.ticket, gridDim.x - 1);
+      s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last && warp_in_cta == 0) {
+      __threadfence();
+#pragma unroll
+      for (int k = 0; k < CASIM_NUM_STATS; k++) {
+        double s = 0;
+        for (int b = lane; b < (int)gridDim.x; b += 32) s += p.partials[(size_t)b * CASIM_NUM_STATS + k];
+        s = warp_sum(s);
+        if (lane == 0) p.o.stats[k] = (float)s;
+      }
+    }
+  }
+}
+
+template <int MODE>
+cudaError_t launch_mode(const CoreArgs& a, int ap, dim3 grid, dim3 block, size_t smem, cudaStream_t s) {
+#define CASE(AP)                                                                                       \
+  case AP: {                                                                                           \
+    if (smem > 48 * 1024)                                                                              \
+      cudaFuncSetAttribute(k_core<MODE, AP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
+    k_core<MODE, AP><<<grid, block, smem, s>>>(a);                                                     \
+    break;                                                                                             \
+  }
+  switch (ap) {
+    CASE(2)
+    CASE(4)
+    CASE(6)
+    CASE(8)
+    CASE(10)
+    CASE(12)
+    CASE(16)
+    CASE(20)
+    CASE(24)
+    CASE(32)
+    default:
+      return cudaErrorInvalidValue;
+  }
+#undef CASE
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const float* ext_actions,
+                              const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s) {
+  CoreArgs a;
+  a.c = h->dc;
+  a.state = reinterpret_cast<float4*>(state);
+  a.ext_actions = ext_actions;
+  a.policy_actions = policy_actions;
+  a.traj = h->traj;
+  a.T = h->T;
+  a.init = h->init;
+  a.type0 = h->type0;
+  a.n_agents = h->n_agents;
+  a.map_planes = h->map_planes;
+  a.n_maps = h->n_maps;
+  a.prev_game_over = h->prev_game_over;
+  a.pose64 = h->pose64;
+  a.partials = h->partials;
+  a.ticket = h->ticket;
+  a.o = *obs;
+  a.dt = dt;
+  a.E = h->E;
+  a.A = h->A;
+  a.epw = 32 / h->A;
+  a.write_pose = (obs->laserscan != nullptr || obs->local_grid != nullptr) ? 1 : 0;
+  static const int aps[] = {2, 4, 6, 8, 10, 12, 16, 20, 24, 32};
+  int ap = 32;
+  for (int k = 0; k < 10; k++)
+    if (aps[k] >= h->A) {
+      ap = aps[k];
+      break;
+    }
+  int warps = (h->E + a.epw - 1) / a.epw;
+  size_t per_warp = obs->other_agents_states ? (size_t)32 * h->dc.rows * 10 * sizeof(float) : 0;
+  int wpc = 4;
+  while (wpc > 1 && per_warp * wpc > 96 * 1024) wpc >>= 1;
+  dim3 block(32 * wpc), grid((warps + wpc - 1) / wpc);
+  if ((int)grid.x > h->max_ctas) return cudaErrorInvalidConfiguration;
+  size_t smem = per_warp * wpc;
+  h->launches++;
+  switch (mode) {
+    case CASIM_MODE_STEP:
+      return launch_mode<CASIM_MODE_STEP>(a, ap, grid, block, smem, s);
+    case CASIM_MODE_RESET:
+      return launch_mode<CASIM_MODE_RESET>(a, ap, grid, block, smem, s);
+    default:
+      return launch_mode<CASIM_MODE_OBSERVE>(a, ap, grid, block, smem, s);
+  }
+}

@@ -1,0 +1,102 @@
+"""ctypes binding of libcasim.so (include/casim.h).
+
+The library is the product's only compute path: there is no Python/CPU fallback.  Importing this
+module on a machine where ``libcasim.so`` has not been built raises immediately.
+"""
+import ctypes
+import os
+
+from .config import SimConfig, NUM_STATS
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcasim.so")
+
+ABI_VERSION = 1
+EINVAL = 10001
+
+c_void_p = ctypes.c_void_p
+c_int = ctypes.c_int
+c_double = ctypes.c_double
+
+
+class Obs(ctypes.Structure):
+    """``struct casim_obs``: device (or host, for the *_host call) pointers; 0 = not wanted."""
+    _fields_ = [("obs_misc", c_void_p), ("other_agents_states", c_void_p), ("laserscan", c_void_p),
+                ("local_grid", c_void_p), ("rewards", c_void_p), ("done", c_void_p), ("game_over", c_void_p),
+                ("collision_flags", c_void_p), ("nearest_dist", c_void_p), ("stats", c_void_p)]
+
+
+OBS_FIELDS = tuple(n for n, _ in Obs._fields_)
+
+# every symbol include/casim.h declares: name -> (restype, argtypes)
+_PCFG = ctypes.POINTER(SimConfig)
+_POBS = ctypes.POINTER(Obs)
+SYMBOLS = {
+    "casim_last_error": (ctypes.c_char_p, []),
+    "casim_abi_version": (c_int, []),
+    "casim_default_config": (None, [_PCFG]),
+    "casim_create": (c_int, [_PCFG, c_int, c_int, ctypes.POINTER(c_void_p)]),
+    "casim_destroy": (c_int, [c_void_p]),
+    "casim_set_config": (c_int, [c_void_p, _PCFG]),
+    "casim_set_obstacles": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "casim_set_map": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "casim_set_trajectories": (c_int, [c_void_p, c_void_p, c_int]),
+    "casim_reset": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _POBS, c_void_p]),
+    "casim_observe": (c_int, [c_void_p, c_void_p, _POBS, c_void_p]),
+    "casim_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_double, _POBS, c_void_p]),
+    "casim_step_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_double, _POBS, _POBS,
+                                c_void_p]),
+    "casim_explore_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p]),
+    "casim_ga3c_set_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "casim_ga3c_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "casim_launch_count": (ctypes.c_ulonglong, [c_void_p]),
+}
+
+_lib = None
+
+
+class CasimError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libcasim.so and bind every declared symbol.  Raises if the library is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CasimError("libcasim.so is not built (%s). Run `python -c 'import __graft_entry__ as g; g.build()'` "
+                         "or `make -C gym-exploration-2d_b200/casim/csrc`. There is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the .so does not export a declared symbol
+        fn.restype = restype
+        fn.argtypes = argtypes
+    if lib.casim_abi_version() != ABI_VERSION:
+        raise CasimError("libcasim.so ABI version %d, binding expects %d" % (lib.casim_abi_version(), ABI_VERSION))
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().casim_last_error()
+        raise CasimError("%s failed (code %d): %s" % (what, rc, msg.decode() if msg else ""))
+
+
+def default_config():
+    c = SimConfig()
+    load().casim_default_config(ctypes.byref(c))
+    return c
+
+
+def ptr(t):
+    """Device (or pinned host) pointer of a torch tensor / numpy array; None -> NULL."""
+    if t is None:
+        return None
+    if hasattr(t, "data_ptr"):
+        if not t.is_contiguous():
+            raise CasimError("tensor passed to libcasim must be contiguous")
+        return c_void_p(t.data_ptr())
+    return c_void_p(t.ctypes.data)

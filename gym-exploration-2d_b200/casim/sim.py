@@ -1,0 +1,216 @@
+"""BatchedSim -- the device-resident state of E environments x A agent slots and thin wrappers around
+the C ABI calls.  PyTorch is only the buffer / stream / interop layer: every computation is a kernel of
+libcasim.so.
+
+Layout (include/casim.h): ``state[6, E, A, 4]`` float32 (six float4 planes; step_num / flags / type are
+int32 bit patterns), observations as dense ``[E, A, ...]`` tensors.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import layout as L
+from . import lib as _lib
+from .config import Config, SimConfig, make_sim_config, MAP_DIM, NUM_STATS
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return ctypes.c_void_p(s.cuda_stream)
+
+
+class BatchedSim:
+    def __init__(self, num_envs, max_agents, cfg=None, device=None, sensors=(), want_debug=True, want_stats=True):
+        """``cfg``: a SimConfig (default: snapshot of casim.config.Config).  ``sensors``: iterable of sensor
+        bit masks / names for which observation buffers are allocated ("other_agents_states", "laserscan",
+        "local_grid")."""
+        if not torch.cuda.is_available():
+            raise _lib.CasimError("casim needs a CUDA device (B200); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.E, self.A = int(num_envs), int(max_agents)
+        self.cfg = cfg if cfg is not None else make_sim_config(Config)
+        self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        torch.cuda.set_device(self.device)
+        h = ctypes.c_void_p()
+        _lib.check(self.lib.casim_create(ctypes.byref(self.cfg), self.E, self.A, ctypes.byref(h)), "casim_create")
+        self.handle = h
+        E, A, dev = self.E, self.A, self.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        u8 = dict(dtype=torch.uint8, device=dev)
+        self.state = torch.zeros((L.NUM_PACKS, E, A, 4), **f32)
+        names = set()
+        for s in sensors:
+            if isinstance(s, str):
+                names.add(s)
+            else:
+                if s & L.SENSOR_OTHER_AGENTS:
+                    names.add("other_agents_states")
+                if s & L.SENSOR_LASERSCAN:
+                    names.add("laserscan")
+                if s & L.SENSOR_OCCUPANCY_GRID:
+                    names.add("local_grid")
+        rows = self.cfg.max_other_agents_rows
+        self.buf = {
+            "obs_misc": torch.zeros((E, A, 4), **f32),
+            "other_agents_states": torch.zeros((E, A, rows, 10), **f32) if "other_agents_states" in names else None,
+            "laserscan": torch.zeros((E, A, self.cfg.laser_num_beams), **f32) if "laserscan" in names else None,
+            "local_grid": torch.zeros((E, A, self.cfg.submap_w, self.cfg.submap_h), **u8) if "local_grid" in names else None,
+            "rewards": torch.zeros((E, A), **f32),
+            "done": torch.zeros((E, A), **u8),
+            "game_over": torch.zeros((E,), **u8),
+            "collision_flags": torch.zeros((E, A), **u8) if want_debug else None,
+            "nearest_dist": torch.zeros((E, A), **f32) if want_debug else None,
+            "stats": torch.zeros((NUM_STATS,), **f32) if want_stats else None,
+        }
+        self._obs = self._obs_struct(self.buf)
+        self._keep = {}          # tensors the library borrows (init, types, n_agents, traj)
+        self.has_map = False
+
+    # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def _obs_struct(bufs):
+        o = _lib.Obs()
+        for name in _lib.OBS_FIELDS:
+            t = bufs.get(name)
+            setattr(o, name, None if t is None else _lib.ptr(t))
+        return o
+
+    def close(self):
+        if getattr(self, "handle", None) is not None and self.handle:
+            torch.cuda.synchronize(self.device)
+            self.lib.casim_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _dev(self, a, dtype):
+        if a is None:
+            return None
+        if isinstance(a, torch.Tensor):
+            return a.to(device=self.device, dtype=dtype).contiguous()
+        return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(self.device).contiguous()
+
+    # ------------------------------------------------------------------------------------------
+    def set_config(self, cfg):
+        self.cfg = cfg
+        _lib.check(self.lib.casim_set_config(self.handle, ctypes.byref(cfg)), "casim_set_config")
+
+    def set_obstacles(self, rects, n_rects=None, want_map=False):
+        """rects: [n_maps, max_rects, 4] (x1, y1, x3, y3) in metres, or [max_rects, 4] for one shared map,
+        or None / empty for "no obstacles"."""
+        if rects is None or len(rects) == 0:
+            _lib.check(self.lib.casim_set_obstacles(self.handle, None, None, 0, 0, None, _stream_ptr()), "casim_set_obstacles")
+            self.has_map = False
+            return None
+        r = self._dev(rects, torch.float32)
+        if r.dim() == 2:
+            r = r.unsqueeze(0)
+        n_maps, max_rects = r.shape[0], r.shape[1]
+        if n_rects is None:
+            n_rects = torch.full((n_maps,), max_rects, dtype=torch.int32, device=self.device)
+        else:
+            n_rects = self._dev(n_rects, torch.int32)
+        out = torch.zeros((n_maps, MAP_DIM, MAP_DIM), dtype=torch.uint8, device=self.device) if want_map else None
+        _lib.check(self.lib.casim_set_obstacles(self.handle, _lib.ptr(r), _lib.ptr(n_rects), n_maps, max_rects,
+                                                _lib.ptr(out), _stream_ptr()), "casim_set_obstacles")
+        torch.cuda.current_stream().synchronize()      # r / n_rects may be freed after return
+        self.has_map = True
+        return out
+
+    def set_map(self, static_map):
+        """static_map: [300,300] or [n_maps,300,300] bool/uint8 (Map.static_map)."""
+        if static_map is None:
+            _lib.check(self.lib.casim_set_map(self.handle, None, 0, _stream_ptr()), "casim_set_map")
+            self.has_map = False
+            return
+        m = self._dev(static_map, torch.uint8)
+        if m.dim() == 2:
+            m = m.unsqueeze(0)
+        _lib.check(self.lib.casim_set_map(self.handle, _lib.ptr(m), m.shape[0], _stream_ptr()), "casim_set_map")
+        torch.cuda.current_stream().synchronize()
+        self.has_map = True
+
+    def set_trajectories(self, traj):
+        """traj: [E,A,T,4] (pose_x, pose_y, vel_x, vel_y) for ExternalDynamics agents."""
+        if traj is None:
+            self._keep["traj"] = None
+            _lib.check(self.lib.casim_set_trajectories(self.handle, None, 0), "casim_set_trajectories")
+            return
+        t = self._dev(traj, torch.float32)
+        self._keep["traj"] = t
+        _lib.check(self.lib.casim_set_trajectories(self.handle, _lib.ptr(t), t.shape[2]), "casim_set_trajectories")
+
+    def reset(self, init, types, n_agents=None):
+        """init [E,A,7] = start_x, start_y, goal_x, goal_y, radius, pref_speed, heading (NaN = towards goal);
+        types [E,A] int32 type words (layout.encode_type)."""
+        init = self._dev(init, torch.float32)
+        types = self._dev(types, torch.int32)
+        n_agents = self._dev(n_agents, torch.int32)
+        assert init.shape == (self.E, self.A, 7) and types.shape == (self.E, self.A)
+        self._keep.update(init=init, types=types, n_agents=n_agents)
+        _lib.check(self.lib.casim_reset(self.handle, _lib.ptr(self.state), _lib.ptr(init), _lib.ptr(types),
+                                        _lib.ptr(n_agents), ctypes.byref(self._obs), _stream_ptr()), "casim_reset")
+
+    def bind(self, types=None, n_agents=None, init=None):
+        """Tell the library about n_agents / types without re-initialising the state (used by tests that
+        inject a mid-episode state)."""
+        init = self._dev(init if init is not None else np.zeros((self.E, self.A, 7), np.float32), torch.float32)
+        types = self._dev(types, torch.int32)
+        n_agents = self._dev(n_agents, torch.int32)
+        scratch = torch.zeros_like(self.state)
+        self._keep.update(init=init, types=types, n_agents=n_agents)
+        o = self._obs_struct({})
+        _lib.check(self.lib.casim_reset(self.handle, _lib.ptr(scratch), _lib.ptr(init), _lib.ptr(types),
+                                        _lib.ptr(n_agents), ctypes.byref(o), _stream_ptr()), "casim_reset")
+        torch.cuda.current_stream().synchronize()
+
+    def observe(self):
+        _lib.check(self.lib.casim_observe(self.handle, _lib.ptr(self.state), ctypes.byref(self._obs), _stream_ptr()),
+                   "casim_observe")
+
+    def step(self, ext_actions=None, policy_actions=None, dt=None):
+        """One env.step for every environment, asynchronous on the current CUDA stream.
+        ext_actions / policy_actions: float32 CUDA tensors [E,A,2] (or None)."""
+        _lib.check(self.lib.casim_step(self.handle, _lib.ptr(self.state), _lib.ptr(ext_actions),
+                                       _lib.ptr(policy_actions), float(dt) if dt is not None else 0.0,
+                                       ctypes.byref(self._obs), _stream_ptr()), "casim_step")
+
+    def step_host(self, host_bufs, ext_actions_host=None, ext_actions_dev=None, policy_actions=None, dt=None):
+        """Host-buffer step: H2D of the actions, the step, D2H of every buffer present in ``host_bufs``
+        (dict name -> pinned host tensor); returns when the results are in host memory."""
+        ho = self._obs_struct(host_bufs)
+        _lib.check(self.lib.casim_step_host(self.handle, _lib.ptr(self.state), _lib.ptr(ext_actions_host),
+                                            _lib.ptr(ext_actions_dev), _lib.ptr(policy_actions),
+                                            float(dt) if dt is not None else 0.0, ctypes.byref(self._obs),
+                                            ctypes.byref(ho), _stream_ptr()), "casim_step_host")
+
+    def launch_count(self):
+        return int(self.lib.casim_launch_count(self.handle))
+
+    # ------------------------------------------------------------------------------------------
+    # host-side views (tests / drop-in shim)
+    def state_numpy(self):
+        """float64 [E,A,24] copy of the state (int words decoded)."""
+        packs = self.state.detach().cpu().numpy()
+        P, E, A, _ = packs.shape
+        w = np.ascontiguousarray(packs.transpose(1, 2, 0, 3).reshape(E, A, P * 4))
+        out = w.astype(np.float64)
+        iw = w.view(np.int32)
+        for k in L.INT_WORDS:
+            out[..., k] = iw[..., k]
+        return out
+
+    def load_state_numpy(self, state):
+        """Inverse of state_numpy: float64 [E,A,24] -> device state (values rounded to fp32)."""
+        E, A, W = state.shape
+        w = state.astype(np.float32)
+        iw = w.view(np.int32)
+        for k in L.INT_WORDS:
+            iw[..., k] = state[..., k].astype(np.int32)
+        packs = np.ascontiguousarray(w.reshape(E, A, W // 4, 4).transpose(2, 0, 1, 3))
+        self.state.copy_(torch.from_numpy(packs).to(self.device))

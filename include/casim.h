@@ -200,15 +200,16 @@ int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, voi
  * fp32 action rounding :289, Agent.take_action agent.py:147-190, dynamics), _compute_rewards +
  * _check_for_collisions (:502-567, :630-671), _get_obs (sensors), _check_which_agents_done (:711-738).
  * ext_actions: [E,A,2] caller-supplied actions (external / learning / CARRL agents); may be NULL if none.
- * policy_actions: [E,A,2] actions chosen by casim_explore_step / casim_ga3c_forward; may be NULL if none. */
+ * policy_actions: [E,A,2] actions chosen by casim_explore_step / casim_ga3c_forward; may be NULL if none.
+ * dt: the step length (step(actions, dt=None), :181-182); dt <= 0 means Config.DT. */
 int casim_step(casim_handle* h, float* state, const float* ext_actions, const float* policy_actions,
-               float dt, const casim_obs* obs, void* stream);
+               double dt, const casim_obs* obs, void* stream);
 
 /* Host-buffer variant: ext_actions_host (pinned, may be NULL) is copied H2D, the step runs, and rewards, done and
  * game_over (and obs_misc/sensor buffers if the host pointers are non-NULL) are copied D2H into `host`; blocks until
  * the results are in host memory.  `dev` holds the device buffers used for the step. */
 int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
-                    const float* policy_actions, float dt, const casim_obs* dev, const casim_obs* host,
+                    const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
                     void* stream);
 
 /* Replaces ig_greedy.find_next_action for every ig_greedy agent (policies/ig_greedy.py:31-93,

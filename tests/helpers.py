@@ -52,3 +52,113 @@ def assert_state_close(s, ref, n_agents, what):
             assert np.array_equal(s[e, :n, k], ref[e, :n, k]), (what, "word", k, "env", e, s[e, :n, k], ref[e, :n, k])
         # angles may differ by the wrap convention only within tolerance; compare directly
         assert_close(s[e, :n][:, CONT_WORDS], ref[e, :n][:, CONT_WORDS], "%s env %d" % (what, e))
+
+
+# ---------------------------------------------------------------------------------------------
+# random mid-episode batches (vectorised variant of oracle/gen_golden.py:random_case) for GPU-vs-oracle tests
+def f32(x):
+    return np.asarray(x, dtype=np.float32).astype(np.float64)
+
+
+def random_batch(rng, E, A, sensor_choices=(0, 1), policies=None, dynamics=None, spread=None, n_min=2, T=6):
+    """Returns dict(init, types, state, ext, traj, n_agents): fp32-representable doubles."""
+    policies = policies or [L.POLICY_STATIC, L.POLICY_NONCOOPERATIVE, L.POLICY_NONCOOPERATIVE, L.POLICY_NONCOOPERATIVE,
+                            L.POLICY_EXTERNAL, L.POLICY_CARRL, L.POLICY_PEDESTRIAN, L.POLICY_LEARNING]
+    dynamics = dynamics or [L.DYN_UNICYCLE, L.DYN_UNICYCLE, L.DYN_FIRST_ORDER, L.DYN_UNICYCLE_MAX_TURN_RATE]
+    n_agents = rng.integers(min(n_min, A), A + 1, size=E).astype(np.int32)
+    pol = rng.choice(policies, size=(E, A))
+    dyn = rng.choice(dynamics, size=(E, A))
+    dyn = np.where(pol == L.POLICY_PEDESTRIAN, L.DYN_EXTERNAL, dyn)
+    mask = rng.choice(list(sensor_choices), size=(E, A))
+    types = (pol | (dyn << 8) | (mask << 16)).astype(np.int32)
+    sp = rng.choice([2.0, 4.0, 8.0, 14.0], size=(E, 1, 1)) if spread is None else np.full((E, 1, 1), spread)
+    start = f32(rng.uniform(-1, 1, (E, A, 2)) * sp)
+    goal = f32(rng.uniform(-1, 1, (E, A, 2)) * sp)
+    radius = f32(rng.uniform(0.2, 0.8, (E, A)))
+    pref = f32(rng.uniform(0.5, 1.5, (E, A)))
+    head0 = f32(rng.uniform(-np.pi, np.pi, (E, A)))
+    init = np.concatenate([start, goal, radius[..., None], pref[..., None], head0[..., None]], -1)
+    s = np.zeros((E, A, L.STATE_WORDS))
+    along = start + (goal - start) * rng.uniform(0, 1.05, (E, A, 1)) + rng.normal(0, 0.3, (E, A, 2))
+    clustered = rng.normal(0, 1.2, (E, A, 2))
+    pos = f32(np.where(rng.random((E, A, 1)) < 0.5, along, clustered))
+    fl = np.zeros((E, A), np.int64)
+    u = rng.random((E, A))
+    at_goal = u < 0.12
+    pos = np.where(at_goal[..., None], f32(goal + rng.uniform(-0.3, 0.3, (E, A, 2))), pos)
+    fl = np.where(at_goal, L.F_IS_AT_GOAL | L.F_IS_DONE | np.where(rng.random((E, A)) < 0.5, L.F_WAS_AT_GOAL_ALREADY, 0), fl)
+    coll = (u >= 0.12) & (u < 0.24)
+    fl = np.where(coll, L.F_IN_COLLISION | L.F_IS_DONE | np.where(rng.random((E, A)) < 0.6, L.F_WAS_IN_COLLISION_ALREADY, 0)
+                  | np.where(rng.random((E, A)) < 0.3, L.F_RAN_OUT_OF_TIME, 0), fl)
+    tout = (u >= 0.24) & (u < 0.32)
+    fl = np.where(tout, L.F_RAN_OUT_OF_TIME | L.F_IS_DONE, fl)
+    s[..., L.PX], s[..., L.PY] = pos[..., 0], pos[..., 1]
+    s[..., L.GX], s[..., L.GY] = goal[..., 0], goal[..., 1]
+    s[..., L.RADIUS], s[..., L.PREF_SPEED] = radius, pref
+    s[..., L.HEADING] = f32(rng.uniform(-np.pi, np.pi, (E, A)))
+    spd = f32(rng.uniform(0, 1, (E, A)) * pref)
+    s[..., L.SPEED] = spd
+    s[..., L.VX] = f32(spd * np.cos(s[..., L.HEADING]))
+    s[..., L.VY] = f32(spd * np.sin(s[..., L.HEADING]))
+    s[..., L.DELTA_HEADING] = f32(rng.uniform(-0.5, 0.5, (E, A)))
+    s[..., L.TURNING_DIR] = f32(rng.choice([0.0, 0.11, -0.11, 0.05, -0.3, 1.0], size=(E, A)) * rng.uniform(0.5, 1, (E, A)))
+    step_num = rng.integers(0, 60, (E, A))
+    step_num = np.where(rng.random((E, A)) < 0.15, 0, step_num)
+    s[..., L.STEP_NUM] = step_num
+    s[..., L.T] = f32(step_num * 0.1)
+    s[..., L.TIME_REMAINING] = f32(np.where(rng.random((E, A)) < 0.5, rng.uniform(0.5, 30, (E, A)), rng.uniform(-0.05, 0.25, (E, A))))
+    gd = goal - pos
+    s[..., L.DIST_TO_GOAL] = f32(np.hypot(gd[..., 0], gd[..., 1]))
+    s[..., L.PAST_DIST_TO_GOAL] = f32(s[..., L.DIST_TO_GOAL] + rng.uniform(0, 0.15, (E, A)))
+    for k, lo, hi in ((L.PAST_ACT0_V, 0, 1.5), (L.PAST_ACT0_W, -1, 1), (L.PAST_ACT1_V, 0, 1.5), (L.PAST_ACT1_W, -1, 1)):
+        s[..., k] = f32(rng.uniform(lo, hi, (E, A)))
+    he = s[..., L.HEADING] - np.arctan2(gd[..., 1], gd[..., 0])
+    s[..., L.HEADING_EGO] = f32((he + np.pi) % (2 * np.pi) - np.pi)
+    s[..., L.FLAGS] = fl
+    s[..., L.TYPE] = types
+    ext = f32(np.stack([rng.uniform(0, 1.5, (E, A)), rng.uniform(-1.2, 1.2, (E, A))], -1))
+    ext[..., 0] = np.where(pol == L.POLICY_CARRL, rng.integers(0, 11, (E, A)), ext[..., 0])
+    ext[..., 1] = np.where(pol == L.POLICY_CARRL, 0, ext[..., 1])
+    ext[..., 1] = np.where(pol == L.POLICY_LEARNING, f32(rng.uniform(0, 1, (E, A))), ext[..., 1])
+    p0 = pos + rng.normal(0, 0.2, (E, A, 2))
+    v = rng.uniform(-1, 1, (E, A, T, 2))
+    kk = np.arange(T)[None, None, :, None]
+    traj = f32(np.concatenate([p0[:, :, None, :] + 0.1 * kk * v, v], -1))
+    # zero the padded slots
+    pad = np.arange(A)[None, :] >= n_agents[:, None]
+    s[pad] = 0
+    types = np.where(pad, 0, types).astype(np.int32)
+    return dict(init=init, types=types, state=s, ext=ext, traj=traj, n_agents=n_agents)
+
+
+def compare_step(what, n_agents, gstate, gbuf, ostate, oobs, check_sensors=True):
+    """GPU (gstate float64 [E,A,24] decoded, gbuf dict of numpy arrays) vs oracle (ostate, ObsBuffers).
+    Flags / done / ordering / laser hit index / grid cells exact; continuous values within RTOL/ATOL."""
+    assert_state_close(gstate, ostate, n_agents, what)
+    E, A = gstate.shape[:2]
+    valid = np.arange(A)[None, :] < np.asarray(n_agents)[:, None]
+    assert np.array_equal(gbuf["done"][valid], oobs.done[valid]), what + " done"
+    assert np.array_equal(gbuf["game_over"], oobs.game_over), what + " game_over"
+    if gbuf.get("collision_flags") is not None:
+        assert np.array_equal(gbuf["collision_flags"][valid], oobs.collision_flags[valid]), what + " collision flags"
+        assert_close(gbuf["nearest_dist"][valid], oobs.nearest_dist[valid], what + " nearest")
+    assert_close(gbuf["rewards"][valid], oobs.rewards[valid], what + " rewards", atol=1e-7)
+    compare_obs(what, n_agents, gbuf, oobs, check_sensors)
+
+
+def compare_obs(what, n_agents, gbuf, oobs, check_sensors=True):
+    E, A = gbuf["obs_misc"].shape[:2]
+    valid = np.arange(A)[None, :] < np.asarray(n_agents)[:, None]
+    assert_close(gbuf["obs_misc"][valid], oobs.obs_misc[valid], what + " obs_misc")
+    if not check_sensors:
+        return
+    if gbuf.get("other_agents_states") is not None:
+        g, o = gbuf["other_agents_states"][valid], oobs.other_agents_states[valid]
+        # closest-N ordering: type and radius columns pin which agent sits in which row
+        assert np.array_equal(g[..., 9], o[..., 9]), what + " other_agents ordering (type column)"
+        assert np.array_equal(g[..., 6], o[..., 6].astype(np.float32)), what + " other_agents ordering (radius column)"
+        assert_close(g, o, what + " other_agents_states")
+    if gbuf.get("laserscan") is not None:
+        assert_close(gbuf["laserscan"][valid], oobs.laserscan[valid], what + " laserscan", rtol=0, atol=1e-6)
+    if gbuf.get("local_grid") is not None:
+        assert np.array_equal(gbuf["local_grid"][valid], oobs.local_grid[valid]), what + " local_grid"
