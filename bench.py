@@ -1,0 +1,414 @@
+#!/usr/bin/env python
+"""bench.py -- agent-steps/s of the batched CollisionAvoidanceEnv step on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|full] [--impl reference]
+
+One "step" = one pass of the hot path (casim_step) over one batch of E envs x A agents of synthetic
+scenarios (casim/scenarios.py).  Default workload = BASELINE.json configs[1] (C2): 4096 envs x 10 agents per
+GPU, NonCooperative/Static mix, collision + reward step only.  Prints ONE JSON line (rank 0).
+
+Timing: device-side CUDA events on the launching stream around exactly K steps, after W warm-up steps, with a
+barrier + synchronize on both sides, max over ranks.  The K steps are captured in one CUDA graph (no Python
+in the timed region) and walk a RING of independent env batches whose combined footprint exceeds the 126 MB
+L2, so no step finds its inputs in cache ("inputs larger than L2").  `e2e` is the same metric through the
+host-buffer call (pinned host actions H2D, step, rewards/done/game_over/stats D2H, blocking) per step.
+`cpu_baseline` / `--impl reference` time the CPU oracle port (oracle/casim_oracle.c, plain C fp64 restatement
+of the reference's Python step, POSIX threads over environments) on the host cores: the reference itself is
+Python that needs /root/reference, which does not exist on the GPU box.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "gym-exploration-2d_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+L2_BYTES = 126 * 1024 * 1024
+
+# algorithmic bytes per agent-step (DESIGN.md "Algorithmic bytes")
+BYTES_CORE = 177          # 96 B state read + 76 B mutable state written + 4 B reward + 1 B done
+BYTES_OAS = 384           # 9 x 10 fp32 rows + 6 scalar observation words
+BYTES_LASER = 320         # 16 fp32 ranges written + 256 one-byte cell samples
+BYTES_WALL = 81           # disc of cells around the agent (r = 0.5 m)
+BYTES_GRID = 11169        # 3600 B written + <= 87^2 B rotated window read
+
+WORKLOADS = {
+    "c2": dict(E=4096, A=10, sensors=(), desc="4096 envs x 10 agents, NonCooperative/Static mix, collision + reward step only"),
+    "c3": dict(E=4096, A=10, sensors=("other_agents_states", "laserscan"),
+               desc="4096 envs x 10 agents, OtherAgentsStates + LaserScan ray-casting against the crossing map"),
+    "full": dict(E=4096, A=10, sensors=("other_agents_states", "laserscan", "local_grid"),
+                 desc="4096 envs x 10 agents, OtherAgentsStates + LaserScan + OccupancyGrid, crossing map"),
+}
+
+
+def algorithmic_bytes(wl):
+    b = BYTES_CORE
+    s = WORKLOADS[wl]["sensors"]
+    if "other_agents_states" in s:
+        b += BYTES_OAS
+    if "laserscan" in s:
+        b += BYTES_LASER + BYTES_WALL
+    if "local_grid" in s:
+        b += BYTES_GRID
+    return b
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_for(wl):
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(wl)
+    except Exception:
+        return None
+
+
+# ------------------------------------------------------------------------------------------------
+def scenario(wl, E, A, seed):
+    from casim import layout as L
+    from casim import scenarios as S
+    sensors = WORKLOADS[wl]["sensors"]
+    mask = 0
+    if "other_agents_states" in sensors:
+        mask |= L.SENSOR_OTHER_AGENTS
+    if "laserscan" in sensors:
+        mask |= L.SENSOR_LASERSCAN
+    if "local_grid" in sensors:
+        mask |= L.SENSOR_OCCUPANCY_GRID
+    if wl == "c2":
+        init, types, n = S.open_space(E, A, seed=seed, sensors=0)
+        return init, types, n, None
+    return S.crossing(E, A, seed=seed, sensors=mask)
+
+
+def oracle_run(wl, E, A, steps, warmup, threads, seed=1234):
+    """CPU oracle port on the same synthetic workload; returns (agent-steps/s, seconds per step)."""
+    from oracle import oracle
+    from casim import lib
+    cfg = lib.default_config()
+    cfg.auto_reset = 1
+    init, types, n, rects = scenario(wl, E, A, seed)
+    maps = None
+    if rects is not None:
+        maps = oracle.rasterize(cfg, rects.astype(np.float64))
+    # the oracle only runs sensors whose output buffer exists; give it exactly the workload's
+    sensors = WORKLOADS[wl]["sensors"]
+    state, obs = oracle.reset(cfg, init.astype(np.float64), types, n_agents=n, maps=maps)
+    if "other_agents_states" not in sensors:
+        obs.other_agents_states = None
+    if "laserscan" not in sensors:
+        obs.laserscan = None
+    if "local_grid" not in sensors:
+        obs.local_grid = None
+    init64 = init.astype(np.float64)
+    go = np.zeros((E,), np.uint8)
+    for _ in range(warmup):
+        oracle.step(cfg, state, n_agents=n, maps=maps, init=init64, types0=types, prev_game_over=go, obs=obs, n_threads=threads)
+        go = obs.game_over.copy()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle.step(cfg, state, n_agents=n, maps=maps, init=init64, types0=types, prev_game_over=go, obs=obs, n_threads=threads)
+        go = obs.game_over.copy()
+    dt = time.perf_counter() - t0
+    return E * A * steps / dt, dt / max(steps, 1)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled in the background while the GPU is under load."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.samples = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.perf_counter(), line.strip()))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        sm, mx, reasons = [], [], set()
+        for t, line in self.samples:
+            if t < t0 or t > t1:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    """--impl reference: the CPU implementation of the path (oracle port, all host threads) on a bounded sample."""
+    if rank != 0:
+        return
+    wl = args.workload
+    W = WORKLOADS[wl]
+    threads = min(os.cpu_count() or 1, 64)
+    E, A = W["E"], W["A"]
+    # bounded sample: the full per-GPU batch for the cheap workloads, fewer envs when sensors make a step slow
+    Es = E if wl == "c2" else (512 if wl == "c3" else 64)
+    steps = max(1, min(args.steps, 200))
+    warm = max(1, min(args.warmup, 5))
+    v, sps = oracle_run(wl, Es, A, steps, warm, threads)
+    line = {
+        "impl": "reference", "metric": "agent-steps/s", "value": v, "unit": "agent-steps/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warm, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl + ": " + W["desc"], "envs_per_step": Es, "agents_per_env": A},
+        "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": threads, "kind": "port",
+                         "sample": "%d steps of %d envs x %d agents (oracle/casim_oracle.c, %d POSIX threads over envs; the Python "
+                                   "reference itself measured 2.9e3 agent-steps/s/core in the build container, BASELINE.md)"
+                                   % (steps, Es, A, threads)},
+        "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="casim", choices=["casim", "reference"])
+    ap.add_argument("--envs", type=int, default=None, help="override envs per GPU (parity/sweep use; default = the named config)")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of one CUDA graph")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=200)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from casim import lib
+    from casim.sim import BatchedSim
+    from casim.config import NUM_STATS
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    wl = args.workload
+    W = WORKLOADS[wl]
+    E, A = (args.envs or W["E"]), W["A"]
+    K, Wm = args.steps, max(args.warmup, 3)
+    cfg = lib.default_config()
+    cfg.auto_reset = 1
+
+    # ---- ring of independent env batches, footprint > L2 ----
+    per_agent_resident = 96 + 5 + (16 if W["sensors"] else 0)
+    if "other_agents_states" in W["sensors"]:
+        per_agent_resident += 360
+    if "laserscan" in W["sensors"]:
+        per_agent_resident += 64 + 32
+    if "local_grid" in W["sensors"]:
+        per_agent_resident += 3600 + 32
+    batch_bytes = E * A * per_agent_resident
+    R = int(min(max(2, -(-int(1.5 * L2_BYTES) // batch_bytes)), 96))
+    stats_all = torch.zeros((max(K, Wm, args.e2e_steps), NUM_STATS), dtype=torch.float32, device=dev)
+    sims = []
+    for r in range(R):
+        sim = BatchedSim(E, A, cfg=cfg, sensors=W["sensors"], want_debug=False, want_misc=bool(W["sensors"]), want_stats=True)
+        init, types, n, rects = scenario(wl, E, A, seed=1234 + 1000 * rank + r)
+        if rects is not None:
+            sim.set_obstacles(rects)
+        sim.reset(init, types, n)
+        sims.append(sim)
+    torch.cuda.synchronize()
+    launches_per_step = 1 + (1 if "laserscan" in W["sensors"] else 0) + (1 if "local_grid" in W["sensors"] else 0)
+
+    stream = torch.cuda.Stream(device=dev)
+
+    def run_steps(k0, k):
+        for i in range(k0, k0 + k):
+            sims[i % R].step()
+
+    with torch.cuda.stream(stream):
+        run_steps(0, Wm)                                  # warm-up (also loads the kernels)
+    stream.synchronize()
+
+    graph = None
+    if not args.no_graph:
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(stream):
+            with torch.cuda.graph(graph, stream=stream):
+                run_steps(Wm, K)
+        stream.synchronize()
+        # one untimed replay: graph upload + every ring batch touched once more
+        with torch.cuda.stream(stream):
+            graph.replay()
+        stream.synchronize()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.15)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- timed region: exactly K steps ----
+    barrier()
+    t_load0 = time.perf_counter()
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        if graph is not None:
+            graph.replay()
+        else:
+            run_steps(Wm, K)
+        ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    # keep the same workload running ~1.2 s so that nvidia-smi (50 ms period) sees the clocks under this load
+    t_end = time.perf_counter() + 1.2
+    with torch.cuda.stream(stream):
+        while time.perf_counter() < t_end:
+            if graph is not None:
+                graph.replay()
+            else:
+                run_steps(0, 50)
+            stream.synchronize()
+    t_load1 = time.perf_counter()
+    if sampler:
+        time.sleep(0.1)
+        sampler.stop()
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    total_agent_steps = float(E * A * K * world)
+    value = total_agent_steps / (ms * 1e-3)
+
+    # ---- e2e: host-buffer call per step (pinned H2D of the actions, D2H of rewards/done/game_over/stats) ----
+    Ke = min(args.e2e_steps, K)
+    host = {"rewards": torch.zeros((E, A), dtype=torch.float32).pin_memory(),
+            "done": torch.zeros((E, A), dtype=torch.uint8).pin_memory(),
+            "game_over": torch.zeros((E,), dtype=torch.uint8).pin_memory(),
+            "stats": torch.zeros((NUM_STATS,), dtype=torch.float32).pin_memory()}
+    for name in W["sensors"]:
+        host[name] = torch.zeros(sims[0].buf[name].shape, dtype=sims[0].buf[name].dtype).pin_memory()
+    if W["sensors"]:
+        host["obs_misc"] = torch.zeros((E, A, 4), dtype=torch.float32).pin_memory()
+    act_host = torch.zeros((E, A, 2), dtype=torch.float32).pin_memory()
+    act_dev = torch.zeros((E, A, 2), dtype=torch.float32, device=dev)
+    h2d = act_host.numel() * 4
+    d2h = sum(t.numel() * t.element_size() for t in host.values())
+    with torch.cuda.stream(stream):
+        for i in range(3):
+            sims[i % R].step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
+        barrier()
+        ev0.record(stream)
+        t0 = time.perf_counter()
+        for i in range(Ke):
+            sims[i % R].step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
+        ev1.record(stream)
+        barrier()
+        e2e_s = max(ev0.elapsed_time(ev1) * 1e-3, time.perf_counter() - t0)
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = float(E * A * Ke * world) / e2e_s
+
+    # ---- per-step episode statistics: the one collective of the design (NCCL all-reduce of [8] floats) ----
+    stats = sims[0].buf["stats"].clone()
+    if world > 1:
+        dist.all_reduce(stats)
+    stats = [float(x) for x in stats.cpu()]
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        alg = algorithmic_bytes(wl)
+        step_s = ms * 1e-3 / K
+        achieved = alg * E * A / step_s / 1e9
+        line = {
+            "metric": "agent-steps/s", "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": wl + ": " + W["desc"], "envs_per_gpu": E, "agents_per_env": A,
+                       "l2": "inputs larger than L2: ring of %d independent env batches, %.0f MB resident per GPU"
+                             % (R, R * batch_bytes / 1e6),
+                       "launch": "one CUDA graph of K steps" if graph is not None else "one C-ABI call per step from Python",
+                       "parallelism": "envs sharded over %d GPU(s), no data-path collective" % world,
+                       "state": "fp32 SoA state, fp64 predicates (dtype = arithmetic of the decision path)"},
+            "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": Ke, "call": "casim_step_host via BatchedSim.step_host (blocking, pinned host buffers)"},
+            "gpu_launches": launches_per_step * K,
+            "roofline": {"bound": "hbm", "kernel": "k_core (fused step)" if wl == "c2" else "whole step (%d kernels)" % launches_per_step,
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic_for(wl), "algorithmic_bytes_per_agent_step": alg, "peak_source": peak_src,
+                         "duration_us": step_s * 1e6},
+            "clocks": dict(sampler.summary(t_load0, t_load1), sampled_over="timed region + 1.2 s of the same workload"),
+            "episode_stats_last_step": stats,
+        }
+        if not args.no_cpu_baseline:
+            threads = min(os.cpu_count() or 1, 64)
+            Es = E if wl == "c2" else (512 if wl == "c3" else 64)
+            n_steps = 100 if wl == "c2" else 20
+            v, sps = oracle_run(wl, Es, A, n_steps, 2, threads)
+            line["cpu_baseline"] = {"value": v, "unit": "agent-steps/s", "cores": threads, "kind": "port",
+                                    "sample": "%d steps of %d envs x %d agents, oracle/casim_oracle.c with %d POSIX threads"
+                                              % (n_steps, Es, A, threads)}
+        print(json.dumps(line), flush=True)
+    for s in sims:
+        s.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

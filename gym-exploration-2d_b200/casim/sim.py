@@ -21,7 +21,8 @@ def _stream_ptr(stream=None):
 
 
 class BatchedSim:
-    def __init__(self, num_envs, max_agents, cfg=None, device=None, sensors=(), want_debug=True, want_stats=True):
+    def __init__(self, num_envs, max_agents, cfg=None, device=None, sensors=(), want_debug=True, want_stats=True,
+                 want_misc=True, stats_buffer=None):
         """``cfg``: a SimConfig (default: snapshot of casim.config.Config).  ``sensors``: iterable of sensor
         bit masks / names for which observation buffers are allocated ("other_agents_states", "laserscan",
         "local_grid")."""
@@ -52,7 +53,7 @@ class BatchedSim:
                     names.add("local_grid")
         rows = self.cfg.max_other_agents_rows
         self.buf = {
-            "obs_misc": torch.zeros((E, A, 4), **f32),
+            "obs_misc": torch.zeros((E, A, 4), **f32) if want_misc else None,
             "other_agents_states": torch.zeros((E, A, rows, 10), **f32) if "other_agents_states" in names else None,
             "laserscan": torch.zeros((E, A, self.cfg.laser_num_beams), **f32) if "laserscan" in names else None,
             "local_grid": torch.zeros((E, A, self.cfg.submap_w, self.cfg.submap_h), **u8) if "local_grid" in names else None,
@@ -61,7 +62,7 @@ class BatchedSim:
             "game_over": torch.zeros((E,), **u8),
             "collision_flags": torch.zeros((E, A), **u8) if want_debug else None,
             "nearest_dist": torch.zeros((E, A), **f32) if want_debug else None,
-            "stats": torch.zeros((NUM_STATS,), **f32) if want_stats else None,
+            "stats": (stats_buffer if stats_buffer is not None else torch.zeros((NUM_STATS,), **f32)) if want_stats else None,
         }
         self._obs = self._obs_struct(self.buf)
         self._keep = {}          # tensors the library borrows (init, types, n_agents, traj)

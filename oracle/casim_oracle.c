@@ -599,7 +599,9 @@ static void step_range(const casim_config* c, int e0, int e1, int A, const int32
                        const double* ext_actions, const double* policy_actions, double dt,
                        const uint8_t* maps, int n_maps, const double* traj, int T, const double* init,
                        const int32_t* type0, const uint8_t* prev_game_over, const casim_oracle_obs* o,
-                       double* stats) {
+                       double* stats_out) {
+  double local_stats[CASIM_NUM_STATS] = {0}; /* thread-private: no false sharing between worker threads */
+  double* stats = stats_out ? local_stats : NULL;
   for (int e = e0; e < e1; e++) {
     int n = n_agents ? n_agents[e] : A;
     double* env = state + (size_t)e * A * NF;
@@ -723,6 +725,8 @@ static void step_range(const casim_config* c, int e0, int e1, int A, const int32
     if (o->game_over) o->game_over[e] = (uint8_t)go;
     if (stats) stats[3] += go;
   }
+  if (stats_out)
+    for (int k = 0; k < CASIM_NUM_STATS; k++) stats_out[k] += local_stats[k];
 }
 
 typedef struct step_job {
