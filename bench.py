@@ -220,6 +220,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of one CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=200)
+    ap.add_argument("--ring", type=int, default=None, help="override the number of env batches in the ring (diagnostics)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -256,6 +257,8 @@ def main():
         per_agent_resident += 3600 + 32
     batch_bytes = E * A * per_agent_resident
     R = int(min(max(2, -(-int(1.5 * L2_BYTES) // batch_bytes)), 96))
+    if args.ring:
+        R = args.ring
     stats_all = torch.zeros((max(K, Wm, args.e2e_steps), NUM_STATS), dtype=torch.float32, device=dev)
     sims = []
     for r in range(R):

@@ -124,6 +124,7 @@ static int derive(const casim_config* c, DevCfg* d) {
   d->wiggly_thr = c->wiggly_behavior_threshold;
   d->r_min = c->reward_min;
   d->r_max = c->reward_max;
+  d->r_inv_span = 1.0 / (c->reward_max - c->reward_min);
   d->close_range = c->getting_close_range;
   d->near_goal = c->near_goal_threshold;
   d->max_time_ratio = c->max_time_ratio;

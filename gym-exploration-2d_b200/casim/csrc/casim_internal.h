@@ -21,7 +21,7 @@
 struct DevCfg {
   double dt, dt_nominal;
   double r_at_goal, r_coll_agent, r_timeout, r_infeasible, r_coll_wall, r_time_step, r_dist_goal;
-  double r_wiggly, wiggly_thr, r_min, r_max;
+  double r_wiggly, wiggly_thr, r_min, r_max, r_inv_span;
   double close_range, near_goal, max_time_ratio, sensing_horizon, max_heading_change;
   double map_ox, map_oy; /* (width/2)/cell, (height/2)/cell : Map.py:31-32 */
   double cell, inv_cell;

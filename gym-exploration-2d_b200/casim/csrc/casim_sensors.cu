@@ -46,12 +46,15 @@ __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
   }
   const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[0];
   const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[1];
-  const double px = q0.x, py = q0.y, heading = q1.x, radius = q1.y;
+  const double px = q0.x, py = q0.y, ch = q1.x, sh = q1.y;
+  const double radius = (double)p.state[2 * N + g].z;
   const uint32_t* pl =
       p.n_maps > 0 ? p.map_planes + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_NUM_PLANES * CASIM_PLANE_WORDS : nullptr;
   int r0, c0;
-  const bool ego_in = world_to_map_div(c, px, py, r0, c0);
-  const double rc = radius / c.cell, rc2 = rc * rc;
+  const bool ego_in = world_to_map_mul(c, px, py, r0, c0);
+  const double rc = radius * c.inv_cell, rc2 = rc * rc;
+  /* integer form of the ego-disc test d^2 < rc2 (d^2 integer): d^2 <= ceil(rc2) - 1; no disc if out of map */
+  const int disc_thr = ego_in ? (int)fmin(ceil(rc2), 2.0e9) - 1 : -1;
   /* lanes per beam: 32 / next_pow2(nb) */
   int nbp = 1;
   while (nbp < nb) nbp <<= 1;
@@ -59,14 +62,16 @@ __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
   const int b = lane / P, part = lane - b * P;
   unsigned mask = 0;
   if (b < nb && pl) {
-    double sn, cs;
-    sincos(c.laser_ang[b] + heading, &sn, &cs);
+    /* beam direction cos/sin(angle_b + heading) by angle addition from the step kernel's cos/sin(heading);
+     * lattice point k in CELL units: col = floor(oy + (px + r_k cs)/cell), row = floor(ox - (py + r_k sn)/cell) */
+    const double cs = c.laser_cos[b] * ch - c.laser_sin[b] * sh, sn = c.laser_sin[b] * ch + c.laser_cos[b] * sh;
+    const double u0 = c.map_oy + px * c.inv_cell, du = cs * c.inv_cell;  /* column coordinate, cells */
+    const double v0 = c.map_ox - py * c.inv_cell, dv = -(sn * c.inv_cell); /* row coordinate, cells */
     for (int k = part; k < nr; k += P) {
-      double x = px + c.laser_r[k] * cs, y = py + c.laser_r[k] * sn;
-      int row, col;
-      if (world_to_map_mul(c, x, y, row, col) && map_bit(pl, row, col)) {
-        bool ego = ego_in && in_disc(row, col, r0, c0, rc2);
-        if (!ego) mask |= 1u << k;
+      int col = __double2int_rd(fma(c.laser_r[k], du, u0)), row = __double2int_rd(fma(c.laser_r[k], dv, v0));
+      if ((unsigned)row < (unsigned)CASIM_MAP_DIM && (unsigned)col < (unsigned)CASIM_MAP_DIM && map_bit(pl, row, col)) {
+        int dr = row - r0, dc = col - c0;
+        if (dr * dr + dc * dc > disc_thr) mask |= 1u << k;
       }
     }
   }
@@ -117,9 +122,9 @@ __global__ void __launch_bounds__(256) k_grid(const GridArgs p) {
   }
   const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[0];
   const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[1];
-  const double px = q0.x, py = q0.y, heading = q1.x;
+  const double px = q0.x, py = q0.y, ch = q1.x, sh = q1.y;
   int row0, col0;
-  world_to_map_div(c, px, py, row0, col0);
+  world_to_map_mul(c, px, py, row0, col0);
   /* Map.getSubmapByIndices (Map.py:81-105) */
   int sx = max(row0 - W / 2, 0), sy = max(col0 - H / 2, 0);
   int ex = sx + W, ey = sy + H;
@@ -134,10 +139,8 @@ __global__ void __launch_bounds__(256) k_grid(const GridArgs p) {
   const int nrows = min(ex - sx, W), ncols = min(ey - sy, H);
   if (threadIdx.x < 128) {
     /* cv2.getRotationMatrix2D(center=(col0,row0), angle=-heading*180/pi, 1) then warpAffine's inversion */
-    double angle_deg = -heading * 180 / CASIM_PI;
-    double ang = angle_deg * (CASIM_PI / 180);
-    double beta, alpha;
-    sincos(ang, &beta, &alpha);
+    /* angle = -heading (degrees and back in the reference): alpha = cos(heading), beta = -sin(heading) */
+    double alpha = ch, beta = -sh;
     double cx = (double)(float)col0, cy = (double)(float)row0;
     double M0 = alpha, M1 = beta, M2 = (1 - alpha) * cx - beta * cy;
     double M3 = -beta, M4 = alpha, M5 = beta * cx + (1 - alpha) * cy;

@@ -16,9 +16,23 @@
  * Thread mapping: one lane per agent; a warp holds floor(32/A) whole environments, so lane L of warp w
  * is element (w*epw*A + L) of every [E,A] array: all state loads/stores are contiguous float4 per warp.
  * Agents of an environment exchange their post-move pose with warp shuffles (no shared memory, no
- * barrier).  Every decision predicate is evaluated in fp64 on the fp32 state, like the float64
- * reference; state is stored back as fp32.  The observation rows are staged in shared memory and
- * written out as contiguous 16-byte stores.
+ * barrier).
+ *
+ * Arithmetic: the state is fp32, the reference is float64.  Everything a decision depends on (heading
+ * wrap, pose update, goal / timeout tests, pair distances, cell indices) is computed in fp64 from the fp32
+ * state exactly like the reference.  Two devices keep the fp64 instruction count low without giving up
+ * exact decisions:
+ *   - pair predicates are evaluated on SQUARED distances (no fp64 sqrt): with s = dx^2+dy^2 and the exact
+ *     c = r_i + r_j, "sqrt(s) <= c" is decided by s <= c^2 / s > c^2(1+4.5e-16); only the (astronomically
+ *     rare) band in between runs the exact sqrt.  The closest-N ordering and the GETTING_CLOSE test use
+ *     fp32 keys with a guard band; a warp in which any lane falls inside the band (|key difference| < 1e-4,
+ *     |nearest - 0.2| < 1e-5, or an exact tie) recomputes that decision with the reference's fp64 formula.
+ *   - the wall test "some occupied cell lies inside the agent's disc of cells" is min-over-occupied-cells
+ *     of the integer squared distance < (r/cell)^2, i.e. ONE lookup in the exact squared distance field
+ *     built at map-set time (casim_map.cu) instead of a scan over the disc.
+ * Quantities that are only reported (dist_to_goal, heading_ego, the observation rows, rewards) are
+ * evaluated in fp32 from fp64 differences (error ~1e-7, tolerance 1e-5).
+ * The observation rows are staged in shared memory and written out as contiguous 16-byte stores.
  */
 #include <stdio.h>
 
@@ -36,6 +50,7 @@ struct CoreArgs {
   const int32_t* type0;        /* [E*A] */
   const int32_t* n_agents;     /* [E] or NULL */
   const uint32_t* map_planes;  /* [n_maps][4][300][10] or NULL */
+  const int32_t* edf_d2;       /* [n_maps][300][300] exact squared distance (cells^2) to the nearest occupied cell */
   uint8_t* prev_game_over;     /* [E] */
   double* pose64;              /* [E*A][4] or NULL */
   double* partials;            /* [ctas][8] */
@@ -46,13 +61,12 @@ struct CoreArgs {
 };
 
 struct Agent {
-  double px, py, heading, speed;
-  double vx, vy, dheading, turning;
-  double gx, gy, radius, pref;
-  double t, trem, dgoal, pdgoal;
-  double a0v, a0w, a1v, a1w;
-  double hego;
+  /* decision-carrying words in fp64 (exact widening of the fp32 state), reported-only words in fp32 */
+  double px, py, heading, turning, t, trem;
+  double cs, sn; /* cos/sin of the heading when this step's dynamics computed them */
+  float speed, vx, vy, dheading, gx, gy, radius, pref, dgoal, pdgoal, a0v, a0w, a1v, a1w, hego;
   int step_num, flags, type;
+  bool have_cs;
 };
 
 __device__ __forceinline__ void load_agent(const float4* st, size_t plane, size_t g, Agent& a) {
@@ -67,25 +81,42 @@ __device__ __forceinline__ void load_agent(const float4* st, size_t plane, size_
   a.step_num = __float_as_int(p5.y);
   a.flags = __float_as_int(p5.z);
   a.type = __float_as_int(p5.w);
+  a.have_cs = false;
 }
 
 __device__ __forceinline__ void store_agent(float4* st, size_t plane, size_t g, const Agent& a, bool all) {
-  st[g] = make_float4((float)a.px, (float)a.py, (float)a.heading, (float)a.speed);
-  st[plane + g] = make_float4((float)a.vx, (float)a.vy, (float)a.dheading, (float)a.turning);
-  if (all) st[2 * plane + g] = make_float4((float)a.gx, (float)a.gy, (float)a.radius, (float)a.pref);
-  st[3 * plane + g] = make_float4((float)a.t, (float)a.trem, (float)a.dgoal, (float)a.pdgoal);
-  st[4 * plane + g] = make_float4((float)a.a0v, (float)a.a0w, (float)a.a1v, (float)a.a1w);
-  st[5 * plane + g] = make_float4((float)a.hego, __int_as_float(a.step_num), __int_as_float(a.flags),
-                                  __int_as_float(a.type));
+  st[g] = make_float4((float)a.px, (float)a.py, (float)a.heading, a.speed);
+  st[plane + g] = make_float4(a.vx, a.vy, a.dheading, (float)a.turning);
+  if (all) st[2 * plane + g] = make_float4(a.gx, a.gy, a.radius, a.pref);
+  st[3 * plane + g] = make_float4((float)a.t, (float)a.trem, a.dgoal, a.pdgoal);
+  st[4 * plane + g] = make_float4(a.a0v, a.a0w, a.a1v, a.a1w);
+  st[5 * plane + g] = make_float4(a.hego, __int_as_float(a.step_num), __int_as_float(a.flags), __int_as_float(a.type));
 }
 
-/* agent.py:250-269 get_ref */
-__device__ __forceinline__ void ref_axes(const Agent& a, double& p0, double& p1, double& dist) {
-  double gdx = a.gx - a.px, gdy = a.gy - a.py;
-  dist = sqrt(gdx * gdx + gdy * gdy);
-  if (dist > 1e-8) {
-    p0 = gdx / dist;
-    p1 = gdy / dist;
+/* util.py:27-32 wrap() for the common case (at most one turn off), same decisions as the loop */
+__device__ __forceinline__ double wrap_pi1(double a) {
+  if (a >= CASIM_PI) a -= CASIM_2PI;
+  if (a < -CASIM_PI) a += CASIM_2PI;
+  if (!(a >= -CASIM_PI && a < CASIM_PI)) a = wrap_pi(a);
+  return a;
+}
+
+__device__ __forceinline__ float wrap_pif(float a) {
+  const float PI = 3.14159265358979323846f, TWO_PI = 6.28318530717958647692f;
+  if (a >= PI) a -= TWO_PI;
+  if (a < -PI) a += TWO_PI;
+  if (!(a >= -PI && a < PI)) a = (float)wrap_pi((double)a);
+  return a;
+}
+
+/* agent.py:250-269 get_ref.  Reported quantities only: fp32 from the fp64 goal offset. */
+__device__ __forceinline__ void ref_axes(const Agent& a, float& p0, float& p1) {
+  float gdx = (float)((double)a.gx - a.px), gdy = (float)((double)a.gy - a.py);
+  float dist = sqrtf(gdx * gdx + gdy * gdy);
+  if (dist > 1e-8f) {
+    float inv = 1.0f / dist;
+    p0 = gdx * inv;
+    p1 = gdy * inv;
   } else {
     p0 = gdx;
     p1 = gdy;
@@ -94,27 +125,32 @@ __device__ __forceinline__ void ref_axes(const Agent& a, double& p0, double& p1,
 
 /* dynamics/Dynamics.py:14-28 update_ego_frame */
 __device__ __forceinline__ void update_ego_frame(Agent& a) {
-  double p0, p1, dist;
-  ref_axes(a, p0, p1, dist);
+  float gdx = (float)((double)a.gx - a.px), gdy = (float)((double)a.gy - a.py);
+  float dist = sqrtf(gdx * gdx + gdy * gdy);
   a.pdgoal = a.dgoal;
   a.dgoal = dist;
   if (a.t == 0.0) a.pdgoal = dist;
-  a.hego = wrap_pi(a.heading - atan2(p1, p0));
+  /* atan2(ref_prll) == atan2(goal offset): the normalisation (or its 1e-8 guard) does not change the angle */
+  a.hego = wrap_pif((float)a.heading - atan2f(gdy, gdx));
 }
 
 /* agent.py:9-112 Agent.__init__ */
 __device__ __forceinline__ void agent_init(const DevCfg& c, const float* in, int type, Agent& a) {
-  double sx = in[0], sy = in[1], gx = in[2], gy = in[3], radius = in[4], pref = in[5];
+  double sx = in[0], sy = in[1], gx = in[2], gy = in[3], pref = in[5];
   float h = in[6];
-  a.px = sx; a.py = sy; a.gx = gx; a.gy = gy; a.radius = radius; a.pref = pref;
+  a.px = sx; a.py = sy; a.gx = in[2]; a.gy = in[3]; a.radius = in[4]; a.pref = in[5];
   a.heading = isnan(h) ? atan2(gy - sy, gx - sx) : (double)h;
   a.speed = 0; a.vx = 0; a.vy = 0; a.dheading = 0; a.turning = 0;
   a.t = 0; a.dgoal = 0; a.pdgoal = 0; a.a0v = a.a0w = a.a1v = a.a1w = 0; a.hego = 0;
   a.step_num = 0; a.flags = 0; a.type = type;
+  a.have_cs = false;
   double dx = sx - gx, dy = sy - gy;
   double straight = (sqrt(dx * dx + dy * dy) - c.near_goal) / pref;
   a.trem = c.max_time_ratio * straight;
   update_ego_frame(a);
+  /* With auto-reset the policy reads this heading_ego within the same launch, so it is evaluated in fp64 and
+   * rounded once, exactly like the reference's stored value (a fresh episode is off the per-step fast path). */
+  a.hego = (float)wrap_pi(a.heading - atan2(gy - sy, gx - sx));
 }
 
 /* collision_avoidance_env.py:298-320: the action each policy contributes, rounded to fp32 (:289) */
@@ -125,8 +161,8 @@ __device__ __forceinline__ void choose_action(const DevCfg& c, const Agent& a, c
   if (a.flags & CASIM_F_IS_DONE) return;
   switch (a.type & 0xff) {
     case CASIM_POLICY_NONCOOPERATIVE: /* NonCooperativePolicy.py:10-13 */
-      a0 = (float)a.pref;
-      a1 = (float)(-a.hego);
+      a0 = a.pref;
+      a1 = -a.hego;
       break;
     case CASIM_POLICY_EXTERNAL:
       if (ext) {
@@ -137,7 +173,7 @@ __device__ __forceinline__ void choose_action(const DevCfg& c, const Agent& a, c
     case CASIM_POLICY_LEARNING: /* LearningPolicy.py:11-16 */
       if (ext) {
         double heading = c.max_heading_change * (2. * (double)ext[2 * g + 1] - 1.);
-        double speed = a.pref * (double)ext[2 * g];
+        double speed = (double)a.pref * (double)ext[2 * g];
         a0 = (float)speed;
         a1 = (float)heading;
       }
@@ -175,38 +211,42 @@ __device__ __forceinline__ void dynamics_step(const DevCfg& c, Agent& a, float a
     float4 row = *reinterpret_cast<const float4*>(traj + (g * (size_t)T + k) * 4);
     double heading = atan2((double)row.z, (double)row.w) - a.heading; /* x/y swapped, sic */
     double px = row.x, py = row.y;
-    if (a.step_num == 0) {
-      a.vx = 0;
-      a.vy = 0;
-    } else {
-      a.vx = (px - a.px) / c.dt_nominal;
-      a.vy = (py - a.py) / c.dt_nominal;
+    double vx = 0, vy = 0;
+    if (a.step_num != 0) {
+      vx = (px - a.px) / c.dt_nominal;
+      vy = (py - a.py) / c.dt_nominal;
     }
-    a.dheading = wrap_pi(heading - a.heading);
+    a.vx = (float)vx;
+    a.vy = (float)vy;
+    a.dheading = (float)wrap_pi(heading - a.heading);
     a.px = px;
     a.py = py;
-    a.speed = sqrt(a.vx * a.vx + a.vy * a.vy);
+    a.speed = (float)sqrt(vx * vx + vy * vy);
     a.heading = heading;
     return;
   }
   double speed = (double)a0, sel;
   if (dyn == CASIM_DYN_FIRST_ORDER) /* FirstOrderDynamics.py:10-23 */
-    sel = wrap_pi((double)a1 * dt + a.heading);
+    sel = wrap_pi1((double)a1 * dt + a.heading);
   else if (dyn == CASIM_DYN_UNICYCLE_MAX_TURN_RATE) { /* UnicycleDynamicsMaxTurnRate.py:11-26 */
     double rate = (double)a1 / dt;
     rate = fmin(fmax(rate, -3.0), 3.0);
-    sel = wrap_pi(rate * dt + a.heading);
+    sel = wrap_pi1(rate * dt + a.heading);
   } else /* UnicycleDynamics.py:10-31 */
-    sel = wrap_pi((double)a1 + a.heading);
+    sel = wrap_pi1((double)a1 + a.heading);
   double sn, cs;
   sincos(sel, &sn, &cs);
-  a.px += speed * cs * dt;
-  a.py += speed * sn * dt;
-  a.vx = speed * cs;
-  a.vy = speed * sn;
-  a.speed = speed;
-  a.dheading = wrap_pi(sel - a.heading);
+  double vx = speed * cs, vy = speed * sn;
+  a.px += vx * dt;
+  a.py += vy * dt;
+  a.vx = (float)vx;
+  a.vy = (float)vy;
+  a.speed = a0;
+  a.dheading = (float)wrap_pi1(sel - a.heading);
   a.heading = sel;
+  a.cs = cs;
+  a.sn = sn;
+  a.have_cs = true;
   if (dyn == CASIM_DYN_UNICYCLE) {
     double td = a.turning;
     if (fabs(td) < 1e-5)
@@ -234,11 +274,11 @@ __device__ __forceinline__ void take_action(const DevCfg& c, Agent& a, float a0,
   }
   a.a1v = a.a0v;
   a.a1w = a.a0w;
-  a.a0v = (double)a0;
-  a.a0w = (double)a1;
+  a.a0v = a0;
+  a.a0w = a1;
   dynamics_step(c, a, a0, a1, dt, traj, T, g);
   update_ego_frame(a);
-  double ex = a.px - a.gx, ey = a.py - a.gy;
+  double ex = a.px - (double)a.gx, ey = a.py - (double)a.gy;
   if (ex * ex + ey * ey <= c.near_goal * c.near_goal)
     flags |= CASIM_F_IS_AT_GOAL;
   else
@@ -250,10 +290,13 @@ __device__ __forceinline__ void take_action(const DevCfg& c, Agent& a, float a0,
   a.flags = flags;
 }
 
+#define CASIM_CORE_THREADS 64
+#define CASIM_CORE_WARPS (CASIM_CORE_THREADS / 32)
+
 template <int MODE, int AP>
-__global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
+__global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   extern __shared__ __align__(16) float s_stage[];
-  __shared__ double s_part[4][CASIM_NUM_STATS];
+  __shared__ double s_part[CASIM_CORE_WARPS][CASIM_NUM_STATS];
   __shared__ bool s_last;
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
@@ -285,10 +328,11 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
       }
     }
   } else {
-    a = Agent();
-    a.px = a.py = a.heading = a.speed = a.vx = a.vy = a.dheading = a.turning = a.gx = a.gy = a.radius = a.pref =
-        a.t = a.trem = a.dgoal = a.pdgoal = a.a0v = a.a0w = a.a1v = a.a1w = a.hego = 0;
+    a.px = a.py = a.heading = a.turning = a.t = a.trem = a.cs = a.sn = 0;
+    a.speed = a.vx = a.vy = a.dheading = a.gx = a.gy = a.radius = a.pref = a.dgoal = a.pdgoal = 0.f;
+    a.a0v = a.a0w = a.a1v = a.a1w = a.hego = 0.f;
     a.step_num = a.flags = a.type = 0;
+    a.have_cs = false;
   }
 
   if (MODE == CASIM_MODE_STEP && valid) {
@@ -298,42 +342,88 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
     take_action(c, a, a0, a1, p.dt, p.traj, p.T, g);
   }
 
-  /* ---- all pairs of my environment: distances to every other agent (registers, static indexing) ---- */
+  /* ---- all pairs of my environment ---- */
   const bool me_static = (a.type & 0xff) == CASIM_POLICY_STATIC;
   const int sensors = (a.type >> 16) & 0xff;
   const bool want_oas = p.o.other_agents_states != nullptr;
-  double dist[AP];
-  bool coll_agent = false;
-  double nearest = INFINITY;
+  const double rme = (double)a.radius;
+  float d32[AP];
+  bool coll_agent = false, amb = false;
+  float nearest = INFINITY;
+  if (MODE == CASIM_MODE_STEP || want_oas) {
 #pragma unroll
-  for (int j = 0; j < AP; j++) {
-    int src = (base + j) & 31;
-    double ox = __shfl_sync(FULL_MASK, a.px, src), oy = __shfl_sync(FULL_MASK, a.py, src);
-    float orad = __shfl_sync(FULL_MASK, (float)a.radius, src);
-    int ostatic = __shfl_sync(FULL_MASK, (int)me_static, src);
-    double dx = a.px - ox, dy = a.py - oy;
-    double d = sqrt(dx * dx + dy * dy);
-    dist[j] = d;
-    if (MODE == CASIM_MODE_STEP && valid && j < n && j != ai) {
-      /* pair (lo, hi): skipped when the HIGHER index is Static (collision_avoidance_env.py:643-644) */
-      bool hi_static = j > ai ? (ostatic != 0) : me_static;
-      if (!(hi_static && !c.coll_w_static)) {
-        double cr = j > ai ? a.radius + (double)orad : (double)orad + a.radius;
-        if (j > ai) nearest = fmin(nearest, d - cr); /* :649 lower index only */
-        if (d <= cr) coll_agent = true;
+    for (int j = 0; j < AP; j++) {
+      int src = (base + j) & 31;
+      double ox = __shfl_sync(FULL_MASK, a.px, src), oy = __shfl_sync(FULL_MASK, a.py, src);
+      float orad = __shfl_sync(FULL_MASK, a.radius, src);
+      int ostatic = __shfl_sync(FULL_MASK, (int)me_static, src);
+      double dx = a.px - ox, dy = a.py - oy;
+      double s = dx * dx + dy * dy;
+      float d = sqrtf((float)s);
+      d32[j] = d;
+      if (MODE == CASIM_MODE_STEP && valid && j < n && j != ai) {
+        /* pair (lo, hi): skipped when the HIGHER index is Static (collision_avoidance_env.py:643-644) */
+        bool hi_static = j > ai ? (ostatic != 0) : me_static;
+        if (!(hi_static && !c.coll_w_static)) {
+          double cr = rme + (double)orad; /* exact: both radii are fp32 values */
+          double t = cr * cr;             /* exact: <= 50 significant bits */
+          if (s <= t)
+            coll_agent = true;                 /* sqrt(s) <= cr, hence fl(sqrt(s)) <= cr */
+          else if (s <= t * (1.0 + 4.5e-16))
+            amb = true;                        /* fl(sqrt(s)) may still round down onto cr */
+          if (j > ai) { /* :649 lower index only; value reported / used with a guard band */
+            float gap = (float)(s - t) / fmaxf(d + (float)cr, 1e-30f);
+            nearest = fminf(nearest, gap);
+          }
+        }
       }
+    }
+  }
+  bool close = nearest <= (float)c.close_range;
+  if (MODE == CASIM_MODE_STEP) {
+    if (fabsf(nearest - (float)c.close_range) < 1e-5f) amb = true;
+    if (__any_sync(FULL_MASK, amb)) {
+      /* exact path: the reference's own fp64 formulas (collision_avoidance_env.py:640-655) */
+      bool ce = false;
+      double ne = INFINITY;
+#pragma unroll 1
+      for (int j = 0; j < AP; j++) {
+        int src = (base + j) & 31;
+        double ox = __shfl_sync(FULL_MASK, a.px, src), oy = __shfl_sync(FULL_MASK, a.py, src);
+        float orad = __shfl_sync(FULL_MASK, a.radius, src);
+        int ostatic = __shfl_sync(FULL_MASK, (int)me_static, src);
+        if (valid && j < n && j != ai) {
+          bool hi_static = j > ai ? (ostatic != 0) : me_static;
+          if (!(hi_static && !c.coll_w_static)) {
+            double dx = a.px - ox, dy = a.py - oy;
+            double dd = sqrt(dx * dx + dy * dy);
+            double cr = rme + (double)orad;
+            if (j > ai) ne = fmin(ne, dd - cr);
+            if (dd <= cr) ce = true;
+          }
+        }
+      }
+      coll_agent = ce;
+      nearest = (float)ne;
+      close = ne <= c.close_range;
     }
   }
 
   bool coll_wall = false;
   float reward = 0.f;
   bool done = false;
-  double st_new_coll = 0, st_new_goal = 0, st_new_to = 0, st_rew = 0, st_active = 0, st_agents = 0, st_go = 0;
+  int st_new_coll = 0, st_new_goal = 0, st_new_to = 0, st_active = 0, st_agents = 0, st_go = 0;
+  double st_rew = 0;
   if (MODE == CASIM_MODE_STEP) {
-    if (valid && p.n_maps > 0) { /* :656-666 */
-      const uint32_t* pl = p.map_planes + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_NUM_PLANES * CASIM_PLANE_WORDS;
+    if (valid && p.n_maps > 0) {
+      /* :656-666 + Map.py:67-71: an occupied cell inside the disc (col-c0)^2+(row-r0)^2 < (r/cell)^2
+       * <=> the exact squared distance from the agent's cell to the nearest occupied cell is < (r/cell)^2 */
       int r0, c0;
-      if (world_to_map_div(c, a.px, a.py, r0, c0)) coll_wall = disc_hits_map(c, pl, r0, c0, a.radius);
+      if (world_to_map_mul(c, a.px, a.py, r0, c0)) {
+        const int32_t* ed = p.edf_d2 + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
+        double rc = rme * c.inv_cell;
+        coll_wall = (double)__ldg(ed + r0 * CASIM_MAP_DIM + c0) < rc * rc;
+      }
     }
     if (valid) { /* _compute_rewards :502-567 */
       int flags = a.flags;
@@ -349,17 +439,19 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
             r = c.r_coll_wall;
             flags |= CASIM_F_IN_COLLISION;
           } else {
-            if (nearest <= c.close_range) r += -0.1 - nearest / 2.;
-            double wv = a.a1v - a.a0v, ww = a.a1w - a.a0w;
-            if (sqrt(wv * wv + ww * ww) > c.wiggly_thr) r += c.r_wiggly;
+            if (close) r += -0.1 - (double)nearest / 2.;
+            if (c.r_wiggly != 0.0) {
+              double wv = (double)a.a1v - (double)a.a0v, ww = (double)a.a1w - (double)a.a0w;
+              if (sqrt(wv * wv + ww * ww) > c.wiggly_thr) r += c.r_wiggly;
+            }
           }
         } else if (flags & CASIM_F_RAN_OUT_OF_TIME)
           r += c.r_timeout;
         if (flags & CASIM_F_IS_INFEASIBLE) r += c.r_infeasible;
-        r += c.r_dist_goal * (a.pdgoal - a.dgoal);
+        if (c.r_dist_goal != 0.0) r += c.r_dist_goal * ((double)a.pdgoal - (double)a.dgoal);
       }
       r = fmin(fmax(r, c.r_min), c.r_max);
-      r = r / (c.r_max - c.r_min);
+      r = r * c.r_inv_span;
       /* _check_which_agents_done :711-720 */
       done = (flags & (CASIM_F_IS_AT_GOAL | CASIM_F_RAN_OUT_OF_TIME | CASIM_F_IN_COLLISION)) != 0;
       if (done)
@@ -377,7 +469,7 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
       st_agents = 1;
     }
     /* game over :722-736 */
-    unsigned envmask = (A == 32 ? 0xffffffffu : ((1u << A) - 1u)) << base;
+    unsigned envmask = (A == 32 ? 0xffffffffu : ((1u << A) - 1u)) << (base & 31);
     bool learning = (a.type & 0xff) == CASIM_POLICY_LEARNING;
     unsigned b_all = __ballot_sync(FULL_MASK, done || !valid);
     unsigned b_learn = __ballot_sync(FULL_MASK, done || !valid || !learning);
@@ -398,7 +490,7 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
       if (p.o.rewards) p.o.rewards[g] = reward;
       if (p.o.done) p.o.done[g] = (uint8_t)done;
       if (p.o.collision_flags) p.o.collision_flags[g] = (uint8_t)((coll_agent ? 1 : 0) | (coll_wall ? 2 : 0));
-      if (p.o.nearest_dist) p.o.nearest_dist[g] = valid ? (float)nearest : 0.f;
+      if (p.o.nearest_dist) p.o.nearest_dist[g] = valid ? nearest : 0.f;
     }
   } else if (MODE == CASIM_MODE_RESET) {
     if (slot && ai == 0) p.prev_game_over[e] = 0;
@@ -410,10 +502,11 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
   } else if (MODE == CASIM_MODE_RESET) {
     if (slot) store_agent(p.state, plane, g, a, true);
   }
-  if (p.write_pose && slot) {
+  if (p.write_pose && slot) { /* fp64 pose for the sensor kernels: px, py, cos(heading), sin(heading) */
+    if (!a.have_cs) sincos(a.heading, &a.sn, &a.cs);
     double2* q = reinterpret_cast<double2*>(p.pose64 + 4 * g);
     q[0] = make_double2(a.px, a.py);
-    q[1] = make_double2(a.heading, a.radius);
+    q[1] = make_double2(a.cs, a.sn);
   }
 
   /* ---- OtherAgentsStatesSensor (OtherAgentsStatesSensor.py:11-77) ---- */
@@ -424,15 +517,19 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
     float* stage = s_stage + (size_t)warp_in_cta * 32 * rowlen;
     float* mine = stage + lane * rowlen;
     const bool sense = valid && (sensors & CASIM_SENSOR_OTHER_AGENTS);
-    /* keys + ranks: ascending stable order of (dist - r_h - r_o), ties -> lower index first */
-    double key[AP];
+    const float horizon = (float)c.sensing_horizon;
+    /* ascending stable order of key = dist - r_h - r_o (ties -> lower index first): fp32 keys, guard band */
+    float key[AP];
     int rank[AP];
     int m = 0;
+    bool amb_rank = false;
 #pragma unroll
     for (int j = 0; j < AP; j++) {
-      float orad = __shfl_sync(FULL_MASK, (float)a.radius, (base + j) & 31);
-      bool ok = sense && j < n && j != ai && !(dist[j] > c.sensing_horizon);
-      key[j] = ok ? dist[j] - a.radius - (double)orad : INFINITY;
+      float orad = __shfl_sync(FULL_MASK, a.radius, (base + j) & 31);
+      bool cand = sense && j < n && j != ai;
+      bool ok = cand && !(d32[j] > horizon);
+      if (cand && fabsf(d32[j] - horizon) < 1e-4f + 2e-6f * horizon) amb_rank = true;
+      key[j] = ok ? d32[j] - a.radius - orad : INFINITY;
       rank[j] = 0;
       m += ok;
     }
@@ -440,15 +537,44 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
     for (int j = 0; j < AP; j++)
 #pragma unroll
       for (int k = j + 1; k < AP; k++) {
-        bool kfirst = key[k] < key[j];
+        float diff = key[k] - key[j];
+        bool kfirst = diff < 0.f;
         rank[j] += kfirst;
         rank[k] += !kfirst;
+        if (fabsf(diff) < 1e-4f + 2e-6f * fabsf(key[j])) amb_rank = true;
       }
+    if (__any_sync(FULL_MASK, amb_rank)) {
+      /* exact path: the reference's fp64 keys (OtherAgentsStatesSensor.py:22-29) decide the order */
+      double key64[AP];
+      m = 0;
+#pragma unroll
+      for (int j = 0; j < AP; j++) {
+        int src = (base + j) & 31;
+        double ox = __shfl_sync(FULL_MASK, a.px, src), oy = __shfl_sync(FULL_MASK, a.py, src);
+        float orad = __shfl_sync(FULL_MASK, a.radius, src);
+        double dx = a.px - ox, dy = a.py - oy;
+        double dd = sqrt(dx * dx + dy * dy);
+        bool ok = sense && j < n && j != ai && !(dd > c.sensing_horizon);
+        key64[j] = ok ? dd - rme - (double)orad : INFINITY;
+        key[j] = ok ? key[j] : INFINITY;
+        if (ok && !(key[j] < INFINITY)) key[j] = (float)key64[j];
+        rank[j] = 0;
+        m += ok;
+      }
+#pragma unroll
+      for (int j = 0; j < AP; j++)
+#pragma unroll
+        for (int k = j + 1; k < AP; k++) {
+          bool kfirst = key64[k] < key64[j];
+          rank[j] += kfirst;
+          rank[k] += !kfirst;
+        }
+    }
     const int K = min(m, c.max_obs);
     nobs = min(K, rows);
-    double p0 = 0, p1 = 0, dgoal;
-    ref_axes(a, p0, p1, dgoal);
-    const double q0 = -p1, q1 = p0;
+    float p0 = 0.f, p1 = 0.f;
+    ref_axes(a, p0, p1);
+    const float q0 = -p1, q1 = p0;
     if (slot)
       for (int r = nobs; r < rows; r++)
 #pragma unroll
@@ -457,23 +583,22 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
     for (int j = 0; j < AP; j++) {
       int src = (base + j) & 31;
       double ox = __shfl_sync(FULL_MASK, a.px, src), oy = __shfl_sync(FULL_MASK, a.py, src);
-      double ovx = __shfl_sync(FULL_MASK, a.vx, src), ovy = __shfl_sync(FULL_MASK, a.vy, src);
-      float orad = __shfl_sync(FULL_MASK, (float)a.radius, src);
+      float ovx = __shfl_sync(FULL_MASK, a.vx, src), ovy = __shfl_sync(FULL_MASK, a.vy, src);
+      float orad = __shfl_sync(FULL_MASK, a.radius, src);
       int ostatic = __shfl_sync(FULL_MASK, (int)me_static, src);
-      bool ok = sense && j < n && j != ai && !(dist[j] > c.sensing_horizon);
       int row = K - 1 - rank[j];
-      if (ok && rank[j] < K && row < rows) {
-        double rx = ox - a.px, ry = oy - a.py;
+      if (key[j] < INFINITY && rank[j] < K && row < rows) {
+        float rx = (float)(ox - a.px), ry = (float)(oy - a.py);
         float* wr = mine + row * 10;
-        wr[0] = (float)rx;
-        wr[1] = (float)ry;
-        wr[2] = (float)(rx * p0 + ry * p1);
-        wr[3] = (float)(rx * q0 + ry * q1);
-        wr[4] = (float)(ovx * p0 + ovy * p1);
-        wr[5] = (float)(ovx * q0 + ovy * q1);
+        wr[0] = rx;
+        wr[1] = ry;
+        wr[2] = rx * p0 + ry * p1;
+        wr[3] = rx * q0 + ry * q1;
+        wr[4] = ovx * p0 + ovy * p1;
+        wr[5] = ovx * q0 + ovy * q1;
         wr[6] = orad;
-        wr[7] = (float)(a.radius + (double)orad);
-        wr[8] = (float)(sqrt(rx * rx + ry * ry) - a.radius - (double)orad);
+        wr[7] = a.radius + orad;
+        wr[8] = key[j];
         wr[9] = ostatic ? 1.f : 2.f;
       }
     }
@@ -495,19 +620,21 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
   if (p.o.obs_misc && slot) { /* rel_goal (Dynamics.py:28), num_other_agents, use_ppo (config.py:208-213) */
     float4 mo = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid)
-      mo = make_float4((float)(a.gx - a.px), (float)(a.gy - a.py), (float)nobs,
+      mo = make_float4((float)((double)a.gx - a.px), (float)((double)a.gy - a.py), (float)nobs,
                        (a.type & 0xff) == CASIM_POLICY_LEARNING ? 1.f : 0.f);
     reinterpret_cast<float4*>(p.o.obs_misc)[g] = mo;
   }
 
   /* ---- per-step statistics: warp -> CTA -> last block (deterministic, atomic-free on the data) ---- */
   if (MODE == CASIM_MODE_STEP && p.o.stats) {
-    double v[CASIM_NUM_STATS] = {st_new_coll, st_new_goal, st_new_to, st_go, st_rew, st_active, st_agents, 0.0};
-#pragma unroll
-    for (int k = 0; k < 7; k++) v[k] = warp_sum(v[k]);
-    if (lane == 0)
-#pragma unroll
-      for (int k = 0; k < CASIM_NUM_STATS; k++) s_part[warp_in_cta][k] = v[k];
+    int c0 = __reduce_add_sync(FULL_MASK, st_new_coll), c1 = __reduce_add_sync(FULL_MASK, st_new_goal);
+    int c2 = __reduce_add_sync(FULL_MASK, st_new_to), c3 = __reduce_add_sync(FULL_MASK, st_go);
+    int c5 = __reduce_add_sync(FULL_MASK, st_active), c6 = __reduce_add_sync(FULL_MASK, st_agents);
+    double rs = warp_sum(st_rew);
+    if (lane == 0) {
+      double* sp = s_part[warp_in_cta];
+      sp[0] = c0; sp[1] = c1; sp[2] = c2; sp[3] = c3; sp[4] = rs; sp[5] = c5; sp[6] = c6; sp[7] = 0;
+    }
     __syncthreads();
     if (threadIdx.x < CASIM_NUM_STATS) {
       double s = 0;
@@ -526,7 +653,7 @@ __global__ void __launch_bounds__(128) k_core(const CoreArgs p) {
 #pragma unroll
       for (int k = 0; k < CASIM_NUM_STATS; k++) {
         double s = 0;
-        for (int b = lane; b < (int)gridDim.x; b += 32) s += p.partials[(size_t)b * CASIM_NUM_STATS + k];
+        for (int b = lane; b < (int)gridDim.x; b += 32) s += __ldcg(p.partials + (size_t)b * CASIM_NUM_STATS + k);
         s = warp_sum(s);
         if (lane == 0) p.o.stats[k] = (float)s;
       }
@@ -576,6 +703,7 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
   a.type0 = h->type0;
   a.n_agents = h->n_agents;
   a.map_planes = h->map_planes;
+  a.edf_d2 = h->edf_d2;
   a.n_maps = h->n_maps;
   a.prev_game_over = h->prev_game_over;
   a.pose64 = h->pose64;
@@ -596,7 +724,7 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
     }
   int warps = (h->E + a.epw - 1) / a.epw;
   size_t per_warp = obs->other_agents_states ? (size_t)32 * h->dc.rows * 10 * sizeof(float) : 0;
-  int wpc = 4;
+  int wpc = CASIM_CORE_WARPS;
   while (wpc > 1 && per_warp * wpc > 96 * 1024) wpc >>= 1;
   dim3 block(32 * wpc), grid((warps + wpc - 1) / wpc);
   if ((int)grid.x > h->max_ctas) return cudaErrorInvalidConfiguration;

@@ -50,8 +50,12 @@ def assert_state_close(s, ref, n_agents, what):
         n = int(n_agents[e])
         for k in L.INT_WORDS:
             assert np.array_equal(s[e, :n, k], ref[e, :n, k]), (what, "word", k, "env", e, s[e, :n, k], ref[e, :n, k])
-        # angles may differ by the wrap convention only within tolerance; compare directly
-        assert_close(s[e, :n][:, CONT_WORDS], ref[e, :n][:, CONT_WORDS], "%s env %d" % (what, e))
+        a, b = s[e, :n][:, CONT_WORDS].copy(), ref[e, :n][:, CONT_WORDS]
+        # heading_ego is reported in fp32: at the +-pi branch cut it may land on the other side (same angle)
+        k = CONT_WORDS.index(L.HEADING_EGO)
+        d = a[:, k] - b[:, k]
+        a[:, k] = b[:, k] + (d + np.pi) % (2 * np.pi) - np.pi
+        assert_close(a, b, "%s env %d" % (what, e))
 
 
 # ---------------------------------------------------------------------------------------------
