@@ -1,0 +1,125 @@
+"""TEST INFRASTRUCTURE -- generates tests/golden/explore.npz by running the UNMODIFIED reference classes
+edfMap / targetMap / ig_greedy (gym_collision_avoidance/envs/information_models/, policies/ig_greedy.py)
+in the build container.  Run through ``python oracle/gen_golden.py explore``.
+
+The one shim: ig_greedy.find_next_action calls targetMap.update(pose, targets) with a bare pose
+(ig_greedy.py:39) which raises once a target is detected; the harness wraps update() so that it receives
+([pose], [targets]) -- the form ig_mcts.update_belief uses (ig_mcts.py:117-133).  No reference source is edited.
+"""
+import os
+import types
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(os.path.dirname(_HERE), "tests", "golden")
+
+CROSSING = [[2, 10, 10, 2], [-10, 10, -2, 2], [2, -2, 10, -10], [-10, -2, -2, -10]]
+HALLWAY = [[3, 7, 10, -7], [-10, 7, -3, -7], [-10.5, 10, -10, -10], [10.5, 10, 10, -10]]
+# not symmetric in y: exposes the vertical mirroring between Map.static_map and edfMap indexing
+ASYM = [[-12, 12, -4, 9], [1, 6, 3, -1], [5, -3, 12, -5], [-9, -4, -6, -12], [-2, 13, 9, 11.5]]
+MAPS = [CROSSING, HALLWAY, ASYM]
+
+
+def obstacles_of(rects):
+    """rect (x1, y1, x3, y3) -> the reference's obstacle format: 4 corners of which Map.get_occupancy_grid reads
+    index 1 (top-left) and index 3 (bottom-right) (Map.py:117-118, envs/test_cases.py:3081-3084)"""
+    return [[(r[2], r[1]), (r[0], r[1]), (r[0], r[3]), (r[2], r[3])] for r in rects]
+
+
+def make_policy(ns, ref_map, radius):
+    pol = ns.ig_greedy()
+    ego = types.SimpleNamespace(radius=float(radius))
+    pol.init_maps(ego, ref_map, (30, 30), 0.1, 60.0, 5.0, dt=0.1)
+    orig = pol.targetMap.update
+    pol.targetMap.update = lambda pose, targets, frame='global': orig([pose], [targets], frame=frame)
+    return pol
+
+
+def free_pose(rng, edf, radius):
+    for _ in range(10000):
+        p = np.float32(rng.uniform(-13.5, 13.5, 2)).astype(np.float64)
+        if edf.get_edf_value_from_pose(p) > radius + 0.05:
+            return p
+    raise RuntimeError("no free pose")
+
+
+def main(ns, ncases=48, seed=2024):
+    rng = np.random.default_rng(seed)
+    ref_maps = [ns.Map(30, 30, 0.1, obstacles_of(r)) for r in MAPS]
+    out = {"rects_%d" % k: np.array(r, np.float64) for k, r in enumerate(MAPS)}
+    for k, m in enumerate(ref_maps):
+        out["static_%d" % k] = np.packbits(m.static_map.astype(np.uint8))
+        e = ns.edfMap(m, 0.1, (30, 30))
+        d2 = np.rint((e.map / 0.1) ** 2).astype(np.int32)
+        assert np.array_equal(np.sqrt(d2.astype(np.float64)) * 0.1, e.map)      # EDT == sqrt(int) * cell, exactly
+        out["edf_d2_%d" % k] = d2
+    rec = {k: [] for k in ("map_id", "pose", "radius", "oas", "belief0", "vis", "occ", "action", "cand_mi", "best_mi",
+                           "n_targets")}
+    for case in range(ncases):
+        mid = case % len(MAPS)
+        radius = float(np.float32(rng.choice([0.2, 0.35, 0.5])))
+        pol = make_policy(ns, ref_maps[mid], radius)
+        p = free_pose(rng, pol.edfMap, radius)
+        heading = float(np.float32(rng.uniform(-np.pi, np.pi)))
+        if case % 7 == 3:       # hug a wall so that some candidate next poses are infeasible
+            for _ in range(200):
+                q = free_pose(rng, pol.edfMap, radius)
+                if pol.edfMap.get_edf_value_from_pose(q) < radius + 0.3:
+                    p = q
+                    break
+        # other_agents_states rows: zero-padded [9,10]; a few Static (type 1) and dynamic (type 2) agents
+        oas = np.zeros((9, 10))
+        n_rows = int(rng.integers(0, 5))
+        for r in range(n_rows):
+            if rng.random() < 0.7:   # in front of the agent, often inside FOV / range
+                d, a = rng.uniform(0.5, 6.0), heading + rng.uniform(-0.7, 0.7)
+            else:
+                d, a = rng.uniform(0.5, 9.0), rng.uniform(-np.pi, np.pi)
+            oas[r, 0], oas[r, 1] = np.float32(d * np.cos(a)), np.float32(d * np.sin(a))
+            oas[r, 2:9] = np.float32(rng.uniform(-1, 1, 7))
+            oas[r, 9] = 1.0 if rng.random() < 0.7 else 2.0
+        # non-trivial belief: products of rOcc / rEmp powers, rounded to fp32 (the GPU stores fp32 odds)
+        a = rng.integers(0, 4, (60, 60)) * (rng.random((60, 60)) < 0.3)
+        b = rng.integers(0, 6, (60, 60)) * (rng.random((60, 60)) < 0.5)
+        belief0 = np.float32(1.5 ** a * 0.66 ** b)
+        if case % 5 == 0:
+            belief0[:] = 1.0
+        pol.targetMap.map = belief0.astype(np.float64).copy()
+        obs = {"pos_global_frame": p.copy(), "heading_global_frame": heading, "other_agents_states": oas.copy()}
+        pose = np.append(p, heading)
+        targets = pol.find_targets_in_obs(obs)
+        action = pol.find_next_action(obs, None, 0, None)
+        after = pol.targetMap.map
+        ratio = after / belief0.astype(np.float64)
+        vis = ~np.isclose(ratio, 1.0)
+        occ = np.isclose(ratio, 1.5)
+        assert np.all(np.isclose(ratio[vis & ~occ], 0.66))
+        cand = []
+        for v in (0.0, 2.0, 4.0):
+            for w in (-np.pi, 0, np.pi):
+                nxt = pol.get_next_pose(pose, np.array([v, w]))
+                cand.append(-1.0 if nxt is None else pol.targetMap.get_reward_from_pose(nxt))
+        cand = np.array(cand)
+        if isinstance(action, np.ndarray):
+            act = action.astype(np.float64)
+            best = cand.max()
+        else:
+            act = np.array([-1.0, -1.0])
+            best = -1.0
+        rec["map_id"].append(mid); rec["pose"].append(pose); rec["radius"].append(radius); rec["oas"].append(oas)
+        rec["belief0"].append(belief0); rec["vis"].append(np.packbits(vis)); rec["occ"].append(np.packbits(occ))
+        rec["action"].append(act); rec["cand_mi"].append(cand); rec["best_mi"].append(best)
+        rec["n_targets"].append(len(targets))
+    for k, v in rec.items():
+        out[k] = np.array(v)
+    # SURVEY Appendix B known answers (crossing map, pose (-5, 0, 0))
+    pol = make_policy(ns, ref_maps[0], 0.5)
+    pose = np.array([-5.0, 0.0, 0.0])
+    cells = pol.targetMap.getVisibleCells(pose)
+    out["kb_num_visible"] = np.array(len(cells))
+    out["kb_reward_prior"] = np.array(pol.targetMap.get_reward_from_pose(pose))
+    np.savez_compressed(os.path.join(GOLDEN, "explore.npz"), **out)
+    print("wrote explore.npz: %d cases, targets detected in %d, infeasible candidates in %d, kb %d cells %.16f" % (
+        ncases, sum(1 for n in rec["n_targets"] if n > 0), sum(1 for c in rec["cand_mi"] if (c < 0).any()),
+        len(cells), float(out["kb_reward_prior"])))

@@ -25,8 +25,9 @@ _lib = None
 
 
 def build(force=False):
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith(".c")]
     if force or not os.path.exists(_LIB_PATH) or \
-            os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, "casim_oracle.c")):
+            os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE, "libcasim_oracle.so"])
     return _LIB_PATH
 
@@ -148,6 +149,55 @@ def step(cfg, state, ext_actions=None, policy_actions=None, dt=None, n_agents=No
                                  _p(init), _p(types0), _p(prev_game_over), ctypes.byref(o), int(n_threads))
     assert rc == 0, rc
     return obs
+
+
+# ------------------------------------------------------------------------------------------
+# exploration (casim_oracle_explore.c)
+def edt(static_map):
+    """edfMap.update: exact squared EDT (cells^2) of one [300,300] map; edfMap.map == sqrt(d2) * 0.1."""
+    m = np.ascontiguousarray(static_map, dtype=np.uint8).reshape(MAP_DIM, MAP_DIM)
+    d2 = np.zeros((MAP_DIM, MAP_DIM), np.int32)
+    lib().casim_oracle_edt(_p(m), _p(d2))
+    return d2
+
+
+def visible_cells(cfg, static_map, pose):
+    """targetMap.getVisibleCells -> uint8 mask [dim,dim] indexed [j (y cell), i (x cell)]."""
+    m = np.ascontiguousarray(static_map, dtype=np.uint8).reshape(MAP_DIM, MAP_DIM)
+    pose = np.ascontiguousarray(pose, dtype=np.float64)
+    vis = np.zeros((cfg.ig_map_dim, cfg.ig_map_dim), np.uint8)
+    lib().casim_oracle_visible_cells(ctypes.byref(cfg), _p(m), _p(pose), _p(vis))
+    return vis
+
+
+def reward_from_pose(cfg, static_map, pose, belief):
+    m = np.ascontiguousarray(static_map, dtype=np.uint8).reshape(MAP_DIM, MAP_DIM)
+    pose = np.ascontiguousarray(pose, dtype=np.float64)
+    belief = np.ascontiguousarray(belief, dtype=np.float64)
+    f = lib().casim_oracle_reward_from_pose
+    f.restype = ctypes.c_double
+    return float(f(ctypes.byref(cfg), _p(m), _p(pose), _p(belief)))
+
+
+def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_game_over=None):
+    """ig_greedy.find_next_action for every ig_greedy agent.  belief [E,A,dim,dim] f64 is updated in place.
+    Returns dict(policy_actions [E,A,2], best_mi [E,A], cand_mi [E,A,9], counters [4], visible [E,A,dim,dim])."""
+    assert state.dtype == np.float64 and belief.dtype == np.float64 and belief.flags.c_contiguous
+    E, A = state.shape[:2]
+    dim = cfg.ig_map_dim
+    oas = np.ascontiguousarray(oas, dtype=np.float64)
+    n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
+    init = None if init is None else np.ascontiguousarray(init, dtype=np.float64)
+    prev_game_over = None if prev_game_over is None else np.ascontiguousarray(prev_game_over, dtype=np.uint8)
+    maps, n_maps = maps_arg(maps)
+    out = dict(policy_actions=np.zeros((E, A, 2)), best_mi=np.zeros((E, A)), cand_mi=np.zeros((E, A, 9)),
+               counters=np.zeros((4,), np.uint64), visible=np.zeros((E, A, dim, dim), np.uint8))
+    rc = lib().casim_oracle_explore_step(ctypes.byref(cfg), E, A, _p(n_agents), _p(np.ascontiguousarray(state)),
+                                         _p(oas), _p(belief), _p(maps), n_maps, _p(out["policy_actions"]),
+                                         _p(out["best_mi"]), _p(out["cand_mi"]), _p(out["counters"]),
+                                         _p(out["visible"]), _p(init), _p(prev_game_over))
+    assert rc == 0, rc
+    return out
 
 
 # ------------------------------------------------------------------------------------------

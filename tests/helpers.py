@@ -29,8 +29,8 @@ def unpack_maps():
 
 
 def assert_close(a, b, what, rtol=RTOL, atol=ATOL):
-    a = np.asarray(a, dtype=np.float64)
-    b = np.asarray(b, dtype=np.float64)
+    a = np.atleast_1d(np.asarray(a, dtype=np.float64))
+    b = np.atleast_1d(np.asarray(b, dtype=np.float64))
     assert a.shape == b.shape, (what, a.shape, b.shape)
     both_inf = np.isinf(a) & np.isinf(b) & (np.sign(a) == np.sign(b))
     err = np.abs(a - b)
@@ -166,3 +166,55 @@ def compare_obs(what, n_agents, gbuf, oobs, check_sensors=True):
         assert_close(gbuf["laserscan"][valid], oobs.laserscan[valid], what + " laserscan", rtol=0, atol=1e-6)
     if gbuf.get("local_grid") is not None:
         assert np.array_equal(gbuf["local_grid"][valid], oobs.local_grid[valid]), what + " local_grid"
+
+
+# ------------------------------------------------------------------------------------------------
+# exploration fixtures (tests/golden/explore.npz, generated from the reference by oracle/gen_golden_explore.py)
+def explore_maps(z):
+    """-> list of [300,300] uint8 static maps, list of exact squared EDTs"""
+    maps, d2 = [], []
+    k = 0
+    while "static_%d" % k in z.files:
+        maps.append(np.unpackbits(z["static_%d" % k])[:300 * 300].reshape(300, 300).astype(np.uint8))
+        d2.append(z["edf_d2_%d" % k])
+        k += 1
+    return maps, d2
+
+
+def explore_case_batch(z, cases):
+    """Stack golden explore cases (all sharing one map) into a batch of E = len(cases) envs x A = 1 agent.
+    Returns dict(state [E,1,24] f64, oas [E,1,9,10], belief0 [E,1,60,60] f64, vis, occ [E,60,60] bool)."""
+    E = len(cases)
+    state = np.zeros((E, 1, L.STATE_WORDS))
+    state[:, 0, L.PX] = z["pose"][cases, 0]
+    state[:, 0, L.PY] = z["pose"][cases, 1]
+    state[:, 0, L.HEADING] = z["pose"][cases, 2]
+    state[:, 0, L.RADIUS] = z["radius"][cases]
+    state[:, 0, L.PREF_SPEED] = 1.0
+    state[:, 0, L.TYPE] = L.encode_type(L.POLICY_IG_GREEDY, L.DYN_FIRST_ORDER, L.SENSOR_OTHER_AGENTS)
+    oas = z["oas"][cases][:, None]
+    belief0 = z["belief0"][cases].astype(np.float64)[:, None]
+    vis = np.unpackbits(z["vis"][cases], axis=-1)[:, :3600].reshape(E, 60, 60).astype(bool)
+    occ = np.unpackbits(z["occ"][cases], axis=-1)[:, :3600].reshape(E, 60, 60).astype(bool)
+    return dict(state=state, oas=np.ascontiguousarray(oas), belief0=np.ascontiguousarray(belief0), vis=vis, occ=occ)
+
+
+def check_explore_vs_golden(what, z, cases, cfg, belief_after, out, rtol=RTOL):
+    """belief_after [E,1,60,60], out = dict(policy_actions, best_mi, cand_mi, visible) vs the reference's results:
+    visible-cell set, occupied/empty choice and the chosen action exact; MI scores within rtol."""
+    b = explore_case_batch(z, cases)
+    for n, k in enumerate(cases):
+        vis = np.asarray(out["visible"][n, 0]).astype(bool)
+        assert np.array_equal(vis, b["vis"][n]), (what, "visible set", k, int(vis.sum()), int(b["vis"][n].sum()))
+        expect = b["belief0"][n, 0] * np.where(b["occ"][n], cfg.ig_rocc, np.where(b["vis"][n], cfg.ig_remp, 1.0))
+        assert_close(belief_after[n, 0], expect, "%s belief case %d" % (what, k), rtol=rtol, atol=0)
+        cand_ref = z["cand_mi"][k]
+        cand = np.asarray(out["cand_mi"][n, 0], dtype=np.float64)
+        assert np.array_equal(cand < 0, cand_ref < 0), (what, "feasibility", k, cand, cand_ref)
+        assert_close(cand, cand_ref, "%s cand_mi case %d" % (what, k), rtol=rtol, atol=1e-9)
+        assert_close(out["best_mi"][n, 0], z["best_mi"][k], "%s best_mi case %d" % (what, k), rtol=rtol, atol=1e-9)
+        # the argmax is exact unless the reference's own top two candidates are closer than rounding
+        srt = np.sort(cand_ref[cand_ref >= 0])
+        decisive = len(srt) < 2 or (srt[-1] - srt[-2]) > 1e-9 * max(1.0, srt[-1]) or srt[-1] == srt[-2]
+        if decisive:
+            assert_close(out["policy_actions"][n, 0], z["action"][k], "%s action case %d" % (what, k), rtol=1e-6, atol=0)

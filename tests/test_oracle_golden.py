@@ -144,3 +144,49 @@ def test_occupancy_grid_vs_cv2(oracle_lib):
         obs = oracle.observe(cfg, st, maps=maps[int(z["map_id"][k])])
         mism += int((obs.local_grid[0, 0] != grids[k]).sum())
     assert mism == 0
+
+
+def test_edt_vs_scipy_reference(oracle_lib):
+    """edfMap.update (scipy.ndimage.distance_transform_edt) == sqrt(exact squared EDT) * 0.1, three maps."""
+    z = H.load("explore.npz")
+    maps, d2 = H.explore_maps(z)
+    assert len(maps) == 3
+    cfg = oracle_lib.default_config()
+    for k, m in enumerate(maps):
+        assert np.array_equal(oracle_lib.rasterize(cfg, z["rects_%d" % k]), m)
+        assert np.array_equal(oracle_lib.edt(m), d2[k])
+
+
+def test_explore_step_vs_reference(oracle_lib):
+    """ig_greedy.find_next_action (detector emulation, targetMap.update, greedy one-step MI argmax) against the
+    reference classes: visible cells / occupied-empty choice / feasibility / action exact, MI to 1e-9."""
+    oracle = oracle_lib
+    z = H.load("explore.npz")
+    maps, _ = H.explore_maps(z)
+    cfg = oracle.default_config()
+    ncases = len(z["map_id"])
+    assert ncases >= 40 and (z["n_targets"] > 0).sum() >= 10
+    for mid in range(len(maps)):
+        cases = [k for k in range(ncases) if int(z["map_id"][k]) == mid]
+        b = H.explore_case_batch(z, cases)
+        belief = b["belief0"].copy()
+        out = oracle.explore_step(cfg, b["state"], b["oas"], belief, maps[mid])
+        H.check_explore_vs_golden("oracle map %d" % mid, z, cases, cfg, belief, out, rtol=1e-9)
+        assert int(out["counters"][3]) == 0          # nothing clamped: all samples stayed inside the arrays
+
+
+def test_explore_known_answers(oracle_lib):
+    """crossing map, pose (-5, 0, 0): 52 visible cells, reward 1.0740499287868415 on the prior."""
+    oracle = oracle_lib
+    z = H.load("explore.npz")
+    maps, d2 = H.explore_maps(z)
+    cfg = oracle.default_config()
+    assert abs(np.sqrt(d2[0].max()) * 0.1 - 7.0710678118654755) < 1e-12
+    pose = np.array([-5.0, 0.0, 0.0])
+    vis = oracle.visible_cells(cfg, maps[0], pose)
+    assert int(vis.sum()) == 52 == int(z["kb_num_visible"])
+    jj, ii = np.nonzero(vis)
+    cells = sorted(zip(ii.tolist(), jj.tolist()))
+    assert cells[:6] == [(21, 29), (21, 30), (22, 29), (22, 30), (23, 28), (23, 29)]
+    r = oracle.reward_from_pose(cfg, maps[0], pose, np.ones((60, 60)))
+    assert abs(r - 1.0740499287868415) < 1e-12 and abs(r - float(z["kb_reward_prior"])) < 1e-12
