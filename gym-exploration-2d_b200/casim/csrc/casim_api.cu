@@ -155,6 +155,12 @@ static int derive(const casim_config* c, DevCfg* d) {
   d->ig_pfp = c->ig_p_false_pos;
   d->ig_dt = c->ig_dt;
   d->ig_det_thresh = sqrt(0.5) * c->ig_cell + c->ig_tolerance;
+  d->ig_fov = c->ig_sens_fov;
+  d->ig_tan_half = (c->ig_sens_fov / 2 < 1.5) ? tan(c->ig_sens_fov / 2) : 0.0;
+  d->ig_prior = c->ig_prior;
+  d->map_hw = c->map_width / 2;
+  d->map_hh = c->map_height / 2;
+  REQUIRE(c->ig_map_dim >= 1 && c->ig_map_dim <= 64, "ig_map_dim must be in 1..64");
   d->coll_w_static = c->collision_av_w_static_agent;
   d->max_obs = c->max_other_agents_observed;
   d->rows = c->max_other_agents_rows;

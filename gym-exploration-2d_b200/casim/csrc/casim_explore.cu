@@ -1,3 +1,404 @@
+/*
+ * casim_explore.cu -- the exploration policy step: ig_greedy.find_next_action for every ig_greedy agent
+ * (citations relative to gym_collision_avoidance/envs/ of mlodel/gym-exploration-2d):
+ *   policies/ig_greedy.py:45-62     find_targets_in_obs  (detector emulation from other_agents_states rows)
+ *   information_models/targetMap.py:43-84   getVisibleCells (bounding box, range / FOV wedge, line of sight)
+ *   information_models/edfMap.py:21-47      checkVisibility (sphere tracing on the Euclidean distance field)
+ *   information_models/targetMap.py:86-128  update          (odds *= rOcc / rEmp on the visible cells)
+ *   information_models/targetMap.py:130-147 get_reward_from_cells / get_reward_from_pose (mutual information)
+ *   policies/ig_greedy.py:64-93     greedy_action / get_next_pose (9 candidates, EDF feasibility, strict-> argmax)
+ *
+ * One CTA per agent slot (slots that are not ig_greedy agents exit at once).  Ten poses are evaluated: pose 0
+ * = the agent's pose (belief update), poses 1..9 = the candidate next poses (scoring on the UPDATED belief).
+ * Two phases per batch of poses, both atomic-free on the data path (each belief cell is owned by one thread):
+ *   phase 1  one thread per cell of the pose's bounding box: ego-frame rotation, range and FOV tests; cells
+ *            inside the wedge are appended to a shared-memory queue (keeps phase 2 balanced: ~13 % of the box
+ *            survives);
+ *   phase 2  one thread per queued cell: sphere tracing on the exact squared EDT, then the odds multiply
+ *            (pose 0) or the cell's mutual information (poses 1..9), accumulated per candidate as a 64-bit
+ *            fixed-point integer so that the sum -- hence the argmax and its ties -- does not depend on the order
+ *            in which threads arrive.
+ *
+ * Arithmetic: fp64 like the reference for every decision (cell indices, range / FOV / visibility, feasibility,
+ * detection radius); the two wedge predicates are decided from squared / cross-multiplied forms with a
+ * relative guard band of 1e-12 and fall back to the reference's sqrt / atan2 inside the band.  The belief is
+ * stored as fp32 odds (clamped to FLT_MAX); MI is evaluated in fp64.
+ */
+#include <float.h>
+
 #include "casim_device.cuh"
-cudaError_t casim_launch_explore(casim_handle*, const float*, const float*, float*, float*, float*, float*,
-                                 unsigned long long*, cudaStream_t) { return cudaErrorNotSupported; }
+
+namespace {
+
+#define XQ_CAP 4096        /* queue entries: >= ig_dim^2 (ig_dim <= 64), so one pose always fits */
+#define X_THREADS 256
+#define X_NPOSE 10
+#define X_MI_SCALE 17592186044416.0 /* 2^44 */
+
+struct ExploreArgs {
+  DevCfg c;
+  const float4* state;
+  const float* oas;          /* [E*A][rows][10] */
+  float* belief;             /* [E*A][dim][dim] */
+  float* policy_actions;     /* [E*A][2] */
+  float* best_mi;            /* [E*A] or NULL */
+  float* cand_mi;            /* [E*A][9] or NULL */
+  unsigned long long* counters; /* [4] or NULL */
+  const int32_t* n_agents;
+  const int32_t* edf_d2;
+  const float* init;
+  const uint8_t* prev_game_over;
+  int E, A, n_maps;
+};
+
+struct PoseBox {
+  double x, y, cs, sn;
+  int x0, y0, w, h;       /* box origin and extent in target-map cells (w*h cells) */
+  int feasible;
+};
+
+/* edfMap.map[yIdc, xIdc] (edfMap.py:14-19,38-40; no y flip, sic); indices clamped into the array */
+__device__ __forceinline__ double edf_value(const DevCfg& c, const int32_t* __restrict__ d2, double px, double py,
+                                            unsigned& clamped) {
+  double fx = floor((px + c.map_hw) / c.cell), fy = floor((py + c.map_hh) / c.cell);
+  if (!(fx >= 0.0)) { fx = 0.0; clamped++; }
+  if (fx > (double)(CASIM_MAP_DIM - 1)) { fx = (double)(CASIM_MAP_DIM - 1); clamped++; }
+  if (!(fy >= 0.0)) { fy = 0.0; clamped++; }
+  if (fy > (double)(CASIM_MAP_DIM - 1)) { fy = (double)(CASIM_MAP_DIM - 1); clamped++; }
+  int xi = (int)fx, yi = (int)fy;
+  return sqrt((double)__ldg(d2 + yi * CASIM_MAP_DIM + xi)) * c.cell;
+}
+
+/* edfMap.py:21-47 checkVisibility */
+__device__ __forceinline__ bool line_of_sight(const DevCfg& c, const int32_t* __restrict__ d2, double px, double py,
+                                              double gx, double gy, unsigned& samples, unsigned& clamped) {
+  double dx = gx - px, dy = gy - py;
+  double L = sqrt(dx * dx + dy * dy);
+  double u = 0.05 / L;
+  while (u < 1.0) {
+    double nx = (1.0 - u) * px + u * gx, ny = (1.0 - u) * py + u * gy;
+    double md = edf_value(c, d2, nx, ny, clamped);
+    samples++;
+    if (md < 0.001) return false;
+    u += md / L;
+  }
+  return true;
+}
+
+/* targetMap.py:33-36 getPoseFromCell (one axis) */
+__device__ __forceinline__ double cell_centre(const DevCfg& c, int i, double half) {
+  return (double)i * c.ig_cell - half + c.ig_cell / 2;
+}
+__device__ __forceinline__ int cell_index(const DevCfg& c, double v, double half) {
+  double f = floor((v + half) / c.ig_cell);
+  f = fmin(fmax(f, -1.0e6), 1.0e6);
+  return (int)f;
+}
+__device__ __forceinline__ double lim_axis(double v, double half) { return fmax(fmin(v, half), -half); }
+
+/* range and FOV wedge test of targetMap.py:75-79: sqrt(r0^2+r1^2) < R and |atan2(r1, r0)| < F/2 */
+__device__ __forceinline__ bool in_wedge(const DevCfg& c, double r0, double r1) {
+  const double R = c.ig_range;
+  double s = r0 * r0 + r1 * r1, R2 = R * R;
+  bool in_range;
+  if (s < R2 * (1.0 - 1e-12)) in_range = true;
+  else if (s > R2 * (1.0 + 1e-12)) in_range = false;
+  else in_range = sqrt(s) < R;
+  if (!in_range) return false;
+  if (c.ig_tan_half > 0.0) {
+    if (r0 <= 0.0) return false; /* |dphi| >= pi/2 > F/2 */
+    double a = fabs(r1), b = c.ig_tan_half * r0;
+    double t = a - b;
+    if (fabs(t) > 1e-12 * (a + b)) return t < 0.0;
+  }
+  return fabs(atan2(r1, r0)) < c.ig_fov_half;
+}
+
+/* targetMap.py:130-143, one cell */
+__device__ __forceinline__ double cell_mi(const DevCfg& c, double r, double log_rocc, double log_remp) {
+  double p = r / (r + 1.0);
+  double f_p = log((r + 1.0) / (r + (1.0 / c.ig_rocc))) - log_rocc / (r * c.ig_rocc + 1.0);
+  double f_n = log((r + 1.0) / (r + (1.0 / c.ig_remp))) - log_remp / (r * c.ig_remp + 1.0);
+  double P_p = p * (1.0 - c.ig_pfn) + (1.0 - p) * c.ig_pfp;
+  double P_n = p * c.ig_pfn + (1.0 - p) * (1.0 - c.ig_pfp);
+  return P_p * f_p + P_n * f_n;
+}
+
+/* bounding box of targetMap.py:46-66 for one pose: cells of {pose, centre, left, right}, end-exclusive */
+__device__ __forceinline__ void pose_box(const DevCfg& c, double x, double y, double phi, PoseBox& b, unsigned& clamped) {
+  const double R = c.ig_range, F = c.ig_fov;
+  double s0, c0, s1, c1, s2, c2;
+  sincos(phi, &s0, &c0);
+  sincos(phi + F, &s1, &c1);
+  sincos(phi - F, &s2, &c2);
+  double xs[4] = {x, lim_axis(x + R * c0, c.map_hw), lim_axis(x + R * c1, c.map_hw), lim_axis(x + R * c2, c.map_hw)};
+  double ys[4] = {y, lim_axis(y + R * s0, c.map_hh), lim_axis(y + R * s1, c.map_hh), lim_axis(y + R * s2, c.map_hh)};
+  int x0 = INT_MAX, x1 = INT_MIN, y0 = INT_MAX, y1 = INT_MIN;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    int cx = cell_index(c, xs[k], c.map_hw), cy = cell_index(c, ys[k], c.map_hh);
+    x0 = min(x0, cx); x1 = max(x1, cx);
+    y0 = min(y0, cy); y1 = max(y1, cy);
+  }
+  const int dim = c.ig_dim;
+  if (x0 < 0) { x0 = 0; clamped++; }
+  if (y0 < 0) { y0 = 0; clamped++; }
+  if (x1 > dim) { x1 = dim; clamped++; }
+  if (y1 > dim) { y1 = dim; clamped++; }
+  b.x = x; b.y = y; b.cs = c0; b.sn = s0;
+  b.x0 = x0; b.y0 = y0;
+  b.w = max(x1 - x0, 0);
+  b.h = max(y1 - y0, 0);
+}
+
+__global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
+  const DevCfg& c = p.c;
+  const int g = blockIdx.x;
+  const int e = g / p.A, ai = g - e * p.A;
+  const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+  if (ai >= n) return;
+  const size_t N = (size_t)p.E * p.A;
+  const float4 p5 = p.state[5 * N + g];
+  const int type = __float_as_int(p5.w), flags = __float_as_int(p5.z);
+  if ((type & 0xff) != CASIM_POLICY_IG_GREEDY) return;
+  const int tid = threadIdx.x;
+  const bool restart = c.auto_reset && p.prev_game_over && p.init && p.prev_game_over[e];
+  if (!restart && (flags & CASIM_F_IS_DONE)) { /* collision_avoidance_env.py:298-300: no policy query */
+    if (tid == 0) {
+      p.policy_actions[2 * g] = 0.f;
+      p.policy_actions[2 * g + 1] = 0.f;
+      if (p.best_mi) p.best_mi[g] = -1.f;
+    }
+    if (p.cand_mi && tid < 9) p.cand_mi[9 * (size_t)g + tid] = -1.f;
+    return;
+  }
+
+  __shared__ PoseBox s_pose[X_NPOSE];
+  __shared__ double s_det[CASIM_MAX_AGENTS][2];
+  __shared__ int s_ndet, s_qn;
+  __shared__ unsigned int s_queue[XQ_CAP];
+  __shared__ unsigned long long s_mi[X_NPOSE];
+  __shared__ unsigned int s_cnt[4];
+  __shared__ double s_pose0[4]; /* x, y, heading, radius */
+
+  const int dim = c.ig_dim;
+  float* belief = p.belief + (size_t)g * dim * dim;
+  const int32_t* d2 = p.edf_d2 + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
+  unsigned cnt_tested = 0, cnt_samples = 0, cnt_visible = 0, cnt_clamped = 0;
+
+  if (tid == 0) {
+    s_ndet = 0;
+    s_qn = 0;
+    double x, y, h, rad;
+    if (restart) { /* agent.py:21-33 with the initial condition kept by casim_reset */
+      const float* in = p.init + (size_t)g * 7;
+      x = in[0]; y = in[1]; rad = in[4];
+      h = isnan(in[6]) ? atan2((double)in[3] - (double)in[1], (double)in[2] - (double)in[0]) : (double)in[6];
+    } else {
+      const float4 p0 = p.state[g], p2 = p.state[2 * N + g];
+      x = p0.x; y = p0.y; h = p0.z; rad = p2.z;
+    }
+    s_pose0[0] = x; s_pose0[1] = y; s_pose0[2] = h; s_pose0[3] = rad;
+  }
+  if (tid < X_NPOSE) s_mi[tid] = 0ull;
+  if (tid < 4) s_cnt[tid] = 0u;
+  if (restart)
+    for (int k = tid; k < dim * dim; k += X_THREADS) belief[k] = (float)c.ig_prior;
+  __syncthreads();
+  const double px = s_pose0[0], py = s_pose0[1], ph = s_pose0[2], prad = s_pose0[3];
+
+  /* ---- detector emulation (ig_greedy.py:45-62) + ego-frame detections (targetMap.py:91-103) ---- */
+  if (tid < 32) {
+    double rx = 0, ry = 0;
+    bool hit = false;
+    if (restart) {
+      if (tid < n && tid != ai && (__float_as_int(p.state[5 * N + (size_t)e * p.A + tid].w) & 0xff) == CASIM_POLICY_STATIC) {
+        const float* oin = p.init + ((size_t)e * p.A + tid) * 7;
+        rx = (double)oin[0] - px;
+        ry = (double)oin[1] - py;
+        hit = true;
+      }
+    } else if (tid < c.rows) {
+      const float* row = p.oas + ((size_t)g * c.rows + tid) * 10;
+      if (row[9] == 1.0f) {
+        rx = row[0];
+        ry = row[1];
+        hit = true;
+      }
+    }
+    if (hit) {
+      double dphi = atan2(ry, rx) - ph;
+      bool in_fov = fabs(dphi) <= c.ig_detect_fov_half; /* degrees vs radians, sic */
+      double rn = sqrt(rx * rx + ry * ry);
+      hit = in_fov && rn <= c.ig_range;
+    }
+    unsigned m = __ballot_sync(FULL_MASK, hit);
+    if (hit) {
+      int k = __popc(m & ((1u << tid) - 1u));
+      /* target = r + pose; detection = R_minus (target - pose) */
+      double tx = rx + px, ty = ry + py;
+      double dx = tx - px, dy = ty - py;
+      double cs, sn;
+      sincos(ph, &sn, &cs);
+      s_det[k][0] = cs * dx + sn * dy;
+      s_det[k][1] = -sn * dx + cs * dy;
+    }
+    if (tid == 0) s_ndet = __popc(m);
+  }
+  /* ---- the ten poses: 0 = current, 1..9 = get_next_pose(action a) (ig_greedy.py:81-93) ---- */
+  if (tid >= 32 && tid < 32 + X_NPOSE) {
+    int k = tid - 32;
+    double x = px, y = py, h = ph;
+    int feasible = 1;
+    if (k > 0) {
+      int a = k - 1;
+      double v = 2.0 * (double)(a / 3), w = (a % 3 == 0) ? -CASIM_PI : ((a % 3 == 2) ? CASIM_PI : 0.0);
+      double sn, cs;
+      sincos(ph, &sn, &cs);
+      double vx = cs * v + (-sn) * 0.0, vy = sn * v + cs * 0.0;
+      x = px + vx * c.ig_dt;
+      y = py + vy * c.ig_dt;
+      h = ph + w * c.ig_dt;
+      unsigned cl = 0;
+      feasible = edf_value(c, d2, x, y, cl) > prad + 0.1;
+      cnt_samples++;
+      cnt_clamped += cl;
+    }
+    PoseBox b;
+    pose_box(c, x, y, h, b, cnt_clamped);
+    b.feasible = feasible;
+    if (!feasible) b.w = b.h = 0;
+    s_pose[k] = b;
+  }
+  __syncthreads();
+
+  const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
+  const int ndet = s_ndet;
+  int pstart = 0;
+  while (pstart < X_NPOSE) {
+    /* pose 0 (the update) runs alone; the candidate poses are batched while their boxes fit the queue */
+    int pend = pstart + 1;
+    int total = s_pose[pstart].w * s_pose[pstart].h;
+    if (pstart > 0)
+      while (pend < X_NPOSE && total + s_pose[pend].w * s_pose[pend].h <= XQ_CAP) {
+        total += s_pose[pend].w * s_pose[pend].h;
+        pend++;
+      }
+    /* ---- phase 1: range / FOV wedge test of every box cell (targetMap.py:73-79) ---- */
+    for (int idx = tid; idx < total; idx += X_THREADS) {
+      int k = pstart, off = idx;
+      while (off >= s_pose[k].w * s_pose[k].h) {
+        off -= s_pose[k].w * s_pose[k].h;
+        k++;
+      }
+      const PoseBox& b = s_pose[k];
+      int ii = off / b.h, jj = off - ii * b.h;
+      int i = b.x0 + ii, j = b.y0 + jj;
+      double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
+      double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy; /* R = ((c, s), (-s, c)) */
+      cnt_tested++;
+      if (in_wedge(c, r0, r1)) {
+        int q = atomicAdd(&s_qn, 1);
+        s_queue[q] = ((unsigned)k << 12) | ((unsigned)j << 6) | (unsigned)i;
+      }
+    }
+    __syncthreads();
+    const int qn = s_qn;
+    /* ---- phase 2: line of sight, then odds update (pose 0) or mutual information (candidates) ---- */
+    for (int q = tid; q < qn; q += X_THREADS) {
+      unsigned en = s_queue[q];
+      int k = (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
+      const PoseBox& b = s_pose[k];
+      double gx = cell_centre(c, i, c.map_hw), gy = cell_centre(c, j, c.map_hh);
+      if (!line_of_sight(c, d2, b.x, b.y, gx, gy, cnt_samples, cnt_clamped)) continue;
+      cnt_visible++;
+      float* cellp = belief + j * dim + i;
+      if (k == 0) { /* targetMap.py:104-126 */
+        double rs = c.ig_remp;
+        if (ndet > 0) {
+          double dx = gx - b.x, dy = gy - b.y;
+          double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
+          for (int t = 0; t < ndet; t++) {
+            double ex = s_det[t][0] - r0, ey = s_det[t][1] - r1;
+            if (sqrt(ex * ex + ey * ey) < c.ig_det_thresh) {
+              rs = c.ig_rocc;
+              break;
+            }
+          }
+        }
+        *cellp = fminf((float)((double)*cellp * rs), FLT_MAX);
+      } else { /* targetMap.py:130-143 */
+        double mi = cell_mi(c, (double)*cellp, log_rocc, log_remp);
+        long long fx = __double2ll_rn(mi * X_MI_SCALE);
+        atomicAdd(&s_mi[k], (unsigned long long)fx);
+      }
+    }
+    __syncthreads();
+    if (tid == 0) s_qn = 0;
+    __syncthreads();
+    pstart = pend;
+  }
+
+  /* ---- greedy argmax, strict '>' in action order, starting from -1 (ig_greedy.py:64-78) ---- */
+  if (tid == 0) {
+    double max_mi = -1.0;
+    float a0 = -1.f, a1 = -1.f; /* the integer -1 broadcast into all_actions[i, :] */
+    for (int a = 0; a < 9; a++) {
+      double mi = -1.0;
+      if (s_pose[a + 1].feasible) {
+        mi = (double)(long long)s_mi[a + 1] / X_MI_SCALE;
+        if (mi > max_mi) {
+          max_mi = mi;
+          a0 = 2.0f * (float)(a / 3);
+          a1 = (a % 3 == 0) ? (float)-CASIM_PI : ((a % 3 == 2) ? (float)CASIM_PI : 0.f);
+        }
+      }
+      if (p.cand_mi) p.cand_mi[9 * (size_t)g + a] = (float)mi;
+    }
+    p.policy_actions[2 * g] = a0;
+    p.policy_actions[2 * g + 1] = a1;
+    if (p.best_mi) p.best_mi[g] = (float)max_mi;
+  }
+  if (p.counters) { /* instrumentation only: per-CTA totals, one global atomic per counter */
+    unsigned v0 = __reduce_add_sync(FULL_MASK, cnt_tested), v1 = __reduce_add_sync(FULL_MASK, cnt_samples);
+    unsigned v2 = __reduce_add_sync(FULL_MASK, cnt_visible), v3 = __reduce_add_sync(FULL_MASK, cnt_clamped);
+    if ((tid & 31) == 0) {
+      atomicAdd(&s_cnt[0], v0);
+      atomicAdd(&s_cnt[1], v1);
+      atomicAdd(&s_cnt[2], v2);
+      atomicAdd(&s_cnt[3], v3);
+    }
+    __syncthreads();
+    if (tid < 4) atomicAdd(p.counters + tid, (unsigned long long)s_cnt[tid]);
+  }
+}
+
+}  // namespace
+
+cudaError_t casim_launch_explore(casim_handle* h, const float* state, const float* oas, float* belief,
+                                 float* policy_actions, float* best_mi, float* cand_mi,
+                                 unsigned long long* counters, cudaStream_t s) {
+  ExploreArgs a;
+  a.c = h->dc;
+  a.state = reinterpret_cast<const float4*>(state);
+  a.oas = oas;
+  a.belief = belief;
+  a.policy_actions = policy_actions;
+  a.best_mi = best_mi;
+  a.cand_mi = cand_mi;
+  a.counters = counters;
+  a.n_agents = h->n_agents;
+  a.edf_d2 = h->edf_d2;
+  a.init = h->init;
+  a.prev_game_over = h->prev_game_over;
+  a.E = h->E;
+  a.A = h->A;
+  a.n_maps = h->n_maps;
+  if (counters) {
+    cudaError_t e = cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), s);
+    if (e != cudaSuccess) return e;
+  }
+  h->launches++;
+  k_explore<<<(unsigned)((size_t)h->E * h->A), X_THREADS, 0, s>>>(a);
+  return cudaGetLastError();
+}

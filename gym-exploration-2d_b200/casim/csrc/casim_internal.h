@@ -31,6 +31,8 @@ struct DevCfg {
   /* exploration */
   double ig_fov_half, ig_detect_fov_half, ig_range, ig_cell, ig_rocc, ig_remp, ig_tol, ig_pfn, ig_pfp, ig_dt;
   double ig_det_thresh; /* sqrt(0.5)*cell + tolerance */
+  double ig_fov, ig_tan_half, ig_prior; /* full FOV (radians), tan(FOV/2) (0 when FOV/2 >= pi/2), prior odds */
+  double map_hw, map_hh; /* map_width/2, map_height/2 (metres) */
   int nb, nr;
   int coll_w_static, max_obs, rows, submap_w, submap_h, game_over_mode, auto_reset, ig_dim;
 };

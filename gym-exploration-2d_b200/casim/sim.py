@@ -190,6 +190,36 @@ class BatchedSim:
                                             float(dt) if dt is not None else 0.0, ctypes.byref(self._obs),
                                             ctypes.byref(ho), _stream_ptr()), "casim_step_host")
 
+    # ------------------------------------------------------------------------------------------
+    # exploration (ig_greedy) and GA3C-CADRL policies: both write into the shared ``policy_actions`` buffer
+    def _policy_buffers(self):
+        if "policy_actions" not in self.buf or self.buf.get("policy_actions") is None:
+            self.buf["policy_actions"] = torch.zeros((self.E, self.A, 2), dtype=torch.float32, device=self.device)
+        return self.buf["policy_actions"]
+
+    def enable_exploration(self, want_debug=True):
+        """Allocate the target-map belief [E,A,dim,dim] (fp32 odds, prior everywhere) and the result buffers of
+        casim_explore_step."""
+        dim = self.cfg.ig_map_dim
+        f32 = dict(dtype=torch.float32, device=self.device)
+        self.belief = torch.full((self.E, self.A, dim, dim), float(self.cfg.ig_prior), **f32)
+        self._policy_buffers()
+        self.buf["best_mi"] = torch.zeros((self.E, self.A), **f32) if want_debug else None
+        self.buf["cand_mi"] = torch.zeros((self.E, self.A, 9), **f32) if want_debug else None
+        self.buf["explore_counters"] = torch.zeros((4,), dtype=torch.int64, device=self.device) if want_debug else None
+
+    def explore_step(self):
+        """ig_greedy.find_next_action for every ig_greedy agent: belief update + greedy action into
+        ``buf['policy_actions']`` (pass it to ``step(policy_actions=...)``)."""
+        if self.buf.get("other_agents_states") is None:
+            raise _lib.CasimError("explore_step needs the other_agents_states observation buffer")
+        _lib.check(self.lib.casim_explore_step(self.handle, _lib.ptr(self.state), _lib.ptr(self.buf["other_agents_states"]),
+                                               _lib.ptr(self.belief), _lib.ptr(self.buf["policy_actions"]),
+                                               _lib.ptr(self.buf.get("best_mi")), _lib.ptr(self.buf.get("cand_mi")),
+                                               _lib.ptr(self.buf.get("explore_counters")), _stream_ptr()),
+                   "casim_explore_step")
+        return self.buf["policy_actions"]
+
     def launch_count(self):
         return int(self.lib.casim_launch_count(self.handle))
 
