@@ -201,6 +201,65 @@ def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_g
 
 
 # ------------------------------------------------------------------------------------------
+# GA3C-CADRL (casim_oracle_ga3c.c)
+GA3C_NUM_PARAMS = 170764
+# (name, shape) of the parameter blob in order; TF variable names of GA3C_CADRL/network.py
+GA3C_LAYOUT = [("rnn/lstm_cell/kernel", (71, 256)), ("rnn/lstm_cell/bias", (256,)),
+               ("layer1/kernel", (68, 256)), ("layer1/bias", (256,)),
+               ("layer2/kernel", (256, 256)), ("layer2/bias", (256,)),
+               ("fullyconnected1/kernel", (256, 256)), ("fullyconnected1/bias", (256,)),
+               ("logits_p/kernel", (256, 11)), ("logits_p/bias", (11,)),
+               ("logits_v/kernel", (256, 1)), ("logits_v/bias", (1,))]
+
+
+def ga3c_random_weights(seed=0):
+    """Random-init weights of the architecture: Glorot-uniform kernels, zero biases (the TF1 defaults of
+    tf.layers.dense / LSTMCell), numpy Generator(seed)."""
+    rng = np.random.default_rng(seed)
+    parts = []
+    for name, shape in GA3C_LAYOUT:
+        if len(shape) == 2:
+            lim = np.sqrt(6.0 / (shape[0] + shape[1]))
+            parts.append(rng.uniform(-lim, lim, shape).astype(np.float32).ravel())
+        else:
+            parts.append(np.zeros(shape, np.float32))
+    w = np.concatenate(parts)
+    assert w.size == GA3C_NUM_PARAMS
+    return w
+
+
+def ga3c_actions():
+    t = np.zeros((11, 2))
+    lib().casim_oracle_ga3c_actions(_p(t))
+    return t
+
+
+def ga3c_forward(cfg, state, weights, n_agents=None, n_threads=1):
+    """GA3CCADRLPolicy.find_next_action for every GA3C agent.  Returns dict(policy_actions [E,A,2] f64,
+    action_idx [E,A] i32, probs [E,A,11] f32, nn_input [E,A,75] f64)."""
+    state = np.ascontiguousarray(state, dtype=np.float64)
+    E, A = state.shape[:2]
+    weights = np.ascontiguousarray(weights, dtype=np.float32)
+    n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
+    out = dict(policy_actions=np.zeros((E, A, 2)), action_idx=np.zeros((E, A), np.int32),
+               probs=np.zeros((E, A, 11), np.float32), nn_input=np.zeros((E, A, 75)))
+    rc = lib().casim_oracle_ga3c_forward(ctypes.byref(cfg), E, A, _p(n_agents), _p(state), _p(weights),
+                                         int(weights.size), _p(out["policy_actions"]), _p(out["action_idx"]),
+                                         _p(out["probs"]), _p(out["nn_input"]), int(n_threads))
+    assert rc == 0, rc
+    return out
+
+
+def ga3c_network(weights, x):
+    """Network forward alone: x [B,75] f32 -> probs [B,11] f32."""
+    weights = np.ascontiguousarray(weights, dtype=np.float32)
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    probs = np.zeros((x.shape[0], 11), np.float32)
+    lib().casim_oracle_ga3c_network(_p(weights), _p(x), int(x.shape[0]), _p(probs))
+    return probs
+
+
+# ------------------------------------------------------------------------------------------
 # conversions between the GPU layout (state [6,E,A,4] fp32 with int32 words) and the oracle's
 # [E,A,24] doubles
 def state_from_packs(packs):

@@ -190,3 +190,82 @@ def test_explore_known_answers(oracle_lib):
     assert cells[:6] == [(21, 29), (21, 30), (22, 29), (22, 30), (23, 28), (23, 29)]
     r = oracle.reward_from_pose(cfg, maps[0], pose, np.ones((60, 60)))
     assert abs(r - 1.0740499287868415) < 1e-12 and abs(r - float(z["kb_reward_prior"])) < 1e-12
+
+
+def test_ga3c_state_vector_vs_reference(oracle_lib):
+    """agents_to_ga3c_cadrl_state (GA3CCADRLPolicy.py:45-106): slot ORDER exact (Python round(x, 2), stable sort on
+    (-round(dist, 2), p_orthog), clip to the closest N), values to 1e-12."""
+    oracle = oracle_lib
+    z = H.load("ga3c_state.npz")
+    w = oracle.ga3c_random_weights(0)
+    ncases = z["state"].shape[0]
+    n_ties = 0
+    for k in range(ncases):
+        cfg = oracle.default_config()
+        cfg.max_other_agents_observed = int(z["max_obs"][k])
+        n = int(z["n_agents"][k])
+        out = oracle.ga3c_forward(cfg, z["state"][k:k + 1], w, n_agents=z["n_agents"][k:k + 1])
+        ref = z["nn_input"][k, :n]
+        got = out["nn_input"][0, :n]
+        assert np.array_equal(got[:, 0], ref[:, 0]), k          # number of other agents observed
+        # slot order: the (radius, combined radius) columns identify which agent sits in which slot
+        np.testing.assert_allclose(got, ref, rtol=0, atol=1e-12, err_msg="case %d" % k)
+        d = np.round(ref[:, 5:].reshape(n, 10, 7)[:, :, 6], 2)
+        n_ties += int(sum((np.diff(np.sort(row[:int(c)])) == 0).sum() for row, c in zip(d, ref[:, 0])))
+    assert n_ties > 50            # the fixtures do exercise the tie-break
+
+
+def test_ga3c_network_vs_torch(oracle_lib):
+    """Network restatement (TF1 LSTMCell gate order i, j, f, o + forget_bias 1, masked sequence, 3 x Dense(256) ReLU,
+    Dense(11), softmax floor) against an independent torch implementation.  PARITY UNPINNED w.r.t. TensorFlow."""
+    import torch
+    oracle = oracle_lib
+    w = oracle.ga3c_random_weights(3)
+    rng = np.random.default_rng(5)
+    B = 64
+    x = np.zeros((B, 75), np.float32)
+    x[:, 0] = rng.integers(0, 11, B)
+    x[:, 1:5] = rng.uniform(0, 5, (B, 4))
+    for b in range(B):
+        L_ = int(x[b, 0])
+        x[b, 5:5 + 7 * L_] = rng.uniform(-3, 3, 7 * L_)
+    probs = oracle.ga3c_network(w, x)
+    # torch version
+    parts, off = {}, 0
+    for name, shape in oracle.GA3C_LAYOUT:
+        size = int(np.prod(shape))
+        parts[name] = torch.from_numpy(w[off:off + size].reshape(shape).copy())
+        off += size
+    K, bvec = parts["rnn/lstm_cell/kernel"], parts["rnn/lstm_cell/bias"]
+    # torch LSTMCell gate order is i, f, g, o; TF1 LSTMCell is i, j(=g), f, o with forget_bias added to f
+    def reorder(t):
+        i, j, f, o = t.split(64, dim=-1)
+        return torch.cat([i, f, j, o], dim=-1)
+    cell = torch.nn.LSTMCell(7, 64)
+    with torch.no_grad():
+        cell.weight_ih.copy_(reorder(K[:7]).T)
+        cell.weight_hh.copy_(reorder(K[7:]).T)
+        bb = reorder(bvec).clone()
+        bb[64:128] += 1.0
+        cell.bias_ih.copy_(bb)
+        cell.bias_hh.zero_()
+        xt = torch.from_numpy(x)
+        avg = torch.tensor([0.0] + [0, 0, 1, 0.5] + [0, 0, 0, 0, 0.5, 0, 1] * 10)
+        std = torch.tensor([1.0] + [5, 3.14, 1, 1] + [5, 5, 1, 1, 1, 5, 1] * 10)
+        xn = (xt - avg) / std
+        h = torch.zeros(B, 64)
+        c = torch.zeros(B, 64)
+        seq = xn[:, 5:].reshape(B, 10, 7)
+        for t in range(10):
+            h2, c2 = cell(seq[:, t], (h, c))
+            m = (xt[:, 0] > t).unsqueeze(1)
+            h, c = torch.where(m, h2, h), torch.where(m, c2, c)
+        a = torch.cat([xn[:, 1:5], h], 1)
+        for name in ("layer1", "layer2", "fullyconnected1"):
+            a = torch.relu(a @ parts[name + "/kernel"] + parts[name + "/bias"])
+        logits = a @ parts["logits_p/kernel"] + parts["logits_p/bias"]
+        ref = (torch.softmax(logits, 1) + 1e-4) / (1 + 11e-4)
+    np.testing.assert_allclose(probs, ref.numpy(), rtol=2e-4, atol=2e-6)
+    assert np.array_equal(probs.argmax(1), ref.numpy().argmax(1))
+    np.testing.assert_allclose(oracle.ga3c_actions()[[0, 4, 6, 10]],
+                               [[1.0, -np.pi / 6], [1.0, np.pi / 6], [0.5, 0.0], [0.0, np.pi / 6]], atol=1e-15)
