@@ -218,6 +218,7 @@ int casim_destroy(casim_handle* h) {
   cudaFree(h->edf_scratch);
   cudaFree(h->ga3c_w);
   cudaFree(h->ga3c_wb);
+  cudaFree(h->ga3c_x);
   free(h);
   return 0;
 }

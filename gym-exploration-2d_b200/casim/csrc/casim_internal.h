@@ -65,6 +65,7 @@ struct casim_handle {
   /* GA3C */
   float* ga3c_w;           /* fp32 parameter blob on the device */
   void* ga3c_wb;           /* bf16 tiles for the tensor-core path */
+  float* ga3c_x;           /* [E*A][76] network input scratch */
   unsigned long long launches;
 };
 

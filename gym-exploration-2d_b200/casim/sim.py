@@ -220,6 +220,26 @@ class BatchedSim:
                    "casim_explore_step")
         return self.buf["policy_actions"]
 
+    def ga3c_set_weights(self, weights, want_debug=True):
+        """weights: float32 [170764] parameter blob in the order of include/casim.h (TF variables of
+        GA3C_CADRL/network.py: lstm kernel/bias, layer1, layer2, fullyconnected1, logits_p, logits_v)."""
+        w = np.ascontiguousarray(weights, dtype=np.float32)
+        _lib.check(self.lib.casim_ga3c_set_weights(self.handle, _lib.ptr(w), int(w.size), _stream_ptr()),
+                   "casim_ga3c_set_weights")
+        self._policy_buffers()
+        dev = self.device
+        self.buf["action_idx"] = torch.zeros((self.E, self.A), dtype=torch.int32, device=dev) if want_debug else None
+        self.buf["probs"] = torch.zeros((self.E, self.A, 11), dtype=torch.float32, device=dev) if want_debug else None
+        self.buf["nn_input"] = torch.zeros((self.E, self.A, 75), dtype=torch.float32, device=dev) if want_debug else None
+
+    def ga3c_forward(self, use_tensor_cores=False):
+        """GA3CCADRLPolicy.find_next_action for every GA3C agent -> ``buf['policy_actions']``."""
+        _lib.check(self.lib.casim_ga3c_forward(self.handle, _lib.ptr(self.state), _lib.ptr(self.buf["policy_actions"]),
+                                               _lib.ptr(self.buf.get("action_idx")), _lib.ptr(self.buf.get("probs")),
+                                               _lib.ptr(self.buf.get("nn_input")), int(bool(use_tensor_cores)),
+                                               _stream_ptr()), "casim_ga3c_forward")
+        return self.buf["policy_actions"]
+
     def launch_count(self):
         return int(self.lib.casim_launch_count(self.handle))
 

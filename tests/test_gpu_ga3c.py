@@ -1,0 +1,92 @@
+"""GPU parity of the GA3C-CADRL policy (casim_ga3c_forward): the state vector against golden vectors recorded
+from the reference's agents_to_ga3c_cadrl_state (slot order exact), the network forward against the fp32 CPU
+oracle (network numerics are "parity unpinned" w.r.t. TensorFlow, see oracle/casim_oracle_ga3c.c)."""
+import numpy as np
+import pytest
+
+import helpers as H
+from casim import layout as L
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(**kw):
+    from casim import lib
+    c = lib.default_config()
+    c.game_over_mode = 1
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+def test_ga3c_state_vector_golden(oracle_lib):
+    import torch
+    from casim.sim import BatchedSim
+    z = H.load("ga3c_state.npz")
+    w = oracle_lib.ga3c_random_weights(0)
+    for mo in sorted(set(z["max_obs"].tolist())):
+        sel = np.where(z["max_obs"] == mo)[0]
+        cfg = _cfg(max_other_agents_observed=int(mo))
+        E, A = len(sel), z["state"].shape[1]
+        sim = BatchedSim(E, A, cfg=cfg, sensors=())
+        st = np.ascontiguousarray(z["state"][sel])
+        types = st[:, :, L.TYPE].astype(np.int32)
+        sim.bind(types=types, n_agents=z["n_agents"][sel])
+        sim.load_state_numpy(st)
+        sim.ga3c_set_weights(w)
+        sim.ga3c_forward()
+        torch.cuda.synchronize()
+        got = sim.buf["nn_input"].cpu().numpy().astype(np.float64)
+        for n_, k in enumerate(sel):
+            n = int(z["n_agents"][k])
+            ref = z["nn_input"][k, :n]
+            assert np.array_equal(got[n_, :n, 0], ref[:, 0]), k
+            # identical slot order: radius / combined radius / distance columns identify the agents
+            H.assert_close(got[n_, :n], ref, "nn_input case %d" % k, rtol=1e-6, atol=1e-6)
+        sim.close()
+
+
+@pytest.mark.parametrize("use_tc", [False])
+def test_ga3c_forward_vs_oracle(oracle_lib, use_tc):
+    import torch
+    from casim import scenarios as S
+    from casim.sim import BatchedSim
+    oracle = oracle_lib
+    E, A = 96, 20
+    init, types, n = S.formations(E, A, seed=11)
+    n = n.copy()
+    n[::7] = 13                  # ragged environments
+    n[3] = 1                     # a lone agent: empty sequence
+    cfg = _cfg(near_goal_threshold=0.2)
+    w = oracle.ga3c_random_weights(1)
+    sim = BatchedSim(E, A, cfg=cfg, sensors=("other_agents_states",))
+    sim.reset(init, types, n)
+    sim.ga3c_set_weights(w)
+    tol_p = 2e-2 if use_tc else 2e-5
+    agree = total = 0
+    for t in range(6):
+        state = sim.state_numpy()
+        o = oracle.ga3c_forward(cfg, state, w, n_agents=n)
+        sim.ga3c_forward(use_tensor_cores=use_tc)
+        torch.cuda.synchronize()
+        gp = sim.buf["probs"].cpu().numpy()
+        gi = sim.buf["action_idx"].cpu().numpy()
+        ga = sim.buf["policy_actions"].cpu().numpy()
+        for e in range(E):
+            k = int(n[e])
+            H.assert_close(sim.buf["nn_input"].cpu().numpy()[e, :k], o["nn_input"][e, :k], "nn_input t=%d env %d" % (t, e),
+                           rtol=1e-6, atol=1e-6)
+            act = o["action_idx"][e, :k] >= 0
+            assert np.array_equal(gi[e, :k] >= 0, act)
+            assert np.abs(gp[e, :k][act] - o["probs"][e, :k][act]).max() < tol_p, (t, e)
+            srt = np.sort(o["probs"][e, :k][act], axis=1)
+            decisive = srt[:, -1] - srt[:, -2] > 4 * tol_p
+            same = gi[e, :k][act] == o["action_idx"][e, :k][act]
+            assert same[decisive].all(), (t, e)
+            agree += int(same.sum())
+            total += int(act.sum())
+            m = same
+            H.assert_close(ga[e, :k][act][m], o["policy_actions"][e, :k][act][m], "action t=%d env %d" % (t, e), rtol=1e-6, atol=1e-7)
+        sim.step(policy_actions=sim.buf["policy_actions"])
+    assert total > 5000 and agree / total > (0.97 if use_tc else 0.999)
+    sim.close()
