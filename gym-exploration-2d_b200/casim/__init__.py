@@ -4,5 +4,7 @@ C ABI of include/casim.h).  No CPU fallback: modules that compute import ``casim
 when the library is missing."""
 from . import layout  # noqa: F401
 from .config import Config, SimConfig, make_sim_config  # noqa: F401
+from . import plugins  # noqa: F401
+from .plugins import Agent  # noqa: F401
 
-__all__ = ["layout", "Config", "SimConfig", "make_sim_config"]
+__all__ = ["layout", "plugins", "Agent", "Config", "SimConfig", "make_sim_config"]

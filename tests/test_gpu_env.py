@@ -1,0 +1,92 @@
+"""GPU: the gym-shaped boundary (casim.env.BatchedCollisionAvoidanceEnv + casim.plugins) -- the reference's
+example scenario through reset()/step() with Agent objects, checked against SURVEY.md Appendix B known answers
+(recorded from the reference) and against the oracle in lock-step."""
+import numpy as np
+import pytest
+
+import helpers as H
+from casim import layout as L
+from casim import plugins as P
+from casim.config import Config
+from casim.plugins import Agent
+
+pytestmark = pytest.mark.gpu
+
+
+class _Cfg(Config):
+    TRAIN_SINGLE_AGENT = False
+    STATES_IN_OBS = ['dist_to_goal', 'rel_goal', 'radius', 'heading_ego_frame', 'pref_speed', 'other_agents_states']
+
+
+def test_c1_example_through_env_api(oracle_lib):
+    """BASELINE.json configs[0]: example.py 2-agent scenario, NonCooperativePolicy + UnicycleDynamics +
+    OtherAgentsStatesSensor, one env (envs/test_cases.py:79-86)."""
+    import torch
+    from casim.env import BatchedCollisionAvoidanceEnv
+    agents = [Agent(-3, -3, 3, 3, 0.5, 1.0, 0.5, P.NonCooperativePolicy, P.UnicycleDynamics, [P.OtherAgentsStatesSensor], 0),
+              Agent(3, 3, -3, -3, 0.5, 1.0, 0.5, P.NonCooperativePolicy, P.UnicycleDynamics, [P.OtherAgentsStatesSensor], 1)]
+    env = BatchedCollisionAvoidanceEnv(num_envs=1, max_agents=2, config=_Cfg)
+    env.set_agents(agents)
+    obs = env.reset()
+    assert set(obs.keys()) == set(_Cfg.STATES_IN_OBS)
+    cfg = env.cfg
+    first_done = None
+    for t in range(60):
+        ostate = env.sim.state_numpy()
+        oobs = oracle_lib.step(cfg, ostate)
+        obs, rewards, game_over, info = env.step({})
+        torch.cuda.synchronize()
+        assert rewards.shape == (2,) and info["which_agents_done"].shape == (2,)
+        H.assert_close(rewards.cpu().numpy(), oobs.rewards[0], "rewards t=%d" % t)
+        assert np.array_equal(info["which_agents_done"].cpu().numpy(), oobs.done[0].astype(bool))
+        H.assert_close(obs[0]["other_agents_states"], oobs.other_agents_states[0, 0], "oas t=%d" % t)
+        H.assert_close(obs["dist_to_goal"].cpu().numpy()[0], ostate[0, :, L.DIST_TO_GOAL], "dist_to_goal t=%d" % t)
+        if t == 0:   # SURVEY.md Appendix B (reference run)
+            assert abs(agents[0].pos_global_frame[0] - (-2.9292893186211586)) < 1e-5
+            assert abs(float(rewards[0]) - (-0.00076923076923077)) < 1e-8
+            assert abs(float(obs[0]["dist_to_goal"]) - 8.38528136962797) < 1e-5
+            np.testing.assert_allclose(obs[0]["rel_goal"], [5.929289318621159, 5.929289318621159], rtol=1e-6)
+            np.testing.assert_allclose(obs[0]["other_agents_states"][0],
+                                       [5.8585786372423172, 5.8585786372423172, 8.2852813650173704, 0, -0.999999982885729, 0,
+                                        0.5, 1.0, 7.2852813650173704, 2.0], atol=1e-5)
+        if first_done is None and bool(info["which_agents_done"].any()):
+            first_done = t
+            assert agents[0].in_collision and agents[1].in_collision
+            assert abs(float(rewards[0]) - (-0.7692307692307693)) < 1e-6
+    assert first_done == 37
+    env.close()
+
+
+def test_env_runs_exploration_and_ga3c_policies(oracle_lib):
+    """ig_greedy and GA3C-CADRL agents are driven by the env itself (casim_explore_step / casim_ga3c_forward inside
+    step()), batched over several environments, with the reference's obstacle format."""
+    import torch
+    from casim.env import BatchedCollisionAvoidanceEnv
+    E = 8
+    envs_agents = []
+    rng = np.random.default_rng(0)
+    for e in range(E):
+        x = float(rng.uniform(-9, -4))
+        envs_agents.append([
+            Agent(x, 0.3, 9, 0, 0.5, 1.0, 0.0, P.ig_greedy, P.FirstOrderDynamics, [P.OtherAgentsStatesSensor], 0),
+            Agent(x + 2.5, -0.2, 0, 0, 0.2, 1.0, 0.0, P.StaticPolicy, P.UnicycleDynamics, [], 1),
+            Agent(0.5, -8, 0.5, 8, 0.4, 1.0, None, P.GA3CCADRLPolicy, P.UnicycleDynamics, [P.OtherAgentsStatesSensor], 2)])
+    crossing = [[(10, 10), (2, 10), (2, 2), (10, 2)], [(-2, 10), (-10, 10), (-10, 2), (-2, 2)],
+                [(10, -2), (2, -2), (2, -10), (10, -10)], [(-2, -2), (-10, -2), (-10, -10), (-2, -10)]]
+    env = BatchedCollisionAvoidanceEnv(num_envs=E, max_agents=3, config=_Cfg)
+    env.set_agents(envs_agents)
+    env.set_static_map(crossing)
+    env.set_ga3c_weights(oracle_lib.ga3c_random_weights(2))
+    env.reset()
+    p0 = env.sim.state[0, :, :, 0:2].clone()
+    for t in range(10):
+        obs, rewards, game_over, info = env.step()
+    torch.cuda.synchronize()
+    assert rewards.shape == (E, 3) and game_over.shape == (E,)
+    moved = (env.sim.state[0, :, :, 0:2] - p0).norm(dim=-1).cpu().numpy()
+    assert (moved[:, 0] > 0.1).all() and (moved[:, 1] == 0).all() and (moved[:, 2] > 0.05).all()
+    belief = env.sim.belief.cpu().numpy()
+    assert (belief[:, 0] > 1.0).any() and (belief[:, 0] < 1.0).any()      # occupied and empty updates happened
+    assert (belief[:, 1:] == 1.0).all()                                   # only the ig_greedy agent owns a belief
+    assert obs[3][0]["other_agents_states"].shape == (9, 10)
+    env.close()
