@@ -47,7 +47,14 @@ WORKLOADS = {
                desc="4096 envs x 10 agents, OtherAgentsStates + LaserScan ray-casting against the crossing map"),
     "full": dict(E=4096, A=10, sensors=("other_agents_states", "laserscan", "local_grid"),
                  desc="4096 envs x 10 agents, OtherAgentsStates + LaserScan + OccupancyGrid, crossing map"),
+    "c4": dict(E=1024, A=4, sensors=("other_agents_states",),
+               desc="1024 envs x 4 agents (2 ig_greedy + 2 Static targets), exploration: target-map odds update + "
+                    "information-gain scoring of 9 candidate poses, crossing map"),
+    "c5": dict(E=1024, A=20, sensors=("other_agents_states",),
+               desc="8192/8 = 1024 envs per GPU x 20 agents (CADRL formations), batched GA3C-CADRL LSTM policy forward, "
+                    "random-init weights"),
 }
+GA3C_FLOP_PER_AGENT = 666112      # 2*[10*71*256 + 68*256 + 256*256 + 256*256 + 256*11]
 
 
 def algorithmic_bytes(wl):
@@ -70,10 +77,45 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_for(wl):
+def tensor_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["bf16_tflops"]), "measured (MEASURED_PEAKS.json bf16_tflops, burst: kernel timed alone)"
+    except Exception:
+        return 2250.0, "fallback (nominal dense bf16)"
+
+
+def roofline_obj(wl, kern, dominant, step_s, step_bytes, explore_counts):
+    """Roofline of the DOMINANT kernel of the step (algorithmic bytes or flops per launch / its measured launch
+    duration) plus the per-kernel breakdown and the whole-step figure."""
+    peak, peak_src = peaks()
+    t, units, how = kern[dominant]
+    tensor = dominant.startswith("k_ga3c")
+    if tensor:
+        tpeak, tsrc = tensor_peak()
+        ach = units / t / 1e12
+        out = {"bound": "tensor", "kernel": dominant, "achieved": ach, "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
+               "peak_source": tsrc, "algorithmic_flops_per_launch": units}
+    else:
+        ach = units / t / 1e9
+        out = {"bound": "hbm", "kernel": dominant, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+               "peak_source": peak_src, "algorithmic_bytes_per_launch": units}
+    out["duration_us"] = t * 1e6
+    out["how"] = how
+    out["traffic"] = traffic_for(wl, dominant)
+    out["kernels"] = {k: {"duration_us": v[0] * 1e6, "share_of_step": v[0] / step_s, "how": v[2]} for k, v in kern.items()}
+    out["whole_step"] = {"duration_us": step_s * 1e6, "algorithmic_bytes": step_bytes,
+                         "achieved_GBps": step_bytes / step_s / 1e9, "frac_of_hbm_peak": step_bytes / step_s / 1e9 / peak}
+    if explore_counts is not None:
+        out["explore_counters_one_launch"] = dict(zip(("cells_tested", "edf_samples", "visible_cells", "clamped"), explore_counts))
+    return out
+
+
+def traffic_for(wl, kernel=None):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(wl)
+            d = json.load(f).get(wl)
+            return d.get(kernel) if isinstance(d, dict) else d
     except Exception:
         return None
 
@@ -93,7 +135,26 @@ def scenario(wl, E, A, seed):
     if wl == "c2":
         init, types, n = S.open_space(E, A, seed=seed, sensors=0)
         return init, types, n, None
+    if wl == "c4":
+        return S.exploration(E, seed=seed)
+    if wl == "c5":
+        init, types, n = S.formations(E, A, seed=seed)
+        return init, types, n, None
     return S.crossing(E, A, seed=seed, sensors=mask)
+
+
+def ga3c_weights(seed=0):
+    """Random-init weights of the GA3C-CADRL architecture: Glorot-uniform kernels, zero biases (TF1 defaults)."""
+    rng = np.random.default_rng(seed)
+    shapes = [(71, 256), (256,), (68, 256), (256,), (256, 256), (256,), (256, 256), (256,), (256, 11), (11,), (256, 1), (1,)]
+    parts = []
+    for sh in shapes:
+        if len(sh) == 2:
+            lim = np.sqrt(6.0 / (sh[0] + sh[1]))
+            parts.append(rng.uniform(-lim, lim, sh).astype(np.float32).ravel())
+        else:
+            parts.append(np.zeros(sh, np.float32))
+    return np.concatenate(parts)
 
 
 def oracle_run(wl, E, A, steps, warmup, threads, seed=1234):
@@ -117,13 +178,27 @@ def oracle_run(wl, E, A, steps, warmup, threads, seed=1234):
         obs.local_grid = None
     init64 = init.astype(np.float64)
     go = np.zeros((E,), np.uint8)
+    belief = np.ones((E, A, cfg.ig_map_dim, cfg.ig_map_dim)) if wl == "c4" else None
+    w = ga3c_weights() if wl == "c5" else None
+    if wl == "c5":
+        cfg.near_goal_threshold = 0.2
+
+    def one_step():
+        pol = None
+        if wl == "c4":
+            pol = oracle.explore_step(cfg, state, obs.other_agents_states, belief, maps, n_agents=n, init=init64,
+                                      prev_game_over=go, n_threads=threads)["policy_actions"]
+        elif wl == "c5":
+            pol = oracle.ga3c_forward(cfg, state, w, n_agents=n, n_threads=threads)["policy_actions"]
+        oracle.step(cfg, state, policy_actions=pol, n_agents=n, maps=maps, init=init64, types0=types, prev_game_over=go,
+                    obs=obs, n_threads=threads)
+        return obs.game_over.copy()
+
     for _ in range(warmup):
-        oracle.step(cfg, state, n_agents=n, maps=maps, init=init64, types0=types, prev_game_over=go, obs=obs, n_threads=threads)
-        go = obs.game_over.copy()
+        go = one_step()
     t0 = time.perf_counter()
     for _ in range(steps):
-        oracle.step(cfg, state, n_agents=n, maps=maps, init=init64, types0=types, prev_game_over=go, obs=obs, n_threads=threads)
-        go = obs.game_over.copy()
+        go = one_step()
     dt = time.perf_counter() - t0
     return E * A * steps / dt, dt / max(steps, 1)
 
@@ -182,6 +257,9 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
+REF_SAMPLE_ENVS = {"c2": 4096, "c3": 512, "full": 64, "c4": 128, "c5": 256}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the CPU implementation of the path (oracle port, all host threads) on a bounded sample."""
     if rank != 0:
@@ -191,8 +269,8 @@ def run_reference(args, rank, world):
     threads = min(os.cpu_count() or 1, 64)
     E, A = W["E"], W["A"]
     # bounded sample: the full per-GPU batch for the cheap workloads, fewer envs when sensors make a step slow
-    Es = E if wl == "c2" else (512 if wl == "c3" else 64)
-    steps = max(1, min(args.steps, 200))
+    Es = REF_SAMPLE_ENVS[wl]
+    steps = max(1, min(args.steps, 200 if wl == "c2" else 40))
     warm = max(1, min(args.warmup, 5))
     v, sps = oracle_run(wl, Es, A, steps, warm, threads)
     line = {
@@ -220,6 +298,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of one CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=200)
+    ap.add_argument("--ga3c-fp32", action="store_true", help="c5: use the fp32 SIMT forward instead of the tensor-core path")
     ap.add_argument("--ring", type=int, default=None, help="override the number of env batches in the ring (diagnostics)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -255,6 +334,11 @@ def main():
         per_agent_resident += 64 + 32
     if "local_grid" in W["sensors"]:
         per_agent_resident += 3600 + 32
+    if wl == "c4":
+        per_agent_resident += 60 * 60 * 4 + 8          # fp32 belief + action
+    if wl == "c5":
+        per_agent_resident += 76 * 4 + 8               # network input scratch + action
+        cfg.near_goal_threshold = 0.2                   # experiments/src/run_cadrl_formations.py:21
     batch_bytes = E * A * per_agent_resident
     R = int(min(max(2, -(-int(1.5 * L2_BYTES) // batch_bytes)), 96))
     if args.ring:
@@ -266,16 +350,30 @@ def main():
         init, types, n, rects = scenario(wl, E, A, seed=1234 + 1000 * rank + r)
         if rects is not None:
             sim.set_obstacles(rects)
+        if wl == "c4":
+            sim.enable_exploration(want_debug=False)
+        if wl == "c5":
+            sim.ga3c_set_weights(ga3c_weights(), want_debug=False)
         sim.reset(init, types, n)
         sims.append(sim)
     torch.cuda.synchronize()
     launches_per_step = 1 + (1 if "laserscan" in W["sensors"] else 0) + (1 if "local_grid" in W["sensors"] else 0)
+    launches_per_step += 1 if wl == "c4" else (2 if wl == "c5" else 0)
+    use_tc = not args.ga3c_fp32
 
     stream = torch.cuda.Stream(device=dev)
 
+    def policy_step(sim):
+        if wl == "c4":
+            return sim.explore_step()
+        if wl == "c5":
+            return sim.ga3c_forward(use_tensor_cores=use_tc)
+        return None
+
     def run_steps(k0, k):
         for i in range(k0, k0 + k):
-            sims[i % R].step()
+            sim = sims[i % R]
+            sim.step(policy_actions=policy_step(sim))
 
     with torch.cuda.stream(stream):
         run_steps(0, Wm)                                  # warm-up (also loads the kernels)
@@ -352,12 +450,12 @@ def main():
     d2h = sum(t.numel() * t.element_size() for t in host.values())
     with torch.cuda.stream(stream):
         for i in range(3):
-            sims[i % R].step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
+            sims[i % R].step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev, policy_actions=policy_step(sims[i % R]))
         barrier()
         ev0.record(stream)
         t0 = time.perf_counter()
         for i in range(Ke):
-            sims[i % R].step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
+            sims[i % R].step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev, policy_actions=policy_step(sims[i % R]))
         ev1.record(stream)
         barrier()
         e2e_s = max(ev0.elapsed_time(ev1) * 1e-3, time.perf_counter() - t0)
@@ -373,10 +471,67 @@ def main():
         dist.all_reduce(stats)
     stats = [float(x) for x in stats.cpu()]
 
+    # ---- per-kernel durations, measured live with CUDA events on the launching stream: each kernel class is
+    # replayed alone (one CUDA graph of `reps` launches walking the same ring of batches, inputs > L2) ----
+    from casim import layout as LY
+
+    def time_alone(fn, reps=200):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(stream):
+            for i in range(3):
+                fn(sims[i % R])
+            stream.synchronize()
+            with torch.cuda.graph(g, stream=stream):
+                for i in range(reps):
+                    fn(sims[i % R])
+            g.replay()
+            stream.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            g.replay()
+            b.record(stream)
+            stream.synchronize()
+        return a.elapsed_time(b) * 1e-3 / reps
+
+    step_s = ms * 1e-3 / K
+    kern = {}          # name -> (seconds per launch, algorithmic units per launch, how)
+    NA = E * A
+    t_sens = 0.0
+    if "laserscan" in W["sensors"]:
+        t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_LASERSCAN))
+        kern["k_laser"] = (t, BYTES_LASER * NA, "timed alone")
+        t_sens += t
+    if "local_grid" in W["sensors"]:
+        t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_OCCUPANCY_GRID))
+        kern["k_grid"] = (t, BYTES_GRID * NA, "timed alone")
+        t_sens += t
+    explore_counts = None
+    if wl == "c4":
+        t = time_alone(lambda sm: sm.explore_step())
+        cnt = torch.zeros((4,), dtype=torch.int64, device=dev)
+        sims[0].buf["explore_counters"] = cnt
+        with torch.cuda.stream(stream):
+            sims[0].explore_step()
+        stream.synchronize()
+        sims[0].buf["explore_counters"] = None
+        explore_counts = [int(x) for x in cnt.cpu()]
+        # EDF samples x 8 B + visible cells of the update x 16 B (RMW) + visible cells of the 9
+        # candidates x 8 B, from the instrumented counters of one launch (all 10 poses share counter 2)
+        xbytes = explore_counts[1] * 8 + explore_counts[2] * 8 + (explore_counts[2] // 10) * 8
+        kern["k_explore"] = (t, xbytes, "timed alone")
+        t_sens += t
+    if wl == "c5":
+        t = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc))
+        kern["k_ga3c_state+fwd"] = (t, GA3C_FLOP_PER_AGENT * NA, "timed alone (state-vector kernel + forward kernel)")
+        t_sens += t
+    core_units = (BYTES_CORE + (BYTES_OAS if "other_agents_states" in W["sensors"] else 0)
+                  + (BYTES_WALL if "laserscan" in W["sensors"] or "local_grid" in W["sensors"] else 0)) * NA
+    kern["k_core"] = (max(step_s - t_sens, 1e-9), core_units, "timed alone" if not kern else "step time minus the kernels timed alone")
+    dominant = max(kern, key=lambda k: kern[k][0])
+
     if rank == 0:
         peak, peak_src = peaks()
         alg = algorithmic_bytes(wl)
-        step_s = ms * 1e-3 / K
         achieved = alg * E * A / step_s / 1e9
         line = {
             "metric": "agent-steps/s", "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": Wm,
@@ -391,16 +546,13 @@ def main():
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": Ke, "call": "casim_step_host via BatchedSim.step_host (blocking, pinned host buffers)"},
             "gpu_launches": launches_per_step * K,
-            "roofline": {"bound": "hbm", "kernel": "k_core (fused step)" if wl == "c2" else "whole step (%d kernels)" % launches_per_step,
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic_for(wl), "algorithmic_bytes_per_agent_step": alg, "peak_source": peak_src,
-                         "duration_us": step_s * 1e6},
+            "roofline": roofline_obj(wl, kern, dominant, step_s, sum(v[1] for k, v in kern.items() if not k.startswith("k_ga3c")), explore_counts),
             "clocks": dict(sampler.summary(t_load0, t_load1), sampled_over="timed region + 1.2 s of the same workload"),
             "episode_stats_last_step": stats,
         }
         if not args.no_cpu_baseline:
             threads = min(os.cpu_count() or 1, 64)
-            Es = E if wl == "c2" else (512 if wl == "c3" else 64)
+            Es = REF_SAMPLE_ENVS[wl]
             n_steps = 100 if wl == "c2" else 20
             v, sps = oracle_run(wl, Es, A, n_steps, 2, threads)
             line["cpu_baseline"] = {"value": v, "unit": "agent-steps/s", "cores": threads, "kind": "port",

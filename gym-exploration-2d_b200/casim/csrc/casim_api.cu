@@ -336,6 +336,21 @@ int casim_step(casim_handle* h, float* state, const float* ext_actions, const fl
   return run_sensors(h, state, obs, s);
 }
 
+int casim_run_sensor(casim_handle* h, const float* state, const casim_obs* obs, int which, void* stream) {
+  REQUIRE(h && state && obs, "null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (which == CASIM_SENSOR_LASERSCAN) {
+    REQUIRE(obs->laserscan, "laserscan buffer missing");
+    CK(casim_launch_laser(h, state, obs->laserscan, s));
+  } else if (which == CASIM_SENSOR_OCCUPANCY_GRID) {
+    REQUIRE(obs->local_grid, "local_grid buffer missing");
+    CK(casim_launch_grid(h, state, obs->local_grid, s));
+  } else {
+    REQUIRE(false, "which must be CASIM_SENSOR_LASERSCAN or CASIM_SENSOR_OCCUPANCY_GRID");
+  }
+  return 0;
+}
+
 int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
                     const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
                     void* stream) {

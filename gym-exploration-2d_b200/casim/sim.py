@@ -181,6 +181,11 @@ class BatchedSim:
                                        _lib.ptr(policy_actions), float(dt) if dt is not None else 0.0,
                                        ctypes.byref(self._obs), _stream_ptr()), "casim_step")
 
+    def run_sensor(self, which):
+        """Launch one sensor kernel alone (profiling aid): which = layout.SENSOR_LASERSCAN / SENSOR_OCCUPANCY_GRID."""
+        _lib.check(self.lib.casim_run_sensor(self.handle, _lib.ptr(self.state), ctypes.byref(self._obs), int(which),
+                                             _stream_ptr()), "casim_run_sensor")
+
     def step_host(self, host_bufs, ext_actions_host=None, ext_actions_dev=None, policy_actions=None, dt=None):
         """Host-buffer step: H2D of the actions, the step, D2H of every buffer present in ``host_bufs``
         (dict name -> pinned host tensor); returns when the results are in host memory."""

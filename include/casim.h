@@ -205,6 +205,11 @@ int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, voi
 int casim_step(casim_handle* h, float* state, const float* ext_actions, const float* policy_actions,
                double dt, const casim_obs* obs, void* stream);
 
+/* Profiling / benchmark aid: launch ONE sensor kernel -- `which` = CASIM_SENSOR_LASERSCAN (LaserScanSensor.py:27-58)
+ * or CASIM_SENSOR_OCCUPANCY_GRID (OccupancyGridSensor.py:70-98) -- on the post-move poses left by the last
+ * casim_step / casim_reset / casim_observe of this handle, so that the kernel can be timed alone. */
+int casim_run_sensor(casim_handle* h, const float* state, const casim_obs* obs, int which, void* stream);
+
 /* Host-buffer variant: ext_actions_host (pinned, may be NULL) is copied H2D, the step runs, and rewards, done and
  * game_over (and obs_misc/sensor buffers if the host pointers are non-NULL) are copied D2H into `host`; blocks until
  * the results are in host memory.  `dev` holds the device buffers used for the step. */

@@ -16,6 +16,7 @@
  * counted in counters[3].
  */
 #include <math.h>
+#include <pthread.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -260,22 +261,29 @@ static int find_targets(const casim_config* c, const double* rows, int nrows, co
  * (collision_avoidance_env.py:298-300).  All arrays are doubles except maps / vis_out (uint8) and
  * counters (uint64[4]).  With auto_reset and prev_game_over[e] set, the agent acts from its initial
  * condition with a fresh prior belief (batched-env extension, see include/casim.h). */
-int casim_oracle_explore_step(const casim_config* c, int E, int A, const int32_t* n_agents, const double* state,
-                              const double* oas, double* belief, const uint8_t* maps, int n_maps,
-                              double* policy_actions, double* best_mi, double* cand_mi,
-                              unsigned long long* counters, uint8_t* vis_out, const double* init,
-                              const uint8_t* prev_game_over) {
-  if (n_maps <= 0 || !maps) return CASIM_EINVAL;
-  const int dim = c->ig_map_dim, rows = c->max_other_agents_rows;
-  int32_t* d2 = (int32_t*)malloc(sizeof(int32_t) * MD * MD);
+typedef struct {
+  const casim_config* c; int e0, e1, A; const int32_t* n_agents; const double* state; const double* oas;
+  double* belief; const uint8_t* maps; int n_maps; const int32_t* d2_shared; double* policy_actions; double* best_mi;
+  double* cand_mi; uint8_t* vis_out; const double* init; const uint8_t* prev_game_over;
+  unsigned long long cnt[4];
+} xjob;
+
+static void* explore_range(void* pj) {
+  xjob* J = (xjob*)pj;
+  const casim_config* c = J->c;
+  const int A = J->A, dim = c->ig_map_dim, rows = c->max_other_agents_rows;
+  const double *state = J->state, *oas = J->oas, *init = J->init;
+  double *belief = J->belief, *policy_actions = J->policy_actions, *best_mi = J->best_mi, *cand_mi = J->cand_mi;
+  uint8_t* vis_out = J->vis_out;
+  int32_t* d2_own = J->d2_shared ? NULL : (int32_t*)malloc(sizeof(int32_t) * MD * MD);
   uint8_t* vis = (uint8_t*)malloc((size_t)dim * dim);
   uint8_t* vis2 = (uint8_t*)malloc((size_t)dim * dim);
-  if (counters) memset(counters, 0, 4 * sizeof(unsigned long long));
-  for (int e = 0; e < E; e++) {
-    if (e == 0 || n_maps > 1) casim_oracle_edt(maps + (size_t)(n_maps == 1 ? 0 : e) * MD * MD, d2);
-    xctx x = {c, d2, counters};
-    int n = n_agents ? n_agents[e] : A;
-    int restart = c->auto_reset && prev_game_over && init && prev_game_over[e];
+  memset(J->cnt, 0, sizeof(J->cnt));
+  for (int e = J->e0; e < J->e1; e++) {
+    if (d2_own) casim_oracle_edt(J->maps + (size_t)e * MD * MD, d2_own);
+    xctx x = {c, d2_own ? d2_own : J->d2_shared, J->cnt};
+    int n = J->n_agents ? J->n_agents[e] : A;
+    int restart = c->auto_reset && J->prev_game_over && init && J->prev_game_over[e];
     for (int i = 0; i < n; i++) {
       size_t g = (size_t)e * A + i;
       const double* s = state + g * NF;
@@ -318,7 +326,50 @@ int casim_oracle_explore_step(const casim_config* c, int E, int A, const int32_t
       if (cand_mi) memcpy(cand_mi + 9 * g, cand, sizeof(cand));
     }
   }
-  free(d2); free(vis); free(vis2);
+  free(d2_own); free(vis); free(vis2);
+  return NULL;
+}
+
+int casim_oracle_explore_step(const casim_config* c, int E, int A, const int32_t* n_agents, const double* state,
+                              const double* oas, double* belief, const uint8_t* maps, int n_maps,
+                              double* policy_actions, double* best_mi, double* cand_mi,
+                              unsigned long long* counters, uint8_t* vis_out, const double* init,
+                              const uint8_t* prev_game_over, int n_threads) {
+  if (n_maps <= 0 || !maps) return CASIM_EINVAL;
+  /* the EDF is built once per map (edfMap.__init__), not per step: keep the last shared map's transform */
+  static uint8_t* cache_map = NULL;
+  static int32_t* cache_d2 = NULL;
+  const int32_t* d2_shared = NULL;
+  if (n_maps == 1) {
+    if (!cache_map) {
+      cache_map = (uint8_t*)malloc(MD * MD);
+      cache_d2 = (int32_t*)malloc(sizeof(int32_t) * MD * MD);
+      memset(cache_map, 0xff, MD * MD);
+    }
+    if (memcmp(cache_map, maps, MD * MD) != 0) {
+      casim_oracle_edt(maps, cache_d2);
+      memcpy(cache_map, maps, MD * MD);
+    }
+    d2_shared = cache_d2;
+  }
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 64) n_threads = 64;
+  xjob jobs[64];
+  pthread_t th[64];
+  for (int t = 0; t < n_threads; t++) {
+    xjob* j = &jobs[t];
+    j->c = c; j->A = A; j->n_agents = n_agents; j->state = state; j->oas = oas; j->belief = belief; j->maps = maps;
+    j->n_maps = n_maps; j->d2_shared = d2_shared; j->policy_actions = policy_actions; j->best_mi = best_mi;
+    j->cand_mi = cand_mi; j->vis_out = vis_out; j->init = init; j->prev_game_over = prev_game_over;
+    j->e0 = (int)((long long)E * t / n_threads);
+    j->e1 = (int)((long long)E * (t + 1) / n_threads);
+    if (n_threads == 1) explore_range(j); else pthread_create(&th[t], NULL, explore_range, j);
+  }
+  if (n_threads > 1) for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
+  if (counters) {
+    memset(counters, 0, 4 * sizeof(unsigned long long));
+    for (int t = 0; t < n_threads; t++) for (int k = 0; k < 4; k++) counters[k] += jobs[t].cnt[k];
+  }
   return 0;
 }
 

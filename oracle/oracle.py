@@ -179,7 +179,7 @@ def reward_from_pose(cfg, static_map, pose, belief):
     return float(f(ctypes.byref(cfg), _p(m), _p(pose), _p(belief)))
 
 
-def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_game_over=None):
+def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_game_over=None, n_threads=1):
     """ig_greedy.find_next_action for every ig_greedy agent.  belief [E,A,dim,dim] f64 is updated in place.
     Returns dict(policy_actions [E,A,2], best_mi [E,A], cand_mi [E,A,9], counters [4], visible [E,A,dim,dim])."""
     assert state.dtype == np.float64 and belief.dtype == np.float64 and belief.flags.c_contiguous
@@ -195,7 +195,7 @@ def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_g
     rc = lib().casim_oracle_explore_step(ctypes.byref(cfg), E, A, _p(n_agents), _p(np.ascontiguousarray(state)),
                                          _p(oas), _p(belief), _p(maps), n_maps, _p(out["policy_actions"]),
                                          _p(out["best_mi"]), _p(out["cand_mi"]), _p(out["counters"]),
-                                         _p(out["visible"]), _p(init), _p(prev_game_over))
+                                         _p(out["visible"]), _p(init), _p(prev_game_over), int(n_threads))
     assert rc == 0, rc
     return out
 
