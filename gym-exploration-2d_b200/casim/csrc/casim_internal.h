@@ -17,6 +17,17 @@
 #define CASIM_PLANE_WORDS (CASIM_MAP_DIM * CASIM_MAP_WORDS) /* 3000 words = 12 000 B per bit plane */
 #define CASIM_NUM_PLANES 4 /* S, S|right, S|down, S|right|down|diag  (OccupancyGrid bilinear footprint) */
 
+/* OccupancyGrid fast path (casim_sensors.cu k_grid): the four footprint planes again, zero-padded by
+ * CASIM_GPAD cells on every side (96 = 3 words, so padded word w is map word w-3), plus a 2-bit classification per
+ * anchor cell: bit 0 = no occupied cell in the 6x6 box anchored there, bit 1 = all 36 cells occupied and in-map. */
+#define CASIM_GPAD 96
+#define CASIM_GROWS (CASIM_MAP_DIM + 2 * CASIM_GPAD)  /* 492 padded rows */
+#define CASIM_GWORDS 16                                /* 512 padded columns */
+#define CASIM_GCLS_WORDS 32                            /* 2 bits x 512 anchors per row */
+#define CASIM_GBOX 6
+#define CASIM_GPLANE_WORDS (CASIM_GROWS * CASIM_GWORDS)
+#define CASIM_GMAP_WORDS (CASIM_NUM_PLANES * CASIM_GPLANE_WORDS + CASIM_GROWS * CASIM_GCLS_WORDS)
+
 /* Derived, device-side view of casim_config (thresholds stay doubles: predicates are fp64). */
 struct DevCfg {
   double dt, dt_nominal;
@@ -49,6 +60,7 @@ struct casim_handle {
   int32_t* edf_d2;         /* [n_maps_alloc][300][300] squared distance (cells^2) to the nearest occupied cell;
                               edfMap.map[r][c] == sqrt(edf_d2) * cell exactly (information_models/edfMap.py:11-12) */
   int32_t* edf_scratch;    /* [n_maps_alloc][300][300] column pass */
+  uint32_t* grid_maps;     /* [n_maps_alloc][CASIM_GMAP_WORDS]: 4 padded planes then the classification plane */
   int n_maps_alloc;
   /* borrowed from the caller (casim_reset / casim_set_trajectories) */
   const float* init;

@@ -82,6 +82,52 @@ __global__ void k_derive(int n_maps, uint32_t* planes, uint8_t* map_out) {
   }
 }
 
+/* OccupancyGrid fast path: zero-padded copies of the four footprint planes (pad = 96 cells = 3 words) */
+__global__ void k_grid_pad(int n_maps, const uint32_t* planes, uint32_t* gmaps) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per_map = CASIM_NUM_PLANES * CASIM_GPLANE_WORDS;
+  if (i >= n_maps * per_map) return;
+  int m = i / per_map, r = i - m * per_map;
+  int pl = r / CASIM_GPLANE_WORDS, q = r - pl * CASIM_GPLANE_WORDS;
+  int pr = q / CASIM_GWORDS, pw = q - pr * CASIM_GWORDS;
+  int row = pr - CASIM_GPAD, wc = pw - CASIM_GPAD / 32;
+  uint32_t v = 0;
+  if (row >= 0 && row < CASIM_MAP_DIM && wc >= 0 && wc < CASIM_MAP_WORDS)
+    v = planes[((size_t)m * CASIM_NUM_PLANES + pl) * CASIM_PLANE_WORDS + row * CASIM_MAP_WORDS + wc];
+  gmaps[(size_t)m * CASIM_GMAP_WORDS + r] = v;
+}
+
+/* 2-bit classification of every anchor (padded row pr, padded col pc): over the box rows [pr, pr+6) x cols
+ * [pc, pc+6) of plane 0 (cells outside the padded array count as free): bit 0 = all free, bit 1 = all occupied.
+ * One thread per output word (16 anchors). */
+__global__ void k_grid_classify(int n_maps, uint32_t* gmaps) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per_map = CASIM_GROWS * CASIM_GCLS_WORDS;
+  if (i >= n_maps * per_map) return;
+  int m = i / per_map, r = i - m * per_map;
+  int pr = r / CASIM_GCLS_WORDS, cw = r - pr * CASIM_GCLS_WORDS;
+  const uint32_t* p0 = gmaps + (size_t)m * CASIM_GMAP_WORDS; /* padded plane 0 */
+  uint32_t out = 0;
+  for (int a = 0; a < 16; a++) {
+    int pc = cw * 16 + a;
+    bool allz = true, allo = true;
+    for (int dr = 0; dr < CASIM_GBOX; dr++) {
+      int rr = pr + dr;
+      uint32_t bits = 0;
+      if (rr < CASIM_GROWS) {
+        int w = pc >> 5, sh = pc & 31;
+        uint32_t lo = p0[rr * CASIM_GWORDS + w];
+        uint32_t hi = (w + 1 < CASIM_GWORDS) ? p0[rr * CASIM_GWORDS + w + 1] : 0u;
+        bits = __funnelshift_r(lo, hi, sh) & ((1u << CASIM_GBOX) - 1u);
+      }
+      allz = allz && bits == 0u;
+      allo = allo && bits == ((1u << CASIM_GBOX) - 1u);
+    }
+    out |= ((allz ? 1u : 0u) | (allo ? 2u : 0u)) << (2 * a);
+  }
+  gmaps[(size_t)m * CASIM_GMAP_WORDS + CASIM_NUM_PLANES * CASIM_GPLANE_WORDS + r] = out;
+}
+
 /* pass 1: per column, distance (in cells) to the nearest occupied cell in that column (big = none) */
 __global__ void k_edt_cols(int n_maps, const uint32_t* planes, int* gdist) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -151,6 +197,14 @@ cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_ou
   k_derive<<<(total + 255) / 256, 256, 0, s>>>(n_maps, h->map_planes, map_out);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return err;
+  {
+    int tp = n_maps * CASIM_NUM_PLANES * CASIM_GPLANE_WORDS, tc = n_maps * CASIM_GROWS * CASIM_GCLS_WORDS;
+    h->launches += 2;
+    k_grid_pad<<<(tp + 255) / 256, 256, 0, s>>>(n_maps, h->map_planes, h->grid_maps);
+    k_grid_classify<<<(tc + 127) / 128, 128, 0, s>>>(n_maps, h->grid_maps);
+    err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+  }
   int* gdist = h->edf_scratch;
   k_edt_cols<<<(n_maps * CASIM_MAP_DIM + 127) / 128, 128, 0, s>>>(n_maps, h->map_planes, gdist);
   k_edt_rows<<<n_maps * CASIM_MAP_DIM, 128, 0, s>>>(n_maps, gdist, h->edf_d2);

@@ -95,12 +95,14 @@ struct GridArgs {
   const int32_t* n_agents;
   const uint32_t* map_planes;
   uint8_t* out;
+  const uint32_t* grid_maps;
   int E, A, n_maps;
 };
 
-/* One CTA per agent: warps 0-1 build the per-row / per-column fixed-point tables in fp64, then every thread
+/* Generic-shape fallback (submap sides that are not multiples of 4, unaligned output).
+ * One CTA per agent: warps 0-1 build the per-row / per-column fixed-point tables in fp64, then every thread
  * produces 4-cell output words with integer arithmetic and one bit lookup per cell. */
-__global__ void __launch_bounds__(256) k_grid(const GridArgs p) {
+__global__ void __launch_bounds__(256) k_grid_generic(const GridArgs p) {
   const DevCfg& c = p.c;
   const long long g = blockIdx.x;
   const long long N = (long long)p.E * p.A;
@@ -208,6 +210,166 @@ __global__ void __launch_bounds__(256) k_grid(const GridArgs p) {
   }
 }
 
+
+/* ------------------------------------------------------------------------------------------------ */
+/* k_grid: one WARP per agent, three phases.
+ *   tables   per-row / per-column fixed-point terms of OpenCV's warpAffine (fp64, once per agent), biased by the
+ *            96-cell padding of the fast-path planes so that no lookup needs a bounds check;
+ *   phase 1  one lane per output word (4 cells of a destination row).  The source cells of the word lie between
+ *            those of its end cells (the per-axis terms are monotone), i.e. inside the 6x6 box anchored at the
+ *            component-wise minimum: the 2-bit classification plane says whether that box is entirely free
+ *            (word = 0), entirely occupied (word = 0x01010101) or mixed (queued);
+ *   phase 2  the queued words only: exact per-cell lookup in the footprint plane chosen by (fx > 0, fy > 0);
+ *   phase 3  the 3600-byte grid leaves shared memory as 16-byte coalesced stores.
+ * Maps are unions of rectangles (Map.get_occupancy_grid), so most words are uniform.                 */
+#define GRID_WARPS 4
+#define GRID_MAXW 16  /* words per row (submap side <= 64) */
+
+__device__ __forceinline__ uint32_t grid_cell_exact(const uint32_t* __restrict__ gp, int X, int Y) {
+  /* X, Y: biased 1/32-cell fixed point (already >> 5) */
+  int xi = X >> 5, yi = Y >> 5;
+  int plane = ((X & 31) ? 1 : 0) + ((Y & 31) ? 2 : 0);
+  uint32_t w = __ldg(gp + plane * CASIM_GPLANE_WORDS + yi * CASIM_GWORDS + (xi >> 5));
+  return (w >> (xi & 31)) & 1u;
+}
+
+__global__ void __launch_bounds__(32 * GRID_WARPS) k_grid(const GridArgs p) {
+  const DevCfg& c = p.c;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const long long N = (long long)p.E * p.A;
+  const long long g = (long long)blockIdx.x * GRID_WARPS + wid;
+  __shared__ __align__(16) uint32_t s_out[GRID_WARPS][64 * GRID_MAXW];
+  __shared__ int s_rx[GRID_WARPS][64], s_ry[GRID_WARPS][64], s_cx[GRID_WARPS][64], s_cy[GRID_WARPS][64];
+  __shared__ uint16_t s_list[GRID_WARPS][64 * GRID_MAXW];
+  if (g >= N) return;
+  const int e = (int)(g / p.A), ai = (int)(g - (long long)e * p.A);
+  const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+  const int H = c.submap_h, W = c.submap_w; /* out[oy*H + ox]: W rows of H cells */
+  const int wpr = H >> 2, nwords = W * wpr;
+  uint32_t* out = s_out[wid];
+  uint4* gout = reinterpret_cast<uint4*>(p.out + g * (long long)(H * W));
+  const int type = __float_as_int(p.state[5 * N + g].w);
+  const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_OCCUPANCY_GRID) && p.n_maps > 0;
+  if (!on) {
+    for (int i = lane; i < (nwords >> 2); i += 32) gout[i] = make_uint4(0u, 0u, 0u, 0u);
+    return;
+  }
+  const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[0];
+  const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[1];
+  const double px = q0.x, py = q0.y, ch = q1.x, sh = q1.y;
+  int row0, col0;
+  world_to_map_mul(c, px, py, row0, col0);
+  /* Map.getSubmapByIndices (Map.py:81-105) */
+  int sx = max(row0 - W / 2, 0), sy = max(col0 - H / 2, 0);
+  if (sx + W > CASIM_MAP_DIM - 1) sx = CASIM_MAP_DIM - 1 - W;
+  if (sy + H > CASIM_MAP_DIM - 1) sy = CASIM_MAP_DIM - 1 - H;
+  /* cv2.getRotationMatrix2D(center=(col0,row0), angle=-heading*180/pi, 1), inverted as in warpAffine */
+  double M0, M1, M2, M3, M4, M5;
+  {
+    double alpha = ch, beta = -sh;
+    double cx = (double)(float)col0, cy = (double)(float)row0;
+    M0 = alpha; M1 = beta; M2 = (1 - alpha) * cx - beta * cy;
+    M3 = -beta; M4 = alpha; M5 = beta * cx + (1 - alpha) * cy;
+    double D = M0 * M4 - M1 * M3;
+    D = D != 0 ? 1. / D : 0;
+    double A11 = M4 * D, A22 = M0 * D;
+    M0 = A11; M1 *= -D; M3 *= -D; M4 = A22;
+    double b1 = -M0 * M2 - M1 * M5, b2 = -M3 * M2 - M4 * M5;
+    M2 = b1; M5 = b2;
+  }
+  const int BIAS = CASIM_GPAD << 10; /* 96 cells in 1/1024 units: shifts >> 5 >> 5 keep it exact */
+  bool ok = true;                    /* every lookup stays inside the padded planes */
+  for (int t = lane; t < 64; t += 32) {
+    double rxd = 0, ryd = 0, cxd = 0, cyd = 0;
+    if (t < W) {
+      int y = sx + t;
+      rxd = rint((M1 * y + M2) * 1024);
+      ryd = rint((M4 * y + M5) * 1024);
+    }
+    if (t < H) {
+      int x = sy + t;
+      cxd = rint(M0 * x * 1024);
+      cyd = rint(M3 * x * 1024);
+    }
+    ok = ok && fabs(rxd) < 5.0e8 && fabs(ryd) < 5.0e8 && fabs(cxd) < 5.0e8 && fabs(cyd) < 5.0e8;
+    s_rx[wid][t] = (int)rxd + 16 + BIAS;
+    s_ry[wid][t] = (int)ryd + 16 + BIAS;
+    s_cx[wid][t] = (int)cxd;
+    s_cy[wid][t] = (int)cyd;
+  }
+  __syncwarp();
+  /* the four corner cells bound every source coordinate (monotone terms) */
+  if (lane < 4) {
+    int oy = (lane & 1) ? W - 1 : 0, ox = (lane & 2) ? H - 1 : 0;
+    int xi = (s_rx[wid][oy] + s_cx[wid][ox]) >> 10, yi = (s_ry[wid][oy] + s_cy[wid][ox]) >> 10;
+    ok = ok && xi >= 1 && yi >= 1 && xi < CASIM_GWORDS * 32 - CASIM_GBOX - 1 && yi < CASIM_GROWS - CASIM_GBOX - 1;
+  }
+  ok = __all_sync(FULL_MASK, ok);
+  if (!ok) {
+    /* far outside the map (agent off the grid): per-cell path with bounds checks on the unpadded plane 0 */
+    const uint32_t* pl = p.map_planes + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_NUM_PLANES * CASIM_PLANE_WORDS;
+    auto S = [&](int r, int cc) -> uint32_t {
+      return (r >= 0 && r < CASIM_MAP_DIM && cc >= 0 && cc < CASIM_MAP_DIM) ? (uint32_t)map_bit(pl, r, cc) : 0u;
+    };
+    for (int wi = lane; wi < nwords; wi += 32) {
+      int oy = wi / wpr, ox0 = (wi - oy * wpr) << 2;
+      uint32_t word = 0;
+      for (int k = 0; k < 4; k++) {
+        long long Xl = ((long long)s_rx[wid][oy] - BIAS + s_cx[wid][ox0 + k]) >> 5;
+        long long Yl = ((long long)s_ry[wid][oy] - BIAS + s_cy[wid][ox0 + k]) >> 5;
+        int X = (int)Xl, Y = (int)Yl;
+        int sxi = X >> 5, syi = Y >> 5, fx = X & 31, fy = Y & 31;
+        uint32_t v = S(syi, sxi);
+        if (fx > 0) v |= S(syi, sxi + 1);
+        if (fy > 0) v |= S(syi + 1, sxi);
+        if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
+        word |= v << (8 * k);
+      }
+      out[wi] = word;
+    }
+  } else {
+    const uint32_t* gp = p.grid_maps + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_GMAP_WORDS;
+    const uint32_t* cls = gp + CASIM_NUM_PLANES * CASIM_GPLANE_WORDS;
+    int nmixed = 0;
+    /* ---- phase 1: classify every word ---- */
+    for (int w0 = 0; w0 < nwords; w0 += 32) {
+      int wi = w0 + lane;
+      bool mixed = false;
+      if (wi < nwords) {
+        int oy = wi / wpr, ox0 = (wi - oy * wpr) << 2;
+        int rx = s_rx[wid][oy], ry = s_ry[wid][oy];
+        int xa = (rx + s_cx[wid][ox0]) >> 10, xb = (rx + s_cx[wid][ox0 + 3]) >> 10;
+        int ya = (ry + s_cy[wid][ox0]) >> 10, yb = (ry + s_cy[wid][ox0 + 3]) >> 10;
+        int xm = min(xa, xb), ym = min(ya, yb);
+        uint32_t code = (__ldg(cls + ym * CASIM_GCLS_WORDS + (xm >> 4)) >> ((xm & 15) << 1)) & 3u;
+        mixed = code == 0u;
+        if (!mixed) out[wi] = (code & 2u) ? 0x01010101u : 0u;
+      }
+      unsigned bal = __ballot_sync(FULL_MASK, mixed);
+      if (mixed) s_list[wid][nmixed + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)wi;
+      nmixed += __popc(bal);
+    }
+    __syncwarp();
+    /* ---- phase 2: exact cells of the mixed words ---- */
+    for (int m = lane; m < nmixed; m += 32) {
+      int wi = s_list[wid][m];
+      int oy = wi / wpr, ox0 = (wi - oy * wpr) << 2;
+      int rx = s_rx[wid][oy], ry = s_ry[wid][oy];
+      uint32_t word = 0;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        int X = (rx + s_cx[wid][ox0 + k]) >> 5, Y = (ry + s_cy[wid][ox0 + k]) >> 5;
+        word |= grid_cell_exact(gp, X, Y) << (8 * k);
+      }
+      out[wi] = word;
+    }
+  }
+  __syncwarp();
+  /* ---- phase 3: coalesced copy-out ---- */
+  const uint4* so = reinterpret_cast<const uint4*>(out);
+  for (int i = lane; i < (nwords >> 2); i += 32) gout[i] = so[i];
+}
+
 }  // namespace
 
 cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laserscan, cudaStream_t s) {
@@ -237,12 +399,19 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
   a.pose64 = h->pose64;
   a.n_agents = h->n_agents;
   a.map_planes = h->map_planes;
+  a.grid_maps = h->grid_maps;
   a.n_maps = h->n_maps;
   a.out = local_grid;
   a.E = h->E;
   a.A = h->A;
   long long N = (long long)h->E * h->A;
   h->launches++;
-  k_grid<<<(unsigned)N, 256, 0, s>>>(a);
+  const int cells = h->dc.submap_w * h->dc.submap_h;
+  /* fast path: rows are whole 4-cell words, every agent's grid is 16-byte aligned and a multiple of 16 bytes */
+  const bool fast = (h->dc.submap_h & 3) == 0 && (cells & 15) == 0 && (((uintptr_t)local_grid) & 15) == 0;
+  if (fast)
+    k_grid<<<(unsigned)((N + GRID_WARPS - 1) / GRID_WARPS), 32 * GRID_WARPS, 0, s>>>(a);
+  else
+    k_grid_generic<<<(unsigned)N, 256, 0, s>>>(a);
   return cudaGetLastError();
 }

@@ -296,3 +296,38 @@ def test_c2_full_size_properties(oracle_lib, torch_mod):
     g = {k: (None if v is None else v[sel]) for k, v in bufs_numpy(sim).items() if k != "stats"}
     H.compare_step("C2 sample", b["n_agents"][sel], sim.state_numpy()[sel], g, ostate, oobs)
     sim.close()
+
+
+def test_occupancy_grid_far_outside_and_edge_agents(oracle_lib, torch_mod):
+    """OccupancyGridSensor for agents on the map border and far off the grid (the rotated window leaves the padded
+    fast-path planes -> bounds-checked path), on both maps, against the oracle: cells bit-exact."""
+    oracle = oracle_lib
+    maps, rects = H.unpack_maps()
+    rng = np.random.default_rng(77)
+    pos = [(14.96, 14.96), (-14.99, 14.2), (14.3, -14.97), (-15.0, -15.0), (15.2, 3.0), (-16.0, -2.0), (0.0, 22.0),
+           (31.0, 31.0), (-45.0, 7.0), (250.0, -90.0), (3.0e4, 2.0e4), (14.0, 0.05), (0.0, 0.0), (9.9, 9.9)]
+    E, A = len(pos), 2
+    cfg = gcfg(0)
+    t = L.encode_type(L.POLICY_STATIC, L.DYN_UNICYCLE, L.SENSOR_OCCUPANCY_GRID)
+    st = np.zeros((E, A, L.STATE_WORDS))
+    for e, (x, y) in enumerate(pos):
+        for a in range(A):
+            st[e, a, L.PX], st[e, a, L.PY] = x + 0.37 * a, y - 0.21 * a
+            st[e, a, L.HEADING] = rng.uniform(-np.pi, np.pi)
+            st[e, a, L.RADIUS] = 0.4
+            st[e, a, L.PREF_SPEED] = 1.0
+            st[e, a, L.TYPE] = t
+    st = H.f32(st)
+    st[..., L.TYPE] = t
+    for mid in (1, 2):
+        sim = make_sim(E, A, cfg, sensors=("local_grid",))
+        sim.set_obstacles(rects[mid].astype(np.float32))
+        sim.bind(types=st[..., L.TYPE].astype(np.int32), n_agents=np.full((E,), A, np.int32))
+        sim.load_state_numpy(st)
+        sim.observe()
+        torch_mod.cuda.synchronize()
+        oobs = oracle.observe(cfg, st, maps=maps[mid])
+        g = sim.buf["local_grid"].cpu().numpy()
+        assert np.array_equal(g, oobs.local_grid), (mid, np.argwhere(g != oobs.local_grid)[:5])
+        assert g.any()
+        sim.close()
