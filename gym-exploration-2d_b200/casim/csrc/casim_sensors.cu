@@ -224,6 +224,7 @@ __global__ void __launch_bounds__(256) k_grid_generic(const GridArgs p) {
  * Maps are unions of rectangles (Map.get_occupancy_grid), so most words are uniform.                 */
 #define GRID_WARPS 4
 #define GRID_MAXW 16  /* words per row (submap side <= 64) */
+#define GRID_MAXWORDS 1024 /* words per grid: the fast path takes grids of up to 4096 cells */
 
 __device__ __forceinline__ uint32_t grid_cell_exact(const uint32_t* __restrict__ gp, int X, int Y) {
   /* X, Y: biased 1/32-cell fixed point (already >> 5) */
@@ -233,20 +234,21 @@ __device__ __forceinline__ uint32_t grid_cell_exact(const uint32_t* __restrict__
   return (w >> (xi & 31)) & 1u;
 }
 
-__global__ void __launch_bounds__(32 * GRID_WARPS) k_grid(const GridArgs p) {
+__global__ void __launch_bounds__(32 * GRID_WARPS, 12) k_grid(const GridArgs p) {
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const long long N = (long long)p.E * p.A;
   const long long g = (long long)blockIdx.x * GRID_WARPS + wid;
-  __shared__ __align__(16) uint32_t s_out[GRID_WARPS][64 * GRID_MAXW];
-  __shared__ int s_rx[GRID_WARPS][64], s_ry[GRID_WARPS][64], s_cx[GRID_WARPS][64], s_cy[GRID_WARPS][64];
-  __shared__ uint16_t s_list[GRID_WARPS][64 * GRID_MAXW];
+  __shared__ __align__(16) uint8_t s_out[GRID_WARPS][GRID_MAXWORDS]; /* one nibble per output word: bit k = cell k */
+  __shared__ __align__(16) int2 s_r[GRID_WARPS][64];                 /* per destination row: (X, Y) terms */
+  __shared__ __align__(16) int s_cx[GRID_WARPS][64], s_cy[GRID_WARPS][64]; /* per destination column */
+  __shared__ uint16_t s_list[GRID_WARPS][GRID_MAXWORDS];
   if (g >= N) return;
   const int e = (int)(g / p.A), ai = (int)(g - (long long)e * p.A);
   const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
   const int H = c.submap_h, W = c.submap_w; /* out[oy*H + ox]: W rows of H cells */
   const int wpr = H >> 2, nwords = W * wpr;
-  uint32_t* out = s_out[wid];
+  uint8_t* out = s_out[wid];
   uint4* gout = reinterpret_cast<uint4*>(p.out + g * (long long)(H * W));
   const int type = __float_as_int(p.state[5 * N + g].w);
   const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_OCCUPANCY_GRID) && p.n_maps > 0;
@@ -292,8 +294,7 @@ __global__ void __launch_bounds__(32 * GRID_WARPS) k_grid(const GridArgs p) {
       cyd = rint(M3 * x * 1024);
     }
     ok = ok && fabs(rxd) < 5.0e8 && fabs(ryd) < 5.0e8 && fabs(cxd) < 5.0e8 && fabs(cyd) < 5.0e8;
-    s_rx[wid][t] = (int)rxd + 16 + BIAS;
-    s_ry[wid][t] = (int)ryd + 16 + BIAS;
+    s_r[wid][t] = make_int2((int)rxd + 16 + BIAS, (int)ryd + 16 + BIAS);
     s_cx[wid][t] = (int)cxd;
     s_cy[wid][t] = (int)cyd;
   }
@@ -301,7 +302,7 @@ __global__ void __launch_bounds__(32 * GRID_WARPS) k_grid(const GridArgs p) {
   /* the four corner cells bound every source coordinate (monotone terms) */
   if (lane < 4) {
     int oy = (lane & 1) ? W - 1 : 0, ox = (lane & 2) ? H - 1 : 0;
-    int xi = (s_rx[wid][oy] + s_cx[wid][ox]) >> 10, yi = (s_ry[wid][oy] + s_cy[wid][ox]) >> 10;
+    int xi = (s_r[wid][oy].x + s_cx[wid][ox]) >> 10, yi = (s_r[wid][oy].y + s_cy[wid][ox]) >> 10;
     ok = ok && xi >= 1 && yi >= 1 && xi < CASIM_GWORDS * 32 - CASIM_GBOX - 1 && yi < CASIM_GROWS - CASIM_GBOX - 1;
   }
   ok = __all_sync(FULL_MASK, ok);
@@ -315,59 +316,84 @@ __global__ void __launch_bounds__(32 * GRID_WARPS) k_grid(const GridArgs p) {
       int oy = wi / wpr, ox0 = (wi - oy * wpr) << 2;
       uint32_t word = 0;
       for (int k = 0; k < 4; k++) {
-        long long Xl = ((long long)s_rx[wid][oy] - BIAS + s_cx[wid][ox0 + k]) >> 5;
-        long long Yl = ((long long)s_ry[wid][oy] - BIAS + s_cy[wid][ox0 + k]) >> 5;
+        long long Xl = ((long long)s_r[wid][oy].x - BIAS + s_cx[wid][ox0 + k]) >> 5;
+        long long Yl = ((long long)s_r[wid][oy].y - BIAS + s_cy[wid][ox0 + k]) >> 5;
         int X = (int)Xl, Y = (int)Yl;
         int sxi = X >> 5, syi = Y >> 5, fx = X & 31, fy = Y & 31;
         uint32_t v = S(syi, sxi);
         if (fx > 0) v |= S(syi, sxi + 1);
         if (fy > 0) v |= S(syi + 1, sxi);
         if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
-        word |= v << (8 * k);
+        word |= v << k;
       }
-      out[wi] = word;
+      out[wi] = (uint8_t)word;
     }
   } else {
     const uint32_t* gp = p.grid_maps + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_GMAP_WORDS;
     const uint32_t* cls = gp + CASIM_NUM_PLANES * CASIM_GPLANE_WORDS;
     int nmixed = 0;
-    /* ---- phase 1: classify every word ---- */
-    for (int w0 = 0; w0 < nwords; w0 += 32) {
-      int wi = w0 + lane;
-      bool mixed = false;
-      if (wi < nwords) {
-        int oy = wi / wpr, ox0 = (wi - oy * wpr) << 2;
-        int rx = s_rx[wid][oy], ry = s_ry[wid][oy];
-        int xa = (rx + s_cx[wid][ox0]) >> 10, xb = (rx + s_cx[wid][ox0 + 3]) >> 10;
-        int ya = (ry + s_cy[wid][ox0]) >> 10, yb = (ry + s_cy[wid][ox0 + 3]) >> 10;
-        int xm = min(xa, xb), ym = min(ya, yb);
-        uint32_t code = (__ldg(cls + ym * CASIM_GCLS_WORDS + (xm >> 4)) >> ((xm & 15) << 1)) & 3u;
-        mixed = code == 0u;
-        if (!mixed) out[wi] = (code & 2u) ? 0x01010101u : 0u;
+    /* ---- phase 1: classify every word.  A lane keeps its word column (its column terms stay in registers) and
+     * walks down the rows: rpi rows of wpr words per iteration. ---- */
+    const int rpi = 32 / wpr;
+    const int lr = lane / wpr, wx = lane - lr * wpr;
+    const bool act = lr < rpi;
+    const int cxa = s_cx[wid][4 * wx], cxb = s_cx[wid][4 * wx + 3], cya = s_cy[wid][4 * wx], cyb = s_cy[wid][4 * wx + 3];
+    constexpr int U = 5; /* rows in flight per lane: the classification loads of a batch are independent */
+    for (int oy0 = 0; oy0 < W; oy0 += rpi * U) {
+      uint32_t cw[U];
+      int sh[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int oy = oy0 + u * rpi + lr;
+        cw[u] = 0u;
+        sh[u] = 0;
+        if (act && oy < W) {
+          const int2 r = s_r[wid][oy];
+          int xm = min(r.x + cxa, r.x + cxb) >> 10, ym = min(r.y + cya, r.y + cyb) >> 10;
+          cw[u] = __ldg(cls + ym * CASIM_GCLS_WORDS + (xm >> 4));
+          sh[u] = (xm & 15) << 1;
+        }
       }
-      unsigned bal = __ballot_sync(FULL_MASK, mixed);
-      if (mixed) s_list[wid][nmixed + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)wi;
-      nmixed += __popc(bal);
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int oy = oy0 + u * rpi + lr;
+        const bool valid = act && oy < W;
+        const uint32_t code = (cw[u] >> sh[u]) & 3u;
+        const bool mixed = valid && code == 0u;
+        if (valid && !mixed) out[oy * wpr + wx] = (code & 2u) ? (uint8_t)0xF : (uint8_t)0;
+        unsigned bal = __ballot_sync(FULL_MASK, mixed);
+        if (mixed) s_list[wid][nmixed + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)((oy << 4) | wx);
+        nmixed += __popc(bal);
+      }
     }
     __syncwarp();
     /* ---- phase 2: exact cells of the mixed words ---- */
     for (int m = lane; m < nmixed; m += 32) {
-      int wi = s_list[wid][m];
-      int oy = wi / wpr, ox0 = (wi - oy * wpr) << 2;
-      int rx = s_rx[wid][oy], ry = s_ry[wid][oy];
-      uint32_t word = 0;
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        int X = (rx + s_cx[wid][ox0 + k]) >> 5, Y = (ry + s_cy[wid][ox0 + k]) >> 5;
-        word |= grid_cell_exact(gp, X, Y) << (8 * k);
-      }
-      out[wi] = word;
+      const int en = s_list[wid][m];
+      const int oy = en >> 4, w4 = en & 15;
+      const int2 r = s_r[wid][oy];
+      const int4 cx = *reinterpret_cast<const int4*>(&s_cx[wid][4 * w4]);
+      const int4 cy = *reinterpret_cast<const int4*>(&s_cy[wid][4 * w4]);
+      uint32_t word = grid_cell_exact(gp, (r.x + cx.x) >> 5, (r.y + cy.x) >> 5);
+      word |= grid_cell_exact(gp, (r.x + cx.y) >> 5, (r.y + cy.y) >> 5) << 1;
+      word |= grid_cell_exact(gp, (r.x + cx.z) >> 5, (r.y + cy.z) >> 5) << 2;
+      word |= grid_cell_exact(gp, (r.x + cx.w) >> 5, (r.y + cy.w) >> 5) << 3;
+      out[oy * wpr + w4] = (uint8_t)word;
     }
   }
   __syncwarp();
   /* ---- phase 3: coalesced copy-out ---- */
-  const uint4* so = reinterpret_cast<const uint4*>(out);
-  for (int i = lane; i < (nwords >> 2); i += 32) gout[i] = so[i];
+  /* nibble -> four 0/1 bytes: bit k of b lands on bit 8k of b * (1 + 2^7 + 2^14 + 2^21) */
+  const uint32_t* so = reinterpret_cast<const uint32_t*>(out);
+  for (int i = lane; i < (nwords >> 2); i += 32) {
+    const uint32_t q = so[i];
+    uint4 v;
+    v.x = ((q & 0xFu) * 0x00204081u) & 0x01010101u;
+    v.y = (((q >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
+    v.z = (((q >> 16) & 0xFu) * 0x00204081u) & 0x01010101u;
+    v.w = (((q >> 24) & 0xFu) * 0x00204081u) & 0x01010101u;
+    gout[i] = v;
+  }
 }
 
 }  // namespace
