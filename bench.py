@@ -299,6 +299,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=200)
     ap.add_argument("--ga3c-fp32", action="store_true", help="c5: use the fp32 SIMT forward instead of the tensor-core path")
+    ap.add_argument("--no-stats", action="store_true", help="diagnostics: do not compute the per-step episode statistics")
     ap.add_argument("--ring", type=int, default=None, help="override the number of env batches in the ring (diagnostics)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -346,7 +347,7 @@ def main():
     stats_all = torch.zeros((max(K, Wm, args.e2e_steps), NUM_STATS), dtype=torch.float32, device=dev)
     sims = []
     for r in range(R):
-        sim = BatchedSim(E, A, cfg=cfg, sensors=W["sensors"], want_debug=False, want_misc=bool(W["sensors"]), want_stats=True)
+        sim = BatchedSim(E, A, cfg=cfg, sensors=W["sensors"], want_debug=False, want_misc=bool(W["sensors"]), want_stats=not args.no_stats)
         init, types, n, rects = scenario(wl, E, A, seed=1234 + 1000 * rank + r)
         if rects is not None:
             sim.set_obstacles(rects)
@@ -440,6 +441,8 @@ def main():
             "done": torch.zeros((E, A), dtype=torch.uint8).pin_memory(),
             "game_over": torch.zeros((E,), dtype=torch.uint8).pin_memory(),
             "stats": torch.zeros((NUM_STATS,), dtype=torch.float32).pin_memory()}
+    if args.no_stats:
+        del host["stats"]
     for name in W["sensors"]:
         host[name] = torch.zeros(sims[0].buf[name].shape, dtype=sims[0].buf[name].dtype).pin_memory()
     if W["sensors"]:
@@ -466,7 +469,7 @@ def main():
     e2e_value = float(E * A * Ke * world) / e2e_s
 
     # ---- per-step episode statistics: the one collective of the design (NCCL all-reduce of [8] floats) ----
-    stats = sims[0].buf["stats"].clone()
+    stats = sims[0].buf["stats"].clone() if sims[0].buf["stats"] is not None else torch.zeros((NUM_STATS,), device=dev)
     if world > 1:
         dist.all_reduce(stats)
     stats = [float(x) for x in stats.cpu()]

@@ -189,7 +189,8 @@ int casim_create(const casim_config* cfg, int E, int A, casim_handle** out) {
   cudaError_t e = cudaGetDevice(&h->device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device);
   int epw = 32 / A;
-  h->max_ctas = (E + epw - 1) / epw;
+  (void)epw;
+  h->max_ctas = E; /* upper bound of the core grid: one warp per environment, one warp per CTA */
   size_t N = (size_t)E * A;
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->pose64, N * 4 * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->prev_game_over, (size_t)E);
@@ -197,6 +198,7 @@ int casim_create(const casim_config* cfg, int E, int A, casim_handle** out) {
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->ticket, sizeof(unsigned int));
   if (e == cudaSuccess) e = cudaMemset(h->prev_game_over, 0, (size_t)E);
   if (e == cudaSuccess) e = cudaMemset(h->ticket, 0, sizeof(unsigned int));
+  if (e == cudaSuccess) e = cudaMemset(h->partials, 0, (size_t)h->max_ctas * CASIM_NUM_STATS * sizeof(double));
   if (e == cudaSuccess) e = cudaMemset(h->pose64, 0, N * 4 * sizeof(double));
   if (e != cudaSuccess) {
     casim_set_error("casim_create: %s", cudaGetErrorString(e));

@@ -35,6 +35,7 @@
  * The observation rows are staged in shared memory and written out as contiguous 16-byte stores.
  */
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "casim_device.cuh"
 
@@ -296,8 +297,6 @@ __device__ __forceinline__ void take_action(const DevCfg& c, Agent& a, float a0,
 template <int MODE, int AP>
 __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   extern __shared__ __align__(16) float s_stage[];
-  __shared__ double s_part[CASIM_CORE_WARPS][CASIM_NUM_STATS];
-  __shared__ bool s_last;
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
   const int warps_per_cta = blockDim.x >> 5;
@@ -496,6 +495,43 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     if (slot && ai == 0) p.prev_game_over[e] = 0;
   }
 
+  /* ---- per-step statistics: warp totals -> 64-bit integer accumulators (counts are integers, the reward sum is
+   * 2^-32 fixed point, so the result does not depend on the order of arrival) -> the last warp to arrive converts
+   * them to the float vector and clears them for the next launch.  Done BEFORE the state / observation stores so that
+   * the fence in front of the ticket does not wait for them. ---- */
+  if (MODE == CASIM_MODE_STEP && p.o.stats) {
+    long long v[CASIM_NUM_STATS];
+    v[0] = __reduce_add_sync(FULL_MASK, st_new_coll);
+    v[1] = __reduce_add_sync(FULL_MASK, st_new_goal);
+    v[2] = __reduce_add_sync(FULL_MASK, st_new_to);
+    v[3] = __reduce_add_sync(FULL_MASK, st_go);
+    v[4] = warp_sum(__double2ll_rn(st_rew * 4294967296.0));
+    v[5] = __reduce_add_sync(FULL_MASK, st_active);
+    v[6] = __reduce_add_sync(FULL_MASK, st_agents);
+    v[7] = 0;
+    /* 32 stripes of accumulators (one 64-byte line each) keep same-address contention low */
+    unsigned long long* acc = reinterpret_cast<unsigned long long*>(p.partials);
+    unsigned last = 0;
+    if (lane == 0) {
+      unsigned long long* mine = acc + (size_t)(w & 31) * CASIM_NUM_STATS;
+#pragma unroll
+      for (int k = 0; k < CASIM_NUM_STATS - 1; k++)
+        if (v[k] != 0) atomicAdd(mine + k, (unsigned long long)v[k]);
+      __threadfence();
+      const unsigned total = gridDim.x * warps_per_cta;
+      last = atomicInc(p.ticket, total - 1) == total - 1;
+    }
+    if (__shfl_sync(FULL_MASK, last, 0)) { /* lane = stripe */
+      __threadfence();
+#pragma unroll
+      for (int k = 0; k < CASIM_NUM_STATS; k++) {
+        long long t = k == CASIM_NUM_STATS - 1 ? 0ll : (long long)atomicExch(acc + (size_t)lane * CASIM_NUM_STATS + k, 0ull);
+        t = warp_sum(t);
+        if (lane == 0) p.o.stats[k] = k == 4 ? (float)((double)t * (1.0 / 4294967296.0)) : (float)t;
+      }
+    }
+  }
+
   /* ---- state write-back ---- */
   if (MODE == CASIM_MODE_STEP) {
     if (valid) store_agent(p.state, plane, g, a, wrote_all);
@@ -625,40 +661,6 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     reinterpret_cast<float4*>(p.o.obs_misc)[g] = mo;
   }
 
-  /* ---- per-step statistics: warp -> CTA -> last block (deterministic, atomic-free on the data) ---- */
-  if (MODE == CASIM_MODE_STEP && p.o.stats) {
-    int c0 = __reduce_add_sync(FULL_MASK, st_new_coll), c1 = __reduce_add_sync(FULL_MASK, st_new_goal);
-    int c2 = __reduce_add_sync(FULL_MASK, st_new_to), c3 = __reduce_add_sync(FULL_MASK, st_go);
-    int c5 = __reduce_add_sync(FULL_MASK, st_active), c6 = __reduce_add_sync(FULL_MASK, st_agents);
-    double rs = warp_sum(st_rew);
-    if (lane == 0) {
-      double* sp = s_part[warp_in_cta];
-      sp[0] = c0; sp[1] = c1; sp[2] = c2; sp[3] = c3; sp[4] = rs; sp[5] = c5; sp[6] = c6; sp[7] = 0;
-    }
-    __syncthreads();
-    if (threadIdx.x < CASIM_NUM_STATS) {
-      double s = 0;
-      for (int q = 0; q < warps_per_cta; q++) s += s_part[q][threadIdx.x];
-      p.partials[(size_t)blockIdx.x * CASIM_NUM_STATS + threadIdx.x] = s;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      unsigned int t = atomicInc(p.ticket, gridDim.x - 1);
-      s_last = (t == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (s_last && warp_in_cta == 0) {
-      __threadfence();
-#pragma unroll
-      for (int k = 0; k < CASIM_NUM_STATS; k++) {
-        double s = 0;
-        for (int b = lane; b < (int)gridDim.x; b += 32) s += __ldcg(p.partials + (size_t)b * CASIM_NUM_STATS + k);
-        s = warp_sum(s);
-        if (lane == 0) p.o.stats[k] = (float)s;
-      }
-    }
-  }
 }
 
 template <int MODE>
@@ -714,6 +716,16 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
   a.E = h->E;
   a.A = h->A;
   a.epw = 32 / h->A;
+  {
+    /* The step is latency-bound at the named batch sizes (a few thousand warps for the whole GPU): fewer
+     * environments per warp means more warps in flight per scheduler.  CASIM_EPW overrides (tuning aid). */
+    static int epw_env = -1;
+    if (epw_env < 0) {
+      const char* ev = getenv("CASIM_EPW");
+      epw_env = ev ? atoi(ev) : 0;
+    }
+    if (epw_env > 0 && epw_env < a.epw) a.epw = epw_env;
+  }
   a.write_pose = (obs->laserscan != nullptr || obs->local_grid != nullptr) ? 1 : 0;
   static const int aps[] = {2, 4, 6, 8, 10, 12, 16, 20, 24, 32};
   int ap = 32;
