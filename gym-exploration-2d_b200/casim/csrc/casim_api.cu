@@ -222,6 +222,7 @@ int casim_destroy(casim_handle* h) {
   cudaFree(h->ga3c_w);
   cudaFree(h->ga3c_wb);
   cudaFree(h->ga3c_x);
+  cudaFree(h->ga3c_xb);
   free(h);
   return 0;
 }

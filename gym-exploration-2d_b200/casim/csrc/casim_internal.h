@@ -78,6 +78,7 @@ struct casim_handle {
   float* ga3c_w;           /* fp32 parameter blob on the device */
   void* ga3c_wb;           /* bf16 tiles for the tensor-core path */
   float* ga3c_x;           /* [E*A][76] network input scratch */
+  void* ga3c_xb;           /* [tiles][10][128] x 16 B: bf16 LSTM input chunks for the tensor-core path */
   unsigned long long launches;
 };
 

@@ -46,7 +46,7 @@ def test_ga3c_state_vector_golden(oracle_lib):
         sim.close()
 
 
-@pytest.mark.parametrize("use_tc", [False])
+@pytest.mark.parametrize("use_tc", [False, True])
 def test_ga3c_forward_vs_oracle(oracle_lib, use_tc):
     import torch
     from casim import scenarios as S
