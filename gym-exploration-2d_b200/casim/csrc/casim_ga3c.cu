@@ -94,20 +94,27 @@ __device__ __forceinline__ long long py_round2_hundredths(double x) {
   return x < 0.0 ? -k : k;
 }
 
-__global__ void __launch_bounds__(128) k_ga3c_state(const Ga3cArgs p) {
+/* One warp per agent, lane j <-> other agent j of the same environment (A <= 32): every lane evaluates one
+ * candidate (distance, rounded key, p_orthog), the stable rank of sorted(key = (-round(dist, 2), p_orthog)) is counted
+ * with shuffles, and the 76-float row is assembled in shared memory so that x / nn_input / xb leave the warp as
+ * contiguous stores. */
+#define GS_WARPS 8
+__global__ void __launch_bounds__(GS_WARPS * 32) k_ga3c_state(const Ga3cArgs p) {
+  __shared__ __align__(16) float s_row[GS_WARPS][G_XS + 4];
   const DevCfg& c = p.c;
   const size_t N = (size_t)p.E * p.A;
-  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const size_t g = (size_t)blockIdx.x * GS_WARPS + wib;
   if (g >= N) return;
   const int e = (int)(g / p.A), i = (int)(g - (size_t)e * p.A);
   const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
   float* x = p.x + g * G_XS;
+  float* row = s_row[wib];
   const int type = __float_as_int(p.state[5 * N + g].w);
   uint4* xb = p.xb ? p.xb + (g / T_M) * (size_t)(G_SLOTS * T_M) + (g % T_M) : nullptr;
   if (i >= n || (type & 0xff) != CASIM_POLICY_GA3C_CADRL) {
-    x[0] = -1.f; /* marks "no GA3C agent in this slot" for the forward kernel */
-    if (xb)
-      for (int sl = 0; sl < G_SLOTS; sl++) xb[sl * T_M] = make_uint4(0u, 0u, 0u, 0u);
+    if (lane == 0) x[0] = -1.f; /* marks "no GA3C agent in this slot" for the forward kernel */
+    if (xb && lane < G_SLOTS) xb[lane * T_M] = make_uint4(0u, 0u, 0u, 0u);
     return;
   }
   const size_t base = (size_t)e * p.A;
@@ -122,70 +129,66 @@ __global__ void __launch_bounds__(128) k_ga3c_state(const Ga3cArgs p) {
     pry = gy / dg;
   }
   const double orx = -pry, ory = prx;
-  int kr[CASIM_MAX_AGENTS];
-  double po[CASIM_MAX_AGENTS];
-  int m = 0;
-  for (int j = 0; j < n; j++) {
-    kr[j] = INT_MIN; /* not a candidate */
-    po[j] = 0.0;
-    if (j == i) continue;
-    const float4 o0 = p.state[base + j], o2 = p.state[2 * N + base + j];
-    double rx = (double)o0.x - px, ry = (double)o0.y - py;
-    double dc = sqrt(rx * rx + ry * ry);
-    if (dc > c.sensing_horizon) continue;
-    double d2o = dc - rh - (double)o2.z;
-    kr[j] = (int)py_round2_hundredths(d2o);
-    po[j] = rx * orx + ry * ory;
-    m++;
+  /* my candidate: other agent j = lane */
+  const int j = lane;
+  bool cand = j < n && j != i;
+  float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
+  if (cand) {
+    o0 = p.state[base + j];
+    o1 = p.state[N + base + j];
+    o2 = p.state[2 * N + base + j];
   }
-  int K = min(min(m, c.max_obs), G_SLOTS);
-  for (int k = 1; k < G_IN; k++) x[k] = 0.f;
-  x[0] = (float)K;
-  x[1] = h3.z;  /* dist_to_goal */
-  x[2] = h5.x;  /* heading_ego_frame */
-  x[3] = h2.w;  /* pref_speed */
-  x[4] = h2.z;  /* radius */
+  const double rx = (double)o0.x - px, ry = (double)o0.y - py;
+  const double dc = sqrt(rx * rx + ry * ry);
+  if (dc > c.sensing_horizon) cand = false;
+  const double d2o = dc - rh - (double)o2.z;
+  const int kr = cand ? (int)py_round2_hundredths(d2o) : INT_MIN;
+  const double po = rx * orx + ry * ory;
+  const unsigned cmask = __ballot_sync(FULL_MASK, cand);
+  const int m = __popc(cmask);
+  const int K = min(min(m, c.max_obs), G_SLOTS);
   /* sorted(key = (-round(dist, 2), p_orthog)) is stable: rank = number of candidates that sort before me */
-  for (int j = 0; j < n; j++) {
-    if (kr[j] == INT_MIN) continue;
-    int rank = 0;
-    for (int k = 0; k < n; k++) {
-      if (k == j || kr[k] == INT_MIN) continue;
-      bool before = (kr[k] > kr[j]) || (kr[k] == kr[j] && (po[k] < po[j] || (po[k] == po[j] && k < j)));
-      rank += before;
-    }
-    int slot = rank - (m - K); /* keep the last K of the ascending order */
-    if (slot < 0) continue;
-    const float4 o0 = p.state[base + j], o1 = p.state[N + base + j], o2 = p.state[2 * N + base + j];
-    double rx = (double)o0.x - px, ry = (double)o0.y - py;
-    double vx = o1.x, vy = o1.y;
-    float* w = x + 1 + G_HOST + G_OTHER * slot;
+  int rank = 0;
+  for (int k = 0; k < n; k++) {
+    const int krk = __shfl_sync(FULL_MASK, kr, k);
+    const double pok = __shfl_sync(FULL_MASK, po, k);
+    const bool before = (krk > kr) || (krk == kr && (pok < po || (pok == po && k < j)));
+    rank += ((cmask >> k) & 1u) && k != j && before;
+  }
+  for (int k = lane; k < G_XS; k += 32) row[k] = 0.f;
+  __syncwarp();
+  if (lane == 0) {
+    row[0] = (float)K;
+    row[1] = h3.z; /* dist_to_goal */
+    row[2] = h5.x; /* heading_ego_frame */
+    row[3] = h2.w; /* pref_speed */
+    row[4] = h2.z; /* radius */
+  }
+  const int slot = rank - (m - K); /* keep the last K of the ascending order */
+  if (cand && slot >= 0) {
+    const double vx = o1.x, vy = o1.y;
+    float* w = row + 1 + G_HOST + G_OTHER * slot;
     w[0] = (float)(rx * prx + ry * pry);
-    w[1] = (float)(rx * orx + ry * ory);
+    w[1] = (float)po;
     w[2] = (float)(vx * prx + vy * pry);
     w[3] = (float)(vx * orx + vy * ory);
     w[4] = o2.z;
     w[5] = (float)(rh + (double)o2.z);
-    w[6] = (float)(sqrt(rx * rx + ry * ry) - rh - (double)o2.z);
+    w[6] = (float)d2o;
   }
+  __syncwarp();
+  for (int k = lane; k < G_IN; k += 32) x[k] = row[k];
   if (p.nn_input) {
     float* o = p.nn_input + g * G_IN;
-    for (int k = 0; k < G_IN; k++) o[k] = x[k];
+    for (int k = lane; k < G_IN; k += 32) o[k] = row[k];
   }
-  if (xb) { /* tensor-core path: per slot the K-chunk [x_0..x_6 normalised, 1.0] of the LSTM A operand */
-    for (int sl = 0; sl < G_SLOTS; sl++) {
-      const float* v = x + 1 + G_HOST + G_OTHER * sl;
-      float nv[8];
+  if (xb && lane < G_SLOTS) { /* tensor-core path: per slot the K-chunk [x_0..x_6 normalised, 1.0] of the LSTM A operand */
+    const float* v = row + 1 + G_HOST + G_OTHER * lane;
+    float nv[8];
 #pragma unroll
-      for (int k = 0; k < G_OTHER; k++) nv[k] = (v[k] - c_oth_avg[k]) / c_oth_std[k];
-      nv[7] = 1.0f;
-      uint4 q;
-      q.x = pack_bf16(nv[0], nv[1]);
-      q.y = pack_bf16(nv[2], nv[3]);
-      q.z = pack_bf16(nv[4], nv[5]);
-      q.w = pack_bf16(nv[6], nv[7]);
-      xb[sl * T_M] = q;
-    }
+    for (int k = 0; k < G_OTHER; k++) nv[k] = (v[k] - c_oth_avg[k]) / c_oth_std[k];
+    nv[7] = 1.0f;
+    xb[lane * T_M] = make_uint4(pack_bf16(nv[0], nv[1]), pack_bf16(nv[2], nv[3]), pack_bf16(nv[4], nv[5]), pack_bf16(nv[6], nv[7]));
   }
 }
 
@@ -866,7 +869,7 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
   a.E = h->E;
   a.A = h->A;
   h->launches += 2;
-  k_ga3c_state<<<(unsigned)((N + 127) / 128), 128, 0, s>>>(a);
+  k_ga3c_state<<<(unsigned)((N + GS_WARPS - 1) / GS_WARPS), GS_WARPS * 32, 0, s>>>(a);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   if (use_tc)
