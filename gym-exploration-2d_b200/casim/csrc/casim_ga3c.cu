@@ -94,101 +94,157 @@ __device__ __forceinline__ long long py_round2_hundredths(double x) {
   return x < 0.0 ? -k : k;
 }
 
-/* One warp per agent, lane j <-> other agent j of the same environment (A <= 32): every lane evaluates one
- * candidate (distance, rounded key, p_orthog), the stable rank of sorted(key = (-round(dist, 2), p_orthog)) is counted
- * with shuffles, and the 76-float row is assembled in shared memory so that x / nn_input / xb leave the warp as
- * contiguous stores. */
-#define GS_WARPS 8
-__global__ void __launch_bounds__(GS_WARPS * 32) k_ga3c_state(const Ga3cArgs p) {
-  __shared__ __align__(16) float s_row[GS_WARPS][G_XS + 4];
+/* One CTA per group of 32 consecutive agent slots.  fp64 is scarce on B200, so every fp64 instruction runs with
+ * (nearly) all lanes useful: phase A = one lane per agent (reference frame), phase B = one lane per (agent, other)
+ * pair (distance, rounded key, p_orthog), phase C = stable rank of sorted(key = (-round(dist, 2), p_orthog)) per pair
+ * (integer compares, fp64 only on key ties), then the 76-float rows are assembled in shared memory and leave the
+ * CTA as contiguous stores (x, nn_input) and 16-byte bf16 chunks (xb). */
+#define GS_AG 32
+#define GS_THREADS 128
+__global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
+  __shared__ double s_fr[GS_AG][6];                 /* px, py, prx, pry, rh, - */
+  __shared__ double s_po[GS_AG][CASIM_MAX_AGENTS];
+  __shared__ int s_kr[GS_AG][CASIM_MAX_AGENTS];
+  __shared__ int s_m[GS_AG], s_n[GS_AG], s_ok[GS_AG];
+  __shared__ __align__(16) float s_row[GS_AG][G_XS];
   const DevCfg& c = p.c;
   const size_t N = (size_t)p.E * p.A;
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const size_t g = (size_t)blockIdx.x * GS_WARPS + wib;
-  if (g >= N) return;
-  const int e = (int)(g / p.A), i = (int)(g - (size_t)e * p.A);
-  const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
-  float* x = p.x + g * G_XS;
-  float* row = s_row[wib];
-  const int type = __float_as_int(p.state[5 * N + g].w);
-  uint4* xb = p.xb ? p.xb + (g / T_M) * (size_t)(G_SLOTS * T_M) + (g % T_M) : nullptr;
-  if (i >= n || (type & 0xff) != CASIM_POLICY_GA3C_CADRL) {
-    if (lane == 0) x[0] = -1.f; /* marks "no GA3C agent in this slot" for the forward kernel */
-    if (xb && lane < G_SLOTS) xb[lane * T_M] = make_uint4(0u, 0u, 0u, 0u);
-    return;
+  const int tid = threadIdx.x, A = p.A;
+  const size_t gb = (size_t)blockIdx.x * GS_AG;
+  const int nag = (int)min((size_t)GS_AG, N - gb);
+  for (int k = tid; k < GS_AG * G_XS; k += GS_THREADS) (&s_row[0][0])[k] = 0.f;
+  if (tid < GS_AG) { /* phase A */
+    const int a = tid;
+    int ok = 0, n = 0;
+    if (a < nag) {
+      const size_t g = gb + a;
+      const int e = (int)(g / A), i = (int)(g - (size_t)e * A);
+      n = p.n_agents ? min(p.n_agents[e], A) : A;
+      const int type = __float_as_int(p.state[5 * N + g].w);
+      ok = (i < n && (type & 0xff) == CASIM_POLICY_GA3C_CADRL) ? 1 : 0;
+      if (ok) {
+        const float4 h0 = p.state[g], h2 = p.state[2 * N + g];
+        const double px = h0.x, py = h0.y;
+        /* agent.py:250-269 get_ref */
+        double gx = (double)h2.x - px, gy = (double)h2.y - py;
+        const double dg = sqrt(gx * gx + gy * gy);
+        if (dg > 1e-8) {
+          gx = gx / dg;
+          gy = gy / dg;
+        }
+        s_fr[a][0] = px;
+        s_fr[a][1] = py;
+        s_fr[a][2] = gx;
+        s_fr[a][3] = gy;
+        s_fr[a][4] = (double)h2.z;
+      }
+    }
+    s_ok[a] = ok;
+    s_n[a] = n;
+    s_m[a] = 0;
   }
-  const size_t base = (size_t)e * p.A;
-  const float4 h0 = p.state[g], h2 = p.state[2 * N + g], h3 = p.state[3 * N + g], h5 = p.state[5 * N + g];
-  const double px = h0.x, py = h0.y, rh = h2.z;
-  /* agent.py:250-269 get_ref */
-  double gx = (double)h2.x - px, gy = (double)h2.y - py;
-  double dg = sqrt(gx * gx + gy * gy);
-  double prx = gx, pry = gy;
-  if (dg > 1e-8) {
-    prx = gx / dg;
-    pry = gy / dg;
+  __syncthreads();
+  const int npairs = nag * A;
+  for (int idx = tid; idx < npairs; idx += GS_THREADS) { /* phase B */
+    const int a = idx / A, j = idx - a * A;
+    int kr = INT_MIN;
+    double po = 0.0;
+    if (s_ok[a]) {
+      const size_t g = gb + a;
+      const int e = (int)(g / A), i = (int)(g - (size_t)e * A);
+      if (j < s_n[a] && j != i) {
+        const size_t o = (size_t)e * A + j;
+        const float4 o0 = p.state[o], o2 = p.state[2 * N + o];
+        const double rx = (double)o0.x - s_fr[a][0], ry = (double)o0.y - s_fr[a][1];
+        const double dc = sqrt(rx * rx + ry * ry);
+        if (!(dc > c.sensing_horizon)) {
+          kr = (int)py_round2_hundredths(dc - s_fr[a][4] - (double)o2.z);
+          po = rx * (-s_fr[a][3]) + ry * s_fr[a][2];
+          atomicAdd(&s_m[a], 1);
+        }
+      }
+    }
+    s_kr[a][j] = kr;
+    s_po[a][j] = po;
   }
-  const double orx = -pry, ory = prx;
-  /* my candidate: other agent j = lane */
-  const int j = lane;
-  bool cand = j < n && j != i;
-  float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
-  if (cand) {
-    o0 = p.state[base + j];
-    o1 = p.state[N + base + j];
-    o2 = p.state[2 * N + base + j];
-  }
-  const double rx = (double)o0.x - px, ry = (double)o0.y - py;
-  const double dc = sqrt(rx * rx + ry * ry);
-  if (dc > c.sensing_horizon) cand = false;
-  const double d2o = dc - rh - (double)o2.z;
-  const int kr = cand ? (int)py_round2_hundredths(d2o) : INT_MIN;
-  const double po = rx * orx + ry * ory;
-  const unsigned cmask = __ballot_sync(FULL_MASK, cand);
-  const int m = __popc(cmask);
-  const int K = min(min(m, c.max_obs), G_SLOTS);
-  /* sorted(key = (-round(dist, 2), p_orthog)) is stable: rank = number of candidates that sort before me */
-  int rank = 0;
-  for (int k = 0; k < n; k++) {
-    const int krk = __shfl_sync(FULL_MASK, kr, k);
-    const double pok = __shfl_sync(FULL_MASK, po, k);
-    const bool before = (krk > kr) || (krk == kr && (pok < po || (pok == po && k < j)));
-    rank += ((cmask >> k) & 1u) && k != j && before;
-  }
-  for (int k = lane; k < G_XS; k += 32) row[k] = 0.f;
-  __syncwarp();
-  if (lane == 0) {
-    row[0] = (float)K;
-    row[1] = h3.z; /* dist_to_goal */
-    row[2] = h5.x; /* heading_ego_frame */
-    row[3] = h2.w; /* pref_speed */
-    row[4] = h2.z; /* radius */
-  }
-  const int slot = rank - (m - K); /* keep the last K of the ascending order */
-  if (cand && slot >= 0) {
+  __syncthreads();
+  for (int idx = tid; idx < npairs; idx += GS_THREADS) { /* phase C */
+    const int a = idx / A, j = idx - a * A;
+    const int kr = s_kr[a][j];
+    if (kr == INT_MIN) continue;
+    const double po = s_po[a][j];
+    const int n = s_n[a], m = s_m[a];
+    const int K = min(min(m, c.max_obs), G_SLOTS);
+    int rank = 0; /* stable sort: number of candidates that sort before me */
+    for (int k = 0; k < n; k++) {
+      const int krk = s_kr[a][k];
+      bool before = krk > kr;
+      if (krk == kr && k != j) {
+        const double pok = s_po[a][k];
+        before = pok < po || (pok == po && k < j);
+      }
+      rank += (krk != INT_MIN) && before;
+    }
+    const int slot = rank - (m - K); /* keep the last K of the ascending order */
+    if (slot < 0) continue;
+    const size_t g = gb + a;
+    const size_t o = (g / A) * A + j;
+    const float4 o0 = p.state[o], o1 = p.state[N + o], o2 = p.state[2 * N + o];
+    const double prx = s_fr[a][2], pry = s_fr[a][3], rh = s_fr[a][4];
+    const double rx = (double)o0.x - s_fr[a][0], ry = (double)o0.y - s_fr[a][1];
     const double vx = o1.x, vy = o1.y;
-    float* w = row + 1 + G_HOST + G_OTHER * slot;
+    float* w = &s_row[a][1 + G_HOST + G_OTHER * slot];
     w[0] = (float)(rx * prx + ry * pry);
     w[1] = (float)po;
     w[2] = (float)(vx * prx + vy * pry);
-    w[3] = (float)(vx * orx + vy * ory);
+    w[3] = (float)(vx * (-pry) + vy * prx);
     w[4] = o2.z;
     w[5] = (float)(rh + (double)o2.z);
-    w[6] = (float)d2o;
+    w[6] = (float)(sqrt(rx * rx + ry * ry) - rh - (double)o2.z);
   }
-  __syncwarp();
-  for (int k = lane; k < G_IN; k += 32) x[k] = row[k];
-  if (p.nn_input) {
-    float* o = p.nn_input + g * G_IN;
-    for (int k = lane; k < G_IN; k += 32) o[k] = row[k];
+  if (tid < nag) {
+    const int a = tid;
+    if (s_ok[a]) {
+      const size_t g = gb + a;
+      const float4 h2 = p.state[2 * N + g], h3 = p.state[3 * N + g], h5 = p.state[5 * N + g];
+      s_row[a][0] = (float)min(min(s_m[a], c.max_obs), G_SLOTS);
+      s_row[a][1] = h3.z; /* dist_to_goal */
+      s_row[a][2] = h5.x; /* heading_ego_frame */
+      s_row[a][3] = h2.w; /* pref_speed */
+      s_row[a][4] = h2.z; /* radius */
+    } else {
+      s_row[a][0] = -1.f; /* marks "no GA3C agent in this slot" for the forward kernels */
+    }
   }
-  if (xb && lane < G_SLOTS) { /* tensor-core path: per slot the K-chunk [x_0..x_6 normalised, 1.0] of the LSTM A operand */
-    const float* v = row + 1 + G_HOST + G_OTHER * lane;
-    float nv[8];
+  __syncthreads();
+  {
+    float* x = p.x + gb * G_XS; /* rows are contiguous: G_XS floats per agent */
+    const float* src = &s_row[0][0];
+    for (int k = tid; k < nag * G_XS; k += GS_THREADS) x[k] = src[k];
+    if (p.nn_input) {
+      float* o = p.nn_input + gb * G_IN;
+      for (int k = tid; k < nag * G_IN; k += GS_THREADS) {
+        const int a = k / G_IN, q = k - a * G_IN;
+        if (s_ok[a]) o[k] = s_row[a][q];
+      }
+    }
+  }
+  if (p.xb) { /* tensor-core path: per (slot, agent) the K-chunk [x_0..x_6 normalised, 1.0] of the LSTM A operand */
+    for (int idx = tid; idx < G_SLOTS * GS_AG; idx += GS_THREADS) {
+      const int sl = idx / GS_AG, a = idx - sl * GS_AG;
+      if (a >= nag) continue;
+      const size_t g = gb + a;
+      uint4 q = make_uint4(0u, 0u, 0u, 0u);
+      if (s_ok[a]) {
+        const float* v = &s_row[a][1 + G_HOST + G_OTHER * sl];
+        float nv[8];
 #pragma unroll
-    for (int k = 0; k < G_OTHER; k++) nv[k] = (v[k] - c_oth_avg[k]) / c_oth_std[k];
-    nv[7] = 1.0f;
-    xb[lane * T_M] = make_uint4(pack_bf16(nv[0], nv[1]), pack_bf16(nv[2], nv[3]), pack_bf16(nv[4], nv[5]), pack_bf16(nv[6], nv[7]));
+        for (int k = 0; k < G_OTHER; k++) nv[k] = (v[k] - c_oth_avg[k]) / c_oth_std[k];
+        nv[7] = 1.0f;
+        q = make_uint4(pack_bf16(nv[0], nv[1]), pack_bf16(nv[2], nv[3]), pack_bf16(nv[4], nv[5]), pack_bf16(nv[6], nv[7]));
+      }
+      p.xb[(g / T_M) * (size_t)(G_SLOTS * T_M) + (size_t)sl * T_M + (g % T_M)] = q;
+    }
   }
 }
 
@@ -869,7 +925,7 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
   a.E = h->E;
   a.A = h->A;
   h->launches += 2;
-  k_ga3c_state<<<(unsigned)((N + GS_WARPS - 1) / GS_WARPS), GS_WARPS * 32, 0, s>>>(a);
+  k_ga3c_state<<<(unsigned)((N + GS_AG - 1) / GS_AG), GS_THREADS, 0, s>>>(a);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   if (use_tc)
