@@ -71,7 +71,8 @@ __constant__ float c_oth_std[7] = {5.0f, 5.0f, 1.0f, 1.0f, 1.0f, 5.0f, 1.0f};
 /* network.py:8-17 Actions, np.mgrid rows = start + k*step (filled by casim_ga3c_upload) */
 __constant__ float c_actions[G_ACT][2];
 
-#define T_M 128 /* agents per CTA of the tensor-core path = UMMA M */
+#define U_NA 144 /* agents per CTA of the tensor-core path */
+#define U_XB_SLOTS 11
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi); /* .x = lo (low half) */
@@ -229,21 +230,29 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
       }
     }
   }
-  if (p.xb) { /* tensor-core path: per (slot, agent) the K-chunk [x_0..x_6 normalised, 1.0] of the LSTM A operand */
-    for (int idx = tid; idx < G_SLOTS * GS_AG; idx += GS_THREADS) {
+  if (p.xb) { /* tensor-core path: plane sl < 10 = per agent the K chunk [x_0..x_6 normalised, 1.0] of LSTM step sl;
+                 plane 10 = header {host inputs normalised (network.py:83-84), 1, 1, sequence length or -1} */
+    const size_t npad = (N + U_NA - 1) / U_NA * U_NA;
+    for (int idx = tid; idx < U_XB_SLOTS * GS_AG; idx += GS_THREADS) {
       const int sl = idx / GS_AG, a = idx - sl * GS_AG;
       if (a >= nag) continue;
-      const size_t g = gb + a;
-      uint4 q = make_uint4(0u, 0u, 0u, 0u);
+      uint4 q = make_uint4(0u, 0u, 0u, sl == G_SLOTS ? 0xffffffffu : 0u);
       if (s_ok[a]) {
-        const float* v = &s_row[a][1 + G_HOST + G_OTHER * sl];
-        float nv[8];
+        if (sl < G_SLOTS) {
+          const float* v = &s_row[a][1 + G_HOST + G_OTHER * sl];
+          float nv[8];
 #pragma unroll
-        for (int k = 0; k < G_OTHER; k++) nv[k] = (v[k] - c_oth_avg[k]) / c_oth_std[k];
-        nv[7] = 1.0f;
-        q = make_uint4(pack_bf16(nv[0], nv[1]), pack_bf16(nv[2], nv[3]), pack_bf16(nv[4], nv[5]), pack_bf16(nv[6], nv[7]));
+          for (int k = 0; k < G_OTHER; k++) nv[k] = (v[k] - c_oth_avg[k]) / c_oth_std[k];
+          nv[7] = 1.0f;
+          q = make_uint4(pack_bf16(nv[0], nv[1]), pack_bf16(nv[2], nv[3]), pack_bf16(nv[4], nv[5]), pack_bf16(nv[6], nv[7]));
+        } else {
+          float hv[4];
+#pragma unroll
+          for (int k = 0; k < G_HOST; k++) hv[k] = (s_row[a][1 + k] - c_host_avg[k]) / c_host_std[k];
+          q = make_uint4(pack_bf16(hv[0], hv[1]), pack_bf16(hv[2], hv[3]), 0x3f803f80u, (uint32_t)(int)s_row[a][0]);
+        }
       }
-      p.xb[(g / T_M) * (size_t)(G_SLOTS * T_M) + (size_t)sl * T_M + (g % T_M)] = q;
+      p.xb[(size_t)sl * npad + gb + a] = q;
     }
   }
 }
@@ -437,33 +446,44 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
 }
 
 /* ------------------------------------------------------------------------------------------------------------
- * k_ga3c_tc: the same network on the 5th-generation tensor cores (tcgen05.mma, kind::f16, bf16 x bf16 -> fp32).
+ * k_ga3c_tc: the same network on the 5th-generation tensor cores (tcgen05.mma, kind::f16, bf16 x bf16 -> fp32),
+ * TRANSPOSED: D^T[outputs x agents] = W^T[outputs x K] * X^T[K x agents].  Weights are the A operand (M = 128 output
+ * rows <-> the 128 TMEM lanes), agents are the N dimension (TMEM columns).  Why: the epilogue is MUFU-bound (5 tanh
+ * per LSTM unit per agent per step), MUFU cost is per warp instruction, and a thread can only read its own TMEM
+ * lane -- with agents on lanes, 20480 agents = 640 row-warps cannot be spread evenly over 592 SM sub-partitions, and
+ * partly filled warps cost as much as full ones.  With outputs on lanes every warp is full and the agents per CTA
+ * are free: 144 per CTA, one CTA per SM.
  *
- * CTA = 128 agents = one UMMA M=128 tile, two CTAs per SM (256 TMEM columns and ~107 KB of shared memory each), so
- * one CTA's MMAs overlap the other's epilogue.  Roles: warps 0-3 = epilogue (thread r owns agent row r = TMEM lane r),
- * warp 4 lane 0 = MMA issuer, warp 5 lane 0 = weight producer (cp.async.bulk of pre-formatted 8 KB slabs, 5-slot
- * ring).  Every GEMM is D[128 x N] = A[128 x K] * W[K x N] with D in TMEM columns 0..N-1:
- *   LSTM step : K = 80 = [h(64) | x_t(7) | 1 | 1 | 0..], N = 256 = gates i,j,f,o x 64; the two "1" columns carry the
- *               bias as a bf16 hi + lo pair; the 40 KB of LSTM weights stay in the ring for all <= 10 steps;
- *   layer1    : K = 80 = [h(64) | host(4) | 1 | 1 | 0..], N = 256;
- *   layer2/fc1: K = 256, N = 256, fp32 bias added in the epilogue;   logits_p: K = 256, N = 16 (11 used).
- * Operands sit in shared memory in the canonical K-major SWIZZLE_NONE layout: 8-row x 16-byte core matrices,
- * element (r, k) of a tile with R rows at (k/8)*R*16 + r*16 + (k%8)*2, i.e. LBO (next K chunk) = R*16 bytes,
- * SBO (next 8-row group) = 128 bytes.  The epilogue writes the next GEMM's A operand (h_t, ReLU activations) straight
- * into that layout as bf16: row r's 16-byte pieces are contiguous across a warp, so the stores are conflict-free.
- * Gate non-linearities use tanh.approx (sigmoid(x) = 0.5 tanh(x/2) + 0.5): one MUFU op each; the epilogue is
- * MUFU-bound (320 per agent per LSTM step), not tensor-bound.
+ * LSTM step: lane l <-> (unit u = l % 64, agent group l / 64); group 0 = agents 0..71 of the CTA, group 1 = 72..143.
+ * Four accumulators (gates i, j, f, o; N = 80 columns each) so that a thread finds all four gates of its unit in
+ * its own lane.  The group split rides on K: gate g's A tile is [W_g ; 0] for K-slabs 0..4 (which multiply agents
+ * 0..79) and [0 ; W_g] for K-slabs 5..9 (agents 72..151), both cut out of one shared-memory image laid out
+ * [0 | W_i | 0 | W_j | 0 | W_f | 0 | W_o | 0] (64-row blocks) by moving the descriptor start.  K = 80 per group =
+ * [h(64) | x_t(7) | 1 | 1 | 0..]; the two "1" columns carry the bias as a bf16 hi + lo pair.
+ * layer1 / layer2 / fullyconnected1: two M = 128 blocks x N = 144; logits_p: one block (11 of 128 rows used).
+ * Operands sit in shared memory in the canonical K-major SWIZZLE_NONE layout (8-row x 16-byte core matrices): element
+ * (r, k) at (k/8)*LBO + r*16 + (k%8)*2, SBO = 128.  The activation tile X[agent][k] uses LBO = 153*16 bytes: the odd
+ * pitch makes the epilogue's 2-byte column stores (32 lanes = 32 consecutive k of one agent) conflict-free.
+ * Roles: warps 0-7 epilogue (warp w reads TMEM lanes 32*(w%4).., warps 4-7 take the other half of the columns),
+ * warp 8 lane 0 = MMA issuer, warp 9 lane 0 = weight producer (cp.async.bulk: the 90 KB LSTM image once, then 8 KB
+ * slabs of the dense layers through a ring that grows into the LSTM image's space when the recurrence is done).
+ * Gate non-linearities use tanh.approx (sigmoid(x) = 0.5 tanh(x/2) + 0.5).
  * ---------------------------------------------------------------------------------------------------------- */
-#define T_THREADS 192
-#define T_KL 80
-#define T_SLAB 8192
-#define T_RING 5
-#define T_ACH 2048                 /* bytes of one 8-wide K chunk of the A tile (128 rows x 16 B) */
-#define T_A_BYTES (32 * T_ACH)     /* K = 256 */
-#define T_NSLAB 43                 /* 5 (lstm) + 5 (layer1) + 16 (layer2) + 16 (fc1) + 1 (logits_p, 32 chunks x 256 B) */
-#define T_IMG_BYTES (T_NSLAB * T_SLAB)
-#define T_NBIAS (G_FC + G_FC + 16) /* fp32 biases of layer2, fc1, logits_p appended to the image */
-#define T_DYN_SMEM (T_A_BYTES + T_RING * T_SLAB)
+#define U_G 72                     /* agents per lane group */
+#define U_XCH (153 * 16)           /* bytes per 8-wide K chunk of the activation tile (153 rows: 144 + overhang + odd) */
+#define U_X_BYTES (32 * U_XCH)     /* K = 256 */
+#define U_LBLK 1024                /* one 64-row block of a K chunk */
+#define U_LCH (9 * U_LBLK)         /* bytes per K chunk of the LSTM block image */
+#define U_L_BYTES (10 * U_LCH)     /* K = 80 */
+#define U_SLAB 8192                /* K16 x 256 rows */
+#define U_RING0 6                  /* ring slots available during the recurrence */
+#define U_RING 17                  /* + 11 slots inside the LSTM image's space afterwards */
+#define U_NSLAB 38                 /* 5 (layer1) + 16 (layer2) + 16 (fc1) + 1 (logits_p: 32 chunks x 256 B) */
+#define U_IMG_BYTES (U_L_BYTES + U_NSLAB * U_SLAB)
+#define U_NBIAS (G_FC + G_FC + 16) /* fp32 biases of layer2, fc1, logits_p appended to the image */
+#define U_DYN_SMEM (U_X_BYTES + U_L_BYTES + U_RING0 * U_SLAB)
+#define U_EPI 256
+#define U_THREADS 320
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -505,6 +525,7 @@ __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); } /* epilogue warps only */
 
 /* shared-memory matrix descriptor, SWIZZLE_NONE, K-major (cute::UMMA::SmemDescriptor bit layout): start >> 4 in
  * [0,14), LBO >> 4 in [16,30), SBO >> 4 in [32,46), version 1 in [46,48), layout type 0 in [61,64) */
@@ -525,7 +546,15 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint6
       ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
 }
-/* thread t of warp w reads TMEM lane 32*(w%4) + t, 8 / 16 consecutive fp32 columns */
+/* thread t of warp w reads TMEM lane 32*(w%4) + t, 4 / 8 consecutive fp32 columns */
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float v[4]) {
+  uint32_t r[4];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(taddr));
+#pragma unroll
+  for (int k = 0; k < 4; k++) v[k] = __uint_as_float(r[k]);
+}
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float v[8]) {
   uint32_t r[8];
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -534,277 +563,301 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float v[8]) {
 #pragma unroll
   for (int k = 0; k < 8; k++) v[k] = __uint_as_float(r[k]);
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float v[16]) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
-      "[%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-#pragma unroll
-  for (int k = 0; k < 16; k++) v[k] = __uint_as_float(r[k]);
-}
 __device__ __forceinline__ float tanh_fast(float x) {
   float y;
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 __device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+__device__ __forceinline__ void sts16(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts_bf16(uint32_t addr, float v) {
+  const __nv_bfloat16 b = __float2bfloat16_rn(v);
+  asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(*reinterpret_cast<const unsigned short*>(&b)) : "memory");
+}
 
-__global__ void __launch_bounds__(T_THREADS, 2) k_ga3c_tc(const Ga3cArgs p) {
+__global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  __shared__ __align__(16) float s_bias[T_NBIAS];
-  __shared__ __align__(8) uint64_t s_bar[2 * T_RING + 2];
+  __shared__ __align__(8) uint64_t s_bar[2 * U_RING + 4];
   __shared__ uint32_t s_tmem;
-  __shared__ int s_len[T_M];
+  __shared__ int s_len[U_NA + 16];
   __shared__ int s_maxlen;
 
   const size_t N = (size_t)p.E * p.A;
-  const size_t g0 = (size_t)blockIdx.x * T_M;
+  const size_t g0 = (size_t)blockIdx.x * U_NA;
+  const size_t npad = (size_t)gridDim.x * U_NA; /* agents per xb slot plane */
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t sA = smem_u32(smem), sW = sA + T_A_BYTES;
-  const uint32_t bar_full = smem_u32(&s_bar[0]), bar_empty = smem_u32(&s_bar[T_RING]);
-  const uint32_t bar_a = smem_u32(&s_bar[2 * T_RING]), bar_d = smem_u32(&s_bar[2 * T_RING + 1]);
+  const uint32_t sX = smem_u32(smem), sL = sX + U_X_BYTES, sR = sL + U_L_BYTES;
+  const uint32_t bar_full = smem_u32(&s_bar[0]), bar_empty = smem_u32(&s_bar[U_RING]);
+  const uint32_t bar_a = smem_u32(&s_bar[2 * U_RING]), bar_d = bar_a + 8, bar_l = bar_a + 16, bar_ldone = bar_a + 24;
+  auto slot_addr = [&](int slot) { return slot < U_RING0 ? sR + slot * U_SLAB : sL + (slot - U_RING0) * U_SLAB; };
 
   if (tid == 0) {
-    for (int k = 0; k < T_RING; k++) {
+    for (int k = 0; k < U_RING; k++) {
       mbar_init(bar_full + 8 * k, 1);
       mbar_init(bar_empty + 8 * k, 1);
     }
-    mbar_init(bar_a, T_M);
+    mbar_init(bar_a, U_EPI);
     mbar_init(bar_d, 1);
+    mbar_init(bar_l, 1);
+    mbar_init(bar_ldone, 1);
     s_maxlen = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) { /* TMEM: 256 fp32 columns x 128 lanes; this warp also frees them */
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(256u)
+  if (warp == 8) { /* TMEM: all 512 fp32 columns x 128 lanes (one CTA per SM); this warp also frees them */
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512u)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if (tid < T_M) {
-    const size_t g = g0 + tid;
-    s_len[tid] = g < N ? min((int)p.x[g * G_XS], G_SLOTS) : -1; /* x[0] = sequence length, -1 = no GA3C agent here */
+  /* header chunk of every agent: {host0,host1 | host2,host3 | 1,1 | sequence length}; -1 = no GA3C agent here */
+  uint4 hdr = make_uint4(0u, 0u, 0u, 0xffffffffu);
+  if (tid < U_NA) {
+    hdr = p.xb[(size_t)(U_XB_SLOTS - 1) * npad + g0 + tid];
+    s_len[tid] = min((int)hdr.w, G_SLOTS);
+  } else if (tid < U_NA + 16) {
+    s_len[tid] = -1;
   }
-  for (int k = tid; k < T_NBIAS; k += T_THREADS) s_bias[k] = __ldg(reinterpret_cast<const float*>(p.wimg + T_IMG_BYTES) + k);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (tid < T_M && s_len[tid] > 0) atomicMax(&s_maxlen, s_len[tid]);
+  if (tid < U_NA && s_len[tid] > 0) atomicMax(&s_maxlen, s_len[tid]);
   __syncthreads();
   const int maxlen = s_maxlen;
   const uint32_t tmem = s_tmem;
 
-  if (warp == 5) {
-    /* ===== weight producer: slab q of the image -> ring slot q % 5 ===== */
+  if (warp == 9) {
+    /* ===== weight producer ===== */
     if (lane == 0) {
-      for (int q = 0; q < T_NSLAB; q++) {
-        const int slot = q % T_RING, use = q / T_RING;
-        if (use > 0) mbar_wait(bar_empty + 8 * slot, (use - 1) & 1);
-        mbar_expect_tx(bar_full + 8 * slot, T_SLAB);
-        bulk_g2s(sW + slot * T_SLAB, p.wimg + (size_t)q * T_SLAB, T_SLAB, bar_full + 8 * slot);
+      mbar_expect_tx(bar_l, U_L_BYTES);
+      for (int k = 0; k < 10; k++) bulk_g2s(sL + k * U_LCH, p.wimg + (size_t)k * U_LCH, U_LCH, bar_l);
+      const uint8_t* slabs = p.wimg + U_L_BYTES;
+      for (int q = 0; q < U_NSLAB; q++) {
+        const int slot = q % U_RING;
+        if (q == U_RING0) mbar_wait(bar_ldone, 0); /* the recurrence is over: its weights' space joins the ring */
+        if (q >= U_RING) mbar_wait(bar_empty + 8 * slot, ((q / U_RING) - 1) & 1);
+        mbar_expect_tx(bar_full + 8 * slot, U_SLAB);
+        bulk_g2s(slot_addr(slot), slabs + (size_t)q * U_SLAB, U_SLAB, bar_full + 8 * slot);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     /* ===== MMA issuer ===== */
     if (lane == 0) {
-      const uint32_t id256 = umma_idesc(T_M, 256), id16 = umma_idesc(T_M, 16);
+      const uint32_t id80 = umma_idesc(128, 80), id144 = umma_idesc(128, U_NA);
       uint32_t a_phase = 0;
-      for (int s = 0; s < T_RING; s++) mbar_wait(bar_full + 8 * s, 0); /* LSTM weights resident */
+      mbar_wait(bar_l, 0);
       for (int t = 0; t < maxlen; t++) {
         mbar_wait(bar_a, a_phase);
         a_phase ^= 1;
         tc_fence_after();
+#pragma unroll 1
+        for (int g = 0; g < 4; g++)
 #pragma unroll
-        for (int s = 0; s < T_KL / 16; s++)
-          umma_bf16(tmem, umma_desc(sA + s * 2 * T_ACH, T_ACH, 128), umma_desc(sW + s * T_SLAB, 4096, 128), id256, s > 0);
-        if (t == maxlen - 1)
-          for (int s = 0; s < T_RING; s++) tc_commit(bar_empty + 8 * s);
+          for (int s = 0; s < 10; s++) {
+            const int grp = s / 5, sc = s % 5;
+            umma_bf16(tmem + g * 80, umma_desc(sL + (2 * sc) * U_LCH + (2 * g + 1 - grp) * U_LBLK, U_LCH, 128),
+                      umma_desc(sX + (2 * sc) * U_XCH + grp * U_G * 16, U_XCH, 128), id80, s > 0);
+          }
+        if (t == maxlen - 1) tc_commit(bar_ldone);
         tc_commit(bar_d);
       }
-      if (maxlen == 0)
-        for (int s = 0; s < T_RING; s++) mbar_arrive(bar_empty + 8 * s);
-      int q = T_RING;
+      if (maxlen == 0) mbar_arrive(bar_ldone);
+      int q = 0;
       for (int layer = 0; layer < 3; layer++) { /* layer1 (5 slabs), layer2 (16), fullyconnected1 (16) */
-        const int nslab = layer == 0 ? T_KL / 16 : G_FC / 16;
+        const int nslab = layer == 0 ? 5 : G_FC / 16;
         mbar_wait(bar_a, a_phase);
         a_phase ^= 1;
         for (int s = 0; s < nslab; s++, q++) {
-          const int slot = q % T_RING;
-          mbar_wait(bar_full + 8 * slot, (q / T_RING) & 1);
+          const int slot = q % U_RING;
+          mbar_wait(bar_full + 8 * slot, (q / U_RING) & 1);
           tc_fence_after();
-          umma_bf16(tmem, umma_desc(sA + s * 2 * T_ACH, T_ACH, 128), umma_desc(sW + slot * T_SLAB, 4096, 128), id256, s > 0);
+          const uint64_t bd = umma_desc(sX + (2 * s) * U_XCH, U_XCH, 128);
+          umma_bf16(tmem, umma_desc(slot_addr(slot), 4096, 128), bd, id144, s > 0);
+          umma_bf16(tmem + U_NA, umma_desc(slot_addr(slot) + 2048, 4096, 128), bd, id144, s > 0);
           tc_commit(bar_empty + 8 * slot);
         }
         tc_commit(bar_d);
       }
-      { /* logits_p: one 8 KB slab = 32 K-chunks of 16 rows x 16 B */
-        const int slot = q % T_RING;
+      { /* logits_p: one 8 KB slab = 32 K-chunks of 16 rows x 16 B; rows 16..127 of the A tile read whatever follows */
+        const int slot = q % U_RING;
         mbar_wait(bar_a, a_phase);
         a_phase ^= 1;
-        mbar_wait(bar_full + 8 * slot, (q / T_RING) & 1);
+        mbar_wait(bar_full + 8 * slot, (q / U_RING) & 1);
         tc_fence_after();
         for (int s = 0; s < G_FC / 16; s++)
-          umma_bf16(tmem, umma_desc(sA + s * 2 * T_ACH, T_ACH, 128), umma_desc(sW + slot * T_SLAB + s * 512, 256, 128), id16,
+          umma_bf16(tmem, umma_desc(slot_addr(slot) + s * 512, 256, 128), umma_desc(sX + (2 * s) * U_XCH, U_XCH, 128), id144,
                     s > 0);
         tc_commit(bar_d);
       }
     }
   } else {
-    /* ===== epilogue: thread r <-> agent row r <-> TMEM lane r ===== */
-    const int r = tid;
-    const size_t g = g0 + r;
-    const int len = s_len[r];
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
-    const uint32_t arow = sA + r * 16;
-    const uint4* xb = p.xb + (size_t)blockIdx.x * (G_SLOTS * T_M) + r;
-    const uint32_t one_bf = 0x3f80u; /* bf16 1.0 in the low half */
-    auto sts16 = [](uint32_t addr, uint4 v) {
-      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-    };
-    /* layer1's K chunks 8, 9: [host0..3 normalised, 1, 1, 0, 0], zeros (network.py:83-84, 89-90) */
-    auto write_host_chunks = [&]() {
-      float hv[4] = {0.f, 0.f, 0.f, 0.f};
-      if (g < N && len >= 0) {
-#pragma unroll
-        for (int k = 0; k < G_HOST; k++) hv[k] = (p.x[g * G_XS + 1 + k] - c_host_avg[k]) / c_host_std[k];
+    /* ===== epilogue: TMEM lane l <-> output row; warps 4-7 take the second half of the columns ===== */
+    const int l = (warp & 3) * 32 + lane, hw = warp >> 2;
+    const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    /* X: h = 0 (chunks 0..7), chunk 8 = first LSTM input (or layer1's host chunk), chunk 9 = [1, 0..] / zeros;
+     * rows 144..152 are only read as overhang of the second agent group and stay zero */
+    for (int k = tid; k < 10 * 153; k += U_EPI) sts16(sX + (k / 153) * U_XCH + (k % 153) * 16, make_uint4(0u, 0u, 0u, 0u));
+    epi_bar();
+    const uint32_t xrow = sX + tid * 16; /* tid < U_NA: my agent's row */
+    const uint4 host_chunk = make_uint4(hdr.x, hdr.y, hdr.z, 0u);
+    if (tid < U_NA) {
+      if (maxlen > 0) {
+        sts16(xrow + 8 * U_XCH, p.xb[g0 + tid]);
+        sts16(xrow + 9 * U_XCH, make_uint4(0x3f80u, 0u, 0u, 0u));
+      } else {
+        sts16(xrow + 8 * U_XCH, host_chunk);
       }
-      sts16(arow + 8 * T_ACH, make_uint4(pack_bf16(hv[0], hv[1]), pack_bf16(hv[2], hv[3]), 0x3f803f80u, 0u));
-      sts16(arow + 9 * T_ACH, make_uint4(0u, 0u, 0u, 0u));
-    };
-    /* A for LSTM step 0: h = 0 | x_0, 1 | 1, 0.. */
-#pragma unroll
-    for (int c8 = 0; c8 < 8; c8++) sts16(arow + c8 * T_ACH, make_uint4(0u, 0u, 0u, 0u));
-    if (maxlen > 0) {
-      sts16(arow + 8 * T_ACH, xb[0]);
-      sts16(arow + 9 * T_ACH, make_uint4(one_bf, 0u, 0u, 0u));
-    } else {
-      write_host_chunks();
     }
     fence_async_smem();
     mbar_arrive(bar_a);
 
     uint32_t d_phase = 0;
-    float cst[G_H];
+    {
+      /* recurrence: unit u of agent group grp; my 36 columns c0..c0+35 of the group's 72 */
+      const int u = l & 63, grp = l >> 6, c0 = hw * (U_G / 2);
+      const uint32_t hdst = sX + (u >> 3) * U_XCH + (u & 7) * 2 + (grp * U_G + c0) * 16;
+      const int* lenp = s_len + grp * U_G + c0;
+      float cst[U_G / 2];
 #pragma unroll
-    for (int u = 0; u < G_H; u++) cst[u] = 0.f;
-    for (int t = 0; t < maxlen; t++) {
-      uint4 nx = make_uint4(0u, 0u, 0u, 0u);
-      if (t + 1 < maxlen) nx = xb[(t + 1) * T_M];
-      mbar_wait(bar_d, d_phase);
-      d_phase ^= 1;
-      tc_fence_after();
-      const bool active = t < len; /* dynamic_rnn(sequence_length): state copied through beyond the last valid step */
+      for (int c = 0; c < U_G / 2; c++) cst[c] = 0.f;
+      for (int t = 0; t < maxlen; t++) {
+        uint4 nx = make_uint4(0u, 0u, 0u, 0u);
+        if (tid < U_NA && t + 1 < maxlen) nx = p.xb[(size_t)(t + 1) * npad + g0 + tid];
+        mbar_wait(bar_d, d_phase);
+        d_phase ^= 1;
+        tc_fence_after();
 #pragma unroll
-      for (int uc = 0; uc < G_H / 8; uc++) {
-        float gi[8], gj[8], gf[8], go[8];
-        tmem_ld8(trow + uc * 8, gi);
-        tmem_ld8(trow + 64 + uc * 8, gj);
-        tmem_ld8(trow + 128 + uc * 8, gf);
-        tmem_ld8(trow + 192 + uc * 8, go);
-        tc_wait_ld();
-        float hn[8];
+        for (int cc = 0; cc < U_G / 2; cc += 4) {
+          float gi[4], gj[4], gf[4], go[4];
+          tmem_ld4(trow + c0 + cc, gi);
+          tmem_ld4(trow + 80 + c0 + cc, gj);
+          tmem_ld4(trow + 160 + c0 + cc, gf);
+          tmem_ld4(trow + 240 + c0 + cc, go);
+          tc_wait_ld();
 #pragma unroll
-        for (int u = 0; u < 8; u++) { /* TF1 LSTMCell: gates i, j, f, o; forget_bias 1.0 */
-          const float cn = fmaf(sigmoid_fast(gf[u] + 1.0f), cst[uc * 8 + u], sigmoid_fast(gi[u]) * tanh_fast(gj[u]));
-          hn[u] = sigmoid_fast(go[u]) * tanh_fast(cn);
-          if (active) cst[uc * 8 + u] = cn;
-        }
-        if (active)
-          sts16(arow + uc * T_ACH, make_uint4(pack_bf16(hn[0], hn[1]), pack_bf16(hn[2], hn[3]), pack_bf16(hn[4], hn[5]),
-                                              pack_bf16(hn[6], hn[7])));
-      }
-      if (t + 1 < maxlen)
-        sts16(arow + 8 * T_ACH, nx);
-      else
-        write_host_chunks();
-      fence_async_smem();
-      tc_fence_before();
-      mbar_arrive(bar_a);
-    }
-    /* layer1, layer2, fullyconnected1: ReLU(D + bias) -> bf16 -> A of the next GEMM (in place: the MMAs that read
-     * A have completed when bar_d fires) */
-    for (int layer = 0; layer < 3; layer++) {
-      mbar_wait(bar_d, d_phase);
-      d_phase ^= 1;
-      tc_fence_after();
-      const float* bias = s_bias + (layer > 0 ? (layer - 1) * G_FC : 0); /* layer1's bias rides in the GEMM */
-#pragma unroll 2
-      for (int cc = 0; cc < G_FC / 16; cc++) {
-        float v[16];
-        tmem_ld16(trow + cc * 16, v);
-        tc_wait_ld();
-        if (layer > 0) {
-#pragma unroll
-          for (int k = 0; k < 16; k++) v[k] += bias[cc * 16 + k];
-        }
-#pragma unroll
-        for (int k = 0; k < 16; k++) v[k] = fmaxf(v[k], 0.f);
-        sts16(arow + (2 * cc) * T_ACH,
-              make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7])));
-        sts16(arow + (2 * cc + 1) * T_ACH, make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]),
-                                                      pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15])));
-      }
-      fence_async_smem();
-      tc_fence_before();
-      mbar_arrive(bar_a);
-    }
-    /* logits_p -> softmax (+1e-4 floor) -> argmax -> action (network.py:45-51, GA3CCADRLPolicy.py:38-42) */
-    mbar_wait(bar_d, d_phase);
-    tc_fence_after();
-    float lg[16];
-    tmem_ld16(trow, lg);
-    tc_wait_ld();
-    tc_fence_before();
-    if (g < N && len >= 0) {
-      const int flags = __float_as_int(p.state[5 * N + g].z);
-      if (flags & CASIM_F_IS_DONE) { /* collision_avoidance_env.py:298-300 */
-        p.policy_actions[2 * g] = 0.f;
-        p.policy_actions[2 * g + 1] = 0.f;
-        if (p.action_idx) p.action_idx[g] = -1;
-      } else {
-        const float* pb = s_bias + 2 * G_FC;
-        float mx = -INFINITY;
-#pragma unroll
-        for (int k = 0; k < G_ACT; k++) {
-          lg[k] += pb[k];
-          mx = fmaxf(mx, lg[k]);
-        }
-        float pr[G_ACT], sum = 0.f;
-#pragma unroll
-        for (int k = 0; k < G_ACT; k++) {
-          pr[k] = expf(lg[k] - mx);
-          sum += pr[k];
-        }
-        int best = 0;
-        float pbest = -1.f;
-#pragma unroll
-        for (int k = 0; k < G_ACT; k++) {
-          pr[k] = (pr[k] / sum + 1e-4f) / (1.0f + 1e-4f * G_ACT);
-          if (pr[k] > pbest) {
-            pbest = pr[k];
-            best = k;
+          for (int k = 0; k < 4; k++) { /* TF1 LSTMCell: gates i, j, f, o; forget_bias 1.0 */
+            const float cn = fmaf(sigmoid_fast(gf[k] + 1.0f), cst[cc + k], sigmoid_fast(gi[k]) * tanh_fast(gj[k]));
+            const float hn = sigmoid_fast(go[k]) * tanh_fast(cn);
+            if (t < lenp[cc + k]) { /* dynamic_rnn(sequence_length): state copied through beyond the last valid step */
+              cst[cc + k] = cn;
+              sts_bf16(hdst + (cc + k) * 16, hn);
+            }
           }
         }
-        if (p.probs) {
-#pragma unroll
-          for (int k = 0; k < G_ACT; k++) p.probs[g * G_ACT + k] = pr[k];
+        if (tid < U_NA) {
+          if (t + 1 < maxlen) {
+            sts16(xrow + 8 * U_XCH, nx);
+          } else { /* layer1's K chunks 8, 9: [host0..3 normalised, 1, 1, 0, 0], zeros (network.py:83-84, 89-90) */
+            sts16(xrow + 8 * U_XCH, host_chunk);
+            sts16(xrow + 9 * U_XCH, make_uint4(0u, 0u, 0u, 0u));
+          }
         }
-        if (p.action_idx) p.action_idx[g] = best;
-        const float pref = p.state[2 * N + g].w;
-        p.policy_actions[2 * g] = (float)((double)pref * (double)c_actions[best][0]);
-        p.policy_actions[2 * g + 1] = c_actions[best][1];
+        fence_async_smem();
+        tc_fence_before();
+        mbar_arrive(bar_a);
       }
-    } else if (g < N && p.action_idx) {
-      p.action_idx[g] = -1;
+    }
+    /* layer1, layer2, fullyconnected1: ReLU(D + bias) -> bf16 -> X (in place: the MMAs that read X have completed
+     * when bar_d fires); output row o = mb*128 + l is K index o of the next GEMM */
+    const float* biasg = reinterpret_cast<const float*>(p.wimg + U_IMG_BYTES);
+    for (int layer = 0; layer < 3; layer++) {
+      float b0 = 0.f, b1 = 0.f; /* layer1's bias rides in the GEMM */
+      if (layer > 0) {
+        b0 = __ldg(biasg + (layer - 1) * G_FC + l);
+        b1 = __ldg(biasg + (layer - 1) * G_FC + 128 + l);
+      }
+      mbar_wait(bar_d, d_phase);
+      d_phase ^= 1;
+      tc_fence_after();
+#pragma unroll
+      for (int mb = 0; mb < 2; mb++) {
+        const float b = mb ? b1 : b0;
+        const int o = mb * 128 + l;
+        const uint32_t dst = sX + (o >> 3) * U_XCH + (o & 7) * 2 + hw * U_G * 16;
+#pragma unroll 3
+        for (int cc = 0; cc < U_G; cc += 8) {
+          float v[8];
+          tmem_ld8(trow + mb * U_NA + hw * U_G + cc, v);
+          tc_wait_ld();
+#pragma unroll
+          for (int k = 0; k < 8; k++) sts_bf16(dst + (cc + k) * 16, fmaxf(v[k] + b, 0.f));
+        }
+      }
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar_a);
+    }
+    /* logits_p: lanes 0..10 hold the 11 logits of every agent (column); transpose through shared memory (X is dead) */
+    mbar_wait(bar_d, d_phase);
+    tc_fence_after();
+    float* s_logit = reinterpret_cast<float*>(smem); /* [U_NA][12] */
+    {
+      const float pb = l < G_ACT ? __ldg(biasg + 2 * G_FC + l) : 0.f;
+#pragma unroll 3
+      for (int cc = 0; cc < U_G; cc += 8) {
+        float v[8];
+        tmem_ld8(trow + hw * U_G + cc, v);
+        tc_wait_ld();
+        if (l < G_ACT) {
+#pragma unroll
+          for (int k = 0; k < 8; k++) s_logit[(hw * U_G + cc + k) * 12 + l] = v[k] + pb;
+        }
+      }
+    }
+    tc_fence_before();
+    epi_bar();
+    const size_t g = g0 + tid;
+    if (tid < U_NA && g < N) {
+      if (s_len[tid] < 0) {
+        if (p.action_idx) p.action_idx[g] = -1;
+      } else {
+        /* softmax (+1e-4 floor) -> argmax -> action (network.py:45-51, GA3CCADRLPolicy.py:38-42) */
+        const int flags = __float_as_int(p.state[5 * N + g].z);
+        if (flags & CASIM_F_IS_DONE) { /* collision_avoidance_env.py:298-300 */
+          p.policy_actions[2 * g] = 0.f;
+          p.policy_actions[2 * g + 1] = 0.f;
+          if (p.action_idx) p.action_idx[g] = -1;
+        } else {
+          float lg[G_ACT], mx = -INFINITY;
+#pragma unroll
+          for (int k = 0; k < G_ACT; k++) {
+            lg[k] = s_logit[tid * 12 + k];
+            mx = fmaxf(mx, lg[k]);
+          }
+          float pr[G_ACT], sum = 0.f;
+#pragma unroll
+          for (int k = 0; k < G_ACT; k++) {
+            pr[k] = expf(lg[k] - mx);
+            sum += pr[k];
+          }
+          int best = 0;
+          float pbest = -1.f;
+#pragma unroll
+          for (int k = 0; k < G_ACT; k++) {
+            pr[k] = (pr[k] / sum + 1e-4f) / (1.0f + 1e-4f * G_ACT);
+            if (pr[k] > pbest) {
+              pbest = pr[k];
+              best = k;
+            }
+          }
+          if (p.probs) {
+#pragma unroll
+            for (int k = 0; k < G_ACT; k++) p.probs[g * G_ACT + k] = pr[k];
+          }
+          if (p.action_idx) p.action_idx[g] = best;
+          const float pref = p.state[2 * N + g].w;
+          p.policy_actions[2 * g] = (float)((double)pref * (double)c_actions[best][0]);
+          p.policy_actions[2 * g + 1] = c_actions[best][1];
+        }
+      }
     }
   }
   __syncwarp();
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256u) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
   }
 }
 
@@ -841,37 +894,41 @@ cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_
   for (int k = 0; k < 3; k++, r++) { table[r][0] = 0.0f; table[r][1] = (float)(-PI / 6 + k * (PI / 6)); }
   e = cudaMemcpyToSymbolAsync(c_actions, table, sizeof(table), 0, cudaMemcpyHostToDevice, s);
   if (e != cudaSuccess) return e;
-  /* tensor-core path: bf16 image of every layer in the shared-memory order k_ga3c_tc feeds to tcgen05.mma
-   * (K-major, SWIZZLE_NONE: element (n, k) of a layer with R output rows at (k/8)*R*16 + n*16 + (k%8)*2) */
-  std::vector<uint8_t> img(T_IMG_BYTES + T_NBIAS * sizeof(float), 0);
-  auto put = [&](size_t layer_off, int rows, int k, int n, float v) {
+  /* tensor-core path: bf16 image of every layer in the shared-memory order k_ga3c_tc feeds to tcgen05.mma as the
+   * A operand (K-major, SWIZZLE_NONE: element (row, k) of a layer at (k/8)*LBO + row*16 + (k%8)*2) */
+  std::vector<uint8_t> img(U_IMG_BYTES + U_NBIAS * sizeof(float), 0);
+  auto put = [&](size_t layer_off, size_t lbo, int k, int row, float v) {
     uint16_t b = f32_to_bf16(v);
-    memcpy(&img[layer_off + (size_t)(k / 8) * rows * 16 + (size_t)n * 16 + (k % 8) * 2], &b, 2);
+    memcpy(&img[layer_off + (size_t)(k / 8) * lbo + (size_t)row * 16 + (k % 8) * 2], &b, 2);
   };
-  auto put_bias = [&](size_t layer_off, int k, int n, float v) { /* bf16 hi + lo pair against two "1" columns */
+  auto put_bias = [&](size_t layer_off, size_t lbo, int k, int row, float v) { /* bf16 hi + lo pair against two "1" columns */
     uint16_t hi = f32_to_bf16(v);
-    put(layer_off, G_FC, k, n, v);
-    put(layer_off, G_FC, k + 1, n, v - bf16_to_f32(hi));
+    put(layer_off, lbo, k, row, v);
+    put(layer_off, lbo, k + 1, row, v - bf16_to_f32(hi));
   };
   const float* w = weights_host;
-  for (int n = 0; n < 4 * G_H; n++) { /* LSTM: A columns [h(64) | x(7) | 1 | 1]; TF kernel rows are [x(7); h(64)] */
-    for (int k = 0; k < G_H; k++) put(0, G_FC, k, n, w[W_LSTM_K + (G_OTHER + k) * 4 * G_H + n]);
-    for (int k = 0; k < G_OTHER; k++) put(0, G_FC, G_H + k, n, w[W_LSTM_K + k * 4 * G_H + n]);
-    put_bias(0, G_H + G_OTHER, n, w[W_LSTM_B + n]);
-  }
-  const size_t o1 = 5 * T_SLAB, o2 = 10 * T_SLAB, o3 = 26 * T_SLAB, o4 = 42 * T_SLAB;
-  for (int n = 0; n < G_FC; n++) { /* layer1: A columns [h(64) | host(4) | 1 | 1]; TF kernel rows are [host(4); h(64)] */
-    for (int k = 0; k < G_H; k++) put(o1, G_FC, k, n, w[W_L1_K + (G_HOST + k) * G_FC + n]);
-    for (int k = 0; k < G_HOST; k++) put(o1, G_FC, G_H + k, n, w[W_L1_K + k * G_FC + n]);
-    put_bias(o1, G_H + G_HOST, n, w[W_L1_B + n]);
+  /* LSTM: per K chunk nine 64-row blocks [0 | W_i | 0 | W_j | 0 | W_f | 0 | W_o | 0]; K order [h(64) | x(7) | 1 | 1];
+   * TF kernel rows are [x(7); h(64)], columns gate*64 + unit */
+  for (int g = 0; g < 4; g++)
+    for (int u = 0; u < G_H; u++) {
+      const int n = g * G_H + u, row = (2 * g + 1) * 64 + u;
+      for (int k = 0; k < G_H; k++) put(0, U_LCH, k, row, w[W_LSTM_K + (G_OTHER + k) * 4 * G_H + n]);
+      for (int k = 0; k < G_OTHER; k++) put(0, U_LCH, G_H + k, row, w[W_LSTM_K + k * 4 * G_H + n]);
+      put_bias(0, U_LCH, G_H + G_OTHER, row, w[W_LSTM_B + n]);
+    }
+  const size_t o1 = U_L_BYTES, o2 = o1 + 5 * U_SLAB, o3 = o2 + 16 * U_SLAB, o4 = o3 + 16 * U_SLAB;
+  for (int n = 0; n < G_FC; n++) { /* layer1: K order [h(64) | host(4) | 1 | 1]; TF kernel rows are [host(4); h(64)] */
+    for (int k = 0; k < G_H; k++) put(o1, 4096, k, n, w[W_L1_K + (G_HOST + k) * G_FC + n]);
+    for (int k = 0; k < G_HOST; k++) put(o1, 4096, G_H + k, n, w[W_L1_K + k * G_FC + n]);
+    put_bias(o1, 4096, G_H + G_HOST, n, w[W_L1_B + n]);
     for (int k = 0; k < G_FC; k++) {
-      put(o2, G_FC, k, n, w[W_L2_K + k * G_FC + n]);
-      put(o3, G_FC, k, n, w[W_FC_K + k * G_FC + n]);
+      put(o2, 4096, k, n, w[W_L2_K + k * G_FC + n]);
+      put(o3, 4096, k, n, w[W_FC_K + k * G_FC + n]);
     }
   }
   for (int n = 0; n < G_ACT; n++)
-    for (int k = 0; k < G_FC; k++) put(o4, 16, k, n, w[W_P_K + k * G_ACT + n]);
-  float* bias = reinterpret_cast<float*>(&img[T_IMG_BYTES]);
+    for (int k = 0; k < G_FC; k++) put(o4, 256, k, n, w[W_P_K + k * G_ACT + n]);
+  float* bias = reinterpret_cast<float*>(&img[U_IMG_BYTES]);
   memcpy(bias, w + W_L2_B, G_FC * sizeof(float));
   memcpy(bias + G_FC, w + W_FC_B, G_FC * sizeof(float));
   memcpy(bias + 2 * G_FC, w + W_P_B, G_ACT * sizeof(float));
@@ -880,11 +937,11 @@ cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_
     if (e != cudaSuccess) return e;
   }
   if (!h->ga3c_xb) { /* allocated here, not in the launcher: the forward must be capturable into a CUDA graph */
-    const size_t ntiles = ((size_t)h->E * h->A + T_M - 1) / T_M;
-    const size_t bytes = ntiles * G_SLOTS * T_M * sizeof(uint4);
+    const size_t ntiles = ((size_t)h->E * h->A + U_NA - 1) / U_NA;
+    const size_t bytes = ntiles * U_XB_SLOTS * U_NA * sizeof(uint4);
     e = cudaMalloc(&h->ga3c_xb, bytes);
     if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(h->ga3c_xb, 0, bytes, s); /* rows past N in the last tile stay zero */
+    e = cudaMemsetAsync(h->ga3c_xb, 0, bytes, s); /* agents past N in the last tile stay zero (sequence length 0) */
     if (e != cudaSuccess) return e;
   }
   if (!h->ga3c_x) {
@@ -893,7 +950,7 @@ cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_
   }
   e = cudaFuncSetAttribute(k_ga3c_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)G_FC * G_TILE * sizeof(float)));
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_ga3c_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_DYN_SMEM);
+  e = cudaFuncSetAttribute(k_ga3c_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)U_DYN_SMEM);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_ga3c_tc, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   if (e != cudaSuccess) return e;
@@ -909,7 +966,7 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
     cudaError_t e = cudaMalloc((void**)&h->ga3c_x, N * G_XS * sizeof(float));
     if (e != cudaSuccess) return e;
   }
-  const unsigned ntiles = (unsigned)((N + T_M - 1) / T_M);
+  const unsigned ntiles = (unsigned)((N + U_NA - 1) / U_NA);
   Ga3cArgs a;
   a.c = h->dc;
   a.state = reinterpret_cast<const float4*>(state);
@@ -929,7 +986,7 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   if (use_tc)
-    k_ga3c_tc<<<ntiles, T_THREADS, T_DYN_SMEM, s>>>(a);
+    k_ga3c_tc<<<ntiles, U_THREADS, U_DYN_SMEM, s>>>(a);
   else
     k_ga3c_fwd<<<(unsigned)((N + G_TILE - 1) / G_TILE), G_THREADS, (size_t)G_FC * G_TILE * sizeof(float), s>>>(a);
   return cudaGetLastError();
