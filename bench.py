@@ -90,7 +90,7 @@ def roofline_obj(wl, kern, dominant, step_s, step_bytes, explore_counts):
     duration) plus the per-kernel breakdown and the whole-step figure."""
     peak, peak_src = peaks()
     t, units, how = kern[dominant]
-    tensor = dominant.startswith("k_ga3c")
+    tensor = dominant in ("k_ga3c_tc", "k_ga3c_fwd")
     if tensor:
         tpeak, tsrc = tensor_peak()
         ach = units / t / 1e12
@@ -524,9 +524,14 @@ def main():
         kern["k_explore"] = (t, xbytes, "timed alone")
         t_sens += t
     if wl == "c5":
-        t = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc))
-        kern["k_ga3c_state+fwd"] = (t, GA3C_FLOP_PER_AGENT * NA, "timed alone (state-vector kernel + forward kernel)")
-        t_sens += t
+        t_both = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc))
+        t_fwd = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc, forward_only=True))
+        fwd_name = "k_ga3c_tc" if use_tc else "k_ga3c_fwd"
+        kern[fwd_name] = (t_fwd, GA3C_FLOP_PER_AGENT * NA, "timed alone (forward kernel on the previous state vectors)")
+        # state-vector kernel: reads 4 state planes of the agent + 3 of each other agent (L1/L2-resident within the
+        # env), writes the 76-float row + 11 bf16 chunks: counted as 64 + 304 + 176 B per agent
+        kern["k_ga3c_state"] = (max(t_both - t_fwd, 1e-9), (64 + 304 + 176) * NA, "state+forward timed alone minus the forward alone")
+        t_sens += t_both
     core_units = (BYTES_CORE + (BYTES_OAS if "other_agents_states" in W["sensors"] else 0)
                   + (BYTES_WALL if "laserscan" in W["sensors"] or "local_grid" in W["sensors"] else 0)) * NA
     kern["k_core"] = (max(step_s - t_sens, 1e-9), core_units, "timed alone" if not kern else "step time minus the kernels timed alone")

@@ -18,6 +18,8 @@
  */
 #include <cuda_bf16.h>
 
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -56,6 +58,7 @@ struct Ga3cArgs {
   float* x;                /* [N][G_XS] scratch: the 75-float network input, fp32 */
   uint4* xb;               /* [tiles][10 slots][128 rows] 16 B: 7 normalised bf16 inputs + bf16 1.0, or NULL */
   const uint8_t* wimg;     /* bf16 weight image in UMMA smem order (tensor-core path) */
+  unsigned long long* trace; /* tuning aid (CASIM_GA3C_TRACE): [CTA][2 roles][64] globaltimer stamps, else NULL */
   float* policy_actions;   /* [N][2] */
   int32_t* action_idx;     /* [N] or NULL */
   float* probs;            /* [N][11] or NULL */
@@ -481,9 +484,31 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
 #define U_NSLAB 38                 /* 5 (layer1) + 16 (layer2) + 16 (fc1) + 1 (logits_p: 32 chunks x 256 B) */
 #define U_IMG_BYTES (U_L_BYTES + U_NSLAB * U_SLAB)
 #define U_NBIAS (G_FC + G_FC + 16) /* fp32 biases of layer2, fc1, logits_p appended to the image */
+#define U_NREP 4                   /* replicas of the image in global memory */
+#define U_IMG_STRIDE ((U_IMG_BYTES + U_NBIAS * 4 + 255) / 256 * 256)
 #define U_DYN_SMEM (U_X_BYTES + U_L_BYTES + U_RING0 * U_SLAB)
 #define U_EPI 256
 #define U_THREADS 320
+
+/* slab q of the stream (5 + 16 + 16 + 1) -> slab of the image this CTA loads at that point: each layer's K slabs
+ * rotated by the CTA index */
+__device__ __forceinline__ int rot_slab(int q, unsigned cta) {
+  if (q < 5) return (int)((q + cta) % 5);
+  if (q < 21) return 5 + (int)((q - 5 + cta) % 16);
+  if (q < 37) return 21 + (int)((q - 21 + cta) % 16);
+  return q;
+}
+
+__device__ __forceinline__ unsigned long long gtime_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE(role, idx)                                                                          \
+  do {                                                                                            \
+    const int i_ = (idx);                                                                         \
+    if (p.trace && i_ < 64) p.trace[((size_t)blockIdx.x * 2 + (role)) * 64 + i_] = gtime_ns();    \
+  } while (0)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -629,15 +654,22 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
   if (warp == 9) {
     /* ===== weight producer ===== */
     if (lane == 0) {
+      /* All CTAs want the same bytes at the same time: to keep them from queueing on the same L2 lines, each CTA
+       * reads its own replica (blockIdx % U_NREP) and walks every layer's K slabs from its own starting point
+       * (accumulation order over K is free); the MMA issuer uses the same rotation. */
+      const uint8_t* img = p.wimg + (size_t)(blockIdx.x % U_NREP) * U_IMG_STRIDE;
       mbar_expect_tx(bar_l, U_L_BYTES);
-      for (int k = 0; k < 10; k++) bulk_g2s(sL + k * U_LCH, p.wimg + (size_t)k * U_LCH, U_LCH, bar_l);
-      const uint8_t* slabs = p.wimg + U_L_BYTES;
+      for (int k = 0; k < 10; k++) {
+        const int kk = (k + blockIdx.x) % 10;
+        bulk_g2s(sL + kk * U_LCH, img + (size_t)kk * U_LCH, U_LCH, bar_l);
+      }
+      const uint8_t* slabs = img + U_L_BYTES;
       for (int q = 0; q < U_NSLAB; q++) {
         const int slot = q % U_RING;
         if (q == U_RING0) mbar_wait(bar_ldone, 0); /* the recurrence is over: its weights' space joins the ring */
         if (q >= U_RING) mbar_wait(bar_empty + 8 * slot, ((q / U_RING) - 1) & 1);
         mbar_expect_tx(bar_full + 8 * slot, U_SLAB);
-        bulk_g2s(slot_addr(slot), slabs + (size_t)q * U_SLAB, U_SLAB, bar_full + 8 * slot);
+        bulk_g2s(slot_addr(slot), slabs + (size_t)rot_slab(q, blockIdx.x) * U_SLAB, U_SLAB, bar_full + 8 * slot);
       }
     }
   } else if (warp == 8) {
@@ -645,11 +677,15 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
     if (lane == 0) {
       const uint32_t id80 = umma_idesc(128, 80), id144 = umma_idesc(128, U_NA);
       uint32_t a_phase = 0;
+      int ti = 0;
+      TRACE(1, ti++);
       mbar_wait(bar_l, 0);
+      TRACE(1, ti++);
       for (int t = 0; t < maxlen; t++) {
         mbar_wait(bar_a, a_phase);
         a_phase ^= 1;
         tc_fence_after();
+        TRACE(1, ti++);
 #pragma unroll 1
         for (int g = 0; g < 4; g++)
 #pragma unroll
@@ -667,16 +703,19 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
         const int nslab = layer == 0 ? 5 : G_FC / 16;
         mbar_wait(bar_a, a_phase);
         a_phase ^= 1;
+        TRACE(1, ti++);
         for (int s = 0; s < nslab; s++, q++) {
           const int slot = q % U_RING;
           mbar_wait(bar_full + 8 * slot, (q / U_RING) & 1);
           tc_fence_after();
-          const uint64_t bd = umma_desc(sX + (2 * s) * U_XCH, U_XCH, 128);
+          const int ks = rot_slab(q, blockIdx.x) - (q - s); /* which K slab of this layer sits in the slot */
+          const uint64_t bd = umma_desc(sX + (2 * ks) * U_XCH, U_XCH, 128);
           umma_bf16(tmem, umma_desc(slot_addr(slot), 4096, 128), bd, id144, s > 0);
           umma_bf16(tmem + U_NA, umma_desc(slot_addr(slot) + 2048, 4096, 128), bd, id144, s > 0);
           tc_commit(bar_empty + 8 * slot);
         }
         tc_commit(bar_d);
+        TRACE(1, ti++);
       }
       { /* logits_p: one 8 KB slab = 32 K-chunks of 16 rows x 16 B; rows 16..127 of the A tile read whatever follows */
         const int slot = q % U_RING;
@@ -712,6 +751,8 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
     mbar_arrive(bar_a);
 
     uint32_t d_phase = 0;
+    int ti = 0;
+    if (tid == 0) TRACE(0, ti++);
     {
       /* recurrence: unit u of agent group grp; my 36 columns c0..c0+35 of the group's 72 */
       const int u = l & 63, grp = l >> 6, c0 = hw * (U_G / 2);
@@ -726,6 +767,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
         mbar_wait(bar_d, d_phase);
         d_phase ^= 1;
         tc_fence_after();
+        if (tid == 0) TRACE(0, ti++);
 #pragma unroll
         for (int cc = 0; cc < U_G / 2; cc += 4) {
           float gi[4], gj[4], gf[4], go[4];
@@ -755,6 +797,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
         fence_async_smem();
         tc_fence_before();
         mbar_arrive(bar_a);
+        if (tid == 0) TRACE(0, ti++);
       }
     }
     /* layer1, layer2, fullyconnected1: ReLU(D + bias) -> bf16 -> X (in place: the MMAs that read X have completed
@@ -769,6 +812,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
       mbar_wait(bar_d, d_phase);
       d_phase ^= 1;
       tc_fence_after();
+      if (tid == 0) TRACE(0, ti++);
 #pragma unroll
       for (int mb = 0; mb < 2; mb++) {
         const float b = mb ? b1 : b0;
@@ -786,10 +830,12 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
       fence_async_smem();
       tc_fence_before();
       mbar_arrive(bar_a);
+      if (tid == 0) TRACE(0, ti++);
     }
     /* logits_p: lanes 0..10 hold the 11 logits of every agent (column); transpose through shared memory (X is dead) */
     mbar_wait(bar_d, d_phase);
     tc_fence_after();
+    if (tid == 0) TRACE(0, ti++);
     float* s_logit = reinterpret_cast<float*>(smem); /* [U_NA][12] */
     {
       const float pb = l < G_ACT ? __ldg(biasg + 2 * G_FC + l) : 0.f;
@@ -852,6 +898,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
       }
     }
   }
+  if (tid == 0) TRACE(0, 63);
   __syncwarp();
   tc_fence_before();
   __syncthreads();
@@ -933,7 +980,11 @@ cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_
   memcpy(bias + G_FC, w + W_FC_B, G_FC * sizeof(float));
   memcpy(bias + 2 * G_FC, w + W_P_B, G_ACT * sizeof(float));
   if (!h->ga3c_wb) {
-    e = cudaMalloc(&h->ga3c_wb, img.size());
+    e = cudaMalloc(&h->ga3c_wb, (size_t)U_NREP * U_IMG_STRIDE);
+    if (e != cudaSuccess) return e;
+  }
+  for (int r = 1; r < U_NREP; r++) {
+    e = cudaMemcpyAsync((uint8_t*)h->ga3c_wb + (size_t)r * U_IMG_STRIDE, img.data(), img.size(), cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return e;
   }
   if (!h->ga3c_xb) { /* allocated here, not in the launcher: the forward must be capturable into a CUDA graph */
@@ -973,20 +1024,42 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
   a.n_agents = h->n_agents;
   a.w = h->ga3c_w;
   a.x = h->ga3c_x;
-  a.xb = use_tc ? reinterpret_cast<uint4*>(h->ga3c_xb) : nullptr;
+  a.xb = (use_tc & 1) ? reinterpret_cast<uint4*>(h->ga3c_xb) : nullptr;
   a.wimg = reinterpret_cast<const uint8_t*>(h->ga3c_wb);
+  a.trace = nullptr;
+  static const char* trace_path = getenv("CASIM_GA3C_TRACE"); /* tuning aid: dumps phase time stamps, synchronises */
+  if (use_tc && trace_path) {
+    cudaMalloc((void**)&a.trace, (size_t)ntiles * 128 * sizeof(unsigned long long));
+    cudaMemsetAsync(a.trace, 0, (size_t)ntiles * 128 * sizeof(unsigned long long), s);
+  }
   a.policy_actions = policy_actions;
   a.action_idx = action_idx;
   a.probs = probs;
   a.nn_input = nn_input;
   a.E = h->E;
   a.A = h->A;
-  h->launches += 2;
-  k_ga3c_state<<<(unsigned)((N + GS_AG - 1) / GS_AG), GS_THREADS, 0, s>>>(a);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
+  const bool skip_state = (use_tc & 2) != 0; /* profiling aid: forward only, on the state vectors of the last call */
+  use_tc &= 1;
+  h->launches += skip_state ? 1 : 2;
+  if (!skip_state) {
+    k_ga3c_state<<<(unsigned)((N + GS_AG - 1) / GS_AG), GS_THREADS, 0, s>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
   if (use_tc)
     k_ga3c_tc<<<ntiles, U_THREADS, U_DYN_SMEM, s>>>(a);
+  if (use_tc && a.trace) {
+    std::vector<unsigned long long> t((size_t)ntiles * 128);
+    cudaStreamSynchronize(s);
+    cudaMemcpy(t.data(), a.trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    cudaFree(a.trace);
+    if (FILE* f = fopen(trace_path, "wb")) {
+      fwrite(t.data(), sizeof(unsigned long long), t.size(), f);
+      fclose(f);
+    }
+    return cudaGetLastError();
+  }
+  if (use_tc) return cudaGetLastError();
   else
     k_ga3c_fwd<<<(unsigned)((N + G_TILE - 1) / G_TILE), G_THREADS, (size_t)G_FC * G_TILE * sizeof(float), s>>>(a);
   return cudaGetLastError();

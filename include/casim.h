@@ -232,7 +232,9 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
  * GA3C_CADRL/network.py:45-98).  weights: fp32 parameter blob, order kernel/bias of lstm [71,256],[256];
  * layer1 [68,256],[256]; layer2 [256,256],[256]; fullyconnected1 [256,256],[256]; logits_p [256,11],[11]
  * (row-major [in,out] like TF).  Writes policy_actions [E,A,2]; optionally action_idx [E,A] (int32, -1 for
- * non-GA3C agents), probs [E,A,11] and nn_input [E,A,75]. */
+ * non-GA3C agents), probs [E,A,11] and nn_input [E,A,75].
+ * use_tensor_cores: bit 0 = bf16 tcgen05 forward (else the fp32 SIMT forward); bit 1 = profiling aid, skip the
+ * state-vector kernel and run the forward on the state vectors of the previous call. */
 int casim_ga3c_set_weights(casim_handle* h, const float* weights_host, int n_params, void* stream);
 int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_actions, int32_t* action_idx,
                        float* probs, float* nn_input, int use_tensor_cores, void* stream);
