@@ -451,6 +451,7 @@ def main():
     act_dev = torch.zeros((E, A, 2), dtype=torch.float32, device=dev)
     h2d = act_host.numel() * 4
     d2h = sum(t.numel() * t.element_size() for t in host.values())
+    host = BatchedSim.HostView(host)
     with torch.cuda.stream(stream):
         for i in range(3):
             sims[i % R].step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev, policy_actions=policy_step(sims[i % R]))

@@ -194,11 +194,13 @@ int casim_create(const casim_config* cfg, int E, int A, casim_handle** out) {
   size_t N = (size_t)E * A;
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->pose64, N * 4 * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->prev_game_over, (size_t)E);
-  if (e == cudaSuccess) e = cudaMalloc((void**)&h->partials, (size_t)h->max_ctas * CASIM_NUM_STATS * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->state0, N * 24 * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemset(h->state0, 0, N * 24 * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->partials, (size_t)(h->max_ctas > 32 ? h->max_ctas : 32) * CASIM_NUM_STATS * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->ticket, sizeof(unsigned int));
   if (e == cudaSuccess) e = cudaMemset(h->prev_game_over, 0, (size_t)E);
   if (e == cudaSuccess) e = cudaMemset(h->ticket, 0, sizeof(unsigned int));
-  if (e == cudaSuccess) e = cudaMemset(h->partials, 0, (size_t)h->max_ctas * CASIM_NUM_STATS * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemset(h->partials, 0, (size_t)(h->max_ctas > 32 ? h->max_ctas : 32) * CASIM_NUM_STATS * sizeof(double));
   if (e == cudaSuccess) e = cudaMemset(h->pose64, 0, N * 4 * sizeof(double));
   if (e != cudaSuccess) {
     casim_set_error("casim_create: %s", cudaGetErrorString(e));
@@ -213,6 +215,7 @@ int casim_destroy(casim_handle* h) {
   if (!h) return 0;
   cudaFree(h->pose64);
   cudaFree(h->prev_game_over);
+  cudaFree(h->state0);
   cudaFree(h->partials);
   cudaFree(h->ticket);
   cudaFree(h->map_planes);
@@ -335,6 +338,7 @@ int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, voi
 int casim_step(casim_handle* h, float* state, const float* ext_actions, const float* policy_actions, double dt,
                const casim_obs* obs, void* stream) {
   REQUIRE(h && state, "null argument");
+  REQUIRE((((uintptr_t)ext_actions) & 7) == 0, "ext_actions must be 8-byte aligned");
   int rc = check_obs(h, obs);
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
@@ -358,34 +362,76 @@ int casim_run_sensor(casim_handle* h, const float* state, const casim_obs* obs, 
   return 0;
 }
 
+/* Device-visible alias of a pinned (page-locked, mapped) host buffer, or NULL when `p` is pageable / not mapped. */
+static void* mapped_alias(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
+}
+
 int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
                     const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
                     void* stream) {
   REQUIRE(h && state && dev && host, "null argument");
   cudaStream_t s = (cudaStream_t)stream;
   size_t N = (size_t)h->E * h->A;
+  static int zc_on = -1;
+  if (zc_on < 0) {
+    const char* ev = getenv("CASIM_ZEROCOPY");
+    zc_on = ev ? atoi(ev) : 1;
+  }
+  /* Actions.  Pinned + mapped and small: the step kernel reads them from host memory itself (every lane, one
+   * coalesced 8-byte read) and refreshes ext_actions_dev on the way -- the copy-engine hop in front of a ~10 us
+   * kernel costs more than the kernel.  Otherwise: cudaMemcpyAsync H2D. */
+  const float* ext_src = nullptr;
   if (ext_actions_host) {
     REQUIRE(ext_actions_dev, "ext_actions_dev required with ext_actions_host");
-    CK(cudaMemcpyAsync(ext_actions_dev, ext_actions_host, N * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
+    void* al = (zc_on && N * 2 * sizeof(float) <= CASIM_ZEROCOPY_MAX) ? mapped_alias(ext_actions_host) : nullptr;
+    if (al) {
+      ext_src = (const float*)al;
+      h->ext_copy_dst = ext_actions_dev;
+    } else {
+      CK(cudaMemcpyAsync(ext_actions_dev, ext_actions_host, N * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
+      ext_src = ext_actions_dev;
+    }
   }
-  int rc = casim_step(h, state, ext_actions_host ? ext_actions_dev : nullptr, policy_actions, dt, dev, s);
-  if (rc) return rc;
-#define D2H(field, bytes)                                                                        \
+  /* Result delivery.  A result whose host buffer is pinned + mapped and at most CASIM_ZEROCOPY_MAX bytes is
+   * written by the kernels STRAIGHT into host memory over PCIe (posted, coalesced stores; the field's device
+   * buffer is not touched by this call): no copy-engine hop and no extra stream operation per field, which is
+   * what bounds a small step (C2: four D2H copies cost more than the step kernel).  Larger results (sensor
+   * planes) and pageable buffers go through cudaMemcpyAsync after the kernels.  CASIM_ZEROCOPY=0 disables. */
+  casim_obs run = *dev;
+  struct Pending { void* dst; const void* src; size_t bytes; } pend[10];
+  int np = 0;
+#define OUT(field, nbytes, zc_ok)                                                                \
   if (host->field) {                                                                             \
-    REQUIRE(dev->field, "host buffer given without its device buffer: " #field);                 \
-    CK(cudaMemcpyAsync(host->field, dev->field, (bytes), cudaMemcpyDeviceToHost, s));            \
+    void* al = ((zc_ok) && zc_on && (size_t)(nbytes) <= CASIM_ZEROCOPY_MAX) ? mapped_alias(host->field) : nullptr; \
+    if (al)                                                                                      \
+      run.field = reinterpret_cast<decltype(run.field)>(al);                                     \
+    else {                                                                                       \
+      REQUIRE(dev->field, "host buffer given without its device buffer: " #field);               \
+      pend[np].dst = host->field; pend[np].src = dev->field; pend[np].bytes = (nbytes); np++;    \
+    }                                                                                            \
   }
-  D2H(rewards, N * sizeof(float))
-  D2H(done, N)
-  D2H(game_over, (size_t)h->E)
-  D2H(collision_flags, N)
-  D2H(nearest_dist, N * sizeof(float))
-  D2H(stats, CASIM_NUM_STATS * sizeof(float))
-  D2H(obs_misc, N * 4 * sizeof(float))
-  D2H(other_agents_states, N * (size_t)h->dc.rows * 10 * sizeof(float))
-  D2H(laserscan, N * (size_t)h->dc.nb * sizeof(float))
-  D2H(local_grid, N * (size_t)h->dc.submap_w * h->dc.submap_h)
-#undef D2H
+  OUT(rewards, N * sizeof(float), 1)
+  OUT(done, N, 1)
+  OUT(game_over, (size_t)h->E, 1)
+  OUT(collision_flags, N, 1)
+  OUT(nearest_dist, N * sizeof(float), 1)
+  OUT(stats, CASIM_NUM_STATS * sizeof(float), 1)
+  OUT(obs_misc, N * 4 * sizeof(float), 1)
+  /* sensor planes are inputs of casim_explore_step / casim_ga3c_forward / the next observe: device copy stays current */
+  OUT(other_agents_states, N * (size_t)h->dc.rows * 10 * sizeof(float), 0)
+  OUT(laserscan, N * (size_t)h->dc.nb * sizeof(float), 0)
+  OUT(local_grid, N * (size_t)h->dc.submap_w * h->dc.submap_h, 0)
+#undef OUT
+  int rc = casim_step(h, state, ext_src, policy_actions, dt, &run, s);
+  h->ext_copy_dst = nullptr;
+  if (rc) return rc;
+  for (int i = 0; i < np; i++) CK(cudaMemcpyAsync(pend[i].dst, pend[i].src, pend[i].bytes, cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   return 0;
 }
@@ -415,6 +461,19 @@ int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_action
                        (cudaStream_t)stream));
   return 0;
 }
+
+}  /* extern "C" */
+
+int casim_pdl_enabled(void) {
+  static int on = -1;
+  if (on < 0) {
+    const char* ev = getenv("CASIM_PDL");
+    on = ev ? (atoi(ev) != 0) : 1;
+  }
+  return on;
+}
+
+extern "C" {
 
 unsigned long long casim_launch_count(const casim_handle* h) { return h ? h->launches : 0ull; }
 

@@ -71,6 +71,8 @@ struct casim_handle {
   /* scratch */
   double* pose64;          /* [E*A][4] post-move px, py, heading, radius in fp64 for the sensor kernels */
   uint8_t* prev_game_over; /* [E] */
+  float* state0;           /* [6][E*A] float4: the episode-start state written by casim_reset; auto_reset re-loads it
+                              instead of re-running Agent.__init__ (fp64 atan2/sqrt/div) inside the step kernel */
   double* partials;        /* [max_ctas][8] */
   unsigned int* ticket;    /* last-block counter */
   int max_ctas;
@@ -79,6 +81,7 @@ struct casim_handle {
   void* ga3c_wb;           /* bf16 tiles for the tensor-core path */
   float* ga3c_x;           /* [E*A][76] network input scratch */
   void* ga3c_xb;           /* [tiles][10][128] x 16 B: bf16 LSTM input chunks for the tensor-core path */
+  float* ext_copy_dst;     /* set by casim_step_host around its casim_step call (see CoreArgs::ext_copy_dst) */
   unsigned long long launches;
 };
 
@@ -101,5 +104,36 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
 cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_params, cudaStream_t s);
 
 void casim_set_error(const char* fmt, ...);
+
+/* Programmatic dependent launch (PDL): the per-step kernels run back to back on one stream and each is short
+ * (a single wave at the named batch sizes), so the launch latency between dependent kernels is a large share of a
+ * step.  Launched with the programmatic-stream-serialization attribute, the next kernel is scheduled while the
+ * previous one drains; every such kernel executes casim_pdl_enter() before its first global-memory access
+ * (griddepcontrol.wait: all memory of the preceding kernel is visible afterwards), so the data dependence is kept.
+ * Works under stream capture (programmatic edges in the CUDA graph).  CASIM_PDL=0 turns it off. */
+int casim_pdl_enabled(void);
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void casim_pdl_enter() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+template <typename Arg>
+static inline cudaError_t casim_launch_pdl(void (*kern)(const Arg), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                           const Arg& arg) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = casim_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, arg);
+}
+#endif
 
 #endif

@@ -44,7 +44,8 @@ namespace {
 struct CoreArgs {
   DevCfg c;
   float4* state;               /* [6][E*A] float4 */
-  const float* ext_actions;    /* [E*A][2] or NULL */
+  const float* ext_actions;    /* [E*A][2] or NULL (device memory, or mapped host memory in the host-buffer step) */
+  float2* ext_copy_dst;        /* [E*A] or NULL: device copy of ext_actions kept current when they are read from host */
   const float* policy_actions; /* [E*A][2] or NULL */
   const float* traj;           /* [E*A][T][4] or NULL */
   const float* init;           /* [E*A][7] */
@@ -53,12 +54,13 @@ struct CoreArgs {
   const uint32_t* map_planes;  /* [n_maps][4][300][10] or NULL */
   const int32_t* edf_d2;       /* [n_maps][300][300] exact squared distance (cells^2) to the nearest occupied cell */
   uint8_t* prev_game_over;     /* [E] */
+  float4* state0;              /* [6][E*A] float4 episode-start state (written by RESET, re-loaded by auto_reset) */
   double* pose64;              /* [E*A][4] or NULL */
   double* partials;            /* [ctas][8] */
   unsigned int* ticket;
   casim_obs o;
   double dt;
-  int E, A, T, n_maps, epw, write_pose;
+  int E, A, T, n_maps, epw, write_pose, diag;
 };
 
 struct Agent {
@@ -155,7 +157,7 @@ __device__ __forceinline__ void agent_init(const DevCfg& c, const float* in, int
 }
 
 /* collision_avoidance_env.py:298-320: the action each policy contributes, rounded to fp32 (:289) */
-__device__ __forceinline__ void choose_action(const DevCfg& c, const Agent& a, const float* ext, const float* pol,
+__device__ __forceinline__ void choose_action(const DevCfg& c, const Agent& a, bool ext, float2 ea, const float* pol,
                                               size_t g, float& a0, float& a1) {
   a0 = 0.f;
   a1 = 0.f;
@@ -167,21 +169,21 @@ __device__ __forceinline__ void choose_action(const DevCfg& c, const Agent& a, c
       break;
     case CASIM_POLICY_EXTERNAL:
       if (ext) {
-        a0 = ext[2 * g];
-        a1 = ext[2 * g + 1];
+        a0 = ea.x;
+        a1 = ea.y;
       }
       break;
     case CASIM_POLICY_LEARNING: /* LearningPolicy.py:11-16 */
       if (ext) {
-        double heading = c.max_heading_change * (2. * (double)ext[2 * g + 1] - 1.);
-        double speed = (double)a.pref * (double)ext[2 * g];
+        double heading = c.max_heading_change * (2. * (double)ea.y - 1.);
+        double speed = (double)a.pref * (double)ea.x;
         a0 = (float)speed;
         a1 = (float)heading;
       }
       break;
     case CASIM_POLICY_CARRL: /* CARRLPolicy.py:7-15 */
       if (ext) {
-        int k = (int)ext[2 * g];
+        int k = (int)ea.x;
         if (k < 0) k += 11;
         k = min(max(k, 0), 10);
         const double mh = CASIM_PI / 6;
@@ -291,12 +293,15 @@ __device__ __forceinline__ void take_action(const DevCfg& c, Agent& a, float a0,
   a.flags = flags;
 }
 
-#define CASIM_CORE_THREADS 64
-#define CASIM_CORE_WARPS (CASIM_CORE_THREADS / 32)
+#define CASIM_CORE_MAX_WARPS 8
+#define CASIM_STAT_BIAS (1ll << 31)
+#define CASIM_CORE_THREADS (32 * CASIM_CORE_MAX_WARPS) /* launch bound; the launcher picks 1..8 warps per CTA */
+#define CASIM_CORE_WARPS 4                             /* default warps per CTA (CASIM_WPC overrides) */
 
 template <int MODE, int AP>
 __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   extern __shared__ __align__(16) float s_stage[];
+  casim_pdl_enter();
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
   const int warps_per_cta = blockDim.x >> 5;
@@ -312,6 +317,15 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   const size_t plane = (size_t)p.E * A;
   const size_t g = (size_t)env0 * A + lane;
 
+  /* caller-supplied actions: one coalesced 8-byte read per lane.  In the host-buffer step the source is mapped host
+   * memory (the read crosses PCIe while the state loads are in flight) and the device copy is refreshed here. */
+  float2 ea = make_float2(0.f, 0.f);
+  const bool have_ext = MODE == CASIM_MODE_STEP && p.ext_actions != nullptr;
+  if (have_ext && slot) {
+    ea = reinterpret_cast<const float2*>(p.ext_actions)[g];
+    if (p.ext_copy_dst) p.ext_copy_dst[g] = ea;
+  }
+
   Agent a;
   int old_flags = 0;
   bool wrote_all = false;
@@ -320,11 +334,11 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
       agent_init(c, p.init + g * 7, p.type0[g], a);
       wrote_all = true;
     } else {
-      load_agent(p.state, plane, g, a);
-      if (MODE == CASIM_MODE_STEP && c.auto_reset && p.init && p.prev_game_over[e]) {
-        agent_init(c, p.init + g * 7, p.type0[g], a);
-        wrote_all = true;
-      }
+      /* auto_reset (the env's reset() folded into the next step): the episode-start state is the one casim_reset
+       * stored, i.e. exactly what reset() followed by step() would read */
+      const bool fresh = MODE == CASIM_MODE_STEP && c.auto_reset && p.init && p.prev_game_over[e];
+      load_agent(fresh ? p.state0 : p.state, plane, g, a);
+      wrote_all = fresh;
     }
   } else {
     a.px = a.py = a.heading = a.turning = a.t = a.trem = a.cs = a.sn = 0;
@@ -337,7 +351,7 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   if (MODE == CASIM_MODE_STEP && valid) {
     old_flags = a.flags;
     float a0, a1;
-    choose_action(c, a, p.ext_actions, p.policy_actions, g, a0, a1);
+    choose_action(c, a, have_ext, ea, p.policy_actions, g, a0, a1);
     take_action(c, a, a0, a1, p.dt, p.traj, p.T, g);
   }
 
@@ -495,11 +509,14 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     if (slot && ai == 0) p.prev_game_over[e] = 0;
   }
 
-  /* ---- per-step statistics: warp totals -> 64-bit integer accumulators (counts are integers, the reward sum is
-   * 2^-32 fixed point, so the result does not depend on the order of arrival) -> the last warp to arrive converts
-   * them to the float vector and clears them for the next launch.  Done BEFORE the state / observation stores so that
-   * the fence in front of the ticket does not wait for them. ---- */
-  if (MODE == CASIM_MODE_STEP && p.o.stats) {
+  /* ---- per-step statistics: warp totals -> CTA totals (shared memory) -> ONE returning 64-bit atomic add per
+   * statistic and CTA on a single accumulator word that carries the arrival count in its top 16 bits and the
+   * (biased, integer) running total in the low 48: whichever CTA's add brings the count to gridDim.x holds the
+   * complete total of that statistic in (returned value + its own contribution), writes the float and clears the
+   * word for the next launch.  One L2 round trip on the critical path, no fence, no ticket, no second pass; integer
+   * sums, so the result does not depend on the order of arrival (the reward sum is 2^-20 fixed point per CTA). ---- */
+  __shared__ long long s_stats[CASIM_CORE_MAX_WARPS][CASIM_NUM_STATS];
+  if (MODE == CASIM_MODE_STEP && p.o.stats != nullptr) {
     long long v[CASIM_NUM_STATS];
     v[0] = __reduce_add_sync(FULL_MASK, st_new_coll);
     v[1] = __reduce_add_sync(FULL_MASK, st_new_goal);
@@ -509,25 +526,23 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     v[5] = __reduce_add_sync(FULL_MASK, st_active);
     v[6] = __reduce_add_sync(FULL_MASK, st_agents);
     v[7] = 0;
-    /* 32 stripes of accumulators (one 64-byte line each) keep same-address contention low */
-    unsigned long long* acc = reinterpret_cast<unsigned long long*>(p.partials);
-    unsigned last = 0;
     if (lane == 0) {
-      unsigned long long* mine = acc + (size_t)(w & 31) * CASIM_NUM_STATS;
 #pragma unroll
-      for (int k = 0; k < CASIM_NUM_STATS - 1; k++)
-        if (v[k] != 0) atomicAdd(mine + k, (unsigned long long)v[k]);
-      __threadfence();
-      const unsigned total = gridDim.x * warps_per_cta;
-      last = atomicInc(p.ticket, total - 1) == total - 1;
+      for (int k = 0; k < CASIM_NUM_STATS; k++) s_stats[warp_in_cta][k] = v[k];
     }
-    if (__shfl_sync(FULL_MASK, last, 0)) { /* lane = stripe */
-      __threadfence();
-#pragma unroll
-      for (int k = 0; k < CASIM_NUM_STATS; k++) {
-        long long t = k == CASIM_NUM_STATS - 1 ? 0ll : (long long)atomicExch(acc + (size_t)lane * CASIM_NUM_STATS + k, 0ull);
-        t = warp_sum(t);
-        if (lane == 0) p.o.stats[k] = k == 4 ? (float)((double)t * (1.0 / 4294967296.0)) : (float)t;
+    __syncthreads();
+    if (warp_in_cta == 0 && lane < CASIM_NUM_STATS && p.diag < 2) { /* lane k owns statistic k */
+      long long t = 0;
+      for (int q = 0; q < warps_per_cta; q++) t += s_stats[q][lane];
+      if (lane == 4) t = (t + (1ll << 11)) >> 12; /* 2^-32 -> 2^-20 fixed point, rounded once per CTA */
+      /* |t| < 2^31 for any CTA (<= 256 agents, |reward| <= 1): the bias keeps the 48-bit field non-negative */
+      const unsigned long long mine = (1ull << 48) + (unsigned long long)(t + CASIM_STAT_BIAS);
+      unsigned long long* acc = reinterpret_cast<unsigned long long*>(p.partials) + lane * 8; /* 64 B apart */
+      const unsigned long long tot = atomicAdd(acc, mine) + mine;
+      if ((unsigned)(tot >> 48) == gridDim.x) {
+        *acc = 0ull;
+        const long long sum = (long long)(tot & ((1ull << 48) - 1)) - (long long)gridDim.x * CASIM_STAT_BIAS;
+        p.o.stats[lane] = lane == 4 ? (float)((double)sum * (1.0 / 1048576.0)) : (float)sum;
       }
     }
   }
@@ -536,7 +551,10 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   if (MODE == CASIM_MODE_STEP) {
     if (valid) store_agent(p.state, plane, g, a, wrote_all);
   } else if (MODE == CASIM_MODE_RESET) {
-    if (slot) store_agent(p.state, plane, g, a, true);
+    if (slot) {
+      store_agent(p.state, plane, g, a, true);
+      store_agent(p.state0, plane, g, a, true);
+    }
   }
   if (p.write_pose && slot) { /* fp64 pose for the sensor kernels: px, py, cos(heading), sin(heading) */
     if (!a.have_cs) sincos(a.heading, &a.sn, &a.cs);
@@ -669,7 +687,8 @@ cudaError_t launch_mode(const CoreArgs& a, int ap, dim3 grid, dim3 block, size_t
   case AP: {                                                                                           \
     if (smem > 48 * 1024)                                                                              \
       cudaFuncSetAttribute(k_core<MODE, AP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
-    k_core<MODE, AP><<<grid, block, smem, s>>>(a);                                                     \
+    cudaError_t le = casim_launch_pdl<CoreArgs>(k_core<MODE, AP>, grid, block, smem, s, a);            \
+    if (le != cudaSuccess) return le;                                                                  \
     break;                                                                                             \
   }
   switch (ap) {
@@ -698,6 +717,7 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
   a.c = h->dc;
   a.state = reinterpret_cast<float4*>(state);
   a.ext_actions = ext_actions;
+  a.ext_copy_dst = reinterpret_cast<float2*>(h->ext_copy_dst);
   a.policy_actions = policy_actions;
   a.traj = h->traj;
   a.T = h->T;
@@ -708,6 +728,7 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
   a.edf_d2 = h->edf_d2;
   a.n_maps = h->n_maps;
   a.prev_game_over = h->prev_game_over;
+  a.state0 = reinterpret_cast<float4*>(h->state0);
   a.pose64 = h->pose64;
   a.partials = h->partials;
   a.ticket = h->ticket;
@@ -725,6 +746,12 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
       epw_env = ev ? atoi(ev) : 0;
     }
     if (epw_env > 0 && epw_env < a.epw) a.epw = epw_env;
+    static int diag_env = -1;
+    if (diag_env < 0) {
+      const char* ev = getenv("CASIM_STATS_DIAG");
+      diag_env = ev ? atoi(ev) : 0;
+    }
+    a.diag = diag_env;
   }
   a.write_pose = (obs->laserscan != nullptr || obs->local_grid != nullptr) ? 1 : 0;
   static const int aps[] = {2, 4, 6, 8, 10, 12, 16, 20, 24, 32};
@@ -736,9 +763,17 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
     }
   int warps = (h->E + a.epw - 1) / a.epw;
   size_t per_warp = obs->other_agents_states ? (size_t)32 * h->dc.rows * 10 * sizeof(float) : 0;
-  int wpc = CASIM_CORE_WARPS;
+  static int wpc_env = -1;
+  if (wpc_env < 0) {
+    const char* ev = getenv("CASIM_WPC");
+    wpc_env = ev ? atoi(ev) : 0;
+  }
+  int wpc = (wpc_env >= 1 && wpc_env <= CASIM_CORE_MAX_WARPS) ? wpc_env : CASIM_CORE_WARPS;
   while (wpc > 1 && per_warp * wpc > 96 * 1024) wpc >>= 1;
+  /* the statistics word counts CTA arrivals in 16 bits: widen the CTAs rather than exceed it */
+  while (wpc < CASIM_CORE_MAX_WARPS && (warps + wpc - 1) / wpc > 65535 && per_warp * wpc * 2 <= 96 * 1024) wpc <<= 1;
   dim3 block(32 * wpc), grid((warps + wpc - 1) / wpc);
+  if (obs->stats && grid.x > 65535) return cudaErrorInvalidConfiguration;
   if ((int)grid.x > h->max_ctas) return cudaErrorInvalidConfiguration;
   size_t smem = per_warp * wpc;
   h->launches++;

@@ -186,10 +186,19 @@ class BatchedSim:
         _lib.check(self.lib.casim_run_sensor(self.handle, _lib.ptr(self.state), ctypes.byref(self._obs), int(which),
                                              _stream_ptr()), "casim_run_sensor")
 
+    class HostView:
+        """Pre-built casim_obs over a fixed set of host tensors (keeps them alive); avoids rebuilding the struct on
+        every ``step_host`` call."""
+
+        def __init__(self, bufs):
+            self.bufs = dict(bufs)
+            self.struct = BatchedSim._obs_struct(self.bufs)
+
     def step_host(self, host_bufs, ext_actions_host=None, ext_actions_dev=None, policy_actions=None, dt=None):
-        """Host-buffer step: H2D of the actions, the step, D2H of every buffer present in ``host_bufs``
-        (dict name -> pinned host tensor); returns when the results are in host memory."""
-        ho = self._obs_struct(host_bufs)
+        """Host-buffer step: H2D of the actions, the step, delivery of every buffer present in ``host_bufs``
+        (dict name -> host tensor, or a ``BatchedSim.HostView`` of such a dict); returns when the results are in
+        host memory.  Pinned scalar buffers are written by the kernel directly (see casim_step_host in casim.h)."""
+        ho = host_bufs.struct if isinstance(host_bufs, BatchedSim.HostView) else self._obs_struct(host_bufs)
         _lib.check(self.lib.casim_step_host(self.handle, _lib.ptr(self.state), _lib.ptr(ext_actions_host),
                                             _lib.ptr(ext_actions_dev), _lib.ptr(policy_actions),
                                             float(dt) if dt is not None else 0.0, ctypes.byref(self._obs),

@@ -155,6 +155,8 @@ typedef struct casim_obs {
                                    n_new_timeouts, n_game_over_envs, reward_sum, n_active_agents, n_agents, 0; may be NULL */
 } casim_obs;
 
+#define CASIM_ZEROCOPY_MAX (1u << 20)
+
 typedef struct casim_handle casim_handle;
 
 const char* casim_last_error(void);
@@ -211,8 +213,13 @@ int casim_step(casim_handle* h, float* state, const float* ext_actions, const fl
 int casim_run_sensor(casim_handle* h, const float* state, const casim_obs* obs, int which, void* stream);
 
 /* Host-buffer variant: ext_actions_host (pinned, may be NULL) is copied H2D, the step runs, and rewards, done and
- * game_over (and obs_misc/sensor buffers if the host pointers are non-NULL) are copied D2H into `host`; blocks until
- * the results are in host memory.  `dev` holds the device buffers used for the step. */
+ * game_over (and obs_misc/sensor buffers if the host pointers are non-NULL) are delivered into `host`; blocks until
+ * the results are in host memory.  `dev` holds the device buffers used for the step.
+ * Delivery: per-agent scalars (rewards, done, game_over, collision_flags, nearest_dist, stats, obs_misc) whose host
+ * buffer is page-locked + mapped (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory) and no larger than
+ * CASIM_ZEROCOPY_MAX bytes are stored by the step kernel directly into host memory over PCIe -- their `dev`
+ * counterparts are then NOT updated by this call; everything else (sensor planes, pageable buffers) is copied with
+ * cudaMemcpyAsync from `dev`.  Environment CASIM_ZEROCOPY=0 forces the copy path for every field. */
 int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
                     const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
                     void* stream);

@@ -90,3 +90,56 @@ def test_env_runs_exploration_and_ga3c_policies(oracle_lib):
     assert (belief[:, 1:] == 1.0).all()                                   # only the ig_greedy agent owns a belief
     assert obs[3][0]["other_agents_states"].shape == (9, 10)
     env.close()
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_step_host_delivery_matches_device_step(pinned):
+    """casim_step_host: results delivered into host memory (zero-copy stores for pinned scalar buffers, staged
+    copies for pageable ones and for sensor planes) equal, bit for bit, what casim_step leaves in device memory."""
+    import torch
+    from casim import lib, scenarios as S
+    from casim.sim import BatchedSim
+    from casim.config import NUM_STATS
+    E, A = 96, 10
+    cfg = lib.default_config()
+    cfg.auto_reset = 1
+    sensors = ("other_agents_states", "laserscan")
+    init, types, n, rects = S.crossing(E, A, seed=7, sensors=L.SENSOR_OTHER_AGENTS | L.SENSOR_LASERSCAN)
+    types = np.array(types).copy()
+    types[:, 1] = L.encode_type(L.POLICY_EXTERNAL, L.DYN_UNICYCLE, L.SENSOR_OTHER_AGENTS | L.SENSOR_LASERSCAN)
+    types[:, 2] = L.encode_type(L.POLICY_LEARNING, L.DYN_UNICYCLE, L.SENSOR_OTHER_AGENTS | L.SENSOR_LASERSCAN)
+    sims = []
+    for _ in range(2):
+        sim = BatchedSim(E, A, cfg=cfg, sensors=sensors, want_debug=True, want_misc=True, want_stats=True)
+        sim.set_obstacles(rects)
+        sim.reset(init, types, n)
+        sims.append(sim)
+    ref, tst = sims
+
+    def hostbuf(shape, dtype):
+        t = torch.full(shape, 77, dtype=dtype)
+        return t.pin_memory() if pinned else t
+    host = {"rewards": hostbuf((E, A), torch.float32), "done": hostbuf((E, A), torch.uint8),
+            "game_over": hostbuf((E,), torch.uint8), "stats": hostbuf((NUM_STATS,), torch.float32),
+            "collision_flags": hostbuf((E, A), torch.uint8), "nearest_dist": hostbuf((E, A), torch.float32),
+            "obs_misc": hostbuf((E, A, 4), torch.float32),
+            "other_agents_states": hostbuf(tuple(ref.buf["other_agents_states"].shape), torch.float32),
+            "laserscan": hostbuf(tuple(ref.buf["laserscan"].shape), torch.float32)}
+    gen = torch.Generator().manual_seed(3)
+    act_host = torch.zeros((E, A, 2), dtype=torch.float32)
+    act_host = act_host.pin_memory() if pinned else act_host
+    act_dev = torch.zeros((E, A, 2), dtype=torch.float32, device=ref.device)
+    for t in range(25):
+        act_host.copy_(torch.rand((E, A, 2), generator=gen))            # the caller's actions change every step
+        ref.step(ext_actions=act_host.to(ref.device))
+        torch.cuda.synchronize()
+        tst.step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
+        assert torch.equal(act_dev.cpu(), act_host), "device copy of the actions not refreshed"
+        for name, hb in host.items():
+            want = ref.buf[name].cpu().numpy()
+            got = hb.numpy()
+            assert np.array_equal(want, got, equal_nan=True), "%s differs at step %d (pinned=%s)" % (name, t, pinned)
+        assert torch.equal(ref.state, tst.state)
+    assert host["done"].any() and host["stats"][6] == E * A
+    for s in sims:
+        s.close()
