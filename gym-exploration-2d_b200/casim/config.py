@@ -43,6 +43,7 @@ class Config:
     NEAR_GOAL_THRESHOLD = 0.75
     MAX_TIME_RATIO = 3.0
     SENSING_HORIZON = np.inf
+    RVO_TIME_HORIZON = 5.0               # config.py:66
     MAX_NUM_AGENTS_IN_ENVIRONMENT = 10
     MAX_NUM_OTHER_AGENTS_IN_ENVIRONMENT = MAX_NUM_AGENTS_IN_ENVIRONMENT - 1
     MAX_NUM_OTHER_AGENTS_OBSERVED = MAX_NUM_AGENTS_IN_ENVIRONMENT - 1

@@ -462,6 +462,30 @@ int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_action
   return 0;
 }
 
+void casim_rvo_default_params(casim_rvo_params* p) {
+  if (!p) return;
+  memset(p, 0, sizeof(*p));
+  p->neighbor_dist = INFINITY;      /* Config.SENSING_HORIZON, config.py:63 */
+  p->time_horizon = 5.0;            /* Config.RVO_TIME_HORIZON, config.py:66 */
+  p->radius_scale = 1 + 15e-2;      /* RVOPolicy.py:78 */
+  p->max_delta_heading = M_PI / 6;  /* RVOPolicy.py:20 */
+  p->max_neighbors = 10;            /* Config.MAX_NUM_AGENTS_IN_ENVIRONMENT, config.py:70 */
+}
+
+int casim_rvo_step(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* params,
+                   float* policy_actions, void* stream) {
+  REQUIRE(h && state && policy_actions, "null argument");
+  REQUIRE(h->n_maps == 0, "casim_rvo_step: obstacle ORCA lines (Agent.cpp:66-284) are not implemented; the handle has a static map");
+  casim_rvo_params def;
+  if (!params) {
+    casim_rvo_default_params(&def);
+    params = &def;
+  }
+  REQUIRE(params->max_neighbors >= 0 && params->time_horizon > 0, "bad casim_rvo_params");
+  CK(casim_launch_rvo(h, state, coop, params, policy_actions, (cudaStream_t)stream));
+  return 0;
+}
+
 }  /* extern "C" */
 
 int casim_pdl_enabled(void) {

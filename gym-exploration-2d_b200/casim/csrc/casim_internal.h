@@ -101,6 +101,8 @@ cudaError_t casim_launch_explore(casim_handle* h, const float* state, const floa
                                  unsigned long long* counters, cudaStream_t s);
 cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy_actions, int32_t* action_idx,
                               float* probs, float* nn_input, int use_tc, cudaStream_t s);
+cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* prm,
+                             float* policy_actions, cudaStream_t s);
 cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_params, cudaStream_t s);
 
 void casim_set_error(const char* fmt, ...);

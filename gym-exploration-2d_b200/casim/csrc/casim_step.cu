@@ -195,6 +195,7 @@ __device__ __forceinline__ void choose_action(const DevCfg& c, const Agent& a, b
       break;
     case CASIM_POLICY_IG_GREEDY:
     case CASIM_POLICY_GA3C_CADRL:
+    case CASIM_POLICY_RVO:
       if (pol) {
         a0 = pol[2 * g];
         a1 = pol[2 * g + 1];

@@ -12,6 +12,7 @@ import numpy as np
 import torch
 
 from . import layout as L
+from . import lib as _lib
 from .config import Config, make_sim_config
 from .plugins import Agent
 from .sim import BatchedSim
@@ -175,6 +176,21 @@ class BatchedCollisionAvoidanceEnv:
         sim.set_trajectories(self._traj)
         self._has_ig = L.POLICY_IG_GREEDY in policies
         self._has_ga3c = L.POLICY_GA3C_CADRL in policies
+        self._has_rvo = L.POLICY_RVO in policies
+        self._rvo_coop = None
+        if self._has_rvo:
+            if self.obstacles is not None:
+                raise RuntimeError("RVOPolicy agents with static obstacles are not supported (obstacle ORCA lines)")
+            coop = np.ones((self.E, self.A), np.float32)
+            if self.agents is not None:
+                for e, ags in enumerate(self.agents):
+                    for i, a in enumerate(ags):
+                        coop[e, i] = a.cooperation_coef
+            self._rvo_coop = torch.from_numpy(coop).to(sim.device)
+            self._rvo_params = _lib.rvo_default_params()
+            self._rvo_params.neighbor_dist = float(self.config.SENSING_HORIZON)
+            self._rvo_params.time_horizon = float(getattr(self.config, "RVO_TIME_HORIZON", 5.0))
+            self._rvo_params.max_neighbors = int(self.config.MAX_NUM_AGENTS_IN_ENVIRONMENT)
         self._needs_actions = bool(policies & {L.POLICY_EXTERNAL, L.POLICY_LEARNING, L.POLICY_CARRL})
         if self._has_ig:
             if self.obstacles is None:
@@ -226,6 +242,8 @@ class BatchedCollisionAvoidanceEnv:
             pol = sim.explore_step()
         if self._has_ga3c:
             pol = sim.ga3c_forward(use_tensor_cores=True)
+        if self._has_rvo:
+            pol = sim.rvo_step(coop=self._rvo_coop, params=self._rvo_params)
         sim.step(ext_actions=ext, policy_actions=pol, dt=dt)
         self.episode_step_number += 1
         self._host_state = None

@@ -28,6 +28,13 @@ class Obs(ctypes.Structure):
 
 OBS_FIELDS = tuple(n for n, _ in Obs._fields_)
 
+
+class RvoParams(ctypes.Structure):
+    """``struct casim_rvo_params``: what RVOPolicy.__init__ reads from Config (RVOPolicy.py:13-28)."""
+    _fields_ = [("neighbor_dist", c_double), ("time_horizon", c_double), ("radius_scale", c_double),
+                ("max_delta_heading", c_double), ("max_neighbors", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
+
+
 # every symbol include/casim.h declares: name -> (restype, argtypes)
 _PCFG = ctypes.POINTER(SimConfig)
 _POBS = ctypes.POINTER(Obs)
@@ -51,6 +58,8 @@ SYMBOLS = {
                                    c_void_p, c_void_p]),
     "casim_ga3c_set_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "casim_ga3c_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "casim_rvo_default_params": (None, [ctypes.POINTER(RvoParams)]),
+    "casim_rvo_step": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.POINTER(RvoParams), c_void_p, c_void_p]),
     "casim_launch_count": (ctypes.c_ulonglong, [c_void_p]),
 }
 
@@ -90,6 +99,12 @@ def default_config():
     c = SimConfig()
     load().casim_default_config(ctypes.byref(c))
     return c
+
+
+def rvo_default_params():
+    p = RvoParams()
+    load().casim_rvo_default_params(ctypes.byref(p))
+    return p
 
 
 def ptr(t):

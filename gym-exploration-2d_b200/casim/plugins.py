@@ -60,6 +60,11 @@ class GA3CCADRLPolicy(Policy):
     policy_id, str = L.POLICY_GA3C_CADRL, "GA3CCADRLPolicy"
 
 
+class RVOPolicy(Policy):
+    """envs/policies/RVOPolicy.py:53-117 + Python-RVO2 (casim_rvo_step); uses Agent.cooperation_coef (:85)"""
+    policy_id, str = L.POLICY_RVO, "RVO"
+
+
 class PedestrianDatasetPolicy(Policy):
     """envs/policies/PedestrianDatasetPolicy.py:15-16 -> zeros (motion comes from ExternalDynamics)"""
     policy_id, str = L.POLICY_PEDESTRIAN, "PedestrianDatasetPolicy"

@@ -255,6 +255,18 @@ class BatchedSim:
                                                _stream_ptr()), "casim_ga3c_forward")
         return self.buf["policy_actions"]
 
+    def rvo_step(self, coop=None, params=None):
+        """RVOPolicy.find_next_action for every RVO agent -> ``buf['policy_actions']`` (pass it to
+        ``step(policy_actions=...)``).  coop: [E,A] float32 Agent.cooperation_coef (None = 1.0)."""
+        self._policy_buffers()
+        if coop is not None:
+            coop = self._dev(coop, torch.float32)
+            self._keep["rvo_coop"] = coop
+        _lib.check(self.lib.casim_rvo_step(self.handle, _lib.ptr(self.state), _lib.ptr(coop),
+                                           ctypes.byref(params) if params is not None else None,
+                                           _lib.ptr(self.buf["policy_actions"]), _stream_ptr()), "casim_rvo_step")
+        return self.buf["policy_actions"]
+
     def launch_count(self):
         return int(self.lib.casim_launch_count(self.handle))
 

@@ -60,7 +60,8 @@ enum casim_policy {            /* envs/policies/ */
   CASIM_POLICY_CARRL = 4,          /* CARRLPolicy.py:14-15 (11-entry table) */
   CASIM_POLICY_IG_GREEDY = 5,      /* ig_greedy.py:31-43 (action from casim_explore_step) */
   CASIM_POLICY_GA3C_CADRL = 6,     /* GA3CCADRLPolicy.py:34-43 (action from casim_ga3c_forward) */
-  CASIM_POLICY_PEDESTRIAN = 7      /* PedestrianDatasetPolicy.py:15-16 (zeros) */
+  CASIM_POLICY_PEDESTRIAN = 7,     /* PedestrianDatasetPolicy.py:15-16 (zeros) */
+  CASIM_POLICY_RVO = 8             /* RVOPolicy.py:53-117 + Python-RVO2/src/Agent.cpp (action from casim_rvo_step) */
 };
 enum casim_dynamics {          /* envs/dynamics/ */
   CASIM_DYN_UNICYCLE = 0,          /* UnicycleDynamics.py:10-31       */
@@ -157,6 +158,16 @@ typedef struct casim_obs {
 
 #define CASIM_ZEROCOPY_MAX (1u << 20)
 
+/* Parameters of the RVO policy's simulator (RVOPolicy.py:13-28): what RVOPolicy.__init__ reads from Config. */
+typedef struct casim_rvo_params {
+  double neighbor_dist;      /* Config.SENSING_HORIZON (inf)                config.py:63, RVOPolicy.py:14 */
+  double time_horizon;       /* Config.RVO_TIME_HORIZON (5.0)               config.py:66, RVOPolicy.py:23 */
+  double radius_scale;       /* 1 + 15e-2                                   RVOPolicy.py:78 */
+  double max_delta_heading;  /* pi/6                                        RVOPolicy.py:20 */
+  int32_t max_neighbors;     /* Config.MAX_NUM_AGENTS_IN_ENVIRONMENT (10)   config.py:70, RVOPolicy.py:15 */
+  int32_t reserved[3];
+} casim_rvo_params;
+
 typedef struct casim_handle casim_handle;
 
 const char* casim_last_error(void);
@@ -245,6 +256,16 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
 int casim_ga3c_set_weights(casim_handle* h, const float* weights_host, int n_params, void* stream);
 int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_actions, int32_t* action_idx,
                        float* probs, float* nn_input, int use_tensor_cores, void* stream);
+
+/* RVO policy.  Replaces RVOPolicy.find_next_action (RVOPolicy.py:53-117) and the
+ * ego agent's share of rvo2.PyRVOSimulator.doStep (Python-RVO2/src/RVOSimulator.cpp:163-183, Agent.cpp:43-56,
+ * 286-631) for every agent whose policy id is CASIM_POLICY_RVO: writes [pref_speed, delta_heading] into
+ * policy_actions [E,A,2] (other agents' entries are left untouched); pass the buffer to casim_step.
+ * coop: [E,A] Agent.cooperation_coef (agent.py:10,103; RVOPolicy.py:85) or NULL = 1.0.  params: NULL = defaults.
+ * Static obstacles are not supported by this entry point (returns CASIM_EINVAL when the handle has a map). */
+void casim_rvo_default_params(casim_rvo_params* params);
+int casim_rvo_step(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* params,
+                   float* policy_actions, void* stream);
 
 /* Introspection for benchmarks: number of kernel launches issued through this handle so far. */
 unsigned long long casim_launch_count(const casim_handle* h);

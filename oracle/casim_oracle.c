@@ -258,6 +258,7 @@ static void choose_action(const casim_config* c, const double* s, const double* 
       break;
     case CASIM_POLICY_IG_GREEDY:
     case CASIM_POLICY_GA3C_CADRL:
+    case CASIM_POLICY_RVO: /* RVOPolicy.py:53-117: action computed by casim_oracle_rvo_actions */
       if (pol) {
         a[0] = (float)pol[0];
         a[1] = (float)pol[1];

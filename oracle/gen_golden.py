@@ -483,6 +483,7 @@ def gen_occgrid_cv2(ns, n=400, seed=5):
 def main():
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     os.makedirs(GOLDEN, exist_ok=True)
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref"))   # real rvo2 binding if built
     ns = rh.modules()
     if what in ("c1", "all"):
         gen_c1(ns)
@@ -501,6 +502,10 @@ def main():
     if what in ("ga3c", "all"):
         from oracle import gen_golden_ga3c
         gen_golden_ga3c.main(ns)
+    if what in ("rvo", "all"):
+        from oracle import gen_golden_rvo
+        assert gen_golden_rvo.main() == 0
+        gen_golden_rvo.main_policy(ns)
 
 
 if __name__ == "__main__":

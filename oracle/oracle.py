@@ -250,6 +250,30 @@ def ga3c_forward(cfg, state, weights, n_agents=None, n_threads=1):
     return out
 
 
+class RvoParams(ctypes.Structure):
+    """casim_rvo_params (include/casim.h): RVOPolicy.py:13-28 defaults."""
+    _fields_ = [("neighbor_dist", ctypes.c_double), ("time_horizon", ctypes.c_double), ("radius_scale", ctypes.c_double),
+                ("max_delta_heading", ctypes.c_double), ("max_neighbors", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
+
+
+def rvo_default_params():
+    return RvoParams(neighbor_dist=float("inf"), time_horizon=5.0, radius_scale=1 + 15e-2, max_delta_heading=np.pi / 6,
+                     max_neighbors=10)
+
+
+def rvo_actions(cfg, state, coop=None, n_agents=None, params=None):
+    """RVOPolicy.find_next_action for every RVO agent: state [E,A,24] f64 -> actions [E,A,2] f64."""
+    state = np.ascontiguousarray(state, dtype=np.float64)
+    E, A = state.shape[:2]
+    coop = None if coop is None else np.ascontiguousarray(coop, dtype=np.float64)
+    n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
+    prm = params or rvo_default_params()
+    out = np.zeros((E, A, 2))
+    rc = lib().casim_oracle_rvo_actions(ctypes.byref(cfg), ctypes.byref(prm), E, A, _p(n_agents), _p(state), _p(coop), _p(out))
+    assert rc == 0, rc
+    return out
+
+
 def ga3c_network(weights, x):
     """Network forward alone: x [B,75] f32 -> probs [B,11] f32."""
     weights = np.ascontiguousarray(weights, dtype=np.float32)

@@ -1,5 +1,7 @@
 """CPU: the C oracle (oracle/casim_oracle.c) against golden vectors produced by the real reference
 (oracle/gen_golden.py).  Flags / ordering / grid cells exact, continuous values 1e-5."""
+import os
+
 import numpy as np
 import pytest
 
@@ -269,3 +271,60 @@ def test_ga3c_network_vs_torch(oracle_lib):
     assert np.array_equal(probs.argmax(1), ref.numpy().argmax(1))
     np.testing.assert_allclose(oracle.ga3c_actions()[[0, 4, 6, 10]],
                                [[1.0, -np.pi / 6], [1.0, np.pi / 6], [0.5, 0.0], [0.0, np.pi / 6]], atol=1e-15)
+
+
+# ---------------------------------------------------------------------------------------------
+# RVO policy
+def _rvo_sim_call(fn, g, i):
+    import ctypes
+    P = ctypes.POINTER(ctypes.c_double)
+    n = int(g["n"][i])
+    arrs = [np.ascontiguousarray(g[k][i, :n], dtype=np.float64) for k in ("pos", "vel", "pref", "radius", "ms")]
+    out = np.zeros(2)
+    fn.restype = ctypes.c_int
+    fn.argtypes = [ctypes.c_int, P, P, P, P, P, ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_double,
+                   ctypes.c_int, ctypes.c_double, P]
+    assert fn(n, *[a.ctypes.data_as(P) for a in arrs], int(g["ego"][i]), float(g["collab"][i]), 0.1, float(g["nd"][i]),
+              int(g["mn"][i]), 5.0, out.ctypes.data_as(P)) == 0
+    return out
+
+
+def test_rvo_simulator_restatement_is_bit_exact_vs_reference_library(oracle_lib):
+    """oracle/casim_oracle_rvo.c vs the new ego positions recorded from the reference's own C++ RVO2 library
+    (oracle/gen_golden_rvo.py, 600 random crowds incl. collisions, negative / zero collaboration, neighbour caps)."""
+    g = np.load(os.path.join(H.GOLDEN, "rvo.npz"))
+    fn = oracle_lib.lib().casim_oracle_rvo_ref_step
+    for i in range(len(g["n"])):
+        got = _rvo_sim_call(fn, g, i)
+        assert np.array_equal(got, g["new_pos"][i]), "case %d: %r != %r" % (i, got, g["new_pos"][i])
+
+
+def test_rvo_reference_library_if_built(oracle_lib):
+    """When oracle/_ref/librvo2_ref.so (the reference's sources compiled by `make -C oracle ref`) travelled with the
+    repo, compare call for call on fresh random inputs, not only on the fixtures."""
+    import ctypes
+    path = os.path.join(os.path.dirname(H.GOLDEN), os.pardir, "oracle", "_ref", "librvo2_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/librvo2_ref.so not built")
+    ref = ctypes.CDLL(path).rvo2_ref_step
+    fn = oracle_lib.lib().casim_oracle_rvo_ref_step
+    rng = np.random.default_rng(2024)
+    for c in range(300):
+        n = int(rng.integers(2, 25))
+        sp = float(rng.choice([1.0, 2.5, 6.0]))
+        g = {"n": [n], "ego": [int(rng.integers(0, n))], "collab": [float(rng.choice([1.0, 0.5, -1.0]))], "nd": [np.inf],
+             "mn": [int(rng.choice([10, 4, 30]))]}
+        f = lambda a: np.asarray(a, np.float32).astype(np.float64)[None]
+        g["pos"], g["vel"] = f(rng.uniform(-sp, sp, (n, 2))), f(rng.uniform(-1, 1, (n, 2)))
+        g["pref"], g["radius"], g["ms"] = f(rng.uniform(-1, 1, (n, 2))), f(rng.uniform(0.2, 0.9, n)), f(rng.uniform(0.5, 1.5, n))
+        assert np.array_equal(_rvo_sim_call(ref, g, 0), _rvo_sim_call(fn, g, 0)), "case %d" % c
+
+
+def test_rvo_policy_restatement_vs_reference_policy(oracle_lib):
+    """casim_oracle_rvo_actions vs the UNMODIFIED RVOPolicy.find_next_action run over the reference's Cython binding
+    (tests/golden/rvo.npz keys state / coop / n_agents / actions)."""
+    from casim import lib
+    g = np.load(os.path.join(H.GOLDEN, "rvo.npz"))
+    act = oracle_lib.rvo_actions(lib.default_config(), g["state"], g["coop"], g["n_agents"])
+    np.testing.assert_allclose(act, g["actions"], rtol=0, atol=1e-12)
+    assert ((act[..., 0] == 0) == (g["actions"][..., 0] == 0)).all()      # the pi/6 turn limit zeroes the same speeds
