@@ -53,6 +53,8 @@ WORKLOADS = {
     "c5": dict(E=1024, A=20, sensors=("other_agents_states",),
                desc="8192/8 = 1024 envs per GPU x 20 agents (CADRL formations), batched GA3C-CADRL LSTM policy forward, "
                     "random-init weights"),
+    "rvo": dict(E=4096, A=10, sensors=(),
+                desc="4096 envs x 10 agents, all RVOPolicy (ORCA, reciprocal), collision + reward step (SURVEY 8(f) rank 1)"),
 }
 GA3C_FLOP_PER_AGENT = 666112      # 2*[10*71*256 + 68*256 + 256*256 + 256*256 + 256*11]
 
@@ -135,6 +137,9 @@ def scenario(wl, E, A, seed):
     if wl == "c2":
         init, types, n = S.open_space(E, A, seed=seed, sensors=0)
         return init, types, n, None
+    if wl == "rvo":
+        init, types, n = S.open_space(E, A, seed=seed, sensors=0, static_every=0, policy=L.POLICY_RVO)
+        return init, types, n, None
     if wl == "c4":
         return S.exploration(E, seed=seed)
     if wl == "c5":
@@ -190,6 +195,8 @@ def oracle_run(wl, E, A, steps, warmup, threads, seed=1234):
                                       prev_game_over=go, n_threads=threads)["policy_actions"]
         elif wl == "c5":
             pol = oracle.ga3c_forward(cfg, state, w, n_agents=n, n_threads=threads)["policy_actions"]
+        elif wl == "rvo":
+            pol = oracle.rvo_actions(cfg, state, n_agents=n, n_threads=threads)
         oracle.step(cfg, state, policy_actions=pol, n_agents=n, maps=maps, init=init64, types0=types, prev_game_over=go,
                     obs=obs, n_threads=threads)
         return obs.game_over.copy()
@@ -257,7 +264,7 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-REF_SAMPLE_ENVS = {"c2": 4096, "c3": 512, "full": 64, "c4": 128, "c5": 256}
+REF_SAMPLE_ENVS = {"c2": 4096, "c3": 512, "full": 64, "c4": 128, "c5": 256, "rvo": 2048}
 
 
 def run_reference(args, rank, world):
@@ -359,7 +366,7 @@ def main():
         sims.append(sim)
     torch.cuda.synchronize()
     launches_per_step = 1 + (1 if "laserscan" in W["sensors"] else 0) + (1 if "local_grid" in W["sensors"] else 0)
-    launches_per_step += 1 if wl == "c4" else (2 if wl == "c5" else 0)
+    launches_per_step += 1 if wl in ("c4", "rvo") else (2 if wl == "c5" else 0)
     use_tc = not args.ga3c_fp32
 
     stream = torch.cuda.Stream(device=dev)
@@ -369,6 +376,8 @@ def main():
             return sim.explore_step()
         if wl == "c5":
             return sim.ga3c_forward(use_tensor_cores=use_tc)
+        if wl == "rvo":
+            return sim.rvo_step()
         return None
 
     def run_steps(k0, k):
@@ -523,6 +532,12 @@ def main():
         # candidates x 8 B, from the instrumented counters of one launch (all 10 poses share counter 2)
         xbytes = explore_counts[1] * 8 + explore_counts[2] * 8 + (explore_counts[2] // 10) * 8
         kern["k_explore"] = (t, xbytes, "timed alone")
+        t_sens += t
+    if wl == "rvo":
+        t = time_alone(lambda sm: sm.rvo_step())
+        # per agent: own 3 state planes read (48 B) + 8 B action written; the neighbours' planes are re-read from
+        # L1/L2 within the environment (A-1 x 48 B per agent, not HBM traffic)
+        kern["k_rvo"] = (t, (48 + 8) * NA, "timed alone")
         t_sens += t
     if wl == "c5":
         t_both = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc))

@@ -462,6 +462,29 @@ int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_action
   return 0;
 }
 
+int casim_flat_row_size(const casim_handle* h, const int32_t* keys, int n_keys) {
+  if (!h || !keys || n_keys < 0) return -1;
+  return casim_flat_row_size_impl(h, keys, n_keys);
+}
+
+int casim_flatten_obs(casim_handle* h, const float* state, const casim_obs* obs, const int32_t* keys, int n_keys,
+                      float* out, void* stream) {
+  REQUIRE(h && state && obs && keys && out, "null argument");
+  REQUIRE(n_keys > 0 && n_keys <= 16, "between 1 and 16 observation keys");
+  REQUIRE(casim_flat_row_size_impl(h, keys, n_keys) > 0, "unknown observation key");
+  for (int i = 0; i < n_keys; i++) {
+    const int k = keys[i];
+    if (k == CASIM_KEY_REL_GOAL || k == CASIM_KEY_NUM_OTHER_AGENTS || k == CASIM_KEY_USE_PPO)
+      REQUIRE(obs->obs_misc, "flatten: obs_misc buffer missing");
+    if (k == CASIM_KEY_OTHER_AGENT_STATES || k == CASIM_KEY_OTHER_AGENTS_STATES)
+      REQUIRE(obs->other_agents_states, "flatten: other_agents_states buffer missing");
+    if (k == CASIM_KEY_LASERSCAN) REQUIRE(obs->laserscan, "flatten: laserscan buffer missing");
+    if (k == CASIM_KEY_LOCAL_GRID) REQUIRE(obs->local_grid, "flatten: local_grid buffer missing");
+  }
+  CK(casim_launch_flatten(h, state, obs, keys, n_keys, out, (cudaStream_t)stream));
+  return 0;
+}
+
 void casim_rvo_default_params(casim_rvo_params* p) {
   if (!p) return;
   memset(p, 0, sizeof(*p));

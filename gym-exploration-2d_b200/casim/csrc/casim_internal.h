@@ -103,6 +103,9 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
                               float* probs, float* nn_input, int use_tc, cudaStream_t s);
 cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* prm,
                              float* policy_actions, cudaStream_t s);
+cudaError_t casim_launch_flatten(casim_handle* h, const float* state, const casim_obs* obs, const int32_t* keys,
+                                 int n_keys, float* out, cudaStream_t s);
+int casim_flat_row_size_impl(const casim_handle* h, const int32_t* keys, int n_keys);
 cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_params, cudaStream_t s);
 
 void casim_set_error(const char* fmt, ...);

@@ -33,3 +33,10 @@ def encode_type(policy_id, dynamics_id, sensor_mask):
 def decode_type(t):
     t = int(t)
     return t & 0xff, (t >> 8) & 0xff, (t >> 16) & 0xff
+
+
+# enum casim_obs_key (include/casim.h): names of Config.STATE_INFO_DICT, envs/config.py:104-215
+OBS_KEYS = ("dist_to_goal", "rel_goal", "radius", "heading_ego_frame", "heading_global_frame", "pos_global_frame",
+            "pref_speed", "num_other_agents", "other_agent_states", "other_agents_states", "local_grid", "laserscan",
+            "use_ppo")
+OBS_KEY_ID = {k: i for i, k in enumerate(OBS_KEYS)}

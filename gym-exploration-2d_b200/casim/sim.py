@@ -267,6 +267,24 @@ class BatchedSim:
                                            _lib.ptr(self.buf["policy_actions"]), _stream_ptr()), "casim_rvo_step")
         return self.buf["policy_actions"]
 
+    def flat_row_size(self, keys):
+        ids = (ctypes.c_int32 * len(keys))(*[L.OBS_KEY_ID[k] for k in keys])
+        n = int(self.lib.casim_flat_row_size(self.handle, ids, len(keys)))
+        if n < 0:
+            raise _lib.CasimError("unknown observation key in %r" % (keys,))
+        return n
+
+    def flatten_obs(self, keys, out=None):
+        """MultiagentFlattenDictWrapper.observation (envs/wrappers.py:37-45) for every environment: float32
+        [E, A*S] with, per agent slot, the listed keys ravel()ed in order (absent slots zero)."""
+        ids = (ctypes.c_int32 * len(keys))(*[L.OBS_KEY_ID[k] for k in keys])
+        S = self.flat_row_size(keys)
+        if out is None:
+            out = torch.empty((self.E, self.A * S), dtype=torch.float32, device=self.device)
+        _lib.check(self.lib.casim_flatten_obs(self.handle, _lib.ptr(self.state), ctypes.byref(self._obs), ids, len(keys),
+                                              _lib.ptr(out), _stream_ptr()), "casim_flatten_obs")
+        return out
+
     def launch_count(self):
         return int(self.lib.casim_launch_count(self.handle))
 

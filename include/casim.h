@@ -267,6 +267,21 @@ void casim_rvo_default_params(casim_rvo_params* params);
 int casim_rvo_step(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* params,
                    float* policy_actions, void* stream);
 
+/* Flattened observation wire format.  Replaces
+ * MultiagentFlattenDictWrapper.observation (envs/wrappers.py:37-45) for all environments at once: out [E,A,S] float32,
+ * for each agent slot the listed keys' values ravel()ed and concatenated in the given order (S = casim_flat_row_size);
+ * absent agent slots are zero (collision_avoidance_env.py:125-134).  out viewed as [E, A*S] is the VecEnv observation
+ * array (experiments/src/env_utils.py:7-39); local_grid cells become 0.0 / 1.0.  keys is a HOST array. */
+enum casim_obs_key {           /* names of Config.STATE_INFO_DICT, envs/config.py:104-215 */
+  CASIM_KEY_DIST_TO_GOAL = 0, CASIM_KEY_REL_GOAL, CASIM_KEY_RADIUS, CASIM_KEY_HEADING_EGO_FRAME,
+  CASIM_KEY_HEADING_GLOBAL_FRAME, CASIM_KEY_POS_GLOBAL_FRAME, CASIM_KEY_PREF_SPEED, CASIM_KEY_NUM_OTHER_AGENTS,
+  CASIM_KEY_OTHER_AGENT_STATES, CASIM_KEY_OTHER_AGENTS_STATES, CASIM_KEY_LOCAL_GRID, CASIM_KEY_LASERSCAN,
+  CASIM_KEY_USE_PPO, CASIM_KEY_COUNT
+};
+int casim_flat_row_size(const casim_handle* h, const int32_t* keys, int n_keys);
+int casim_flatten_obs(casim_handle* h, const float* state, const casim_obs* obs, const int32_t* keys, int n_keys,
+                      float* out, void* stream);
+
 /* Introspection for benchmarks: number of kernel launches issued through this handle so far. */
 unsigned long long casim_launch_count(const casim_handle* h);
 

@@ -23,6 +23,7 @@
  * breaks them by k-d tree visiting order.
  */
 #include <math.h>
+#include <pthread.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -287,11 +288,18 @@ static double np_mod(double a, double b) {
  * state: [E,A,24] doubles (oracle layout); coop: [E,A] Agent.cooperation_coef (agent.py:103) or NULL = 1.0;
  * actions: [E,A,2] = [pref_speed, delta_heading] (zeros for other agents).  The simulator instance of each policy
  * is fed ALL agents of its environment (:66-82) and only the ego agent's new position is read back (:91). */
-int casim_oracle_rvo_actions(const casim_config* cfg, const casim_rvo_params* prm, int E, int A, const int32_t* n_agents,
-                             const double* state, const double* coop, double* actions) {
-  if (A > MAXN) return 1;
+typedef struct {
+  const casim_config* cfg; const casim_rvo_params* prm; int A; const int32_t* n_agents;
+  const double* state; const double* coop; double* actions; int e0, e1;
+} rvo_job;
+
+static void* rvo_job_main(void* arg) {
+  const rvo_job* J = (const rvo_job*)arg;
+  const casim_config* cfg = J->cfg; const casim_rvo_params* prm = J->prm;
+  const int A = J->A; const int32_t* n_agents = J->n_agents;
+  const double* state = J->state; const double* coop = J->coop; double* actions = J->actions;
   const double dt = cfg->dt;
-  for (int e = 0; e < E; e++) {
+  for (int e = J->e0; e < J->e1; e++) {
     const int n = n_agents ? (n_agents[e] < A ? n_agents[e] : A) : A;
     const double* S = state + (size_t)e * A * NF;
     v2 p[MAXN], v[MAXN], pv[MAXN];
@@ -330,5 +338,28 @@ int casim_oracle_rvo_actions(const casim_config* cfg, const casim_rvo_params* pr
       act[1] = delta_heading;
     }
   }
+  return NULL;
+}
+
+int casim_oracle_rvo_actions_mt(const casim_config* cfg, const casim_rvo_params* prm, int E, int A, const int32_t* n_agents,
+                                const double* state, const double* coop, double* actions, int n_threads) {
+  if (A > MAXN) return 1;
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 64) n_threads = 64;
+  rvo_job jobs[64];
+  pthread_t th[64];
+  for (int t = 0; t < n_threads; t++) {
+    rvo_job* j = &jobs[t];
+    j->cfg = cfg; j->prm = prm; j->A = A; j->n_agents = n_agents; j->state = state; j->coop = coop; j->actions = actions;
+    j->e0 = (int)((long long)E * t / n_threads);
+    j->e1 = (int)((long long)E * (t + 1) / n_threads);
+    if (n_threads == 1) rvo_job_main(j); else pthread_create(&th[t], NULL, rvo_job_main, j);
+  }
+  if (n_threads > 1) for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
   return 0;
+}
+
+int casim_oracle_rvo_actions(const casim_config* cfg, const casim_rvo_params* prm, int E, int A, const int32_t* n_agents,
+                             const double* state, const double* coop, double* actions) {
+  return casim_oracle_rvo_actions_mt(cfg, prm, E, A, n_agents, state, coop, actions, 1);
 }

@@ -480,6 +480,36 @@ def gen_occgrid_cv2(ns, n=400, seed=5):
     print("wrote occgrid.npz")
 
 
+FLAT_KEYS = ['dist_to_goal', 'rel_goal', 'radius', 'heading_ego_frame', 'heading_global_frame', 'pos_global_frame',
+             'pref_speed', 'num_other_agents', 'other_agents_states', 'laserscan', 'local_grid', 'use_ppo']
+
+
+def gen_flatten(ns, T=4):
+    """Wire format: the reference's MultiagentFlattenDictWrapper.observation (envs/wrappers.py:37-45) applied to the
+    observation dict of a 3-agent crossing-map environment with all three sensors, 10 agent slots."""
+    from gym_collision_avoidance.envs.wrappers import MultiagentFlattenDictWrapper
+    set_mode(ns, 2)
+    mask = L.SENSOR_OTHER_AGENTS | L.SENSOR_LASERSCAN | L.SENSOR_OCCUPANCY_GRID
+    init = f32(np.array([[-6.0, 0.3, 6.0, -0.5, 0.4, 1.0, 0.1], [-1.0, 5.5, 0.5, -7.0, 0.3, 1.2, -1.5],
+                         [7.0, -0.6, -7.0, 0.4, 0.5, 0.8, 3.0]]))
+    types = np.full((3,), L.encode_type(L.POLICY_NONCOOPERATIVE, L.DYN_UNICYCLE, mask), np.int32)
+    agents = build_agents(ns, init, types)
+    env = rh.make_env(ns, agents, OBSTACLE_SETS[1], FLAT_KEYS)
+    w = object.__new__(MultiagentFlattenDictWrapper)
+    w.dict_keys, w.max_num_agents = FLAT_KEYS, ns.Config.MAX_NUM_AGENTS_IN_ENVIRONMENT
+    states = np.zeros((T, 3, L.STATE_WORDS))
+    flat = []
+    for t in range(T):
+        for i in range(3):
+            states[t, i] = extract_state(agents[i], types[i])
+        flat.append(np.asarray(w.observation(env.observation), np.float64))
+        with rh.quiet():
+            env.step({})
+    np.savez_compressed(os.path.join(GOLDEN, "flatten.npz"), init=init, types=types, states=states, flat=np.stack(flat),
+                        keys=np.array(FLAT_KEYS), map_id=1)
+    print("wrote flatten.npz", np.stack(flat).shape)
+
+
 def main():
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     os.makedirs(GOLDEN, exist_ok=True)
@@ -502,6 +532,8 @@ def main():
     if what in ("ga3c", "all"):
         from oracle import gen_golden_ga3c
         gen_golden_ga3c.main(ns)
+    if what in ("flatten", "all"):
+        gen_flatten(ns)
     if what in ("rvo", "all"):
         from oracle import gen_golden_rvo
         assert gen_golden_rvo.main() == 0

@@ -261,7 +261,7 @@ def rvo_default_params():
                      max_neighbors=10)
 
 
-def rvo_actions(cfg, state, coop=None, n_agents=None, params=None):
+def rvo_actions(cfg, state, coop=None, n_agents=None, params=None, n_threads=1):
     """RVOPolicy.find_next_action for every RVO agent: state [E,A,24] f64 -> actions [E,A,2] f64."""
     state = np.ascontiguousarray(state, dtype=np.float64)
     E, A = state.shape[:2]
@@ -269,7 +269,8 @@ def rvo_actions(cfg, state, coop=None, n_agents=None, params=None):
     n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
     prm = params or rvo_default_params()
     out = np.zeros((E, A, 2))
-    rc = lib().casim_oracle_rvo_actions(ctypes.byref(cfg), ctypes.byref(prm), E, A, _p(n_agents), _p(state), _p(coop), _p(out))
+    rc = lib().casim_oracle_rvo_actions_mt(ctypes.byref(cfg), ctypes.byref(prm), E, A, _p(n_agents), _p(state), _p(coop),
+                                           _p(out), int(n_threads))
     assert rc == 0, rc
     return out
 
