@@ -18,6 +18,11 @@
  * Not covered: obstacle ORCA lines (Agent.cpp:66-284) -- casim_rvo_step refuses a handle that has a static map.
  * Neighbour ties at exactly equal squared distance are broken by agent index (reference: k-d tree visiting order).
  *
+ * Mapping note (measured on B200, C2-shaped all-RVO batch of 40 960 agents): one thread per agent takes 22.8 us;
+ * a sub-warp cooperative variant (16 lanes per agent, one ORCA line per lane, ballot / shuffle linear programs --
+ * kept for reference in scratch/casim_rvo_subwarp.cu.txt, parity-green) took 30.8 us: it issues 2.3x more warp
+ * instructions (23 M vs ~10 M) and the kernel is issue-bound once enough warps are resident.
+ *
  * Bound: latency / fp32 issue (a few hundred dependent flops per neighbour, data-dependent linear programs); the
  * HBM traffic is 48 B read + 8 B written per agent (neighbour reads hit L1/L2 within the environment).
  */

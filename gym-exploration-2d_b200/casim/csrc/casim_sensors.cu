@@ -29,14 +29,31 @@ struct LaserArgs {
 };
 
 __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
+  /* Per-beam / per-sample tables: indexed by lane-dependent b and k, so they live in shared memory (a divergent
+   * index into the kernel-parameter constant bank is serialised, one address per issue).  s_out[k] is the value
+   * reported for "range = sample k" (k == nr: no hit, max range): the fp64 division happens once per CTA. */
+  __shared__ double s_cos[CASIM_MAX_BEAMS], s_sin[CASIM_MAX_BEAMS], s_r[CASIM_MAX_RANGES];
+  __shared__ float s_out[CASIM_MAX_RANGES + 1];
   const DevCfg& c = p.c;
+  const int nb = c.nb, nr = c.nr;
+  if (threadIdx.x < CASIM_MAX_BEAMS) {
+    s_cos[threadIdx.x] = c.laser_cos[threadIdx.x];
+    s_sin[threadIdx.x] = c.laser_sin[threadIdx.x];
+  } else if (threadIdx.x < CASIM_MAX_BEAMS + CASIM_MAX_RANGES) {
+    const int k = threadIdx.x - CASIM_MAX_BEAMS;
+    s_r[k] = c.laser_r[k];
+    s_out[k] = (float)(1.0 - c.laser_r[k] / c.laser_norm);
+  } else if (threadIdx.x == CASIM_MAX_BEAMS + CASIM_MAX_RANGES) {
+    s_out[CASIM_MAX_RANGES] = (float)(1.0 - c.laser_max_range / c.laser_norm);
+  }
+  casim_pdl_enter();
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const long long g = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long N = (long long)p.E * p.A;
   if (g >= N) return;
   const int e = (int)(g / p.A), ai = (int)(g - (long long)e * p.A);
   const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
-  const int nb = c.nb, nr = c.nr;
   float* out = p.out + g * nb;
   const int type = __float_as_int(p.state[5 * N + g].w);
   const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_LASERSCAN);
@@ -64,11 +81,12 @@ __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
   if (b < nb && pl) {
     /* beam direction cos/sin(angle_b + heading) by angle addition from the step kernel's cos/sin(heading);
      * lattice point k in CELL units: col = floor(oy + (px + r_k cs)/cell), row = floor(ox - (py + r_k sn)/cell) */
-    const double cs = c.laser_cos[b] * ch - c.laser_sin[b] * sh, sn = c.laser_sin[b] * ch + c.laser_cos[b] * sh;
+    const double cs = s_cos[b] * ch - s_sin[b] * sh, sn = s_sin[b] * ch + s_cos[b] * sh;
     const double u0 = c.map_oy + px * c.inv_cell, du = cs * c.inv_cell;  /* column coordinate, cells */
     const double v0 = c.map_ox - py * c.inv_cell, dv = -(sn * c.inv_cell); /* row coordinate, cells */
     for (int k = part; k < nr; k += P) {
-      int col = __double2int_rd(fma(c.laser_r[k], du, u0)), row = __double2int_rd(fma(c.laser_r[k], dv, v0));
+      const double rk = s_r[k];
+      int col = __double2int_rd(fma(rk, du, u0)), row = __double2int_rd(fma(rk, dv, v0));
       if ((unsigned)row < (unsigned)CASIM_MAP_DIM && (unsigned)col < (unsigned)CASIM_MAP_DIM && map_bit(pl, row, col)) {
         int dr = row - r0, dc = col - c0;
         if (dr * dr + dc * dc > disc_thr) mask |= 1u << k;
@@ -77,13 +95,12 @@ __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
   }
   for (int o = 1; o < P; o <<= 1) mask |= __shfl_xor_sync(FULL_MASK, mask, o);
   if (b < nb && part == 0) {
-    double range = c.laser_max_range;
+    int idx = CASIM_MAX_RANGES; /* no hit: max range */
     if (mask) {
       unsigned rest = mask & (mask - 1); /* drop the first hit */
-      int idx = rest ? (__ffs(rest) - 2) : (nr - 1);
-      range = c.laser_r[idx];
+      idx = rest ? (__ffs(rest) - 2) : (nr - 1);
     }
-    out[b] = (float)(1.0 - range / c.laser_norm);
+    out[b] = s_out[idx];
   }
 }
 
@@ -103,6 +120,7 @@ struct GridArgs {
  * One CTA per agent: warps 0-1 build the per-row / per-column fixed-point tables in fp64, then every thread
  * produces 4-cell output words with integer arithmetic and one bit lookup per cell. */
 __global__ void __launch_bounds__(256) k_grid_generic(const GridArgs p) {
+  casim_pdl_enter();
   const DevCfg& c = p.c;
   const long long g = blockIdx.x;
   const long long N = (long long)p.E * p.A;
@@ -235,6 +253,7 @@ __device__ __forceinline__ uint32_t grid_cell_exact(const uint32_t* __restrict__
 }
 
 __global__ void __launch_bounds__(32 * GRID_WARPS, 12) k_grid(const GridArgs p) {
+  casim_pdl_enter();
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const long long N = (long long)p.E * p.A;
@@ -413,8 +432,7 @@ cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laser
   int wpc = 8;
   dim3 grid((unsigned)((N + wpc - 1) / wpc)), block(32 * wpc);
   h->launches++;
-  k_laser<<<grid, block, 0, s>>>(a);
-  return cudaGetLastError();
+  return casim_launch_pdl<LaserArgs>(k_laser, grid, block, 0, s, a);
 }
 
 cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s) {
@@ -436,8 +454,6 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
   /* fast path: rows are whole 4-cell words, every agent's grid is 16-byte aligned and a multiple of 16 bytes */
   const bool fast = (h->dc.submap_h & 3) == 0 && (cells & 15) == 0 && (((uintptr_t)local_grid) & 15) == 0;
   if (fast)
-    k_grid<<<(unsigned)((N + GRID_WARPS - 1) / GRID_WARPS), 32 * GRID_WARPS, 0, s>>>(a);
-  else
-    k_grid_generic<<<(unsigned)N, 256, 0, s>>>(a);
-  return cudaGetLastError();
+    return casim_launch_pdl<GridArgs>(k_grid, dim3((unsigned)((N + GRID_WARPS - 1) / GRID_WARPS)), dim3(32 * GRID_WARPS), 0, s, a);
+  return casim_launch_pdl<GridArgs>(k_grid_generic, dim3((unsigned)N), dim3(256), 0, s, a);
 }

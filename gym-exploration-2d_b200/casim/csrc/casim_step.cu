@@ -230,7 +230,27 @@ __device__ __forceinline__ void dynamics_step(const DevCfg& c, Agent& a, float a
     return;
   }
   double speed = (double)a0, sel;
-  if (dyn == CASIM_DYN_FIRST_ORDER) /* FirstOrderDynamics.py:10-23 */
+  float speed_word = a0; /* speed_global_frame */
+  if (dyn == CASIM_DYN_UNICYCLE_MAX_ACC) { /* UnicycleDynamicsMaxAcc.py:17-41 */
+    double cur_speed = (double)a.speed, cur_rate = a.turning;
+    double rate = fmin(fmax((double)a1 / dt, -3.0), 3.0);
+    double lin_acc = fmin(fmax(2.0 * ((double)a0 - cur_speed), -2.0), 2.0);
+    double turn_acc = fmin(fmax(2.0 * (rate - cur_rate), -3.0), 3.0);
+    cur_speed += lin_acc * dt;
+    cur_speed = fmin(fmax(cur_speed, -1.1), 1.1);
+    cur_rate += turn_acc * dt;
+    a.turning = cur_rate;
+    speed = cur_speed;
+    speed_word = (float)cur_speed;
+    sel = wrap_pi1(cur_rate * dt + a.heading);
+  } else if (dyn == CASIM_DYN_UNICYCLE_SECOND_ORDER_EULER) { /* UnicycleSecondOrderEulerDynamics.py:12-31 */
+    double vn = sqrt((double)a.vx * (double)a.vx + (double)a.vy * (double)a.vy);
+    speed = fmin(fmax(vn + (double)a0 * dt, 0.0), 1.0);
+    speed_word = (float)speed;
+    double ang = fmin(fmax(a.turning + (double)a1 * dt, -3.0), 3.0);
+    a.turning = ang;
+    sel = wrap_pi1(ang * dt + a.heading);
+  } else if (dyn == CASIM_DYN_FIRST_ORDER) /* FirstOrderDynamics.py:10-23 */
     sel = wrap_pi1((double)a1 * dt + a.heading);
   else if (dyn == CASIM_DYN_UNICYCLE_MAX_TURN_RATE) { /* UnicycleDynamicsMaxTurnRate.py:11-26 */
     double rate = (double)a1 / dt;
@@ -245,7 +265,7 @@ __device__ __forceinline__ void dynamics_step(const DevCfg& c, Agent& a, float a
   a.py += vy * dt;
   a.vx = (float)vx;
   a.vy = (float)vy;
-  a.speed = a0;
+  a.speed = speed_word;
   a.dheading = (float)wrap_pi1(sel - a.heading);
   a.heading = sel;
   a.cs = cs;

@@ -22,7 +22,8 @@ F_IS_INFEASIBLE = 64
 
 POLICY_STATIC, POLICY_NONCOOPERATIVE, POLICY_EXTERNAL, POLICY_LEARNING, POLICY_CARRL, \
     POLICY_IG_GREEDY, POLICY_GA3C_CADRL, POLICY_PEDESTRIAN, POLICY_RVO = range(9)
-DYN_UNICYCLE, DYN_FIRST_ORDER, DYN_EXTERNAL, DYN_UNICYCLE_MAX_TURN_RATE = range(4)
+DYN_UNICYCLE, DYN_FIRST_ORDER, DYN_EXTERNAL, DYN_UNICYCLE_MAX_TURN_RATE, DYN_UNICYCLE_MAX_ACC, \
+    DYN_UNICYCLE_SECOND_ORDER_EULER = range(6)
 SENSOR_OTHER_AGENTS, SENSOR_LASERSCAN, SENSOR_OCCUPANCY_GRID = 1, 2, 4
 
 

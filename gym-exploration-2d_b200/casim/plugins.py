@@ -93,6 +93,16 @@ class ExternalDynamics(Dynamics):
     dynamics_id = L.DYN_EXTERNAL
 
 
+class UnicycleDynamicsMaxAcc(Dynamics):
+    """envs/dynamics/UnicycleDynamicsMaxAcc.py:17-41"""
+    dynamics_id = L.DYN_UNICYCLE_MAX_ACC
+
+
+class UnicycleSecondOrderEulerDynamics(Dynamics):
+    """envs/dynamics/UnicycleSecondOrderEulerDynamics.py:12-31"""
+    dynamics_id = L.DYN_UNICYCLE_SECOND_ORDER_EULER
+
+
 class UnicycleDynamicsMaxTurnRate(Dynamics):
     """envs/dynamics/UnicycleDynamicsMaxTurnRate.py:11-26"""
     dynamics_id = L.DYN_UNICYCLE_MAX_TURN_RATE

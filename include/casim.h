@@ -67,7 +67,11 @@ enum casim_dynamics {          /* envs/dynamics/ */
   CASIM_DYN_UNICYCLE = 0,          /* UnicycleDynamics.py:10-31       */
   CASIM_DYN_FIRST_ORDER = 1,       /* FirstOrderDynamics.py:10-23     */
   CASIM_DYN_EXTERNAL = 2,          /* ExternalDynamics.py:8-23 + agent.py:125-145 */
-  CASIM_DYN_UNICYCLE_MAX_TURN_RATE = 3 /* UnicycleDynamicsMaxTurnRate.py:11-26 */
+  CASIM_DYN_UNICYCLE_MAX_TURN_RATE = 3, /* UnicycleDynamicsMaxTurnRate.py:11-26 */
+  CASIM_DYN_UNICYCLE_MAX_ACC = 4,       /* UnicycleDynamicsMaxAcc.py:17-41: current_speed lives in the SPEED word,
+                                           current_turning_rate in the TURNING_DIR word */
+  CASIM_DYN_UNICYCLE_SECOND_ORDER_EULER = 5 /* UnicycleSecondOrderEulerDynamics.py:12-31:
+                                           Agent.angular_speed_global_frame (agent.py:27) lives in the TURNING_DIR word */
 };
 enum casim_sensor {            /* envs/sensors/ */
   CASIM_SENSOR_OTHER_AGENTS = 1,   /* OtherAgentsStatesSensor.py:11-77 */

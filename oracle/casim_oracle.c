@@ -301,7 +301,24 @@ static void dynamics_step(const casim_config* c, double* s, const float* a, doub
   }
   double speed = (double)a[0];
   double sel;
-  if (dyn == CASIM_DYN_FIRST_ORDER)
+  if (dyn == CASIM_DYN_UNICYCLE_MAX_ACC) { /* UnicycleDynamicsMaxAcc.py:17-41 (kp 2, limits 3 rad/s, 2 m/s^2, 3 rad/s^2, 1.1 m/s) */
+    double cur_speed = s[CASIM_SPEED], cur_rate = s[CASIM_TURNING_DIR];
+    double rate = fmin(fmax((double)a[1] / dt, -3.0), 3.0);
+    double lin_acc = fmin(fmax(2.0 * ((double)a[0] - cur_speed), -2.0), 2.0);
+    double turn_acc = fmin(fmax(2.0 * (rate - cur_rate), -3.0), 3.0);
+    cur_speed += lin_acc * dt;
+    cur_speed = fmin(fmax(cur_speed, -1.1), 1.1);
+    cur_rate += turn_acc * dt;
+    s[CASIM_TURNING_DIR] = cur_rate;
+    speed = cur_speed;
+    sel = wrap(cur_rate * dt + s[CASIM_HEADING]);
+  } else if (dyn == CASIM_DYN_UNICYCLE_SECOND_ORDER_EULER) { /* UnicycleSecondOrderEulerDynamics.py:12-31 */
+    double vn = sqrt(s[CASIM_VX] * s[CASIM_VX] + s[CASIM_VY] * s[CASIM_VY]);
+    speed = fmin(fmax(vn + (double)a[0] * dt, 0.0), 1.0);
+    double ang = fmin(fmax(s[CASIM_TURNING_DIR] + (double)a[1] * dt, -3.0), 3.0);
+    s[CASIM_TURNING_DIR] = ang;
+    sel = wrap(ang * dt + s[CASIM_HEADING]);
+  } else if (dyn == CASIM_DYN_FIRST_ORDER)
     sel = wrap((double)a[1] * dt + s[CASIM_HEADING]);
   else if (dyn == CASIM_DYN_UNICYCLE_MAX_TURN_RATE) {
     double rate = (double)a[1] / dt;

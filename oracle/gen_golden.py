@@ -55,11 +55,14 @@ def policy_classes(ns):
 
     from gym_collision_avoidance.envs.policies.PedestrianDatasetPolicy import PedestrianDatasetPolicy
     from gym_collision_avoidance.envs.dynamics.UnicycleDynamicsMaxTurnRate import UnicycleDynamicsMaxTurnRate
+    from gym_collision_avoidance.envs.dynamics.UnicycleDynamicsMaxAcc import UnicycleDynamicsMaxAcc
+    from gym_collision_avoidance.envs.dynamics.UnicycleSecondOrderEulerDynamics import UnicycleSecondOrderEulerDynamics
     pol = {L.POLICY_STATIC: ns.StaticPolicy, L.POLICY_NONCOOPERATIVE: ns.NonCooperativePolicy,
            L.POLICY_EXTERNAL: PassThroughExternalPolicy, L.POLICY_CARRL: ns.CARRLPolicy,
            L.POLICY_PEDESTRIAN: PedestrianDatasetPolicy}
     dyn = {L.DYN_UNICYCLE: ns.UnicycleDynamics, L.DYN_FIRST_ORDER: ns.FirstOrderDynamics,
-           L.DYN_EXTERNAL: ns.ExternalDynamics, L.DYN_UNICYCLE_MAX_TURN_RATE: UnicycleDynamicsMaxTurnRate}
+           L.DYN_EXTERNAL: ns.ExternalDynamics, L.DYN_UNICYCLE_MAX_TURN_RATE: UnicycleDynamicsMaxTurnRate,
+           L.DYN_UNICYCLE_MAX_ACC: UnicycleDynamicsMaxAcc, L.DYN_UNICYCLE_SECOND_ORDER_EULER: UnicycleSecondOrderEulerDynamics}
     return pol, dyn
 
 
@@ -100,6 +103,13 @@ def inject_state(ag, s):
     ag.vel_global_frame = np.array([s[L.VX], s[L.VY]], dtype=np.float64)
     ag.delta_heading_global_frame = np.float64(s[L.DELTA_HEADING])
     ag.turning_dir = np.float64(s[L.TURNING_DIR])
+    # the TURNING_DIR / SPEED words double as the extra dynamics state (only one dynamics model owns an agent):
+    # UnicycleDynamicsMaxAcc.current_turning_rate / current_speed, Agent.angular_speed_global_frame
+    if hasattr(ag.dynamics_model, "current_turning_rate"):
+        ag.dynamics_model.current_turning_rate = np.float64(s[L.TURNING_DIR])
+        ag.dynamics_model.current_speed = np.float64(s[L.SPEED])
+    if type(ag.dynamics_model).__name__ == "UnicycleSecondOrderEulerDynamics":
+        ag.angular_speed_global_frame = np.float64(s[L.TURNING_DIR])
     ag.goal_global_frame = np.array([s[L.GX], s[L.GY]], dtype=np.float64)
     ag.radius = float(s[L.RADIUS])
     ag.pref_speed = float(s[L.PREF_SPEED])
@@ -134,6 +144,11 @@ def extract_state(ag, type_word):
     s[L.VX], s[L.VY] = ag.vel_global_frame
     s[L.DELTA_HEADING] = ag.delta_heading_global_frame
     s[L.TURNING_DIR] = ag.turning_dir
+    if hasattr(ag.dynamics_model, "current_turning_rate"):
+        s[L.TURNING_DIR] = ag.dynamics_model.current_turning_rate
+        assert ag.dynamics_model.current_speed == ag.speed_global_frame
+    if type(ag.dynamics_model).__name__ == "UnicycleSecondOrderEulerDynamics":
+        s[L.TURNING_DIR] = ag.angular_speed_global_frame
     s[L.GX], s[L.GY] = ag.goal_global_frame
     s[L.RADIUS] = ag.radius
     s[L.PREF_SPEED] = ag.pref_speed
@@ -224,6 +239,9 @@ class Recorder:
         return dict(self.__dict__)
 
 
+DYN_CHOICES = [L.DYN_UNICYCLE, L.DYN_UNICYCLE, L.DYN_FIRST_ORDER, L.DYN_UNICYCLE_MAX_TURN_RATE]
+
+
 def random_case(rng, sensors_mode):
     """One random mid-episode environment.  Returns init, types, state_in, ext, traj, n, map_id."""
     n = int(rng.integers(2, A_MAX + 1))
@@ -241,7 +259,7 @@ def random_case(rng, sensors_mode):
         if pol == L.POLICY_PEDESTRIAN:
             dyn = L.DYN_EXTERNAL
         else:
-            dyn = int(rng.choice([L.DYN_UNICYCLE, L.DYN_UNICYCLE, L.DYN_FIRST_ORDER, L.DYN_UNICYCLE_MAX_TURN_RATE]))
+            dyn = int(rng.choice(DYN_CHOICES))
         if sensors_mode:
             mask = int(rng.choice([1, 3, 5, 7, 2, 4, 0]))
         else:
@@ -521,6 +539,14 @@ def main():
         gen_single_step(ns, "core_single_step.npz", 300, 11, sensors_mode=False)
     if what in ("sensors", "all"):
         gen_single_step(ns, "sensors_single_step.npz", 120, 12, sensors_mode=True)
+    if what in ("dynamics", "all"):
+        # the two remaining dynamics models, in their own fixture so that the older ones keep
+        # their random streams
+        global DYN_CHOICES
+        keep = DYN_CHOICES
+        DYN_CHOICES = [L.DYN_UNICYCLE_MAX_ACC, L.DYN_UNICYCLE_SECOND_ORDER_EULER, L.DYN_UNICYCLE]
+        gen_single_step(ns, "dynamics_extra_single_step.npz", 160, 13, sensors_mode=False)
+        DYN_CHOICES = keep
     if what in ("reset", "all"):
         gen_reset(ns)
     if what in ("maps", "all"):

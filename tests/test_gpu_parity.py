@@ -41,7 +41,7 @@ def test_library_loaded_and_default_config_matches_oracle(oracle_lib, torch_mod)
     assert bytes(a) == bytes(b)
 
 
-@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz"])
+@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz", "dynamics_extra_single_step.npz"])
 def test_golden_single_step(oracle_lib, torch_mod, name):
     """Every golden case (reference outputs) through casim_step, grouped by (game-over mode, map)."""
     torch = torch_mod

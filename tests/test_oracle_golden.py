@@ -25,7 +25,7 @@ def run_single_step(oracle, z, k, maps):
     return n, state, obs
 
 
-@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz"])
+@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz", "dynamics_extra_single_step.npz"])
 def test_single_step_vs_reference(oracle_lib, name):
     oracle = oracle_lib
     z = H.load(name)
