@@ -111,6 +111,12 @@ class BatchedCollisionAvoidanceEnv:
     def set_trajectories(self, traj):
         self._traj = traj
 
+    def initialize_network(self, checkpoints_root, **kwargs):
+        """GA3CCADRLPolicy.initialize_network (GA3CCADRLPolicy.py:21-32): load a shipped TF1 checkpoint
+        (kwargs checkpt_dir, checkpt_name as in the reference; checkpoints_root = .../GA3C_CADRL/checkpoints)."""
+        from .ga3c_checkpoint import checkpoint_prefix, ga3c_weights_from_checkpoint
+        self.set_ga3c_weights(ga3c_weights_from_checkpoint(checkpoint_prefix(checkpoints_root, **kwargs)))
+
     def set_ga3c_weights(self, weights):
         """float32 [170764] parameter blob (GA3CCADRLPolicy.initialize_network's counterpart)"""
         self._ga3c_weights = np.asarray(weights, np.float32)

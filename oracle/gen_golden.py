@@ -558,6 +558,7 @@ def main():
     if what in ("ga3c", "all"):
         from oracle import gen_golden_ga3c
         gen_golden_ga3c.main(ns)
+        gen_golden_ga3c.gen_checkpoint_fixture()
     if what in ("flatten", "all"):
         gen_flatten(ns)
     if what in ("rvo", "all"):

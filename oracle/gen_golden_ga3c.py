@@ -73,3 +73,18 @@ def main(ns, ncases=160, seed=4242):
     np.savez_compressed(os.path.join(GOLDEN, "ga3c_state.npz"), state=states, n_agents=n_agents, max_obs=max_obs,
                         nn_input=nn_input)
     print("wrote ga3c_state.npz: %d cases, up to %d agents" % (ncases, A))
+
+
+def gen_checkpoint_fixture():
+    """tests/golden/ga3c_iros18.npz: the 170 764 trained parameters of the reference's default checkpoint
+    (GA3C_CADRL/checkpoints/IROS18/network_01900000, GA3CCADRLPolicy.py:24-30) read by casim.ga3c_checkpoint, plus
+    per-variable float64 sums as known answers for the reader."""
+    from oracle import ref_harness as rh
+    from casim.ga3c_checkpoint import GA3C_VARIABLES, ga3c_weights_from_checkpoint, read_checkpoint
+    prefix = os.path.join(rh.REFERENCE_ROOT, "gym_collision_avoidance", "envs", "policies", "GA3C_CADRL", "checkpoints",
+                          "IROS18", "network_01900000")
+    w = ga3c_weights_from_checkpoint(prefix)
+    t = read_checkpoint(prefix)
+    sums = np.array([t[name].astype(np.float64).sum() for name, _ in GA3C_VARIABLES])
+    np.savez_compressed(os.path.join(GOLDEN, "ga3c_iros18.npz"), weights=w, sums=sums, step=t["step:0"])
+    print("wrote ga3c_iros18.npz", w.shape, int(t["step:0"]))

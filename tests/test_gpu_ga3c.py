@@ -46,8 +46,10 @@ def test_ga3c_state_vector_golden(oracle_lib):
         sim.close()
 
 
-@pytest.mark.parametrize("use_tc", [False, True])
-def test_ga3c_forward_vs_oracle(oracle_lib, use_tc):
+@pytest.mark.parametrize("use_tc,trained", [(False, False), (True, False), (False, True), (True, True)])
+def test_ga3c_forward_vs_oracle(oracle_lib, use_tc, trained):
+    """trained = the reference's shipped IROS18 checkpoint (tests/golden/ga3c_iros18.npz, read from the TF1 bundle by
+    casim.ga3c_checkpoint) instead of random-init weights."""
     import torch
     from casim import scenarios as S
     from casim.sim import BatchedSim
@@ -58,11 +60,11 @@ def test_ga3c_forward_vs_oracle(oracle_lib, use_tc):
     n[::7] = 13                  # ragged environments
     n[3] = 1                     # a lone agent: empty sequence
     cfg = _cfg(near_goal_threshold=0.2)
-    w = oracle.ga3c_random_weights(1)
+    w = H.load("ga3c_iros18.npz")["weights"] if trained else oracle.ga3c_random_weights(1)
     sim = BatchedSim(E, A, cfg=cfg, sensors=("other_agents_states",))
     sim.reset(init, types, n)
     sim.ga3c_set_weights(w)
-    tol_p = 2e-2 if use_tc else 2e-5
+    tol_p = (6e-2 if trained else 2e-2) if use_tc else 2e-5
     agree = total = 0
     for t in range(6):
         state = sim.state_numpy()
@@ -88,5 +90,5 @@ def test_ga3c_forward_vs_oracle(oracle_lib, use_tc):
             m = same
             H.assert_close(ga[e, :k][act][m], o["policy_actions"][e, :k][act][m], "action t=%d env %d" % (t, e), rtol=1e-6, atol=1e-7)
         sim.step(policy_actions=sim.buf["policy_actions"])
-    assert total > 5000 and agree / total > (0.97 if use_tc else 0.999)
+    assert total > 5000 and agree / total > ((0.93 if trained else 0.97) if use_tc else 0.999)
     sim.close()

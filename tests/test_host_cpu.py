@@ -97,3 +97,86 @@ def test_stats_all_reduce_world2_gloo():
         assert total == expect and tmax == 2.0
     blocks = sorted(r[3] for r in res)
     assert blocks == [(0, 5), (5, 11)]
+
+
+# ---------------------------------------------------------------------------------------------
+# GA3C-CADRL checkpoint reader
+def _write_bundle(prefix, tensors):
+    """A minimal tensor-bundle writer (one data block, no compression) to exercise the reader without TensorFlow."""
+    import struct
+
+    def varint(v):
+        out = bytearray()
+        while True:
+            b = v & 0x7f
+            v >>= 7
+            out.append(b | (0x80 if v else 0))
+            if not v:
+                return bytes(out)
+
+    def block(entries):
+        body, prev = bytearray(), b""
+        for k, v in entries:            # prefix compression against the previous key (restart only at entry 0)
+            shared = 0
+            while shared < min(len(prev), len(k)) and prev[shared] == k[shared]:
+                shared += 1
+            body += varint(shared) + varint(len(k) - shared) + varint(len(v)) + k[shared:] + v
+            prev = k
+        body += struct.pack("<I", 0) + struct.pack("<I", 1)
+        return bytes(body)
+
+    data, entries = bytearray(), [(b"", b"\x08\x01")]
+    for name in sorted(tensors):
+        t = np.asarray(tensors[name])          # (ascontiguousarray would turn a scalar into shape (1,))
+        dt = {np.dtype(np.float32): 1, np.dtype(np.int32): 3}[t.dtype]
+        shape = b"".join(b"\x12" + varint(len(d)) + d for d in [b"\x08" + varint(s) for s in t.shape])
+        e = b"\x08" + varint(dt) + b"\x12" + varint(len(shape)) + shape + b"\x20" + varint(len(data)) + b"\x28" + varint(t.nbytes)
+        entries.append((name.encode(), e))
+        data += t.tobytes()
+    blk = block(entries)
+    out = bytearray(blk) + b"\x00" + b"\x00" * 4                      # block + compression tag + crc (unchecked)
+    meta_off = len(out)
+    meta = block([])
+    out += meta + b"\x00" + b"\x00" * 4
+    idx_off = len(out)
+    idx = block([(b"~", varint(0) + varint(len(blk)))])
+    out += idx + b"\x00" + b"\x00" * 4
+    footer = varint(meta_off) + varint(len(meta)) + varint(idx_off) + varint(len(idx))
+    out += footer + b"\x00" * (40 - len(footer)) + struct.pack("<Q", 0xdb4775248b80fb57)
+    open(prefix + ".index", "wb").write(bytes(out))
+    open(prefix + ".data-00000-of-00001", "wb").write(bytes(data))
+
+
+def test_checkpoint_reader_roundtrip(tmp_path):
+    from casim.ga3c_checkpoint import GA3C_VARIABLES, ga3c_weights_from_checkpoint, read_checkpoint
+    rng = np.random.default_rng(0)
+    tensors = {name: rng.standard_normal(shape).astype(np.float32) for name, shape in GA3C_VARIABLES}
+    tensors["step:0"] = np.array(7, np.int32)
+    tensors["layer1/kernel/Adam:0"] = rng.standard_normal((68, 256)).astype(np.float32)      # optimiser slots are ignored
+    prefix = str(tmp_path / "network_00000007")
+    _write_bundle(prefix, tensors)
+    got = read_checkpoint(prefix)
+    assert set(got) == set(tensors)
+    for k in tensors:
+        assert np.array_equal(got[k], tensors[k]), k
+    w = ga3c_weights_from_checkpoint(prefix)
+    assert w.shape == (170764,) and np.array_equal(w[:71 * 256], tensors["rnn/lstm_cell/kernel:0"].ravel())
+    assert np.array_equal(w[-257:-1], tensors["logits_v/kernel:0"].ravel())
+
+
+def test_checkpoint_reader_on_reference_checkpoint():
+    """The shipped IROS18 checkpoint (only where /root/reference exists) against tests/golden/ga3c_iros18.npz."""
+    import os
+    import helpers as H
+    from casim.ga3c_checkpoint import GA3C_VARIABLES, checkpoint_prefix, ga3c_weights_from_checkpoint, read_checkpoint
+    root = "/root/reference/gym_collision_avoidance/envs/policies/GA3C_CADRL/checkpoints"
+    z = H.load("ga3c_iros18.npz")
+    assert z["weights"].shape == (170764,) and np.isfinite(z["weights"]).all()
+    if not os.path.isdir(root):
+        pytest.skip("reference checkpoints not present on this machine")
+    prefix = checkpoint_prefix(root)                       # defaults of GA3CCADRLPolicy.initialize_network
+    assert np.array_equal(ga3c_weights_from_checkpoint(prefix), z["weights"])
+    t = read_checkpoint(prefix)
+    np.testing.assert_allclose([t[n].astype(np.float64).sum() for n, _ in GA3C_VARIABLES], z["sums"], rtol=0, atol=0)
+    for d, name in (("ICRA21", "network_01990000"), ("run-20190727_192048-qedrf08y", "network_01900000")):
+        assert ga3c_weights_from_checkpoint(checkpoint_prefix(root, d, name)).shape == (170764,)
