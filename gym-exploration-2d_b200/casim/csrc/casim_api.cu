@@ -216,6 +216,7 @@ int casim_destroy(casim_handle* h) {
   cudaFree(h->pose64);
   cudaFree(h->prev_game_over);
   cudaFree(h->state0);
+  casim_rvo_obstacles_free(h);
   cudaFree(h->partials);
   cudaFree(h->ticket);
   cudaFree(h->map_planes);
@@ -495,10 +496,24 @@ void casim_rvo_default_params(casim_rvo_params* p) {
   p->max_neighbors = 10;            /* Config.MAX_NUM_AGENTS_IN_ENVIRONMENT, config.py:70 */
 }
 
+int casim_rvo_set_obstacles(casim_handle* h, const double* vertices, const int32_t* poly_sizes, int n_polys) {
+  REQUIRE(h, "null argument");
+  casim_rvo_obstacles_free(h);
+  if (n_polys <= 0) return 0;
+  REQUIRE(vertices && poly_sizes, "null argument");
+  CK(cudaDeviceSynchronize()); /* the previous set may still be read by a kernel in flight */
+  int rc = casim_rvo_obstacles_build(h, vertices, poly_sizes, n_polys);
+  REQUIRE(rc != -1, "casim_rvo_set_obstacles: a polygon needs at least 2 vertices");
+  REQUIRE(rc != -2, "casim_rvo_set_obstacles: more than 64 obstacle vertices after edge splitting");
+  REQUIRE(rc == 0, "casim_rvo_set_obstacles: CUDA allocation / upload failed");
+  return 0;
+}
+
 int casim_rvo_step(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* params,
                    float* policy_actions, void* stream) {
   REQUIRE(h && state && policy_actions, "null argument");
-  REQUIRE(h->n_maps == 0, "casim_rvo_step: obstacle ORCA lines (Agent.cpp:66-284) are not implemented; the handle has a static map");
+  REQUIRE(h->n_maps == 0 || h->rvo_n > 0,
+          "casim_rvo_step: the handle has a static map but no RVO obstacle polygons; call casim_rvo_set_obstacles");
   casim_rvo_params def;
   if (!params) {
     casim_rvo_default_params(&def);

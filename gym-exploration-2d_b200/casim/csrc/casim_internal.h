@@ -81,6 +81,11 @@ struct casim_handle {
   void* ga3c_wb;           /* bf16 tiles for the tensor-core path */
   float* ga3c_x;           /* [E*A][76] network input scratch */
   void* ga3c_xb;           /* [tiles][10][128] x 16 B: bf16 LSTM input chunks for the tensor-core path */
+  /* RVO obstacle set (casim_rvo_set_obstacles): processed vertices + obstacle tree, see casim_rvo.cu */
+  float2 *rvo_point, *rvo_unitdir;
+  int *rvo_next, *rvo_prev, *rvo_convex;
+  int4* rvo_node;
+  int rvo_n, rvo_root;
   float* ext_copy_dst;     /* set by casim_step_host around its casim_step call (see CoreArgs::ext_copy_dst) */
   unsigned long long launches;
 };
@@ -103,6 +108,8 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
                               float* probs, float* nn_input, int use_tc, cudaStream_t s);
 cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* prm,
                              float* policy_actions, cudaStream_t s);
+int casim_rvo_obstacles_build(casim_handle* h, const double* verts, const int32_t* poly_sizes, int n_polys);
+void casim_rvo_obstacles_free(casim_handle* h);
 cudaError_t casim_launch_flatten(casim_handle* h, const float* state, const casim_obs* obs, const int32_t* keys,
                                  int n_keys, float* out, cudaStream_t s);
 int casim_flat_row_size_impl(const casim_handle* h, const int32_t* keys, int n_keys);

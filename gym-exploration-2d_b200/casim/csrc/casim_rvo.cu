@@ -15,7 +15,9 @@
  * order (the library is built with -fmad=false, IEEE division and square root), so the new position is bit-identical
  * to the C++ library; the host-side arithmetic of RVOPolicy.py around it (preferred velocity, heading change, the
  * pi/6 turn limit that zeroes the speed) is fp64 like the reference.
- * Not covered: obstacle ORCA lines (Agent.cpp:66-284) -- casim_rvo_step refuses a handle that has a static map.
+ * Static obstacles: addObstacle + buildObstacleTree (RVOSimulator.cpp:124-161, KdTree.cpp:113-245) run on the host in
+ * casim_rvo_set_obstacles; k_rvo<true> queries the tree (KdTree.cpp:300-329) and emits the obstacle ORCA lines
+ * (Agent.cpp:66-284).
  * Neighbour ties at exactly equal squared distance are broken by agent index (reference: k-d tree visiting order).
  *
  * Mapping note (measured on B200, C2-shaped all-RVO batch of 40 960 agents): one thread per agent takes 22.8 us;
@@ -26,6 +28,10 @@
  * Bound: latency / fp32 issue (a few hundred dependent flops per neighbour, data-dependent linear programs); the
  * HBM traffic is 48 B read + 8 B written per agent (neighbour reads hit L1/L2 within the environment).
  */
+#include <algorithm>
+#include <utility>
+#include <vector>
+
 #include "casim_device.cuh"
 
 namespace {
@@ -33,7 +39,21 @@ namespace {
 #define RVO_EPS 0.00001f
 #define RVO_MAXN CASIM_MAX_AGENTS
 
+#define RVO_MAX_OBST 64 /* obstacle vertices after edge splitting (the crossing map has 16) */
+
+struct RvoObst { /* device image of the processed obstacle set, struct of arrays */
+  const float2* point;   /* Obstacle::point_ */
+  const float2* unitDir; /* Obstacle::unitDir_ */
+  const int* next;       /* nextObstacle_ */
+  const int* prev;       /* prevObstacle_ */
+  const int* convex;     /* isConvex_ */
+  const int4* node;      /* obstacle tree: (obstacle, left, right, -) */
+  int n, root;
+};
+
 struct RvoArgs {
+  RvoObst ob;
+  float time_horizon_obst;
   const float4* state; /* [6][E*A] */
   const float* coop;   /* [E*A] Agent.cooperation_coef or NULL (= 1.0, agent.py:10) */
   const int32_t* n_agents;
@@ -62,6 +82,7 @@ __device__ __forceinline__ float det(float2 a, float2 b) { return a.x * b.y - a.
 __device__ __forceinline__ float absSq(float2 a) { return dot(a, a); }
 __device__ __forceinline__ float2 normalize(float2 a) { return divs(a, sqrtf(dot(a, a))); }
 __device__ __forceinline__ float sqr(float a) { return a * a; }
+__device__ __forceinline__ float leftOf(float2 a, float2 b, float2 c) { return det(sub(a, c), sub(b, a)); } /* Definitions.h:93 */
 
 /* Agent.cpp:477-546 */
 __device__ bool lp1(const Line* lines, int lineNo, float radius, float2 opt, bool dirOpt, float2& result) {
@@ -123,13 +144,14 @@ __device__ int lp2(const Line* lines, int nl, float radius, float2 opt, bool dir
   return nl;
 }
 
-/* Agent.cpp:580-630 with numObstLines = 0 */
-__device__ void lp3(const Line* lines, int nl, int beginLine, float radius, float2& result, Line* proj) {
+/* Agent.cpp:580-630 */
+__device__ void lp3(const Line* lines, int nl, int numObst, int beginLine, float radius, float2& result, Line* proj) {
   float distance = 0.0f;
   for (int i = beginLine; i < nl; i++) {
     if (det(lines[i].direction, sub(lines[i].point, result)) > distance) {
       int np = 0;
-      for (int j = 0; j < i; j++) {
+      for (int j = 0; j < numObst; j++) proj[np++] = lines[j];
+      for (int j = numObst; j < i; j++) {
         Line l;
         const float determinant = det(lines[i].direction, lines[j].direction);
         if (fabsf(determinant) <= RVO_EPS) {
@@ -149,8 +171,188 @@ __device__ void lp3(const Line* lines, int nl, int beginLine, float radius, floa
   }
 }
 
+/* Definitions.h:68-82 */
+__device__ __forceinline__ float distSqPointLineSegment(float2 a, float2 b, float2 c) {
+  const float r = dot(sub(c, a), sub(b, a)) / absSq(sub(b, a));
+  if (r < 0.0f) return absSq(sub(c, a));
+  if (r > 1.0f) return absSq(sub(c, b));
+  return absSq(sub(c, add(a, mulsv(r, sub(b, a)))));
+}
+
+/* KdTree::queryObstacleTreeRecursive (KdTree.cpp:300-329) with an explicit stack + Agent::insertObstacleNeighbor
+ * (Agent.cpp:475-493): obstacle edges within rangeSq that the agent sees from their right side, ascending distance. */
+__device__ int obstacle_neighbors(const RvoObst& O, float2 position, float rangeSq, float* nd, int* no) {
+  int nn = 0;
+  int stack[2 * RVO_MAX_OBST + 2]; /* node << 1 | stage */
+  int sp = 0;
+  if (O.root >= 0) stack[sp++] = O.root << 1;
+  while (sp > 0) {
+    const int en = stack[--sp];
+    const int4 nd4 = O.node[en >> 1];
+    const int o1 = nd4.x, o2 = O.next[o1];
+    const float2 p1 = O.point[o1], p2 = O.point[o2];
+    const float agentLeftOfLine = leftOf(p1, p2, position);
+    const int first = agentLeftOfLine >= 0.0f ? nd4.y : nd4.z, second = agentLeftOfLine >= 0.0f ? nd4.z : nd4.y;
+    if ((en & 1) == 0) { /* descend into the agent's side first, come back to this node afterwards */
+      stack[sp++] = en | 1;
+      if (first >= 0) stack[sp++] = first << 1;
+    } else {
+      const float distSqLine = sqr(agentLeftOfLine) / absSq(sub(p2, p1));
+      if (distSqLine < rangeSq) {
+        if (agentLeftOfLine < 0.0f) {
+          const float distSq = distSqPointLineSegment(p1, p2, position);
+          if (distSq < rangeSq && nn < RVO_MAX_OBST) {
+            int i = nn++;
+            while (i != 0 && distSq < nd[i - 1]) {
+              nd[i] = nd[i - 1];
+              no[i] = no[i - 1];
+              --i;
+            }
+            nd[i] = distSq;
+            no[i] = o1;
+          }
+        }
+        if (second >= 0) stack[sp++] = second << 1;
+      }
+    }
+  }
+  return nn;
+}
+
+/* Agent.cpp:66-284: ORCA lines of the obstacle neighbours */
+__device__ int obstacle_lines(const RvoObst& O, const int* no, int nn, float2 position_, float2 velocity_, float radius_,
+                              float timeHorizonObst_, Line* lines) {
+  int nl = 0;
+  const float invTimeHorizonObst = 1.0f / timeHorizonObst_;
+  for (int i = 0; i < nn; i++) {
+    int obstacle1 = no[i];
+    int obstacle2 = O.next[obstacle1];
+    const float2 P1 = O.point[obstacle1], P2 = O.point[obstacle2];
+    const float2 relativePosition1 = sub(P1, position_);
+    const float2 relativePosition2 = sub(P2, position_);
+    bool alreadyCovered = false;
+    for (int j = 0; j < nl; j++) {
+      if (det(sub(mulsv(invTimeHorizonObst, relativePosition1), lines[j].point), lines[j].direction) - invTimeHorizonObst * radius_ >= -RVO_EPS &&
+          det(sub(mulsv(invTimeHorizonObst, relativePosition2), lines[j].point), lines[j].direction) - invTimeHorizonObst * radius_ >= -RVO_EPS) {
+        alreadyCovered = true;
+        break;
+      }
+    }
+    if (alreadyCovered) continue;
+    const float distSq1 = absSq(relativePosition1);
+    const float distSq2 = absSq(relativePosition2);
+    const float radiusSq = sqr(radius_);
+    const float2 obstacleVector = sub(P2, P1);
+    const float s = dot(neg(relativePosition1), obstacleVector) / absSq(obstacleVector);
+    const float distSqLine = absSq(sub(neg(relativePosition1), mulsv(s, obstacleVector)));
+    const float2 unitDir1 = O.unitDir[obstacle1], unitDir2o = O.unitDir[obstacle2];
+    const bool convex1 = O.convex[obstacle1] != 0, convex2o = O.convex[obstacle2] != 0;
+    Line line;
+    if (s < 0.0f && distSq1 <= radiusSq) {
+      if (convex1) {
+        line.point = V(0.0f, 0.0f);
+        line.direction = normalize(V(-relativePosition1.y, relativePosition1.x));
+        lines[nl++] = line;
+      }
+      continue;
+    } else if (s > 1.0f && distSq2 <= radiusSq) {
+      if (convex2o && det(relativePosition2, unitDir2o) >= 0.0f) {
+        line.point = V(0.0f, 0.0f);
+        line.direction = normalize(V(-relativePosition2.y, relativePosition2.x));
+        lines[nl++] = line;
+      }
+      continue;
+    } else if (s >= 0.0f && s < 1.0f && distSqLine <= radiusSq) {
+      line.point = V(0.0f, 0.0f);
+      line.direction = neg(unitDir1);
+      lines[nl++] = line;
+      continue;
+    }
+    float2 leftLegDirection, rightLegDirection;
+    if (s < 0.0f && distSqLine <= radiusSq) {
+      if (!convex1) continue;
+      obstacle2 = obstacle1;
+      const float leg1 = sqrtf(distSq1 - radiusSq);
+      leftLegDirection = divs(V(relativePosition1.x * leg1 - relativePosition1.y * radius_, relativePosition1.x * radius_ + relativePosition1.y * leg1), distSq1);
+      rightLegDirection = divs(V(relativePosition1.x * leg1 + relativePosition1.y * radius_, -relativePosition1.x * radius_ + relativePosition1.y * leg1), distSq1);
+    } else if (s > 1.0f && distSqLine <= radiusSq) {
+      if (!convex2o) continue;
+      obstacle1 = obstacle2;
+      const float leg2 = sqrtf(distSq2 - radiusSq);
+      leftLegDirection = divs(V(relativePosition2.x * leg2 - relativePosition2.y * radius_, relativePosition2.x * radius_ + relativePosition2.y * leg2), distSq2);
+      rightLegDirection = divs(V(relativePosition2.x * leg2 + relativePosition2.y * radius_, -relativePosition2.x * radius_ + relativePosition2.y * leg2), distSq2);
+    } else {
+      if (convex1) {
+        const float leg1 = sqrtf(distSq1 - radiusSq);
+        leftLegDirection = divs(V(relativePosition1.x * leg1 - relativePosition1.y * radius_, relativePosition1.x * radius_ + relativePosition1.y * leg1), distSq1);
+      } else {
+        leftLegDirection = neg(unitDir1);
+      }
+      if (convex2o) {
+        const float leg2 = sqrtf(distSq2 - radiusSq);
+        rightLegDirection = divs(V(relativePosition2.x * leg2 + relativePosition2.y * radius_, -relativePosition2.x * radius_ + relativePosition2.y * leg2), distSq2);
+      } else {
+        rightLegDirection = unitDir1;
+      }
+    }
+    /* obstacle1 / obstacle2 may have been merged above: re-read their attributes */
+    const float2 uD1 = O.unitDir[obstacle1], uD2 = O.unitDir[obstacle2];
+    const bool cv1 = O.convex[obstacle1] != 0, cv2 = O.convex[obstacle2] != 0;
+    const float2 uLeftNb = O.unitDir[O.prev[obstacle1]];
+    bool isLeftLegForeign = false, isRightLegForeign = false;
+    if (cv1 && det(leftLegDirection, neg(uLeftNb)) >= 0.0f) {
+      leftLegDirection = neg(uLeftNb);
+      isLeftLegForeign = true;
+    }
+    if (cv2 && det(rightLegDirection, uD2) <= 0.0f) {
+      rightLegDirection = uD2;
+      isRightLegForeign = true;
+    }
+    const float2 leftCutoff = mulsv(invTimeHorizonObst, sub(O.point[obstacle1], position_));
+    const float2 rightCutoff = mulsv(invTimeHorizonObst, sub(O.point[obstacle2], position_));
+    const float2 cutoffVec = sub(rightCutoff, leftCutoff);
+    const bool same = obstacle1 == obstacle2;
+    const float t = same ? 0.5f : dot(sub(velocity_, leftCutoff), cutoffVec) / absSq(cutoffVec);
+    const float tLeft = dot(sub(velocity_, leftCutoff), leftLegDirection);
+    const float tRight = dot(sub(velocity_, rightCutoff), rightLegDirection);
+    if ((t < 0.0f && tLeft < 0.0f) || (same && tLeft < 0.0f && tRight < 0.0f)) {
+      const float2 unitW = normalize(sub(velocity_, leftCutoff));
+      line.direction = V(unitW.y, -unitW.x);
+      line.point = add(leftCutoff, mulsv(radius_ * invTimeHorizonObst, unitW));
+      lines[nl++] = line;
+      continue;
+    } else if (t > 1.0f && tRight < 0.0f) {
+      const float2 unitW = normalize(sub(velocity_, rightCutoff));
+      line.direction = V(unitW.y, -unitW.x);
+      line.point = add(rightCutoff, mulsv(radius_ * invTimeHorizonObst, unitW));
+      lines[nl++] = line;
+      continue;
+    }
+    const float distSqCutoff = (t < 0.0f || t > 1.0f || same) ? INFINITY : absSq(sub(velocity_, add(leftCutoff, mulsv(t, cutoffVec))));
+    const float distSqLeft = tLeft < 0.0f ? INFINITY : absSq(sub(velocity_, add(leftCutoff, mulsv(tLeft, leftLegDirection))));
+    const float distSqRight = tRight < 0.0f ? INFINITY : absSq(sub(velocity_, add(rightCutoff, mulsv(tRight, rightLegDirection))));
+    if (distSqCutoff <= distSqLeft && distSqCutoff <= distSqRight) {
+      line.direction = neg(uD1);
+      line.point = add(leftCutoff, mulsv(radius_ * invTimeHorizonObst, V(-line.direction.y, line.direction.x)));
+      lines[nl++] = line;
+    } else if (distSqLeft <= distSqRight) {
+      if (isLeftLegForeign) continue;
+      line.direction = leftLegDirection;
+      line.point = add(leftCutoff, mulsv(radius_ * invTimeHorizonObst, V(-line.direction.y, line.direction.x)));
+      lines[nl++] = line;
+    } else {
+      if (isRightLegForeign) continue;
+      line.direction = neg(rightLegDirection);
+      line.point = add(rightCutoff, mulsv(radius_ * invTimeHorizonObst, V(-line.direction.y, line.direction.x)));
+      lines[nl++] = line;
+    }
+  }
+  return nl;
+}
+
 #define RVO_THREADS 128
 
+template <bool OBST>
 __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
   casim_pdl_enter();
   const size_t N = (size_t)p.E * p.A;
@@ -204,8 +406,16 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
     }
   }
 
-  Line lines[RVO_MAXN + 2], proj[RVO_MAXN + 2];
+  constexpr int NOB = OBST ? RVO_MAX_OBST : 0;
+  Line lines[NOB + RVO_MAXN + 2], proj[NOB + RVO_MAXN + 2];
   int nl = 0;
+  if (OBST) { /* Agent.cpp:45-47 (obstacle neighbours) + 66-284 (their ORCA lines come first) */
+    float od[RVO_MAX_OBST];
+    int oo[RVO_MAX_OBST];
+    const int on = obstacle_neighbors(p.ob, position, sqr(p.time_horizon_obst * maxSpeed + radius_), od, oo);
+    nl = obstacle_lines(p.ob, oo, on, position, velocity, radius_, p.time_horizon_obst, lines);
+  }
+  const int numObstLines = nl;
   const float invTimeHorizon = 1.0f / p.time_horizon;
   if (collab == 0.0f) {
     /* Agent.cpp:290-292 */
@@ -283,7 +493,7 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
   }
   float2 newVel = V(0.f, 0.f);
   const int lineFail = lp2(lines, nl, maxSpeed, prefVel, false, newVel);
-  if (lineFail < nl) lp3(lines, nl, lineFail, maxSpeed, newVel, proj);
+  if (lineFail < nl) lp3(lines, nl, numObstLines, lineFail, maxSpeed, newVel, proj);
   const float2 newPos = add(position, mulvs(newVel, p.time_step)); /* Agent.cpp:516-521 */
 
   /* RVOPolicy.py:91-110 (fp64) */
@@ -302,9 +512,163 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
 
 }  // namespace
 
+/* ---- host side: RVOSimulator::addObstacle (RVOSimulator.cpp:124-161) + KdTree::buildObstacleTree (KdTree.cpp:113-245),
+ * run once per casim_rvo_set_obstacles; the processed set is uploaded as flat arrays ---- */
+namespace {
+
+struct HostObstacles {
+  std::vector<float2> point, unitDir;
+  std::vector<int> next, prev, convex;
+  std::vector<int4> node;
+
+  static float2 hsub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+  static float hdet(float2 a, float2 b) { return a.x * b.y - a.y * b.x; }
+  static float hleft(float2 a, float2 b, float2 c) { return hdet(hsub(a, c), hsub(b, a)); }
+  static float2 hnorm(float2 a) {
+    const float inv = 1.0f / sqrtf(a.x * a.x + a.y * a.y);
+    return make_float2(a.x * inv, a.y * inv);
+  }
+
+  void add_polygon(const std::vector<float2>& v) {
+    const int nv = (int)v.size(), first = (int)point.size();
+    for (int i = 0; i < nv; i++) {
+      const int k = first + i;
+      point.push_back(v[i]);
+      unitDir.push_back(hnorm(hsub(v[(i + 1) % nv], v[i])));
+      next.push_back(i == nv - 1 ? first : k + 1);
+      prev.push_back(i == 0 ? first + nv - 1 : k - 1);
+      convex.push_back(nv == 2 ? 1 : (hleft(v[(i + nv - 1) % nv], v[i], v[(i + 1) % nv]) >= 0.0f ? 1 : 0));
+    }
+  }
+
+  /* side of edge j relative to the line through edge i: +1 left, -1 right, 0 straddles */
+  int side(int i1, int j1, float& j1Left) const {
+    const int i2 = next[i1], j2 = next[j1];
+    j1Left = hleft(point[i1], point[i2], point[j1]);
+    const float j2Left = hleft(point[i1], point[i2], point[j2]);
+    if (j1Left >= -RVO_EPS && j2Left >= -RVO_EPS) return 1;
+    if (j1Left <= RVO_EPS && j2Left <= RVO_EPS) return -1;
+    return 0;
+  }
+
+  int build(const std::vector<int>& list) {
+    if (list.empty()) return -1;
+    const size_t cnt = list.size();
+    /* the split edge minimises (max(left, right), min(left, right)) lexicographically; first best wins */
+    size_t best = 0, bestL = cnt, bestR = cnt;
+    for (size_t i = 0; i < cnt; i++) {
+      size_t l = 0, r = 0;
+      const std::pair<size_t, size_t> bound(std::max(bestL, bestR), std::min(bestL, bestR));
+      for (size_t j = 0; j < cnt; j++) {
+        if (i == j) continue;
+        float dummy;
+        const int sd = side(list[i], list[j], dummy);
+        if (sd >= 0) ++l;
+        if (sd <= 0) ++r;
+        if (std::make_pair(std::max(l, r), std::min(l, r)) >= bound) break;
+      }
+      if (std::make_pair(std::max(l, r), std::min(l, r)) < bound) {
+        best = i;
+        bestL = l;
+        bestR = r;
+      }
+    }
+    std::vector<int> L, R;
+    const int i1 = list[best];
+    for (size_t j = 0; j < cnt; j++) {
+      if (j == best) continue;
+      const int j1 = list[j];
+      float j1Left;
+      const int sd = side(i1, j1, j1Left);
+      if (sd > 0) L.push_back(j1);
+      else if (sd < 0) R.push_back(j1);
+      else { /* edge j crosses the line: a new vertex splits it */
+        const int i2 = next[i1], j2 = next[j1];
+        const float t = hdet(hsub(point[i2], point[i1]), hsub(point[j1], point[i1])) /
+                        hdet(hsub(point[i2], point[i1]), hsub(point[j1], point[j2]));
+        const float2 d = hsub(point[j2], point[j1]);
+        const int nw = (int)point.size();
+        point.push_back(make_float2(point[j1].x + t * d.x, point[j1].y + t * d.y));
+        unitDir.push_back(unitDir[j1]);
+        prev.push_back(j1);
+        next.push_back(j2);
+        convex.push_back(1);
+        next[j1] = nw;
+        prev[j2] = nw;
+        if (j1Left > 0.0f) { L.push_back(j1); R.push_back(nw); }
+        else { R.push_back(j1); L.push_back(nw); }
+      }
+    }
+    const int me = (int)node.size();
+    node.push_back(make_int4(i1, -1, -1, 0));
+    const int l = build(L);
+    const int r = build(R);
+    node[me].y = l;
+    node[me].z = r;
+    return me;
+  }
+};
+
+template <typename T>
+cudaError_t upload(T** dst, const std::vector<T>& v) {
+  cudaFree(*dst);
+  *dst = nullptr;
+  if (v.empty()) return cudaSuccess;
+  cudaError_t e = cudaMalloc((void**)dst, v.size() * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*dst, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+}  // namespace
+
+int casim_rvo_obstacles_build(casim_handle* h, const double* verts, const int32_t* poly_sizes, int n_polys) {
+  HostObstacles H;
+  int off = 0;
+  for (int p = 0; p < n_polys; p++) {
+    if (poly_sizes[p] < 2) return -1;
+    std::vector<float2> v;
+    for (int k = 0; k < poly_sizes[p]; k++) v.push_back(make_float2((float)verts[2 * (off + k)], (float)verts[2 * (off + k) + 1]));
+    H.add_polygon(v);
+    off += poly_sizes[p];
+  }
+  std::vector<int> all(H.point.size());
+  for (size_t k = 0; k < all.size(); k++) all[k] = (int)k;
+  const int root = H.build(all);
+  if ((int)H.point.size() > RVO_MAX_OBST) return -2;
+  cudaError_t e = upload(&h->rvo_point, H.point);
+  if (e == cudaSuccess) e = upload(&h->rvo_unitdir, H.unitDir);
+  if (e == cudaSuccess) e = upload(&h->rvo_next, H.next);
+  if (e == cudaSuccess) e = upload(&h->rvo_prev, H.prev);
+  if (e == cudaSuccess) e = upload(&h->rvo_convex, H.convex);
+  if (e == cudaSuccess) e = upload(&h->rvo_node, H.node);
+  if (e != cudaSuccess) return (int)e;
+  h->rvo_n = (int)H.point.size();
+  h->rvo_root = n_polys > 0 ? root : -1;
+  return 0;
+}
+
+void casim_rvo_obstacles_free(casim_handle* h) {
+  cudaFree(h->rvo_point); cudaFree(h->rvo_unitdir); cudaFree(h->rvo_next); cudaFree(h->rvo_prev);
+  cudaFree(h->rvo_convex); cudaFree(h->rvo_node);
+  h->rvo_point = h->rvo_unitdir = nullptr;
+  h->rvo_next = h->rvo_prev = h->rvo_convex = nullptr;
+  h->rvo_node = nullptr;
+  h->rvo_n = 0;
+  h->rvo_root = -1;
+}
+
 cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* prm,
                              float* policy_actions, cudaStream_t s) {
   RvoArgs a;
+  a.ob.point = h->rvo_point;
+  a.ob.unitDir = h->rvo_unitdir;
+  a.ob.next = h->rvo_next;
+  a.ob.prev = h->rvo_prev;
+  a.ob.convex = h->rvo_convex;
+  a.ob.node = h->rvo_node;
+  a.ob.n = h->rvo_n;
+  a.ob.root = h->rvo_n > 0 ? h->rvo_root : -1;
+  a.time_horizon_obst = (float)prm->time_horizon; /* RVOPolicy.py:26-27: timeHorizonObst = time_horizon */
   a.state = reinterpret_cast<const float4*>(state);
   a.coop = coop;
   a.n_agents = h->n_agents;
@@ -320,5 +684,7 @@ cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* c
   a.A = h->A;
   const size_t N = (size_t)h->E * h->A;
   h->launches++;
-  return casim_launch_pdl<RvoArgs>(k_rvo, dim3((unsigned)((N + RVO_THREADS - 1) / RVO_THREADS)), dim3(RVO_THREADS), 0, s, a);
+  const dim3 grid((unsigned)((N + RVO_THREADS - 1) / RVO_THREADS)), block(RVO_THREADS);
+  if (a.ob.root >= 0) return casim_launch_pdl<RvoArgs>(k_rvo<true>, grid, block, 0, s, a);
+  return casim_launch_pdl<RvoArgs>(k_rvo<false>, grid, block, 0, s, a);
 }

@@ -100,10 +100,13 @@ class BatchedCollisionAvoidanceEnv:
     def set_static_map(self, obstacles):
         """obstacles: the reference's format (list of 4-corner lists; corners 1 and 3 are read, Map.py:117-118), or
         an array [n,4] / [E,n,4] of (x1, y1, x3, y3) rectangles, or None."""
+        self._obstacle_polys = None
         if obstacles is None or len(obstacles) == 0:
             self.obstacles = None
             return
         ob = obstacles
+        if not isinstance(ob, np.ndarray) and hasattr(ob[0][0], "__len__"):
+            self._obstacle_polys = [np.asarray(o, np.float64) for o in ob]     # what RVOPolicy hands to sim.addObstacle
         if not isinstance(ob, np.ndarray) and len(ob[0]) == 4 and hasattr(ob[0][0], "__len__"):
             ob = np.array([[o[1][0], o[1][1], o[3][0], o[3][1]] for o in ob], np.float32)
         self.obstacles = np.asarray(ob, np.float32)
@@ -186,7 +189,12 @@ class BatchedCollisionAvoidanceEnv:
         self._rvo_coop = None
         if self._has_rvo:
             if self.obstacles is not None:
-                raise RuntimeError("RVOPolicy agents with static obstacles are not supported (obstacle ORCA lines)")
+                if getattr(self, "_obstacle_polys", None) is None:
+                    raise RuntimeError("RVOPolicy agents need the obstacles as polygons (the reference's list-of-corners "
+                                       "format), not as rectangles")
+                sim.rvo_set_obstacles(self._obstacle_polys)
+            else:
+                sim.rvo_set_obstacles(None)
             coop = np.ones((self.E, self.A), np.float32)
             if self.agents is not None:
                 for e, ags in enumerate(self.agents):

@@ -59,6 +59,7 @@ SYMBOLS = {
     "casim_ga3c_set_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "casim_ga3c_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "casim_rvo_default_params": (None, [ctypes.POINTER(RvoParams)]),
+    "casim_rvo_set_obstacles": (c_int, [c_void_p, ctypes.POINTER(c_double), ctypes.POINTER(ctypes.c_int32), c_int]),
     "casim_rvo_step": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.POINTER(RvoParams), c_void_p, c_void_p]),
     "casim_flat_row_size": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_int32), c_int]),
     "casim_flatten_obs": (c_int, [c_void_p, c_void_p, _POBS, ctypes.POINTER(ctypes.c_int32), c_int, c_void_p, c_void_p]),

@@ -255,6 +255,15 @@ class BatchedSim:
                                                _stream_ptr()), "casim_ga3c_forward")
         return self.buf["policy_actions"]
 
+    def rvo_set_obstacles(self, polygons):
+        """sim.addObstacle for every polygon + sim.processObstacles (RVOPolicy.py:44,56-57): ``polygons`` = list of
+        vertex lists [(x, y), ...] (counter-clockwise), ONE set shared by all environments; None / [] removes it."""
+        polygons = [] if polygons is None else [np.asarray(p, np.float64).reshape(-1, 2) for p in polygons]
+        sizes = (ctypes.c_int32 * max(len(polygons), 1))(*[len(p) for p in polygons])
+        flat = np.ascontiguousarray(np.concatenate(polygons) if polygons else np.zeros((0, 2)), np.float64)
+        _lib.check(self.lib.casim_rvo_set_obstacles(self.handle, flat.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), sizes,
+                                                    len(polygons)), "casim_rvo_set_obstacles")
+
     def rvo_step(self, coop=None, params=None):
         """RVOPolicy.find_next_action for every RVO agent -> ``buf['policy_actions']`` (pass it to
         ``step(policy_actions=...)``).  coop: [E,A] float32 Agent.cooperation_coef (None = 1.0)."""

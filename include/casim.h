@@ -266,8 +266,13 @@ int casim_ga3c_forward(casim_handle* h, const float* state, float* policy_action
  * 286-631) for every agent whose policy id is CASIM_POLICY_RVO: writes [pref_speed, delta_heading] into
  * policy_actions [E,A,2] (other agents' entries are left untouched); pass the buffer to casim_step.
  * coop: [E,A] Agent.cooperation_coef (agent.py:10,103; RVOPolicy.py:85) or NULL = 1.0.  params: NULL = defaults.
- * Static obstacles are not supported by this entry point (returns CASIM_EINVAL when the handle has a map). */
+ * casim_rvo_set_obstacles replaces sim.addObstacle (RVOPolicy.py:56-57, RVOSimulator.cpp:124-161) +
+ * sim.processObstacles (RVOPolicy.py:44, KdTree.cpp:113-245, edge splitting included) for ONE obstacle set shared by
+ * all environments: n_polys polygons, poly_sizes[p] vertices each, counter-clockwise, vertices [sum][2] doubles in
+ * HOST memory (synchronous; at most 64 vertices after splitting; n_polys = 0 removes the set).  The obstacle ORCA
+ * lines are Agent.cpp:66-284.  A handle with a static map refuses casim_rvo_step until an obstacle set is given. */
 void casim_rvo_default_params(casim_rvo_params* params);
+int casim_rvo_set_obstacles(casim_handle* h, const double* vertices, const int32_t* poly_sizes, int n_polys);
 int casim_rvo_step(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* params,
                    float* policy_actions, void* stream);
 

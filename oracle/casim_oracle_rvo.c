@@ -16,9 +16,10 @@
  * Parity status: PINNED.  The reference's own C++ sources compile here (oracle/Makefile `ref` ->
  * oracle/_ref/librvo2_ref.so); tests/test_oracle_golden.py checks this file bit for bit against that library when
  * it is present and against tests/golden/rvo.npz (generated from it by oracle/gen_golden_rvo.py) everywhere.
- * Scope: agent-agent ORCA lines.  Static obstacles reach the reference simulator only through the first
- * find_next_action call (RVOPolicy.py:56-57 adds them on every call but processObstacles runs once, :44); obstacle
- * ORCA lines (Agent.cpp:66-284) are not restated -- the entry point refuses RVO agents together with obstacles.
+ * Scope: agent-agent and static-obstacle ORCA lines.  Static obstacles reach the reference simulator only through the
+ * first find_next_action call (RVOPolicy.py:56-57 adds them on every call but processObstacles runs once, :44): the
+ * obstacle set is an episode constant here (RVOSimulator::addObstacle, KdTree::buildObstacleTree with edge splitting,
+ * queryObstacleTreeRecursive, Agent.cpp:66-284 are all restated below).
  * Neighbour ties (two agents at exactly the same squared distance) are broken by agent index; the reference
  * breaks them by k-d tree visiting order.
  */
@@ -33,6 +34,7 @@
 #define NF CASIM_STATE_WORDS
 #define RVO_EPS 0.00001f /* Definitions.h:52 */
 #define MAXN CASIM_MAX_AGENTS
+#define MAXOBST 1024 /* obstacle vertices incl. the ones edge splitting creates */
 
 typedef struct { float x, y; } v2;
 typedef struct { v2 point, direction; } line_t;
@@ -113,7 +115,7 @@ static int lp2(const line_t* lines, int nl, float radius, v2 opt, int dirOpt, v2
 /* Agent.cpp:580-630 (numObstLines = 0 here) */
 static void lp3(const line_t* lines, int nl, int numObst, int beginLine, float radius, v2* result) {
   float distance = 0.0f;
-  line_t proj[2 * MAXN];
+  static __thread line_t proj[MAXOBST + 2 * MAXN];
   for (int i = beginLine; i < nl; i++) {
     if (det(lines[i].direction, sub(lines[i].point, *result)) > distance) {
       int np = 0;
@@ -138,11 +140,283 @@ static void lp3(const line_t* lines, int nl, int numObst, int beginLine, float r
   }
 }
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Static obstacles: RVOSimulator::addObstacle (RVOSimulator.cpp:124-161), KdTree::buildObstacleTree(Recursive)
+ * (KdTree.cpp:113-245, including the edge splitting), KdTree::queryObstacleTreeRecursive (:300-329),
+ * Agent::insertObstacleNeighbor (Agent.cpp:475-493) and the obstacle ORCA lines (Agent.cpp:66-284).
+ * --------------------------------------------------------------------------------------------------------- */
+typedef struct {
+  int n;                       /* vertices ("obstacles" in RVO2's vocabulary), including the ones splitting created */
+  v2 point[MAXOBST], unitDir[MAXOBST];
+  int next[MAXOBST], prev[MAXOBST], convex[MAXOBST];
+  int n_nodes, root;
+  int node_obst[MAXOBST], node_left[MAXOBST], node_right[MAXOBST];
+} obst_set;
+
+static float leftOf(v2 a, v2 b, v2 c) { return det(sub(a, c), sub(b, a)); } /* Definitions.h:93-96 */
+
+static int obst_add_polygon(obst_set* O, const v2* vert, int nv) { /* RVOSimulator.cpp:124-161 */
+  if (nv < 2 || O->n + nv > MAXOBST) return -1;
+  const int first = O->n;
+  for (int i = 0; i < nv; i++) {
+    const int k = O->n;
+    O->point[k] = vert[i];
+    if (i != 0) {
+      O->prev[k] = k - 1;
+      O->next[k - 1] = k;
+    }
+    if (i == nv - 1) {
+      O->next[k] = first;
+      O->prev[first] = k;
+    }
+    O->unitDir[k] = normalize(sub(vert[i == nv - 1 ? 0 : i + 1], vert[i]));
+    O->convex[k] = nv == 2 ? 1 : (leftOf(vert[i == 0 ? nv - 1 : i - 1], vert[i], vert[i == nv - 1 ? 0 : i + 1]) >= 0.0f);
+    O->n++;
+  }
+  return first;
+}
+
+static int pair_lt(size_t a1, size_t a2, size_t b1, size_t b2) { return a1 < b1 || (a1 == b1 && a2 < b2); }
+
+static int obst_build(obst_set* O, const int* list, int count) { /* KdTree.cpp:127-245 */
+  if (count == 0) return -1;
+  const int node = O->n_nodes++;
+  size_t optimalSplit = 0, minLeft = (size_t)count, minRight = (size_t)count;
+  for (int i = 0; i < count; i++) {
+    size_t leftSize = 0, rightSize = 0;
+    const int i1 = list[i], i2 = O->next[i1];
+    for (int j = 0; j < count; j++) {
+      if (i == j) continue;
+      const int j1 = list[j], j2 = O->next[j1];
+      const float j1LeftOfI = leftOf(O->point[i1], O->point[i2], O->point[j1]);
+      const float j2LeftOfI = leftOf(O->point[i1], O->point[i2], O->point[j2]);
+      if (j1LeftOfI >= -RVO_EPS && j2LeftOfI >= -RVO_EPS) ++leftSize;
+      else if (j1LeftOfI <= RVO_EPS && j2LeftOfI <= RVO_EPS) ++rightSize;
+      else { ++leftSize; ++rightSize; }
+      size_t a1 = leftSize > rightSize ? leftSize : rightSize, a2 = leftSize > rightSize ? rightSize : leftSize;
+      size_t b1 = minLeft > minRight ? minLeft : minRight, b2 = minLeft > minRight ? minRight : minLeft;
+      if (!pair_lt(a1, a2, b1, b2)) break; /* >= */
+    }
+    size_t a1 = leftSize > rightSize ? leftSize : rightSize, a2 = leftSize > rightSize ? rightSize : leftSize;
+    size_t b1 = minLeft > minRight ? minLeft : minRight, b2 = minLeft > minRight ? minRight : minLeft;
+    if (pair_lt(a1, a2, b1, b2)) {
+      minLeft = leftSize;
+      minRight = rightSize;
+      optimalSplit = (size_t)i;
+    }
+  }
+  int* leftL = (int*)malloc(sizeof(int) * (minLeft + 1));
+  int* rightL = (int*)malloc(sizeof(int) * (minRight + 1));
+  size_t lc = 0, rc = 0;
+  const int i = (int)optimalSplit;
+  const int i1 = list[i], i2 = O->next[i1];
+  for (int j = 0; j < count; j++) {
+    if (i == j) continue;
+    const int j1 = list[j], j2 = O->next[j1];
+    const float j1LeftOfI = leftOf(O->point[i1], O->point[i2], O->point[j1]);
+    const float j2LeftOfI = leftOf(O->point[i1], O->point[i2], O->point[j2]);
+    if (j1LeftOfI >= -RVO_EPS && j2LeftOfI >= -RVO_EPS) leftL[lc++] = j1;
+    else if (j1LeftOfI <= RVO_EPS && j2LeftOfI <= RVO_EPS) rightL[rc++] = j1;
+    else { /* split edge j at the line through edge i */
+      const float t = det(sub(O->point[i2], O->point[i1]), sub(O->point[j1], O->point[i1])) /
+                      det(sub(O->point[i2], O->point[i1]), sub(O->point[j1], O->point[j2]));
+      const v2 splitpoint = add(O->point[j1], scalel(t, sub(O->point[j2], O->point[j1])));
+      const int nw = O->n++;
+      O->point[nw] = splitpoint;
+      O->prev[nw] = j1;
+      O->next[nw] = j2;
+      O->convex[nw] = 1;
+      O->unitDir[nw] = O->unitDir[j1];
+      O->next[j1] = nw;
+      O->prev[j2] = nw;
+      if (j1LeftOfI > 0.0f) { leftL[lc++] = j1; rightL[rc++] = nw; }
+      else { rightL[rc++] = j1; leftL[lc++] = nw; }
+    }
+  }
+  O->node_obst[node] = i1;
+  const int l = obst_build(O, leftL, (int)lc);
+  const int r = obst_build(O, rightL, (int)rc);
+  O->node_left[node] = l;
+  O->node_right[node] = r;
+  free(leftL);
+  free(rightL);
+  return node;
+}
+
+static void obst_process(obst_set* O) { /* KdTree.cpp:113-124 */
+  int* all = (int*)malloc(sizeof(int) * (O->n + 1));
+  const int n0 = O->n;
+  for (int k = 0; k < n0; k++) all[k] = k;
+  O->n_nodes = 0;
+  O->root = obst_build(O, all, n0);
+  free(all);
+}
+
+static float distSqPointLineSegment(v2 a, v2 b, v2 c) { /* Definitions.h:68-82 */
+  const float r = dot(sub(c, a), sub(b, a)) / absSq(sub(b, a));
+  if (r < 0.0f) return absSq(sub(c, a));
+  if (r > 1.0f) return absSq(sub(c, b));
+  return absSq(sub(c, add(a, scalel(r, sub(b, a)))));
+}
+
+typedef struct { float d[MAXOBST]; int o[MAXOBST]; int n; } obst_nb;
+
+static void obst_query(const obst_set* O, v2 position, float rangeSq, int node, obst_nb* nb) { /* KdTree.cpp:300-329 */
+  if (node < 0) return;
+  const int o1 = O->node_obst[node], o2 = O->next[o1];
+  const float agentLeftOfLine = leftOf(O->point[o1], O->point[o2], position);
+  obst_query(O, position, rangeSq, agentLeftOfLine >= 0.0f ? O->node_left[node] : O->node_right[node], nb);
+  const float distSqLine = sqr(agentLeftOfLine) / absSq(sub(O->point[o2], O->point[o1]));
+  if (distSqLine < rangeSq) {
+    if (agentLeftOfLine < 0.0f) { /* Agent.cpp:475-493 insertObstacleNeighbor */
+      const float distSq = distSqPointLineSegment(O->point[o1], O->point[O->next[o1]], position);
+      if (distSq < rangeSq) {
+        int i = nb->n++;
+        while (i != 0 && distSq < nb->d[i - 1]) {
+          nb->d[i] = nb->d[i - 1];
+          nb->o[i] = nb->o[i - 1];
+          --i;
+        }
+        nb->d[i] = distSq;
+        nb->o[i] = o1;
+      }
+    }
+    obst_query(O, position, rangeSq, agentLeftOfLine >= 0.0f ? O->node_right[node] : O->node_left[node], nb);
+  }
+}
+
+/* Agent.cpp:66-284: ORCA lines of the obstacle neighbours (sorted by distance); returns the number of lines */
+static int obstacle_lines(const obst_set* O, const obst_nb* nb, v2 position_, v2 velocity_, float radius_,
+                          float timeHorizonObst_, line_t* lines) {
+  int nl = 0;
+  const float invTimeHorizonObst = 1.0f / timeHorizonObst_;
+  for (int i = 0; i < nb->n; i++) {
+    int obstacle1 = nb->o[i];
+    int obstacle2 = O->next[obstacle1];
+    const v2 relativePosition1 = sub(O->point[obstacle1], position_);
+    const v2 relativePosition2 = sub(O->point[obstacle2], position_);
+    int alreadyCovered = 0;
+    for (int j = 0; j < nl; j++) {
+      if (det(sub(scalel(invTimeHorizonObst, relativePosition1), lines[j].point), lines[j].direction) - invTimeHorizonObst * radius_ >= -RVO_EPS &&
+          det(sub(scalel(invTimeHorizonObst, relativePosition2), lines[j].point), lines[j].direction) - invTimeHorizonObst * radius_ >= -RVO_EPS) {
+        alreadyCovered = 1;
+        break;
+      }
+    }
+    if (alreadyCovered) continue;
+    const float distSq1 = absSq(relativePosition1);
+    const float distSq2 = absSq(relativePosition2);
+    const float radiusSq = sqr(radius_);
+    const v2 obstacleVector = sub(O->point[obstacle2], O->point[obstacle1]);
+    const float s = dot(neg(relativePosition1), obstacleVector) / absSq(obstacleVector);
+    const float distSqLine = absSq(sub(neg(relativePosition1), scalel(s, obstacleVector)));
+    line_t line;
+    if (s < 0.0f && distSq1 <= radiusSq) {
+      if (O->convex[obstacle1]) {
+        line.point = V(0.0f, 0.0f);
+        line.direction = normalize(V(-relativePosition1.y, relativePosition1.x));
+        lines[nl++] = line;
+      }
+      continue;
+    } else if (s > 1.0f && distSq2 <= radiusSq) {
+      if (O->convex[obstacle2] && det(relativePosition2, O->unitDir[obstacle2]) >= 0.0f) {
+        line.point = V(0.0f, 0.0f);
+        line.direction = normalize(V(-relativePosition2.y, relativePosition2.x));
+        lines[nl++] = line;
+      }
+      continue;
+    } else if (s >= 0.0f && s < 1.0f && distSqLine <= radiusSq) {
+      line.point = V(0.0f, 0.0f);
+      line.direction = neg(O->unitDir[obstacle1]);
+      lines[nl++] = line;
+      continue;
+    }
+    v2 leftLegDirection, rightLegDirection;
+    if (s < 0.0f && distSqLine <= radiusSq) {
+      if (!O->convex[obstacle1]) continue;
+      obstacle2 = obstacle1;
+      const float leg1 = sqrtf(distSq1 - radiusSq);
+      leftLegDirection = divs(V(relativePosition1.x * leg1 - relativePosition1.y * radius_, relativePosition1.x * radius_ + relativePosition1.y * leg1), distSq1);
+      rightLegDirection = divs(V(relativePosition1.x * leg1 + relativePosition1.y * radius_, -relativePosition1.x * radius_ + relativePosition1.y * leg1), distSq1);
+    } else if (s > 1.0f && distSqLine <= radiusSq) {
+      if (!O->convex[obstacle2]) continue;
+      obstacle1 = obstacle2;
+      const float leg2 = sqrtf(distSq2 - radiusSq);
+      leftLegDirection = divs(V(relativePosition2.x * leg2 - relativePosition2.y * radius_, relativePosition2.x * radius_ + relativePosition2.y * leg2), distSq2);
+      rightLegDirection = divs(V(relativePosition2.x * leg2 + relativePosition2.y * radius_, -relativePosition2.x * radius_ + relativePosition2.y * leg2), distSq2);
+    } else {
+      if (O->convex[obstacle1]) {
+        const float leg1 = sqrtf(distSq1 - radiusSq);
+        leftLegDirection = divs(V(relativePosition1.x * leg1 - relativePosition1.y * radius_, relativePosition1.x * radius_ + relativePosition1.y * leg1), distSq1);
+      } else {
+        leftLegDirection = neg(O->unitDir[obstacle1]);
+      }
+      if (O->convex[obstacle2]) {
+        const float leg2 = sqrtf(distSq2 - radiusSq);
+        rightLegDirection = divs(V(relativePosition2.x * leg2 + relativePosition2.y * radius_, -relativePosition2.x * radius_ + relativePosition2.y * leg2), distSq2);
+      } else {
+        rightLegDirection = O->unitDir[obstacle1];
+      }
+    }
+    const int leftNeighbor = O->prev[obstacle1];
+    int isLeftLegForeign = 0, isRightLegForeign = 0;
+    if (O->convex[obstacle1] && det(leftLegDirection, neg(O->unitDir[leftNeighbor])) >= 0.0f) {
+      leftLegDirection = neg(O->unitDir[leftNeighbor]);
+      isLeftLegForeign = 1;
+    }
+    if (O->convex[obstacle2] && det(rightLegDirection, O->unitDir[obstacle2]) <= 0.0f) {
+      rightLegDirection = O->unitDir[obstacle2];
+      isRightLegForeign = 1;
+    }
+    const v2 leftCutoff = scalel(invTimeHorizonObst, sub(O->point[obstacle1], position_));
+    const v2 rightCutoff = scalel(invTimeHorizonObst, sub(O->point[obstacle2], position_));
+    const v2 cutoffVec = sub(rightCutoff, leftCutoff);
+    const float t = obstacle1 == obstacle2 ? 0.5f : dot(sub(velocity_, leftCutoff), cutoffVec) / absSq(cutoffVec);
+    const float tLeft = dot(sub(velocity_, leftCutoff), leftLegDirection);
+    const float tRight = dot(sub(velocity_, rightCutoff), rightLegDirection);
+    if ((t < 0.0f && tLeft < 0.0f) || (obstacle1 == obstacle2 && tLeft < 0.0f && tRight < 0.0f)) {
+      const v2 unitW = normalize(sub(velocity_, leftCutoff));
+      line.direction = V(unitW.y, -unitW.x);
+      line.point = add(leftCutoff, scalel(radius_ * invTimeHorizonObst, unitW));
+      lines[nl++] = line;
+      continue;
+    } else if (t > 1.0f && tRight < 0.0f) {
+      const v2 unitW = normalize(sub(velocity_, rightCutoff));
+      line.direction = V(unitW.y, -unitW.x);
+      line.point = add(rightCutoff, scalel(radius_ * invTimeHorizonObst, unitW));
+      lines[nl++] = line;
+      continue;
+    }
+    const float distSqCutoff = (t < 0.0f || t > 1.0f || obstacle1 == obstacle2) ? INFINITY : absSq(sub(velocity_, add(leftCutoff, scalel(t, cutoffVec))));
+    const float distSqLeft = tLeft < 0.0f ? INFINITY : absSq(sub(velocity_, add(leftCutoff, scalel(tLeft, leftLegDirection))));
+    const float distSqRight = tRight < 0.0f ? INFINITY : absSq(sub(velocity_, add(rightCutoff, scalel(tRight, rightLegDirection))));
+    if (distSqCutoff <= distSqLeft && distSqCutoff <= distSqRight) {
+      line.direction = neg(O->unitDir[obstacle1]);
+      line.point = add(leftCutoff, scalel(radius_ * invTimeHorizonObst, V(-line.direction.y, line.direction.x)));
+      lines[nl++] = line;
+      continue;
+    } else if (distSqLeft <= distSqRight) {
+      if (isLeftLegForeign) continue;
+      line.direction = leftLegDirection;
+      line.point = add(leftCutoff, scalel(radius_ * invTimeHorizonObst, V(-line.direction.y, line.direction.x)));
+      lines[nl++] = line;
+      continue;
+    } else {
+      if (isRightLegForeign) continue;
+      line.direction = neg(rightLegDirection);
+      line.point = add(rightCutoff, scalel(radius_ * invTimeHorizonObst, V(-line.direction.y, line.direction.x)));
+      lines[nl++] = line;
+      continue;
+    }
+  }
+  return nl;
+}
+
 /* One ego agent of RVOSimulator::doStep (RVOSimulator.cpp:163-183): computeNeighbors + computeNewVelocity + update.
  * pos/vel/pref/radius/max_speed are the values AFTER the binding's float conversion. */
 static void rvo_ego_step(int n, const v2* pos, const v2* vel, const v2* pref, const float* radius, const float* max_speed,
                          int ego, float collab, float timeStep, float neighborDist, int maxNeighbors, float timeHorizon,
-                         v2* new_pos) {
+                         const obst_set* O, float timeHorizonObst, v2* new_pos) {
   /* Agent.cpp:43-56 + 449-473: neighbours sorted by squared distance, at most maxNeighbors */
   float ndist[MAXN];
   int nidx[MAXN];
@@ -166,11 +440,18 @@ static void rvo_ego_step(int n, const v2* pos, const v2* vel, const v2* pref, co
       }
     }
   }
-  line_t lines[MAXN + 2];
+  static __thread line_t lines[MAXOBST + MAXN + 2];
   int nl = 0;
   v2 prefVel = pref[ego];
   const v2 position = pos[ego], velocity = vel[ego];
   const float radius_ = radius[ego];
+  if (O && O->root >= 0) { /* Agent.cpp:45-47 + 66-284 */
+    static __thread obst_nb nb;
+    nb.n = 0;
+    obst_query(O, position, sqr(timeHorizonObst * max_speed[ego] + radius_), O->root, &nb);
+    nl = obstacle_lines(O, &nb, position, velocity, radius_, timeHorizonObst, lines);
+  }
+  const int numObstLines = nl;
   const float invTimeHorizon = 1.0f / timeHorizon;
   if (collab == 0.0f) {
     /* Agent.cpp:290-292: ignores the other agents */
@@ -244,15 +525,33 @@ static void rvo_ego_step(int n, const v2* pos, const v2* vel, const v2* pref, co
   }
   v2 newVel = V(0.f, 0.f);
   const int lineFail = lp2(lines, nl, max_speed[ego], prefVel, 0, &newVel);
-  if (lineFail < nl) lp3(lines, nl, 0, lineFail, max_speed[ego], &newVel);
+  if (lineFail < nl) lp3(lines, nl, numObstLines, lineFail, max_speed[ego], &newVel);
   /* Agent.cpp:516-521 update */
   *new_pos = add(position, scale(newVel, timeStep));
 }
 
-/* Same signature as oracle/rvo2_ref_shim.cpp:rvo2_ref_step, so that the two can be compared call for call. */
-int casim_oracle_rvo_ref_step(int n, const double* pos, const double* vel, const double* pref_vel, const double* radius,
-                              const double* max_speed, int ego, double collab, double dt, double neighbor_dist,
-                              int max_neighbors, double time_horizon, double* new_pos) {
+static obst_set* obst_from_polys(int n_polys, const int32_t* poly_sizes, const double* verts) {
+  if (n_polys <= 0) return NULL;
+  obst_set* O = (obst_set*)calloc(1, sizeof(obst_set));
+  O->root = -1;
+  int off = 0;
+  for (int p = 0; p < n_polys; p++) {
+    v2 tmp[64];
+    const int nv = poly_sizes[p];
+    if (nv > 64) { free(O); return NULL; }
+    for (int k = 0; k < nv; k++) tmp[k] = V((float)verts[2 * (off + k)], (float)verts[2 * (off + k) + 1]); /* rvo2.pyx:119-120 */
+    if (obst_add_polygon(O, tmp, nv) < 0) { free(O); return NULL; }
+    off += nv;
+  }
+  obst_process(O);
+  return O;
+}
+
+/* Same signatures as oracle/rvo2_ref_shim.cpp, so that the two can be compared call for call. */
+int casim_oracle_rvo_ref_step_obst(int n, const double* pos, const double* vel, const double* pref_vel, const double* radius,
+                                   const double* max_speed, int ego, double collab, double dt, double neighbor_dist,
+                                   int max_neighbors, double time_horizon, int n_polys, const int32_t* poly_sizes,
+                                   const double* poly_verts, double* new_pos) {
   if (n > MAXN) return 1;
   v2 p[MAXN], v[MAXN], pv[MAXN];
   float r[MAXN], ms[MAXN];
@@ -263,11 +562,40 @@ int casim_oracle_rvo_ref_step(int n, const double* pos, const double* vel, const
     r[a] = (float)radius[a];
     ms[a] = (float)max_speed[a];
   }
+  obst_set* O = obst_from_polys(n_polys, poly_sizes, poly_verts);
+  if (n_polys > 0 && !O) return 2;
   v2 np_;
-  rvo_ego_step(n, p, v, pv, r, ms, ego, (float)collab, (float)dt, (float)neighbor_dist, max_neighbors, (float)time_horizon, &np_);
+  rvo_ego_step(n, p, v, pv, r, ms, ego, (float)collab, (float)dt, (float)neighbor_dist, max_neighbors, (float)time_horizon,
+               O, (float)time_horizon, &np_);
+  free(O);
   new_pos[0] = np_.x;
   new_pos[1] = np_.y;
   return 0;
+}
+
+int casim_oracle_rvo_ref_step(int n, const double* pos, const double* vel, const double* pref_vel, const double* radius,
+                              const double* max_speed, int ego, double collab, double dt, double neighbor_dist,
+                              int max_neighbors, double time_horizon, double* new_pos) {
+  return casim_oracle_rvo_ref_step_obst(n, pos, vel, pref_vel, radius, max_speed, ego, collab, dt, neighbor_dist,
+                                        max_neighbors, time_horizon, 0, NULL, NULL, new_pos);
+}
+
+/* The processed obstacle set (vertices incl. split points, links, tree) for cross-checking the product's own
+ * preprocessing: returns the number of vertices; arrays must hold MAXOBST entries. */
+int casim_oracle_rvo_obstacles(int n_polys, const int32_t* poly_sizes, const double* poly_verts, float* points /*[n][2]*/,
+                               int32_t* next, int32_t* prev, int32_t* convex, int32_t* n_nodes, int32_t* node_obst,
+                               int32_t* node_left, int32_t* node_right) {
+  obst_set* O = obst_from_polys(n_polys, poly_sizes, poly_verts);
+  if (!O) return -1;
+  for (int k = 0; k < O->n; k++) {
+    points[2 * k] = O->point[k].x; points[2 * k + 1] = O->point[k].y;
+    next[k] = O->next[k]; prev[k] = O->prev[k]; convex[k] = O->convex[k];
+  }
+  *n_nodes = O->n_nodes;
+  for (int k = 0; k < O->n_nodes; k++) { node_obst[k] = O->node_obst[k]; node_left[k] = O->node_left[k]; node_right[k] = O->node_right[k]; }
+  int n = O->n;
+  free(O);
+  return n;
 }
 
 /* util.py:27-32 */
@@ -290,7 +618,7 @@ static double np_mod(double a, double b) {
  * is fed ALL agents of its environment (:66-82) and only the ego agent's new position is read back (:91). */
 typedef struct {
   const casim_config* cfg; const casim_rvo_params* prm; int A; const int32_t* n_agents;
-  const double* state; const double* coop; double* actions; int e0, e1;
+  const double* state; const double* coop; double* actions; int e0, e1; const obst_set* O;
 } rvo_job;
 
 static void* rvo_job_main(void* arg) {
@@ -322,7 +650,8 @@ static void* rvo_job_main(void* arg) {
       if ((((int)s[CASIM_TYPE]) & 0xff) != CASIM_POLICY_RVO) continue;
       v2 np_;
       rvo_ego_step(n, p, v, pv, r, ms, a, (float)(coop ? coop[(size_t)e * A + a] : 1.0), (float)dt,
-                   (float)prm->neighbor_dist, prm->max_neighbors, (float)prm->time_horizon, &np_);
+                   (float)prm->neighbor_dist, prm->max_neighbors, (float)prm->time_horizon, J->O,
+                   (float)prm->time_horizon, &np_);
       /* :91-110 */
       double ddx = (double)np_.x - s[CASIM_PX], ddy = (double)np_.y - s[CASIM_PY];
       double ang1 = atan2(ddy, ddx);
@@ -341,9 +670,14 @@ static void* rvo_job_main(void* arg) {
   return NULL;
 }
 
-int casim_oracle_rvo_actions_mt(const casim_config* cfg, const casim_rvo_params* prm, int E, int A, const int32_t* n_agents,
-                                const double* state, const double* coop, double* actions, int n_threads) {
+/* obstacles: the polygons RVOPolicy hands to sim.addObstacle on its first call (RVOPolicy.py:56-57, :44), shared by
+ * all environments; n_polys = 0 for none. */
+int casim_oracle_rvo_actions_obst(const casim_config* cfg, const casim_rvo_params* prm, int E, int A, const int32_t* n_agents,
+                                  const double* state, const double* coop, double* actions, int n_threads, int n_polys,
+                                  const int32_t* poly_sizes, const double* poly_verts) {
   if (A > MAXN) return 1;
+  obst_set* O = obst_from_polys(n_polys, poly_sizes, poly_verts);
+  if (n_polys > 0 && !O) return 2;
   if (n_threads < 1) n_threads = 1;
   if (n_threads > 64) n_threads = 64;
   rvo_job jobs[64];
@@ -351,12 +685,19 @@ int casim_oracle_rvo_actions_mt(const casim_config* cfg, const casim_rvo_params*
   for (int t = 0; t < n_threads; t++) {
     rvo_job* j = &jobs[t];
     j->cfg = cfg; j->prm = prm; j->A = A; j->n_agents = n_agents; j->state = state; j->coop = coop; j->actions = actions;
+    j->O = O;
     j->e0 = (int)((long long)E * t / n_threads);
     j->e1 = (int)((long long)E * (t + 1) / n_threads);
     if (n_threads == 1) rvo_job_main(j); else pthread_create(&th[t], NULL, rvo_job_main, j);
   }
   if (n_threads > 1) for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
+  free(O);
   return 0;
+}
+
+int casim_oracle_rvo_actions_mt(const casim_config* cfg, const casim_rvo_params* prm, int E, int A, const int32_t* n_agents,
+                                const double* state, const double* coop, double* actions, int n_threads) {
+  return casim_oracle_rvo_actions_obst(cfg, prm, E, A, n_agents, state, coop, actions, n_threads, 0, NULL, NULL);
 }
 
 int casim_oracle_rvo_actions(const casim_config* cfg, const casim_rvo_params* prm, int E, int A, const int32_t* n_agents,

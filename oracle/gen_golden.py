@@ -565,6 +565,7 @@ def main():
         from oracle import gen_golden_rvo
         assert gen_golden_rvo.main() == 0
         gen_golden_rvo.main_policy(ns)
+        gen_golden_rvo.main_policy_obstacles(ns)
 
 
 if __name__ == "__main__":

@@ -96,6 +96,62 @@ def main():
     return bad
 
 
+CROSSING = [[(10, 10), (2, 10), (2, 2), (10, 2)], [(-2, 10), (-10, 10), (-10, 2), (-2, 2)],
+            [(10, -2), (2, -2), (2, -10), (10, -10)], [(-2, -2), (-10, -2), (-10, -10), (-2, -10)]]
+
+
+def main_policy_obstacles(ns, ncases=120, seed=7):
+    """As main_policy, with the crossing-map obstacles (envs/test_cases.py:3081-3085) handed to find_next_action: the
+    policy adds them to its simulator before the first processObstacles (RVOPolicy.py:56-63, :44)."""
+    from oracle import gen_golden as G
+    from casim import layout as L
+    import rvo2
+    assert hasattr(rvo2, "PyRVOSimulator") and "Mock" not in type(rvo2).__name__
+    from gym_collision_avoidance.envs.policies.RVOPolicy import RVOPolicy
+    rng = np.random.default_rng(seed)
+    A = 10
+    states = np.zeros((ncases, A, L.STATE_WORDS))
+    coop = np.ones((ncases, A))
+    n_agents = np.zeros((ncases,), np.int32)
+    actions = np.zeros((ncases, A, 2))
+    t = L.encode_type(L.POLICY_RVO, L.DYN_UNICYCLE, L.SENSOR_OTHER_AGENTS)
+    tb = L.encode_type(L.POLICY_NONCOOPERATIVE, L.DYN_UNICYCLE, L.SENSOR_OTHER_AGENTS)
+    for k in range(ncases):
+        n = int(rng.integers(1, 7))
+        n_agents[k] = n
+        init = np.zeros((n, 7))
+        arm = rng.integers(0, 4, n)
+        along, across = rng.uniform(0.5, 11.0, n), rng.uniform(-1.6, 1.6, n)      # inside the free cross, near the walls
+        init[:, 0] = np.where(arm == 0, along, np.where(arm == 1, -along, across))
+        init[:, 1] = np.where(arm == 2, along, np.where(arm == 3, -along, across))
+        init[:, 2:4] = rng.uniform(-11, 11, (n, 2))                                # goals anywhere: through the blocks
+        init[:, 4] = rng.uniform(0.2, 0.6, n)
+        init[:, 5] = rng.uniform(0.5, 1.5, n)
+        init[:, 6] = rng.uniform(-np.pi, np.pi, n)
+        init = np.float32(init).astype(np.float64)
+        agents = G.build_agents(ns, init, np.full((n,), tb, np.int32))
+        for i, ag in enumerate(agents):
+            s = G.extract_state(ag, t)
+            sp = rng.uniform(0, 1) * s[L.PREF_SPEED]
+            s[L.VX], s[L.VY] = sp * np.cos(s[L.HEADING]), sp * np.sin(s[L.HEADING])
+            s = np.float32(s).astype(np.float64)
+            s[L.TYPE] = t
+            G.inject_state(ag, s)
+            states[k, i] = s
+            coop[k, i] = float(rng.choice([1.0, 1.0, 0.5, 0.0]))
+            ag.cooperation_coef = coop[k, i]
+        for i in range(n):
+            with rh.quiet():
+                pol = RVOPolicy()
+                actions[k, i] = pol.find_next_action({}, agents, i, [list(p) for p in CROSSING])
+    path = os.path.join(ROOT, "tests", "golden", "rvo.npz")
+    old = dict(np.load(path)) if os.path.exists(path) else {}
+    old.update(obst_state=states, obst_coop=coop, obst_n_agents=n_agents, obst_actions=actions,
+               obst_polygons=np.array(CROSSING, np.float64))
+    np.savez_compressed(path, **old)
+    print("wrote rvo.npz policy cases with obstacles: %d" % ncases)
+
+
 def main_policy(ns, ncases=200, seed=99):
     """Policy level: the UNMODIFIED RVOPolicy.find_next_action (RVOPolicy.py:53-117) over the reference's own Cython
     binding (oracle/_ref/rvo2*.so, built by `make -C oracle ref`) -> tests/golden/rvo.npz keys state / coop /

@@ -261,16 +261,20 @@ def rvo_default_params():
                      max_neighbors=10)
 
 
-def rvo_actions(cfg, state, coop=None, n_agents=None, params=None, n_threads=1):
-    """RVOPolicy.find_next_action for every RVO agent: state [E,A,24] f64 -> actions [E,A,2] f64."""
+def rvo_actions(cfg, state, coop=None, n_agents=None, params=None, n_threads=1, polygons=None):
+    """RVOPolicy.find_next_action for every RVO agent: state [E,A,24] f64 -> actions [E,A,2] f64.
+    polygons: the obstacle vertex lists handed to sim.addObstacle (shared by all environments)."""
     state = np.ascontiguousarray(state, dtype=np.float64)
     E, A = state.shape[:2]
     coop = None if coop is None else np.ascontiguousarray(coop, dtype=np.float64)
     n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
     prm = params or rvo_default_params()
     out = np.zeros((E, A, 2))
-    rc = lib().casim_oracle_rvo_actions_mt(ctypes.byref(cfg), ctypes.byref(prm), E, A, _p(n_agents), _p(state), _p(coop),
-                                           _p(out), int(n_threads))
+    polygons = [] if polygons is None else [np.asarray(p, np.float64).reshape(-1, 2) for p in polygons]
+    sizes = np.array([len(p) for p in polygons] or [0], np.int32)
+    verts = np.ascontiguousarray(np.concatenate(polygons) if polygons else np.zeros((1, 2)), np.float64)
+    rc = lib().casim_oracle_rvo_actions_obst(ctypes.byref(cfg), ctypes.byref(prm), E, A, _p(n_agents), _p(state), _p(coop),
+                                             _p(out), int(n_threads), len(polygons), _p(sizes), _p(verts))
     assert rc == 0, rc
     return out
 

@@ -87,3 +87,37 @@ def test_wrapper_and_vecenv_api():
     torch.cuda.synchronize()
     assert int(env.sim.state[5, :, 0, 1].max().item()) < 400              # step_num was reset at least once
     venv.close()
+
+
+def test_flatten_full_size_equals_concatenation():
+    """BASELINE full size (4096 envs x 10 agents, all three sensors): the kernel's [E, A*S] array equals the
+    concatenation of the per-key device buffers (size-independent property; exact)."""
+    import torch
+    from casim import lib, scenarios as S
+    from casim.sim import BatchedSim
+    E, A = 4096, 10
+    cfg = lib.default_config()
+    init, types, n, rects = S.crossing(E, A, seed=3, sensors=L.SENSOR_OTHER_AGENTS | L.SENSOR_LASERSCAN | L.SENSOR_OCCUPANCY_GRID)
+    n = n.copy()
+    n[::5] = 7                                             # ragged environments: absent slots must be zero
+    sim = BatchedSim(E, A, cfg=cfg, sensors=("other_agents_states", "laserscan", "local_grid"))
+    sim.set_obstacles(rects)
+    sim.reset(init, types, n)
+    for _ in range(3):
+        sim.step()
+    keys = ['dist_to_goal', 'rel_goal', 'radius', 'heading_ego_frame', 'heading_global_frame', 'pos_global_frame',
+            'pref_speed', 'num_other_agents', 'other_agent_states', 'other_agents_states', 'laserscan', 'local_grid', 'use_ppo']
+    flat = sim.flatten_obs(keys).view(E, A, -1)
+    st, b = sim.state, sim.buf
+    w = lambda k: st[k // 4, :, :, k % 4].unsqueeze(-1)    # noqa: E731
+    parts = [w(L.DIST_TO_GOAL), b["obs_misc"][..., 0:2], w(L.RADIUS), w(L.HEADING_EGO), w(L.HEADING), st[0, :, :, 0:2],
+             w(L.PREF_SPEED), b["obs_misc"][..., 2:3], b["other_agents_states"][:, :, 0, :],
+             b["other_agents_states"].reshape(E, A, -1), b["laserscan"], b["local_grid"].reshape(E, A, -1).float(),
+             b["obs_misc"][..., 3:4]]
+    want = torch.cat(parts, dim=-1)
+    valid = (torch.arange(A, device=want.device)[None, :] < torch.as_tensor(n, device=want.device)[:, None]).unsqueeze(-1)
+    want = torch.where(valid, want, torch.zeros_like(want))
+    torch.cuda.synchronize()
+    assert flat.shape == want.shape == (E, A, sim.flat_row_size(keys))
+    assert torch.equal(flat, want)
+    sim.close()

@@ -328,3 +328,62 @@ def test_rvo_policy_restatement_vs_reference_policy(oracle_lib):
     act = oracle_lib.rvo_actions(lib.default_config(), g["state"], g["coop"], g["n_agents"])
     np.testing.assert_allclose(act, g["actions"], rtol=0, atol=1e-12)
     assert ((act[..., 0] == 0) == (g["actions"][..., 0] == 0)).all()      # the pi/6 turn limit zeroes the same speeds
+
+
+def test_rvo_policy_with_obstacles_vs_reference_policy(oracle_lib):
+    """Obstacle ORCA lines (Agent.cpp:66-284) + obstacle tree (KdTree.cpp:113-329): actions recorded from the unmodified
+    RVOPolicy.find_next_action called with the crossing-map obstacles."""
+    from casim import lib
+    g = np.load(os.path.join(H.GOLDEN, "rvo.npz"))
+    act = oracle_lib.rvo_actions(lib.default_config(), g["obst_state"], g["obst_coop"], g["obst_n_agents"],
+                                 polygons=list(g["obst_polygons"]))
+    np.testing.assert_allclose(act, g["obst_actions"], rtol=0, atol=1e-12)
+    free = oracle_lib.rvo_actions(lib.default_config(), g["obst_state"], g["obst_coop"], g["obst_n_agents"])
+    assert (np.abs(free - act).max(-1) > 1e-6).sum() > 50            # the obstacles do constrain many of the agents
+
+
+def test_rvo_obstacle_simulator_vs_reference_library_if_built(oracle_lib):
+    """Random star-shaped (non-convex) polygons, 2-vertex walls and the crossing map, incl. edge splitting in the
+    obstacle tree: bit-exact new positions against oracle/_ref/librvo2_ref.so when it travelled with the repo."""
+    import ctypes
+    path = os.path.join(os.path.dirname(H.GOLDEN), os.pardir, "oracle", "_ref", "librvo2_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/librvo2_ref.so not built")
+    ref = ctypes.CDLL(path).rvo2_ref_step_obst
+    orc = oracle_lib.lib().casim_oracle_rvo_ref_step_obst
+    P, PI = ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int32)
+    for fn in (ref, orc):
+        fn.restype = ctypes.c_int
+        fn.argtypes = [ctypes.c_int, P, P, P, P, P, ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_int,
+                       ctypes.c_double, ctypes.c_int, PI, P, P]
+
+    def call(fn, arrs, ego, collab, polys):
+        out = np.zeros(2)
+        sizes = np.array([len(p) for p in polys], np.int32)
+        verts = np.ascontiguousarray(np.concatenate(polys), np.float64)
+        assert fn(len(arrs[3]), *[a.ctypes.data_as(P) for a in arrs], ego, collab, 0.1, float("inf"), 10, 5.0, len(polys),
+                  sizes.ctypes.data_as(PI), verts.ctypes.data_as(P), out.ctypes.data_as(P)) == 0
+        return out
+    rng = np.random.default_rng(5)
+    f = lambda a: np.ascontiguousarray(np.asarray(a, np.float32).astype(np.float64))   # noqa: E731
+    for c in range(400):
+        n = int(rng.integers(1, 8))
+        if c % 3 == 0:
+            polys = [np.array(p, float) for p in g_cross()]
+        elif c % 3 == 1:
+            polys = []
+            for k in range(int(rng.integers(1, 5))):
+                m = int(rng.integers(3, 7))
+                ang, rad = np.sort(rng.uniform(0, 2 * np.pi, m)), rng.uniform(0.5, 2.5, m)
+                polys.append(rng.uniform(-6, 6, 2) + np.stack([rad * np.cos(ang), rad * np.sin(ang)], 1))
+        else:
+            polys = [np.array([[x, y], [x + w, y + h]]) for x, y, w, h in rng.uniform(-5, 5, (3, 4))]
+        pos, vel, sp = f(rng.uniform(-4, 4, (n, 2))), f(rng.uniform(-1, 1, (n, 2))), f(rng.uniform(0.5, 1.5, n))
+        arrs = [pos, vel, f(rng.uniform(-1, 1, (n, 2))), f(rng.uniform(0.25, 0.9, n)), sp]
+        ego, collab = int(rng.integers(0, n)), float(rng.choice([1.0, 0.5, 0.0, -0.5]))
+        assert np.array_equal(call(ref, arrs, ego, collab, polys), call(orc, arrs, ego, collab, polys)), "case %d" % c
+
+
+def g_cross():
+    return [[(10, 10), (2, 10), (2, 2), (10, 2)], [(-2, 10), (-10, 10), (-10, 2), (-2, 2)],
+            [(10, -2), (2, -2), (2, -10), (10, -10)], [(-2, -2), (-10, -2), (-10, -10), (-2, -10)]]
