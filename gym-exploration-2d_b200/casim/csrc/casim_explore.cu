@@ -60,7 +60,12 @@ struct PoseBox {
 /* edfMap.map[yIdc, xIdc] (edfMap.py:14-19,38-40; no y flip, sic); indices clamped into the array */
 __device__ __forceinline__ double edf_value(const DevCfg& c, const int32_t* __restrict__ d2, double px, double py,
                                             unsigned& clamped) {
-  double fx = floor((px + c.map_hw) / c.cell), fy = floor((py + c.map_hh) / c.cell);
+  /* floor((p + half) / cell): the product with 1/cell differs from the quotient by at most an ulp, so its floor is the
+   * quotient's unless it lands within 1e-9 of an integer; only then is the division itself evaluated */
+  double tx = (px + c.map_hw) * c.inv_cell, ty = (py + c.map_hh) * c.inv_cell;
+  double fx = floor(tx), fy = floor(ty);
+  if (!(tx - fx > 1e-9 && fx + 1.0 - tx > 1e-9)) fx = floor((px + c.map_hw) / c.cell);
+  if (!(ty - fy > 1e-9 && fy + 1.0 - ty > 1e-9)) fy = floor((py + c.map_hh) / c.cell);
   if (!(fx >= 0.0)) { fx = 0.0; clamped++; }
   if (fx > (double)(CASIM_MAP_DIM - 1)) { fx = (double)(CASIM_MAP_DIM - 1); clamped++; }
   if (!(fy >= 0.0)) { fy = 0.0; clamped++; }
@@ -178,6 +183,7 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
   __shared__ int s_ndet, s_qn;
   __shared__ unsigned int s_queue[XQ_CAP];
   __shared__ unsigned long long s_mi[X_NPOSE];
+  __shared__ unsigned int s_vis[64 * 64]; /* per target-map cell: bit k = visible from candidate pose k (this batch) */
   __shared__ unsigned int s_cnt[4];
   __shared__ double s_pose0[4]; /* x, y, heading, radius */
 
@@ -201,6 +207,7 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
     s_pose0[0] = x; s_pose0[1] = y; s_pose0[2] = h; s_pose0[3] = rad;
   }
   if (tid < X_NPOSE) s_mi[tid] = 0ull;
+  for (int k = tid; k < 64 * 64; k += X_THREADS) s_vis[k] = 0u;
   if (tid < 4) s_cnt[tid] = 0u;
   if (restart)
     for (int k = tid; k < dim * dim; k += X_THREADS) belief[k] = (float)c.ig_prior;
@@ -327,10 +334,35 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
           }
         }
         *cellp = fminf((float)((double)*cellp * rs), FLT_MAX);
-      } else { /* targetMap.py:130-143 */
-        double mi = cell_mi(c, (double)*cellp, log_rocc, log_remp);
-        long long fx = __double2ll_rn(mi * X_MI_SCALE);
-        atomicAdd(&s_mi[k], (unsigned long long)fx);
+      } else {
+        /* The candidate poses' wedges overlap heavily and a cell's mutual information depends on the cell alone:
+         * record who sees it, evaluate the two fp64 logs once per cell below (not once per pose and cell). */
+        atomicOr(&s_vis[j * 64 + i], 1u << k);
+      }
+    }
+    __syncthreads();
+    if (pstart > 0) { /* targetMap.py:130-143 over the union box of this batch's poses */
+      int ux0 = INT_MAX, uy0 = INT_MAX, ux1 = INT_MIN, uy1 = INT_MIN;
+      for (int k = pstart; k < pend; k++) {
+        const PoseBox& b = s_pose[k];
+        if (b.w <= 0 || b.h <= 0) continue;
+        ux0 = min(ux0, b.x0); uy0 = min(uy0, b.y0);
+        ux1 = max(ux1, b.x0 + b.w); uy1 = max(uy1, b.y0 + b.h);
+      }
+      const int uw = ux1 > ux0 ? ux1 - ux0 : 0, uh = uy1 > uy0 ? uy1 - uy0 : 0; /* (all boxes empty: nothing to do) */
+      for (int idx = tid; idx < uw * uh; idx += X_THREADS) {
+        const int ii = idx / uh, jj = idx - ii * uh;
+        const int i = ux0 + ii, j = uy0 + jj;
+        unsigned m = s_vis[j * 64 + i];
+        if (m == 0u) continue;
+        s_vis[j * 64 + i] = 0u;
+        const double mi = cell_mi(c, (double)belief[j * dim + i], log_rocc, log_remp);
+        const unsigned long long fx = (unsigned long long)__double2ll_rn(mi * X_MI_SCALE);
+        while (m) { /* integer (fixed-point) sums: independent of the order of arrival */
+          const int k = __ffs(m) - 1;
+          m &= m - 1;
+          atomicAdd(&s_mi[k], fx);
+        }
       }
     }
     __syncthreads();
