@@ -26,6 +26,7 @@ struct LaserArgs {
   const uint32_t* map_planes;
   float* out;
   int E, A, n_maps;
+  int lg2P; /* lanes per beam = 1 << lg2P = 32 / next_pow2(num_beams), computed by the launcher */
 };
 
 __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
@@ -49,22 +50,22 @@ __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
   casim_pdl_enter();
   __syncthreads();
   const int lane = threadIdx.x & 31;
-  const long long g = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const long long N = (long long)p.E * p.A;
+  const unsigned g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); /* E*A < 2^31 (checked by the launcher) */
+  const unsigned N = (unsigned)p.E * (unsigned)p.A;
   if (g >= N) return;
-  const int e = (int)(g / p.A), ai = (int)(g - (long long)e * p.A);
+  const int e = (int)(g / (unsigned)p.A), ai = (int)(g - (unsigned)e * (unsigned)p.A);
   const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
-  float* out = p.out + g * nb;
-  const int type = __float_as_int(p.state[5 * N + g].w);
+  float* out = p.out + (size_t)g * nb;
+  const int type = __float_as_int(p.state[5 * (size_t)N + g].w);
   const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_LASERSCAN);
   if (!on) {
     for (int b = lane; b < nb; b += 32) out[b] = 0.f;
     return;
   }
-  const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[0];
-  const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * g)[1];
+  const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)g)[0];
+  const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)g)[1];
   const double px = q0.x, py = q0.y, ch = q1.x, sh = q1.y;
-  const double radius = (double)p.state[2 * N + g].z;
+  const double radius = (double)p.state[2 * (size_t)N + g].z;
   const uint32_t* pl =
       p.n_maps > 0 ? p.map_planes + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_NUM_PLANES * CASIM_PLANE_WORDS : nullptr;
   int r0, c0;
@@ -72,11 +73,9 @@ __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
   const double rc = radius * c.inv_cell, rc2 = rc * rc;
   /* integer form of the ego-disc test d^2 < rc2 (d^2 integer): d^2 <= ceil(rc2) - 1; no disc if out of map */
   const int disc_thr = ego_in ? (int)fmin(ceil(rc2), 2.0e9) - 1 : -1;
-  /* lanes per beam: 32 / next_pow2(nb) */
-  int nbp = 1;
-  while (nbp < nb) nbp <<= 1;
-  const int P = 32 / nbp; /* nb <= 32 */
-  const int b = lane / P, part = lane - b * P;
+  /* lanes per beam: P = 32 / next_pow2(nb), nb <= 32 */
+  const int P = 1 << p.lg2P;
+  const int b = lane >> p.lg2P, part = lane & (P - 1);
   unsigned mask = 0;
   if (b < nb && pl) {
     /* beam direction cos/sin(angle_b + heading) by angle addition from the step kernel's cos/sin(heading);
@@ -356,7 +355,8 @@ __global__ void __launch_bounds__(32 * GRID_WARPS, 12) k_grid(const GridArgs p) 
     const int rpi = 32 / wpr;
     const int lr = lane / wpr, wx = lane - lr * wpr;
     const bool act = lr < rpi;
-    const int cxa = s_cx[wid][4 * wx], cxb = s_cx[wid][4 * wx + 3], cya = s_cy[wid][4 * wx], cyb = s_cy[wid][4 * wx + 3];
+    /* min over the word's end cells of (row term + column term) = row term + min of the two column terms */
+    const int cmx = min(s_cx[wid][4 * wx], s_cx[wid][4 * wx + 3]), cmy = min(s_cy[wid][4 * wx], s_cy[wid][4 * wx + 3]);
     constexpr int U = 5; /* rows in flight per lane: the classification loads of a batch are independent */
     for (int oy0 = 0; oy0 < W; oy0 += rpi * U) {
       uint32_t cw[U];
@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(32 * GRID_WARPS, 12) k_grid(const GridArgs p) 
         sh[u] = 0;
         if (act && oy < W) {
           const int2 r = s_r[wid][oy];
-          int xm = min(r.x + cxa, r.x + cxb) >> 10, ym = min(r.y + cya, r.y + cyb) >> 10;
+          const int xm = (r.x + cmx) >> 10, ym = (r.y + cmy) >> 10;
           cw[u] = __ldg(cls + ym * CASIM_GCLS_WORDS + (xm >> 4));
           sh[u] = (xm & 15) << 1;
         }
@@ -429,6 +429,11 @@ cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laser
   a.E = h->E;
   a.A = h->A;
   long long N = (long long)h->E * h->A;
+  if (N >= (1ll << 31)) return cudaErrorInvalidValue;
+  int nbp = 1, lg = 5;
+  while (nbp < h->dc.nb) nbp <<= 1;
+  for (int t = nbp; t > 1; t >>= 1) lg--;
+  a.lg2P = lg;
   int wpc = 8;
   dim3 grid((unsigned)((N + wpc - 1) / wpc)), block(32 * wpc);
   h->launches++;

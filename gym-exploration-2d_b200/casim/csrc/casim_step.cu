@@ -382,6 +382,8 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   const bool want_oas = p.o.other_agents_states != nullptr;
   const double rme = (double)a.radius;
   float d32[AP];
+  const bool need_dist = want_oas || p.o.nearest_dist != nullptr;
+  const double close_band = c.close_range + 1e-3;
   bool coll_agent = false, amb = false;
   float nearest = INFINITY;
   if (MODE == CASIM_MODE_STEP || want_oas) {
@@ -393,8 +395,11 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
       int ostatic = __shfl_sync(FULL_MASK, (int)me_static, src);
       double dx = a.px - ox, dy = a.py - oy;
       double s = dx * dx + dy * dy;
-      float d = sqrtf((float)s);
-      d32[j] = d;
+      float d = 0.f;
+      if (need_dist) { /* distances themselves: only the sensor rows and the reported nearest_dist need every one */
+        d = sqrtf((float)s);
+        d32[j] = d;
+      }
       if (MODE == CASIM_MODE_STEP && valid && j < n && j != ai) {
         /* pair (lo, hi): skipped when the HIGHER index is Static (collision_avoidance_env.py:643-644) */
         bool hi_static = j > ai ? (ostatic != 0) : me_static;
@@ -406,8 +411,14 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
           else if (s <= t * (1.0 + 4.5e-16))
             amb = true;                        /* fl(sqrt(s)) may still round down onto cr */
           if (j > ai) { /* :649 lower index only; value reported / used with a guard band */
-            float gap = (float)(s - t) / fmaxf(d + (float)cr, 1e-30f);
-            nearest = fminf(nearest, gap);
+            /* the reward only asks whether the smallest gap is <= GETTING_CLOSE_RANGE (and its value then): pairs whose
+             * gap is beyond the range plus a guard cannot matter unless the value itself is reported */
+            const double far = cr + close_band;
+            if (need_dist || s <= far * far) {
+              if (!need_dist) d = sqrtf((float)s);
+              float gap = (float)(s - t) / fmaxf(d + (float)cr, 1e-30f);
+              nearest = fminf(nearest, gap);
+            }
           }
         }
       }
