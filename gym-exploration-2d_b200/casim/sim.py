@@ -204,6 +204,26 @@ class BatchedSim:
                                             float(dt) if dt is not None else 0.0, ctypes.byref(self._obs),
                                             ctypes.byref(ho), _stream_ptr()), "casim_step_host")
 
+    def bind_host_step(self, host_bufs, ext_actions_host=None, ext_actions_dev=None, policy_actions=None, dt=None,
+                       stream=None):
+        """Pre-bound ``step_host``: every pointer / struct / the stream handle is resolved ONCE and the returned
+        callable is a bare ``casim_step_host`` call (an RL loop steps the same buffers every iteration; building the
+        ctypes arguments costs more host time than the C-ABI call).  The tensors must stay alive and must not be
+        re-allocated while the callable is in use; ``stream`` defaults to the stream current at bind time."""
+        view = host_bufs if isinstance(host_bufs, BatchedSim.HostView) else BatchedSim.HostView(host_bufs)
+        stream = torch.cuda.current_stream(self.device) if stream is None else stream
+        fn, check = self.lib.casim_step_host, _lib.check
+        args = (self.handle, _lib.ptr(self.state), _lib.ptr(ext_actions_host), _lib.ptr(ext_actions_dev),
+                _lib.ptr(policy_actions), float(dt) if dt is not None else 0.0, ctypes.byref(self._obs),
+                ctypes.byref(view.struct), ctypes.c_void_p(stream.cuda_stream))
+        keep = (view, ext_actions_host, ext_actions_dev, policy_actions, stream)
+
+        def call(_keep=keep):
+            rc = fn(*args)
+            if rc:
+                check(rc, "casim_step_host")
+        return call
+
     # ------------------------------------------------------------------------------------------
     # exploration (ig_greedy) and GA3C-CADRL policies: both write into the shared ``policy_actions`` buffer
     def _policy_buffers(self):

@@ -129,11 +129,16 @@ def test_step_host_delivery_matches_device_step(pinned):
     act_host = torch.zeros((E, A, 2), dtype=torch.float32)
     act_host = act_host.pin_memory() if pinned else act_host
     act_dev = torch.zeros((E, A, 2), dtype=torch.float32, device=ref.device)
+    bound = None
     for t in range(25):
         act_host.copy_(torch.rand((E, A, 2), generator=gen))            # the caller's actions change every step
         ref.step(ext_actions=act_host.to(ref.device))
         torch.cuda.synchronize()
-        tst.step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
+        if pinned:                  # the pre-bound form (arguments resolved once) and the plain call alternate
+            bound = bound if t else tst.bind_host_step(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
+            (bound if t % 2 == 0 else lambda: tst.step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev))()
+        else:
+            tst.step_host(host, ext_actions_host=act_host, ext_actions_dev=act_dev)
         assert torch.equal(act_dev.cpu(), act_host), "device copy of the actions not refreshed"
         for name, hb in host.items():
             want = ref.buf[name].cpu().numpy()
