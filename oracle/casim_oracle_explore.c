@@ -394,3 +394,60 @@ double casim_oracle_reward_from_pose(const casim_config* c, const uint8_t* map, 
   free(d2); free(vis);
   return r;
 }
+
+/* Dec-MCTS simulation rollouts: policies/ig_mcts.py:173-198 get_next_pose, :223-244 mcts_sim_state_storer,
+ * :246-253 mcts_reward, driven the way pydecmcts/DecMCTS.py:233-269 _simulate drives them.  One agent:
+ * K action sequences of H action indices (index = 3 * vel_idx + dphi_idx into vel_list (0, 2, 4) x dphi_list
+ * (-pi/2, 0, pi/2), ig_mcts.py:259-265; 255 = the sequence has ended).  A tree node's state followed by a
+ * rollout equals the whole root-to-leaf sequence replayed here, because the tree only keeps feasible steps
+ * (mcts_state_storer, :200-221) and a feasible step does the same thing in both storers.
+ * An infeasible step leaves the pose where it was and observes nothing (:237-243).  The cells seen from the
+ * ROOT pose are not part of obsvd_cells (:226-228).  exclude: [dim*dim] cells claimed by the other robots'
+ * paths (mcts_reward's other_agents_obsvd_cells) or NULL.  rewards [K]; end_pose [K][3] and obsvd
+ * [K][dim*dim] (the state's obsvd_cells, before the difference) are optional.  The sum runs in row-major cell order (the reference: Python-set order). */
+int casim_oracle_explore_rollouts(const casim_config* c, const uint8_t* map, const double* pose, double radius,
+                                  const double* belief, const uint8_t* actions, int K, int H, int xdt,
+                                  const uint8_t* exclude, double* rewards, double* end_pose, uint8_t* obsvd) {
+  const int dim = c->ig_map_dim;
+  int32_t* d2 = (int32_t*)malloc(sizeof(int32_t) * MD * MD);
+  uint8_t* vis = (uint8_t*)malloc((size_t)dim * dim);
+  uint8_t* seen = (uint8_t*)malloc((size_t)dim * dim);
+  casim_oracle_edt(map, d2);
+  xctx x = {c, d2, NULL};
+  const double vel_list[3] = {0.0, 2.0, 4.0}, dphi_list[3] = {-0.5 * M_PI, 0, 0.5 * M_PI};
+  for (int k = 0; k < K; k++) {
+    double cur[3] = {pose[0], pose[1], pose[2]};
+    memset(seen, 0, (size_t)dim * dim);
+    for (int t = 0; t < H; t++) {
+      int a = actions[(size_t)k * H + t];
+      if (a > 8) break;
+      double v = vel_list[a / 3], w = dphi_list[a % 3];
+      double nx[3] = {cur[0], cur[1], cur[2]};
+      int ok = 1;
+      for (int i = 0; i < xdt && ok; i++) {
+        double cs = cos(nx[2]), sn = sin(nx[2]);
+        double vx = cs * v + (-sn) * 0.0, vy = sn * v + cs * 0.0;
+        nx[0] = nx[0] + vx * c->ig_dt;
+        nx[1] = nx[1] + vy * c->ig_dt;
+        nx[2] = nx[2] + w * c->ig_dt;
+        if (v == 0.0) continue;
+        int in_map = c->map_width / 2 > nx[0] && c->map_height / 2 > nx[1] && nx[0] > -c->map_width / 2 &&
+                     nx[1] > -c->map_height / 2;
+        if (!in_map || !(edf_at(&x, nx[0], nx[1]) > radius + 0.1)) ok = 0;
+      }
+      if (!ok) continue; /* pose kept, nothing observed */
+      cur[0] = nx[0]; cur[1] = nx[1]; cur[2] = nx[2];
+      visible_cells(&x, cur, vis);
+      for (int q = 0; q < dim * dim; q++) seen[q] |= vis[q];
+    }
+    double s = 0;
+    for (int q = 0; q < dim * dim; q++) {
+      if (seen[q] && !(exclude && exclude[q])) s += cell_mi(c, belief[q]);
+    }
+    rewards[k] = s;
+    if (end_pose) { end_pose[3 * k] = cur[0]; end_pose[3 * k + 1] = cur[1]; end_pose[3 * k + 2] = cur[2]; }
+    if (obsvd) memcpy(obsvd + (size_t)k * dim * dim, seen, (size_t)dim * dim);
+  }
+  free(d2); free(vis); free(seen);
+  return 0;
+}

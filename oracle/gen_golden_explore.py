@@ -123,3 +123,77 @@ def main(ns, ncases=48, seed=2024):
     print("wrote explore.npz: %d cases, targets detected in %d, infeasible candidates in %d, kb %d cells %.16f" % (
         ncases, sum(1 for n in rec["n_targets"] if n > 0), sum(1 for c in rec["cand_mi"] if (c < 0).any()),
         len(cells), float(out["kb_reward_prior"])))
+
+
+def main_rollouts(ns, ncases=24, K=6, H=10, seed=777):
+    """tests/golden/rollouts.npz: Dec-MCTS simulation rollouts through the UNMODIFIED reference --
+    pydecmcts.DecMCTS.Tree._simulate from the root node with ig_mcts's own callbacks
+    (mcts_sim_state_storer / get_next_pose / mcts_reward, ig_mcts.py:173-265).  The one substitution is the
+    rollout's random choice (mcts_sim_selection_func, :255-257), replaced by a scripted choice so that the
+    sequence is known."""
+    from gym_collision_avoidance.envs.policies.ig_mcts import ig_mcts, MCTS_state
+    from gym_collision_avoidance.envs.policies.pydecmcts.DecMCTS import Tree
+    rng = np.random.default_rng(seed)
+    ref_maps = [ns.Map(30, 30, 0.1, obstacles_of(r)) for r in MAPS]
+    out = {"static_%d" % k: np.packbits(m.static_map.astype(np.uint8)) for k, m in enumerate(ref_maps)}
+    rec = {k: [] for k in ("map_id", "pose", "radius", "belief", "actions", "exclude", "rewards", "end_pose", "obsvd",
+                           "n_infeasible")}
+    for case in range(ncases):
+        mid = case % len(MAPS)
+        radius = float(np.float32(rng.choice([0.2, 0.35, 0.5])))
+        pol = ig_mcts()
+        ego = types.SimpleNamespace(radius=radius)
+        pol.set_param(ego, ref_maps[mid], (30, 30), 0.1, 60.0, 5.0, dt=0.1, xdt=1, mcts_horizon=H)
+        p = free_pose(rng, pol.edfMap, radius)
+        if case % 3 == 1:      # start next to a wall or the map border: infeasible steps
+            for _ in range(400):
+                q = free_pose(rng, pol.edfMap, radius)
+                if pol.edfMap.get_edf_value_from_pose(q) < radius + 0.4 or np.abs(q).max() > 13.0:
+                    p = q
+                    break
+        heading = float(np.float32(rng.uniform(-np.pi, np.pi)))
+        pose = np.append(p, heading)
+        a = rng.integers(0, 4, (60, 60)) * (rng.random((60, 60)) < 0.3)
+        b = rng.integers(0, 6, (60, 60)) * (rng.random((60, 60)) < 0.5)
+        belief = np.float32(1.5 ** a * 0.66 ** b)
+        if case % 5 == 0:
+            belief[:] = 1.0
+        pol.targetMap.map = belief.astype(np.float64).copy()
+        # the other robots' claimed cells: what they would see from a pose near ours (or nothing)
+        other_cells = set()
+        if case % 2 == 0:
+            op = np.append(p + rng.uniform(-2, 2, 2), heading + rng.uniform(-1, 1))
+            other_cells = set(pol.targetMap.getVisibleCells(op))
+        exclude = np.zeros((60, 60), bool)
+        for (i, j) in other_cells:
+            exclude[j, i] = True
+        acts = rng.integers(0, 9, (K, H)).astype(np.uint8)
+        acts[0, :] = 7                                   # straight ahead at full speed until something stops it
+        acts[1, :] = rng.choice([6, 7, 8], H)            # always moving
+        if case % 4 == 2:
+            acts[2, H // 2:] = 255                       # a shorter sequence (a node rollout cut by the horizon)
+        options = ig_mcts.mcts_avail_actions(None, None, 0)
+        rewards, ends, obs_k, ninf = [], [], [], 0
+        for k in range(K):
+            seq = [int(v) for v in acts[k] if v != 255]
+            sel = lambda data, opts, st, seq=seq: opts[seq[len(st.action_seq)]]
+            tree = Tree({"current_pose": pose}, pol.mcts_reward, pol.mcts_avail_actions, pol.mcts_state_storer, sel,
+                        pol.mcts_avail_actions, pol.mcts_sim_state_storer, 5, robot_id=0, horizon=len(seq))
+            res = tree._simulate(1, {1: MCTS_state([], [], set(), set(other_cells), 0)})
+            st = res["temp_state"]
+            assert len(st.action_seq) == len(seq)
+            ninf += sum(1 for t, aa in enumerate(st.action_seq)
+                        if options[seq[t]][0] != 0.0 and aa[0] == 0.0)
+            m = np.zeros((60, 60), bool)
+            for (i, j) in st.obsvd_cells:
+                m[j, i] = True
+            rewards.append(float(res["reward"])); ends.append(np.asarray(st.pose_seq[-1], np.float64))
+            obs_k.append(np.packbits(m))
+        rec["map_id"].append(mid); rec["pose"].append(pose); rec["radius"].append(radius); rec["belief"].append(belief)
+        rec["actions"].append(acts); rec["exclude"].append(np.packbits(exclude)); rec["rewards"].append(rewards)
+        rec["end_pose"].append(ends); rec["obsvd"].append(obs_k); rec["n_infeasible"].append(ninf)
+    for k, v in rec.items():
+        out[k] = np.array(v)
+    np.savez_compressed(os.path.join(GOLDEN, "rollouts.npz"), **out)
+    print("wrote rollouts.npz: %d cases x %d rollouts x %d steps, %d infeasible steps, reward range %.3f..%.3f" % (
+        ncases, K, H, int(np.sum(rec["n_infeasible"])), np.min(rec["rewards"]), np.max(rec["rewards"])))

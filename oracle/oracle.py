@@ -179,6 +179,31 @@ def reward_from_pose(cfg, static_map, pose, belief):
     return float(f(ctypes.byref(cfg), _p(m), _p(pose), _p(belief)))
 
 
+def explore_rollouts(cfg, static_map, pose, radius, belief, actions, exclude=None, xdt=1):
+    """Dec-MCTS simulation rollouts of ONE agent (ig_mcts.py:173-253 driven like DecMCTS._simulate).
+    actions [K,H] uint8 (3*vel_idx + dphi_idx, 255 = ended); exclude [dim,dim] bool or None.
+    Returns dict(rewards [K], end_pose [K,3], obsvd [K,dim,dim] uint8)."""
+    m = np.ascontiguousarray(static_map, dtype=np.uint8).reshape(MAP_DIM, MAP_DIM)
+    pose = np.ascontiguousarray(pose, dtype=np.float64)
+    belief = np.ascontiguousarray(belief, dtype=np.float64)
+    actions = np.ascontiguousarray(actions, dtype=np.uint8)
+    K, H = actions.shape
+    dim = cfg.ig_map_dim
+    ex = None if exclude is None else np.ascontiguousarray(exclude, dtype=np.uint8).reshape(dim, dim)
+    rewards = np.zeros(K, np.float64)
+    end_pose = np.zeros((K, 3), np.float64)
+    obsvd = np.zeros((K, dim, dim), np.uint8)
+    f = lib().casim_oracle_explore_rollouts
+    f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double, ctypes.c_void_p,
+                  ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                  ctypes.c_void_p, ctypes.c_void_p]
+    f.restype = ctypes.c_int
+    rc = f(ctypes.addressof(cfg), _p(m), _p(pose), float(radius), _p(belief), _p(actions), K, H, int(xdt),
+           None if ex is None else _p(ex), _p(rewards), _p(end_pose), _p(obsvd))
+    assert rc == 0
+    return dict(rewards=rewards, end_pose=end_pose, obsvd=obsvd)
+
+
 def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_game_over=None, n_threads=1):
     """ig_greedy.find_next_action for every ig_greedy agent.  belief [E,A,dim,dim] f64 is updated in place.
     Returns dict(policy_actions [E,A,2], best_mi [E,A], cand_mi [E,A,9], counters [4], visible [E,A,dim,dim])."""

@@ -218,3 +218,21 @@ def check_explore_vs_golden(what, z, cases, cfg, belief_after, out, rtol=RTOL):
         decisive = len(srt) < 2 or (srt[-1] - srt[-2]) > 1e-9 * max(1.0, srt[-1]) or srt[-1] == srt[-2]
         if decisive:
             assert_close(out["policy_actions"][n, 0], z["action"][k], "%s action case %d" % (what, k), rtol=1e-6, atol=0)
+
+
+def rollout_cases(z):
+    """tests/golden/rollouts.npz -> list of dicts (one per case) with unpacked masks."""
+    maps = []
+    k = 0
+    while "static_%d" % k in z.files:
+        maps.append(np.unpackbits(z["static_%d" % k])[:300 * 300].reshape(300, 300).astype(np.uint8))
+        k += 1
+    cases = []
+    for n in range(len(z["map_id"])):
+        K = z["actions"][n].shape[0]
+        cases.append(dict(
+            map_id=int(z["map_id"][n]), pose=z["pose"][n], radius=float(z["radius"][n]), belief=z["belief"][n],
+            actions=z["actions"][n], exclude=np.unpackbits(z["exclude"][n])[:3600].reshape(60, 60).astype(bool),
+            rewards=z["rewards"][n], end_pose=z["end_pose"][n],
+            obsvd=np.stack([np.unpackbits(z["obsvd"][n][k])[:3600].reshape(60, 60).astype(bool) for k in range(K)])))
+    return maps, cases

@@ -194,6 +194,22 @@ def test_explore_known_answers(oracle_lib):
     assert abs(r - 1.0740499287868415) < 1e-12 and abs(r - float(z["kb_reward_prior"])) < 1e-12
 
 
+def test_explore_rollouts_vs_reference(oracle_lib):
+    """Dec-MCTS simulation rollouts (ig_mcts.get_next_pose / mcts_sim_state_storer / mcts_reward driven by
+    pydecmcts Tree._simulate): observed-cell sets and feasibility exact, end pose to 1e-12, reward to 1e-9."""
+    oracle = oracle_lib
+    z = H.load("rollouts.npz")
+    maps, cases = H.rollout_cases(z)
+    cfg = oracle.default_config()
+    assert len(cases) >= 20 and int(z["n_infeasible"].sum()) >= 50
+    for n, cs in enumerate(cases):
+        out = oracle.explore_rollouts(cfg, maps[cs["map_id"]], cs["pose"], cs["radius"], cs["belief"].astype(np.float64),
+                                      cs["actions"], exclude=cs["exclude"] if cs["exclude"].any() else None)
+        assert np.array_equal(out["obsvd"].astype(bool), cs["obsvd"]), "case %d observed cells" % n
+        assert np.abs(out["end_pose"] - cs["end_pose"]).max() < 1e-12, "case %d end pose" % n
+        H.assert_close(out["rewards"], cs["rewards"], "case %d rewards" % n, rtol=1e-9, atol=1e-12)
+
+
 def test_ga3c_state_vector_vs_reference(oracle_lib):
     """agents_to_ga3c_cadrl_state (GA3CCADRLPolicy.py:45-106): slot ORDER exact (Python round(x, 2), stable sort on
     (-round(dist, 2), p_orthog), clip to the closest N), values to 1e-12."""
