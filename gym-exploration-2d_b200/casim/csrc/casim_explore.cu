@@ -405,6 +405,173 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
   }
 }
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Dec-MCTS simulation rollouts (policies/ig_mcts.py:173-198 get_next_pose, :223-244 mcts_sim_state_storer,
+ * :246-253 mcts_reward; driven like pydecmcts/DecMCTS.py:233-269 _simulate).  One CTA per (agent, rollout):
+ *   1. thread 0 replays the action sequence (the only serial part: each pose depends on whether the previous
+ *      step was feasible) and writes one bounding box per feasible step;
+ *   2. the boxes are processed like k_explore's candidate poses -- wedge test per box cell, survivors queued,
+ *      sphere tracing per queued cell -- and every visible cell sets its bit in a 4096-bit shared-memory mask
+ *      (obsvd_cells is a set: a cell seen at several steps counts once, and is traced once if a previous batch
+ *      already saw it);
+ *   3. the mask minus the other robots' cells is scored: fp64 mutual information per cell, 64-bit fixed-point
+ *      sum (order-independent).
+ * --------------------------------------------------------------------------------------------------------- */
+#define XR_THREADS 128
+#define XR_MASK_WORDS (64 * 64 / 32)
+
+struct RolloutArgs {
+  DevCfg c;
+  const float4* state;
+  const float* belief;        /* [E*A][dim][dim] */
+  const uint8_t* actions;     /* [E*A][K][H] */
+  const uint32_t* exclude;    /* [E*A][128] or [E*A][K][128] or NULL; bit (j*64 + i) */
+  float* rewards;             /* [E*A][K] */
+  float* end_pose;            /* [E*A][K][3] or NULL */
+  uint32_t* obsvd;            /* [E*A][K][128] or NULL */
+  const int32_t* n_agents;
+  const int32_t* edf_d2;
+  int E, A, n_maps, K, H, xdt, exclude_per_rollout;
+};
+
+__global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
+  const DevCfg& c = p.c;
+  const int gk = blockIdx.x;
+  const int g = gk / p.K;
+  const int e = g / p.A, ai = g - e * p.A;
+  const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+  const size_t N = (size_t)p.E * p.A;
+  const int tid = threadIdx.x;
+  const float4 p5 = p.state[5 * N + g];
+  const bool explorer = ai < n && (__float_as_int(p5.w) & 0xff) == CASIM_POLICY_IG_GREEDY;
+  if (!explorer) {
+    if (tid == 0) {
+      p.rewards[gk] = 0.f;
+      if (p.end_pose) {
+        const float4 p0 = p.state[g];
+        p.end_pose[3 * (size_t)gk] = p0.x; p.end_pose[3 * (size_t)gk + 1] = p0.y; p.end_pose[3 * (size_t)gk + 2] = p0.z;
+      }
+    }
+    if (p.obsvd) p.obsvd[(size_t)gk * XR_MASK_WORDS + tid] = 0u;
+    return;
+  }
+
+  __shared__ PoseBox s_pose[CASIM_ROLLOUT_MAX_H];
+  __shared__ unsigned int s_queue[XQ_CAP];
+  __shared__ unsigned int s_seen[XR_MASK_WORDS];
+  __shared__ unsigned long long s_sum;
+  __shared__ int s_qn, s_nposes;
+
+  const int dim = c.ig_dim;
+  const int32_t* d2 = p.edf_d2 + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
+  unsigned cnt_samples = 0, cnt_clamped = 0;
+  s_seen[tid] = 0u;
+  if (tid == 0) {
+    s_qn = 0;
+    s_sum = 0ull;
+    const float4 p0 = p.state[g], p2 = p.state[2 * N + g];
+    double x = p0.x, y = p0.y, h = p0.z;
+    const double rad = p2.z;
+    const uint8_t* seq = p.actions + (size_t)gk * p.H;
+    int np_ = 0;
+    for (int t = 0; t < p.H; t++) {
+      const int a = seq[t];
+      if (a > 8) break;
+      const double v = 2.0 * (double)(a / 3);
+      const double w = (a % 3 == 0) ? -0.5 * CASIM_PI : ((a % 3 == 2) ? 0.5 * CASIM_PI : 0.0);
+      double nx = x, ny = y, nh = h;
+      bool ok = true;
+      for (int i = 0; i < p.xdt && ok; i++) {
+        double sn, cs;
+        sincos(nh, &sn, &cs);
+        const double vx = cs * v + (-sn) * 0.0, vy = sn * v + cs * 0.0;
+        nx = nx + vx * c.ig_dt;
+        ny = ny + vy * c.ig_dt;
+        nh = nh + w * c.ig_dt;
+        if (v == 0.0) continue;
+        const bool in_map = c.map_hw > nx && c.map_hh > ny && nx > -c.map_hw && ny > -c.map_hh;
+        if (!in_map || !(edf_value(c, d2, nx, ny, cnt_clamped) > rad + 0.1)) ok = false;
+      }
+      if (!ok) continue; /* ig_mcts.py:237-243: the pose stays, nothing is observed */
+      x = nx; y = ny; h = nh;
+      PoseBox b;
+      pose_box(c, x, y, h, b, cnt_clamped);
+      b.feasible = 1;
+      s_pose[np_++] = b;
+    }
+    s_nposes = np_;
+    if (p.end_pose) {
+      p.end_pose[3 * (size_t)gk] = (float)x; p.end_pose[3 * (size_t)gk + 1] = (float)y;
+      p.end_pose[3 * (size_t)gk + 2] = (float)h;
+    }
+  }
+  __syncthreads();
+  const int nposes = s_nposes;
+
+  int pstart = 0;
+  while (pstart < nposes) {
+    int pend = pstart + 1;
+    int total = s_pose[pstart].w * s_pose[pstart].h;
+    while (pend < nposes && total + s_pose[pend].w * s_pose[pend].h <= XQ_CAP) {
+      total += s_pose[pend].w * s_pose[pend].h;
+      pend++;
+    }
+    for (int idx = tid; idx < total; idx += XR_THREADS) {
+      int k = pstart, off = idx;
+      while (off >= s_pose[k].w * s_pose[k].h) {
+        off -= s_pose[k].w * s_pose[k].h;
+        k++;
+      }
+      const PoseBox& b = s_pose[k];
+      const int ii = off / b.h, jj = off - ii * b.h;
+      const int i = b.x0 + ii, j = b.y0 + jj;
+      const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
+      const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
+      if (in_wedge(c, r0, r1)) {
+        const int q = atomicAdd(&s_qn, 1);
+        s_queue[q] = ((unsigned)k << 12) | ((unsigned)j << 6) | (unsigned)i;
+      }
+    }
+    __syncthreads();
+    const int qn = s_qn;
+    for (int q = tid; q < qn; q += XR_THREADS) {
+      const unsigned en = s_queue[q];
+      const int k = (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
+      const int bit = j * 64 + i;
+      if ((s_seen[bit >> 5] >> (bit & 31)) & 1u) continue; /* already in the set (earlier batch, or a faster thread) */
+      const PoseBox& b = s_pose[k];
+      if (line_of_sight(c, d2, b.x, b.y, cell_centre(c, i, c.map_hw), cell_centre(c, j, c.map_hh), cnt_samples, cnt_clamped))
+        atomicOr(&s_seen[bit >> 5], 1u << (bit & 31));
+    }
+    __syncthreads();
+    if (tid == 0) s_qn = 0;
+    __syncthreads();
+    pstart = pend;
+  }
+
+  /* ---- mcts_reward: MI over obsvd_cells minus the other robots' cells (targetMap.py:130-143) ---- */
+  {
+    const unsigned int seen = s_seen[tid]; /* XR_THREADS == XR_MASK_WORDS: one word (32 cells of one row half) each */
+    if (p.obsvd) p.obsvd[(size_t)gk * XR_MASK_WORDS + tid] = seen;
+    unsigned int m = seen;
+    if (p.exclude) m &= ~p.exclude[((size_t)(p.exclude_per_rollout ? gk : g)) * XR_MASK_WORDS + tid];
+    const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
+    const float* belief = p.belief + (size_t)g * dim * dim;
+    long long part = 0;
+    const int j = tid >> 1, i0 = (tid & 1) * 32;
+    while (m) {
+      const int b = __ffs(m) - 1;
+      m &= m - 1;
+      part += __double2ll_rn(cell_mi(c, (double)belief[j * dim + i0 + b], log_rocc, log_remp) * X_MI_SCALE);
+    }
+    /* the set bits are spread unevenly over the words: rebalancing is not worth a second pass at <= ~300 cells */
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL_MASK, part, o);
+    if ((tid & 31) == 0 && part) atomicAdd(&s_sum, (unsigned long long)part);
+  }
+  __syncthreads();
+  if (tid == 0) p.rewards[gk] = (float)((double)(long long)s_sum / X_MI_SCALE);
+}
+
 }  // namespace
 
 cudaError_t casim_launch_explore(casim_handle* h, const float* state, const float* oas, float* belief,
@@ -432,5 +599,32 @@ cudaError_t casim_launch_explore(casim_handle* h, const float* state, const floa
   }
   h->launches++;
   k_explore<<<(unsigned)((size_t)h->E * h->A), X_THREADS, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+
+cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
+                                  int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
+                                  float* end_pose, uint32_t* obsvd, cudaStream_t s) {
+  RolloutArgs a;
+  a.c = h->dc;
+  a.state = reinterpret_cast<const float4*>(state);
+  a.belief = belief;
+  a.actions = actions;
+  a.exclude = exclude;
+  a.rewards = rewards;
+  a.end_pose = end_pose;
+  a.obsvd = obsvd;
+  a.n_agents = h->n_agents;
+  a.edf_d2 = h->edf_d2;
+  a.E = h->E;
+  a.A = h->A;
+  a.n_maps = h->n_maps;
+  a.K = K;
+  a.H = H;
+  a.xdt = xdt;
+  a.exclude_per_rollout = exclude_per_rollout;
+  h->launches++;
+  k_rollouts<<<(unsigned)((size_t)h->E * h->A * K), XR_THREADS, 0, s>>>(a);
   return cudaGetLastError();
 }

@@ -254,6 +254,35 @@ class BatchedSim:
                    "casim_explore_step")
         return self.buf["policy_actions"]
 
+    def explore_rollouts(self, actions, exclude=None, xdt=1, want_end_pose=True, want_obsvd=True):
+        """Dec-MCTS simulation rollouts (ig_mcts.get_next_pose / mcts_sim_state_storer / mcts_reward, the body of
+        pydecmcts Tree._simulate) for every explorer agent from its current pose.
+        actions: uint8 [E,A,K,H] (3*vel_idx + dphi_idx, > 8 ends a sequence); exclude: packed cell masks
+        (``pack_cell_mask``) [E,A,128] or [E,A,K,128] of the other robots' cells, or None.
+        Returns dict(rewards [E,A,K], end_pose [E,A,K,3] | None, obsvd [E,A,K,128] int32 | None)."""
+        if getattr(self, "belief", None) is None:
+            raise _lib.CasimError("explore_rollouts needs enable_exploration() first")
+        actions = torch.as_tensor(actions, dtype=torch.uint8, device=self.device).contiguous()
+        if actions.dim() != 4 or tuple(actions.shape[:2]) != (self.E, self.A):
+            raise _lib.CasimError("actions must be [E, A, K, H]")
+        K, H = int(actions.shape[2]), int(actions.shape[3])
+        per = 0
+        if exclude is not None:
+            exclude = torch.as_tensor(exclude, dtype=torch.int32, device=self.device).contiguous()
+            if tuple(exclude.shape) == (self.E, self.A, K, 128):
+                per = 1
+            elif tuple(exclude.shape) != (self.E, self.A, 128):
+                raise _lib.CasimError("exclude must be [E, A, 128] or [E, A, K, 128]")
+        f32 = dict(dtype=torch.float32, device=self.device)
+        rewards = torch.empty((self.E, self.A, K), **f32)
+        end_pose = torch.empty((self.E, self.A, K, 3), **f32) if want_end_pose else None
+        obsvd = torch.empty((self.E, self.A, K, 128), dtype=torch.int32, device=self.device) if want_obsvd else None
+        _lib.check(self.lib.casim_explore_rollouts(self.handle, _lib.ptr(self.state), _lib.ptr(self.belief),
+                                                   _lib.ptr(actions), K, H, int(xdt), _lib.ptr(exclude), per,
+                                                   _lib.ptr(rewards), _lib.ptr(end_pose), _lib.ptr(obsvd), _stream_ptr()),
+                   "casim_explore_rollouts")
+        return dict(rewards=rewards, end_pose=end_pose, obsvd=obsvd)
+
     def ga3c_set_weights(self, weights, want_debug=True):
         """weights: float32 [170764] parameter blob in the order of include/casim.h (TF variables of
         GA3C_CADRL/network.py: lstm kernel/bias, layer1, layer2, fullyconnected1, logits_p, logits_v)."""
@@ -339,3 +368,21 @@ class BatchedSim:
             iw[..., k] = state[..., k].astype(np.int32)
         packs = np.ascontiguousarray(w.reshape(E, A, W // 4, 4).transpose(2, 0, 1, 3))
         self.state.copy_(torch.from_numpy(packs).to(self.device))
+
+
+def pack_cell_mask(mask):
+    """bool [..., dim, dim] (row j = y cell, column i = x cell, dim <= 64) -> int32 [..., 128] with bit
+    (j * 64 + i) set for every true cell: the mask layout of casim_explore_rollouts (include/casim.h)."""
+    m = np.asarray(mask, dtype=bool)
+    dim = m.shape[-1]
+    full = np.zeros(m.shape[:-2] + (64, 64), dtype=np.uint8)
+    full[..., :dim, :dim] = m
+    bits = np.packbits(full.reshape(m.shape[:-2] + (128, 32)), axis=-1, bitorder="little")
+    return np.ascontiguousarray(bits).view(np.uint32).reshape(m.shape[:-2] + (128,)).view(np.int32)
+
+
+def unpack_cell_mask(words, dim):
+    """Inverse of ``pack_cell_mask``: int32/uint32 [..., 128] -> bool [..., dim, dim]."""
+    w = np.ascontiguousarray(np.asarray(words)).view(np.uint32)
+    b = np.unpackbits(w.view(np.uint8).reshape(w.shape[:-1] + (512,)), axis=-1, bitorder="little")
+    return b.reshape(w.shape[:-1] + (64, 64))[..., :dim, :dim].astype(bool)

@@ -250,6 +250,27 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
                        float* policy_actions, float* best_mi, float* cand_mi, unsigned long long* counters,
                        void* stream);
 
+/* Dec-MCTS simulation rollouts for every ig_* agent (policy id CASIM_POLICY_IG_GREEDY): replaces the body of
+ * pydecmcts Tree._simulate (policies/pydecmcts/DecMCTS.py:233-269) with ig_mcts's callbacks -- get_next_pose
+ * (policies/ig_mcts.py:173-198: first-order step, strict in-map test, EDF clearance > radius + 0.1),
+ * mcts_sim_state_storer (:223-244: an infeasible step keeps the pose and observes nothing) and mcts_reward
+ * (:246-253: mutual information of the cells observed along the path minus the cells the other robots'
+ * paths claim; targetMap.py:43-84, 130-143).  K rollouts per agent, evaluated from the agent's current pose:
+ * a tree node's state followed by its rollout is the root-to-leaf action sequence replayed here.
+ * actions: [E,A,K,H] uint8, action index = 3 * vel_idx + dphi_idx into vel_list (0, 2, 4) x dphi_list
+ *   (-pi/2, 0, pi/2) (:259-265); a value > 8 ends the sequence.  H <= CASIM_ROLLOUT_MAX_H; xdt = ig_mcts.xDT.
+ * belief: [E,A,dim,dim] fp32 odds (read only).
+ * exclude: cell masks of the other robots' observed cells, 128 uint32 per mask, bit (j * 64 + i) for cell
+ *   (x cell i, y cell j); [E,A,128] shared by an agent's K rollouts, or [E,A,K,128] if exclude_per_rollout;
+ *   NULL = nothing claimed.
+ * rewards: [E,A,K] (0 for non-explorers).  end_pose [E,A,K,3] and obsvd [E,A,K,128] (the state's obsvd_cells
+ * as a mask, BEFORE the difference -- what a robot communicates) are optional. */
+#define CASIM_ROLLOUT_MAX_H 32
+#define CASIM_CELL_MASK_WORDS 128
+int casim_explore_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
+                           int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
+                           float* end_pose, uint32_t* obsvd, void* stream);
+
 /* Replaces GA3CCADRLPolicy.find_next_action for every GA3C agent (policies/GA3CCADRLPolicy.py:34-106,
  * GA3C_CADRL/network.py:45-98).  weights: fp32 parameter blob, order kernel/bias of lstm [71,256],[256];
  * layer1 [68,256],[256]; layer2 [256,256],[256]; fullyconnected1 [256,256],[256]; logits_p [256,11],[11]

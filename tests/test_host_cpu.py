@@ -180,3 +180,16 @@ def test_checkpoint_reader_on_reference_checkpoint():
     np.testing.assert_allclose([t[n].astype(np.float64).sum() for n, _ in GA3C_VARIABLES], z["sums"], rtol=0, atol=0)
     for d, name in (("ICRA21", "network_01990000"), ("run-20190727_192048-qedrf08y", "network_01900000")):
         assert ga3c_weights_from_checkpoint(checkpoint_prefix(root, d, name)).shape == (170764,)
+
+
+def test_cell_mask_pack_roundtrip():
+    """pack_cell_mask / unpack_cell_mask: bit (j * 64 + i) of 128 words, the layout of casim_explore_rollouts."""
+    from casim.sim import pack_cell_mask, unpack_cell_mask
+    rng = np.random.default_rng(0)
+    m = rng.random((3, 2, 60, 60)) < 0.2
+    w = pack_cell_mask(m)
+    assert w.shape == (3, 2, 128) and w.dtype == np.int32
+    assert np.array_equal(unpack_cell_mask(w, 60), m)
+    one = np.zeros((60, 60), bool)
+    one[7, 37] = True                       # y cell 7, x cell 37 -> bit 7*64+37 = 485 -> word 15, bit 5
+    assert pack_cell_mask(one).view(np.uint32)[15] == (1 << 5) and pack_cell_mask(one).view(np.uint32).sum() == 32
