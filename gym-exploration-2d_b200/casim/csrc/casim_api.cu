@@ -221,6 +221,7 @@ int casim_destroy(casim_handle* h) {
   cudaFree(h->ticket);
   cudaFree(h->map_planes);
   cudaFree(h->edf_d2);
+  cudaFree(h->edf);
   cudaFree(h->edf_scratch);
   cudaFree(h->grid_maps);
   cudaFree(h->ga3c_w);
@@ -245,14 +246,17 @@ static int ensure_maps(casim_handle* h, int n_maps) {
   if (n_maps <= h->n_maps_alloc) return 0;
   cudaFree(h->map_planes);
   cudaFree(h->edf_d2);
+  cudaFree(h->edf);
   cudaFree(h->edf_scratch);
   cudaFree(h->grid_maps);
   h->grid_maps = nullptr;
   h->map_planes = nullptr;
   h->edf_d2 = h->edf_scratch = nullptr;
+  h->edf = nullptr;
   h->n_maps_alloc = 0;
   CK(cudaMalloc((void**)&h->map_planes, (size_t)n_maps * CASIM_NUM_PLANES * CASIM_PLANE_WORDS * sizeof(uint32_t)));
   CK(cudaMalloc((void**)&h->edf_d2, (size_t)n_maps * CASIM_MAP_DIM * CASIM_MAP_DIM * sizeof(int32_t)));
+  CK(cudaMalloc((void**)&h->edf, (size_t)n_maps * CASIM_MAP_DIM * CASIM_MAP_DIM * sizeof(double)));
   CK(cudaMalloc((void**)&h->edf_scratch, (size_t)n_maps * CASIM_MAP_DIM * CASIM_MAP_DIM * sizeof(int32_t)));
   CK(cudaMalloc((void**)&h->grid_maps, (size_t)n_maps * CASIM_GMAP_WORDS * sizeof(uint32_t)));
   h->n_maps_alloc = n_maps;

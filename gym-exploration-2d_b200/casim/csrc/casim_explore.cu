@@ -45,7 +45,7 @@ struct ExploreArgs {
   float* cand_mi;            /* [E*A][9] or NULL */
   unsigned long long* counters; /* [4] or NULL */
   const int32_t* n_agents;
-  const int32_t* edf_d2;
+  const double* edf;
   const float* init;
   const uint8_t* prev_game_over;
   int E, A, n_maps;
@@ -55,10 +55,11 @@ struct PoseBox {
   double x, y, cs, sn;
   int x0, y0, w, h;       /* box origin and extent in target-map cells (w*h cells) */
   int feasible;
+  int inv_h;              /* ceil(2^18 / h): (off * inv_h) >> 18 == off / h for off < 4096, h <= 64 */
 };
 
 /* edfMap.map[yIdc, xIdc] (edfMap.py:14-19,38-40; no y flip, sic); indices clamped into the array */
-__device__ __forceinline__ double edf_value(const DevCfg& c, const int32_t* __restrict__ d2, double px, double py,
+__device__ __forceinline__ double edf_value(const DevCfg& c, const double* __restrict__ d2, double px, double py,
                                             unsigned& clamped) {
   /* floor((p + half) / cell): the product with 1/cell differs from the quotient by at most an ulp, so its floor is the
    * quotient's unless it lands within 1e-9 of an integer; only then is the division itself evaluated */
@@ -71,11 +72,11 @@ __device__ __forceinline__ double edf_value(const DevCfg& c, const int32_t* __re
   if (!(fy >= 0.0)) { fy = 0.0; clamped++; }
   if (fy > (double)(CASIM_MAP_DIM - 1)) { fy = (double)(CASIM_MAP_DIM - 1); clamped++; }
   int xi = (int)fx, yi = (int)fy;
-  return sqrt((double)__ldg(d2 + yi * CASIM_MAP_DIM + xi)) * c.cell;
+  return __ldg(d2 + yi * CASIM_MAP_DIM + xi);
 }
 
 /* edfMap.py:21-47 checkVisibility */
-__device__ __forceinline__ bool line_of_sight(const DevCfg& c, const int32_t* __restrict__ d2, double px, double py,
+__device__ __forceinline__ bool line_of_sight(const DevCfg& c, const double* __restrict__ d2, double px, double py,
                                               double gx, double gy, unsigned& samples, unsigned& clamped) {
   double dx = gx - px, dy = gy - py;
   double L = sqrt(dx * dx + dy * dy);
@@ -154,6 +155,7 @@ __device__ __forceinline__ void pose_box(const DevCfg& c, double x, double y, do
   b.x0 = x0; b.y0 = y0;
   b.w = max(x1 - x0, 0);
   b.h = max(y1 - y0, 0);
+  b.inv_h = b.h > 0 ? ((1 << 18) + b.h - 1) / b.h : 0;
 }
 
 __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
@@ -189,7 +191,7 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
 
   const int dim = c.ig_dim;
   float* belief = p.belief + (size_t)g * dim * dim;
-  const int32_t* d2 = p.edf_d2 + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
+  const double* d2 = p.edf + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
   unsigned cnt_tested = 0, cnt_samples = 0, cnt_visible = 0, cnt_clamped = 0;
 
   if (tid == 0) {
@@ -292,14 +294,16 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
         pend++;
       }
     /* ---- phase 1: range / FOV wedge test of every box cell (targetMap.py:73-79) ---- */
+    int k = pstart, base = 0, cnt = s_pose[pstart].w * s_pose[pstart].h; /* idx only grows: the pose cursor never rewinds */
     for (int idx = tid; idx < total; idx += X_THREADS) {
-      int k = pstart, off = idx;
-      while (off >= s_pose[k].w * s_pose[k].h) {
-        off -= s_pose[k].w * s_pose[k].h;
+      while (idx - base >= cnt) {
+        base += cnt;
         k++;
+        cnt = s_pose[k].w * s_pose[k].h;
       }
+      const int off = idx - base;
       const PoseBox& b = s_pose[k];
-      int ii = off / b.h, jj = off - ii * b.h;
+      int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
       int i = b.x0 + ii, j = b.y0 + jj;
       double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
       double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy; /* R = ((c, s), (-s, c)) */
@@ -430,7 +434,7 @@ struct RolloutArgs {
   float* end_pose;            /* [E*A][K][3] or NULL */
   uint32_t* obsvd;            /* [E*A][K][128] or NULL */
   const int32_t* n_agents;
-  const int32_t* edf_d2;
+  const double* edf;
   int E, A, n_maps, K, H, xdt, exclude_per_rollout;
 };
 
@@ -463,7 +467,7 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   __shared__ int s_qn, s_nposes;
 
   const int dim = c.ig_dim;
-  const int32_t* d2 = p.edf_d2 + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
+  const double* d2 = p.edf + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
   unsigned cnt_samples = 0, cnt_clamped = 0;
   s_seen[tid] = 0u;
   if (tid == 0) {
@@ -494,10 +498,8 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
       }
       if (!ok) continue; /* ig_mcts.py:237-243: the pose stays, nothing is observed */
       x = nx; y = ny; h = nh;
-      PoseBox b;
-      pose_box(c, x, y, h, b, cnt_clamped);
-      b.feasible = 1;
-      s_pose[np_++] = b;
+      s_pose[np_].x = x; s_pose[np_].y = y; s_pose[np_].cs = h; /* heading parked in .cs until the boxes are built */
+      np_++;
     }
     s_nposes = np_;
     if (p.end_pose) {
@@ -507,6 +509,13 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   }
   __syncthreads();
   const int nposes = s_nposes;
+  if (tid < nposes) { /* the boxes (three fp64 sincos each) do not depend on one another: one thread per pose */
+    PoseBox b;
+    pose_box(c, s_pose[tid].x, s_pose[tid].y, s_pose[tid].cs, b, cnt_clamped);
+    b.feasible = 1;
+    s_pose[tid] = b;
+  }
+  __syncthreads();
 
   int pstart = 0;
   while (pstart < nposes) {
@@ -516,14 +525,16 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
       total += s_pose[pend].w * s_pose[pend].h;
       pend++;
     }
+    int k = pstart, base = 0, cnt = s_pose[pstart].w * s_pose[pstart].h;
     for (int idx = tid; idx < total; idx += XR_THREADS) {
-      int k = pstart, off = idx;
-      while (off >= s_pose[k].w * s_pose[k].h) {
-        off -= s_pose[k].w * s_pose[k].h;
+      while (idx - base >= cnt) {
+        base += cnt;
         k++;
+        cnt = s_pose[k].w * s_pose[k].h;
       }
+      const int off = idx - base;
       const PoseBox& b = s_pose[k];
-      const int ii = off / b.h, jj = off - ii * b.h;
+      const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
       const int i = b.x0 + ii, j = b.y0 + jj;
       const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
       const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
@@ -587,7 +598,7 @@ cudaError_t casim_launch_explore(casim_handle* h, const float* state, const floa
   a.cand_mi = cand_mi;
   a.counters = counters;
   a.n_agents = h->n_agents;
-  a.edf_d2 = h->edf_d2;
+  a.edf = h->edf;
   a.init = h->init;
   a.prev_game_over = h->prev_game_over;
   a.E = h->E;
@@ -616,7 +627,7 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   a.end_pose = end_pose;
   a.obsvd = obsvd;
   a.n_agents = h->n_agents;
-  a.edf_d2 = h->edf_d2;
+  a.edf = h->edf;
   a.E = h->E;
   a.A = h->A;
   a.n_maps = h->n_maps;

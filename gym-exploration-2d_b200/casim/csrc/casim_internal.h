@@ -57,6 +57,7 @@ struct casim_handle {
   /* maps */
   int n_maps;              /* 0 = no obstacles */
   uint32_t* map_planes;    /* [n_maps_alloc][4][300][10] bit planes (plane 0 = static_map) */
+  double* edf;             /* [n_maps_alloc][300][300] edfMap.map itself: sqrt(edf_d2) * cell in fp64 */
   int32_t* edf_d2;         /* [n_maps_alloc][300][300] squared distance (cells^2) to the nearest occupied cell;
                               edfMap.map[r][c] == sqrt(edf_d2) * cell exactly (information_models/edfMap.py:11-12) */
   int32_t* edf_scratch;    /* [n_maps_alloc][300][300] column pass */

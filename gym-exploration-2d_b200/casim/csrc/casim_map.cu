@@ -151,7 +151,7 @@ __global__ void k_edt_cols(int n_maps, const uint32_t* planes, int* gdist) {
 }
 
 /* pass 2: exact minimum over the row of dx^2 + g^2 (300 candidates per cell), sqrt, * cell */
-__global__ void k_edt_rows(int n_maps, const int* gdist, int32_t* edf_d2) {
+__global__ void k_edt_rows(int n_maps, const int* gdist, int32_t* edf_d2, double* edf, double cell) {
   __shared__ int sg[CASIM_MAP_DIM];
   int m = blockIdx.x / CASIM_MAP_DIM, row = blockIdx.x - m * CASIM_MAP_DIM;
   const int* g = gdist + ((size_t)m * CASIM_MAP_DIM + row) * CASIM_MAP_DIM;
@@ -170,7 +170,9 @@ __global__ void k_edt_rows(int n_maps, const int* gdist, int32_t* edf_d2) {
     /* no obstacle anywhere: scipy returns the distance to a non-existent background; the exploration
      * kernels are only used with obstacles, keep a large finite value */
     size_t o = ((size_t)m * CASIM_MAP_DIM + row) * CASIM_MAP_DIM + col;
-    edf_d2[o] = best < 0 ? (1 << 30) : (int32_t)best;
+    const int32_t d2 = best < 0 ? (1 << 30) : (int32_t)best;
+    edf_d2[o] = d2;
+    edf[o] = sqrt((double)d2) * cell; /* edfMap.map (edfMap.py:11-12), the value the exploration kernels sample */
   }
 }
 
@@ -207,6 +209,6 @@ cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_ou
   }
   int* gdist = h->edf_scratch;
   k_edt_cols<<<(n_maps * CASIM_MAP_DIM + 127) / 128, 128, 0, s>>>(n_maps, h->map_planes, gdist);
-  k_edt_rows<<<n_maps * CASIM_MAP_DIM, 128, 0, s>>>(n_maps, gdist, h->edf_d2);
+  k_edt_rows<<<n_maps * CASIM_MAP_DIM, 128, 0, s>>>(n_maps, gdist, h->edf_d2, h->edf, h->dc.cell);
   return cudaGetLastError();
 }
