@@ -421,7 +421,7 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
  *   3. the mask minus the other robots' cells is scored: fp64 mutual information per cell, 64-bit fixed-point
  *      sum (order-independent).
  * --------------------------------------------------------------------------------------------------------- */
-#define XR_THREADS 128
+#define XR_QCAP 2048         /* box cells per batch (queue entries are 16 bit: 4-bit pose, 6+6-bit cell) */
 #define XR_MASK_WORDS (64 * 64 / 32)
 
 struct RolloutArgs {
@@ -435,9 +435,10 @@ struct RolloutArgs {
   uint32_t* obsvd;            /* [E*A][K][128] or NULL */
   const int32_t* n_agents;
   const double* edf;
-  int E, A, n_maps, K, H, xdt, exclude_per_rollout;
+  int E, A, n_maps, K, H, xdt, exclude_per_rollout, qcap;
 };
 
+template <int XR_THREADS>
 __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   const DevCfg& c = p.c;
   const int gk = blockIdx.x;
@@ -456,12 +457,13 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
         p.end_pose[3 * (size_t)gk] = p0.x; p.end_pose[3 * (size_t)gk + 1] = p0.y; p.end_pose[3 * (size_t)gk + 2] = p0.z;
       }
     }
-    if (p.obsvd) p.obsvd[(size_t)gk * XR_MASK_WORDS + tid] = 0u;
+    if (p.obsvd)
+      for (int w = tid; w < XR_MASK_WORDS; w += XR_THREADS) p.obsvd[(size_t)gk * XR_MASK_WORDS + w] = 0u;
     return;
   }
 
   __shared__ PoseBox s_pose[CASIM_ROLLOUT_MAX_H];
-  __shared__ unsigned int s_queue[XQ_CAP];
+  __shared__ unsigned short s_queue[XR_QCAP];
   __shared__ unsigned int s_seen[XR_MASK_WORDS];
   __shared__ unsigned long long s_sum;
   __shared__ int s_qn, s_nposes;
@@ -469,7 +471,7 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   const int dim = c.ig_dim;
   const double* d2 = p.edf + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
   unsigned cnt_samples = 0, cnt_clamped = 0;
-  s_seen[tid] = 0u;
+  for (int w = tid; w < XR_MASK_WORDS; w += XR_THREADS) s_seen[w] = 0u;
   if (tid == 0) {
     s_qn = 0;
     s_sum = 0ull;
@@ -521,7 +523,7 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   while (pstart < nposes) {
     int pend = pstart + 1;
     int total = s_pose[pstart].w * s_pose[pstart].h;
-    while (pend < nposes && total + s_pose[pend].w * s_pose[pend].h <= XQ_CAP) {
+    while (pend < nposes && pend - pstart < 16 && total + s_pose[pend].w * s_pose[pend].h <= p.qcap) {
       total += s_pose[pend].w * s_pose[pend].h;
       pend++;
     }
@@ -536,18 +538,19 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
       const PoseBox& b = s_pose[k];
       const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
       const int i = b.x0 + ii, j = b.y0 + jj;
+      if ((s_seen[(j * 64 + i) >> 5] >> (i & 31)) & 1u) continue; /* in the set since an earlier batch */
       const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
       const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
       if (in_wedge(c, r0, r1)) {
         const int q = atomicAdd(&s_qn, 1);
-        s_queue[q] = ((unsigned)k << 12) | ((unsigned)j << 6) | (unsigned)i;
+        s_queue[q] = (unsigned short)(((unsigned)(k - pstart) << 12) | ((unsigned)j << 6) | (unsigned)i);
       }
     }
     __syncthreads();
     const int qn = s_qn;
     for (int q = tid; q < qn; q += XR_THREADS) {
       const unsigned en = s_queue[q];
-      const int k = (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
+      const int k = pstart + (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
       const int bit = j * 64 + i;
       if ((s_seen[bit >> 5] >> (bit & 31)) & 1u) continue; /* already in the set (earlier batch, or a faster thread) */
       const PoseBox& b = s_pose[k];
@@ -562,20 +565,21 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
 
   /* ---- mcts_reward: MI over obsvd_cells minus the other robots' cells (targetMap.py:130-143) ---- */
   {
-    const unsigned int seen = s_seen[tid]; /* XR_THREADS == XR_MASK_WORDS: one word (32 cells of one row half) each */
-    if (p.obsvd) p.obsvd[(size_t)gk * XR_MASK_WORDS + tid] = seen;
-    unsigned int m = seen;
-    if (p.exclude) m &= ~p.exclude[((size_t)(p.exclude_per_rollout ? gk : g)) * XR_MASK_WORDS + tid];
     const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
     const float* belief = p.belief + (size_t)g * dim * dim;
     long long part = 0;
-    const int j = tid >> 1, i0 = (tid & 1) * 32;
-    while (m) {
-      const int b = __ffs(m) - 1;
-      m &= m - 1;
-      part += __double2ll_rn(cell_mi(c, (double)belief[j * dim + i0 + b], log_rocc, log_remp) * X_MI_SCALE);
+    for (int w = tid; w < XR_MASK_WORDS; w += XR_THREADS) { /* one word = 32 cells of one half row */
+      const unsigned int seen = s_seen[w];
+      if (p.obsvd) p.obsvd[(size_t)gk * XR_MASK_WORDS + w] = seen;
+      unsigned int m = seen;
+      if (p.exclude) m &= ~p.exclude[((size_t)(p.exclude_per_rollout ? gk : g)) * XR_MASK_WORDS + w];
+      const int j = w >> 1, i0 = (w & 1) * 32;
+      while (m) {
+        const int b = __ffs(m) - 1;
+        m &= m - 1;
+        part += __double2ll_rn(cell_mi(c, (double)belief[j * dim + i0 + b], log_rocc, log_remp) * X_MI_SCALE);
+      }
     }
-    /* the set bits are spread unevenly over the words: rebalancing is not worth a second pass at <= ~300 cells */
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL_MASK, part, o);
     if ((tid & 31) == 0 && part) atomicAdd(&s_sum, (unsigned long long)part);
   }
@@ -636,6 +640,12 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   a.xdt = xdt;
   a.exclude_per_rollout = exclude_per_rollout;
   h->launches++;
-  k_rollouts<<<(unsigned)((size_t)h->E * h->A * K), XR_THREADS, 0, s>>>(a);
+  static const int threads = [] { const char* v = getenv("CASIM_XR_THREADS"); return v ? atoi(v) : 64; }();
+  static const int qcap = [] { const char* v = getenv("CASIM_XR_QCAP"); int q = v ? atoi(v) : 1024; return q < 1 ? 1 : (q > XR_QCAP ? XR_QCAP : q); }();
+  a.qcap = qcap;
+  const unsigned grid = (unsigned)((size_t)h->E * h->A * K);
+  if (threads == 32) k_rollouts<32><<<grid, 32, 0, s>>>(a);
+  else if (threads == 128) k_rollouts<128><<<grid, 128, 0, s>>>(a);
+  else k_rollouts<64><<<grid, 64, 0, s>>>(a);
   return cudaGetLastError();
 }
