@@ -453,14 +453,14 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
 
 int casim_explore_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                            int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
-                           float* end_pose, uint32_t* obsvd, void* stream) {
+                           float* end_pose, uint32_t* obsvd, int32_t* n_feasible, void* stream) {
   REQUIRE(h && state && belief && actions && rewards, "null argument");
   REQUIRE(h->n_maps > 0, "casim_explore_rollouts needs a static map (casim_set_obstacles / casim_set_map)");
   REQUIRE(K >= 1 && H >= 1 && H <= CASIM_ROLLOUT_MAX_H, "rollouts: K >= 1 and 1 <= H <= CASIM_ROLLOUT_MAX_H");
   REQUIRE(xdt >= 1, "rollouts: xdt >= 1");
   REQUIRE((size_t)h->E * h->A * (size_t)K <= 0x7fffffffull, "rollouts: E * A * K exceeds the grid limit");
   CK(casim_launch_rollouts(h, state, belief, actions, K, H, xdt, exclude, exclude_per_rollout, rewards, end_pose, obsvd,
-                           (cudaStream_t)stream));
+                           n_feasible, (cudaStream_t)stream));
   return 0;
 }
 

@@ -433,6 +433,7 @@ struct RolloutArgs {
   float* rewards;             /* [E*A][K] */
   float* end_pose;            /* [E*A][K][3] or NULL */
   uint32_t* obsvd;            /* [E*A][K][128] or NULL */
+  int32_t* n_feasible;        /* [E*A][K] or NULL: steps of the sequence that were applied */
   const int32_t* n_agents;
   const double* edf;
   int E, A, n_maps, K, H, xdt, exclude_per_rollout, qcap;
@@ -452,6 +453,7 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   if (!explorer) {
     if (tid == 0) {
       p.rewards[gk] = 0.f;
+      if (p.n_feasible) p.n_feasible[gk] = 0;
       if (p.end_pose) {
         const float4 p0 = p.state[g];
         p.end_pose[3 * (size_t)gk] = p0.x; p.end_pose[3 * (size_t)gk + 1] = p0.y; p.end_pose[3 * (size_t)gk + 2] = p0.z;
@@ -504,6 +506,7 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
       np_++;
     }
     s_nposes = np_;
+    if (p.n_feasible) p.n_feasible[gk] = np_;
     if (p.end_pose) {
       p.end_pose[3 * (size_t)gk] = (float)x; p.end_pose[3 * (size_t)gk + 1] = (float)y;
       p.end_pose[3 * (size_t)gk + 2] = (float)h;
@@ -620,7 +623,7 @@ cudaError_t casim_launch_explore(casim_handle* h, const float* state, const floa
 
 cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                                   int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
-                                  float* end_pose, uint32_t* obsvd, cudaStream_t s) {
+                                  float* end_pose, uint32_t* obsvd, int32_t* n_feasible, cudaStream_t s) {
   RolloutArgs a;
   a.c = h->dc;
   a.state = reinterpret_cast<const float4*>(state);
@@ -630,6 +633,7 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   a.rewards = rewards;
   a.end_pose = end_pose;
   a.obsvd = obsvd;
+  a.n_feasible = n_feasible;
   a.n_agents = h->n_agents;
   a.edf = h->edf;
   a.E = h->E;

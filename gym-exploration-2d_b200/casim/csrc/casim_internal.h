@@ -107,7 +107,7 @@ cudaError_t casim_launch_explore(casim_handle* h, const float* state, const floa
                                  unsigned long long* counters, cudaStream_t s);
 cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                                   int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
-                                  float* end_pose, uint32_t* obsvd, cudaStream_t s);
+                                  float* end_pose, uint32_t* obsvd, int32_t* n_feasible, cudaStream_t s);
 cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy_actions, int32_t* action_idx,
                               float* probs, float* nn_input, int use_tc, cudaStream_t s);
 cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* coop, const casim_rvo_params* prm,

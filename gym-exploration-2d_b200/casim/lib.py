@@ -57,7 +57,7 @@ SYMBOLS = {
     "casim_explore_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
     "casim_explore_rollouts": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
-                                       c_void_p, c_void_p, c_void_p, c_void_p]),
+                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "casim_ga3c_set_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "casim_ga3c_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "casim_rvo_default_params": (None, [ctypes.POINTER(RvoParams)]),

@@ -1,0 +1,269 @@
+"""Dec-MCTS planner for the explorer agents of a batch: the reference's ``Tree`` (policies/pydecmcts/DecMCTS.py:62-420)
+with ig_mcts's callbacks (policies/ig_mcts.py:79-109, 173-265), grown for every tree in lock-step -- one node per
+tree per ``grow`` -- with the expensive part (expansion feasibility and the ``nsims`` simulations, 86 % of the
+reference's step time) evaluated by ONE ``casim_explore_rollouts`` launch per iteration.
+
+What stays on the host is the tree bookkeeping, as arrays over [tree, node]: UCT selection (``_select``, :140-153),
+expansion (``_expansion``, :201-231), statistics + discounted back-propagation (``grow``, :334-357), the top-n action
+distribution (``_update_distribution``, :162-180) and the communication of best rollouts between the robots of one
+environment (``send_comms`` / ``receive_comms`` / ``_get_system_state``, :182-194, :364-380).
+
+Node numbering follows the reference (creation order; node 0 here = node 1 there), so that a tree grown here and a
+tree grown by the reference with the same random choices are the same tree.
+"""
+import numpy as np
+
+N_ACTIONS = 9
+END = 255
+VEL_LIST = (0.0, 2.0, 4.0)                       # ig_mcts.py:259-265 mcts_avail_actions
+DPHI_LIST = (-0.5 * np.pi, 0.0, 0.5 * np.pi)
+
+
+def action_value(idx):
+    """action index -> the [vel, dphi] array of mcts_avail_actions (vel-major order)."""
+    idx = np.asarray(idx)
+    return np.stack([np.take(VEL_LIST, idx // 3), np.take(DPHI_LIST, idx % 3)], -1)
+
+
+class ActionDistribution:
+    """DecMCTS.py:21-59 for every tree: ``seqs`` [T,n,H] uint8 best rollouts of the top-n nodes (END padded), ``q`` [T,n]
+    normalised weights (0 = slot unused), ``masks`` [T,n,128] int32 observed-cell masks of those rollouts."""
+
+    def __init__(self, seqs, q, masks=None):
+        self.seqs, self.masks = seqs, masks
+        q = np.asarray(q, np.float64)
+        tot = q.sum(1, keepdims=True)
+        used = (seqs[:, :, 0] != END)
+        n_used = used.sum(1, keepdims=True)
+        uniform = np.where(used, 1.0 / np.maximum(n_used, 1), 0.0)        # sum(q) == 0 -> uniform (:39-40)
+        self.q = np.where(tot > 0, q / np.where(tot > 0, tot, 1.0), uniform)
+        self.n = n_used[:, 0]
+
+
+class BatchedDecMCTS:
+    """``evaluate(actions [T,K,H] uint8, exclude [T,128] int32 | None) -> (rewards [T,K], n_feasible [T,K])`` is the
+    rollout evaluator (``sim_evaluator`` below wraps casim_explore_rollouts).  T trees, all rooted at their agent's
+    current pose."""
+
+    def __init__(self, n_trees, evaluate, horizon=10, c_p=1.0, comm_n=5, seed=0, reference_order=False):
+        self.T, self.H, self.c_p, self.comm_n = int(n_trees), int(horizon), float(c_p), int(comm_n)
+        self.evaluate = evaluate
+        self.reference_order = bool(reference_order)       # draw from np.random exactly like the reference (tests)
+        self.rng = np.random.default_rng(seed)
+        self.comms = []                                    # list of (ActionDistribution, valid [T] bool)
+        self.launches = 0
+        self._alloc(1 + N_ACTIONS * 4)
+        T = self.T
+        self.n_nodes = np.ones(T, np.int64)
+        # root (Tree.__init__, :120-133): mu = N = best_reward = 0, stage 0, then _expansion(root)
+        self._expand(np.zeros(T, np.int64), self._rollouts(np.zeros(T, np.int64), 0, None)[1])
+
+    # ---------------------------------------------------------------- storage
+    def _alloc(self, M):
+        T, H = self.T, self.H
+        new = dict(parent=np.full((T, M), -1, np.int64), stage=np.zeros((T, M), np.int64),
+                   mu=np.zeros((T, M)), N=np.zeros((T, M)), best_reward=np.zeros((T, M)),
+                   child=np.full((T, M, N_ACTIONS), -1, np.int64), nchild=np.zeros((T, M), np.int64),
+                   path=np.full((T, M, H), END, np.uint8), has_rollout=np.zeros((T, M), bool),
+                   best_seq=np.full((T, M, H), END, np.uint8))
+        if hasattr(self, "M"):
+            for k, v in new.items():
+                v[:, :self.M] = getattr(self, k)
+        for k, v in new.items():
+            setattr(self, k, v)
+        self.M = M
+
+    def _rows(self):
+        return np.arange(self.T)
+
+    # ---------------------------------------------------------------- the one GPU call per iteration
+    def _rollouts(self, node, nsims, exclude):
+        """Sequences for `node` of every tree: its 9 one-step extensions (expansion feasibility) followed by `nsims`
+        random completions up to the horizon (_simulate, :233-269).  Returns (sim_seqs [T,nsims,H], feasible [T,9],
+        rewards [T,nsims]).  The sequences keep the REQUESTED actions: replaying one reproduces its infeasible
+        steps, whereas the reference's stored [0, 0] substitute (:243) would be a feasible stand-still step."""
+        T, H = self.T, self.H
+        r = self._rows()
+        path, stage = self.path[r, node], self.stage[r, node]
+        seqs = np.repeat(path[:, None, :], N_ACTIONS + nsims, axis=1)
+        can = stage < H
+        ext = seqs[:, :N_ACTIONS]
+        ext[r[can], :, stage[can]] = np.arange(N_ACTIONS, dtype=np.uint8)[None, :]
+        if nsims:
+            if self.reference_order:        # per tree, per simulation, per step: np.random.choice(len(options)), ig_mcts.py:257
+                draws = np.full((T, nsims, H), END, np.uint8)
+                for t in range(T):
+                    for i in range(nsims):
+                        for d in range(stage[t], H):
+                            draws[t, i, d] = np.random.choice(N_ACTIONS)
+            else:
+                draws = self.rng.integers(0, N_ACTIONS, (T, nsims, H)).astype(np.uint8)
+            tail = np.arange(H)[None, None, :] >= stage[:, None, None]
+            sims = seqs[:, N_ACTIONS:]
+            sims[tail.repeat(nsims, 1)] = draws[tail.repeat(nsims, 1)]
+        rewards, n_feasible = self.evaluate(seqs, exclude)
+        self.launches += 1
+        feasible = can[:, None] & (n_feasible[:, :N_ACTIONS] == (stage + 1)[:, None])
+        return seqs[:, N_ACTIONS:], feasible, np.asarray(rewards[:, N_ACTIONS:], np.float64)
+
+    def _expand(self, node, feasible):
+        """_expansion (:201-231): a child per feasible action, in action order; nothing at stage == horizon."""
+        T = self.T
+        r = self._rows()
+        need = int((self.n_nodes + N_ACTIONS).max())
+        if need > self.M:
+            self._alloc(max(need, 2 * self.M))
+        for a in range(N_ACTIONS):
+            ok = feasible[:, a] & (self.nchild[r, node] < N_ACTIONS)
+            t = r[ok]
+            if t.size == 0:
+                continue
+            new, par = self.n_nodes[t], node[t]
+            self.parent[t, new] = par
+            self.stage[t, new] = self.stage[t, par] + 1
+            self.path[t, new] = self.path[t, par]
+            self.path[t, new, self.stage[t, par]] = a
+            self.child[t, par, self.nchild[t, par]] = new
+            self.nchild[t, par] += 1
+            self.n_nodes[t] += 1
+
+    # ---------------------------------------------------------------- one iteration
+    def _system_exclude(self):
+        """_get_system_state (:182-194): one weighted-random best rollout per communicating robot; the union of their
+        observed cells is what mcts_reward subtracts (ig_mcts.py:246-253)."""
+        if not self.comms:
+            return None
+        out = np.zeros((self.T, 128), np.int32)
+        for dist, valid in self.comms:
+            n = dist.q.shape[1]
+            if self.reference_order:
+                pick = np.array([np.random.choice(n, p=dist.q[t]) if valid[t] else 0 for t in range(self.T)])
+            else:
+                u = self.rng.random(self.T)[:, None]
+                pick = np.minimum((u > np.cumsum(dist.q, 1)).sum(1), n - 1)
+            out |= np.where(valid[:, None], dist.masks[self._rows(), pick], 0)
+        return out
+
+    def grow(self, nsims=10, gamma=0.9):
+        """Tree.grow (:273-360) for every tree.  Returns the average simulation reward [T]."""
+        T = self.T
+        r = self._rows()
+        exclude = self._system_exclude()                 # sampled first, like the reference
+        # SELECTION: descend by UCT while the node has children (:287-288, _select :140-153, _UCT :14-18)
+        node = np.zeros(T, np.int64)
+        while True:
+            nc = self.nchild[r, node]
+            go = nc > 0
+            if not go.any():
+                break
+            ch = self.child[r, node]                                          # [T,9], -1 = none
+            chs = np.where(ch >= 0, ch, 0)
+            mu_j, n_j = self.mu[r[:, None], chs], self.N[r[:, None], chs]
+            n_p = self.N[r, node][:, None]
+            with np.errstate(divide="ignore", invalid="ignore"):
+                uct = mu_j + 2.0 * self.c_p * (2.0 * np.log(n_p) / n_j) ** 0.5
+            uct = np.where(n_j == 0, np.inf, uct)
+            uct = np.where(ch >= 0, uct, -np.inf)
+            best = ch[r, np.argmax(uct, 1)]                                   # first maximum, like np.argmax on the list
+            node = np.where(go, best, node)
+        # EXPANSION + SIMULATION: one launch
+        seqs, feasible, rewards = self._rollouts(node, nsims, exclude)
+        self._expand(node, feasible)
+        avg = self._seq_mean(rewards)
+        k_best = np.argmax(rewards, 1)                                        # first strict maximum (:330-332)
+        best_reward = rewards[r, k_best]
+        best_seq = seqs[r, k_best]
+        self.mu[r, node] = avg
+        self.best_reward[r, node] = best_reward
+        self.N[r, node] = 1.0
+        self.best_seq[r, node] = best_seq
+        self.has_rollout[r, node] = True
+        # BACK-PROPAGATION (:341-357)
+        cur = node.copy()
+        while True:
+            up = self.parent[r, cur]
+            go = up >= 0
+            if not go.any():
+                break
+            t, u = r[go], up[go]
+            n_old = self.N[t, u]
+            self.mu[t, u] = (gamma * self.mu[t, u] * n_old + avg[go]) / (n_old + 1.0)
+            self.N[t, u] = gamma * n_old + 1.0
+            better = best_reward[go] > self.best_reward[t, u]
+            tb, ub = t[better], u[better]
+            self.best_reward[tb, ub] = best_reward[go][better]
+            self.best_seq[tb, ub] = best_seq[go][better]
+            self.has_rollout[tb, ub] = True
+            cur = np.where(go, up, cur)
+        self.last_node = node
+        return avg
+
+    @staticmethod
+    def _seq_mean(rewards):
+        """avg_reward accumulated left to right then divided (:323, :334), not a pairwise sum"""
+        acc = np.zeros(rewards.shape[0])
+        for i in range(rewards.shape[1]):
+            acc = acc + rewards[:, i]
+        return acc / rewards.shape[1]
+
+    # ---------------------------------------------------------------- results and communication
+    def distribution(self, with_masks=None):
+        """_update_distribution (:162-180): the comm_n non-root nodes of highest mu (ties: lowest node id, as the
+        stable reversed sort gives), those that hold a best rollout, weighted by mu^2.  ``with_masks`` = an evaluator
+        returning observed-cell masks for [T,n,H] sequences (needed only when the distribution is communicated)."""
+        T, n = self.T, self.comm_n
+        r = self._rows()
+        mu = np.where(np.arange(self.M)[None, :] < self.n_nodes[:, None], self.mu, -np.inf)
+        mu[:, 0] = -np.inf
+        top = np.argsort(-mu, axis=1, kind="stable")[:, :n]                   # [T,n]
+        ok = np.isfinite(mu[r[:, None], top]) & self.has_rollout[r[:, None], top]
+        seqs = np.where(ok[:, :, None], self.best_seq[r[:, None], top], END).astype(np.uint8)
+        q = np.where(ok, self.mu[r[:, None], top] ** 2, 0.0)
+        # compact the kept entries to the front (the reference builds X, q from the kept nodes only)
+        order = np.argsort(~ok, axis=1, kind="stable")
+        seqs, q, top = seqs[r[:, None], order], q[r[:, None], order], top[r[:, None], order]
+        d = ActionDistribution(seqs, q, with_masks(seqs) if with_masks is not None else None)
+        d.nodes = np.where(np.take_along_axis(ok, order, 1), top, -1)
+        return d
+
+    def best_action_index(self):
+        """ig_mcts.find_next_action's result (ig_mcts.py:106-109): the first action of the best rollout of the
+        highest-mu node = the first step of that node's path.  -1 where the distribution is empty (the reference
+        raises IndexError there)."""
+        d = self.distribution()
+        a = d.seqs[:, 0, 0].astype(np.int64)
+        return np.where(d.n > 0, a, -1)
+
+    def receive_comms(self, dist, valid=None):
+        """receive_comms (:367-380) for every tree at once: ``dist`` holds, per tree, ONE other robot's distribution
+        (with masks); ``valid`` [T] marks the trees that do have such a robot.  Call once per communicating robot."""
+        valid = np.ones(self.T, bool) if valid is None else np.asarray(valid, bool)
+        self.comms.append((dist, valid & (dist.n > 0)))
+
+
+def sim_evaluator(sim, xdt=1):
+    """The GPU evaluator: trees = the explorer agents of ``sim`` (policy id IG_GREEDY) in (env, agent) order.
+    Returns (n_trees, evaluate, masks_of) for BatchedDecMCTS / distribution(with_masks=)."""
+    import torch
+    from . import layout as L
+    types = sim._keep["types"].cpu().numpy()
+    te, ta = np.nonzero((types & 0xff) == L.POLICY_IG_GREEDY)
+    E, A = sim.E, sim.A
+
+    def scatter(x, fill, dtype):
+        full = np.full((E, A) + x.shape[1:], fill, dtype)
+        full[te, ta] = x
+        return full
+
+    def evaluate(actions, exclude):
+        ex = None if exclude is None else scatter(exclude, 0, np.int32)
+        out = sim.explore_rollouts(scatter(actions, END, np.uint8), exclude=ex, xdt=xdt, want_end_pose=False,
+                                   want_obsvd=False)
+        torch.cuda.current_stream().synchronize()
+        return out["rewards"].cpu().numpy()[te, ta].astype(np.float64), out["n_feasible"].cpu().numpy()[te, ta]
+
+    def masks_of(seqs):
+        out = sim.explore_rollouts(scatter(seqs, END, np.uint8), xdt=xdt, want_end_pose=False, want_obsvd=True)
+        return out["obsvd"].cpu().numpy()[te, ta]
+
+    return len(te), evaluate, masks_of, (te, ta)

@@ -259,7 +259,8 @@ class BatchedSim:
         pydecmcts Tree._simulate) for every explorer agent from its current pose.
         actions: uint8 [E,A,K,H] (3*vel_idx + dphi_idx, > 8 ends a sequence); exclude: packed cell masks
         (``pack_cell_mask``) [E,A,128] or [E,A,K,128] of the other robots' cells, or None.
-        Returns dict(rewards [E,A,K], end_pose [E,A,K,3] | None, obsvd [E,A,K,128] int32 | None)."""
+        Returns dict(rewards [E,A,K], end_pose [E,A,K,3] | None, obsvd [E,A,K,128] int32 | None,
+        n_feasible [E,A,K] int32 = steps of each sequence that were applied)."""
         if getattr(self, "belief", None) is None:
             raise _lib.CasimError("explore_rollouts needs enable_exploration() first")
         actions = torch.as_tensor(actions, dtype=torch.uint8, device=self.device).contiguous()
@@ -277,11 +278,13 @@ class BatchedSim:
         rewards = torch.empty((self.E, self.A, K), **f32)
         end_pose = torch.empty((self.E, self.A, K, 3), **f32) if want_end_pose else None
         obsvd = torch.empty((self.E, self.A, K, 128), dtype=torch.int32, device=self.device) if want_obsvd else None
+        n_feasible = torch.empty((self.E, self.A, K), dtype=torch.int32, device=self.device)
         _lib.check(self.lib.casim_explore_rollouts(self.handle, _lib.ptr(self.state), _lib.ptr(self.belief),
                                                    _lib.ptr(actions), K, H, int(xdt), _lib.ptr(exclude), per,
-                                                   _lib.ptr(rewards), _lib.ptr(end_pose), _lib.ptr(obsvd), _stream_ptr()),
+                                                   _lib.ptr(rewards), _lib.ptr(end_pose), _lib.ptr(obsvd), _lib.ptr(n_feasible),
+                                                   _stream_ptr()),
                    "casim_explore_rollouts")
-        return dict(rewards=rewards, end_pose=end_pose, obsvd=obsvd)
+        return dict(rewards=rewards, end_pose=end_pose, obsvd=obsvd, n_feasible=n_feasible)
 
     def ga3c_set_weights(self, weights, want_debug=True):
         """weights: float32 [170764] parameter blob in the order of include/casim.h (TF variables of

@@ -264,12 +264,14 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
  *   (x cell i, y cell j); [E,A,128] shared by an agent's K rollouts, or [E,A,K,128] if exclude_per_rollout;
  *   NULL = nothing claimed.
  * rewards: [E,A,K] (0 for non-explorers).  end_pose [E,A,K,3] and obsvd [E,A,K,128] (the state's obsvd_cells
- * as a mask, BEFORE the difference -- what a robot communicates) are optional. */
+ * as a mask, BEFORE the difference -- what a robot communicates) and n_feasible [E,A,K] (int32: how many steps of
+ * the sequence were applied; == the sequence length iff mcts_state_storer would accept every step, :200-221) are
+ * optional. */
 #define CASIM_ROLLOUT_MAX_H 32
 #define CASIM_CELL_MASK_WORDS 128
 int casim_explore_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                            int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
-                           float* end_pose, uint32_t* obsvd, void* stream);
+                           float* end_pose, uint32_t* obsvd, int32_t* n_feasible, void* stream);
 
 /* Replaces GA3CCADRLPolicy.find_next_action for every GA3C agent (policies/GA3CCADRLPolicy.py:34-106,
  * GA3C_CADRL/network.py:45-98).  weights: fp32 parameter blob, order kernel/bias of lstm [71,256],[256];

@@ -407,7 +407,8 @@ double casim_oracle_reward_from_pose(const casim_config* c, const uint8_t* map, 
  * [K][dim*dim] (the state's obsvd_cells, before the difference) are optional.  The sum runs in row-major cell order (the reference: Python-set order). */
 int casim_oracle_explore_rollouts(const casim_config* c, const uint8_t* map, const double* pose, double radius,
                                   const double* belief, const uint8_t* actions, int K, int H, int xdt,
-                                  const uint8_t* exclude, double* rewards, double* end_pose, uint8_t* obsvd) {
+                                  const uint8_t* exclude, double* rewards, double* end_pose, uint8_t* obsvd,
+                                  int32_t* n_feasible) {
   const int dim = c->ig_map_dim;
   int32_t* d2 = (int32_t*)malloc(sizeof(int32_t) * MD * MD);
   uint8_t* vis = (uint8_t*)malloc((size_t)dim * dim);
@@ -417,6 +418,7 @@ int casim_oracle_explore_rollouts(const casim_config* c, const uint8_t* map, con
   const double vel_list[3] = {0.0, 2.0, 4.0}, dphi_list[3] = {-0.5 * M_PI, 0, 0.5 * M_PI};
   for (int k = 0; k < K; k++) {
     double cur[3] = {pose[0], pose[1], pose[2]};
+    int applied = 0;
     memset(seen, 0, (size_t)dim * dim);
     for (int t = 0; t < H; t++) {
       int a = actions[(size_t)k * H + t];
@@ -437,6 +439,7 @@ int casim_oracle_explore_rollouts(const casim_config* c, const uint8_t* map, con
       }
       if (!ok) continue; /* pose kept, nothing observed */
       cur[0] = nx[0]; cur[1] = nx[1]; cur[2] = nx[2];
+      applied++;
       visible_cells(&x, cur, vis);
       for (int q = 0; q < dim * dim; q++) seen[q] |= vis[q];
     }
@@ -445,6 +448,7 @@ int casim_oracle_explore_rollouts(const casim_config* c, const uint8_t* map, con
       if (seen[q] && !(exclude && exclude[q])) s += cell_mi(c, belief[q]);
     }
     rewards[k] = s;
+    if (n_feasible) n_feasible[k] = applied;
     if (end_pose) { end_pose[3 * k] = cur[0]; end_pose[3 * k + 1] = cur[1]; end_pose[3 * k + 2] = cur[2]; }
     if (obsvd) memcpy(obsvd + (size_t)k * dim * dim, seen, (size_t)dim * dim);
   }

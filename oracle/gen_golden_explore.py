@@ -197,3 +197,56 @@ def main_rollouts(ns, ncases=24, K=6, H=10, seed=777):
     np.savez_compressed(os.path.join(GOLDEN, "rollouts.npz"), **out)
     print("wrote rollouts.npz: %d cases x %d rollouts x %d steps, %d infeasible steps, reward range %.3f..%.3f" % (
         ncases, K, H, int(np.sum(rec["n_infeasible"])), np.min(rec["rewards"]), np.max(rec["rewards"])))
+
+
+def main_mcts(ns, seed=4242, H=6, nsims=4, ntree=40, gamma=0.9):
+    """tests/golden/mcts.npz: two Dec-MCTS trees grown by the UNMODIFIED reference (pydecmcts Tree + ig_mcts callbacks,
+    np.random seeded): tree A alone; tree B after receiving A's action distribution (receive_comms).  Recorded per
+    tree: every node's parent / stage / action path / mu / N, the per-iteration average reward and the final action."""
+    from gym_collision_avoidance.envs.policies.ig_mcts import ig_mcts
+    from gym_collision_avoidance.envs.policies.pydecmcts.DecMCTS import Tree
+    rng = np.random.default_rng(seed)
+    ref_map = ns.Map(30, 30, 0.1, obstacles_of(CROSSING))
+    out = {"static": np.packbits(ref_map.static_map.astype(np.uint8)), "H": H, "nsims": nsims, "ntree": ntree,
+           "gamma": gamma, "seed": seed}
+    options = ig_mcts.mcts_avail_actions(None, None, 0)
+
+    def idx_of(a):
+        return [k for k, o in enumerate(options) if (o == a).all()][0]
+
+    radius = 0.5
+    a = rng.integers(0, 4, (60, 60)) * (rng.random((60, 60)) < 0.3)
+    b = rng.integers(0, 6, (60, 60)) * (rng.random((60, 60)) < 0.5)
+    belief = np.float32(1.5 ** a * 0.66 ** b)
+    poses = [np.array([-6.0, 0.5, 0.2]), np.array([-4.5, 1.2, 1.3])]        # B faces a wall: infeasible expansions
+    out.update(belief=belief, poses=np.array(poses), radius=radius)
+    trees = []
+    for k, pose in enumerate(poses):
+        pol = ig_mcts()
+        pol.set_param(types.SimpleNamespace(radius=radius), ref_map, (30, 30), 0.1, 60.0, 5.0, dt=0.1, xdt=1, mcts_horizon=H)
+        pol.targetMap.map = belief.astype(np.float64).copy()
+        np.random.seed(seed + k)
+        tree = Tree({"current_pose": pose}, pol.mcts_reward, pol.mcts_avail_actions, pol.mcts_state_storer,
+                    pol.mcts_sim_selection_func, pol.mcts_avail_actions, pol.mcts_sim_state_storer, 5, robot_id=k,
+                    horizon=H, c_p=1.0)
+        if k == 1:
+            tree.receive_comms(trees[0].send_comms(), 0)
+        avgs = [tree.grow(nsims=nsims, gamma=gamma) for _ in range(ntree)]
+        g = tree.graph
+        n = len(g)
+        parent = np.array([-1] + [list(g.predecessors(i))[0] - 1 for i in range(2, n + 1)])
+        stage = np.array([g.nodes[i]["stage"] for i in range(1, n + 1)])
+        mu = np.array([g.nodes[i]["mu"] for i in range(1, n + 1)])
+        N = np.array([g.nodes[i]["N"] for i in range(1, n + 1)], np.float64)
+        path = np.full((n, H), 255, np.uint8)
+        for i in range(1, n + 1):
+            for d, act in enumerate(g.nodes[i]["state"].action_seq):
+                path[i - 1, d] = idx_of(act)
+        dist = tree.send_comms()
+        out.update({"parent_%d" % k: parent, "stage_%d" % k: stage, "mu_%d" % k: mu, "N_%d" % k: N, "path_%d" % k: path,
+                    "avg_%d" % k: np.array(avgs), "q_%d" % k: np.array(dist.q),
+                    "action_%d" % k: idx_of(dist.X[0].action_seq[0])})
+        trees.append(tree)
+        print("tree %d: %d nodes, max stage %d, avg reward %.4f -> %.4f, action %d" % (
+            k, n, stage.max(), avgs[0], avgs[-1], out["action_%d" % k]))
+    np.savez_compressed(os.path.join(GOLDEN, "mcts.npz"), **out)

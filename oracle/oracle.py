@@ -193,15 +193,16 @@ def explore_rollouts(cfg, static_map, pose, radius, belief, actions, exclude=Non
     rewards = np.zeros(K, np.float64)
     end_pose = np.zeros((K, 3), np.float64)
     obsvd = np.zeros((K, dim, dim), np.uint8)
+    n_feasible = np.zeros(K, np.int32)
     f = lib().casim_oracle_explore_rollouts
     f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double, ctypes.c_void_p,
                   ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
-                  ctypes.c_void_p, ctypes.c_void_p]
+                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     f.restype = ctypes.c_int
     rc = f(ctypes.addressof(cfg), _p(m), _p(pose), float(radius), _p(belief), _p(actions), K, H, int(xdt),
-           None if ex is None else _p(ex), _p(rewards), _p(end_pose), _p(obsvd))
+           None if ex is None else _p(ex), _p(rewards), _p(end_pose), _p(obsvd), _p(n_feasible))
     assert rc == 0
-    return dict(rewards=rewards, end_pose=end_pose, obsvd=obsvd)
+    return dict(rewards=rewards, end_pose=end_pose, obsvd=obsvd, n_feasible=n_feasible)
 
 
 def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_game_over=None, n_threads=1):

@@ -60,6 +60,9 @@ def test_rollouts_golden_vs_reference():
         obs = unpack_cell_mask(out["obsvd"].cpu().numpy(), 60)[:, 0]
         rew = out["rewards"].cpu().numpy()[:, 0]
         end = out["end_pose"].cpu().numpy()[:, 0]
+        lens = (actions != 255).sum(-1)[:, 0]
+        n_inf = (lens - out["n_feasible"].cpu().numpy()[:, 0]).sum(-1)
+        assert np.array_equal(n_inf, [int(z["n_infeasible"][cases.index(cs)]) for cs in sel])
         for k, cs in enumerate(sel):
             assert np.array_equal(obs[k], cs["obsvd"]), "map %d case %d observed cells" % (mid, k)
             H.assert_close(rew[k], cs["rewards"], "map %d case %d rewards" % (mid, k), rtol=1e-5, atol=1e-7)
@@ -101,6 +104,7 @@ def test_rollouts_batch_vs_oracle(oracle_lib):
     belief = sim.belief.cpu().numpy().astype(np.float64)
     rew = out["rewards"].cpu().numpy()
     end = out["end_pose"].cpu().numpy()
+    nfe = out["n_feasible"].cpu().numpy()
     obs = unpack_cell_mask(out["obsvd"].cpu().numpy(), cfg.ig_map_dim)
     ig = (types & 0xff) == L.POLICY_IG_GREEDY
     assert ig.sum() == 2 * E and not rew[~ig].any() and not obs[~ig].any()
@@ -111,6 +115,7 @@ def test_rollouts_batch_vs_oracle(oracle_lib):
             assert np.array_equal(obs[e, a], o["obsvd"].astype(bool)), (e, a)
             H.assert_close(rew[e, a], o["rewards"], "rewards %d %d" % (e, a), rtol=1e-5, atol=1e-7)
             H.assert_close(end[e, a], o["end_pose"], "end pose %d %d" % (e, a), rtol=1e-6, atol=1e-5)
+            assert np.array_equal(nfe[e, a], o["n_feasible"]), (e, a)
     sim.close()
 
 

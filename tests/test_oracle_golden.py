@@ -208,6 +208,8 @@ def test_explore_rollouts_vs_reference(oracle_lib):
         assert np.array_equal(out["obsvd"].astype(bool), cs["obsvd"]), "case %d observed cells" % n
         assert np.abs(out["end_pose"] - cs["end_pose"]).max() < 1e-12, "case %d end pose" % n
         H.assert_close(out["rewards"], cs["rewards"], "case %d rewards" % n, rtol=1e-9, atol=1e-12)
+        lens = (cs["actions"] != 255).sum(1)
+        assert int((lens - out["n_feasible"]).sum()) == int(z["n_infeasible"][n]), "case %d infeasible steps" % n
 
 
 def test_ga3c_state_vector_vs_reference(oracle_lib):
