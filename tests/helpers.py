@@ -231,7 +231,7 @@ def rollout_cases(z):
     for n in range(len(z["map_id"])):
         K = z["actions"][n].shape[0]
         cases.append(dict(
-            map_id=int(z["map_id"][n]), pose=z["pose"][n], radius=float(z["radius"][n]), belief=z["belief"][n],
+            index=n, map_id=int(z["map_id"][n]), pose=z["pose"][n], radius=float(z["radius"][n]), belief=z["belief"][n],
             actions=z["actions"][n], exclude=np.unpackbits(z["exclude"][n])[:3600].reshape(60, 60).astype(bool),
             rewards=z["rewards"][n], end_pose=z["end_pose"][n],
             obsvd=np.stack([np.unpackbits(z["obsvd"][n][k])[:3600].reshape(60, 60).astype(bool) for k in range(K)])))

@@ -1,0 +1,107 @@
+"""The batched Dec-MCTS planner with the GPU rollout evaluator (casim_explore_rollouts): the reference-grown trees
+of tests/golden/mcts.npz node for node, and a C4-size planning step (2048 trees) for determinism and sanity."""
+import numpy as np
+import pytest
+
+import helpers as H
+from casim import layout as L
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg():
+    from casim import lib
+    c = lib.default_config()
+    c.game_over_mode = 0
+    return c
+
+
+def _sim(E, A, cfg):
+    from casim.sim import BatchedSim
+    sim = BatchedSim(E, A, cfg=cfg, sensors=("other_agents_states",))
+    sim.enable_exploration()
+    return sim
+
+
+def test_mcts_golden_trees_on_gpu():
+    import torch
+    from casim.mcts import BatchedDecMCTS, sim_evaluator
+    z = H.load("mcts.npz")
+    cfg = _cfg()
+    smap = np.unpackbits(z["static"])[:300 * 300].reshape(300, 300).astype(np.uint8)
+    Hn, nsims, ntree, gamma, seed = int(z["H"]), int(z["nsims"]), int(z["ntree"]), float(z["gamma"]), int(z["seed"])
+    dist_a = None
+    for k in (0, 1):
+        sim = _sim(1, 1, cfg)
+        sim.set_map(smap)
+        state = np.zeros((1, 1, L.STATE_WORDS))
+        state[0, 0, L.PX], state[0, 0, L.PY], state[0, 0, L.HEADING] = z["poses"][k]
+        state[0, 0, L.RADIUS] = float(z["radius"])
+        state[0, 0, L.PREF_SPEED] = 1.0
+        state[0, 0, L.TYPE] = L.encode_type(L.POLICY_IG_GREEDY, L.DYN_FIRST_ORDER, L.SENSOR_OTHER_AGENTS)
+        sim.bind(types=state[:, :, L.TYPE].astype(np.int32), n_agents=np.ones((1,), np.int32))
+        sim.load_state_numpy(state)
+        sim.belief.copy_(torch.from_numpy(z["belief"])[None, None])
+        T, ev, masks_of, _ = sim_evaluator(sim)
+        assert T == 1
+        np.random.seed(seed + k)
+        tree = BatchedDecMCTS(T, ev, horizon=Hn, c_p=1.0, comm_n=5, reference_order=True)
+        if k == 1:
+            tree.receive_comms(dist_a)
+        avgs = [float(tree.grow(nsims=nsims, gamma=gamma)[0]) for _ in range(ntree)]
+        n = len(z["parent_%d" % k])
+        assert int(tree.n_nodes[0]) == n
+        assert np.array_equal(tree.parent[0, :n], z["parent_%d" % k])
+        assert np.array_equal(tree.path[0, :n], z["path_%d" % k])
+        H.assert_close(tree.mu[0, :n], z["mu_%d" % k], "mu of tree %d" % k, rtol=1e-5, atol=1e-7)
+        H.assert_close(np.array(avgs), z["avg_%d" % k], "avg reward of tree %d" % k, rtol=1e-5, atol=1e-7)
+        assert int(tree.best_action_index()[0]) == int(z["action_%d" % k])
+        if k == 0:
+            dist_a = tree.distribution(with_masks=masks_of)
+        sim.close()
+
+
+def test_mcts_c4_planning_step():
+    """C4 size: 1024 envs x (2 explorers + 2 targets): 20 iterations x 10 simulations x horizon 10 for all 2048 trees;
+    the two explorers of an environment exchange their distributions half way (Dec-MCTS comms)."""
+    import torch
+    from casim import scenarios as S
+    from casim.mcts import BatchedDecMCTS, sim_evaluator, action_value
+    E = 1024
+    init, types, n, rects = S.exploration(E, seed=5)
+    cfg = _cfg()
+    sim = _sim(E, 4, cfg)
+    sim.set_obstacles(rects)
+    sim.reset(init, types, n)
+    for _ in range(2):
+        sim.explore_step()
+        sim.step(policy_actions=sim.buf["policy_actions"])
+
+    def plan(seed):
+        T, ev, masks_of, (te, ta) = sim_evaluator(sim)
+        assert T == 2 * E
+        tree = BatchedDecMCTS(T, ev, horizon=10, c_p=1.0, seed=seed)
+        for _ in range(10):
+            tree.grow(nsims=10, gamma=1.0)
+        d = tree.distribution(with_masks=masks_of)
+        # trees are in (env, agent) order and every env has exactly two explorers: the partner is the neighbour
+        assert np.array_equal(te[0::2], te[1::2])
+        partner = np.arange(T) ^ 1
+        from casim.mcts import ActionDistribution
+        other = ActionDistribution(d.seqs[partner], d.q[partner], d.masks[partner])
+        tree.receive_comms(other)
+        avg = None
+        for _ in range(10):
+            avg = tree.grow(nsims=10, gamma=1.0)
+        return tree, avg
+
+    t1, avg1 = plan(3)
+    t2, avg2 = plan(3)
+    assert np.array_equal(t1.n_nodes, t2.n_nodes) and np.array_equal(t1.mu, t2.mu) and np.array_equal(avg1, avg2)
+    a = t1.best_action_index()
+    assert a.min() >= 0 and a.max() <= 8
+    assert t1.launches == 21 and (t1.n_nodes > 10).all() and (t1.n_nodes <= 1 + 9 * 21).all()
+    act = action_value(a)
+    assert act.shape == (2 * E, 2) and np.isin(act[:, 0], (0.0, 2.0, 4.0)).all()
+    assert float(t1.mu[:, 1:].max()) > 0.3 and np.isfinite(t1.mu).all()
+    sim.close()

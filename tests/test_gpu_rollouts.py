@@ -62,7 +62,7 @@ def test_rollouts_golden_vs_reference():
         end = out["end_pose"].cpu().numpy()[:, 0]
         lens = (actions != 255).sum(-1)[:, 0]
         n_inf = (lens - out["n_feasible"].cpu().numpy()[:, 0]).sum(-1)
-        assert np.array_equal(n_inf, [int(z["n_infeasible"][cases.index(cs)]) for cs in sel])
+        assert np.array_equal(n_inf, [int(z["n_infeasible"][cs["index"]]) for cs in sel])
         for k, cs in enumerate(sel):
             assert np.array_equal(obs[k], cs["obsvd"]), "map %d case %d observed cells" % (mid, k)
             H.assert_close(rew[k], cs["rewards"], "map %d case %d rewards" % (mid, k), rtol=1e-5, atol=1e-7)
