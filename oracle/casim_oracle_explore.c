@@ -455,3 +455,65 @@ int casim_oracle_explore_rollouts(const casim_config* c, const uint8_t* map, con
   free(d2); free(vis); free(seen);
   return 0;
 }
+
+/* ig_mcts.update_belief (policies/ig_mcts.py:117-137) for every explorer agent of a batch, in the order
+ * collision_avoidance_env.py:341-368 calls it (ascending agent index, done agents skipped, :298-299):
+ *   poses   = [own pose] + [pose of every OTHER explorer j (ascending j), done or not]
+ *   targets = [own detections (find_targets_in_obs, :139-156)] + [agents[j].policy.obsvd_targets]
+ * where obsvd_targets of j is what j detected at ITS latest update: this step's if j < i and j is not done, else
+ * the previous call's (targets_prev / n_prev; none before j's first update, :127).  targetMap.update multiplies
+ * every visible cell once per pose that sees it (targetMap.py:86-128); team_obsv_cells is the union and team_reward
+ * the mutual information of the union on the UPDATED map (:136-137).
+ * state [E][A][NF], oas [E][A][rows][10], belief [E][A][dim][dim] RMW, one shared map.
+ * targets_prev/new [E][A][CASIM_MAX_AGENTS][2] global-frame doubles with counts n_prev/new [E][A] (a done agent
+ * keeps its previous list).  team_mask [E][A][dim*dim] uint8 and team_reward [E][A] are optional. */
+int casim_oracle_team_update(const casim_config* c, int E, int A, const int32_t* n_agents, const double* state,
+                             const double* oas, double* belief, const uint8_t* map, const double* targets_prev,
+                             const int32_t* n_prev, double* targets_new, int32_t* n_new, uint8_t* team_mask,
+                             double* team_reward) {
+  const int dim = c->ig_map_dim, rows = c->max_other_agents_rows;
+  const int TM = CASIM_MAX_AGENTS;
+  int32_t* d2 = (int32_t*)malloc(sizeof(int32_t) * MD * MD);
+  uint8_t* vis = (uint8_t*)malloc((size_t)dim * dim);
+  uint8_t* uni = (uint8_t*)malloc((size_t)dim * dim);
+  casim_oracle_edt(map, d2);
+  xctx x = {c, d2, NULL};
+  memcpy(targets_new, targets_prev, sizeof(double) * (size_t)E * A * TM * 2);
+  memcpy(n_new, n_prev, sizeof(int32_t) * (size_t)E * A);
+  for (int e = 0; e < E; e++) {
+    int n = n_agents ? n_agents[e] : A;
+    for (int i = 0; i < n; i++) {
+      size_t g = (size_t)e * A + i;
+      const double* s = state + g * NF;
+      if (((int)s[CASIM_TYPE] & 0xff) != CASIM_POLICY_IG_GREEDY) continue;
+      if (team_reward) team_reward[g] = 0;
+      if (team_mask) memset(team_mask + g * dim * dim, 0, (size_t)dim * dim);
+      if ((int)s[CASIM_FLAGS] & CASIM_F_IS_DONE) continue;
+      double* b = belief + g * dim * dim;
+      double pose[3] = {s[CASIM_PX], s[CASIM_PY], s[CASIM_HEADING]};
+      /* own detections become this agent's obsvd_targets: later agents of this step read them from targets_new */
+      n_new[g] = find_targets(c, oas + g * rows * 10, rows, pose, targets_new + g * TM * 2);
+      memset(uni, 0, (size_t)dim * dim);
+      belief_update(&x, pose, targets_new + g * TM * 2, n_new[g], b, vis);
+      for (int q = 0; q < dim * dim; q++) uni[q] |= vis[q];
+      for (int j = 0; j < n; j++) {
+        size_t gj = (size_t)e * A + j;
+        const double* sj = state + gj * NF;
+        if (j == i || ((int)sj[CASIM_TYPE] & 0xff) != CASIM_POLICY_IG_GREEDY) continue;
+        double pj[3] = {sj[CASIM_PX], sj[CASIM_PY], sj[CASIM_HEADING]};
+        /* j < i and not done: already replaced by this step's list above; otherwise still the previous one */
+        belief_update(&x, pj, targets_new + gj * TM * 2, n_new[gj], b, vis);
+        for (int q = 0; q < dim * dim; q++) uni[q] |= vis[q];
+      }
+      if (team_mask) memcpy(team_mask + g * dim * dim, uni, (size_t)dim * dim);
+      if (team_reward) {
+        double r = 0;
+        for (int q = 0; q < dim * dim; q++)
+          if (uni[q]) r += cell_mi(c, b[q]);
+        team_reward[g] = r;
+      }
+    }
+  }
+  free(d2); free(vis); free(uni);
+  return 0;
+}

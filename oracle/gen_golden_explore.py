@@ -250,3 +250,84 @@ def main_mcts(ns, seed=4242, H=6, nsims=4, ntree=40, gamma=0.9):
         print("tree %d: %d nodes, max stage %d, avg reward %.4f -> %.4f, action %d" % (
             k, n, stage.max(), avgs[0], avgs[-1], out["action_%d" % k]))
     np.savez_compressed(os.path.join(GOLDEN, "mcts.npz"), **out)
+
+
+def main_team(ns, seed=99, nsteps=3):
+    """tests/golden/team.npz: ig_mcts.update_belief (ig_mcts.py:117-137) of the UNMODIFIED reference for small teams
+    over several steps, called in the order collision_avoidance_env._take_action_dmcts does (ascending index, done
+    agents skipped).  Scenes: 3 explorers + 2 static targets; explorer 1 is done from step 1 on in scene 1."""
+    from gym_collision_avoidance.envs.policies.ig_mcts import ig_mcts
+    rng = np.random.default_rng(seed)
+    ref_map = ns.Map(30, 30, 0.1, obstacles_of(CROSSING))
+    out = {"static": np.packbits(ref_map.static_map.astype(np.uint8))}
+    nscenes, A, n_ig = 4, 5, 3
+    rec = {k: [] for k in ("pose", "oas", "done", "belief_after", "team_mask", "team_reward", "n_targets", "belief0")}
+    for sc in range(nscenes):
+        pols = []
+        a = rng.integers(0, 4, (60, 60)) * (rng.random((60, 60)) < 0.3)
+        b = rng.integers(0, 6, (60, 60)) * (rng.random((60, 60)) < 0.5)
+        belief0 = np.float32(1.5 ** a * 0.66 ** b)
+        for i in range(n_ig):
+            pol = ig_mcts()
+            pol.set_param(types.SimpleNamespace(radius=0.5), ref_map, (30, 30), 0.1, 60.0, 5.0, dt=0.1, xdt=1)
+            pol.targetMap.map = belief0.astype(np.float64).copy()
+            pols.append(pol)
+        agents = [types.SimpleNamespace(policy=pols[i] if i < n_ig else ns.StaticPolicy(), pos_global_frame=None,
+                                        heading_global_frame=None) for i in range(A)]
+        centre = free_pose(rng, pols[0].edfMap, 1.5)
+        srec = {k: [] for k in rec}
+        srec["belief0"] = belief0
+        for step in range(nsteps):
+            poses = np.zeros((A, 3))
+            for i in range(A):       # a loose cluster so that the explorers see each other's cells and the targets
+                for _ in range(1000):
+                    p = np.float32(np.clip(centre + rng.uniform(-3, 3, 2), -13.5, 13.5)).astype(np.float64)
+                    if pols[0].edfMap.get_edf_value_from_pose(p) > 0.6:
+                        break
+                poses[i, :2] = p
+                poses[i, 2] = float(np.float32(rng.uniform(-np.pi, np.pi)))
+                agents[i].pos_global_frame = poses[i, :2].copy()
+                agents[i].heading_global_frame = poses[i, 2]
+            for i in range(n_ig):    # look at a target, so that detections happen
+                tgt = poses[n_ig + (i % 2), :2]
+                if rng.random() < 0.8:
+                    d = tgt - poses[i, :2]
+                    poses[i, 2] = float(np.float32(np.arctan2(d[1], d[0]) + rng.uniform(-0.3, 0.3)))
+                    agents[i].heading_global_frame = poses[i, 2]
+            done = np.zeros(A, bool)
+            if sc == 1 and step >= 1:
+                done[1] = True
+            oas = np.zeros((A, 9, 10))
+            for i in range(n_ig):
+                others = [j for j in range(A) if j != i]
+                for r, j in enumerate(others):
+                    oas[i, r, 0:2] = np.float32(poses[j, :2] - poses[i, :2])
+                    oas[i, r, 2:9] = np.float32(rng.uniform(-1, 1, 7))
+                    oas[i, r, 9] = 1.0 if j >= n_ig else 2.0
+            ba, tm, tr, nt = [], [], [], []
+            for i in range(n_ig):
+                if done[i]:
+                    ba.append(pols[i].targetMap.map.copy()); tm.append(np.packbits(np.zeros((60, 60), bool)))
+                    tr.append(0.0); nt.append(-1)
+                    continue
+                obs = {"pos_global_frame": poses[i, :2].copy(), "heading_global_frame": poses[i, 2],
+                       "other_agents_states": oas[i].copy()}
+                dm = [j for j in range(A) if "ig_" in str(type(agents[j].policy)) and j != i]
+                pols[i].update_belief(dm, np.append(poses[i, :2], poses[i, 2]), agents, obs)
+                m = np.zeros((60, 60), bool)
+                for (ci, cj) in pols[i].team_obsv_cells:
+                    m[cj, ci] = True
+                ba.append(pols[i].targetMap.map.copy()); tm.append(np.packbits(m)); tr.append(float(pols[i].team_reward))
+                nt.append(len(pols[i].obsvd_targets))
+            srec["pose"].append(poses); srec["oas"].append(oas); srec["done"].append(done)
+            srec["belief_after"].append(ba); srec["team_mask"].append(tm); srec["team_reward"].append(tr)
+            srec["n_targets"].append(nt)
+        for k in rec:
+            rec[k].append(srec[k])
+    for k, v in rec.items():
+        out[k] = np.array(v)
+    out["n_ig"] = n_ig
+    np.savez_compressed(os.path.join(GOLDEN, "team.npz"), **out)
+    nt = out["n_targets"]
+    print("wrote team.npz: %d scenes x %d steps x %d explorers; detections %d; mean team cells %.1f" % (
+        nscenes, nsteps, n_ig, int(nt[nt > 0].sum()), np.mean([np.unpackbits(m).sum() for m in out["team_mask"].reshape(-1, out["team_mask"].shape[-1])])))

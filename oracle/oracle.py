@@ -205,6 +205,32 @@ def explore_rollouts(cfg, static_map, pose, radius, belief, actions, exclude=Non
     return dict(rewards=rewards, end_pose=end_pose, obsvd=obsvd, n_feasible=n_feasible)
 
 
+def team_update(cfg, state, oas, belief, static_map, targets_prev, n_prev, n_agents=None):
+    """ig_mcts.update_belief for every explorer (sequenced like collision_avoidance_env._take_action_dmcts).
+    belief [E,A,dim,dim] f64 is updated in place.  targets_prev [E,A,32,2] f64, n_prev [E,A] int32.
+    Returns dict(targets [E,A,32,2], n_targets [E,A], team_mask [E,A,dim,dim] uint8, team_reward [E,A])."""
+    assert state.dtype == np.float64 and belief.dtype == np.float64 and belief.flags.c_contiguous
+    E, A = state.shape[:2]
+    dim = cfg.ig_map_dim
+    m = np.ascontiguousarray(static_map, dtype=np.uint8).reshape(MAP_DIM, MAP_DIM)
+    state = np.ascontiguousarray(state)
+    oas = np.ascontiguousarray(oas, dtype=np.float64)
+    targets_prev = np.ascontiguousarray(targets_prev, dtype=np.float64)
+    n_prev = np.ascontiguousarray(n_prev, dtype=np.int32)
+    n_agents = None if n_agents is None else np.ascontiguousarray(n_agents, dtype=np.int32)
+    targets = np.zeros((E, A, 32, 2), np.float64)
+    n_t = np.zeros((E, A), np.int32)
+    mask = np.zeros((E, A, dim, dim), np.uint8)
+    reward = np.zeros((E, A), np.float64)
+    f = lib().casim_oracle_team_update
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 11
+    f.restype = ctypes.c_int
+    rc = f(ctypes.addressof(cfg), E, A, _p(n_agents), _p(state), _p(oas), _p(belief), _p(m), _p(targets_prev),
+           _p(n_prev), _p(targets), _p(n_t), _p(mask), _p(reward))
+    assert rc == 0
+    return dict(targets=targets, n_targets=n_t, team_mask=mask, team_reward=reward)
+
+
 def explore_step(cfg, state, oas, belief, maps, n_agents=None, init=None, prev_game_over=None, n_threads=1):
     """ig_greedy.find_next_action for every ig_greedy agent.  belief [E,A,dim,dim] f64 is updated in place.
     Returns dict(policy_actions [E,A,2], best_mi [E,A], cand_mi [E,A,9], counters [4], visible [E,A,dim,dim])."""

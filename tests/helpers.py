@@ -236,3 +236,27 @@ def rollout_cases(z):
             rewards=z["rewards"][n], end_pose=z["end_pose"][n],
             obsvd=np.stack([np.unpackbits(z["obsvd"][n][k])[:3600].reshape(60, 60).astype(bool) for k in range(K)])))
     return maps, cases
+
+
+def team_scene(z, sc):
+    """tests/golden/team.npz scene -> per-step batch inputs (E = 1, A = 5: 3 explorers + 2 static targets)."""
+    from casim import layout as L
+    n_ig = int(z["n_ig"])
+    steps = []
+    for st in range(z["pose"].shape[1]):
+        poses, done = z["pose"][sc, st], z["done"][sc, st]
+        A = poses.shape[0]
+        state = np.zeros((1, A, L.STATE_WORDS))
+        state[0, :, L.PX], state[0, :, L.PY], state[0, :, L.HEADING] = poses[:, 0], poses[:, 1], poses[:, 2]
+        state[0, :, L.RADIUS] = 0.5
+        state[0, :, L.PREF_SPEED] = 1.0
+        for i in range(A):
+            pol = L.POLICY_IG_GREEDY if i < n_ig else L.POLICY_STATIC
+            state[0, i, L.TYPE] = L.encode_type(pol, L.DYN_FIRST_ORDER, L.SENSOR_OTHER_AGENTS)
+            state[0, i, L.FLAGS] = L.F_IS_DONE if done[i] else 0
+        steps.append(dict(state=state, oas=z["oas"][sc, st][None], done=done,
+                          belief_after=z["belief_after"][sc, st], team_reward=z["team_reward"][sc, st],
+                          n_targets=z["n_targets"][sc, st],
+                          team_mask=np.stack([np.unpackbits(m)[:3600].reshape(60, 60).astype(bool)
+                                              for m in z["team_mask"][sc, st]])))
+    return steps

@@ -212,6 +212,33 @@ def test_explore_rollouts_vs_reference(oracle_lib):
         assert int((lens - out["n_feasible"]).sum()) == int(z["n_infeasible"][n]), "case %d infeasible steps" % n
 
 
+def test_team_update_vs_reference(oracle_lib):
+    """ig_mcts.update_belief over 3 steps for teams of 3 explorers (sequencing of obsvd_targets: this step's for
+    lower-index agents, the previous step's for the others and for done agents): belief to 1e-12, team cells exact."""
+    oracle = oracle_lib
+    z = H.load("team.npz")
+    cfg = oracle.default_config()
+    smap = np.unpackbits(z["static"])[:300 * 300].reshape(300, 300).astype(np.uint8)
+    n_ig = int(z["n_ig"])
+    assert (z["n_targets"] > 0).sum() >= 10 and z["done"].any()
+    for sc in range(z["pose"].shape[0]):
+        steps = H.team_scene(z, sc)
+        A = steps[0]["state"].shape[1]
+        belief = np.repeat(z["belief0"][sc].astype(np.float64)[None, None], A, axis=1).copy()
+        tp, npv = np.zeros((1, A, 32, 2)), np.zeros((1, A), np.int32)
+        for st, s in enumerate(steps):
+            o = oracle.team_update(cfg, s["state"], s["oas"], belief, smap, tp, npv)
+            tp, npv = o["targets"], o["n_targets"]
+            for i in range(n_ig):
+                H.assert_close(belief[0, i], s["belief_after"][i], "scene %d step %d agent %d belief" % (sc, st, i),
+                               rtol=1e-12, atol=0)
+                if s["done"][i]:
+                    continue
+                assert np.array_equal(o["team_mask"][0, i].astype(bool), s["team_mask"][i]), (sc, st, i)
+                H.assert_close(o["team_reward"][0, i], s["team_reward"][i], "team reward", rtol=1e-9, atol=1e-12)
+                assert int(npv[0, i]) == int(s["n_targets"][i])
+
+
 def test_ga3c_state_vector_vs_reference(oracle_lib):
     """agents_to_ga3c_cadrl_state (GA3CCADRLPolicy.py:45-106): slot ORDER exact (Python round(x, 2), stable sort on
     (-round(dist, 2), p_orthog), clip to the closest N), values to 1e-12."""
