@@ -451,6 +451,17 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
   return 0;
 }
 
+int casim_explore_team_update(casim_handle* h, const float* state, const float* other_agents_states, float* belief,
+                              const double* targets_prev, const int32_t* n_prev, double* targets_new, int32_t* n_new,
+                              uint32_t* team_mask, float* team_reward, void* stream) {
+  REQUIRE(h && state && other_agents_states && belief && targets_prev && n_prev && targets_new && n_new, "null argument");
+  REQUIRE(targets_prev != targets_new && n_prev != n_new, "team update: previous and new target lists must not alias");
+  REQUIRE(h->n_maps > 0, "casim_explore_team_update needs a static map (casim_set_obstacles / casim_set_map)");
+  CK(casim_launch_team_update(h, state, other_agents_states, belief, targets_prev, n_prev, targets_new, n_new, team_mask,
+                              team_reward, (cudaStream_t)stream));
+  return 0;
+}
+
 int casim_explore_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                            int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
                            float* end_pose, uint32_t* obsvd, int32_t* n_feasible, void* stream) {

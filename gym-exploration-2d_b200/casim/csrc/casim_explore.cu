@@ -590,6 +590,188 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   if (tid == 0) p.rewards[gk] = (float)((double)(long long)s_sum / X_MI_SCALE);
 }
 
+/* ---------------------------------------------------------------------------------------------------------
+ * ig_mcts.update_belief (policies/ig_mcts.py:117-137): the team version of the target-map update.  One CTA per
+ * explorer agent i; its belief is multiplied once per pose that sees a cell -- own pose with own detections, then
+ * every other explorer j of the environment (ascending j) with j's obsvd_targets: the list j detected at its own
+ * latest update, i.e. this step's when j < i and j is not done (recomputed here from j's observation rows rather
+ * than waited for: the detector emulation is 9 rows), else the previous call's (targets_prev).  The poses are
+ * processed one after the other (a cell seen from two poses is multiplied twice, targetMap.py:86-128); inside a
+ * pose every cell is owned by one thread.  team_obsv_cells = union mask, team_reward = MI of the union on the
+ * updated map (:136-137).
+ * --------------------------------------------------------------------------------------------------------- */
+struct TeamArgs {
+  DevCfg c;
+  const float4* state;
+  const float* oas;            /* [E*A][rows][10] */
+  float* belief;               /* [E*A][dim][dim] */
+  const double* targets_prev;  /* [E*A][32][2] global frame */
+  const int32_t* n_prev;       /* [E*A] */
+  double* targets_new;
+  int32_t* n_new;
+  uint32_t* team_mask;         /* [E*A][128] or NULL */
+  float* team_reward;          /* [E*A] or NULL */
+  const int32_t* n_agents;
+  const double* edf;
+  int E, A, n_maps;
+};
+
+__global__ void __launch_bounds__(X_THREADS) k_team_update(const TeamArgs p) {
+  const DevCfg& c = p.c;
+  const int g = blockIdx.x;
+  const int e = g / p.A, ai = g - e * p.A;
+  const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+  if (ai >= n) return;
+  const size_t N = (size_t)p.E * p.A;
+  const int tid = threadIdx.x;
+  const float4 p5 = p.state[5 * N + g];
+  if ((__float_as_int(p5.w) & 0xff) != CASIM_POLICY_IG_GREEDY) return;
+  const bool done = (__float_as_int(p5.z) & CASIM_F_IS_DONE) != 0;
+  if (p.team_mask && done)
+    for (int w = tid; w < XR_MASK_WORDS; w += X_THREADS) p.team_mask[(size_t)g * XR_MASK_WORDS + w] = 0u;
+  if (done) { /* collision_avoidance_env.py:298-299: no update; the agent keeps the list of its last update */
+    const int np_ = p.n_prev[g];
+    if (tid == 0) {
+      p.n_new[g] = np_;
+      if (p.team_reward) p.team_reward[g] = 0.f;
+    }
+    if (tid < 2 * np_) p.targets_new[(size_t)g * 64 + tid] = p.targets_prev[(size_t)g * 64 + tid];
+    return;
+  }
+
+  __shared__ PoseBox s_box;
+  __shared__ double s_det[CASIM_MAX_AGENTS][2];
+  __shared__ int s_ndet, s_qn, s_np;
+  __shared__ int s_who[CASIM_MAX_AGENTS];
+  __shared__ unsigned short s_queue[XQ_CAP];
+  __shared__ unsigned int s_seen[XR_MASK_WORDS];
+  __shared__ unsigned long long s_sum;
+
+  const int dim = c.ig_dim;
+  float* belief = p.belief + (size_t)g * dim * dim;
+  const double* d2 = p.edf + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
+  unsigned cnt_samples = 0, cnt_clamped = 0;
+  for (int w = tid; w < XR_MASK_WORDS; w += X_THREADS) s_seen[w] = 0u;
+  if (tid == 0) { /* poses: self first, then the other explorers in index order (ig_mcts.py:84, 125-130) */
+    int m = 0;
+    s_who[m++] = ai;
+    for (int j = 0; j < n; j++)
+      if (j != ai && (__float_as_int(p.state[5 * N + (size_t)e * p.A + j].w) & 0xff) == CASIM_POLICY_IG_GREEDY) s_who[m++] = j;
+    s_np = m;
+    s_sum = 0ull;
+  }
+  __syncthreads();
+  const int nposes = s_np;
+
+  for (int m = 0; m < nposes; m++) {
+    const int j = s_who[m];
+    const size_t gj = (size_t)e * p.A + j;
+    const float4 q0 = p.state[gj];
+    const double px = q0.x, py = q0.y, ph = q0.z;
+    /* ---- this pose's detections, in its ego frame (targetMap.py:89-103) ---- */
+    if (tid < 32) {
+      const bool j_done = (__float_as_int(p.state[5 * N + gj].z) & CASIM_F_IS_DONE) != 0;
+      const bool fresh = (m == 0) || (j < ai && !j_done);
+      double tx = 0, ty = 0;
+      bool hit = false;
+      if (fresh) { /* find_targets_in_obs (ig_mcts.py:139-156) on j's own observation */
+        if (tid < c.rows) {
+          const float* row = p.oas + (gj * c.rows + tid) * 10;
+          if (row[9] == 1.0f) {
+            const double rx = row[0], ry = row[1];
+            const double dphi = atan2(ry, rx) - ph;
+            const bool in_fov = fabs(dphi) <= c.ig_detect_fov_half; /* degrees vs radians, sic */
+            const double rn = sqrt(rx * rx + ry * ry);
+            hit = in_fov && rn <= c.ig_range;
+            tx = rx + px;
+            ty = ry + py;
+          }
+        }
+      } else if (tid < p.n_prev[gj]) {
+        tx = p.targets_prev[gj * 64 + 2 * tid];
+        ty = p.targets_prev[gj * 64 + 2 * tid + 1];
+        hit = true;
+      }
+      const unsigned bal = __ballot_sync(FULL_MASK, hit);
+      if (hit) {
+        const int k = __popc(bal & ((1u << tid) - 1u));
+        const double dx = tx - px, dy = ty - py;
+        double cs, sn;
+        sincos(ph, &sn, &cs);
+        s_det[k][0] = cs * dx + sn * dy;
+        s_det[k][1] = -sn * dx + cs * dy;
+        if (m == 0) { /* becomes this agent's obsvd_targets */
+          p.targets_new[(size_t)g * 64 + 2 * k] = tx;
+          p.targets_new[(size_t)g * 64 + 2 * k + 1] = ty;
+        }
+      }
+      if (tid == 0) {
+        s_ndet = __popc(bal);
+        if (m == 0) p.n_new[g] = __popc(bal);
+        s_qn = 0;
+        PoseBox b;
+        pose_box(c, px, py, ph, b, cnt_clamped);
+        s_box = b;
+      }
+    }
+    __syncthreads();
+    const PoseBox& b = s_box;
+    const int total = b.w * b.h, ndet = s_ndet;
+    for (int off = tid; off < total; off += X_THREADS) {
+      const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
+      const int i = b.x0 + ii, jc = b.y0 + jj;
+      const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, jc, c.map_hh) - b.y;
+      const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
+      if (in_wedge(c, r0, r1)) s_queue[atomicAdd(&s_qn, 1)] = (unsigned short)(((unsigned)jc << 6) | (unsigned)i);
+    }
+    __syncthreads();
+    const int qn = s_qn;
+    for (int q = tid; q < qn; q += X_THREADS) {
+      const unsigned en = s_queue[q];
+      const int jc = (int)((en >> 6) & 63u), i = (int)(en & 63u);
+      const double gx = cell_centre(c, i, c.map_hw), gy = cell_centre(c, jc, c.map_hh);
+      if (!line_of_sight(c, d2, b.x, b.y, gx, gy, cnt_samples, cnt_clamped)) continue;
+      double rs = c.ig_remp;
+      if (ndet > 0) {
+        const double dx = gx - b.x, dy = gy - b.y;
+        const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
+        for (int t = 0; t < ndet; t++) {
+          const double ex = s_det[t][0] - r0, ey = s_det[t][1] - r1;
+          if (sqrt(ex * ex + ey * ey) < c.ig_det_thresh) {
+            rs = c.ig_rocc;
+            break;
+          }
+        }
+      }
+      float* cellp = belief + jc * dim + i;
+      *cellp = fminf((float)((double)*cellp * rs), FLT_MAX);
+      const int bit = jc * 64 + i;
+      atomicOr(&s_seen[bit >> 5], 1u << (bit & 31));
+    }
+    __syncthreads();
+  }
+
+  /* ---- team_obsv_cells / team_reward (ig_mcts.py:136-137) ---- */
+  {
+    const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
+    long long part = 0;
+    for (int w = tid; w < XR_MASK_WORDS; w += X_THREADS) {
+      unsigned int mk = s_seen[w];
+      if (p.team_mask) p.team_mask[(size_t)g * XR_MASK_WORDS + w] = mk;
+      const int jc = w >> 1, i0 = (w & 1) * 32;
+      while (mk && p.team_reward) {
+        const int bb = __ffs(mk) - 1;
+        mk &= mk - 1;
+        part += __double2ll_rn(cell_mi(c, (double)belief[jc * dim + i0 + bb], log_rocc, log_remp) * X_MI_SCALE);
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL_MASK, part, o);
+    if ((tid & 31) == 0 && part) atomicAdd(&s_sum, (unsigned long long)part);
+  }
+  __syncthreads();
+  if (tid == 0 && p.team_reward) p.team_reward[g] = (float)((double)(long long)s_sum / X_MI_SCALE);
+}
+
 }  // namespace
 
 cudaError_t casim_launch_explore(casim_handle* h, const float* state, const float* oas, float* belief,
@@ -651,5 +833,30 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   if (threads == 32) k_rollouts<32><<<grid, 32, 0, s>>>(a);
   else if (threads == 128) k_rollouts<128><<<grid, 128, 0, s>>>(a);
   else k_rollouts<64><<<grid, 64, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+
+cudaError_t casim_launch_team_update(casim_handle* h, const float* state, const float* oas, float* belief,
+                                     const double* targets_prev, const int32_t* n_prev, double* targets_new,
+                                     int32_t* n_new, uint32_t* team_mask, float* team_reward, cudaStream_t s) {
+  TeamArgs a;
+  a.c = h->dc;
+  a.state = reinterpret_cast<const float4*>(state);
+  a.oas = oas;
+  a.belief = belief;
+  a.targets_prev = targets_prev;
+  a.n_prev = n_prev;
+  a.targets_new = targets_new;
+  a.n_new = n_new;
+  a.team_mask = team_mask;
+  a.team_reward = team_reward;
+  a.n_agents = h->n_agents;
+  a.edf = h->edf;
+  a.E = h->E;
+  a.A = h->A;
+  a.n_maps = h->n_maps;
+  h->launches++;
+  k_team_update<<<(unsigned)((size_t)h->E * h->A), X_THREADS, 0, s>>>(a);
   return cudaGetLastError();
 }

@@ -56,6 +56,7 @@ SYMBOLS = {
                                 c_void_p]),
     "casim_explore_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
+    "casim_explore_team_update": (c_int, [c_void_p] * 11),
     "casim_explore_rollouts": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "casim_ga3c_set_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),

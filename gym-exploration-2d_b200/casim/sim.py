@@ -254,6 +254,34 @@ class BatchedSim:
                    "casim_explore_step")
         return self.buf["policy_actions"]
 
+    def explore_team_update(self):
+        """ig_mcts.update_belief for every explorer agent: the belief is updated from the agent's own pose and
+        detections and from the other explorers' poses and detection lists (``buf['team_targets']`` ping-pong)."""
+        if getattr(self, "belief", None) is None:
+            raise _lib.CasimError("explore_team_update needs enable_exploration() first")
+        if self.buf.get("other_agents_states") is None:
+            raise _lib.CasimError("explore_team_update needs the other_agents_states observation buffer")
+        if "team_targets" not in self.buf:
+            dev = self.device
+            self.buf["team_targets"] = [torch.zeros((self.E, self.A, 32, 2), dtype=torch.float64, device=dev) for _ in range(2)]
+            self.buf["team_n"] = [torch.zeros((self.E, self.A), dtype=torch.int32, device=dev) for _ in range(2)]
+            self.buf["team_mask"] = torch.zeros((self.E, self.A, 128), dtype=torch.int32, device=dev)
+            self.buf["team_reward"] = torch.zeros((self.E, self.A), dtype=torch.float32, device=dev)
+        (tp, tn), (cp, cn) = self.buf["team_targets"], self.buf["team_n"]
+        _lib.check(self.lib.casim_explore_team_update(self.handle, _lib.ptr(self.state), _lib.ptr(self.buf["other_agents_states"]),
+                                                      _lib.ptr(self.belief), _lib.ptr(tp), _lib.ptr(cp), _lib.ptr(tn),
+                                                      _lib.ptr(cn), _lib.ptr(self.buf["team_mask"]),
+                                                      _lib.ptr(self.buf["team_reward"]), _stream_ptr()),
+                   "casim_explore_team_update")
+        self.buf["team_targets"], self.buf["team_n"] = [tn, tp], [cn, cp]      # index 0 = the latest lists
+        return self.buf["team_mask"], self.buf["team_reward"]
+
+    def reset_team_targets(self):
+        """Forget the detection lists (a new episode: obsvd_targets is None before the first update, ig_mcts.py:127)."""
+        for k in ("team_targets", "team_n"):
+            for t in self.buf.get(k, []):
+                t.zero_()
+
     def explore_rollouts(self, actions, exclude=None, xdt=1, want_end_pose=True, want_obsvd=True):
         """Dec-MCTS simulation rollouts (ig_mcts.get_next_pose / mcts_sim_state_storer / mcts_reward, the body of
         pydecmcts Tree._simulate) for every explorer agent from its current pose.

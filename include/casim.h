@@ -250,6 +250,19 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
                        float* policy_actions, float* best_mi, float* cand_mi, unsigned long long* counters,
                        void* stream);
 
+/* Replaces ig_mcts.update_belief for every ig_* agent that is not done (policies/ig_mcts.py:117-137, called in
+ * agent order by collision_avoidance_env.py:341-368): the agent's target map is updated from its own pose and
+ * detections (find_targets_in_obs, :139-156) and from the pose of every other explorer j of its environment with
+ * j's obsvd_targets -- this step's list when j < i and j is not done, else the list of j's previous update
+ * (targetMap.update with several poses, information_models/targetMap.py:86-128).
+ * targets_prev / targets_new: [E,A,32,2] fp64 global-frame detections with counts n_prev / n_new [E,A]; the caller
+ * swaps the two pairs between steps (all zero before the first step).  belief: [E,A,dim,dim] fp32 odds, RMW.
+ * team_mask [E,A,128] (team_obsv_cells as a cell mask, layout of casim_explore_rollouts) and team_reward [E,A]
+ * (:137) are optional. */
+int casim_explore_team_update(casim_handle* h, const float* state, const float* other_agents_states, float* belief,
+                              const double* targets_prev, const int32_t* n_prev, double* targets_new, int32_t* n_new,
+                              uint32_t* team_mask, float* team_reward, void* stream);
+
 /* Dec-MCTS simulation rollouts for every ig_* agent (policy id CASIM_POLICY_IG_GREEDY): replaces the body of
  * pydecmcts Tree._simulate (policies/pydecmcts/DecMCTS.py:233-269) with ig_mcts's callbacks -- get_next_pose
  * (policies/ig_mcts.py:173-198: first-order step, strict in-map test, EDF clearance > radius + 0.1),
