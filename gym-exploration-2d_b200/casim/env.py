@@ -210,12 +210,22 @@ class BatchedCollisionAvoidanceEnv:
             if self.obstacles is None:
                 raise RuntimeError("ig_greedy agents need a static map (set_static_map)")
             sim.enable_exploration()
+        self._mcts = None
+        self._mcts_params = None
+        if self._has_ig and self.agents is not None:
+            pols = [a.policy for ags in self.agents for a in ags if getattr(a.policy, "str", "") == "ig_mcts"]
+            if pols:                                   # the planner parameters are the first ig_mcts agent's (:344)
+                self._mcts_params = pols[0]
         if self._has_ga3c:
             if self._ga3c_weights is None:
                 raise RuntimeError("GA3CCADRLPolicy agents need set_ga3c_weights() (random-init or a loaded checkpoint)")
             sim.ga3c_set_weights(self._ga3c_weights)
         sim.reset(init, types, n)
         self._types = types
+        if self._has_ig and getattr(self, "_mcts_params", None) is not None:
+            from .mcts import TeamPlanner
+            sim.reset_team_targets()
+            self._mcts = TeamPlanner(sim, self._mcts_params)
         self._ext = torch.zeros((self.E, self.A, 2), dtype=torch.float32, device=sim.device) if self._needs_actions else None
         # only the entries whose sensors exist are emitted (the reference yields np.array(None) for the others)
         avail = {"other_agents_states": sim.buf["other_agents_states"], "other_agent_states": sim.buf["other_agents_states"],
@@ -252,7 +262,15 @@ class BatchedCollisionAvoidanceEnv:
             raise RuntimeError("call reset() first")
         ext = self._actions_tensor(actions) if self._needs_actions else None
         pol = None
-        if self._has_ig:
+        if self._has_ig and self._mcts is not None:
+            # ig_mcts.find_next_action (ig_mcts.py:79-109): team belief update, then Dec-MCTS planning on the host over
+            # the GPU rollout evaluator
+            sim.explore_team_update()
+            done = (sim.state[5].view(torch.int32)[..., 2] & L.F_IS_DONE) != 0
+            acts = self._mcts.plan(done.cpu().numpy())
+            pol = sim._policy_buffers()
+            pol.copy_(torch.from_numpy(acts))
+        elif self._has_ig:
             pol = sim.explore_step()
         if self._has_ga3c:
             pol = sim.ga3c_forward(use_tensor_cores=True)

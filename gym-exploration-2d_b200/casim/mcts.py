@@ -241,13 +241,15 @@ class BatchedDecMCTS:
         self.comms.append((dist, valid & (dist.n > 0)))
 
 
-def sim_evaluator(sim, xdt=1):
-    """The GPU evaluator: trees = the explorer agents of ``sim`` (policy id IG_GREEDY) in (env, agent) order.
-    Returns (n_trees, evaluate, masks_of) for BatchedDecMCTS / distribution(with_masks=)."""
+def sim_evaluator(sim, xdt=1, select=None):
+    """The GPU evaluator: trees = the explorer agents of ``sim`` (policy id IG_GREEDY) in (env, agent) order, or the
+    agents marked in ``select`` [E,A] bool.  Returns (n_trees, evaluate, masks_of, (env index, agent index))."""
     import torch
     from . import layout as L
-    types = sim._keep["types"].cpu().numpy()
-    te, ta = np.nonzero((types & 0xff) == L.POLICY_IG_GREEDY)
+    if select is None:
+        types = sim._keep["types"].cpu().numpy()
+        select = (types & 0xff) == L.POLICY_IG_GREEDY
+    te, ta = np.nonzero(select)
     E, A = sim.E, sim.A
 
     def scatter(x, fill, dtype):
@@ -267,3 +269,70 @@ def sim_evaluator(sim, xdt=1):
         return out["obsvd"].cpu().numpy()[te, ta]
 
     return len(te), evaluate, masks_of, (te, ta)
+
+
+class TeamPlanner:
+    """ig_mcts.find_next_action for every explorer of a batch, sequenced like collision_avoidance_env._take_action_dmcts
+    (:341-379): ``Ncycles`` cycles; in each cycle the explorers of an environment plan one after the other (so the r-th
+    explorer of every environment forms one batch of trees), each receiving the others' latest action distributions --
+    this cycle's from the explorers that planned before it, the previous cycle's / step's from the others -- and growing
+    its tree ``Ntree`` times.  Cycle 0 of a step starts a new tree (new_step, ig_mcts.py:89-93).
+    Which distributions an agent receives follows ig_mcts.py:96-98 literally: ``for j in range(len(dmcts_agents)):
+    agents[j].policy.best_paths`` -- agents 0 .. n_explorers-2 (sic: an index into the list is used as an agent index),
+    of which its own entry is overwritten by its own state in _get_system_state; explorers are expected first in the
+    agent list, as in the reference's scenarios."""
+
+    def __init__(self, sim, params):
+        from . import layout as L
+        self.sim, self.p = sim, params
+        types = sim._keep["types"].cpu().numpy()
+        self.ig = (types & 0xff) == L.POLICY_IG_GREEDY
+        self.rank = np.where(self.ig, np.cumsum(self.ig, 1) - 1, -1)
+        self.n_ig = self.ig.sum(1)
+        self.R = int(self.n_ig.max()) if self.ig.any() else 0
+        E, H, n = sim.E, params.mcts_horizon, 5
+        self.best = [dict(seqs=np.full((E, n, H), END, np.uint8), q=np.zeros((E, n)), masks=np.zeros((E, n, 128), np.int32))
+                     for _ in range(self.R)]
+        self.trees = [None] * self.R
+        self.steps = 0
+
+    def reset(self):
+        for b in self.best:
+            b["seqs"][:] = END
+            b["q"][:] = 0
+            b["masks"][:] = 0
+        self.steps = 0
+
+    def plan(self, done):
+        """done [E,A] bool (agents that are not asked for an action, collision_avoidance_env.py:298-299).
+        Returns float32 [E,A,2] actions ([vel, dphi]; zeros for everyone who did not plan)."""
+        sim, p = self.sim, self.p
+        actions = np.zeros((sim.E, sim.A, 2), np.float32)
+        for cycle in range(p.Ncycles):
+            for r in range(self.R):
+                sel = self.ig & (self.rank == r) & ~done
+                if not sel.any():
+                    continue
+                T, ev, masks_of, (te, ta) = sim_evaluator(sim, p.xDT, select=sel)
+                if cycle == 0:
+                    tree = BatchedDecMCTS(T, ev, horizon=p.mcts_horizon, c_p=p.mcts_cp, comm_n=5,
+                                          seed=(p.seed, self.steps, r))
+                    self.trees[r] = (tree, te)
+                else:
+                    tree, te_old = self.trees[r]
+                    assert np.array_equal(te_old, te)
+                    tree.comms = []                      # receive_comms replaces the entry of the same robot (:379)
+                for j in range(self.R - 1):             # sic, see the class docstring
+                    if j == r:
+                        continue
+                    b = self.best[j]
+                    dist = ActionDistribution(b["seqs"][te], b["q"][te], b["masks"][te])
+                    tree.receive_comms(dist, valid=(j < self.n_ig[te] - 1))
+                for _ in range(p.Ntree):
+                    tree.grow(nsims=p.Nsims, gamma=p.mcts_gamma)
+                d = tree.distribution(with_masks=masks_of)
+                self.best[r]["seqs"][te], self.best[r]["q"][te], self.best[r]["masks"][te] = d.seqs, d.q, d.masks
+                a = tree.best_action_index()
+                actions[te, ta] = np.where((a >= 0)[:, None], action_value(np.maximum(a, 0)), 0.0)
+        self.steps += 1
+        return actions

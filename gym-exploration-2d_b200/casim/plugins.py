@@ -55,6 +55,25 @@ class ig_greedy(Policy):  # noqa: N801  (reference class name)
     policy_id, str = L.POLICY_IG_GREEDY, "ig_greedy"
 
 
+class ig_mcts(Policy):  # noqa: N801  (reference class name)
+    """envs/policies/ig_mcts.py: team belief update (casim_explore_team_update) + Dec-MCTS planning (casim/mcts.py over
+    casim_explore_rollouts).  An explorer like ig_greedy as far as the kernels are concerned (same policy id); the
+    planner parameters are those of ``set_param`` (ig_mcts.py:54-77) with the reference's defaults (:45-52)."""
+    policy_id, str = L.POLICY_IG_GREEDY, "ig_mcts"
+
+    def __init__(self, Ntree=100, Nsims=10, mcts_cp=1.0, mcts_horizon=10, mcts_gamma=1.0, Ncycles=5, xdt=1, seed=0):
+        self.Ntree, self.Nsims, self.mcts_cp, self.mcts_horizon = int(Ntree), int(Nsims), float(mcts_cp), int(mcts_horizon)
+        self.mcts_gamma, self.Ncycles, self.xDT, self.seed = float(mcts_gamma), int(Ncycles), int(xdt), int(seed)
+
+    def set_param(self, ego_agent=None, occ_map=None, map_size=None, map_res=None, detect_fov=None, detect_range=None,
+                  dt=0.1, xdt=1, Ntree=100, Nsims=10, parallelize_sims=False, mcts_cp=1., mcts_horizon=10, mcts_gamma=1,
+                  Ncycles=5, parallelize_agents=False):
+        """ig_mcts.set_param (ig_mcts.py:54-77): the planner parameters; the map / sensor arguments are the batch's
+        (Config + set_static_map) and are accepted for call compatibility only."""
+        self.__init__(Ntree=Ntree, Nsims=Nsims, mcts_cp=mcts_cp, mcts_horizon=mcts_horizon, mcts_gamma=mcts_gamma,
+                      Ncycles=Ncycles, xdt=xdt, seed=self.seed)
+
+
 class GA3CCADRLPolicy(Policy):
     """envs/policies/GA3CCADRLPolicy.py:34-43 (casim_ga3c_forward)"""
     policy_id, str = L.POLICY_GA3C_CADRL, "GA3CCADRLPolicy"

@@ -105,3 +105,56 @@ def test_mcts_c4_planning_step():
     assert act.shape == (2 * E, 2) and np.isin(act[:, 0], (0.0, 2.0, 4.0)).all()
     assert float(t1.mu[:, 1:].max()) > 0.3 and np.isfinite(t1.mu).all()
     sim.close()
+
+
+def test_env_runs_ig_mcts_policy():
+    """ig_mcts agents driven by the env itself: team belief update + Dec-MCTS planning inside step(); two explorers
+    and two static targets per environment, explorers first (the reference's layout)."""
+    import torch
+    from casim import plugins as P
+    from casim.env import BatchedCollisionAvoidanceEnv
+    from casim.config import Config
+
+    class Cfg(Config):
+        pass
+
+    E = 6
+    rng = np.random.default_rng(1)
+    envs_agents = []
+    for e in range(E):
+        x = float(rng.uniform(-9, -5))
+        ags = [P.Agent(x, 0.4, 9, 0, 0.5, 1.0, 0.0, P.ig_mcts, P.FirstOrderDynamics, [P.OtherAgentsStatesSensor], 0),
+               P.Agent(0.3, -8 + e * 0.3, 0, 9, 0.5, 1.0, 1.5, P.ig_mcts, P.FirstOrderDynamics, [P.OtherAgentsStatesSensor], 1),
+               P.Agent(x + 3.0, -0.3, 0, 0, 0.2, 1.0, 0.0, P.StaticPolicy, P.UnicycleDynamics, [], 2),
+               P.Agent(0.0, -3.0, 0, 0, 0.2, 1.0, 0.0, P.StaticPolicy, P.UnicycleDynamics, [], 3)]
+        for a in ags[:2]:
+            a.policy.set_param(Ntree=6, Nsims=4, mcts_horizon=6, Ncycles=2, mcts_gamma=1)
+        envs_agents.append(ags)
+    crossing = [[(10, 10), (2, 10), (2, 2), (10, 2)], [(-2, 10), (-10, 10), (-10, 2), (-2, 2)],
+                [(10, -2), (2, -2), (2, -10), (10, -10)], [(-2, -2), (-10, -2), (-10, -10), (-2, -10)]]
+
+    def run():
+        env = BatchedCollisionAvoidanceEnv(num_envs=E, max_agents=4, config=Cfg)
+        env.set_agents(envs_agents)
+        env.set_static_map(crossing)
+        env.reset()
+        p0 = env.sim.state[0, :, :, 0:2].clone()
+        acts = []
+        for t in range(4):
+            obs, rewards, game_over, info = env.step()
+            acts.append(env.sim.buf["policy_actions"].cpu().numpy().copy())
+        torch.cuda.synchronize()
+        out = (env.sim.state.cpu().numpy().copy(), env.sim.belief.cpu().numpy().copy(), np.array(acts),
+               (env.sim.state[0, :, :, 0:2] - p0).norm(dim=-1).cpu().numpy(), env._mcts)
+        env.close()
+        return out
+
+    state, belief, acts, moved, planner = run()
+    assert np.isin(acts[:, :, :2, 0], (0.0, 2.0, 4.0)).all()
+    assert np.isin(np.round(acts[:, :, :2, 1] / (0.5 * np.pi)), (-1, 0, 1)).all() and (acts[:, :, 2:] == 0).all()
+    assert (moved[:, :2] > 0.2).any() and (moved[:, 2:] == 0).all()
+    assert (belief[:, :2] != 1.0).any() and (belief[:, 2:] == 1.0).all()
+    # explorer 1 plans after explorer 0 and receives its distribution (the only comms the reference's indexing yields)
+    assert (planner.best[0]["q"].sum(1) > 0).all() and planner.trees[1][0].comms and not planner.trees[0][0].comms
+    state2, belief2, acts2, _, _ = run()
+    assert np.array_equal(acts, acts2) and np.array_equal(state, state2) and np.array_equal(belief, belief2)
