@@ -99,33 +99,38 @@ class BatchedDecMCTS:
             else:
                 draws = self.rng.integers(0, N_ACTIONS, (T, nsims, H)).astype(np.uint8)
             tail = np.arange(H)[None, None, :] >= stage[:, None, None]
-            sims = seqs[:, N_ACTIONS:]
-            sims[tail.repeat(nsims, 1)] = draws[tail.repeat(nsims, 1)]
+            seqs[:, N_ACTIONS:] = np.where(tail, draws, seqs[:, N_ACTIONS:])
         rewards, n_feasible = self.evaluate(seqs, exclude)
         self.launches += 1
         feasible = can[:, None] & (n_feasible[:, :N_ACTIONS] == (stage + 1)[:, None])
         return seqs[:, N_ACTIONS:], feasible, np.asarray(rewards[:, N_ACTIONS:], np.float64)
 
+    def reserve(self, n_grows):
+        """Room for `n_grows` more iterations (each adds at most 9 nodes per tree) without re-allocating."""
+        need = int(self.n_nodes.max()) + N_ACTIONS * int(n_grows)
+        if need > self.M:
+            self._alloc(need)
+
     def _expand(self, node, feasible):
         """_expansion (:201-231): a child per feasible action, in action order; nothing at stage == horizon."""
-        T = self.T
-        r = self._rows()
         need = int((self.n_nodes + N_ACTIONS).max())
         if need > self.M:
             self._alloc(max(need, 2 * self.M))
-        for a in range(N_ACTIONS):
-            ok = feasible[:, a] & (self.nchild[r, node] < N_ACTIONS)
-            t = r[ok]
-            if t.size == 0:
-                continue
-            new, par = self.n_nodes[t], node[t]
-            self.parent[t, new] = par
-            self.stage[t, new] = self.stage[t, par] + 1
-            self.path[t, new] = self.path[t, par]
-            self.path[t, new, self.stage[t, par]] = a
-            self.child[t, par, self.nchild[t, par]] = new
-            self.nchild[t, par] += 1
-            self.n_nodes[t] += 1
+        tt, aa = np.nonzero(feasible)                       # row-major: per tree in action order
+        if tt.size == 0:
+            return
+        k = (np.cumsum(feasible, 1) - 1)[tt, aa]            # position among the tree's new children
+        par = node[tt]
+        new = self.n_nodes[tt] + k
+        st = self.stage[tt, par]
+        self.parent[tt, new] = par
+        self.stage[tt, new] = st + 1
+        self.path[tt, new] = self.path[tt, par]
+        self.path[tt, new, st] = aa
+        self.child[tt, par, k] = new
+        cnt = feasible.sum(1)
+        self.nchild[self._rows(), node] += cnt
+        self.n_nodes += cnt
 
     # ---------------------------------------------------------------- one iteration
     def _system_exclude(self):
@@ -317,6 +322,7 @@ class TeamPlanner:
                 if cycle == 0:
                     tree = BatchedDecMCTS(T, ev, horizon=p.mcts_horizon, c_p=p.mcts_cp, comm_n=5,
                                           seed=(p.seed, self.steps, r))
+                    tree.reserve(p.Ntree * p.Ncycles)
                     self.trees[r] = (tree, te)
                 else:
                     tree, te_old = self.trees[r]
