@@ -363,3 +363,26 @@ def packs_from_state(state):
     for k in L.INT_WORDS:
         iw[..., k] = state[..., k].astype(np.int32)
     return np.ascontiguousarray(w.reshape(E, A, W // 4, 4).transpose(2, 0, 1, 3))
+
+
+# scenario generators (casim_oracle_scenario.c)
+SCENARIO_SWAP_CIRCLE, SCENARIO_RANDOM_POSITIONS = 0, 1
+
+
+def scenario(kind, E, A, number_of_agents, seeds, ego_policy, ego_dynamics, other_dynamics=0):
+    """train_agents_swap_circle / train_agents_random_positions(seed=seeds[e]) for E environments.
+    Returns dict(init [E,A,7] f64 (heading NaN = towards the goal), types [E,A] i32, n_agents [E] i32, coop [E,A])."""
+    seeds = np.ascontiguousarray(seeds, dtype=np.uint32)
+    assert seeds.shape == (E,) and (seeds != 0).all()
+    init = np.zeros((E, A, 7), np.float64)
+    types = np.zeros((E, A), np.int32)
+    n = np.zeros((E,), np.int32)
+    coop = np.zeros((E, A), np.float64)
+    f = lib().casim_oracle_scenario
+    f.argtypes = [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p] * 4
+    f.restype = ctypes.c_int
+    rc = f(int(kind), E, A, int(number_of_agents), _p(seeds), int(ego_policy), int(ego_dynamics), int(other_dynamics),
+           _p(init), _p(types), _p(n), _p(coop))
+    if rc:
+        raise ValueError("casim_oracle_scenario: invalid arguments")
+    return dict(init=init, types=types, n_agents=n, coop=coop)

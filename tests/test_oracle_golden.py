@@ -239,6 +239,24 @@ def test_team_update_vs_reference(oracle_lib):
                 assert int(npv[0, i]) == int(s["n_targets"][i])
 
 
+def test_scenario_generators_vs_reference(oracle_lib):
+    """train_agents_swap_circle / train_agents_random_positions(seed=s): the reference's own scenarios (numpy's and
+    CPython's MT19937 streams restated): positions to 1e-12, policies / dynamics / sensors / counts exact."""
+    oracle = oracle_lib
+    z = H.load("scenarios.npz")
+    A = z["init"].shape[1]
+    assert len(z["kind"]) >= 80 and set(z["kind"].tolist()) == {0, 1}
+    for k in range(len(z["kind"])):
+        o = oracle.scenario(int(z["kind"][k]), 1, A, int(z["number_of_agents"][k]), z["seed"][k:k + 1],
+                            L.POLICY_LEARNING, L.DYN_FIRST_ORDER, L.DYN_UNICYCLE)
+        n = int(z["n_agents"][k])
+        assert int(o["n_agents"][0]) == n, k
+        assert np.array_equal(o["types"][0], z["types"][k]), k
+        H.assert_close(o["init"][0, :n, :6], z["init"][k, :n, :6], "scenario %d init" % k, rtol=1e-12, atol=1e-12)
+        assert np.isnan(o["init"][0, :n, 6]).all() and not o["init"][0, n:].any()
+        assert np.array_equal(o["coop"][0], z["coop"][k]), k
+
+
 def test_ga3c_state_vector_vs_reference(oracle_lib):
     """agents_to_ga3c_cadrl_state (GA3CCADRLPolicy.py:45-106): slot ORDER exact (Python round(x, 2), stable sort on
     (-round(dist, 2), p_orthog), clip to the closest N), values to 1e-12."""
