@@ -105,6 +105,9 @@ cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_ou
 cudaError_t casim_launch_explore(casim_handle* h, const float* state, const float* oas, float* belief,
                                  float* policy_actions, float* best_mi, float* cand_mi,
                                  unsigned long long* counters, cudaStream_t s);
+cudaError_t casim_launch_scenario(casim_handle* h, int kind, int number_of_agents, const uint32_t* seeds, int ego_policy,
+                                  int ego_dynamics, int other_dynamics, float* init, int32_t* types, int32_t* n_agents,
+                                  float* coop, cudaStream_t s);
 cudaError_t casim_launch_team_update(casim_handle* h, const float* state, const float* oas, float* belief,
                                      const double* targets_prev, const int32_t* n_prev, double* targets_new,
                                      int32_t* n_new, uint32_t* team_mask, float* team_reward, cudaStream_t s);

@@ -56,6 +56,8 @@ SYMBOLS = {
                                 c_void_p]),
     "casim_explore_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
+    "casim_generate_scenario": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p]),
     "casim_explore_team_update": (c_int, [c_void_p] * 11),
     "casim_explore_rollouts": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -146,6 +146,23 @@ class BatchedSim:
         self._keep["traj"] = t
         _lib.check(self.lib.casim_set_trajectories(self.handle, _lib.ptr(t), t.shape[2]), "casim_set_trajectories")
 
+    def generate_scenario(self, kind, number_of_agents, seeds, ego_policy, ego_dynamics, other_dynamics=L.DYN_UNICYCLE):
+        """The reference's seeded scenario generators on the device (test_cases.py:1192-1463): kind =
+        layout.SCENARIO_SWAP_CIRCLE / SCENARIO_RANDOM_POSITIONS, seeds [E] (non-zero).  Returns device tensors
+        (init [E,A,7], types [E,A], n_agents [E], coop [E,A]) ready for ``reset``."""
+        seeds = torch.as_tensor(np.ascontiguousarray(seeds, dtype=np.uint32).view(np.int32)).to(self.device) \
+            if not isinstance(seeds, torch.Tensor) else seeds.to(device=self.device, dtype=torch.int32).contiguous()
+        assert seeds.shape == (self.E,)
+        init = torch.empty((self.E, self.A, 7), dtype=torch.float32, device=self.device)
+        types = torch.empty((self.E, self.A), dtype=torch.int32, device=self.device)
+        n = torch.empty((self.E,), dtype=torch.int32, device=self.device)
+        coop = torch.empty((self.E, self.A), dtype=torch.float32, device=self.device)
+        _lib.check(self.lib.casim_generate_scenario(self.handle, int(kind), int(number_of_agents), _lib.ptr(seeds),
+                                                    int(ego_policy), int(ego_dynamics), int(other_dynamics), _lib.ptr(init),
+                                                    _lib.ptr(types), _lib.ptr(n), _lib.ptr(coop), _stream_ptr()),
+                   "casim_generate_scenario")
+        return init, types, n, coop
+
     def reset(self, init, types, n_agents=None):
         """init [E,A,7] = start_x, start_y, goal_x, goal_y, radius, pref_speed, heading (NaN = towards goal);
         types [E,A] int32 type words (layout.encode_type)."""
