@@ -139,14 +139,15 @@ class BatchedDecMCTS:
         if not self.comms:
             return None
         out = np.zeros((self.T, 128), np.int32)
-        for dist, valid in self.comms:
+        for dist, valid, draw in self.comms:
             n = dist.q.shape[1]
             if self.reference_order:
-                pick = np.array([np.random.choice(n, p=dist.q[t]) if valid[t] else 0 for t in range(self.T)])
+                pick = np.array([np.random.choice(n, p=dist.q[t]) if (valid[t] or draw[t]) else 0 for t in range(self.T)])
             else:
                 u = self.rng.random(self.T)[:, None]
                 pick = np.minimum((u > np.cumsum(dist.q, 1)).sum(1), n - 1)
-            out |= np.where(valid[:, None], dist.masks[self._rows(), pick], 0)
+            if valid.any():
+                out |= np.where(valid[:, None], dist.masks[self._rows(), pick], 0)
         return out
 
     def grow(self, nsims=10, gamma=0.9):
@@ -239,11 +240,14 @@ class BatchedDecMCTS:
         a = d.seqs[:, 0, 0].astype(np.int64)
         return np.where(d.n > 0, a, -1)
 
-    def receive_comms(self, dist, valid=None):
+    def receive_comms(self, dist, valid=None, draw_only=None):
         """receive_comms (:367-380) for every tree at once: ``dist`` holds, per tree, ONE other robot's distribution
-        (with masks); ``valid`` [T] marks the trees that do have such a robot.  Call once per communicating robot."""
+        (with masks); ``valid`` [T] marks the trees that do have such a robot.  Call once per communicating robot.
+        ``draw_only`` [T]: entries whose sampled path is discarded but whose random draw still happens (a tree that
+        was handed its own distribution: _get_system_state samples it, then overwrites it, :192-193)."""
         valid = np.ones(self.T, bool) if valid is None else np.asarray(valid, bool)
-        self.comms.append((dist, valid & (dist.n > 0)))
+        draw = np.zeros(self.T, bool) if draw_only is None else np.asarray(draw_only, bool)
+        self.comms.append((dist, valid & (dist.n > 0), draw & (dist.n > 0)))
 
 
 def sim_evaluator(sim, xdt=1, select=None):
@@ -321,7 +325,8 @@ class TeamPlanner:
                 T, ev, masks_of, (te, ta) = sim_evaluator(sim, p.xDT, select=sel)
                 if cycle == 0:
                     tree = BatchedDecMCTS(T, ev, horizon=p.mcts_horizon, c_p=p.mcts_cp, comm_n=5,
-                                          seed=(p.seed, self.steps, r))
+                                          seed=(p.seed, self.steps, r),
+                                          reference_order=getattr(p, "reference_order", False))
                     tree.reserve(p.Ntree * p.Ncycles)
                     self.trees[r] = (tree, te)
                 else:
@@ -329,11 +334,13 @@ class TeamPlanner:
                     assert np.array_equal(te_old, te)
                     tree.comms = []                      # receive_comms replaces the entry of the same robot (:379)
                 for j in range(self.R - 1):             # sic, see the class docstring
-                    if j == r:
-                        continue
                     b = self.best[j]
                     dist = ActionDistribution(b["seqs"][te], b["q"][te], b["masks"][te])
-                    tree.receive_comms(dist, valid=(j < self.n_ig[te] - 1))
+                    listed = j < self.n_ig[te] - 1
+                    if j == r:                          # its own entry: sampled, then overwritten by its own state
+                        tree.receive_comms(dist, valid=np.zeros(T, bool), draw_only=listed)
+                    else:
+                        tree.receive_comms(dist, valid=listed)
                 for _ in range(p.Ntree):
                     tree.grow(nsims=p.Nsims, gamma=p.mcts_gamma)
                 d = tree.distribution(with_masks=masks_of)

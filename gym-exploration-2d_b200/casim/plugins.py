@@ -64,6 +64,7 @@ class ig_mcts(Policy):  # noqa: N801  (reference class name)
     def __init__(self, Ntree=100, Nsims=10, mcts_cp=1.0, mcts_horizon=10, mcts_gamma=1.0, Ncycles=5, xdt=1, seed=0):
         self.Ntree, self.Nsims, self.mcts_cp, self.mcts_horizon = int(Ntree), int(Nsims), float(mcts_cp), int(mcts_horizon)
         self.mcts_gamma, self.Ncycles, self.xDT, self.seed = float(mcts_gamma), int(Ncycles), int(xdt), int(seed)
+        self.reference_order = getattr(self, "reference_order", False)   # tests: draw from np.random like the reference
 
     def set_param(self, ego_agent=None, occ_map=None, map_size=None, map_res=None, detect_fov=None, detect_range=None,
                   dt=0.1, xdt=1, Ntree=100, Nsims=10, parallelize_sims=False, mcts_cp=1., mcts_horizon=10, mcts_gamma=1,

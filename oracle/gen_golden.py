@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz by executing the UNMODIFIED reference
 (/root/reference, behind oracle/ref_harness.py) in the build container.
 
-    python oracle/gen_golden.py [core|sensors|c1|reset|maps|explore|rollouts|mcts|team|scenarios|ga3c|all]
+    python oracle/gen_golden.py [core|sensors|c1|reset|maps|explore|rollouts|mcts|mcts_env|team|scenarios|ga3c|all]
 
 The fixtures are committed; this script is the provenance.  Inputs are float32-representable
 doubles (the GPU state is fp32) and headings / dt are passed as np.float64 so that numpy 2
@@ -564,6 +564,9 @@ def main():
     if what in ("scenarios", "all"):
         from oracle import gen_golden_scenarios
         gen_golden_scenarios.main(ns)
+    if what in ("mcts_env", "all"):
+        from oracle import gen_golden_explore
+        gen_golden_explore.main_mcts_env(ns)
     if what in ("team", "all"):
         from oracle import gen_golden_explore
         gen_golden_explore.main_team(ns)

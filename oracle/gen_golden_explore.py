@@ -331,3 +331,41 @@ def main_team(ns, seed=99, nsteps=3):
     nt = out["n_targets"]
     print("wrote team.npz: %d scenes x %d steps x %d explorers; detections %d; mean team cells %.1f" % (
         nscenes, nsteps, n_ig, int(nt[nt > 0].sum()), np.mean([np.unpackbits(m).sum() for m in out["team_mask"].reshape(-1, out["team_mask"].shape[-1])])))
+
+
+def main_mcts_env(ns, seed=31, nsteps=3, Ntree=6, Nsims=3, H=4, Ncycles=2):
+    """tests/golden/mcts_env.npz: the UNMODIFIED reference CollisionAvoidanceEnv.step on the fork's own exploration
+    scenario tc.IG_agent_crossing (test_cases.py:3209-3239: three ig_mcts explorers, two static targets, crossing map),
+    planner parameters set through ig_mcts.set_param, np.random seeded before every step.  Recorded per step: every
+    agent's pose and action, every explorer's target map, detections and planned first action."""
+    from oracle import ref_harness as rh
+    with rh.quiet():
+        from gym_collision_avoidance.envs import test_cases as tc
+        agents, obstacles = tc.IG_agent_crossing()
+    env = rh.make_env(ns, agents, obstacles, ['dist_to_goal', 'rel_goal', 'radius', 'heading_ego_frame',
+                                              'heading_global_frame', 'pos_global_frame', 'pref_speed',
+                                              'other_agents_states', 'laserscan'])
+    ig = [i for i, a in enumerate(agents) if "ig_mcts" in str(type(a.policy))]
+    for i in ig:
+        agents[i].policy.set_param(agents[i], env.map, (30, 30), 0.1, 60.0, 5.0, dt=0.1, xdt=1, Ntree=Ntree, Nsims=Nsims,
+                                   mcts_horizon=H, mcts_gamma=1, Ncycles=Ncycles)
+    A = len(agents)
+    out = {"static": np.packbits(env.map.static_map.astype(np.uint8)), "seed": seed, "Ntree": Ntree, "Nsims": Nsims,
+           "H": H, "Ncycles": Ncycles, "n_ig": len(ig),
+           "init": np.array([[a.pos_global_frame[0], a.pos_global_frame[1], a.goal_global_frame[0], a.goal_global_frame[1],
+                              a.radius, a.pref_speed, a.heading_global_frame] for a in agents])}
+    rec = {k: [] for k in ("pose", "belief", "action", "n_targets", "rewards", "done")}
+    for step in range(nsteps):
+        np.random.seed(seed + step)
+        obs, rewards, game_over, info = rh.step(env)
+        rec["pose"].append([[a.pos_global_frame[0], a.pos_global_frame[1], a.heading_global_frame] for a in agents])
+        rec["belief"].append([agents[i].policy.targetMap.map.copy() for i in ig])
+        rec["action"].append([np.asarray(agents[i].policy.best_paths.X[0].action_seq[0], np.float64) for i in ig])
+        rec["n_targets"].append([len(agents[i].policy.obsvd_targets) for i in ig])
+        rec["rewards"].append(np.asarray(rewards, np.float64).reshape(-1)[:A])
+        rec["done"].append([bool(a.is_done) for a in agents])
+    for k, v in rec.items():
+        out[k] = np.array(v)
+    np.savez_compressed(os.path.join(GOLDEN, "mcts_env.npz"), **out)
+    print("wrote mcts_env.npz: %d steps, actions %s, moved %s" % (
+        nsteps, out["action"].tolist(), np.round(out["pose"][-1][:, :2] - out["init"][:, :2], 3).tolist()))

@@ -155,6 +155,54 @@ def test_env_runs_ig_mcts_policy():
     assert (moved[:, :2] > 0.2).any() and (moved[:, 2:] == 0).all()
     assert (belief[:, :2] != 1.0).any() and (belief[:, 2:] == 1.0).all()
     # explorer 1 plans after explorer 0 and receives its distribution (the only comms the reference's indexing yields)
-    assert (planner.best[0]["q"].sum(1) > 0).all() and planner.trees[1][0].comms and not planner.trees[0][0].comms
+    assert (planner.best[0]["q"].sum(1) > 0).all() and \
+        any(v.any() for _, v, _ in planner.trees[1][0].comms) and not any(v.any() for _, v, _ in planner.trees[0][0].comms)
     state2, belief2, acts2, _, _ = run()
     assert np.array_equal(acts, acts2) and np.array_equal(state, state2) and np.array_equal(belief, belief2)
+
+
+def test_env_step_with_ig_mcts_vs_reference_env():
+    """The reference's own CollisionAvoidanceEnv.step on the fork's exploration scenario (tc.IG_agent_crossing: three
+    ig_mcts explorers + two static targets, crossing map; tests/golden/mcts_env.npz) against this env's step with the
+    same planner parameters and the same np.random stream: planned actions exact, poses / target maps to 1e-5."""
+    import torch
+    from casim import plugins as P
+    from casim.env import BatchedCollisionAvoidanceEnv
+    from casim.config import Config
+
+    class Cfg(Config):
+        TRAIN_SINGLE_AGENT = False        # as in the harness that recorded the golden (rewards for every agent)
+
+    z = H.load("mcts_env.npz")
+    n_ig = int(z["n_ig"])
+    agents = []
+    for k, row in enumerate(z["init"]):
+        if k < n_ig:
+            a = P.Agent(row[0], row[1], row[2], row[3], row[4], row[5], row[6], P.ig_mcts, P.FirstOrderDynamics,
+                        [P.OtherAgentsStatesSensor, P.LaserScanSensor], k)
+            a.policy.set_param(Ntree=int(z["Ntree"]), Nsims=int(z["Nsims"]), mcts_horizon=int(z["H"]),
+                               Ncycles=int(z["Ncycles"]), mcts_gamma=1)
+            a.policy.reference_order = True
+        else:
+            a = P.Agent(row[0], row[1], row[2], row[3], row[4], row[5], row[6], P.StaticPolicy, P.FirstOrderDynamics, [], k)
+        agents.append(a)
+    crossing = [[(10, 10), (2, 10), (2, 2), (10, 2)], [(-2, 10), (-10, 10), (-10, 2), (-2, 2)],
+                [(10, -2), (2, -2), (2, -10), (10, -10)], [(-2, -2), (-10, -2), (-10, -10), (-2, -10)]]
+    env = BatchedCollisionAvoidanceEnv(num_envs=1, max_agents=len(agents), config=Cfg)
+    env.set_agents(agents)
+    env.set_static_map(crossing)
+    env.reset()
+    for step in range(z["pose"].shape[0]):
+        np.random.seed(int(z["seed"]) + step)
+        obs, rewards, game_over, info = env.step()
+        torch.cuda.synchronize()
+        acts = env.sim.buf["policy_actions"].cpu().numpy()[0]
+        assert np.array_equal(acts[:n_ig].astype(np.float64), z["action"][step].astype(np.float32).astype(np.float64)), step
+        st = env.sim.state_numpy()[0]
+        pose = st[:, [L.PX, L.PY, L.HEADING]]
+        H.assert_close(pose, z["pose"][step], "pose after step %d" % step, rtol=1e-5, atol=1e-5)
+        b = env.sim.belief.cpu().numpy()[0, :n_ig].astype(np.float64)
+        H.assert_close(b, z["belief"][step], "target maps after step %d" % step, rtol=1e-5, atol=0)
+        assert np.array_equal(env.sim.buf["team_n"][0].cpu().numpy()[0, :n_ig], z["n_targets"][step])
+        H.assert_close(rewards.cpu().numpy().reshape(-1), z["rewards"][step], "rewards step %d" % step, rtol=1e-5, atol=1e-6)
+    env.close()
