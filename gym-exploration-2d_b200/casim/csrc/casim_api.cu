@@ -455,7 +455,7 @@ int casim_generate_scenario(casim_handle* h, int kind, int number_of_agents, con
                             int ego_dynamics, int other_dynamics, float* init, int32_t* types, int32_t* n_agents,
                             float* coop, void* stream) {
   REQUIRE(h && seeds && init && types && n_agents, "null argument");
-  REQUIRE(kind == CASIM_SCENARIO_SWAP_CIRCLE || kind == CASIM_SCENARIO_RANDOM_POSITIONS, "unknown scenario kind");
+  REQUIRE(kind >= CASIM_SCENARIO_SWAP_CIRCLE && kind <= CASIM_SCENARIO_PAIRWISE_SWAP, "unknown scenario kind");
   const int n = number_of_agents > 2 ? number_of_agents : 2;
   REQUIRE(n <= CASIM_MAX_AGENTS && 2 * (n / 2) <= h->A, "scenario: more agents than slots per environment");
   CK(casim_launch_scenario(h, kind, number_of_agents, seeds, ego_policy, ego_dynamics, other_dynamics, init, types, n_agents,

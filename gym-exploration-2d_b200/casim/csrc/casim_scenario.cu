@@ -3,6 +3,7 @@
  * straight into the device buffers casim_reset reads (no host loop, no H2D of the initial conditions):
  *   gym_collision_avoidance/envs/test_cases.py:1192-1281  train_agents_swap_circle(seed=s)
  *   gym_collision_avoidance/envs/test_cases.py:1365-1463  train_agents_random_positions(seed=s)
+ *   gym_collision_avoidance/envs/test_cases.py:1283-1363  train_agents_pairwise_swap(seed=s)
  *   gym_collision_avoidance/envs/test_cases.py:129-133    is_pose_valid (rejection sampling on pairwise distance)
  * A seed gives the reference's own scenario: the generators draw from numpy's legacy global generator
  * (np.random.seed(s), np.random.uniform) and from CPython's `random` (random.seed(s), random.choice), both the
@@ -68,6 +69,13 @@ __device__ double mt_uniform(Mt& m, double low, double high) { /* legacy uniform
 __device__ int py_choice2(Mt& m) { /* random.choice of a 2-list: getrandbits(2) until < 2 */
   uint32_t r;
   do r = mt_next(m) >> 30; while (r >= 2u);
+  return (int)r;
+}
+
+__device__ int py_randbelow(Mt& m, int n) { /* Random._randbelow_with_getrandbits: getrandbits(n.bit_length()) until < n */
+  const int k = 32 - __clz(n);
+  uint32_t r;
+  do r = mt_next(m) >> (32 - k); while (r >= (uint32_t)n);
   return (int)r;
 }
 
@@ -138,6 +146,34 @@ __global__ void __launch_bounds__(64) k_scenario(const ScenarioArgs p) {
       else put_agent(p, e, 2 * ag, pos[2 * ag], pos[2 * ag + 1], pa, p.other_dyn, OAS | GRID, 0.5f);
       const int pb = mt_uniform(m, 0.0, 1.0) > 0.8 ? CASIM_POLICY_NONCOOPERATIVE : CASIM_POLICY_RVO;
       put_agent(p, e, 2 * ag + 1, pos[2 * ag + 1], pos[2 * ag], pb, p.other_dyn, OAS, 0.5f);
+    }
+  } else if (p.kind == CASIM_SCENARIO_PAIRWISE_SWAP) { /* test_cases.py:1283-1363 */
+    double ip[CASIM_MAX_AGENTS][2];
+    int pol[CASIM_MAX_AGENTS];
+    int k = 1;
+    ip[0][0] = mt_uniform(m, -7.5, 7.5);
+    ip[0][1] = mt_uniform(m, -7.5, 7.5);
+    for (int ag = 0; ag < n - 1; ag++) {
+      double x, y;
+      do {
+        x = mt_uniform(m, -7.5, 7.5);
+        y = mt_uniform(m, -7.5, 7.5);
+      } while (!pose_valid(x, y, ip, k, 2.0));
+      ip[k][0] = x; ip[k][1] = y; k++;
+    }
+    /* policy draws: numpy's stream; the shuffle (:1324): Python's.  Independent streams, so numpy's draws first. */
+    for (int q = 0; q < 2 * P; q++) pol[q] = mt_uniform(m, 0.0, 1.0) > 0.8 ? CASIM_POLICY_NONCOOPERATIVE : CASIM_POLICY_RVO;
+    mt_init_by_key(m, seed);
+    for (int i = n - 1; i >= 1; i--) { /* random.shuffle */
+      const int j = py_randbelow(m, i + 1);
+      const double tx = ip[i][0], ty = ip[i][1];
+      ip[i][0] = ip[j][0]; ip[i][1] = ip[j][1];
+      ip[j][0] = tx; ip[j][1] = ty;
+    }
+    for (int ag = 0; ag < P; ag++) {
+      if (ag == 0) put_agent(p, e, 0, ip[0], ip[1], p.ego_policy, p.ego_dyn, OAS, 1.0f);
+      else put_agent(p, e, 2 * ag, ip[2 * ag], ip[2 * ag + 1], pol[2 * ag], p.other_dyn, OAS, 0.5f);
+      put_agent(p, e, 2 * ag + 1, ip[2 * ag + 1], ip[2 * ag], pol[2 * ag + 1], p.other_dyn, OAS, 0.5f);
     }
   } else {
     double ip[CASIM_MAX_AGENTS][2], gp[CASIM_MAX_AGENTS][2];

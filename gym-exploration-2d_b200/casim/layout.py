@@ -43,4 +43,4 @@ OBS_KEYS = ("dist_to_goal", "rel_goal", "radius", "heading_ego_frame", "heading_
 OBS_KEY_ID = {k: i for i, k in enumerate(OBS_KEYS)}
 
 # enum casim_scenario (include/casim.h): envs/test_cases.py:1192-1281 / :1365-1463
-SCENARIO_SWAP_CIRCLE, SCENARIO_RANDOM_POSITIONS = 0, 1
+SCENARIO_SWAP_CIRCLE, SCENARIO_RANDOM_POSITIONS, SCENARIO_PAIRWISE_SWAP = 0, 1, 2

@@ -252,13 +252,13 @@ int casim_explore_step(casim_handle* h, const float* state, const float* other_a
 
 /* The reference's seeded training-scenario generators, one environment per seed, written into the device buffers
  * that casim_reset reads: envs/test_cases.py:1192-1281 train_agents_swap_circle(number_of_agents, seed=seeds[e]) and
- * :1365-1463 train_agents_random_positions(...).  A seed yields the reference's own scenario (numpy's and CPython's
+ * :1365-1463 train_agents_random_positions(...), :1283-1363 train_agents_pairwise_swap(...).  A seed yields the reference's own scenario (numpy's and CPython's
  * MT19937 streams are reproduced); seeds must be non-zero (`if seed:`, :1198).  2 * (max(number_of_agents, 2) / 2)
  * agents per environment (<= A); ego_policy / ego_dynamics describe agent 0 (a GA3C-CADRL ego gets
  * UnicycleDynamicsMaxAcc, :1254-1257), the other agents are RVO / NonCooperative with other_dynamics.
  * seeds [E] uint32, init [E,A,7] fp32, types [E,A] int32, n_agents [E] int32, coop [E,A] fp32 cooperation_coef
  * (optional): all device pointers. */
-enum casim_scenario { CASIM_SCENARIO_SWAP_CIRCLE = 0, CASIM_SCENARIO_RANDOM_POSITIONS = 1 };
+enum casim_scenario { CASIM_SCENARIO_SWAP_CIRCLE = 0, CASIM_SCENARIO_RANDOM_POSITIONS = 1, CASIM_SCENARIO_PAIRWISE_SWAP = 2 };
 int casim_generate_scenario(casim_handle* h, int kind, int number_of_agents, const uint32_t* seeds, int ego_policy,
                             int ego_dynamics, int other_dynamics, float* init, int32_t* types, int32_t* n_agents,
                             float* coop, void* stream);

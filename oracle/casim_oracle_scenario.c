@@ -2,6 +2,7 @@
  * TEST INFRASTRUCTURE -- CPU restatement of the reference's seeded training-scenario generators
  *   gym_collision_avoidance/envs/test_cases.py:1192-1281  train_agents_swap_circle(seed=s)
  *   gym_collision_avoidance/envs/test_cases.py:1365-1463  train_agents_random_positions(seed=s)
+ *   gym_collision_avoidance/envs/test_cases.py:1283-1363  train_agents_pairwise_swap(seed=s)
  *   gym_collision_avoidance/envs/test_cases.py:129-133    is_pose_valid
  * for a batch of environments, one seed per environment.  The reference draws from numpy's legacy global generator
  * (np.random.seed(s); np.random.uniform) and from Python's `random` (random.seed(s); random.choice): both are the
@@ -72,6 +73,15 @@ static int py_choice2(mt_t* m) {
   return (int)r;
 }
 
+/* CPython Random._randbelow_with_getrandbits(n): getrandbits(n.bit_length()) until < n */
+static int py_randbelow(mt_t* m, int n) {
+  int k = 0;
+  while ((n >> k) != 0) k++;
+  uint32_t r;
+  do r = mt_next(m) >> (32 - k); while (r >= (uint32_t)n);
+  return (int)r;
+}
+
 /* test_cases.py:129-133 */
 static int pose_valid(double x, double y, const double (*list)[2], int n, double distance) {
   for (int k = 0; k < n; k++) {
@@ -96,7 +106,7 @@ static void put_agent(double* init, int32_t* types, double* coop, int slot, cons
   if (coop) coop[slot] = c;
 }
 
-/* kind: CASIM_SCENARIO_SWAP_CIRCLE (0) or CASIM_SCENARIO_RANDOM_POSITIONS (1).  seeds [E] (non-zero: `if seed:`).
+/* kind: CASIM_SCENARIO_SWAP_CIRCLE (0), CASIM_SCENARIO_RANDOM_POSITIONS (1) or CASIM_SCENARIO_PAIRWISE_SWAP (2).  seeds [E] (non-zero: `if seed:`).
  * init [E][A][7] doubles, types [E][A], n_agents [E], coop [E][A] (optional; cooperation_coef, agent.py).  Slots past
  * the generated agents are zeroed.  Returns 0, or CASIM_EINVAL if 2 * (max(number_of_agents, 2) / 2) > A. */
 int casim_oracle_scenario(int kind, int E, int A, int number_of_agents, const uint32_t* seeds, int ego_policy,
@@ -104,7 +114,7 @@ int casim_oracle_scenario(int kind, int E, int A, int number_of_agents, const ui
                           double* coop) {
   const int n = number_of_agents > 2 ? number_of_agents : 2;
   const int P = n / 2;
-  if (2 * P > A || n > SC_MAX || (kind != 0 && kind != 1)) return CASIM_EINVAL;
+  if (2 * P > A || n > SC_MAX || (kind < 0 || kind > 2)) return CASIM_EINVAL;
   const int ga3c = ego_policy == CASIM_POLICY_GA3C_CADRL;
   const int ego_dyn = ga3c ? CASIM_DYN_UNICYCLE_MAX_ACC : ego_dynamics; /* :1254-1257, :1435-1438 */
   const int OAS = CASIM_SENSOR_OTHER_AGENTS, GRID = CASIM_SENSOR_OCCUPANCY_GRID;
@@ -141,6 +151,30 @@ int casim_oracle_scenario(int kind, int E, int A, int number_of_agents, const ui
         else put_agent(in, ty, co, 2 * ag, pos[2 * ag], pos[2 * ag + 1], pa, other_dynamics, OAS | GRID, 0.5);
         int pb = mt_uniform(&m, 0, 1) > 0.8 ? CASIM_POLICY_NONCOOPERATIVE : CASIM_POLICY_RVO;
         put_agent(in, ty, co, 2 * ag + 1, pos[2 * ag + 1], pos[2 * ag], pb, other_dynamics, OAS, 0.5);
+      }
+    } else if (kind == 2) { /* train_agents_pairwise_swap, test_cases.py:1283-1363 */
+      double ip[SC_MAX][2];
+      int pol[SC_MAX];
+      int k = 0;
+      ip[0][0] = mt_uniform(&m, -7.5, 7.5); ip[0][1] = mt_uniform(&m, -7.5, 7.5); k = 1;
+      for (int ag = 0; ag < n - 1; ag++) {
+        double x, y;
+        do { x = mt_uniform(&m, -7.5, 7.5); y = mt_uniform(&m, -7.5, 7.5); } while (!pose_valid(x, y, ip, k, 2.0));
+        ip[k][0] = x; ip[k][1] = y; k++;
+      }
+      /* the policy draws come from numpy's stream, the shuffle (:1324) from Python's: independent, so numpy first */
+      for (int q = 0; q < 2 * P; q++) pol[q] = mt_uniform(&m, 0, 1) > 0.8 ? CASIM_POLICY_NONCOOPERATIVE : CASIM_POLICY_RVO;
+      mt_init_by_array(&m, &seeds[e], 1);
+      for (int i = n - 1; i >= 1; i--) { /* random.shuffle */
+        int j = py_randbelow(&m, i + 1);
+        double tx = ip[i][0], ty = ip[i][1];
+        ip[i][0] = ip[j][0]; ip[i][1] = ip[j][1];
+        ip[j][0] = tx; ip[j][1] = ty;
+      }
+      for (int ag = 0; ag < P; ag++) {
+        if (ag == 0) put_agent(in, ty, co, 0, ip[0], ip[1], ego_policy, ego_dyn, OAS, 1.0);
+        else put_agent(in, ty, co, 2 * ag, ip[2 * ag], ip[2 * ag + 1], pol[2 * ag], other_dynamics, OAS, 0.5);
+        put_agent(in, ty, co, 2 * ag + 1, ip[2 * ag + 1], ip[2 * ag], pol[2 * ag + 1], other_dynamics, OAS, 0.5);
       }
     } else {
       double ip[SC_MAX][2], gp[SC_MAX][2];

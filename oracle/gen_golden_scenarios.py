@@ -1,5 +1,6 @@
 """TEST INFRASTRUCTURE -- generates tests/golden/scenarios.npz by running the UNMODIFIED reference generators
-train_agents_swap_circle / train_agents_random_positions (gym_collision_avoidance/envs/test_cases.py:1192-1463) with
+train_agents_swap_circle / train_agents_pairwise_swap / train_agents_random_positions
+(gym_collision_avoidance/envs/test_cases.py:1192-1463) with
 explicit seeds in the build container.  Run through ``python oracle/gen_golden.py scenarios``."""
 import os
 
@@ -17,7 +18,7 @@ def main(ns, A=12):
     from oracle import ref_harness
     with ref_harness.quiet():
         from gym_collision_avoidance.envs import test_cases as tc
-    funcs = [tc.train_agents_swap_circle, tc.train_agents_random_positions]
+    funcs = [tc.train_agents_swap_circle, tc.train_agents_random_positions, tc.train_agents_pairwise_swap]
     rec = {k: [] for k in ("kind", "seed", "number_of_agents", "init", "types", "n_agents", "coop")}
     for kind, f in enumerate(funcs):
         for n in (2, 4, 5, 6, 10, 12):
@@ -44,4 +45,4 @@ def main(ns, A=12):
     out["seed"] = out["seed"].astype(np.uint32)
     np.savez_compressed(os.path.join(GOLDEN, "scenarios.npz"), **out)
     nc = sum(int(((t & 0xff) == 1).sum()) for t in rec["types"])
-    print("wrote scenarios.npz: %d scenarios (2 generators x 6 sizes x 7 seeds), %d NonCooperative agents" % (len(rec["kind"]), nc))
+    print("wrote scenarios.npz: %d scenarios (3 generators x 6 sizes x 7 seeds), %d NonCooperative agents" % (len(rec["kind"]), nc))

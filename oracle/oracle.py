@@ -366,7 +366,7 @@ def packs_from_state(state):
 
 
 # scenario generators (casim_oracle_scenario.c)
-SCENARIO_SWAP_CIRCLE, SCENARIO_RANDOM_POSITIONS = 0, 1
+SCENARIO_SWAP_CIRCLE, SCENARIO_RANDOM_POSITIONS, SCENARIO_PAIRWISE_SWAP = 0, 1, 2
 
 
 def scenario(kind, E, A, number_of_agents, seeds, ego_policy, ego_dynamics, other_dynamics=0):

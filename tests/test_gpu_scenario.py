@@ -21,7 +21,7 @@ def test_scenarios_golden_vs_reference():
     import torch
     z = H.load("scenarios.npz")
     A = z["init"].shape[1]
-    for kind in (0, 1):
+    for kind in (0, 1, 2):
         for nn in sorted(set(z["number_of_agents"].tolist())):
             sel = np.nonzero((z["kind"] == kind) & (z["number_of_agents"] == nn))[0]
             sim = _sim(len(sel), A, sensors=())
@@ -46,7 +46,7 @@ def test_scenarios_full_size_vs_oracle_and_episode(oracle_lib):
     oracle = oracle_lib
     E, A = 4096, 10
     seeds = (np.arange(E, dtype=np.uint32) * 7919 + 11).astype(np.uint32)
-    for kind in (L.SCENARIO_SWAP_CIRCLE, L.SCENARIO_RANDOM_POSITIONS):
+    for kind in (L.SCENARIO_SWAP_CIRCLE, L.SCENARIO_RANDOM_POSITIONS, L.SCENARIO_PAIRWISE_SWAP):
         sim = _sim(E, A, sensors=("other_agents_states",))
         init, types, n, coop = sim.generate_scenario(kind, A, seeds, L.POLICY_NONCOOPERATIVE, L.DYN_UNICYCLE)
         torch.cuda.synchronize()
@@ -56,10 +56,10 @@ def test_scenarios_full_size_vs_oracle_and_episode(oracle_lib):
         H.assert_close(gi[..., :6], o["init"][..., :6], "kind %d init" % kind, rtol=1e-6, atol=1e-6)
         start = gi[..., 0:2].astype(np.float64)
         d = np.linalg.norm(start[:, :, None] - start[:, None, :], axis=-1) + 10 * np.eye(A)[None]
-        assert d.min() > 1.5 - 1e-5                       # is_pose_valid(distance=1.5) on every pair of start positions
+        assert d.min() > (2.0 if kind == 2 else 1.5) - 1e-5                       # is_pose_valid(distance=1.5) on every pair of start positions
         pol = o["types"] & 0xff
         frac_nc = (pol[:, 1:] == L.POLICY_NONCOOPERATIVE).mean()
-        assert (0.15 < frac_nc < 0.25) if kind == 0 else (0.45 < frac_nc < 0.55)       # P(u > 0.8) / random.choice of two
+        assert (0.45 < frac_nc < 0.55) if kind == 1 else (0.15 < frac_nc < 0.25)       # random.choice of two / P(u > 0.8)
         # RVO agents need the RVO step; run the episode with them as NonCooperative (same slots, same geometry)
         t2 = types.clone()
         t2 = (t2 & ~0xff) | L.POLICY_NONCOOPERATIVE

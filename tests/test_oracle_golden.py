@@ -245,7 +245,7 @@ def test_scenario_generators_vs_reference(oracle_lib):
     oracle = oracle_lib
     z = H.load("scenarios.npz")
     A = z["init"].shape[1]
-    assert len(z["kind"]) >= 80 and set(z["kind"].tolist()) == {0, 1}
+    assert len(z["kind"]) >= 120 and set(z["kind"].tolist()) == {0, 1, 2}
     for k in range(len(z["kind"])):
         o = oracle.scenario(int(z["kind"][k]), 1, A, int(z["number_of_agents"][k]), z["seed"][k:k + 1],
                             L.POLICY_LEARNING, L.DYN_FIRST_ORDER, L.DYN_UNICYCLE)
