@@ -81,6 +81,7 @@ class BatchedCollisionAvoidanceEnv:
         self.episode_number = 0
         self.episode_step_number = 0
         self._host_state = None
+        self._generator = None
 
     # ---- scenario injection (the reference's reset() ignores set_agents(): SURVEY.md 3.2) ----
     def set_agents(self, agents):
@@ -96,6 +97,18 @@ class BatchedCollisionAvoidanceEnv:
         self._tensors = (np.asarray(init, np.float32), np.asarray(types, np.int32),
                          None if n_agents is None else np.asarray(n_agents, np.int32))
         self.agents = None
+
+    def set_scenario_generator(self, kind, number_of_agents, ego_policy, ego_dynamics, other_dynamics=None, seed_base=0):
+        """Generate every episode's agents on the device, like _init_agents in evaluate mode does on the host
+        (collision_avoidance_env.py:403-415: ``tc.<scenario>(number_of_agents=..., seed=episode_number)``): kind =
+        layout.SCENARIO_*, ego_policy / dynamics = plugin classes or ids.  Environment e of episode k uses seed
+        ``seed_base + k * num_envs + e + 1`` (E == 1, seed_base == 0: the reference's seed = episode_number)."""
+        ident = lambda x, attr: x if isinstance(x, int) else getattr(x, attr)
+        od = L.DYN_UNICYCLE if other_dynamics is None else ident(other_dynamics, "dynamics_id")
+        self._generator = (int(kind), int(number_of_agents), ident(ego_policy, "policy_id"),
+                           ident(ego_dynamics, "dynamics_id"), od, int(seed_base))
+        self.agents = None
+        self._tensors = None
 
     def set_static_map(self, obstacles):
         """obstacles: the reference's format (list of 4-corner lists; corners 1 and 3 are read, Map.py:117-118), or
@@ -173,7 +186,17 @@ class BatchedCollisionAvoidanceEnv:
     # ---- gym API ----
     def reset(self):
         """collision_avoidance_env.py:234-266: (re)create the agents' state, build the static map, first _get_obs"""
-        init, types, n = self._scenario()
+        gen_coop = None
+        if self._generator is not None:
+            kind, n_ag, ego_pol, ego_dyn, other_dyn, base = self._generator
+            if self.sim is None:    # the generators' sensor lists are fixed (test_cases.py:1262, :1279, :1445)
+                bits = L.SENSOR_OTHER_AGENTS | (L.SENSOR_OCCUPANCY_GRID if kind == L.SCENARIO_SWAP_CIRCLE else 0)
+                self.sim = BatchedSim(self.E, self.A, cfg=self.cfg, device=self.device, sensors=(bits,))
+            seeds = (base + self.episode_number * self.E + np.arange(self.E) + 1).astype(np.uint32)
+            init, types_dev, n, gen_coop = self.sim.generate_scenario(kind, n_ag, seeds, ego_pol, ego_dyn, other_dyn)
+            types = types_dev.cpu().numpy()
+        else:
+            init, types, n = self._scenario()
         sensor_bits = int(np.bitwise_or.reduce((types >> 16).ravel() & 0xff)) if types.size else 0
         policies = set((types & 0xff).ravel().tolist())
         if L.POLICY_IG_GREEDY in policies or L.POLICY_GA3C_CADRL in policies:
@@ -200,7 +223,7 @@ class BatchedCollisionAvoidanceEnv:
                 for e, ags in enumerate(self.agents):
                     for i, a in enumerate(ags):
                         coop[e, i] = a.cooperation_coef
-            self._rvo_coop = torch.from_numpy(coop).to(sim.device)
+            self._rvo_coop = torch.from_numpy(coop).to(sim.device) if gen_coop is None else gen_coop
             self._rvo_params = _lib.rvo_default_params()
             self._rvo_params.neighbor_dist = float(self.config.SENSING_HORIZON)
             self._rvo_params.time_horizon = float(getattr(self.config, "RVO_TIME_HORIZON", 5.0))

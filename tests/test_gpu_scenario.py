@@ -73,3 +73,47 @@ def test_scenarios_full_size_vs_oracle_and_episode(oracle_lib):
         # (agents that collide early stop moving: the floor is one step, the typical agent travels 20 steps x 0.1 s x 1 m/s)
         assert float(moved.min()) > 0.05 and float(moved.median()) > 1.9 and bool(torch.isfinite(sim.state).all())
         sim.close()
+
+
+def test_env_generates_episodes_like_init_agents():
+    """BatchedCollisionAvoidanceEnv.set_scenario_generator: reset() builds the episode on the device with
+    seed = episode_number, as _init_agents does in evaluate mode (collision_avoidance_env.py:403-415); at E = 1 the
+    episodes are the reference's (scenarios.npz seeds 1, 2, 3), and the RVO / NonCooperative mix steps."""
+    import torch
+    from casim import plugins as P
+    from casim.env import BatchedCollisionAvoidanceEnv
+    from casim.config import Config
+
+    class Cfg(Config):
+        TRAIN_SINGLE_AGENT = False
+
+    z = H.load("scenarios.npz")
+    for kind in (L.SCENARIO_SWAP_CIRCLE, L.SCENARIO_PAIRWISE_SWAP):
+        env = BatchedCollisionAvoidanceEnv(num_envs=1, max_agents=z["init"].shape[1], config=Cfg)
+        env.set_scenario_generator(kind, 6, P.LearningPolicy, P.FirstOrderDynamics, P.UnicycleDynamics)
+        for episode in (1, 2, 3):
+            env.reset()
+            g = int(np.nonzero((z["kind"] == kind) & (z["number_of_agents"] == 6) & (z["seed"] == episode))[0][0])
+            n = int(z["n_agents"][g])
+            assert int(env.sim._keep["n_agents"][0]) == n
+            assert np.array_equal(env.sim._keep["types"].cpu().numpy()[0], z["types"][g])
+            H.assert_close(env.sim._keep["init"].cpu().numpy()[0, :n, :6], z["init"][g, :n, :6], "episode %d" % episode,
+                           rtol=1e-6, atol=1e-6)
+            for _ in range(5):
+                obs, rewards, game_over, info = env.step(np.full((1, z["init"].shape[1], 2), 0.5, np.float32))
+            torch.cuda.synchronize()
+            st = env.sim.state_numpy()[0]
+            moved = np.linalg.norm(st[:n, [L.PX, L.PY]] - z["init"][g, :n, 0:2], axis=1)
+            assert np.isfinite(st).all() and moved[1:].sum() > 0.5                # (RVO agents may yield: slow, even still)
+        env.close()
+    E = 256
+    env = BatchedCollisionAvoidanceEnv(num_envs=E, max_agents=8, config=Cfg)
+    env.set_scenario_generator(L.SCENARIO_RANDOM_POSITIONS, 8, P.NonCooperativePolicy, P.UnicycleDynamics, seed_base=1000)
+    env.reset()
+    first = env.sim._keep["init"].clone()
+    for _ in range(10):
+        obs, rewards, game_over, info = env.step()
+    env.reset()
+    assert not torch.equal(first, env.sim._keep["init"])          # a new episode is a new scenario
+    assert rewards.shape == (E, 8) and bool(torch.isfinite(env.sim.state).all())
+    env.close()
