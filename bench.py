@@ -291,7 +291,28 @@ def run_reference(args, rank, world):
                                    % (steps, Es, A, threads)},
         "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def guard_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to fd 1 when the box
+    sets NCCL_DEBUG=VERSION), so fd 1 is pointed at stderr for the whole run and the line goes to the saved descriptor."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
@@ -309,6 +330,7 @@ def main():
     ap.add_argument("--no-stats", action="store_true", help="diagnostics: do not compute the per-step episode statistics")
     ap.add_argument("--ring", type=int, default=None, help="override the number of env batches in the ring (diagnostics)")
     args = ap.parse_args()
+    guard_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -592,7 +614,7 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "agent-steps/s", "cores": threads, "kind": "port",
                                     "sample": "%d steps of %d envs x %d agents, oracle/casim_oracle.c with %d POSIX threads"
                                               % (n_steps, Es, A, threads)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     for s in sims:
         s.close()
     if world > 1:
