@@ -239,7 +239,15 @@ __global__ void __launch_bounds__(256) k_grid_generic(const GridArgs p) {
  *   phase 2  the queued words only: exact per-cell lookup in the footprint plane chosen by (fx > 0, fy > 0);
  *   phase 3  the 3600-byte grid leaves shared memory as 16-byte coalesced stores.
  * Maps are unions of rectangles (Map.get_occupancy_grid), so most words are uniform.                 */
+#ifndef GRID_WARPS
 #define GRID_WARPS 4
+#endif
+#ifndef GRID_MINB
+#define GRID_MINB 8 /* resident CTAs per SM asked of the compiler: 8-10 measured 108 us at C-full, 12 (40-register cap) 115 us, 16 121 us */
+#endif
+#ifndef GRID_U
+#define GRID_U 5
+#endif
 #define GRID_MAXW 16  /* words per row (submap side <= 64) */
 #define GRID_MAXWORDS 1024 /* words per grid: the fast path takes grids of up to 4096 cells */
 
@@ -251,7 +259,7 @@ __device__ __forceinline__ uint32_t grid_cell_exact(const uint32_t* __restrict__
   return (w >> (xi & 31)) & 1u;
 }
 
-__global__ void __launch_bounds__(32 * GRID_WARPS, 12) k_grid(const GridArgs p) {
+__global__ void __launch_bounds__(32 * GRID_WARPS, GRID_MINB) k_grid(const GridArgs p) {
   casim_pdl_enter();
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -357,7 +365,7 @@ __global__ void __launch_bounds__(32 * GRID_WARPS, 12) k_grid(const GridArgs p) 
     const bool act = lr < rpi;
     /* min over the word's end cells of (row term + column term) = row term + min of the two column terms */
     const int cmx = min(s_cx[wid][4 * wx], s_cx[wid][4 * wx + 3]), cmy = min(s_cy[wid][4 * wx], s_cy[wid][4 * wx + 3]);
-    constexpr int U = 5; /* rows in flight per lane: the classification loads of a batch are independent */
+    constexpr int U = GRID_U; /* rows in flight per lane: the classification loads of a batch are independent */
     for (int oy0 = 0; oy0 < W; oy0 += rpi * U) {
       uint32_t cw[U];
       int sh[U];

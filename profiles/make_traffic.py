@@ -15,7 +15,8 @@ SHORT = ("k_core", "k_laser", "k_grid", "k_explore", "k_ga3c_tc", "k_ga3c_state"
 
 
 def main(tag):
-    out = {}
+    dst = os.path.join(ROOT, "profiles", "traffic.json")
+    out = json.load(open(dst)) if os.path.exists(dst) else {}  # a partial pass refreshes only the workloads it captured
     for wl in ("c2", "c3", "full", "c4", "c5", "rvo"):
         path = os.path.join(ROOT, "gpurun_out", "%s_full_%s.ncu-rep" % (tag, wl))
         if not os.path.exists(path):
@@ -35,7 +36,7 @@ def main(tag):
                 tot += float(r[col[m]].replace(",", "")) * UNIT[units[col[m]]]
             per.setdefault(short, []).append(tot)
         out[wl] = {k: statistics.median(v) for k, v in per.items()}
-    json.dump(out, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1, sort_keys=True)
+    json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
     print(json.dumps(out, indent=1))
 
 
