@@ -31,7 +31,10 @@
 namespace {
 
 #define XQ_CAP 4096        /* queue entries: >= ig_dim^2 (ig_dim <= 64), so one pose always fits */
-#define X_THREADS 256
+#ifndef X_THREADS
+#define X_THREADS 192 /* C4 sweep (profiles/r1k_sweep_explore.txt): 64: 170 us, 128: 118, 192: 115, 256: 120, 512: 309; the maximum
+                        * shared-memory carve-out costs 3 us (the EDF samples live in L1) */
+#endif
 #define X_NPOSE 10
 #define X_MI_SCALE 17592186044416.0 /* 2^44 */
 
