@@ -39,6 +39,7 @@ struct DevCfg {
   double laser_max_range, laser_norm;
   double laser_cos[CASIM_MAX_BEAMS], laser_sin[CASIM_MAX_BEAMS], laser_ang[CASIM_MAX_BEAMS];
   double laser_r[CASIM_MAX_RANGES];
+  float laser_out[CASIM_MAX_RANGES + 1]; /* value reported for "range = sample k" (k == nr slot kept at index CASIM_MAX_RANGES: no hit) */
   /* exploration */
   double ig_fov_half, ig_detect_fov_half, ig_range, ig_cell, ig_rocc, ig_remp, ig_tol, ig_pfn, ig_pfp, ig_dt;
   double ig_det_thresh; /* sqrt(0.5)*cell + tolerance */

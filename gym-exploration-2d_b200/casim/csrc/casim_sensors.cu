@@ -29,10 +29,13 @@ struct LaserArgs {
   int lg2P; /* lanes per beam = 1 << lg2P = 32 / next_pow2(num_beams), computed by the launcher */
 };
 
-__global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
+#ifndef LASER_WPC
+#define LASER_WPC 8 /* warps (= agents) per CTA; needs 32 * LASER_WPC >= CASIM_MAX_BEAMS + CASIM_MAX_RANGES + 1 threads for the table fill */
+#endif
+__global__ void __launch_bounds__(32 * LASER_WPC) k_laser(const LaserArgs p) {
   /* Per-beam / per-sample tables: indexed by lane-dependent b and k, so they live in shared memory (a divergent
    * index into the kernel-parameter constant bank is serialised, one address per issue).  s_out[k] is the value
-   * reported for "range = sample k" (k == nr: no hit, max range): the fp64 division happens once per CTA. */
+   * reported for "range = sample k" (k == nr: no hit, max range), divided once on the host (DevCfg.laser_out). */
   __shared__ double s_cos[CASIM_MAX_BEAMS], s_sin[CASIM_MAX_BEAMS], s_r[CASIM_MAX_RANGES];
   __shared__ float s_out[CASIM_MAX_RANGES + 1];
   const DevCfg& c = p.c;
@@ -43,9 +46,9 @@ __global__ void __launch_bounds__(256) k_laser(const LaserArgs p) {
   } else if (threadIdx.x < CASIM_MAX_BEAMS + CASIM_MAX_RANGES) {
     const int k = threadIdx.x - CASIM_MAX_BEAMS;
     s_r[k] = c.laser_r[k];
-    s_out[k] = (float)(1.0 - c.laser_r[k] / c.laser_norm);
+    s_out[k] = c.laser_out[k];
   } else if (threadIdx.x == CASIM_MAX_BEAMS + CASIM_MAX_RANGES) {
-    s_out[CASIM_MAX_RANGES] = (float)(1.0 - c.laser_max_range / c.laser_norm);
+    s_out[CASIM_MAX_RANGES] = c.laser_out[CASIM_MAX_RANGES];
   }
   casim_pdl_enter();
   __syncthreads();
@@ -442,7 +445,7 @@ cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laser
   while (nbp < h->dc.nb) nbp <<= 1;
   for (int t = nbp; t > 1; t >>= 1) lg--;
   a.lg2P = lg;
-  int wpc = 8;
+  int wpc = LASER_WPC;
   dim3 grid((unsigned)((N + wpc - 1) / wpc)), block(32 * wpc);
   h->launches++;
   return casim_launch_pdl<LaserArgs>(k_laser, grid, block, 0, s, a);
