@@ -104,7 +104,9 @@ __device__ __forceinline__ long long py_round2_hundredths(double x) {
  * (integer compares, fp64 only on key ties), then the 76-float rows are assembled in shared memory and leave the
  * CTA as contiguous stores (x, nn_input) and 16-byte bf16 chunks (xb). */
 #define GS_AG 32
+#ifndef GS_THREADS
 #define GS_THREADS 128
+#endif
 __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
   __shared__ double s_fr[GS_AG][6];                 /* px, py, prx, pry, rh, - */
   __shared__ double s_po[GS_AG][CASIM_MAX_AGENTS];

@@ -350,7 +350,9 @@ __device__ int obstacle_lines(const RvoObst& O, const int* no, int nn, float2 po
   return nl;
 }
 
+#ifndef RVO_THREADS
 #define RVO_THREADS 128
+#endif
 
 template <bool OBST>
 __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
