@@ -105,7 +105,7 @@ __device__ __forceinline__ long long py_round2_hundredths(double x) {
  * CTA as contiguous stores (x, nn_input) and 16-byte bf16 chunks (xb). */
 #define GS_AG 32
 #ifndef GS_THREADS
-#define GS_THREADS 128
+#define GS_THREADS 256 /* C5 sweep: 64: 108.6 us per step, 128: 98.5, 192: 97.7, 256: 96.8 (profiles/r1k_sweep_gs.txt) */
 #endif
 __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
   __shared__ double s_fr[GS_AG][6];                 /* px, py, prx, pry, rh, - */
