@@ -1,4 +1,13 @@
 /*
+ * ATTRIBUTION.  The ORCA-line construction and linearProgram1/2/3 below restate, operation for operation, the RVO2
+ * Library (Python-RVO2/src/Agent.cpp, vendored by the reference):
+ *   Copyright 2008 University of North Carolina at Chapel Hill -- Jur van den Berg, Stephen J. Guy, Jamie Snape,
+ *   Ming C. Lin, Dinesh Manocha -- Licensed under the Apache License, Version 2.0
+ *   (http://www.apache.org/licenses/LICENSE-2.0), <http://gamma.cs.unc.edu/RVO2/>.  See NOTICE at the repository root.
+ * Bit-identical new velocities require the library's binary32 operation order, so that arithmetic is the library's
+ * by necessity; the GPU mapping around it is this repository's.
+ */
+/*
  * casim_rvo.cu -- the RVO policy (ORCA) for every agent whose policy id is CASIM_POLICY_RVO, one thread per agent.
  *
  * Replaces (gym_collision_avoidance/envs/policies/ of mlodel/gym-exploration-2d):
@@ -22,7 +31,7 @@
  *
  * Mapping note (measured on B200, C2-shaped all-RVO batch of 40 960 agents): one thread per agent takes 22.8 us;
  * a sub-warp cooperative variant (16 lanes per agent, one ORCA line per lane, ballot / shuffle linear programs --
- * kept for reference in scratch/casim_rvo_subwarp.cu.txt, parity-green) took 30.8 us: it issues 2.3x more warp
+ * kept for reference in profiles/parked/casim_rvo_subwarp16.cu.txt, parity-green) took 30.8 us: it issues 2.3x more warp
  * instructions (23 M vs ~10 M) and the kernel is issue-bound once enough warps are resident.
  *
  * Bound: latency / fp32 issue (a few hundred dependent flops per neighbour, data-dependent linear programs); the

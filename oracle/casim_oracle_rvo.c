@@ -1,4 +1,13 @@
 /*
+ * ATTRIBUTION.  The ORCA-line construction and linearProgram1/2/3 below restate, operation for operation, the RVO2
+ * Library (Python-RVO2/src/Agent.cpp, vendored by the reference):
+ *   Copyright 2008 University of North Carolina at Chapel Hill -- Jur van den Berg, Stephen J. Guy, Jamie Snape,
+ *   Ming C. Lin, Dinesh Manocha -- Licensed under the Apache License, Version 2.0
+ *   (http://www.apache.org/licenses/LICENSE-2.0), <http://gamma.cs.unc.edu/RVO2/>.  See NOTICE at the repository root.
+ * Bit-identical new velocities require the library's binary32 operation order, so that arithmetic is the library's
+ * by necessity; the GPU mapping around it is this repository's.
+ */
+/*
  * casim_oracle_rvo.c -- TEST INFRASTRUCTURE, NOT PRODUCT CODE (see casim_oracle.c).
  *
  * Plain-C restatement of the RVO policy of mlodel/gym-exploration-2d (paths relative to
