@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz by executing the UNMODIFIED reference
 (/root/reference, behind oracle/ref_harness.py) in the build container.
 
-    python oracle/gen_golden.py [core|sensors|c1|reset|maps|explore|rollouts|mcts|mcts_env|team|scenarios|ga3c|all]
+    python oracle/gen_golden.py [core|sensors|learning|c1|reset|maps|explore|rollouts|mcts|mcts_env|team|scenarios|ga3c|all]
 
 The fixtures are committed; this script is the provenance.  Inputs are float32-representable
 doubles (the GPU state is fp32) and headings / dt are passed as np.float64 so that numpy 2
@@ -54,12 +54,22 @@ def policy_classes(ns):
             return np.asarray(a)
 
     from gym_collision_avoidance.envs.policies.PedestrianDatasetPolicy import PedestrianDatasetPolicy
+    from gym_collision_avoidance.envs.policies.LearningPolicy import LearningPolicy
+
+    class CallSiteLearningPolicy(LearningPolicy):
+        """The fork's call site passes (agent_index, agents, actions) (collision_avoidance_env.py:304) while the
+        class it ships still takes (agent, network_output) (LearningPolicy.py:11): the plain class raises TypeError
+        inside env.step.  This adapter only re-routes the arguments; the arithmetic is the reference's own method."""
+
+        def network_output_to_action(self, agent_index, agents, actions):
+            return LearningPolicy.network_output_to_action(self, agents[agent_index], actions[agent_index])
+
     from gym_collision_avoidance.envs.dynamics.UnicycleDynamicsMaxTurnRate import UnicycleDynamicsMaxTurnRate
     from gym_collision_avoidance.envs.dynamics.UnicycleDynamicsMaxAcc import UnicycleDynamicsMaxAcc
     from gym_collision_avoidance.envs.dynamics.UnicycleSecondOrderEulerDynamics import UnicycleSecondOrderEulerDynamics
     pol = {L.POLICY_STATIC: ns.StaticPolicy, L.POLICY_NONCOOPERATIVE: ns.NonCooperativePolicy,
            L.POLICY_EXTERNAL: PassThroughExternalPolicy, L.POLICY_CARRL: ns.CARRLPolicy,
-           L.POLICY_PEDESTRIAN: PedestrianDatasetPolicy}
+           L.POLICY_PEDESTRIAN: PedestrianDatasetPolicy, L.POLICY_LEARNING: CallSiteLearningPolicy}
     dyn = {L.DYN_UNICYCLE: ns.UnicycleDynamics, L.DYN_FIRST_ORDER: ns.FirstOrderDynamics,
            L.DYN_EXTERNAL: ns.ExternalDynamics, L.DYN_UNICYCLE_MAX_TURN_RATE: UnicycleDynamicsMaxTurnRate,
            L.DYN_UNICYCLE_MAX_ACC: UnicycleDynamicsMaxAcc, L.DYN_UNICYCLE_SECOND_ORDER_EULER: UnicycleSecondOrderEulerDynamics}
@@ -87,6 +97,7 @@ def build_agents(ns, init, types, traj=None):
             ag = ns.Agent(float(init[i, 0]), float(init[i, 1]), float(init[i, 2]), float(init[i, 3]),
                           float(init[i, 4]), float(init[i, 5]), None if np.isnan(h) else np.float64(h),
                           pol[p], dyn[d], sensor_list(ns, m), i)
+        ag.max_heading_change = 4          # collision_avoidance_env.py:97,467 (set by _init_agents, which the harness bypasses)
         if d == L.DYN_EXTERNAL and traj is not None:
             tr = traj[i]
             ag.policy.trajectory = _Traj(np.stack([tr[:, 0], tr[:, 1], np.zeros(len(tr))], 1),
@@ -225,7 +236,7 @@ class Recorder:
             self.state_out[k, i] = extract_state(ag, types[i])
             self.obs_misc[k, i, 0:2] = o['rel_goal']
             self.obs_misc[k, i, 2] = getattr(ag, 'num_other_agents_observed', 0) if m & L.SENSOR_OTHER_AGENTS else 0
-            self.obs_misc[k, i, 3] = 0.0
+            self.obs_misc[k, i, 3] = float(ag.get_agent_data_equiv("policy.str", "learning"))   # config.py:209-214 use_ppo
             self.obs_dist_to_goal[k, i] = o['dist_to_goal']
             self.obs_heading_ego[k, i] = o['heading_ego_frame']
             if m & L.SENSOR_OTHER_AGENTS:
@@ -240,6 +251,8 @@ class Recorder:
 
 
 DYN_CHOICES = [L.DYN_UNICYCLE, L.DYN_UNICYCLE, L.DYN_FIRST_ORDER, L.DYN_UNICYCLE_MAX_TURN_RATE]
+POLICY_CHOICES = [L.POLICY_STATIC, L.POLICY_NONCOOPERATIVE, L.POLICY_NONCOOPERATIVE, L.POLICY_NONCOOPERATIVE,
+                  L.POLICY_EXTERNAL, L.POLICY_CARRL, L.POLICY_PEDESTRIAN]
 
 
 def random_case(rng, sensors_mode):
@@ -254,8 +267,7 @@ def random_case(rng, sensors_mode):
     traj = np.zeros((A_MAX, T, 4))
     spread = float(rng.choice([2.0, 4.0, 8.0, 14.0]))
     for i in range(n):
-        pol = int(rng.choice([L.POLICY_STATIC, L.POLICY_NONCOOPERATIVE, L.POLICY_NONCOOPERATIVE,
-                              L.POLICY_NONCOOPERATIVE, L.POLICY_EXTERNAL, L.POLICY_CARRL, L.POLICY_PEDESTRIAN]))
+        pol = int(rng.choice(POLICY_CHOICES))
         if pol == L.POLICY_PEDESTRIAN:
             dyn = L.DYN_EXTERNAL
         else:
@@ -322,6 +334,8 @@ def random_case(rng, sensors_mode):
         s[L.TYPE] = types[i]
         if pol == L.POLICY_CARRL:
             ext[i] = [int(rng.integers(0, 11)), 0]
+        elif pol == L.POLICY_LEARNING:
+            ext[i] = [float(f32(rng.uniform(0, 1))), float(f32(rng.uniform(0, 1)))]
         else:
             ext[i] = [float(f32(rng.uniform(0, 1.5))), float(f32(rng.uniform(-1.2, 1.2)))]
         p0 = pos + rng.normal(0, 0.2, 2)
@@ -368,7 +382,7 @@ def gen_single_step(ns, name, ncases, seed, sensors_mode):
             p = L.decode_type(types[i])[0]
             if p == L.POLICY_CARRL:
                 actions[i] = int(ext[i, 0])
-            elif p == L.POLICY_EXTERNAL:
+            elif p in (L.POLICY_EXTERNAL, L.POLICY_LEARNING):
                 actions[i] = np.array(ext[i])
         with rh.quiet():
             obs, rew, go, info = env.step(actions, dt=np.float64(0.1))
@@ -547,6 +561,15 @@ def main():
         DYN_CHOICES = [L.DYN_UNICYCLE_MAX_ACC, L.DYN_UNICYCLE_SECOND_ORDER_EULER, L.DYN_UNICYCLE]
         gen_single_step(ns, "dynamics_extra_single_step.npz", 160, 13, sensors_mode=False)
         DYN_CHOICES = keep
+    if what in ("learning", "all"):
+        # LearningPolicy (id 3) + game_over mode "all learning agents done" (collision_avoidance_env.py:303-304,722-736),
+        # again in a fixture of its own so that core_single_step.npz keeps its random stream
+        global POLICY_CHOICES
+        keepp = POLICY_CHOICES
+        POLICY_CHOICES = [L.POLICY_LEARNING, L.POLICY_LEARNING, L.POLICY_LEARNING, L.POLICY_NONCOOPERATIVE, L.POLICY_STATIC,
+                          L.POLICY_EXTERNAL, L.POLICY_CARRL]
+        gen_single_step(ns, "learning_single_step.npz", 200, 14, sensors_mode=False)
+        POLICY_CHOICES = keepp
     if what in ("reset", "all"):
         gen_reset(ns)
     if what in ("maps", "all"):

@@ -41,7 +41,8 @@ def test_library_loaded_and_default_config_matches_oracle(oracle_lib, torch_mod)
     assert bytes(a) == bytes(b)
 
 
-@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz", "dynamics_extra_single_step.npz"])
+@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz", "dynamics_extra_single_step.npz",
+                                  "learning_single_step.npz"])
 def test_golden_single_step(oracle_lib, torch_mod, name):
     """Every golden case (reference outputs) through casim_step, grouped by (game-over mode, map)."""
     torch = torch_mod
@@ -75,7 +76,8 @@ def test_golden_single_step(oracle_lib, torch_mod, name):
                       "other_agents_states", "laserscan", "local_grid"):
                 setattr(ref, k, z[k][sel])
             ref.obs_misc = ref.obs_misc.copy()
-            ref.obs_misc[..., 3] = g["obs_misc"][..., 3]      # use_ppo is not recorded by the generator
+            if not name.startswith("learning"):               # older fixtures: use_ppo was not recorded by the generator
+                ref.obs_misc[..., 3] = g["obs_misc"][..., 3]
             H.compare_step(what, n, gs, g, z["state_out"][sel], ref)
             sim.close()
 

@@ -25,7 +25,8 @@ def run_single_step(oracle, z, k, maps):
     return n, state, obs
 
 
-@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz", "dynamics_extra_single_step.npz"])
+@pytest.mark.parametrize("name", ["core_single_step.npz", "sensors_single_step.npz", "dynamics_extra_single_step.npz",
+                                  "learning_single_step.npz"])
 def test_single_step_vs_reference(oracle_lib, name):
     oracle = oracle_lib
     z = H.load(name)
@@ -41,6 +42,8 @@ def test_single_step_vs_reference(oracle_lib, name):
         H.assert_close(obs.rewards[0, :n], z["rewards"][k, :n], what + " rewards")
         H.assert_close(obs.nearest_dist[0, :n], z["nearest_dist"][k, :n], what + " nearest")
         H.assert_close(obs.obs_misc[0, :n, :3], z["obs_misc"][k, :n, :3], what + " obs_misc")
+        if name.startswith("learning"):      # use_ppo recorded from the reference's attr expression (config.py:209-214)
+            assert np.array_equal(obs.obs_misc[0, :n, 3], z["obs_misc"][k, :n, 3]), what + " use_ppo"
         H.assert_close(obs.other_agents_states[0, :n], z["other_agents_states"][k, :n], what + " other_agents")
         # closest-N ordering: the type / radius columns pin the row order exactly
         assert np.array_equal(obs.other_agents_states[0, :n, :, 9], z["other_agents_states"][k, :n, :, 9]), what
