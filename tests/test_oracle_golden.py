@@ -339,6 +339,22 @@ def test_ga3c_network_vs_torch(oracle_lib):
                                [[1.0, -np.pi / 6], [1.0, np.pi / 6], [0.5, 0.0], [0.0, np.pi / 6]], atol=1e-15)
 
 
+def test_ga3c_network_vs_tf_graph_golden(oracle_lib):
+    """a24 pin: the C restatement against tests/golden/ga3c_probs.npz -- the TF graph of GA3C_CADRL/network.py:45-98
+    evaluated in numpy float64 (oracle/gen_golden_ga3c_probs.py, written independently of the C oracle) on the
+    reference's shipped IROS18 weights and 1574 state vectors produced by the reference's own
+    agents_to_ga3c_cadrl_state.  The C oracle computes in float32 like TF: 5e-6 absolute on probabilities (the float32
+    evaluation of the same graph differs from float64 by 3e-6), argmax identical on every vector."""
+    oracle = oracle_lib
+    z = H.load("ga3c_probs.npz")
+    w = H.load("ga3c_iros18.npz")["weights"]
+    assert len(z["x"]) >= 200
+    p = oracle.ga3c_network(w, z["x"])
+    assert np.abs(p - z["probs64"]).max() < 5e-6
+    assert np.array_equal(p.argmax(1), z["action"])
+    assert np.abs(z["probs32"] - z["probs64"]).max() < 5e-6
+
+
 # ---------------------------------------------------------------------------------------------
 # RVO policy (SURVEY.md 8(f) rank 1)
 def _rvo_sim_call(fn, g, i):
