@@ -70,6 +70,28 @@ class Config:
     IG_PRIOR = 1.0
     IG_P_FALSE_NEG = 0.1
     IG_P_FALSE_POS = 0.05
+    # envs/config.py:7-8
+    continuous, discrete = range(2)
+    ACTION_SPACE_TYPE = continuous
+    # envs/config.py:104-215: size / bounds / dtype of every observation entry (the 'attr' strings are replaced by the
+    # SoA tensors of casim.env._obs_tensor); note other_agent_states is declared with size 9 but carries a 10-value row
+    STATE_INFO_DICT = {
+        'dist_to_goal': {'dtype': np.float32, 'size': 1, 'bounds': [-np.inf, np.inf]},
+        'radius': {'dtype': np.float32, 'size': 1, 'bounds': [0, np.inf]},
+        'rel_goal': {'dtype': np.float32, 'size': 2, 'bounds': [-np.inf, np.inf]},
+        'heading_ego_frame': {'dtype': np.float32, 'size': 1, 'bounds': [-np.pi, np.pi]},
+        'heading_global_frame': {'dtype': np.float32, 'size': 1, 'bounds': [-np.pi, np.pi]},
+        'pos_global_frame': {'dtype': np.float32, 'size': 2, 'bounds': [-np.inf, np.inf]},
+        'pref_speed': {'dtype': np.float32, 'size': 1, 'bounds': [0, np.inf]},
+        'num_other_agents': {'dtype': np.float32, 'size': 1, 'bounds': [0, np.inf]},
+        'other_agent_states': {'dtype': np.float32, 'size': 9, 'bounds': [-np.inf, np.inf]},
+        'other_agents_states': {'dtype': np.float32, 'size': (MAX_NUM_OTHER_AGENTS_IN_ENVIRONMENT, 10),
+                                'bounds': [-np.inf, np.inf]},
+        'local_grid': {'dtype': np.float32, 'size': (SUBMAP_WIDTH, SUBMAP_HEIGHT), 'bounds': [-np.inf, np.inf]},
+        'angular_map': {'dtype': np.float32, 'size': NUM_OF_SLICES, 'bounds': [0., 6.]},
+        'laserscan': {'dtype': np.float32, 'size': LASERSCAN_LENGTH, 'bounds': [0., 6.]},
+        'use_ppo': {'dtype': np.float32, 'size': 1, 'bounds': [0., 1.]},
+    }
     # batched-env extension
     AUTO_RESET = False
 

@@ -334,6 +334,17 @@ int casim_reset(casim_handle* h, float* state, const float* init, const int32_t*
   return run_sensors(h, state, obs, s);
 }
 
+int casim_reset_envs(casim_handle* h, float* state, const uint8_t* mask, const casim_obs* obs, void* stream) {
+  REQUIRE(h && state && mask, "null argument");
+  REQUIRE(h->init && h->type0, "casim_reset_envs needs a previous casim_reset (it re-reads its init / type / n_agents buffers)");
+  int rc = check_obs(h, obs);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(casim_launch_core(h, CASIM_MODE_RESET, state, nullptr, nullptr, h->cfg.dt, obs, s, mask));
+  /* the sensor kernels recompute every agent from the fp64 pose scratch; untouched environments get identical bytes */
+  return run_sensors(h, state, obs, s);
+}
+
 int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, void* stream) {
   REQUIRE(h && state, "null argument");
   int rc = check_obs(h, obs);
@@ -386,11 +397,7 @@ int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host
   REQUIRE(h && state && dev && host, "null argument");
   cudaStream_t s = (cudaStream_t)stream;
   size_t N = (size_t)h->E * h->A;
-  static int zc_on = -1;
-  if (zc_on < 0) {
-    const char* ev = getenv("CASIM_ZEROCOPY");
-    zc_on = ev ? atoi(ev) : 1;
-  }
+  static const int zc_on = casim_tuning_int("CASIM_ZEROCOPY", 1);
   /* Actions.  Pinned + mapped and small: the step kernel reads them from host memory itself (every lane, one
    * coalesced 8-byte read) and refreshes ext_actions_dev on the way -- the copy-engine hop in front of a ~10 us
    * kernel costs more than the kernel.  Otherwise: cudaMemcpyAsync H2D. */
@@ -570,11 +577,7 @@ int casim_rvo_step(casim_handle* h, const float* state, const float* coop, const
 }  /* extern "C" */
 
 int casim_pdl_enabled(void) {
-  static int on = -1;
-  if (on < 0) {
-    const char* ev = getenv("CASIM_PDL");
-    on = ev ? (atoi(ev) != 0) : 1;
-  }
+  static const int on = casim_tuning_int("CASIM_PDL", 1) != 0;
   return on;
 }
 

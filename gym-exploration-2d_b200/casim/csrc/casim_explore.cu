@@ -829,8 +829,8 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   a.xdt = xdt;
   a.exclude_per_rollout = exclude_per_rollout;
   h->launches++;
-  static const int threads = [] { const char* v = getenv("CASIM_XR_THREADS"); return v ? atoi(v) : 64; }();
-  static const int qcap = [] { const char* v = getenv("CASIM_XR_QCAP"); int q = v ? atoi(v) : 1024; return q < 1 ? 1 : (q > XR_QCAP ? XR_QCAP : q); }();
+  static const int threads = casim_tuning_int("CASIM_XR_THREADS", 64);
+  static const int qcap = [] { int q = casim_tuning_int("CASIM_XR_QCAP", 1024); return q < 1 ? 1 : (q > XR_QCAP ? XR_QCAP : q); }();
   a.qcap = qcap;
   const unsigned grid = (unsigned)((size_t)h->E * h->A * K);
   if (threads == 32) k_rollouts<32><<<grid, 32, 0, s>>>(a);

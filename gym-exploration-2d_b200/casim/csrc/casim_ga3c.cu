@@ -53,6 +53,8 @@ namespace {
 struct Ga3cArgs {
   DevCfg c;
   const float4* state;
+  const float4* state0;          /* episode-start state kept by casim_reset, or NULL */
+  const uint8_t* prev_game_over; /* [E] or NULL (no auto_reset) */
   const int32_t* n_agents;
   const float* w;          /* fp32 parameter blob */
   float* x;                /* [N][G_XS] scratch: the 75-float network input, fp32 */
@@ -73,6 +75,14 @@ __constant__ float c_oth_avg[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.5f, 0.0f, 1.0f};
 __constant__ float c_oth_std[7] = {5.0f, 5.0f, 1.0f, 1.0f, 1.0f, 5.0f, 1.0f};
 /* network.py:8-17 Actions, np.mgrid rows = start + k*step (filled by casim_ga3c_upload) */
 __constant__ float c_actions[G_ACT][2];
+
+/* auto_reset: an environment whose episode ended last step restarts inside the coming casim_step from the episode-start
+ * state kept by casim_reset (k_core, casim_step.cu); the policy is queried on that fresh state, flags cleared, exactly as
+ * env.reset() followed by env.step() would do.  g = any element of the environment. */
+__device__ __forceinline__ const float4* ga3c_src(const Ga3cArgs& p, size_t g) {
+  if (p.prev_game_over != nullptr && p.prev_game_over[(unsigned)g / (unsigned)p.A]) return p.state0;
+  return p.state;
+}
 
 #define U_NA 144 /* agents per CTA of the tensor-core path */
 #define U_XB_SLOTS 11
@@ -126,10 +136,10 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
       const size_t g = gb + a;
       const int e = (int)(g / A), i = (int)(g - (size_t)e * A);
       n = p.n_agents ? min(p.n_agents[e], A) : A;
-      const int type = __float_as_int(p.state[5 * N + g].w);
+      const int type = __float_as_int(ga3c_src(p, g)[5 * N + g].w);
       ok = (i < n && (type & 0xff) == CASIM_POLICY_GA3C_CADRL) ? 1 : 0;
       if (ok) {
-        const float4 h0 = p.state[g], h2 = p.state[2 * N + g];
+        const float4 h0 = ga3c_src(p, g)[g], h2 = ga3c_src(p, g)[2 * N + g];
         const double px = h0.x, py = h0.y;
         /* agent.py:250-269 get_ref */
         double gx = (double)h2.x - px, gy = (double)h2.y - py;
@@ -160,7 +170,7 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
       const int e = (int)(g / A), i = (int)(g - (size_t)e * A);
       if (j < s_n[a] && j != i) {
         const size_t o = (size_t)e * A + j;
-        const float4 o0 = p.state[o], o2 = p.state[2 * N + o];
+        const float4 o0 = ga3c_src(p, o)[o], o2 = ga3c_src(p, o)[2 * N + o];
         const double rx = (double)o0.x - s_fr[a][0], ry = (double)o0.y - s_fr[a][1];
         const double dc = sqrt(rx * rx + ry * ry);
         if (!(dc > c.sensing_horizon)) {
@@ -195,7 +205,7 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
     if (slot < 0) continue;
     const size_t g = gb + a;
     const size_t o = (g / A) * A + j;
-    const float4 o0 = p.state[o], o1 = p.state[N + o], o2 = p.state[2 * N + o];
+    const float4 o0 = ga3c_src(p, o)[o], o1 = ga3c_src(p, o)[N + o], o2 = ga3c_src(p, o)[2 * N + o];
     const double prx = s_fr[a][2], pry = s_fr[a][3], rh = s_fr[a][4];
     const double rx = (double)o0.x - s_fr[a][0], ry = (double)o0.y - s_fr[a][1];
     const double vx = o1.x, vy = o1.y;
@@ -212,7 +222,7 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
     const int a = tid;
     if (s_ok[a]) {
       const size_t g = gb + a;
-      const float4 h2 = p.state[2 * N + g], h3 = p.state[3 * N + g], h5 = p.state[5 * N + g];
+      const float4 h2 = ga3c_src(p, g)[2 * N + g], h3 = ga3c_src(p, g)[3 * N + g], h5 = ga3c_src(p, g)[5 * N + g];
       s_row[a][0] = (float)min(min(s_m[a], c.max_obs), G_SLOTS);
       s_row[a][1] = h3.z; /* dist_to_goal */
       s_row[a][2] = h5.x; /* heading_ego_frame */
@@ -419,7 +429,7 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
   if (tid < G_TILE) {
     const size_t g = g0 + tid;
     if (g < N && s_len[tid] >= 0) {
-      const int flags = __float_as_int(p.state[5 * N + g].z);
+      const int flags = __float_as_int(ga3c_src(p, g)[5 * N + g].z);
       if (flags & CASIM_F_IS_DONE) { /* collision_avoidance_env.py:298-300 */
         p.policy_actions[2 * g] = 0.f;
         p.policy_actions[2 * g + 1] = 0.f;
@@ -440,7 +450,7 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
         if (p.probs)
           for (int k = 0; k < G_ACT; k++) p.probs[g * G_ACT + k] = pr[k];
         if (p.action_idx) p.action_idx[g] = best;
-        const float pref = p.state[2 * N + g].w;
+        const float pref = ga3c_src(p, g)[2 * N + g].w;
         p.policy_actions[2 * g] = (float)((double)pref * (double)c_actions[best][0]); /* GA3CCADRLPolicy.py:40-42 */
         p.policy_actions[2 * g + 1] = c_actions[best][1];
       }
@@ -860,7 +870,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
         if (p.action_idx) p.action_idx[g] = -1;
       } else {
         /* softmax (+1e-4 floor) -> argmax -> action (network.py:45-51, GA3CCADRLPolicy.py:38-42) */
-        const int flags = __float_as_int(p.state[5 * N + g].z);
+        const int flags = __float_as_int(ga3c_src(p, g)[5 * N + g].z);
         if (flags & CASIM_F_IS_DONE) { /* collision_avoidance_env.py:298-300 */
           p.policy_actions[2 * g] = 0.f;
           p.policy_actions[2 * g + 1] = 0.f;
@@ -893,7 +903,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
             for (int k = 0; k < G_ACT; k++) p.probs[g * G_ACT + k] = pr[k];
           }
           if (p.action_idx) p.action_idx[g] = best;
-          const float pref = p.state[2 * N + g].w;
+          const float pref = ga3c_src(p, g)[2 * N + g].w;
           p.policy_actions[2 * g] = (float)((double)pref * (double)c_actions[best][0]);
           p.policy_actions[2 * g + 1] = c_actions[best][1];
         }
@@ -1023,13 +1033,15 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
   Ga3cArgs a;
   a.c = h->dc;
   a.state = reinterpret_cast<const float4*>(state);
+  a.state0 = reinterpret_cast<const float4*>(h->state0);
+  a.prev_game_over = (h->dc.auto_reset && h->init) ? h->prev_game_over : nullptr;
   a.n_agents = h->n_agents;
   a.w = h->ga3c_w;
   a.x = h->ga3c_x;
   a.xb = (use_tc & 1) ? reinterpret_cast<uint4*>(h->ga3c_xb) : nullptr;
   a.wimg = reinterpret_cast<const uint8_t*>(h->ga3c_wb);
   a.trace = nullptr;
-  static const char* trace_path = getenv("CASIM_GA3C_TRACE"); /* tuning aid: dumps phase time stamps, synchronises */
+  static const char* trace_path = casim_tuning_str("CASIM_GA3C_TRACE"); /* tuning aid: dumps phase time stamps, synchronises */
   if (use_tc && trace_path) {
     cudaMalloc((void**)&a.trace, (size_t)ntiles * 128 * sizeof(unsigned long long));
     cudaMemsetAsync(a.trace, 0, (size_t)ntiles * 128 * sizeof(unsigned long long), s);

@@ -96,7 +96,8 @@ struct casim_handle {
 enum { CASIM_MODE_STEP = 0, CASIM_MODE_RESET = 1, CASIM_MODE_OBSERVE = 2 };
 
 cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const float* ext_actions,
-                              const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s);
+                              const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s,
+                              const uint8_t* reset_mask = nullptr);
 cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laserscan, cudaStream_t s);
 cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s);
 cudaError_t casim_launch_raster(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps,
@@ -127,6 +128,21 @@ int casim_flat_row_size_impl(const casim_handle* h, const int32_t* keys, int n_k
 cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_params, cudaStream_t s);
 
 void casim_set_error(const char* fmt, ...);
+
+/* Tuning knobs (launch shapes, zero-copy, PDL, trace dumps) are read from the environment ONLY in a -DCASIM_TUNING
+ * build (make TUNING=1, used by the sweeps under profiles/); the release library has them compiled out, so that no
+ * environment variable can silently change what the product path launches. */
+#ifdef CASIM_TUNING
+#include <stdlib.h>
+static inline int casim_tuning_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+static inline const char* casim_tuning_str(const char* name) { return getenv(name); }
+#else
+static inline int casim_tuning_int(const char*, int dflt) { return dflt; }
+static inline const char* casim_tuning_str(const char*) { return nullptr; }
+#endif
 
 /* Programmatic dependent launch (PDL): the per-step kernels run back to back on one stream and each is short
  * (a single wave at the named batch sizes), so the launch latency between dependent kernels is a large share of a

@@ -64,6 +64,9 @@ struct RvoArgs {
   RvoObst ob;
   float time_horizon_obst;
   const float4* state; /* [6][E*A] */
+  const float4* state0;          /* episode-start state kept by casim_reset, or NULL */
+  const uint8_t* prev_game_over; /* [E] or NULL: with auto_reset, an environment that ended last step restarts inside the
+                                    coming casim_step from state0 -- the policy must read that state, like k_core does */
   const float* coop;   /* [E*A] Agent.cooperation_coef or NULL (= 1.0, agent.py:10) */
   const int32_t* n_agents;
   float* policy_actions; /* [E*A][2] */
@@ -373,7 +376,7 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
   const int e = (int)(g / A), ego = (int)(g - (size_t)e * A);
   const int n = p.n_agents ? min(p.n_agents[e], A) : A;
   if (ego >= n) return;
-  const float4* s0 = p.state + (size_t)e * A; /* px, py, heading, speed */
+  const float4* s0 = ((p.prev_game_over && p.prev_game_over[e]) ? p.state0 : p.state) + (size_t)e * A; /* px, py, heading, speed */
   const float4* s1 = s0 + N;                  /* vx, vy, ... */
   const float4* s2 = s1 + N;                  /* gx, gy, radius, pref_speed */
   const float4* s5 = s2 + 3 * N;
@@ -681,6 +684,8 @@ cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* c
   a.ob.root = h->rvo_n > 0 ? h->rvo_root : -1;
   a.time_horizon_obst = (float)prm->time_horizon; /* RVOPolicy.py:26-27: timeHorizonObst = time_horizon */
   a.state = reinterpret_cast<const float4*>(state);
+  a.state0 = reinterpret_cast<const float4*>(h->state0);
+  a.prev_game_over = (h->dc.auto_reset && h->init) ? h->prev_game_over : nullptr;
   a.coop = coop;
   a.n_agents = h->n_agents;
   a.policy_actions = policy_actions;

@@ -54,6 +54,8 @@ struct CoreArgs {
   const uint32_t* map_planes;  /* [n_maps][4][300][10] or NULL */
   const int32_t* edf_d2;       /* [n_maps][300][300] exact squared distance (cells^2) to the nearest occupied cell */
   uint8_t* prev_game_over;     /* [E] */
+  const uint8_t* reset_mask;   /* [E] or NULL.  RESET mode only: environments with mask[e] == 0 are left untouched
+                                  (casim_reset_envs: DummyVecEnv-style restart of the finished environments) */
   float4* state0;              /* [6][E*A] float4 episode-start state (written by RESET, re-loaded by auto_reset) */
   double* pose64;              /* [E*A][4] or NULL */
   double* partials;            /* [ctas][8] */
@@ -331,7 +333,8 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   const int le = lane / A, ai = lane - le * A;
   const int env0 = w * epw;
   const int e = env0 + le;
-  const bool slot = le < epw && e < p.E; /* lane maps to an [E,A] element */
+  bool slot = le < epw && e < p.E; /* lane maps to an [E,A] element */
+  if (MODE == CASIM_MODE_RESET && p.reset_mask != nullptr) slot = slot && p.reset_mask[e] != 0;
   const int n = slot ? (p.n_agents ? min(p.n_agents[e], A) : A) : 0;
   const bool valid = slot && ai < n;
   const int base = le * A; /* first lane of my environment */
@@ -693,7 +696,11 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     int nslots = min(epw, max(p.E - env0, 0)) * A;
     int total = nslots * rowlen;
     float* dst = p.o.other_agents_states + (size_t)env0 * A * rowlen;
-    if (total > 0) {
+    if (MODE == CASIM_MODE_RESET && p.reset_mask != nullptr) { /* masked reset: only the rows of the restarted envs */
+      const unsigned live = __ballot_sync(FULL_MASK, slot);
+      for (int i = lane; i < total; i += 32)
+        if ((live >> (i / rowlen)) & 1u) dst[i] = stage[i];
+    } else if (total > 0) {
       if ((((uintptr_t)dst) & 15) == 0 && (total & 3) == 0) {
         const float4* s4 = reinterpret_cast<const float4*>(stage);
         float4* d4 = reinterpret_cast<float4*>(dst);
@@ -744,8 +751,10 @@ cudaError_t launch_mode(const CoreArgs& a, int ap, dim3 grid, dim3 block, size_t
 }  // namespace
 
 cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const float* ext_actions,
-                              const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s) {
+                              const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s,
+                              const uint8_t* reset_mask) {
   CoreArgs a;
+  a.reset_mask = mode == CASIM_MODE_RESET ? reset_mask : nullptr;
   a.c = h->dc;
   a.state = reinterpret_cast<float4*>(state);
   a.ext_actions = ext_actions;
@@ -772,17 +781,9 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
   {
     /* The step is latency-bound at the named batch sizes (a few thousand warps for the whole GPU): fewer
      * environments per warp means more warps in flight per scheduler.  CASIM_EPW overrides (tuning aid). */
-    static int epw_env = -1;
-    if (epw_env < 0) {
-      const char* ev = getenv("CASIM_EPW");
-      epw_env = ev ? atoi(ev) : 0;
-    }
+    static const int epw_env = casim_tuning_int("CASIM_EPW", 0);
     if (epw_env > 0 && epw_env < a.epw) a.epw = epw_env;
-    static int diag_env = -1;
-    if (diag_env < 0) {
-      const char* ev = getenv("CASIM_STATS_DIAG");
-      diag_env = ev ? atoi(ev) : 0;
-    }
+    static const int diag_env = casim_tuning_int("CASIM_STATS_DIAG", 0);
     a.diag = diag_env;
   }
   a.write_pose = (obs->laserscan != nullptr || obs->local_grid != nullptr) ? 1 : 0;
@@ -795,11 +796,7 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
     }
   int warps = (h->E + a.epw - 1) / a.epw;
   size_t per_warp = obs->other_agents_states ? (size_t)32 * h->dc.rows * 10 * sizeof(float) : 0;
-  static int wpc_env = -1;
-  if (wpc_env < 0) {
-    const char* ev = getenv("CASIM_WPC");
-    wpc_env = ev ? atoi(ev) : 0;
-  }
+  static const int wpc_env = casim_tuning_int("CASIM_WPC", 0);
   int wpc = (wpc_env >= 1 && wpc_env <= CASIM_CORE_MAX_WARPS) ? wpc_env : CASIM_CORE_WARPS;
   while (wpc > 1 && per_warp * wpc > 96 * 1024) wpc >>= 1;
   /* the statistics word counts CTA arrivals in 16 bits: widen the CTAs rather than exceed it */

@@ -38,9 +38,12 @@ class StatsReducer:
         """stats: [8] float tensor written by casim_step on the current stream.  Returns the tensor that will hold
         the global sums once ``wait()`` returns."""
         if self.stream is not None:
+            # the snapshot is taken on the CURRENT stream, i.e. ordered before the next casim_step overwrites `stats`;
+            # only the collective runs on the side stream (it overlaps the next step's kernels)
+            self.total = stats.clone()
             self.stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self.stream):
-                self.total = stats.clone()
+                self.total.record_stream(self.stream)
                 if self.world > 1:
                     dist.all_reduce(self.total, op=dist.ReduceOp.SUM)
         else:

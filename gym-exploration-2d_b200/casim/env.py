@@ -14,6 +14,7 @@ import torch
 from . import layout as L
 from . import lib as _lib
 from .config import Config, make_sim_config
+from . import spaces as _spaces
 from .plugins import Agent
 from .sim import BatchedSim
 
@@ -78,10 +79,20 @@ class BatchedCollisionAvoidanceEnv:
         self._traj = None
         self._ga3c_weights = None
         self.states_in_obs = list(config.STATES_IN_OBS)
+        # gym-facing attributes (collision_avoidance_env.py:97-134); per environment, like the reference's
+        self.max_heading_change, self.min_heading_change = 4, -4
+        self.min_speed, self.max_speed = -4, 4
+        self.action_space_type = config.ACTION_SPACE_TYPE
+        self.action_space = _spaces.action_space_from_env(self)
+        self.observation_space = _spaces.observation_space_from_config(config)
+        self.num_envs = self.E
         self.episode_number = 0
         self.episode_step_number = 0
         self._host_state = None
         self._generator = None
+        # GA3C-CADRL forward: the fp32 kernel is the default because the action index it returns equals the fp32
+        # restatement of the reference network on every decisive state; the bf16 tensor-core kernel is opt-in
+        self.ga3c_use_tensor_cores = False
 
     # ---- scenario injection (the reference's reset() ignores set_agents(): SURVEY.md 3.2) ----
     def set_agents(self, agents):
@@ -192,8 +203,10 @@ class BatchedCollisionAvoidanceEnv:
             if self.sim is None:    # the generators' sensor lists are fixed (test_cases.py:1262, :1279, :1445)
                 bits = L.SENSOR_OTHER_AGENTS | (L.SENSOR_OCCUPANCY_GRID if kind == L.SCENARIO_SWAP_CIRCLE else 0)
                 self.sim = BatchedSim(self.E, self.A, cfg=self.cfg, device=self.device, sensors=(bits,))
-            seeds = (base + self.episode_number * self.E + np.arange(self.E) + 1).astype(np.uint32)
-            init, types_dev, n, gen_coop = self.sim.generate_scenario(kind, n_ag, seeds, ego_pol, ego_dyn, other_dyn)
+            self._env_episode = np.full((self.E,), self.episode_number, np.int64)
+            seeds = (base + self._env_episode * self.E + np.arange(self.E) + 1).astype(np.uint32)
+            self._gen_out = self.sim.generate_scenario(kind, n_ag, seeds, ego_pol, ego_dyn, other_dyn)
+            init, types_dev, n, gen_coop = self._gen_out
             types = types_dev.cpu().numpy()
         else:
             init, types, n = self._scenario()
@@ -296,18 +309,39 @@ class BatchedCollisionAvoidanceEnv:
         elif self._has_ig:
             pol = sim.explore_step()
         if self._has_ga3c:
-            pol = sim.ga3c_forward(use_tensor_cores=True)
+            pol = sim.ga3c_forward(use_tensor_cores=self.ga3c_use_tensor_cores)
         if self._has_rvo:
             pol = sim.rvo_step(coop=self._rvo_coop, params=self._rvo_params)
         sim.step(ext_actions=ext, policy_actions=pol, dt=dt)
         self.episode_step_number += 1
         self._host_state = None
-        rewards, done, game_over = sim.buf["rewards"], sim.buf["done"].bool(), sim.buf["game_over"].bool()
+        # copies: the next step overwrites the simulator's result buffers in place
+        rewards, done, game_over = sim.buf["rewards"].clone(), sim.buf["done"].bool(), sim.buf["game_over"].bool()
         if self.config.TRAIN_SINGLE_AGENT:
             rewards = rewards[:, 0]
         if self.E == 1:
             rewards, done, game_over = rewards[0], done[0], game_over[0]
         return BatchedObs(self), rewards, game_over, {"which_agents_done": done}
+
+    def reset_done_envs(self, game_over=None):
+        """DummyVecEnv's ``if done: obs = env.reset()`` for the batch: every environment whose ``game_over`` flag is set
+        starts a new episode NOW (state, observations, exploration belief, Dec-MCTS team state); with a scenario
+        generator the restarted environments draw their next scenario (seed of their own next episode number, like
+        _init_agents, collision_avoidance_env.py:403-415), otherwise they restart from their initial condition.
+        Returns the mask (bool CUDA tensor [E])."""
+        sim = self.sim
+        mask = sim.buf["game_over"] if game_over is None else game_over
+        mb = mask.bool()
+        if self._generator is not None:
+            kind, n_ag, ego_pol, ego_dyn, other_dyn, base = self._generator
+            self._env_episode += mb.cpu().numpy().astype(np.int64)
+            seeds = (base + self._env_episode * self.E + np.arange(self.E) + 1).astype(np.uint32)
+            sim.generate_scenario(kind, n_ag, seeds, ego_pol, ego_dyn, other_dyn, out=self._gen_out)
+        sim.reset_envs(mask)
+        if self._mcts is not None:
+            self._mcts.reset_envs(mb.cpu().numpy())
+        self._host_state = None
+        return mb
 
     def episode_stats(self):
         """per-step sums over this shard: n_new_collisions, n_new_at_goal, n_new_timeouts, n_game_over_envs,
@@ -318,3 +352,24 @@ class BatchedCollisionAvoidanceEnv:
         if self.sim is not None:
             self.sim.close()
             self.sim = None
+
+
+# ---- gym registration (gym_collision_avoidance/__init__.py:6-9) ----
+ENV_ID = "CollisionAvoidance-v0"
+_REGISTRY = {ENV_ID: BatchedCollisionAvoidanceEnv}
+
+
+def register():
+    """Register ``CollisionAvoidance-v0`` with gym when gym is importable (same id and call as the reference's package
+    __init__); ``casim.env.make`` works either way."""
+    try:
+        from gym.envs.registration import register as _reg      # pragma: no cover - gym is absent from the build image
+        _reg(id=ENV_ID, entry_point="casim.env:BatchedCollisionAvoidanceEnv")
+        return True
+    except Exception:
+        return False
+
+
+def make(env_id=ENV_ID, **kwargs):
+    """gym.make(env_id) for this package: ``make('CollisionAvoidance-v0', num_envs=4096)``."""
+    return _REGISTRY[env_id](**kwargs)

@@ -49,6 +49,7 @@ SYMBOLS = {
     "casim_set_map": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "casim_set_trajectories": (c_int, [c_void_p, c_void_p, c_int]),
     "casim_reset": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _POBS, c_void_p]),
+    "casim_reset_envs": (c_int, [c_void_p, c_void_p, c_void_p, _POBS, c_void_p]),
     "casim_observe": (c_int, [c_void_p, c_void_p, _POBS, c_void_p]),
     "casim_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_double, _POBS, c_void_p]),
     "casim_run_sensor": (c_int, [c_void_p, c_void_p, _POBS, c_int, c_void_p]),

@@ -312,6 +312,13 @@ class TeamPlanner:
             b["masks"][:] = 0
         self.steps = 0
 
+    def reset_envs(self, mask):
+        """Forget the communicated action distributions of the environments that start a new episode (mask [E] bool)."""
+        for b in self.best:
+            b["seqs"][mask] = END
+            b["q"][mask] = 0
+            b["masks"][mask] = 0
+
     def plan(self, done):
         """done [E,A] bool (agents that are not asked for an action, collision_avoidance_env.py:298-299).
         Returns float32 [E,A,2] actions ([vel, dphi]; zeros for everyone who did not plan)."""

@@ -146,17 +146,22 @@ class BatchedSim:
         self._keep["traj"] = t
         _lib.check(self.lib.casim_set_trajectories(self.handle, _lib.ptr(t), t.shape[2]), "casim_set_trajectories")
 
-    def generate_scenario(self, kind, number_of_agents, seeds, ego_policy, ego_dynamics, other_dynamics=L.DYN_UNICYCLE):
+    def generate_scenario(self, kind, number_of_agents, seeds, ego_policy, ego_dynamics, other_dynamics=L.DYN_UNICYCLE,
+                          out=None):
         """The reference's seeded scenario generators on the device (test_cases.py:1192-1463): kind =
         layout.SCENARIO_SWAP_CIRCLE / SCENARIO_RANDOM_POSITIONS, seeds [E] (non-zero).  Returns device tensors
-        (init [E,A,7], types [E,A], n_agents [E], coop [E,A]) ready for ``reset``."""
+        (init [E,A,7], types [E,A], n_agents [E], coop [E,A]) ready for ``reset``; ``out`` = such a tuple to overwrite
+        in place (the generator is a pure function of the seed: rows whose seed did not change keep their bytes)."""
         seeds = torch.as_tensor(np.ascontiguousarray(seeds, dtype=np.uint32).view(np.int32)).to(self.device) \
             if not isinstance(seeds, torch.Tensor) else seeds.to(device=self.device, dtype=torch.int32).contiguous()
         assert seeds.shape == (self.E,)
-        init = torch.empty((self.E, self.A, 7), dtype=torch.float32, device=self.device)
-        types = torch.empty((self.E, self.A), dtype=torch.int32, device=self.device)
-        n = torch.empty((self.E,), dtype=torch.int32, device=self.device)
-        coop = torch.empty((self.E, self.A), dtype=torch.float32, device=self.device)
+        if out is not None:
+            init, types, n, coop = out
+        else:
+            init = torch.empty((self.E, self.A, 7), dtype=torch.float32, device=self.device)
+            types = torch.empty((self.E, self.A), dtype=torch.int32, device=self.device)
+            n = torch.empty((self.E,), dtype=torch.int32, device=self.device)
+            coop = torch.empty((self.E, self.A), dtype=torch.float32, device=self.device)
         _lib.check(self.lib.casim_generate_scenario(self.handle, int(kind), int(number_of_agents), _lib.ptr(seeds),
                                                     int(ego_policy), int(ego_dynamics), int(other_dynamics), _lib.ptr(init),
                                                     _lib.ptr(types), _lib.ptr(n), _lib.ptr(coop), _stream_ptr()),
@@ -173,6 +178,20 @@ class BatchedSim:
         self._keep.update(init=init, types=types, n_agents=n_agents)
         _lib.check(self.lib.casim_reset(self.handle, _lib.ptr(self.state), _lib.ptr(init), _lib.ptr(types),
                                         _lib.ptr(n_agents), ctypes.byref(self._obs), _stream_ptr()), "casim_reset")
+
+    def reset_envs(self, mask):
+        """Restart the environments with mask[e] != 0 (uint8 / bool CUDA tensor [E], e.g. ``buf['game_over']``) from the
+        init / types / n_agents tensors of the last ``reset`` (``_keep``; rewrite their rows first for a new scenario)
+        and recompute their observations; every other environment is left untouched (casim_reset_envs)."""
+        m = mask if mask.dtype == torch.uint8 else mask.to(torch.uint8)
+        m = m.contiguous()
+        _lib.check(self.lib.casim_reset_envs(self.handle, _lib.ptr(self.state), _lib.ptr(m), ctypes.byref(self._obs),
+                                             _stream_ptr()), "casim_reset_envs")
+        if getattr(self, "belief", None) is not None:            # a new episode starts from the prior target map
+            self.belief[m.bool()] = float(self.cfg.ig_prior)
+        for k in ("team_targets", "team_n"):                       # obsvd_targets is None before the first update
+            for t in self.buf.get(k, []) or []:
+                t[m.bool()] = 0
 
     def bind(self, types=None, n_agents=None, init=None):
         """Tell the library about n_agents / types without re-initialising the state (used by tests that

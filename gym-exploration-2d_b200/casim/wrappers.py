@@ -41,6 +41,11 @@ class MultiagentFlattenDictWrapper:
             self.observation_indices[agent]['BOUNDS'] = [lo, size]
         self.size = size
         self.single_agent_size = size // max(self.max_num_agents, 1)
+        from . import spaces as _spaces                                  # wrappers.py:31-35
+        self.observation_space = _spaces.Box(-np.inf, np.inf, shape=(size,), dtype='float32')
+        self.single_agent_observation_space = _spaces.Box(-np.inf, np.inf, shape=(self.single_agent_size,), dtype='float32')
+        self.dict_observation_space = self.env.observation_space
+        self.action_space = self.env.action_space
 
     def reset(self):
         self.env.reset()
@@ -70,6 +75,27 @@ class MultiagentFlattenDictWrapper:
                 obs[agent][key] = observation_array[a:b]
         return obs
 
+    def multiEnvObservationArrayToDict(self, observation_array):  # noqa: N802 (reference name, wrappers.py:58-73)
+        """[num_envs, size] array -> object array [num_envs, max_num_agents] of per-agent dicts, filled only for the
+        agents whose 'use_ppo' entry is set, values reshaped to the observation-space shapes -- the reference's
+        semantics; index arithmetic on a host copy (this is the consumer side, not the step path)."""
+        a = observation_array.detach().cpu().numpy() if isinstance(observation_array, torch.Tensor) else np.asarray(observation_array)
+        num_envs = a.shape[0]
+        dict_obs = np.empty((num_envs, self.max_num_agents), dtype=dict)
+        spaces = self.env.observation_space.spaces
+        for env in range(num_envs):
+            for agent in range(self.max_num_agents):
+                lo, hi = self.observation_indices[agent]['use_ppo']
+                if not a[env, lo:hi]:
+                    continue
+                dict_obs[env][agent] = {}
+                for key in self.dict_keys:
+                    lo, hi = self.observation_indices[agent][key]
+                    v = a[env, lo:hi]
+                    shp = spaces[key].shape if key in spaces and int(np.prod(spaces[key].shape)) == v.size else v.shape
+                    dict_obs[env][agent][key] = v.reshape(shp)
+        return dict_obs
+
     def singleAgentObservationArrayToDict(self, observation_array, agent):  # noqa: N802 (wrappers.py:75-84)
         out = []
         for env in range(observation_array.shape[0]):
@@ -97,14 +123,19 @@ class FlattenDictWrapper(MultiagentFlattenDictWrapper):
 
 class BatchedVecEnv:
     """What MultiagentDummyVecEnv([make_env] * n_envs) (envs/wrappers.py:101-106, env_utils.py:29-33) gives a trainer:
-    ``reset() -> obs [num_envs, size]``, ``step(actions) -> (obs, rews, dones, infos)`` with finished environments
-    restarted automatically (DummyVecEnv semantics) -- here through the simulator's auto_reset, with no host loop."""
+    ``reset() -> obs [num_envs, size]``, ``step(actions) -> (obs, rews, dones, infos)`` with DummyVecEnv semantics
+    (stable_baselines dummy_vec_env.step_wait): an environment that reports ``done`` is reset INSIDE the same call, the
+    returned observation row is the new episode's first observation, and the finished episode's last observation is
+    handed over as ``infos['terminal_observation']`` (rows of the environments in ``infos['terminal_mask']``).
+    The restart is one masked launch (casim_reset_envs) -- no host loop over environments; with a scenario generator
+    the restarted environments draw their next scenario, otherwise they restart from their initial condition."""
 
-    def __init__(self, wrapped):
+    def __init__(self, wrapped, keep_terminal_obs=True):
         self.wrapped = wrapped
         self.env = wrapped.env
         self.num_envs = self.env.E
-        self.env.cfg.auto_reset = 1
+        self.keep_terminal_obs = keep_terminal_obs
+        self.env.cfg.auto_reset = 0          # restarts are explicit here (after the step), not folded into the next step
 
     def reset(self):
         if self.env.sim is not None:
@@ -113,6 +144,13 @@ class BatchedVecEnv:
 
     def step(self, actions=None):
         obs, rewards, game_over, info = self.wrapped.step(actions)
+        info = dict(info)
+        if bool(game_over.any()):
+            if self.keep_terminal_obs:
+                info["terminal_observation"] = obs.clone()
+            info["terminal_mask"] = game_over.reshape(-1).clone()
+            self.env.reset_done_envs()
+            obs = self.wrapped.observation()
         return obs, rewards, game_over, info
 
     def step_async(self, actions):

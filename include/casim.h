@@ -210,6 +210,14 @@ int casim_set_trajectories(casim_handle* h, const float* traj, int T);
 int casim_reset(casim_handle* h, float* state, const float* init, const int32_t* type,
                 const int32_t* n_agents, const casim_obs* obs, void* stream);
 
+/* Restart SOME environments: for every environment with mask[e] != 0 (device uint8 [E], e.g. the game_over buffer the
+ * last casim_step wrote) redo what casim_reset does -- Agent.__init__ from the init / type / n_agents buffers given to
+ * the last casim_reset (still borrowed; the caller may have rewritten the rows of those environments with a new
+ * scenario) and the first _get_obs -- and leave every other environment's state and observations untouched.  This is
+ * DummyVecEnv's "if done: obs = env.reset()" (envs/wrappers.py:101-106 MultiagentDummyVecEnv, stable_baselines
+ * dummy_vec_env.step_wait) for the whole batch in one launch.  rewards / done / game_over / stats are not written. */
+int casim_reset_envs(casim_handle* h, float* state, const uint8_t* mask, const casim_obs* obs, void* stream);
+
 /* Recompute sensors/observations from a caller-modified state without stepping (_get_obs, :740-753). */
 int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, void* stream);
 
@@ -234,7 +242,7 @@ int casim_run_sensor(casim_handle* h, const float* state, const casim_obs* obs, 
  * buffer is page-locked + mapped (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory) and no larger than
  * CASIM_ZEROCOPY_MAX bytes are stored by the step kernel directly into host memory over PCIe -- their `dev`
  * counterparts are then NOT updated by this call; everything else (sensor planes, pageable buffers) is copied with
- * cudaMemcpyAsync from `dev`.  Environment CASIM_ZEROCOPY=0 forces the copy path for every field. */
+ * cudaMemcpyAsync from `dev`. */
 int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
                     const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
                     void* stream);
