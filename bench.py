@@ -1,20 +1,23 @@
 #!/usr/bin/env python
 """bench.py -- agent-steps/s of the batched CollisionAvoidanceEnv step on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|full] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload full|c2|c3|c4|c5|rvo] [--impl reference]
 
-One "step" = one pass of the hot path (casim_step) over one batch of E envs x A agents of synthetic
-scenarios (casim/scenarios.py).  Default workload = BASELINE.json configs[1] (C2): 4096 envs x 10 agents per
-GPU, NonCooperative/Static mix, collision + reward step only.  Prints ONE JSON line (rank 0).
+One "step" = one pass of the hot path (casim_step, preceded by the policy kernel of the workload) over one batch of E envs
+x A agents of synthetic scenarios (casim/scenarios.py).  DEFAULT WORKLOAD = `full`: the configuration
+BASELINE.json's north_star quotes its target on -- 4096 envs x 10 agents per GPU with OtherAgentsStates + LaserScan +
+OccupancyGrid on the crossing map.  Prints ONE JSON line (rank 0).
 
-Timing: device-side CUDA events on the launching stream around exactly K steps, after W warm-up steps, with a
-barrier + synchronize on both sides, max over ranks.  The K steps are captured in one CUDA graph (no Python
-in the timed region) and walk a RING of independent env batches whose combined footprint exceeds the 126 MB
-L2, so no step finds its inputs in cache ("inputs larger than L2").  `e2e` is the same metric through the
-host-buffer call (pinned host actions H2D, step, rewards/done/game_over/stats D2H, blocking) per step.
-`cpu_baseline` / `--impl reference` time the CPU oracle port (oracle/casim_oracle.c, plain C fp64 restatement
-of the reference's Python step, POSIX threads over environments) on the host cores: the reference itself is
-Python that needs /root/reference, which does not exist on the GPU box.
+Timing: device-side CUDA events on the launching stream around `reps` replays of ONE CUDA graph of exactly K steps
+(reps chosen so that the timed region is >= 50 ms; ms_per_step = time / (K * reps)), after W warm-up steps, with a
+barrier + synchronize on both sides, max over ranks.  The K steps walk a RING of independent env batches whose combined
+footprint exceeds the 126 MB L2 ("inputs larger than L2").  The design's one collective -- the all-reduce of the [8]
+per-step episode statistics -- is issued once per step INSIDE the graph on a side stream (NCCL, N > 1), overlapping the
+next step's kernels.  `e2e` is the same metric through the host-buffer call (pinned host actions in, results and
+observations out) per step.  `cpu_baseline` / `--impl reference` time the CPU oracle port (oracle/casim_oracle.c, plain
+C fp64 restatement of the reference's Python step, POSIX threads over environments) on the host cores: the reference
+itself is Python that needs /root/reference, which does not exist on the GPU box; its own step rate, measured in the
+build container by oracle/time_reference_python.py, is quoted from profiles/reference_python_rates.json.
 """
 import argparse
 import json
@@ -40,6 +43,13 @@ BYTES_OAS = 384           # 9 x 10 fp32 rows + 6 scalar observation words
 BYTES_LASER = 320         # 16 fp32 ranges written + 256 one-byte cell samples
 BYTES_WALL = 81           # disc of cells around the agent (r = 0.5 m)
 BYTES_GRID = 11169        # 3600 B written + <= 87^2 B rotated window read
+# bytes that HAVE to cross HBM per agent-step: what is written plus the state that is read; a shared map
+# lives in L2 / shared memory and costs nothing, a per-env map adds its bit planes once per environment
+MUST_CORE = 177
+MUST_OAS = 384
+MUST_LASER = 64
+MUST_GRID = 3600
+MAP_PLANE_BYTES = 4 * 300 * 40     # four footprint bit planes of one map (per-env-map runs only)
 
 WORKLOADS = {
     "c2": dict(E=4096, A=10, sensors=(), desc="4096 envs x 10 agents, NonCooperative/Static mix, collision + reward step only"),
@@ -71,6 +81,20 @@ def algorithmic_bytes(wl):
     return b
 
 
+def must_move_bytes(wl, per_env_maps=False, A=10):
+    b = MUST_CORE
+    s = WORKLOADS[wl]["sensors"]
+    if "other_agents_states" in s:
+        b += MUST_OAS
+    if "laserscan" in s:
+        b += MUST_LASER
+    if "local_grid" in s:
+        b += MUST_GRID
+    if per_env_maps and ("laserscan" in s or "local_grid" in s):
+        b += MAP_PLANE_BYTES / A
+    return b
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -87,11 +111,13 @@ def tensor_peak():
         return 2250.0, "fallback (nominal dense bf16)"
 
 
-def roofline_obj(wl, kern, dominant, step_s, step_bytes, explore_counts):
+def roofline_obj(wl, kern, dominant, step_s, step_bytes, step_must, explore_counts):
     """Roofline of the DOMINANT kernel of the step (algorithmic bytes or flops per launch / its measured launch
-    duration) plus the per-kernel breakdown and the whole-step figure."""
+    duration) plus the per-kernel breakdown and the whole-step figure.  Two byte counts are reported for HBM-bound
+    kernels: `frac` on SURVEY.md 8(d)'s algorithmic bytes (which count the rotated map window of the occupancy grid and
+    the laser's cell samples as if they came from HBM) and `frac_must_move` on the bytes that have to cross HBM."""
     peak, peak_src = peaks()
-    t, units, how = kern[dominant]
+    t, units, how, must = kern[dominant]
     tensor = dominant in ("k_ga3c_tc", "k_ga3c_fwd")
     if tensor:
         tpeak, tsrc = tensor_peak()
@@ -101,13 +127,18 @@ def roofline_obj(wl, kern, dominant, step_s, step_bytes, explore_counts):
     else:
         ach = units / t / 1e9
         out = {"bound": "hbm", "kernel": dominant, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-               "peak_source": peak_src, "algorithmic_bytes_per_launch": units}
+               "peak_source": peak_src, "algorithmic_bytes_per_launch": units,
+               "must_move_bytes_per_launch": must, "achieved_must_move": must / t / 1e9, "frac_must_move": must / t / 1e9 / peak}
     out["duration_us"] = t * 1e6
     out["how"] = how
     out["traffic"] = traffic_for(wl, dominant)
-    out["kernels"] = {k: {"duration_us": v[0] * 1e6, "share_of_step": v[0] / step_s, "how": v[2]} for k, v in kern.items()}
+    out["kernels"] = {k: {"duration_us": v[0] * 1e6, "share_of_step": v[0] / step_s, "how": v[2],
+                          "frac": (v[1] / v[0] / 1e9 / peak) if not k.startswith("k_ga3c") else None,
+                          "frac_must_move": (v[3] / v[0] / 1e9 / peak) if not k.startswith("k_ga3c") else None}
+                      for k, v in kern.items()}
     out["whole_step"] = {"duration_us": step_s * 1e6, "algorithmic_bytes": step_bytes,
-                         "achieved_GBps": step_bytes / step_s / 1e9, "frac_of_hbm_peak": step_bytes / step_s / 1e9 / peak}
+                         "achieved_GBps": step_bytes / step_s / 1e9, "frac_of_hbm_peak": step_bytes / step_s / 1e9 / peak,
+                         "must_move_bytes": step_must, "frac_must_move": step_must / step_s / 1e9 / peak}
     if explore_counts is not None:
         out["explore_counters_one_launch"] = dict(zip(("cells_tested", "edf_samples", "visible_cells", "clamped"), explore_counts))
     return out
@@ -122,7 +153,32 @@ def traffic_for(wl, kernel=None):
         return None
 
 
+def reference_python_rates(wl):
+    """The reference's own Python step rate for this workload, measured in the build container (one core) by
+    oracle/time_reference_python.py -- it cannot run on the GPU box (/root/reference is absent there)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "reference_python_rates.json")) as f:
+            d = json.load(f)
+        w = dict(d["workloads"].get(wl, {}))
+        w["measured"] = "build container, 1 core (%s), %s" % (d.get("host", "?"), d.get("how", ""))
+        return w
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------
+_C2_CASES = None
+
+
+def c2_cases():
+    """The reference's 10-agent scenario suite (tests/golden/c2_10_agents_500_cases.npz, derived from
+    envs/test_cases/10_agents_500_cases.p by oracle/gen_bench_scenarios.py)."""
+    global _C2_CASES
+    if _C2_CASES is None:
+        _C2_CASES = np.load(os.path.join(ROOT, "tests", "golden", "c2_10_agents_500_cases.npz"))["cases"]
+    return _C2_CASES
+
+
 def scenario(wl, E, A, seed):
     from casim import layout as L
     from casim import scenarios as S
@@ -135,10 +191,13 @@ def scenario(wl, E, A, seed):
     if "local_grid" in sensors:
         mask |= L.SENSOR_OCCUPANCY_GRID
     if wl == "c2":
-        init, types, n = S.open_space(E, A, seed=seed, sensors=0)
+        init, types, n = (S.from_cases(c2_cases(), E, A, seed=seed) if A == 10 else S.open_space(E, A, seed=seed, sensors=0))
         return init, types, n, None
     if wl == "rvo":
-        init, types, n = S.open_space(E, A, seed=seed, sensors=0, static_every=0, policy=L.POLICY_RVO)
+        if A == 10:
+            init, types, n = S.from_cases(c2_cases(), E, A, seed=seed, static_every=0, policy=L.POLICY_RVO)
+        else:
+            init, types, n = S.open_space(E, A, seed=seed, sensors=0, static_every=0, policy=L.POLICY_RVO)
         return init, types, n, None
     if wl == "c4":
         return S.exploration(E, seed=seed)
@@ -146,6 +205,30 @@ def scenario(wl, E, A, seed):
         init, types, n = S.formations(E, A, seed=seed)
         return init, types, n, None
     return S.crossing(E, A, seed=seed, sensors=mask)
+
+
+def workload_config(wl, E, A, world, per_env_maps=False):
+    """The `config` object of the JSON line -- identical for the GPU arm and the reference arm (it names the workload,
+    not the implementation)."""
+    W = WORKLOADS[wl]
+    return {"workload": wl + ": " + W["desc"], "envs_per_gpu": E, "agents_per_env": A, "sensors": list(W["sensors"]),
+            "scenario": SCENARIO_DESC[wl], "map": ("per-env maps" if per_env_maps else "one map shared by all envs") if wl in ("c3", "full", "c4") else "none",
+            "auto_reset": True, "n_ranks": world,
+            "l2": "inputs larger than L2: ring of independent env batches, > 1.5 x 126 MB resident per GPU",
+            "launch": "one CUDA graph of K steps, replayed `reps` times (timed region >= 50 ms)",
+            "parallelism": "envs sharded over the ranks, no data-path collective; per-step all-reduce of the [8] episode "
+                           "statistics on a side stream inside the timed region (NCCL when n_ranks > 1)",
+            "state": "fp32 SoA state, fp64 predicates (dtype = arithmetic of the decision path)"}
+
+
+SCENARIO_DESC = {
+    "c2": "env e = case (e mod 500) of the reference's 10_agents_500_cases suite + N(0, 0.05^2) jitter; agents i%5==4 Static",
+    "rvo": "same cases as c2, every agent RVOPolicy",
+    "c3": "starts in the free cross of the crossing map, arm uniform, along U(3,12), across U(-1.4,1.4), goal = -start, starts >= 1.2 m apart",
+    "full": "starts in the free cross of the crossing map, arm uniform, along U(3,12), across U(-1.4,1.4), goal = -start, starts >= 1.2 m apart",
+    "c4": "2 ig_greedy explorers on the cross + 2 static targets (IG_agent_crossing layout)",
+    "c5": "starts on a radius-10 circle, goals along the strokes of the formation() letter 'CADRL'[e mod 5]",
+}
 
 
 def ga3c_weights(seed=0):
@@ -162,16 +245,18 @@ def ga3c_weights(seed=0):
     return np.concatenate(parts)
 
 
-def oracle_run(wl, E, A, steps, warmup, threads, seed=1234):
+def oracle_run(wl, E, A, steps, warmup, threads, seed=1234, per_env_maps=False):
     """CPU oracle port on the same synthetic workload; returns (agent-steps/s, seconds per step)."""
     from oracle import oracle
-    from casim import lib
-    cfg = lib.default_config()
-    cfg.auto_reset = 1
+    cfg = oracle.default_config()        # byte-identical to casim_default_config (tests/test_abi_cpu.py); the CPU arms
+    cfg.auto_reset = 1                   # never load libcasim.so
     init, types, n, rects = scenario(wl, E, A, seed)
     maps = None
     if rects is not None:
         maps = oracle.rasterize(cfg, rects.astype(np.float64))
+        if per_env_maps:
+            from casim.scenarios import per_env_crossing_rects
+            maps = np.stack([oracle.rasterize(cfg, r.astype(np.float64)) for r in per_env_crossing_rects(E, seed=77)])
     # the oracle only runs sensors whose output buffer exists; give it exactly the workload's
     sensors = WORKLOADS[wl]["sensors"]
     state, obs = oracle.reset(cfg, init.astype(np.float64), types, n_agents=n, maps=maps)
@@ -267,6 +352,16 @@ class ClockSampler:
 REF_SAMPLE_ENVS = {"c2": 4096, "c3": 512, "full": 64, "c4": 128, "c5": 256, "rvo": 2048}
 
 
+def cpu_baseline_obj(wl, v, threads, sample):
+    out = {"value": v, "unit": "agent-steps/s", "cores": threads, "kind": "port", "sample": sample,
+           "what": "oracle/casim_oracle.c: plain-C fp64 restatement of the reference's Python step (pinned to it by "
+                   "tests/golden), POSIX threads over environments -- a STRONGER baseline than the reference's own Python"}
+    rp = reference_python_rates(wl)
+    if rp is not None:
+        out["reference_python"] = rp
+    return out
+
+
 def run_reference(args, rank, world):
     """--impl reference: the CPU implementation of the path (oracle port, all host threads) on a bounded sample."""
     if rank != 0:
@@ -274,21 +369,19 @@ def run_reference(args, rank, world):
     wl = args.workload
     W = WORKLOADS[wl]
     threads = min(os.cpu_count() or 1, 64)
-    E, A = W["E"], W["A"]
+    E, A = (args.envs or W["E"]), W["A"]
     # bounded sample: the full per-GPU batch for the cheap workloads, fewer envs when sensors make a step slow
-    Es = REF_SAMPLE_ENVS[wl]
+    Es = min(REF_SAMPLE_ENVS[wl], E)
     steps = max(1, min(args.steps, 200 if wl == "c2" else 40))
     warm = max(1, min(args.warmup, 5))
-    v, sps = oracle_run(wl, Es, A, steps, warm, threads)
+    v, sps = oracle_run(wl, Es, A, steps, warm, threads, per_env_maps=bool(args.per_env_maps and wl in ('c3', 'full')))
+    sample = "%d steps of %d envs x %d agents per step (oracle/casim_oracle.c, %d POSIX threads over envs)" % (steps, Es, A, threads)
     line = {
         "impl": "reference", "metric": "agent-steps/s", "value": v, "unit": "agent-steps/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": wl + ": " + W["desc"], "envs_per_step": Es, "agents_per_env": A},
-        "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": threads, "kind": "port",
-                         "sample": "%d steps of %d envs x %d agents (oracle/casim_oracle.c, %d POSIX threads over envs; the Python "
-                                   "reference itself measured 2.9e3 agent-steps/s/core in the build container, BASELINE.md)"
-                                   % (steps, Es, A, threads)},
+        "config": workload_config(wl, E, A, world, args.per_env_maps),
+        "cpu_baseline": cpu_baseline_obj(wl, v, threads, sample),
         "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -318,15 +411,19 @@ def emit(line):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="full", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="casim", choices=["casim", "reference"])
     ap.add_argument("--envs", type=int, default=None, help="override envs per GPU (parity/sweep use; default = the named config)")
+    ap.add_argument("--per-env-maps", action="store_true", help="c3/full: one map per environment (n_maps == E) instead of a shared map")
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of one CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-collective", action="store_true", help="diagnostics: leave the per-step statistics all-reduce out")
+    ap.add_argument("--min-timed-ms", type=float, default=50.0, help="replay the K-step graph until the timed region is this long")
     ap.add_argument("--e2e-steps", type=int, default=200)
-    ap.add_argument("--ga3c-fp32", action="store_true", help="c5: use the fp32 SIMT forward instead of the tensor-core path")
+    ap.add_argument("--ga3c-tc", action="store_true", help="c5: bf16 tensor-core forward (default: the fp32 forward, whose "
+                    "action index equals the reference network's on every decisive state)")
     ap.add_argument("--no-stats", action="store_true", help="diagnostics: do not compute the per-step episode statistics")
     ap.add_argument("--ring", type=int, default=None, help="override the number of env batches in the ring (diagnostics)")
     args = ap.parse_args()
@@ -355,6 +452,7 @@ def main():
     K, Wm = args.steps, max(args.warmup, 3)
     cfg = lib.default_config()
     cfg.auto_reset = 1
+    per_env_maps = bool(args.per_env_maps and wl in ("c3", "full"))
 
     # ---- ring of independent env batches, footprint > L2 ----
     per_agent_resident = 96 + 5 + (16 if W["sensors"] else 0)
@@ -373,13 +471,17 @@ def main():
     R = int(min(max(2, -(-int(1.5 * L2_BYTES) // batch_bytes)), 96))
     if args.ring:
         R = args.ring
-    stats_all = torch.zeros((max(K, Wm, args.e2e_steps), NUM_STATS), dtype=torch.float32, device=dev)
+    stats_rows = torch.zeros((max(K, Wm, 1), NUM_STATS), dtype=torch.float32, device=dev)
     sims = []
     for r in range(R):
         sim = BatchedSim(E, A, cfg=cfg, sensors=W["sensors"], want_debug=False, want_misc=bool(W["sensors"]), want_stats=not args.no_stats)
         init, types, n, rects = scenario(wl, E, A, seed=1234 + 1000 * rank + r)
         if rects is not None:
-            sim.set_obstacles(rects)
+            if per_env_maps:
+                from casim.scenarios import per_env_crossing_rects
+                sim.set_obstacles(per_env_crossing_rects(E, seed=77 + r))
+            else:
+                sim.set_obstacles(rects)
         if wl == "c4":
             sim.enable_exploration(want_debug=False)
         if wl == "c5":
@@ -389,9 +491,11 @@ def main():
     torch.cuda.synchronize()
     launches_per_step = 1 + (1 if "laserscan" in W["sensors"] else 0) + (1 if "local_grid" in W["sensors"] else 0)
     launches_per_step += 1 if wl in ("c4", "rvo") else (2 if wl == "c5" else 0)
-    use_tc = not args.ga3c_fp32
+    use_tc = bool(args.ga3c_tc)
 
     stream = torch.cuda.Stream(device=dev)
+    side = torch.cuda.Stream(device=dev)
+    collective = (not args.no_collective) and (not args.no_stats)
 
     def policy_step(sim):
         if wl == "c4":
@@ -402,58 +506,84 @@ def main():
             return sim.rvo_step()
         return None
 
-    def run_steps(k0, k):
+    def run_steps(k0, k, reduce_stats=True):
+        """Steps k0 .. k0+k-1 on `stream` (current).  Step i writes its episode statistics into row i of `stats_rows`
+        (one row per step of the graph, so nothing has to be cloned) and the row is all-reduced across the ranks on
+        the side stream while the next step's kernels run."""
         for i in range(k0, k0 + k):
             sim = sims[i % R]
+            row = stats_rows[i % stats_rows.shape[0]]
+            if not args.no_stats:
+                sim._obs.stats = row.data_ptr()
             sim.step(policy_actions=policy_step(sim))
+            if collective and reduce_stats:
+                side.wait_stream(stream)
+                with torch.cuda.stream(side):
+                    if world > 1:
+                        dist.all_reduce(row, op=dist.ReduceOp.SUM)
+        if collective and reduce_stats:
+            stream.wait_stream(side)
 
     with torch.cuda.stream(stream):
-        run_steps(0, Wm)                                  # warm-up (also loads the kernels)
+        run_steps(0, Wm)                                  # warm-up (also loads the kernels, creates the NCCL communicator)
     stream.synchronize()
+    side.synchronize()
 
     graph = None
     if not args.no_graph:
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.stream(stream):
             with torch.cuda.graph(graph, stream=stream):
-                run_steps(Wm, K)
+                run_steps(0, K)
         stream.synchronize()
-        # one untimed replay: graph upload + every ring batch touched once more
-        with torch.cuda.stream(stream):
+
+    def one_pass():
+        if graph is not None:
             graph.replay()
-        stream.synchronize()
+        else:
+            run_steps(0, K)
+
+    # untimed passes: graph upload, every ring batch touched once more, and the duration that sizes `reps`
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        one_pass()
+        ev0.record(stream)
+        one_pass()
+        ev1.record(stream)
+    stream.synchronize()
+    pass_ms = max(ev0.elapsed_time(ev1), 1e-3)
+    reps = max(1, int(-(-args.min_timed_ms // pass_ms)))
+    if world > 1:                                        # every rank must replay the same number of collectives
+        t = torch.tensor([reps], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        reps = int(t.item())
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
         time.sleep(0.15)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- timed region: exactly K steps ----
+    # ---- timed region: reps x exactly K steps ----
     barrier()
     t_load0 = time.perf_counter()
     with torch.cuda.stream(stream):
         ev0.record(stream)
-        if graph is not None:
-            graph.replay()
-        else:
-            run_steps(Wm, K)
+        for _ in range(reps):
+            one_pass()
         ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
+    stats_last = stats_rows[:K].clone()
     # keep the same workload running ~1.2 s so that nvidia-smi (50 ms period) sees the clocks under this load
     t_end = time.perf_counter() + 1.2
     with torch.cuda.stream(stream):
         while time.perf_counter() < t_end:
-            if graph is not None:
-                graph.replay()
-            else:
-                run_steps(0, 50)
+            one_pass()
             stream.synchronize()
     t_load1 = time.perf_counter()
     if sampler:
@@ -463,7 +593,7 @@ def main():
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    total_agent_steps = float(E * A * K * world)
+    total_agent_steps = float(E * A * K * reps * world)
     value = total_agent_steps / (ms * 1e-3)
 
     # ---- e2e: host-buffer call per step (pinned H2D of the actions, D2H of rewards/done/game_over/stats) ----
@@ -509,12 +639,23 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_value = float(E * A * Ke * world) / e2e_s
+    e2e_call = "casim_step_host via BatchedSim.bind_host_step (blocking, pinned host buffers; scalars zero-copy)"
 
-    # ---- per-step episode statistics: the one collective of the design (NCCL all-reduce of [8] floats) ----
-    stats = sims[0].buf["stats"].clone() if sims[0].buf["stats"] is not None else torch.zeros((NUM_STATS,), device=dev)
-    if world > 1:
-        dist.all_reduce(stats)
-    stats = [float(x) for x in stats.cpu()]
+    # ---- episode statistics of the timed region's last pass (rows already all-reduced inside the graph when N > 1) ----
+    st = stats_last.double().cpu().numpy()
+    if world > 1 and not collective and not args.no_stats:
+        t = stats_last.clone()
+        dist.all_reduce(t)
+        st = t.double().cpu().numpy()
+    n_ag = max(float(st[:, 6].mean()), 1.0)
+    episode = {"per_step_mean": {"new_collisions": float(st[:, 0].mean()), "new_at_goal": float(st[:, 1].mean()),
+                                 "new_timeouts": float(st[:, 2].mean()), "game_over_envs": float(st[:, 3].mean()),
+                                 "reward_sum": float(st[:, 4].mean()), "active_agents": float(st[:, 5].mean()),
+                                 "agents": float(st[:, 6].mean())},
+               "active_agent_fraction": float(st[:, 5].mean()) / n_ag,
+               "new_collision_fraction_per_step": float(st[:, 0].mean()) / n_ag,
+               "env_resets_per_step": float(st[:, 3].mean()),
+               "all_ranks": world > 1}
 
     # ---- per-kernel durations, measured live with CUDA events on the launching stream: each kernel class is
     # replayed alone (one CUDA graph of `reps` launches walking the same ring of batches, inputs > L2) ----
@@ -538,17 +679,17 @@ def main():
             stream.synchronize()
         return a.elapsed_time(b) * 1e-3 / reps
 
-    step_s = ms * 1e-3 / K
+    step_s = ms * 1e-3 / (K * reps)
     kern = {}          # name -> (seconds per launch, algorithmic units per launch, how)
     NA = E * A
     t_sens = 0.0
     if "laserscan" in W["sensors"]:
         t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_LASERSCAN))
-        kern["k_laser"] = (t, BYTES_LASER * NA, "timed alone")
+        kern["k_laser"] = (t, BYTES_LASER * NA, "timed alone", MUST_LASER * NA + (MAP_PLANE_BYTES * E if per_env_maps else 0))
         t_sens += t
     if "local_grid" in W["sensors"]:
         t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_OCCUPANCY_GRID))
-        kern["k_grid"] = (t, BYTES_GRID * NA, "timed alone")
+        kern["k_grid"] = (t, BYTES_GRID * NA, "timed alone", MUST_GRID * NA + (MAP_PLANE_BYTES * E if per_env_maps else 0))
         t_sens += t
     explore_counts = None
     if wl == "c4":
@@ -563,57 +704,58 @@ def main():
         # EDF samples x 8 B + visible cells of the update x 16 B (RMW) + visible cells of the 9
         # candidates x 8 B, from the instrumented counters of one launch (all 10 poses share counter 2)
         xbytes = explore_counts[1] * 8 + explore_counts[2] * 8 + (explore_counts[2] // 10) * 8
-        kern["k_explore"] = (t, xbytes, "timed alone")
+        kern["k_explore"] = (t, xbytes, "timed alone", explore_counts[2] // 10 * 8 + 64 * NA // 2)
         t_sens += t
     if wl == "rvo":
         t = time_alone(lambda sm: sm.rvo_step())
         # per agent: own 3 state planes read (48 B) + 8 B action written; the neighbours' planes are re-read from
         # L1/L2 within the environment (A-1 x 48 B per agent, not HBM traffic)
-        kern["k_rvo"] = (t, (48 + 8) * NA, "timed alone")
+        kern["k_rvo"] = (t, (48 + 8) * NA, "timed alone", (48 + 8) * NA)
         t_sens += t
     if wl == "c5":
         t_both = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc))
         t_fwd = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc, forward_only=True))
         fwd_name = "k_ga3c_tc" if use_tc else "k_ga3c_fwd"
-        kern[fwd_name] = (t_fwd, GA3C_FLOP_PER_AGENT * NA, "timed alone (forward kernel on the previous state vectors)")
+        kern[fwd_name] = (t_fwd, GA3C_FLOP_PER_AGENT * NA, "timed alone (forward kernel on the previous state vectors)", 0)
         # state-vector kernel: reads 4 state planes of the agent + 3 of each other agent (L1/L2-resident within the
         # env), writes the 76-float row + 11 bf16 chunks: counted as 64 + 304 + 176 B per agent
-        kern["k_ga3c_state"] = (max(t_both - t_fwd, 1e-9), (64 + 304 + 176) * NA, "state+forward timed alone minus the forward alone")
+        kern["k_ga3c_state"] = (max(t_both - t_fwd, 1e-9), (64 + 304 + 176) * NA, "state+forward timed alone minus the forward alone", (64 + 304 + 176) * NA)
         t_sens += t_both
     core_units = (BYTES_CORE + (BYTES_OAS if "other_agents_states" in W["sensors"] else 0)
                   + (BYTES_WALL if "laserscan" in W["sensors"] or "local_grid" in W["sensors"] else 0)) * NA
-    kern["k_core"] = (max(step_s - t_sens, 1e-9), core_units, "timed alone" if not kern else "step time minus the kernels timed alone")
+    core_must = (MUST_CORE + (MUST_OAS if "other_agents_states" in W["sensors"] else 0)) * NA
+    kern["k_core"] = (max(step_s - t_sens, 1e-9), core_units, "timed alone" if not kern else "step time minus the kernels timed alone", core_must)
     dominant = max(kern, key=lambda k: kern[k][0])
 
     if rank == 0:
-        peak, peak_src = peaks()
-        alg = algorithmic_bytes(wl)
-        achieved = alg * E * A / step_s / 1e9
+        cfgd = workload_config(wl, E, A, world, per_env_maps)
         line = {
             "metric": "agent-steps/s", "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": Wm,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": wl + ": " + W["desc"], "envs_per_gpu": E, "agents_per_env": A,
-                       "l2": "inputs larger than L2: ring of %d independent env batches, %.0f MB resident per GPU"
-                             % (R, R * batch_bytes / 1e6),
-                       "launch": "one CUDA graph of K steps" if graph is not None else "one C-ABI call per step from Python",
-                       "parallelism": "envs sharded over %d GPU(s), no data-path collective" % world,
-                       "state": "fp32 SoA state, fp64 predicates (dtype = arithmetic of the decision path)"},
+            "reps": reps, "timed_region_ms": ms, "ms_per_step": ms / (K * reps), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": cfgd,
+            "run": {"ring_batches": R, "resident_MB_per_gpu": R * batch_bytes / 1e6,
+                    "launch": "one CUDA graph of K steps" if graph is not None else "one C-ABI call per step from Python",
+                    "collective_in_timed_region": ("all_reduce(SUM) of the [8] statistics row of every step, side stream, "
+                                                   + ("NCCL over %d ranks" % world if world > 1 else "1 rank: stream fork/join only"))
+                    if collective else "off (--no-collective / --no-stats)",
+                    "ga3c_forward": ("bf16 tcgen05" if use_tc else "fp32") if wl == "c5" else None},
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": Ke, "call": "casim_step_host via BatchedSim.bind_host_step (blocking, pinned host buffers; scalars zero-copy)"},
-            "gpu_launches": launches_per_step * K,
-            "roofline": roofline_obj(wl, kern, dominant, step_s, sum(v[1] for k, v in kern.items() if not k.startswith("k_ga3c")), explore_counts),
+                    "steps": Ke, "call": e2e_call},
+            "gpu_launches": launches_per_step * K * reps,
+            "roofline": roofline_obj(wl, kern, dominant, step_s,
+                                     sum(v[1] for k, v in kern.items() if not k.startswith("k_ga3c")),
+                                     sum(v[3] for k, v in kern.items() if not k.startswith("k_ga3c")), explore_counts),
             "clocks": dict(sampler.summary(t_load0, t_load1), sampled_over="timed region + 1.2 s of the same workload"),
-            "episode_stats_last_step": stats,
+            "episode_stats": episode,
         }
         if not args.no_cpu_baseline:
             threads = min(os.cpu_count() or 1, 64)
-            Es = REF_SAMPLE_ENVS[wl]
+            Es = min(REF_SAMPLE_ENVS[wl], E)
             n_steps = 100 if wl == "c2" else 20
-            v, sps = oracle_run(wl, Es, A, n_steps, 2, threads)
-            line["cpu_baseline"] = {"value": v, "unit": "agent-steps/s", "cores": threads, "kind": "port",
-                                    "sample": "%d steps of %d envs x %d agents, oracle/casim_oracle.c with %d POSIX threads"
-                                              % (n_steps, Es, A, threads)}
+            v, sps = oracle_run(wl, Es, A, n_steps, 2, threads, per_env_maps=per_env_maps)
+            line["cpu_baseline"] = cpu_baseline_obj(wl, v, threads, "%d steps of %d envs x %d agents, oracle/casim_oracle.c with %d POSIX threads"
+                                                    % (n_steps, Es, A, threads))
         emit(line)
     for s in sims:
         s.close()

@@ -256,7 +256,9 @@ class BatchedCollisionAvoidanceEnv:
             if self._ga3c_weights is None:
                 raise RuntimeError("GA3CCADRLPolicy agents need set_ga3c_weights() (random-init or a loaded checkpoint)")
             sim.ga3c_set_weights(self._ga3c_weights)
-        sim.reset(init, types, n)
+        # generator path: hand the device tensors themselves to the library (it borrows them; reset_done_envs
+        # regenerates their rows in place)
+        sim.reset(init, self._gen_out[1] if self._generator is not None else types, n)
         self._types = types
         if self._has_ig and getattr(self, "_mcts_params", None) is not None:
             from .mcts import TeamPlanner
