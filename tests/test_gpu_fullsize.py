@@ -126,10 +126,12 @@ def test_c5_full_size_per_gpu(oracle_lib):
     p32 = sim.buf["probs"].cpu().numpy()
     i32 = sim.buf["action_idx"].cpu().numpy()
     H.assert_close(sim.buf["nn_input"].cpu().numpy()[sel], o["nn_input"], "nn_input", rtol=1e-6, atol=1e-6)
-    assert np.abs(p32[sel] - o["probs"]).max() < 2e-5
+    act = o["action_idx"] >= 0                      # finished agents are not queried (collision_avoidance_env.py:298-300)
+    assert np.array_equal(i32[sel] >= 0, act) and act.mean() > 0.5
+    assert np.abs(p32[sel][act] - o["probs"][act]).max() < 2e-5
     srt = np.sort(o["probs"], axis=-1)
-    dec = (srt[..., -1] - srt[..., -2]) > 1e-4
-    assert np.array_equal(i32[sel][dec], o["action_idx"][dec]) and dec.mean() > 0.9
+    dec = act & ((srt[..., -1] - srt[..., -2]) > 1e-4)
+    assert np.array_equal(i32[sel][dec], o["action_idx"][dec]) and dec.sum() > 0.5 * act.sum()
     # ---- tensor-core forward on the same states ----
     sim.ga3c_forward(use_tensor_cores=True)
     torch.cuda.synchronize()
@@ -146,16 +148,19 @@ def test_c5_full_size_per_gpu(oracle_lib):
         s2.state.copy_(sim.state[:, lo:hi])
         s2.ga3c_forward(use_tensor_cores=True)
         torch.cuda.synchronize()
-        assert torch.equal(s2.buf["probs"], ptc[lo:hi])
         assert torch.equal(s2.buf["action_idx"], itc[lo:hi])
+        lv = itc[lo:hi] >= 0                                   # probabilities are written for the queried agents only
+        assert torch.equal(s2.buf["probs"][lv], ptc[lo:hi][lv])
         assert torch.equal(s2.buf["policy_actions"], atc[lo:hi])
         s2.close()
     ptc = ptc.cpu().numpy()
     itc = itc.cpu().numpy()
     import test_gpu_ga3c as TG
-    assert np.abs(ptc - p32).max() < TG.TC_PROB_TOL
+    live = i32 >= 0
+    assert np.array_equal(itc >= 0, live)
+    assert np.abs(ptc[live] - p32[live]).max() < TG.TC_PROB_TOL
     srt = np.sort(p32, axis=-1)
-    dec = (srt[..., -1] - srt[..., -2]) > TG.TC_MIN_MARGIN
+    dec = live & ((srt[..., -1] - srt[..., -2]) > TG.TC_MIN_MARGIN)
     assert np.array_equal(itc[dec], i32[dec])
-    assert (itc == i32).mean() >= TG.TC_MIN_AGREE
+    assert (itc[live] == i32[live]).mean() >= TG.TC_MIN_AGREE
     sim.close()
