@@ -227,6 +227,8 @@ int casim_destroy(casim_handle* h) {
   cudaFree(h->edf);
   cudaFree(h->edf_scratch);
   cudaFree(h->grid_maps);
+  cudaFree(h->grid2_map);
+  cudaFree(h->grid_work);
   cudaFree(h->ga3c_w);
   cudaFree(h->ga3c_wb);
   cudaFree(h->ga3c_x);
@@ -262,6 +264,12 @@ static int ensure_maps(casim_handle* h, int n_maps) {
   CK(cudaMalloc((void**)&h->edf, (size_t)n_maps * CASIM_MAP_DIM * CASIM_MAP_DIM * sizeof(double)));
   CK(cudaMalloc((void**)&h->edf_scratch, (size_t)n_maps * CASIM_MAP_DIM * CASIM_MAP_DIM * sizeof(int32_t)));
   CK(cudaMalloc((void**)&h->grid_maps, (size_t)n_maps * CASIM_GMAP_WORDS * sizeof(uint32_t)));
+  if (!h->grid2_map) {
+    CK(cudaMalloc((void**)&h->grid2_map, CASIM_G2_BYTES));
+    CK(cudaMalloc((void**)&h->grid_work, 2 * sizeof(unsigned int)));
+    CK(cudaMemset(h->grid_work, 0, 2 * sizeof(unsigned int)));
+    h->grid2_ready = 0;
+  }
   h->n_maps_alloc = n_maps;
   return 0;
 }
@@ -298,6 +306,13 @@ int casim_set_map(casim_handle* h, const uint8_t* static_map, int n_maps, void* 
   CK(casim_launch_pack_map(h, static_map, n_maps, s));
   CK(casim_launch_map_derive(h, n_maps, nullptr, s));
   h->n_maps = n_maps;
+  return 0;
+}
+
+int casim_set_grid_packed_output(casim_handle* h, uint8_t* packed) {
+  REQUIRE(h, "null handle");
+  REQUIRE((((uintptr_t)packed) & 1) == 0, "packed local_grid buffer must be 2-byte aligned");
+  h->grid_packed = packed;
   return 0;
 }
 

@@ -28,6 +28,25 @@
 #define CASIM_GPLANE_WORDS (CASIM_GROWS * CASIM_GWORDS)
 #define CASIM_GMAP_WORDS (CASIM_NUM_PLANES * CASIM_GPLANE_WORDS + CASIM_GROWS * CASIM_GCLS_WORDS)
 
+/* OccupancyGrid shared-map path (casim_sensors.cu k_grid_tma): ONE map padded by CASIM_G2_PAD cells on every side, laid
+ * out so that a persistent CTA stages all of it into shared memory with TMA tile loads:
+ *   4 footprint bit planes [384 rows][12 words]  (73 728 B)
+ *   1 classification byte per EVEN anchor [192][192] (36 864 B): what the 8x8 box of plane 0 anchored there holds --
+ *     bits 0-2: 0 other, 1 all free, 2 all occupied, 3 columns >= p occupied, 4 columns < p occupied, 5 rows >= p occupied,
+ *     6 rows < p occupied (every row / column of the box identical); bits 3-5: p (1..7, relative to the anchor).
+ * Seen as a 2-D tensor of 48-byte rows (12 uint32) it has 2304 rows; the kernel loads it as nine 256-row boxes. */
+#define CASIM_G2_PAD 42
+#define CASIM_G2_DIM (CASIM_MAP_DIM + 2 * CASIM_G2_PAD) /* 384 */
+#define CASIM_G2_WORDS 12
+#define CASIM_G2_PLANE_WORDS (CASIM_G2_DIM * CASIM_G2_WORDS)
+#define CASIM_G2_CLS_DIM (CASIM_G2_DIM / 2)
+#define CASIM_G2_CLS_BYTES (CASIM_G2_CLS_DIM * CASIM_G2_CLS_DIM)
+#define CASIM_G2_BYTES (CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS * 4 + CASIM_G2_CLS_BYTES) /* 110 592 */
+#define CASIM_G2_ROW_BYTES (CASIM_G2_WORDS * 4)
+#define CASIM_G2_ROWS (CASIM_G2_BYTES / CASIM_G2_ROW_BYTES) /* 2304 */
+#define CASIM_G2_BOX_ROWS 256
+#define CASIM_G2_BOXES (CASIM_G2_ROWS / CASIM_G2_BOX_ROWS) /* 9 */
+
 /* Derived, device-side view of casim_config (thresholds stay doubles: predicates are fp64). */
 struct DevCfg {
   double dt, dt_nominal;
@@ -64,6 +83,11 @@ struct casim_handle {
   int32_t* edf_scratch;    /* [n_maps_alloc][300][300] column pass */
   uint32_t* grid_maps;     /* [n_maps_alloc][CASIM_GMAP_WORDS]: 4 padded planes then the classification plane */
   int n_maps_alloc;
+  uint32_t* grid2_map;     /* [CASIM_G2_BYTES] shared-map layout of map 0 for k_grid_tma (built when n_maps == 1) */
+  alignas(64) unsigned char grid2_tmap[128]; /* CUtensorMap over grid2_map (driver-encoded, passed as a kernel parameter) */
+  int grid2_ready;         /* tensor map encoded for the current grid2_map */
+  unsigned int* grid_work; /* [2] self-resetting work counter + finished-warp counter of the persistent k_grid_tma */
+  uint8_t* grid_packed;    /* caller's optional bit-packed local_grid buffer (casim_set_grid_packed_output) or NULL */
   /* borrowed from the caller (casim_reset / casim_set_trajectories) */
   const float* init;
   const int32_t* type0;
@@ -104,6 +128,7 @@ cudaError_t casim_launch_raster(casim_handle* h, const float* rects, const int32
                                 int max_rects, cudaStream_t s);
 cudaError_t casim_launch_pack_map(casim_handle* h, const uint8_t* static_map, int n_maps, cudaStream_t s);
 cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_out, cudaStream_t s);
+cudaError_t casim_grid2_encode_tmap(casim_handle* h);
 cudaError_t casim_launch_explore(casim_handle* h, const float* state, const float* oas, float* belief,
                                  float* policy_actions, float* best_mi, float* cand_mi,
                                  unsigned long long* counters, cudaStream_t s);

@@ -128,6 +128,68 @@ __global__ void k_grid_classify(int n_maps, uint32_t* gmaps) {
   gmaps[(size_t)m * CASIM_GMAP_WORDS + CASIM_NUM_PLANES * CASIM_GPLANE_WORDS + r] = out;
 }
 
+/* Shared-map layout of k_grid_tma: the four footprint planes of map 0, padded by CASIM_G2_PAD (= 32 + 10) cells.
+ * Padded word pw of a row holds padded columns 32 pw .. 32 pw + 31 = map columns 32 (pw - 2) + 22 ...: a funnel shift
+ * of map words pw - 2 and pw - 1. */
+__global__ void k_grid2_planes(const uint32_t* planes, uint32_t* g2) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS) return;
+  int pl = i / CASIM_G2_PLANE_WORDS, q = i - pl * CASIM_G2_PLANE_WORDS;
+  int pr = q / CASIM_G2_WORDS, pw = q - pr * CASIM_G2_WORDS;
+  int row = pr - CASIM_G2_PAD;
+  const int c0 = 32 * pw - CASIM_G2_PAD;                  /* map column of bit 0 */
+  const int wi = (c0 >= 0 ? c0 : c0 - 31) / 32, sh = c0 - 32 * wi; /* floor division */
+  uint32_t v = 0;
+  if (row >= 0 && row < CASIM_MAP_DIM) {
+    const uint32_t* src = planes + (size_t)pl * CASIM_PLANE_WORDS + row * CASIM_MAP_WORDS;
+    uint32_t lo = (wi >= 0 && wi < CASIM_MAP_WORDS) ? src[wi] : 0u;
+    uint32_t hi = (wi + 1 >= 0 && wi + 1 < CASIM_MAP_WORDS) ? src[wi + 1] : 0u;
+    v = __funnelshift_r(lo, hi, sh);
+  }
+  g2[i] = v;
+}
+
+/* One classification byte per even anchor (see casim_internal.h): the 8x8 box of padded plane 0 anchored at
+ * (2 ay2, 2 ax2); cells beyond the padded array count as free. */
+__global__ void k_grid2_classify(uint32_t* g2) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= CASIM_G2_CLS_BYTES) return;
+  const int ay = 2 * (i / CASIM_G2_CLS_DIM), ax = 2 * (i % CASIM_G2_CLS_DIM);
+  uint32_t rows[8];
+  uint32_t all_or = 0, all_and = 0xffu, colpat = 0;
+  bool rows_equal = true, rows_solid = true;
+  for (int j = 0; j < 8; j++) {
+    uint32_t bits = 0;
+    const int rr = ay + j;
+    if (rr < CASIM_G2_DIM) {
+      const int w = ax >> 5, sh = ax & 31;
+      uint32_t lo = g2[rr * CASIM_G2_WORDS + w];
+      uint32_t hi = (w + 1 < CASIM_G2_WORDS) ? g2[rr * CASIM_G2_WORDS + w + 1] : 0u;
+      bits = __funnelshift_r(lo, hi, sh) & 0xffu;
+    }
+    rows[j] = bits;
+    all_or |= bits;
+    all_and &= bits;
+    rows_equal = rows_equal && bits == rows[0];
+    rows_solid = rows_solid && (bits == 0u || bits == 0xffu);
+    colpat |= (bits != 0u ? 1u : 0u) << j;
+  }
+  uint32_t code = 0;
+  if (all_or == 0u)
+    code = 1;
+  else if (all_and == 0xffu)
+    code = 2;
+  else {
+    const uint32_t pat = rows_equal ? rows[0] : (rows_solid ? colpat : 0x100u);
+    const uint32_t base = rows_equal ? 3u : 5u;
+    for (uint32_t pp = 1; pp < 8; pp++) {
+      if (pat == ((0xffu << pp) & 0xffu)) code = base | (pp << 3);          /* columns / rows >= pp occupied */
+      if (pat == ((1u << pp) - 1u)) code = (base + 1u) | (pp << 3);         /* columns / rows <  pp occupied */
+    }
+  }
+  reinterpret_cast<uint8_t*>(g2 + CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS)[i] = (uint8_t)code;
+}
+
 /* pass 1: per column, distance (in cells) to the nearest occupied cell in that column (big = none) */
 __global__ void k_edt_cols(int n_maps, const uint32_t* planes, int* gdist) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -204,6 +266,13 @@ cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_ou
     h->launches += 2;
     k_grid_pad<<<(tp + 255) / 256, 256, 0, s>>>(n_maps, h->map_planes, h->grid_maps);
     k_grid_classify<<<(tc + 127) / 128, 128, 0, s>>>(n_maps, h->grid_maps);
+    err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+  }
+  if (n_maps == 1 && h->grid2_map) { /* shared-map layout for the TMA-staged occupancy-grid kernel */
+    h->launches += 2;
+    k_grid2_planes<<<(CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS + 255) / 256, 256, 0, s>>>(h->map_planes, h->grid2_map);
+    k_grid2_classify<<<(CASIM_G2_CLS_BYTES + 255) / 256, 256, 0, s>>>(h->grid2_map);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
   }

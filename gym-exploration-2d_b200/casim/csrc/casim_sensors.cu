@@ -14,6 +14,8 @@
  * Both read the fp64 post-move pose scratch written by the step kernel (pose64), so that their cell
  * indices are computed from the same float64 numbers the reference would use inside one step.
  */
+#include <cuda.h>
+
 #include "casim_device.cuh"
 
 namespace {
@@ -232,7 +234,7 @@ __global__ void __launch_bounds__(256) k_grid_generic(const GridArgs p) {
 
 
 /* ------------------------------------------------------------------------------------------------ */
-/* k_grid: one WARP per agent, three phases.
+/* k_grid_gather (per-env maps; the shared-map case runs k_grid_tma below): one WARP per agent, three phases.
  *   tables   per-row / per-column fixed-point terms of OpenCV's warpAffine (fp64, once per agent), biased by the
  *            96-cell padding of the fast-path planes so that no lookup needs a bounds check;
  *   phase 1  one lane per output word (4 cells of a destination row).  The source cells of the word lie between
@@ -262,7 +264,7 @@ __device__ __forceinline__ uint32_t grid_cell_exact(const uint32_t* __restrict__
   return (w >> (xi & 31)) & 1u;
 }
 
-__global__ void __launch_bounds__(32 * GRID_WARPS, GRID_MINB) k_grid(const GridArgs p) {
+__global__ void __launch_bounds__(32 * GRID_WARPS, GRID_MINB) k_grid_gather(const GridArgs p) {
   casim_pdl_enter();
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -426,6 +428,321 @@ __global__ void __launch_bounds__(32 * GRID_WARPS, GRID_MINB) k_grid(const GridA
   }
 }
 
+
+/* ------------------------------------------------------------------------------------------------ */
+/* k_grid_tma: OccupancyGridSensor for a map SHARED by all environments (n_maps == 1).
+ *
+ * Persistent kernel, one CTA per SM.  The CTA first stages the WHOLE padded map -- four footprint bit planes and one
+ * classification byte per even anchor, 110 592 B (casim_internal.h CASIM_G2_*) -- into shared memory with nine TMA tile
+ * loads (cp.async.bulk.tensor.2d on one mbarrier), issued before the programmatic-dependent-launch wait so that they
+ * overlap the tail of the preceding kernel.  From then on no map lookup leaves the SM.  Warps then pull agents off a
+ * global work counter (dynamic: agents near obstacle corners cost more) and produce each agent's grid in three passes:
+ *   tables   the per-row / per-column fixed-point terms of OpenCV's warpAffine (fp64, once per agent);
+ *   pass 1   one lane per 4x4 destination TILE.  Its source cells lie in the 8x8 box anchored at the even cell below the
+ *            component-wise minimum of its corner cells (the per-axis terms are monotone and a tile spans < 5 cells per
+ *            axis).  The box's classification byte says: all free / all occupied -> 4 words written at once; a single
+ *            straight edge (every row, or every column, of the box identical) -> queued as an EDGE tile; else queued
+ *            as OTHER;
+ *   pass 2   edge tiles, one lane per 4-cell word: with an axis-aligned edge a cell's value is ONE comparison of its
+ *            own fixed-point coordinate with the edge (footprint max column >= edge, or min column < edge, resp. rows) --
+ *            exact, no lookup;
+ *   pass 3   other tiles (corners, thin walls, noise): exact per-cell lookup in the footprint plane chosen by (fx>0, fy>0);
+ *   copy-out the grid leaves shared memory as 16-byte coalesced stores (+ optional np.packbits form, 2 bytes per lane).
+ * Maps are unions of rectangles (Map.get_occupancy_grid), so nearly every non-uniform tile is an edge tile; the result
+ * is exact for ANY map.  Agents whose rotated window leaves the padded planes (within ~1 cell of the map border, or off
+ * the map) take a bounds-checked per-cell path on the unpadded plane 0 in global memory. */
+#ifndef G2_WARPS
+#define G2_WARPS 16
+#endif
+#define G2_THREADS (32 * G2_WARPS)
+#define G2_OUT_BYTES 4096
+#define G2_WARP_BYTES (G2_OUT_BYTES + 64 * 8 + 64 * 4 + 64 * 4 + 16 * 8 + 256 * 4) /* out, s_r, s_cx, s_cy, s_rmin, queue */
+#define G2_SMEM_BYTES (CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES + 16)
+
+struct Grid2Args {
+  DevCfg c;
+  const float4* state;
+  const double* pose64;
+  const int32_t* n_agents;
+  const uint32_t* map_planes; /* unpadded plane 0 (slow path) */
+  uint8_t* out;
+  uint8_t* packed;            /* optional np.packbits form, or NULL */
+  unsigned int* work;         /* [0] next agent, [1] warps that ran dry */
+  int E, A;
+};
+
+__device__ __forceinline__ uint32_t g2_cell(const uint32_t* __restrict__ sp, int fx, int fy) {
+  /* fx, fy: biased source coordinates in 1/1024 cell (OpenCV's X0 + adelta, before the >> 5) */
+  const int xi = fx >> 10, yi = fy >> 10;
+  const int plane = ((fx & 0x3E0) ? CASIM_G2_PLANE_WORDS : 0) + ((fy & 0x3E0) ? 2 * CASIM_G2_PLANE_WORDS : 0);
+  const uint32_t w = sp[plane + yi * CASIM_G2_WORDS + (xi >> 5)];
+  return (w >> (xi & 31)) & 1u;
+}
+
+__global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constant__ CUtensorMap tmap, const Grid2Args p) {
+  extern __shared__ __align__(128) uint8_t g2_smem[];
+  uint32_t* s_map = reinterpret_cast<uint32_t*>(g2_smem);
+  const uint8_t* s_cls = g2_smem + CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS * 4;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  uint8_t* wbase = g2_smem + CASIM_G2_BYTES + wid * G2_WARP_BYTES;
+  uint32_t* out32 = reinterpret_cast<uint32_t*>(wbase);
+  int2* s_r = reinterpret_cast<int2*>(wbase + G2_OUT_BYTES);
+  int* s_cx = reinterpret_cast<int*>(wbase + G2_OUT_BYTES + 512);
+  int* s_cy = s_cx + 64;
+  int2* s_rmin = reinterpret_cast<int2*>(wbase + G2_OUT_BYTES + 1024);
+  uint32_t* s_q = reinterpret_cast<uint32_t*>(wbase + G2_OUT_BYTES + 1024 + 128);
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(g2_smem + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES);
+
+  /* ---- stage the map: the loads do not depend on the preceding kernels, so they go out before the PDL wait ---- */
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)CASIM_G2_BYTES) : "memory");
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(g2_smem);
+#pragma unroll 1
+    for (int k = 0; k < CASIM_G2_BOXES; k++)
+      asm volatile(
+          "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+              dst + k * CASIM_G2_BOX_ROWS * CASIM_G2_ROW_BYTES),
+          "l"(&tmap), "r"(0), "r"(k * CASIM_G2_BOX_ROWS), "r"(bar)
+          : "memory");
+  }
+  casim_pdl_enter();
+  __syncthreads(); /* the barrier word is initialised for everybody */
+  {
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(bar), "r"(0u)
+          : "memory");
+    }
+  }
+
+  const DevCfg& c = p.c;
+  const unsigned N = (unsigned)p.E * (unsigned)p.A;
+  const int H = c.submap_h, W = c.submap_w; /* out[oy*H + ox]: W rows of H cells */
+  const int TW = H >> 2, TH = W >> 2;       /* 4x4 tiles */
+  const int cells = H * W;
+  const int BIAS = CASIM_G2_PAD << 10;
+  unsigned g = 0;
+  if (lane == 0) g = atomicAdd(&p.work[0], 1u);
+  g = __shfl_sync(FULL_MASK, g, 0);
+  while (g < N) {
+    unsigned gnext = 0;
+    if (lane == 0) gnext = atomicAdd(&p.work[0], 1u); /* the next ticket travels while this agent is computed */
+    const int e = (int)(g / (unsigned)p.A), ai = (int)(g - (unsigned)e * (unsigned)p.A);
+    const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+    uint4* gout = reinterpret_cast<uint4*>(p.out + (size_t)g * cells);
+    const int type = __float_as_int(p.state[5 * (size_t)N + g].w);
+    const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_OCCUPANCY_GRID);
+    if (!on) {
+      for (int i = lane; i < (cells >> 4); i += 32) gout[i] = make_uint4(0u, 0u, 0u, 0u);
+      if (p.packed) {
+        uint16_t* pk = reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3));
+        for (int i = lane; i < (cells >> 4); i += 32) pk[i] = 0;
+      }
+    } else {
+      const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)g)[0];
+      const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)g)[1];
+      const double px = q0.x, py = q0.y, ch = q1.x, sh = q1.y;
+      int row0, col0;
+      world_to_map_mul(c, px, py, row0, col0);
+      /* Map.getSubmapByIndices (Map.py:81-105) */
+      int sx = max(row0 - W / 2, 0), sy = max(col0 - H / 2, 0);
+      if (sx + W > CASIM_MAP_DIM - 1) sx = CASIM_MAP_DIM - 1 - W;
+      if (sy + H > CASIM_MAP_DIM - 1) sy = CASIM_MAP_DIM - 1 - H;
+      /* cv2.getRotationMatrix2D(center=(col0,row0), angle=-heading*180/pi, 1), inverted as in warpAffine */
+      double M0, M1, M2, M3, M4, M5;
+      {
+        double alpha = ch, beta = -sh;
+        double cx = (double)(float)col0, cy = (double)(float)row0;
+        M0 = alpha; M1 = beta; M2 = (1 - alpha) * cx - beta * cy;
+        M3 = -beta; M4 = alpha; M5 = beta * cx + (1 - alpha) * cy;
+        double D = M0 * M4 - M1 * M3;
+        D = D != 0 ? 1. / D : 0;
+        double A11 = M4 * D, A22 = M0 * D;
+        M0 = A11; M1 *= -D; M3 *= -D; M4 = A22;
+        double b1 = -M0 * M2 - M1 * M5, b2 = -M3 * M2 - M4 * M5;
+        M2 = b1; M5 = b2;
+      }
+      bool ok = true; /* every lookup stays inside the padded planes and every tile inside its 8x8 box */
+      for (int t = lane; t < 64; t += 32) {
+        double rxd = 0, ryd = 0, cxd = 0, cyd = 0;
+        if (t < W) {
+          int y = sx + t;
+          rxd = rint((M1 * y + M2) * 1024);
+          ryd = rint((M4 * y + M5) * 1024);
+        }
+        if (t < H) {
+          int x = sy + t;
+          cxd = rint(M0 * x * 1024);
+          cyd = rint(M3 * x * 1024);
+        }
+        ok = ok && fabs(rxd) < 5.0e8 && fabs(ryd) < 5.0e8 && fabs(cxd) < 5.0e8 && fabs(cyd) < 5.0e8;
+        s_r[t] = make_int2((int)rxd + 16 + BIAS, (int)ryd + 16 + BIAS);
+        s_cx[t] = (int)cxd;
+        s_cy[t] = (int)cyd;
+      }
+      __syncwarp();
+      int spx = 0, spy = 0;
+      if (lane < 4) { /* the four corner cells bound every source coordinate (monotone terms) */
+        const int oy = (lane & 1) ? W - 1 : 0, ox = (lane & 2) ? H - 1 : 0;
+        const int xi = (s_r[oy].x + s_cx[ox]) >> 10, yi = (s_r[oy].y + s_cy[ox]) >> 10;
+        ok = ok && xi >= 2 && yi >= 2 && xi <= CASIM_G2_DIM - 12 && yi <= CASIM_G2_DIM - 12;
+      }
+      if (lane < TH) { /* per tile row: minima of the row terms, and how far a tile reaches along each axis */
+        const int2 a = s_r[4 * lane], b = s_r[4 * lane + 3];
+        s_rmin[lane] = make_int2(min(a.x, b.x), min(a.y, b.y));
+        spx = abs(a.x - b.x);
+        spy = abs(a.y - b.y);
+      }
+      int cpx = 0, cpy = 0;
+      if (lane < TW) {
+        cpx = abs(s_cx[4 * lane] - s_cx[4 * lane + 3]);
+        cpy = abs(s_cy[4 * lane] - s_cy[4 * lane + 3]);
+      }
+      /* a tile's source cells span < 5 cells per axis (3 (|cos| + |sin|) <= 4.25 for a rotation): floor indices differ by
+       * at most 5, +1 for the bilinear footprint, +1 for the even anchor = the 8x8 box */
+      spx = __reduce_max_sync(FULL_MASK, spx) + __reduce_max_sync(FULL_MASK, cpx);
+      spy = __reduce_max_sync(FULL_MASK, spy) + __reduce_max_sync(FULL_MASK, cpy);
+      ok = __all_sync(FULL_MASK, ok) && max(spx, spy) < 5 * 1024;
+      __syncwarp();
+      if (!ok) {
+        /* rotated window partly outside the padded planes: per-cell path with bounds checks on the unpadded plane 0 */
+        const uint32_t* pl = p.map_planes;
+        auto S = [&](int r, int cc) -> uint32_t {
+          return (r >= 0 && r < CASIM_MAP_DIM && cc >= 0 && cc < CASIM_MAP_DIM) ? (uint32_t)map_bit(pl, r, cc) : 0u;
+        };
+        for (int wi = lane; wi < W * TW; wi += 32) {
+          const int oy = wi / TW, ox0 = (wi - oy * TW) << 2;
+          uint32_t word = 0;
+          for (int k = 0; k < 4; k++) {
+            long long Xl = ((long long)s_r[oy].x - BIAS + s_cx[ox0 + k]) >> 5;
+            long long Yl = ((long long)s_r[oy].y - BIAS + s_cy[ox0 + k]) >> 5;
+            int X = (int)Xl, Y = (int)Yl;
+            int sxi = X >> 5, syi = Y >> 5, fx = X & 31, fy = Y & 31;
+            uint32_t v = S(syi, sxi);
+            if (fx > 0) v |= S(syi, sxi + 1);
+            if (fy > 0) v |= S(syi + 1, sxi);
+            if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
+            word |= v << (8 * k);
+          }
+          out32[wi] = word;
+        }
+      } else {
+        /* ---- pass 1: classify the 4x4 tiles ---- */
+        const int rpi = 32 / TW; /* tile rows per iteration */
+        const int lr = lane / TW, tx = lane - lr * TW;
+        const bool act = lr < rpi;
+        const int cmx = min(s_cx[4 * tx], s_cx[4 * tx + 3]), cmy = min(s_cy[4 * tx], s_cy[4 * tx + 3]);
+        int nedge = 0, nother = 0;
+        for (int ty0 = 0; ty0 < TH; ty0 += rpi) {
+          const int ty = ty0 + lr;
+          const bool valid = act && ty < TH;
+          uint32_t code = 1u, anchor = 0u;
+          if (valid) {
+            const int2 rm = s_rmin[ty];
+            const int xh = (rm.x + cmx) >> 11, yh = (rm.y + cmy) >> 11; /* even anchor / 2 */
+            code = s_cls[yh * CASIM_G2_CLS_DIM + xh];
+            anchor = ((uint32_t)xh << 14) | ((uint32_t)yh << 22);
+          }
+          const uint32_t kind = code & 7u;
+          if (valid && (kind == 1u || kind == 2u)) {
+            const uint32_t word = kind == 2u ? 0x01010101u : 0u;
+            uint32_t* o = out32 + (4 * ty) * TW + tx;
+            o[0] = word;
+            o[TW] = word;
+            o[2 * TW] = word;
+            o[3 * TW] = word;
+          }
+          const bool edge = valid && kind >= 3u, other = valid && kind == 0u;
+          const unsigned be = __ballot_sync(FULL_MASK, edge), bo = __ballot_sync(FULL_MASK, other);
+          const unsigned below = (1u << lane) - 1u;
+          const uint32_t entry = (uint32_t)ty | ((uint32_t)tx << 4) | ((code & 0x3Fu) << 8) | anchor;
+          if (edge) s_q[nedge + __popc(be & below)] = entry;
+          if (other) s_q[255 - (nother + __popc(bo & below))] = entry;
+          nedge += __popc(be);
+          nother += __popc(bo);
+        }
+        __syncwarp();
+        /* ---- pass 2: edge tiles, one lane per word: a comparison per cell ---- */
+        for (int m = lane; m < 4 * nedge; m += 32) {
+          const uint32_t en = s_q[m >> 2];
+          const int oy = 4 * (int)(en & 15u) + (m & 3), wx = (int)((en >> 4) & 15u);
+          const uint32_t kind = (en >> 8) & 7u, pp = (en >> 11) & 7u;
+          const bool horiz = kind >= 5u, ge = (kind & 1u) != 0u; /* 3, 5: ">= p occupied"; 4, 6: "< p occupied" */
+          const int anc = 2 * (int)(horiz ? ((en >> 22) & 0xFFu) : ((en >> 14) & 0xFFu));
+          /* ge: footprint max index = (v + 992) >> 10 >= anc + p  <=>  v >= (anc + p) * 1024 - 992
+           * lt: footprint min index = v >> 10 < anc + p           <=>  v <  (anc + p) * 1024            */
+          const int thr = ((anc + (int)pp) << 10) - (ge ? 992 : 0);
+          const int2 r = s_r[oy];
+          const int t = thr - (horiz ? r.y : r.x);
+          const int4 cc = *reinterpret_cast<const int4*>((horiz ? s_cy : s_cx) + 4 * wx);
+          uint32_t word = (cc.x < t ? 1u : 0u) | (cc.y < t ? 0x100u : 0u) | (cc.z < t ? 0x10000u : 0u) | (cc.w < t ? 0x1000000u : 0u);
+          if (ge) word ^= 0x01010101u;
+          out32[oy * TW + wx] = word;
+        }
+        /* ---- pass 3: other tiles, exact per-cell lookups in the staged footprint planes ---- */
+        for (int m = lane; m < 4 * nother; m += 32) {
+          const uint32_t en = s_q[255 - (m >> 2)];
+          const int oy = 4 * (int)(en & 15u) + (m & 3), wx = (int)((en >> 4) & 15u);
+          const int2 r = s_r[oy];
+          const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * wx);
+          const int4 cy = *reinterpret_cast<const int4*>(s_cy + 4 * wx);
+          uint32_t word = g2_cell(s_map, r.x + cx.x, r.y + cy.x);
+          word |= g2_cell(s_map, r.x + cx.y, r.y + cy.y) << 8;
+          word |= g2_cell(s_map, r.x + cx.z, r.y + cy.z) << 16;
+          word |= g2_cell(s_map, r.x + cx.w, r.y + cy.w) << 24;
+          out32[oy * TW + wx] = word;
+        }
+      }
+      __syncwarp();
+      /* ---- copy-out: 16-byte coalesced stores (+ the np.packbits form: cell 0 in the most significant bit) ---- */
+      const uint4* so = reinterpret_cast<const uint4*>(out32);
+      uint16_t* pk = p.packed ? reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3)) : nullptr;
+      for (int i = lane; i < (cells >> 4); i += 32) {
+        const uint4 v = so[i];
+        gout[i] = v;
+        if (pk) { /* bytes b0..b3 of a word (0/1 each) -> nibble b0 b1 b2 b3: top 4 bits of w * (2^31 + 2^22 + 2^13 + 2^4) */
+          const uint32_t K = 0x80402010u;
+          const uint32_t b0 = ((v.x * K) >> 28 << 4) | ((v.y * K) >> 28), b1 = ((v.z * K) >> 28 << 4) | ((v.w * K) >> 28);
+          pk[i] = (uint16_t)(b0 | (b1 << 8));
+        }
+      }
+      __syncwarp(); /* the staging area is reused by the next agent */
+    }
+    g = __shfl_sync(FULL_MASK, gnext, 0);
+  }
+  /* the last warp to run dry re-arms the work counters for the next launch */
+  if (lane == 0) {
+    const unsigned total = gridDim.x * G2_WARPS;
+    if (atomicAdd(&p.work[1], 1u) == total - 1u) {
+      p.work[0] = 0u;
+      p.work[1] = 0u;
+      __threadfence();
+    }
+  }
+}
+
+/* np.packbits of the dense grids, for the kernels that do not emit it themselves (per-env maps, odd submap sizes) */
+__global__ void k_grid_pack(const uint8_t* __restrict__ dense, uint8_t* __restrict__ packed, size_t n_cells, int cells) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; /* one output byte */
+  const int per = (cells + 7) >> 3;
+  if (i >= (n_cells / cells) * (size_t)per) return;
+  const size_t ag = i / per;
+  const int b = (int)(i - ag * per);
+  uint32_t v = 0;
+  for (int k = 0; k < 8; k++) {
+    const int cidx = 8 * b + k;
+    v = (v << 1) | ((cidx < cells && dense[ag * cells + cidx]) ? 1u : 0u);
+  }
+  packed[i] = (uint8_t)v;
+}
+
 }  // namespace
 
 cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laserscan, cudaStream_t s) {
@@ -451,6 +768,37 @@ cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laser
   return casim_launch_pdl<LaserArgs>(k_laser, grid, block, 0, s, a);
 }
 
+/* The tensor map of the shared-map layout: a 2-D uint32 tensor of CASIM_G2_ROWS rows x 12 words, loaded in boxes of 256
+ * rows.  cuTensorMapEncodeTiled comes from the driver through the runtime's entry-point query (no -lcuda). */
+cudaError_t casim_grid2_encode_tmap(casim_handle* h) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (!encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess) return e;
+    if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+    encode = reinterpret_cast<EncodeFn>(fn);
+  }
+  static_assert(sizeof(CUtensorMap) <= sizeof(h->grid2_tmap), "tensor map does not fit its slot in the handle");
+  const cuuint64_t dims[2] = {CASIM_G2_WORDS, CASIM_G2_ROWS};
+  const cuuint64_t strides[1] = {CASIM_G2_ROW_BYTES};
+  const cuuint32_t box[2] = {CASIM_G2_WORDS, CASIM_G2_BOX_ROWS};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = encode(reinterpret_cast<CUtensorMap*>(h->grid2_tmap), CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, h->grid2_map, dims,
+                      strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    casim_set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
+    return cudaErrorInvalidValue;
+  }
+  h->grid2_ready = 1;
+  return cudaSuccess;
+}
+
 cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s) {
   if (h->dc.submap_w > 64 || h->dc.submap_h > 64) return cudaErrorInvalidValue;
   GridArgs a;
@@ -469,7 +817,53 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
   const int cells = h->dc.submap_w * h->dc.submap_h;
   /* fast path: rows are whole 4-cell words, every agent's grid is 16-byte aligned and a multiple of 16 bytes */
   const bool fast = (h->dc.submap_h & 3) == 0 && (cells & 15) == 0 && (((uintptr_t)local_grid) & 15) == 0;
+  const bool tiles = fast && (h->dc.submap_w & 3) == 0 && N < (1ll << 31);
+  if (h->grid_packed && (cells & 15) != 0) return cudaErrorInvalidValue; /* casim_set_grid_packed_output's size rule */
+  cudaError_t err;
+  if (tiles && h->n_maps == 1 && h->grid2_map) {
+    /* shared map: persistent kernel, whole map staged into shared memory through TMA */
+    if (!h->grid2_ready) {
+      err = casim_grid2_encode_tmap(h);
+      if (err != cudaSuccess) return err;
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+      err = cudaFuncSetAttribute(k_grid_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G2_SMEM_BYTES);
+      if (err != cudaSuccess) return err;
+      attr_set = true;
+    }
+    Grid2Args b;
+    b.c = h->dc;
+    b.state = a.state;
+    b.pose64 = h->pose64;
+    b.n_agents = h->n_agents;
+    b.map_planes = h->map_planes;
+    b.out = local_grid;
+    b.packed = h->grid_packed;
+    b.work = h->grid_work;
+    b.E = h->E;
+    b.A = h->A;
+    const long long want = (N + G2_WARPS - 1) / G2_WARPS;
+    const int sms = h->num_sms > 0 ? h->num_sms : CASIM_NUM_SMS_FALLBACK;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(want < sms ? want : sms));
+    cfg.blockDim = dim3(G2_THREADS);
+    cfg.dynamicSmemBytes = G2_SMEM_BYTES;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = casim_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, k_grid_tma, *reinterpret_cast<const CUtensorMap*>(h->grid2_tmap), b);
+  }
   if (fast)
-    return casim_launch_pdl<GridArgs>(k_grid, dim3((unsigned)((N + GRID_WARPS - 1) / GRID_WARPS)), dim3(32 * GRID_WARPS), 0, s, a);
-  return casim_launch_pdl<GridArgs>(k_grid_generic, dim3((unsigned)N), dim3(256), 0, s, a);
+    err = casim_launch_pdl<GridArgs>(k_grid_gather, dim3((unsigned)((N + GRID_WARPS - 1) / GRID_WARPS)), dim3(32 * GRID_WARPS), 0, s, a);
+  else
+    err = casim_launch_pdl<GridArgs>(k_grid_generic, dim3((unsigned)N), dim3(256), 0, s, a);
+  if (err != cudaSuccess || !h->grid_packed) return err;
+  h->launches++;
+  const size_t nbytes = (size_t)N * ((cells + 7) >> 3);
+  k_grid_pack<<<(unsigned)((nbytes + 255) / 256), 256, 0, s>>>(local_grid, h->grid_packed, (size_t)N * cells, cells);
+  return cudaGetLastError();
 }

@@ -136,6 +136,21 @@ class BatchedSim:
         torch.cuda.current_stream().synchronize()
         self.has_map = True
 
+    def enable_packed_grid(self, on=True):
+        """Second delivery format of ``local_grid`` (casim_set_grid_packed_output): ``buf['local_grid_packed']``
+        uint8 [E, A, w*h/8] = numpy.packbits of every agent's grid, written by every later step next to the dense form."""
+        if not on:
+            _lib.check(self.lib.casim_set_grid_packed_output(self.handle, None), "casim_set_grid_packed_output")
+            self.buf["local_grid_packed"] = None
+            return None
+        cells = self.cfg.submap_w * self.cfg.submap_h
+        if self.cfg.submap_w % 4 or self.cfg.submap_h % 4:
+            raise _lib.CasimError("packed local_grid needs submap sides that are multiples of 4")
+        t = torch.zeros((self.E, self.A, cells // 8), dtype=torch.uint8, device=self.device)
+        _lib.check(self.lib.casim_set_grid_packed_output(self.handle, _lib.ptr(t)), "casim_set_grid_packed_output")
+        self.buf["local_grid_packed"] = t
+        return t
+
     def set_trajectories(self, traj):
         """traj: [E,A,T,4] (pose_x, pose_y, vel_x, vel_y) for ExternalDynamics agents."""
         if traj is None:

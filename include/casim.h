@@ -198,6 +198,14 @@ int casim_set_obstacles(casim_handle* h, const float* rects, const int32_t* n_re
 /* Same, from a ready-made occupancy raster [n_maps,300,300] uint8 (Map.static_map). */
 int casim_set_map(casim_handle* h, const uint8_t* static_map, int n_maps, void* stream);
 
+/* Optional second delivery format of the OccupancyGrid observation (OccupancyGridSensor.py:98 returns a bool array):
+ * when `packed` is non-NULL every later casim_step / casim_reset / casim_observe ALSO writes each agent's grid bit-packed,
+ * ceil(submap_w*submap_h/8) bytes per agent = numpy.packbits(local_grid[e,a].ravel()) (first cell in the most significant
+ * bit), into packed [E,A,ceil(w*h/8)] (device pointer, 2-byte aligned, borrowed).  1/8 of the bytes of the dense uint8
+ * form: what a host consumer should pull over PCIe (casim_step_host_pipelined).  Needs submap_w and submap_h to be
+ * multiples of 4.  NULL turns it off.  The dense local_grid buffer stays the parity format and is always written. */
+int casim_set_grid_packed_output(casim_handle* h, uint8_t* packed);
+
 /* Trajectory tables for ExternalDynamics (dynamics/ExternalDynamics.py:11-20): traj [E,A,T,4] =
  * (pose_x, pose_y, vel_x, vel_y).  The pointer is borrowed until replaced. */
 int casim_set_trajectories(casim_handle* h, const float* traj, int T);
