@@ -82,7 +82,37 @@ __global__ void k_derive(int n_maps, uint32_t* planes, uint8_t* map_out) {
   }
 }
 
-/* OccupancyGrid fast path: zero-padded copies of the four footprint planes (pad = 96 cells = 3 words) */
+/* Word `pw` of padded row `pr` of plane 0 (S) of one map, for a padding of PAD cells on every side: padded column
+ * 32 pw + b = map column 32 pw + b - PAD; cells outside the map are free. */
+template <int PAD>
+__device__ __forceinline__ uint32_t padded_s_word(const uint32_t* p0, int pr, int pw, int rows, int words) {
+  const int row = pr - PAD;
+  if (pr < 0 || pr >= rows || pw < 0 || pw >= words || row < 0 || row >= CASIM_MAP_DIM) return 0u;
+  const int c0 = 32 * pw - PAD;
+  const int wi = (c0 >= 0 ? c0 : c0 - 31) / 32, sh = c0 - 32 * wi; /* floor division */
+  const uint32_t* src = p0 + row * CASIM_MAP_WORDS;
+  const uint32_t lo = (wi >= 0 && wi < CASIM_MAP_WORDS) ? src[wi] : 0u;
+  const uint32_t hi = (wi + 1 >= 0 && wi + 1 < CASIM_MAP_WORDS) ? src[wi + 1] : 0u;
+  return sh ? __funnelshift_r(lo, hi, sh) : lo;
+}
+
+/* The four bilinear footprints {S}, {S, right}, {S, down}, {S, right, down, diagonal} of padded cell (pr, 32 pw + b),
+ * derived IN PADDED SPACE: the cells just outside the map (column -1, row -1) see the map's first column / row through
+ * their right / lower neighbour, which a padded copy of the unpadded footprint planes would lose. */
+template <int PAD>
+__device__ __forceinline__ uint32_t padded_footprint_word(const uint32_t* p0, int pl, int pr, int pw, int rows, int words) {
+  const uint32_t s = padded_s_word<PAD>(p0, pr, pw, rows, words);
+  if (pl == 0) return s;
+  const uint32_t sn = padded_s_word<PAD>(p0, pr, pw + 1, rows, words);
+  const uint32_t r = (s >> 1) | (sn << 31);
+  if (pl == 1) return s | r;
+  const uint32_t d = padded_s_word<PAD>(p0, pr + 1, pw, rows, words);
+  if (pl == 2) return s | d;
+  const uint32_t dn = padded_s_word<PAD>(p0, pr + 1, pw + 1, rows, words);
+  return s | r | d | ((d >> 1) | (dn << 31));
+}
+
+/* OccupancyGrid gather path (per-env maps): the four footprint planes padded by 96 cells = 3 words */
 __global__ void k_grid_pad(int n_maps, const uint32_t* planes, uint32_t* gmaps) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int per_map = CASIM_NUM_PLANES * CASIM_GPLANE_WORDS;
@@ -90,11 +120,8 @@ __global__ void k_grid_pad(int n_maps, const uint32_t* planes, uint32_t* gmaps) 
   int m = i / per_map, r = i - m * per_map;
   int pl = r / CASIM_GPLANE_WORDS, q = r - pl * CASIM_GPLANE_WORDS;
   int pr = q / CASIM_GWORDS, pw = q - pr * CASIM_GWORDS;
-  int row = pr - CASIM_GPAD, wc = pw - CASIM_GPAD / 32;
-  uint32_t v = 0;
-  if (row >= 0 && row < CASIM_MAP_DIM && wc >= 0 && wc < CASIM_MAP_WORDS)
-    v = planes[((size_t)m * CASIM_NUM_PLANES + pl) * CASIM_PLANE_WORDS + row * CASIM_MAP_WORDS + wc];
-  gmaps[(size_t)m * CASIM_GMAP_WORDS + r] = v;
+  const uint32_t* p0 = planes + (size_t)m * CASIM_NUM_PLANES * CASIM_PLANE_WORDS;
+  gmaps[(size_t)m * CASIM_GMAP_WORDS + r] = padded_footprint_word<CASIM_GPAD>(p0, pl, pr, pw, CASIM_GROWS, CASIM_GWORDS);
 }
 
 /* 2-bit classification of every anchor (padded row pr, padded col pc): over the box rows [pr, pr+6) x cols
@@ -128,25 +155,13 @@ __global__ void k_grid_classify(int n_maps, uint32_t* gmaps) {
   gmaps[(size_t)m * CASIM_GMAP_WORDS + CASIM_NUM_PLANES * CASIM_GPLANE_WORDS + r] = out;
 }
 
-/* Shared-map layout of k_grid_tma: the four footprint planes of map 0, padded by CASIM_G2_PAD (= 32 + 10) cells.
- * Padded word pw of a row holds padded columns 32 pw .. 32 pw + 31 = map columns 32 (pw - 2) + 22 ...: a funnel shift
- * of map words pw - 2 and pw - 1. */
+/* Shared-map layout of k_grid_tma: the four footprint planes of map 0, padded by CASIM_G2_PAD (= 32 + 10) cells */
 __global__ void k_grid2_planes(const uint32_t* planes, uint32_t* g2) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS) return;
   int pl = i / CASIM_G2_PLANE_WORDS, q = i - pl * CASIM_G2_PLANE_WORDS;
   int pr = q / CASIM_G2_WORDS, pw = q - pr * CASIM_G2_WORDS;
-  int row = pr - CASIM_G2_PAD;
-  const int c0 = 32 * pw - CASIM_G2_PAD;                  /* map column of bit 0 */
-  const int wi = (c0 >= 0 ? c0 : c0 - 31) / 32, sh = c0 - 32 * wi; /* floor division */
-  uint32_t v = 0;
-  if (row >= 0 && row < CASIM_MAP_DIM) {
-    const uint32_t* src = planes + (size_t)pl * CASIM_PLANE_WORDS + row * CASIM_MAP_WORDS;
-    uint32_t lo = (wi >= 0 && wi < CASIM_MAP_WORDS) ? src[wi] : 0u;
-    uint32_t hi = (wi + 1 >= 0 && wi + 1 < CASIM_MAP_WORDS) ? src[wi + 1] : 0u;
-    v = __funnelshift_r(lo, hi, sh);
-  }
-  g2[i] = v;
+  g2[i] = padded_footprint_word<CASIM_G2_PAD>(planes, pl, pr, pw, CASIM_G2_DIM, CASIM_G2_WORDS);
 }
 
 /* One classification byte per even anchor (see casim_internal.h): the 8x8 box of padded plane 0 anchored at

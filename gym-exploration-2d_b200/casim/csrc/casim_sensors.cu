@@ -452,11 +452,12 @@ __global__ void __launch_bounds__(32 * GRID_WARPS, GRID_MINB) k_grid_gather(cons
  * is exact for ANY map.  Agents whose rotated window leaves the padded planes (within ~1 cell of the map border, or off
  * the map) take a bounds-checked per-cell path on the unpadded plane 0 in global memory. */
 #ifndef G2_WARPS
-#define G2_WARPS 16
+#define G2_WARPS 32 /* 1024 threads, 64 registers: the kernel is latency-bound below ~8 warps per scheduler */
 #endif
 #define G2_THREADS (32 * G2_WARPS)
-#define G2_OUT_BYTES 4096
-#define G2_WARP_BYTES (G2_OUT_BYTES + 64 * 8 + 64 * 4 + 64 * 4 + 16 * 8 + 256 * 4) /* out, s_r, s_cx, s_cy, s_rmin, queue */
+#define G2_NIB_BYTES 1024 /* one nibble-byte per output word (4 cells, bit k = cell k); grids of up to 64 x 64 cells */
+/* per warp: nibbles, s_r[64] int2, s_cx[64], s_cy[64], s_rmin[16] int2, s_cmin[16] int2, queue[256] uint16 */
+#define G2_WARP_BYTES (G2_NIB_BYTES + 64 * 8 + 64 * 4 + 64 * 4 + 16 * 8 + 16 * 8 + 256 * 2)
 #define G2_SMEM_BYTES (CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES + 16)
 
 struct Grid2Args {
@@ -479,18 +480,32 @@ __device__ __forceinline__ uint32_t g2_cell(const uint32_t* __restrict__ sp, int
   return (w >> (xi & 31)) & 1u;
 }
 
+__device__ __forceinline__ void g2_wait_map(uint32_t bar) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(0u)
+        : "memory");
+  }
+}
+
 __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constant__ CUtensorMap tmap, const Grid2Args p) {
   extern __shared__ __align__(128) uint8_t g2_smem[];
-  uint32_t* s_map = reinterpret_cast<uint32_t*>(g2_smem);
+  const uint32_t* s_map = reinterpret_cast<const uint32_t*>(g2_smem);
   const uint8_t* s_cls = g2_smem + CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS * 4;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   uint8_t* wbase = g2_smem + CASIM_G2_BYTES + wid * G2_WARP_BYTES;
-  uint32_t* out32 = reinterpret_cast<uint32_t*>(wbase);
-  int2* s_r = reinterpret_cast<int2*>(wbase + G2_OUT_BYTES);
-  int* s_cx = reinterpret_cast<int*>(wbase + G2_OUT_BYTES + 512);
+  uint8_t* s_nib = wbase;
+  int2* s_r = reinterpret_cast<int2*>(wbase + G2_NIB_BYTES);
+  int* s_cx = reinterpret_cast<int*>(wbase + G2_NIB_BYTES + 512);
   int* s_cy = s_cx + 64;
-  int2* s_rmin = reinterpret_cast<int2*>(wbase + G2_OUT_BYTES + 1024);
-  uint32_t* s_q = reinterpret_cast<uint32_t*>(wbase + G2_OUT_BYTES + 1024 + 128);
+  int2* s_rmin = reinterpret_cast<int2*>(wbase + G2_NIB_BYTES + 1024);
+  int2* s_cmin = s_rmin + 16;
+  uint16_t* s_q = reinterpret_cast<uint16_t*>(wbase + G2_NIB_BYTES + 1024 + 256);
   const uint32_t bar = (uint32_t)__cvta_generic_to_shared(g2_smem + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES);
 
   /* ---- stage the map: the loads do not depend on the preceding kernels, so they go out before the PDL wait ---- */
@@ -509,18 +524,6 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
   }
   casim_pdl_enter();
   __syncthreads(); /* the barrier word is initialised for everybody */
-  {
-    uint32_t done = 0;
-    while (!done) {
-      asm volatile(
-          "{\n\t.reg .pred p;\n\t"
-          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-          "selp.u32 %0, 1, 0, p;\n\t}"
-          : "=r"(done)
-          : "r"(bar), "r"(0u)
-          : "memory");
-    }
-  }
 
   const DevCfg& c = p.c;
   const unsigned N = (unsigned)p.E * (unsigned)p.A;
@@ -528,9 +531,13 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
   const int TW = H >> 2, TH = W >> 2;       /* 4x4 tiles */
   const int cells = H * W;
   const int BIAS = CASIM_G2_PAD << 10;
+  const int rpi = 32 / TW;                  /* tile rows per pass-1 iteration */
+  const int lr = lane / TW, tx = lane - lr * TW;
+  const bool act = lr < rpi;
   unsigned g = 0;
   if (lane == 0) g = atomicAdd(&p.work[0], 1u);
   g = __shfl_sync(FULL_MASK, g, 0);
+  bool map_ready = false;
   while (g < N) {
     unsigned gnext = 0;
     if (lane == 0) gnext = atomicAdd(&p.work[0], 1u); /* the next ticket travels while this agent is computed */
@@ -588,7 +595,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         s_cy[t] = (int)cyd;
       }
       __syncwarp();
-      int spx = 0, spy = 0;
+      int spx = 0, spy = 0, cpx = 0, cpy = 0;
       if (lane < 4) { /* the four corner cells bound every source coordinate (monotone terms) */
         const int oy = (lane & 1) ? W - 1 : 0, ox = (lane & 2) ? H - 1 : 0;
         const int xi = (s_r[oy].x + s_cx[ox]) >> 10, yi = (s_r[oy].y + s_cy[ox]) >> 10;
@@ -600,10 +607,11 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         spx = abs(a.x - b.x);
         spy = abs(a.y - b.y);
       }
-      int cpx = 0, cpy = 0;
       if (lane < TW) {
-        cpx = abs(s_cx[4 * lane] - s_cx[4 * lane + 3]);
-        cpy = abs(s_cy[4 * lane] - s_cy[4 * lane + 3]);
+        const int ax = s_cx[4 * lane], bx = s_cx[4 * lane + 3], ay = s_cy[4 * lane], by = s_cy[4 * lane + 3];
+        s_cmin[lane] = make_int2(min(ax, bx), min(ay, by));
+        cpx = abs(ax - bx);
+        cpy = abs(ay - by);
       }
       /* a tile's source cells span < 5 cells per axis (3 (|cos| + |sin|) <= 4.25 for a rotation): floor indices differ by
        * at most 5, +1 for the bilinear footprint, +1 for the even anchor = the 8x8 box */
@@ -611,6 +619,10 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
       spy = __reduce_max_sync(FULL_MASK, spy) + __reduce_max_sync(FULL_MASK, cpy);
       ok = __all_sync(FULL_MASK, ok) && max(spx, spy) < 5 * 1024;
       __syncwarp();
+      if (!map_ready) { /* first agent of this warp: the staged map must have landed */
+        g2_wait_map(bar);
+        map_ready = true;
+      }
       if (!ok) {
         /* rotated window partly outside the padded planes: per-cell path with bounds checks on the unpadded plane 0 */
         const uint32_t* pl = p.map_planes;
@@ -619,7 +631,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         };
         for (int wi = lane; wi < W * TW; wi += 32) {
           const int oy = wi / TW, ox0 = (wi - oy * TW) << 2;
-          uint32_t word = 0;
+          uint32_t nib = 0;
           for (int k = 0; k < 4; k++) {
             long long Xl = ((long long)s_r[oy].x - BIAS + s_cx[ox0 + k]) >> 5;
             long long Yl = ((long long)s_r[oy].y - BIAS + s_cy[ox0 + k]) >> 5;
@@ -629,87 +641,83 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
             if (fx > 0) v |= S(syi, sxi + 1);
             if (fy > 0) v |= S(syi + 1, sxi);
             if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
-            word |= v << (8 * k);
+            nib |= v << k;
           }
-          out32[wi] = word;
+          s_nib[wi] = (uint8_t)nib;
         }
       } else {
-        /* ---- pass 1: classify the 4x4 tiles ---- */
-        const int rpi = 32 / TW; /* tile rows per iteration */
-        const int lr = lane / TW, tx = lane - lr * TW;
-        const bool act = lr < rpi;
-        const int cmx = min(s_cx[4 * tx], s_cx[4 * tx + 3]), cmy = min(s_cy[4 * tx], s_cy[4 * tx + 3]);
-        int nedge = 0, nother = 0;
+        /* ---- pass 1: classify the 4x4 tiles; uniform ones are done, the others are queued with their code ---- */
+        const int2 cm = s_cmin[act ? tx : 0];
+        int nq = 0;
         for (int ty0 = 0; ty0 < TH; ty0 += rpi) {
           const int ty = ty0 + lr;
           const bool valid = act && ty < TH;
-          uint32_t code = 1u, anchor = 0u;
+          uint32_t code = 1u;
           if (valid) {
             const int2 rm = s_rmin[ty];
-            const int xh = (rm.x + cmx) >> 11, yh = (rm.y + cmy) >> 11; /* even anchor / 2 */
-            code = s_cls[yh * CASIM_G2_CLS_DIM + xh];
-            anchor = ((uint32_t)xh << 14) | ((uint32_t)yh << 22);
+            code = s_cls[((rm.y + cm.y) >> 11) * CASIM_G2_CLS_DIM + ((rm.x + cm.x) >> 11)]; /* even anchor / 2 */
           }
           const uint32_t kind = code & 7u;
-          if (valid && (kind == 1u || kind == 2u)) {
-            const uint32_t word = kind == 2u ? 0x01010101u : 0u;
-            uint32_t* o = out32 + (4 * ty) * TW + tx;
-            o[0] = word;
-            o[TW] = word;
-            o[2 * TW] = word;
-            o[3 * TW] = word;
+          const bool queued = kind != 1u && kind != 2u;
+          if (valid && !queued) {
+            const uint8_t nib = kind == 2u ? (uint8_t)0xF : (uint8_t)0;
+            uint8_t* o = s_nib + (4 * ty) * TW + tx;
+            o[0] = nib;
+            o[TW] = nib;
+            o[2 * TW] = nib;
+            o[3 * TW] = nib;
           }
-          const bool edge = valid && kind >= 3u, other = valid && kind == 0u;
-          const unsigned be = __ballot_sync(FULL_MASK, edge), bo = __ballot_sync(FULL_MASK, other);
-          const unsigned below = (1u << lane) - 1u;
-          const uint32_t entry = (uint32_t)ty | ((uint32_t)tx << 4) | ((code & 0x3Fu) << 8) | anchor;
-          if (edge) s_q[nedge + __popc(be & below)] = entry;
-          if (other) s_q[255 - (nother + __popc(bo & below))] = entry;
-          nedge += __popc(be);
-          nother += __popc(bo);
+          const unsigned bq = __ballot_sync(FULL_MASK, queued);
+          if (queued) s_q[nq + __popc(bq & ((1u << lane) - 1u))] = (uint16_t)(ty | (tx << 4) | (code << 8));
+          nq += __popc(bq);
         }
         __syncwarp();
-        /* ---- pass 2: edge tiles, one lane per word: a comparison per cell ---- */
-        for (int m = lane; m < 4 * nedge; m += 32) {
+        /* ---- pass 2: the queued tiles, one lane per 4-cell word.  EDGE tile (kinds 3-6: every row, or every column, of
+         * the 8x8 box identical): one comparison per cell, no lookup.  OTHER tile: exact per-cell lookups. ---- */
+        for (int m = lane; m < 4 * nq; m += 32) {
           const uint32_t en = s_q[m >> 2];
-          const int oy = 4 * (int)(en & 15u) + (m & 3), wx = (int)((en >> 4) & 15u);
+          const int qty = (int)(en & 15u), wx = (int)((en >> 4) & 15u);
+          const int oy = 4 * qty + (m & 3);
           const uint32_t kind = (en >> 8) & 7u, pp = (en >> 11) & 7u;
-          const bool horiz = kind >= 5u, ge = (kind & 1u) != 0u; /* 3, 5: ">= p occupied"; 4, 6: "< p occupied" */
-          const int anc = 2 * (int)(horiz ? ((en >> 22) & 0xFFu) : ((en >> 14) & 0xFFu));
-          /* ge: footprint max index = (v + 992) >> 10 >= anc + p  <=>  v >= (anc + p) * 1024 - 992
-           * lt: footprint min index = v >> 10 < anc + p           <=>  v <  (anc + p) * 1024            */
-          const int thr = ((anc + (int)pp) << 10) - (ge ? 992 : 0);
           const int2 r = s_r[oy];
-          const int t = thr - (horiz ? r.y : r.x);
-          const int4 cc = *reinterpret_cast<const int4*>((horiz ? s_cy : s_cx) + 4 * wx);
-          uint32_t word = (cc.x < t ? 1u : 0u) | (cc.y < t ? 0x100u : 0u) | (cc.z < t ? 0x10000u : 0u) | (cc.w < t ? 0x1000000u : 0u);
-          if (ge) word ^= 0x01010101u;
-          out32[oy * TW + wx] = word;
-        }
-        /* ---- pass 3: other tiles, exact per-cell lookups in the staged footprint planes ---- */
-        for (int m = lane; m < 4 * nother; m += 32) {
-          const uint32_t en = s_q[255 - (m >> 2)];
-          const int oy = 4 * (int)(en & 15u) + (m & 3), wx = (int)((en >> 4) & 15u);
-          const int2 r = s_r[oy];
-          const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * wx);
-          const int4 cy = *reinterpret_cast<const int4*>(s_cy + 4 * wx);
-          uint32_t word = g2_cell(s_map, r.x + cx.x, r.y + cy.x);
-          word |= g2_cell(s_map, r.x + cx.y, r.y + cy.y) << 8;
-          word |= g2_cell(s_map, r.x + cx.z, r.y + cy.z) << 16;
-          word |= g2_cell(s_map, r.x + cx.w, r.y + cy.w) << 24;
-          out32[oy * TW + wx] = word;
+          uint32_t nib;
+          if (kind >= 3u) {
+            const bool horiz = kind >= 5u, ge = (kind & 1u) != 0u; /* 3, 5: ">= p occupied"; 4, 6: "< p occupied" */
+            const int2 rm = s_rmin[qty], cmn = s_cmin[wx];
+            const int anc = ((horiz ? rm.y + cmn.y : rm.x + cmn.x) >> 11) << 1;
+            /* ge: footprint max index = (v + 992) >> 10 >= anc + p  <=>  v >= (anc + p) * 1024 - 992
+             * lt: footprint min index = v >> 10 < anc + p           <=>  v <  (anc + p) * 1024            */
+            const int t = ((anc + (int)pp) << 10) - (ge ? 992 : 0) - (horiz ? r.y : r.x);
+            const int4 cc = *reinterpret_cast<const int4*>((horiz ? s_cy : s_cx) + 4 * wx);
+            nib = (cc.x < t ? 1u : 0u) | (cc.y < t ? 2u : 0u) | (cc.z < t ? 4u : 0u) | (cc.w < t ? 8u : 0u);
+            if (ge) nib ^= 0xFu;
+          } else {
+            const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * wx);
+            const int4 cy = *reinterpret_cast<const int4*>(s_cy + 4 * wx);
+            nib = g2_cell(s_map, r.x + cx.x, r.y + cy.x);
+            nib |= g2_cell(s_map, r.x + cx.y, r.y + cy.y) << 1;
+            nib |= g2_cell(s_map, r.x + cx.z, r.y + cy.z) << 2;
+            nib |= g2_cell(s_map, r.x + cx.w, r.y + cy.w) << 3;
+          }
+          s_nib[oy * TW + wx] = (uint8_t)nib;
         }
       }
       __syncwarp();
-      /* ---- copy-out: 16-byte coalesced stores (+ the np.packbits form: cell 0 in the most significant bit) ---- */
-      const uint4* so = reinterpret_cast<const uint4*>(out32);
+      /* ---- copy-out: 16-byte coalesced stores (+ the np.packbits form: cell 0 in the most significant bit) ----
+       * nibble -> four 0/1 bytes: bit k of b lands on bit 8k of b * (1 + 2^7 + 2^14 + 2^21) */
+      const uint32_t* so = reinterpret_cast<const uint32_t*>(s_nib);
       uint16_t* pk = p.packed ? reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3)) : nullptr;
       for (int i = lane; i < (cells >> 4); i += 32) {
-        const uint4 v = so[i];
+        const uint32_t q = so[i];
+        uint4 v;
+        v.x = ((q & 0xFu) * 0x00204081u) & 0x01010101u;
+        v.y = (((q >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
+        v.z = (((q >> 16) & 0xFu) * 0x00204081u) & 0x01010101u;
+        v.w = (((q >> 24) & 0xFu) * 0x00204081u) & 0x01010101u;
         gout[i] = v;
-        if (pk) { /* bytes b0..b3 of a word (0/1 each) -> nibble b0 b1 b2 b3: top 4 bits of w * (2^31 + 2^22 + 2^13 + 2^4) */
-          const uint32_t K = 0x80402010u;
-          const uint32_t b0 = ((v.x * K) >> 28 << 4) | ((v.y * K) >> 28), b1 = ((v.z * K) >> 28 << 4) | ((v.w * K) >> 28);
+        if (pk) { /* 16 cells -> 2 bytes; a nibble holds cell k in bit k, packbits wants the first cell in the top bit */
+          const uint32_t rv = __brev(q); /* byte 3-j of rv = bit-reversed byte j of q: its top nibble = reversed nibble */
+          const uint32_t b0 = ((rv >> 28) << 4) | ((rv >> 20) & 0xFu), b1 = (((rv >> 12) & 0xFu) << 4) | ((rv >> 4) & 0xFu);
           pk[i] = (uint16_t)(b0 | (b1 << 8));
         }
       }
@@ -717,6 +725,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
     }
     g = __shfl_sync(FULL_MASK, gnext, 0);
   }
+  if (!map_ready) g2_wait_map(bar); /* nobody leaves while the bulk copies into this CTA's shared memory are in flight */
   /* the last warp to run dry re-arms the work counters for the next launch */
   if (lane == 0) {
     const unsigned total = gridDim.x * G2_WARPS;
