@@ -452,12 +452,12 @@ __global__ void __launch_bounds__(32 * GRID_WARPS, GRID_MINB) k_grid_gather(cons
  * is exact for ANY map.  Agents whose rotated window leaves the padded planes (within ~1 cell of the map border, or off
  * the map) take a bounds-checked per-cell path on the unpadded plane 0 in global memory. */
 #ifndef G2_WARPS
-#define G2_WARPS 32 /* 1024 threads, 64 registers: the kernel is latency-bound below ~8 warps per scheduler */
+#define G2_WARPS 32 /* 1024 threads, <= 64 registers: the kernel is latency-bound below ~8 warps per scheduler */
 #endif
 #define G2_THREADS (32 * G2_WARPS)
-#define G2_NIB_BYTES 1024 /* one nibble-byte per output word (4 cells, bit k = cell k); grids of up to 64 x 64 cells */
-/* per warp: nibbles, s_r[64] int2, s_cx[64], s_cy[64], s_rmin[16] int2, s_cmin[16] int2, queue[256] uint16 */
-#define G2_WARP_BYTES (G2_NIB_BYTES + 64 * 8 + 64 * 4 + 64 * 4 + 16 * 8 + 16 * 8 + 256 * 2)
+/* per warp: tiles[256] uint16 (bit 4r+k = cell (row r, column k) of the 4x4 tile), s_rx, s_ry, s_cx, s_cy [64] int,
+ * s_rmin[16] int2, s_cmin[16] int2, queue[256] uint16 */
+#define G2_WARP_BYTES (256 * 2 + 4 * 64 * 4 + 16 * 8 + 16 * 8 + 256 * 2)
 #define G2_SMEM_BYTES (CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES + 16)
 
 struct Grid2Args {
@@ -493,19 +493,28 @@ __device__ __forceinline__ void g2_wait_map(uint32_t bar) {
   }
 }
 
+/* 4 cells of one tile row against a threshold: bit k = (c_k < t) */
+__device__ __forceinline__ uint32_t g2_row_lt(const int4 cc, int t) {
+  return ((uint32_t)(cc.x - t) >> 31) | (((uint32_t)(cc.y - t) >> 31) << 1) | (((uint32_t)(cc.z - t) >> 31) << 2) |
+         (((uint32_t)(cc.w - t) >> 31) << 3);
+}
+
+/* CTW, CTH: tile columns / rows as compile-time constants (15 x 15 = the reference's 60 x 60 submap), 0 = run time */
+template <int CTW, int CTH>
 __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constant__ CUtensorMap tmap, const Grid2Args p) {
   extern __shared__ __align__(128) uint8_t g2_smem[];
   const uint32_t* s_map = reinterpret_cast<const uint32_t*>(g2_smem);
   const uint8_t* s_cls = g2_smem + CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS * 4;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   uint8_t* wbase = g2_smem + CASIM_G2_BYTES + wid * G2_WARP_BYTES;
-  uint8_t* s_nib = wbase;
-  int2* s_r = reinterpret_cast<int2*>(wbase + G2_NIB_BYTES);
-  int* s_cx = reinterpret_cast<int*>(wbase + G2_NIB_BYTES + 512);
-  int* s_cy = s_cx + 64;
-  int2* s_rmin = reinterpret_cast<int2*>(wbase + G2_NIB_BYTES + 1024);
+  uint16_t* s_tile = reinterpret_cast<uint16_t*>(wbase);
+  int* s_rx = reinterpret_cast<int*>(wbase + 512);
+  int* s_ry = s_rx + 64;
+  int* s_cx = s_rx + 128;
+  int* s_cy = s_rx + 192;
+  int2* s_rmin = reinterpret_cast<int2*>(wbase + 512 + 1024);
   int2* s_cmin = s_rmin + 16;
-  uint16_t* s_q = reinterpret_cast<uint16_t*>(wbase + G2_NIB_BYTES + 1024 + 256);
+  uint16_t* s_q = reinterpret_cast<uint16_t*>(wbase + 512 + 1024 + 256);
   const uint32_t bar = (uint32_t)__cvta_generic_to_shared(g2_smem + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES);
 
   /* ---- stage the map: the loads do not depend on the preceding kernels, so they go out before the PDL wait ---- */
@@ -527,13 +536,11 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
 
   const DevCfg& c = p.c;
   const unsigned N = (unsigned)p.E * (unsigned)p.A;
-  const int H = c.submap_h, W = c.submap_w; /* out[oy*H + ox]: W rows of H cells */
-  const int TW = H >> 2, TH = W >> 2;       /* 4x4 tiles */
+  const int H = CTW ? 4 * CTW : c.submap_h, W = CTH ? 4 * CTH : c.submap_w; /* out[oy*H + ox]: W rows of H cells */
+  const int TW = H >> 2, TH = W >> 2;                                       /* 4x4 tiles */
+  const int NT = TW * TH;
   const int cells = H * W;
   const int BIAS = CASIM_G2_PAD << 10;
-  const int rpi = 32 / TW;                  /* tile rows per pass-1 iteration */
-  const int lr = lane / TW, tx = lane - lr * TW;
-  const bool act = lr < rpi;
   unsigned g = 0;
   if (lane == 0) g = atomicAdd(&p.work[0], 1u);
   g = __shfl_sync(FULL_MASK, g, 0);
@@ -543,11 +550,12 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
     if (lane == 0) gnext = atomicAdd(&p.work[0], 1u); /* the next ticket travels while this agent is computed */
     const int e = (int)(g / (unsigned)p.A), ai = (int)(g - (unsigned)e * (unsigned)p.A);
     const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
-    uint4* gout = reinterpret_cast<uint4*>(p.out + (size_t)g * cells);
+    uint32_t* gout = reinterpret_cast<uint32_t*>(p.out + (size_t)g * cells);
     const int type = __float_as_int(p.state[5 * (size_t)N + g].w);
     const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_OCCUPANCY_GRID);
     if (!on) {
-      for (int i = lane; i < (cells >> 4); i += 32) gout[i] = make_uint4(0u, 0u, 0u, 0u);
+      uint4* g4 = reinterpret_cast<uint4*>(gout);
+      for (int i = lane; i < (cells >> 4); i += 32) g4[i] = make_uint4(0u, 0u, 0u, 0u);
       if (p.packed) {
         uint16_t* pk = reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3));
         for (int i = lane; i < (cells >> 4); i += 32) pk[i] = 0;
@@ -577,6 +585,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         M2 = b1; M5 = b2;
       }
       bool ok = true; /* every lookup stays inside the padded planes and every tile inside its 8x8 box */
+#pragma unroll
       for (int t = lane; t < 64; t += 32) {
         double rxd = 0, ryd = 0, cxd = 0, cyd = 0;
         if (t < W) {
@@ -590,7 +599,8 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           cyd = rint(M3 * x * 1024);
         }
         ok = ok && fabs(rxd) < 5.0e8 && fabs(ryd) < 5.0e8 && fabs(cxd) < 5.0e8 && fabs(cyd) < 5.0e8;
-        s_r[t] = make_int2((int)rxd + 16 + BIAS, (int)ryd + 16 + BIAS);
+        s_rx[t] = (int)rxd + 16 + BIAS;
+        s_ry[t] = (int)ryd + 16 + BIAS;
         s_cx[t] = (int)cxd;
         s_cy[t] = (int)cyd;
       }
@@ -598,14 +608,14 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
       int spx = 0, spy = 0, cpx = 0, cpy = 0;
       if (lane < 4) { /* the four corner cells bound every source coordinate (monotone terms) */
         const int oy = (lane & 1) ? W - 1 : 0, ox = (lane & 2) ? H - 1 : 0;
-        const int xi = (s_r[oy].x + s_cx[ox]) >> 10, yi = (s_r[oy].y + s_cy[ox]) >> 10;
+        const int xi = (s_rx[oy] + s_cx[ox]) >> 10, yi = (s_ry[oy] + s_cy[ox]) >> 10;
         ok = ok && xi >= 2 && yi >= 2 && xi <= CASIM_G2_DIM - 12 && yi <= CASIM_G2_DIM - 12;
       }
       if (lane < TH) { /* per tile row: minima of the row terms, and how far a tile reaches along each axis */
-        const int2 a = s_r[4 * lane], b = s_r[4 * lane + 3];
-        s_rmin[lane] = make_int2(min(a.x, b.x), min(a.y, b.y));
-        spx = abs(a.x - b.x);
-        spy = abs(a.y - b.y);
+        const int ax = s_rx[4 * lane], bx = s_rx[4 * lane + 3], ay = s_ry[4 * lane], by = s_ry[4 * lane + 3];
+        s_rmin[lane] = make_int2(min(ax, bx), min(ay, by));
+        spx = abs(ax - bx);
+        spy = abs(ay - by);
       }
       if (lane < TW) {
         const int ax = s_cx[4 * lane], bx = s_cx[4 * lane + 3], ay = s_cy[4 * lane], by = s_cy[4 * lane + 3];
@@ -629,96 +639,105 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         auto S = [&](int r, int cc) -> uint32_t {
           return (r >= 0 && r < CASIM_MAP_DIM && cc >= 0 && cc < CASIM_MAP_DIM) ? (uint32_t)map_bit(pl, r, cc) : 0u;
         };
-        for (int wi = lane; wi < W * TW; wi += 32) {
-          const int oy = wi / TW, ox0 = (wi - oy * TW) << 2;
-          uint32_t nib = 0;
-          for (int k = 0; k < 4; k++) {
-            long long Xl = ((long long)s_r[oy].x - BIAS + s_cx[ox0 + k]) >> 5;
-            long long Yl = ((long long)s_r[oy].y - BIAS + s_cy[ox0 + k]) >> 5;
+        for (int ti = lane; ti < NT; ti += 32) {
+          const int ty = ti / TW, tx = ti - ty * TW;
+          uint32_t bits = 0;
+          for (int k = 0; k < 16; k++) {
+            const int oy = 4 * ty + (k >> 2), ox = 4 * tx + (k & 3);
+            long long Xl = ((long long)s_rx[oy] - BIAS + s_cx[ox]) >> 5;
+            long long Yl = ((long long)s_ry[oy] - BIAS + s_cy[ox]) >> 5;
             int X = (int)Xl, Y = (int)Yl;
             int sxi = X >> 5, syi = Y >> 5, fx = X & 31, fy = Y & 31;
             uint32_t v = S(syi, sxi);
             if (fx > 0) v |= S(syi, sxi + 1);
             if (fy > 0) v |= S(syi + 1, sxi);
             if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
-            nib |= v << k;
+            bits |= v << k;
           }
-          s_nib[wi] = (uint8_t)nib;
+          s_tile[ti] = (uint16_t)bits;
         }
       } else {
-        /* ---- pass 1: classify the 4x4 tiles; uniform ones are done, the others are queued with their code ---- */
-        const int2 cm = s_cmin[act ? tx : 0];
+        /* ---- pass 1: one lane per 4x4 tile: uniform tiles are done, the others are queued with their code ---- */
         int nq = 0;
-        for (int ty0 = 0; ty0 < TH; ty0 += rpi) {
-          const int ty = ty0 + lr;
-          const bool valid = act && ty < TH;
+        for (int t0 = 0; t0 < NT; t0 += 32) {
+          const int ti = t0 + lane;
+          const bool valid = ti < NT;
+          const int ty = ti / TW, tx = ti - ty * TW;
           uint32_t code = 1u;
           if (valid) {
-            const int2 rm = s_rmin[ty];
+            const int2 rm = s_rmin[ty], cm = s_cmin[tx];
             code = s_cls[((rm.y + cm.y) >> 11) * CASIM_G2_CLS_DIM + ((rm.x + cm.x) >> 11)]; /* even anchor / 2 */
           }
           const uint32_t kind = code & 7u;
           const bool queued = kind != 1u && kind != 2u;
-          if (valid && !queued) {
-            const uint8_t nib = kind == 2u ? (uint8_t)0xF : (uint8_t)0;
-            uint8_t* o = s_nib + (4 * ty) * TW + tx;
-            o[0] = nib;
-            o[TW] = nib;
-            o[2 * TW] = nib;
-            o[3 * TW] = nib;
-          }
+          if (valid && !queued) s_tile[ti] = kind == 2u ? (uint16_t)0xFFFF : (uint16_t)0;
           const unsigned bq = __ballot_sync(FULL_MASK, queued);
-          if (queued) s_q[nq + __popc(bq & ((1u << lane) - 1u))] = (uint16_t)(ty | (tx << 4) | (code << 8));
+          if (queued) s_q[nq + __popc(bq & ((1u << lane) - 1u))] = (uint16_t)(ti | (code << 8));
           nq += __popc(bq);
         }
         __syncwarp();
-        /* ---- pass 2: the queued tiles, one lane per 4-cell word.  EDGE tile (kinds 3-6: every row, or every column, of
-         * the 8x8 box identical): one comparison per cell, no lookup.  OTHER tile: exact per-cell lookups. ---- */
-        for (int m = lane; m < 4 * nq; m += 32) {
-          const uint32_t en = s_q[m >> 2];
-          const int qty = (int)(en & 15u), wx = (int)((en >> 4) & 15u);
-          const int oy = 4 * qty + (m & 3);
+        /* ---- pass 2: the queued tiles, one lane per tile.  EDGE tile (kinds 3-6: every row, or every column, of the 8x8
+         * box identical): one comparison per cell, no lookup.  OTHER tile: exact per-cell lookups. ---- */
+        for (int m = lane; m < nq; m += 32) {
+          const uint32_t en = s_q[m];
+          const int ti = (int)(en & 255u);
+          const int ty = ti / TW, tx = ti - ty * TW;
           const uint32_t kind = (en >> 8) & 7u, pp = (en >> 11) & 7u;
-          const int2 r = s_r[oy];
-          uint32_t nib;
+          const int4 rx = *reinterpret_cast<const int4*>(s_rx + 4 * ty), ry = *reinterpret_cast<const int4*>(s_ry + 4 * ty);
+          const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * tx), cy = *reinterpret_cast<const int4*>(s_cy + 4 * tx);
+          uint32_t bits;
           if (kind >= 3u) {
             const bool horiz = kind >= 5u, ge = (kind & 1u) != 0u; /* 3, 5: ">= p occupied"; 4, 6: "< p occupied" */
-            const int2 rm = s_rmin[qty], cmn = s_cmin[wx];
+            const int2 rm = s_rmin[ty], cmn = s_cmin[tx];
             const int anc = ((horiz ? rm.y + cmn.y : rm.x + cmn.x) >> 11) << 1;
             /* ge: footprint max index = (v + 992) >> 10 >= anc + p  <=>  v >= (anc + p) * 1024 - 992
              * lt: footprint min index = v >> 10 < anc + p           <=>  v <  (anc + p) * 1024            */
-            const int t = ((anc + (int)pp) << 10) - (ge ? 992 : 0) - (horiz ? r.y : r.x);
-            const int4 cc = *reinterpret_cast<const int4*>((horiz ? s_cy : s_cx) + 4 * wx);
-            nib = (cc.x < t ? 1u : 0u) | (cc.y < t ? 2u : 0u) | (cc.z < t ? 4u : 0u) | (cc.w < t ? 8u : 0u);
-            if (ge) nib ^= 0xFu;
+            const int thr = ((anc + (int)pp) << 10) - (ge ? 992 : 0);
+            const int4 rr = horiz ? ry : rx, cc = horiz ? cy : cx;
+            bits = g2_row_lt(cc, thr - rr.x) | (g2_row_lt(cc, thr - rr.y) << 4) | (g2_row_lt(cc, thr - rr.z) << 8) |
+                   (g2_row_lt(cc, thr - rr.w) << 12);
+            if (ge) bits ^= 0xFFFFu;
           } else {
-            const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * wx);
-            const int4 cy = *reinterpret_cast<const int4*>(s_cy + 4 * wx);
-            nib = g2_cell(s_map, r.x + cx.x, r.y + cy.x);
-            nib |= g2_cell(s_map, r.x + cx.y, r.y + cy.y) << 1;
-            nib |= g2_cell(s_map, r.x + cx.z, r.y + cy.z) << 2;
-            nib |= g2_cell(s_map, r.x + cx.w, r.y + cy.w) << 3;
+            bits = 0;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+              const int rxx = r == 0 ? rx.x : r == 1 ? rx.y : r == 2 ? rx.z : rx.w;
+              const int ryy = r == 0 ? ry.x : r == 1 ? ry.y : r == 2 ? ry.z : ry.w;
+              bits |= g2_cell(s_map, rxx + cx.x, ryy + cy.x) << (4 * r);
+              bits |= g2_cell(s_map, rxx + cx.y, ryy + cy.y) << (4 * r + 1);
+              bits |= g2_cell(s_map, rxx + cx.z, ryy + cy.z) << (4 * r + 2);
+              bits |= g2_cell(s_map, rxx + cx.w, ryy + cy.w) << (4 * r + 3);
+            }
           }
-          s_nib[oy * TW + wx] = (uint8_t)nib;
+          s_tile[ti] = (uint16_t)bits;
         }
       }
       __syncwarp();
-      /* ---- copy-out: 16-byte coalesced stores (+ the np.packbits form: cell 0 in the most significant bit) ----
-       * nibble -> four 0/1 bytes: bit k of b lands on bit 8k of b * (1 + 2^7 + 2^14 + 2^21) */
-      const uint32_t* so = reinterpret_cast<const uint32_t*>(s_nib);
-      uint16_t* pk = p.packed ? reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3)) : nullptr;
-      for (int i = lane; i < (cells >> 4); i += 32) {
-        const uint32_t q = so[i];
-        uint4 v;
-        v.x = ((q & 0xFu) * 0x00204081u) & 0x01010101u;
-        v.y = (((q >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
-        v.z = (((q >> 16) & 0xFu) * 0x00204081u) & 0x01010101u;
-        v.w = (((q >> 24) & 0xFu) * 0x00204081u) & 0x01010101u;
-        gout[i] = v;
-        if (pk) { /* 16 cells -> 2 bytes; a nibble holds cell k in bit k, packbits wants the first cell in the top bit */
-          const uint32_t rv = __brev(q); /* byte 3-j of rv = bit-reversed byte j of q: its top nibble = reversed nibble */
-          const uint32_t b0 = ((rv >> 28) << 4) | ((rv >> 20) & 0xFu), b1 = (((rv >> 12) & 0xFu) << 4) | ((rv >> 4) & 0xFu);
-          pk[i] = (uint16_t)(b0 | (b1 << 8));
+      /* ---- copy-out, one lane per tile: 4 words (one per row; the lanes of a tile row write 4 TW contiguous bytes).
+       * nibble -> four 0/1 bytes: bit k of b lands on bit 8k of b * (1 + 2^7 + 2^14 + 2^21) ---- */
+      for (int t0 = 0; t0 < NT; t0 += 32) {
+        const int ti = t0 + lane;
+        if (ti < NT) {
+          const int ty = ti / TW, tx = ti - ty * TW;
+          const uint32_t q = s_tile[ti];
+          uint32_t* o = gout + (4 * ty) * TW + tx;
+          o[0] = ((q & 0xFu) * 0x00204081u) & 0x01010101u;
+          o[TW] = (((q >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
+          o[2 * TW] = (((q >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
+          o[3 * TW] = ((q >> 12) * 0x00204081u) & 0x01010101u;
+        }
+      }
+      if (p.packed) { /* np.packbits: 16 cells of a row -> 2 bytes, first cell in the most significant bit */
+        uint16_t* pk = reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3));
+        for (int i = lane; i < (cells >> 4); i += 32) {
+          uint32_t v = 0; /* nibbles of words 4i .. 4i+3 (row-major word index), word w = (oy, wx) -> tile (oy/4, wx), row oy%4 */
+#pragma unroll
+          for (int k = 0; k < 4; k++) {
+            const int w = 4 * i + k, oy = w / TW, wx = w - oy * TW;
+            const uint32_t nib = ((uint32_t)s_tile[(oy >> 2) * TW + wx] >> (4 * (oy & 3))) & 0xFu;
+            v |= (__brev(nib) >> 28) << (4 * (3 - k)); /* cell 0 of the nibble to its top bit; first word in the top nibble */
+          }
+          pk[i] = (uint16_t)(((v >> 8) & 0xFFu) | ((v & 0xFFu) << 8)); /* byte 0 = cells 0-7 */
         }
       }
       __syncwarp(); /* the staging area is reused by the next agent */
@@ -835,11 +854,13 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
       err = casim_grid2_encode_tmap(h);
       if (err != cudaSuccess) return err;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-      err = cudaFuncSetAttribute(k_grid_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G2_SMEM_BYTES);
+    const bool ref_shape = h->dc.submap_h == 60 && h->dc.submap_w == 60; /* Config.SUBMAP_WIDTH / HEIGHT, config.py:83-84 */
+    void (*kern)(const CUtensorMap, const Grid2Args) = ref_shape ? k_grid_tma<15, 15> : k_grid_tma<0, 0>;
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[ref_shape]) {
+      err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G2_SMEM_BYTES);
       if (err != cudaSuccess) return err;
-      attr_set = true;
+      attr_set[ref_shape] = true;
     }
     Grid2Args b;
     b.c = h->dc;
@@ -864,7 +885,7 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = casim_pdl_enabled() ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, k_grid_tma, *reinterpret_cast<const CUtensorMap*>(h->grid2_tmap), b);
+    return cudaLaunchKernelEx(&cfg, kern, *reinterpret_cast<const CUtensorMap*>(h->grid2_tmap), b);
   }
   if (fast)
     err = casim_launch_pdl<GridArgs>(k_grid_gather, dim3((unsigned)((N + GRID_WARPS - 1) / GRID_WARPS)), dim3(32 * GRID_WARPS), 0, s, a);
