@@ -545,13 +545,27 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
   if (lane == 0) g = atomicAdd(&p.work[0], 1u);
   g = __shfl_sync(FULL_MASK, g, 0);
   bool map_ready = false;
+  /* an agent's inputs: loaded one agent ahead, so that their global-memory latency hides behind the previous agent */
+  int in_type = 0, in_n = 0;
+  double2 in_q0 = make_double2(0., 0.), in_q1 = make_double2(0., 0.);
+  auto fetch = [&](unsigned ag) {
+    if (ag < N) {
+      const int ee = (int)(ag / (unsigned)p.A);
+      in_n = p.n_agents ? min(p.n_agents[ee], p.A) : p.A;
+      in_type = __float_as_int(p.state[5 * (size_t)N + ag].w);
+      in_q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)ag)[0];
+      in_q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)ag)[1];
+    }
+  };
+  fetch(g);
   while (g < N) {
     unsigned gnext = 0;
     if (lane == 0) gnext = atomicAdd(&p.work[0], 1u); /* the next ticket travels while this agent is computed */
     const int e = (int)(g / (unsigned)p.A), ai = (int)(g - (unsigned)e * (unsigned)p.A);
-    const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
+    const int n = in_n;
     uint32_t* gout = reinterpret_cast<uint32_t*>(p.out + (size_t)g * cells);
-    const int type = __float_as_int(p.state[5 * (size_t)N + g].w);
+    const int type = in_type;
+    const double2 q0 = in_q0, q1 = in_q1;
     const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_OCCUPANCY_GRID);
     if (!on) {
       uint4* g4 = reinterpret_cast<uint4*>(gout);
@@ -560,9 +574,11 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         uint16_t* pk = reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3));
         for (int i = lane; i < (cells >> 4); i += 32) pk[i] = 0;
       }
-    } else {
-      const double2 q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)g)[0];
-      const double2 q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)g)[1];
+      g = __shfl_sync(FULL_MASK, gnext, 0);
+      fetch(g);
+      continue;
+    }
+    {
       const double px = q0.x, py = q0.y, ch = q1.x, sh = q1.y;
       int row0, col0;
       world_to_map_mul(c, px, py, row0, col0);
@@ -629,6 +645,9 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
       spy = __reduce_max_sync(FULL_MASK, spy) + __reduce_max_sync(FULL_MASK, cpy);
       ok = __all_sync(FULL_MASK, ok) && max(spx, spy) < 5 * 1024;
       __syncwarp();
+      const unsigned gcur = g;
+      g = __shfl_sync(FULL_MASK, gnext, 0); /* the ticket has arrived by now: start the next agent's loads */
+      fetch(g);
       if (!map_ready) { /* first agent of this warp: the staged map must have landed */
         g2_wait_map(bar);
         map_ready = true;
@@ -678,15 +697,21 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         __syncwarp();
         /* ---- pass 2: the queued tiles, one lane per tile.  EDGE tile (kinds 3-6: every row, or every column, of the 8x8
          * box identical): one comparison per cell, no lookup.  OTHER tile: exact per-cell lookups. ---- */
-        for (int m = lane; m < nq; m += 32) {
-          const uint32_t en = s_q[m];
+        int no = 0; /* OTHER tiles: compacted in place to the front of the queue (slot no + rank <= the slot just read) */
+        for (int m0 = 0; m0 < nq; m0 += 32) {
+          const int m = m0 + lane;
+          const uint32_t en = m < nq ? s_q[m] : (1u << 8);
           const int ti = (int)(en & 255u);
           const int ty = ti / TW, tx = ti - ty * TW;
           const uint32_t kind = (en >> 8) & 7u, pp = (en >> 11) & 7u;
-          const int4 rx = *reinterpret_cast<const int4*>(s_rx + 4 * ty), ry = *reinterpret_cast<const int4*>(s_ry + 4 * ty);
-          const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * tx), cy = *reinterpret_cast<const int4*>(s_cy + 4 * tx);
-          uint32_t bits;
+          const bool other = kind == 0u;
+          const unsigned bo = __ballot_sync(FULL_MASK, other);
+          if (other) s_q[no + __popc(bo & ((1u << lane) - 1u))] = (uint16_t)ti; /* the ballot orders every lane's read first */
+          no += __popc(bo);
           if (kind >= 3u) {
+            const int4 rx = *reinterpret_cast<const int4*>(s_rx + 4 * ty), ry = *reinterpret_cast<const int4*>(s_ry + 4 * ty);
+            const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * tx), cy = *reinterpret_cast<const int4*>(s_cy + 4 * tx);
+            uint32_t bits;
             const bool horiz = kind >= 5u, ge = (kind & 1u) != 0u; /* 3, 5: ">= p occupied"; 4, 6: "< p occupied" */
             const int2 rm = s_rmin[ty], cmn = s_cmin[tx];
             const int anc = ((horiz ? rm.y + cmn.y : rm.x + cmn.x) >> 11) << 1;
@@ -697,19 +722,27 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
             bits = g2_row_lt(cc, thr - rr.x) | (g2_row_lt(cc, thr - rr.y) << 4) | (g2_row_lt(cc, thr - rr.z) << 8) |
                    (g2_row_lt(cc, thr - rr.w) << 12);
             if (ge) bits ^= 0xFFFFu;
-          } else {
-            bits = 0;
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-              const int rxx = r == 0 ? rx.x : r == 1 ? rx.y : r == 2 ? rx.z : rx.w;
-              const int ryy = r == 0 ? ry.x : r == 1 ? ry.y : r == 2 ? ry.z : ry.w;
-              bits |= g2_cell(s_map, rxx + cx.x, ryy + cy.x) << (4 * r);
-              bits |= g2_cell(s_map, rxx + cx.y, ryy + cy.y) << (4 * r + 1);
-              bits |= g2_cell(s_map, rxx + cx.z, ryy + cy.z) << (4 * r + 2);
-              bits |= g2_cell(s_map, rxx + cx.w, ryy + cy.w) << (4 * r + 3);
-            }
+            s_tile[ti] = (uint16_t)bits;
           }
-          s_tile[ti] = (uint16_t)bits;
+        }
+        __syncwarp();
+        /* ---- pass 3: OTHER tiles, one lane per tile ROW (4 cells): exact lookups in the staged footprint planes; the
+         * four lanes of a tile combine their nibbles with shuffles ---- */
+        for (int m0 = 0; m0 < 4 * no; m0 += 32) {
+          const int m = m0 + lane;
+          const bool live = m < 4 * no;
+          const int ti = live ? (int)s_q[m >> 2] : 0;
+          const int ty = ti / TW, tx = ti - ty * TW, r = m & 3;
+          const int rxx = s_rx[4 * ty + r], ryy = s_ry[4 * ty + r];
+          const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * tx), cy = *reinterpret_cast<const int4*>(s_cy + 4 * tx);
+          uint32_t nib = g2_cell(s_map, rxx + cx.x, ryy + cy.x);
+          nib |= g2_cell(s_map, rxx + cx.y, ryy + cy.y) << 1;
+          nib |= g2_cell(s_map, rxx + cx.z, ryy + cy.z) << 2;
+          nib |= g2_cell(s_map, rxx + cx.w, ryy + cy.w) << 3;
+          nib <<= 4 * r;
+          nib |= __shfl_xor_sync(FULL_MASK, nib, 1);
+          nib |= __shfl_xor_sync(FULL_MASK, nib, 2);
+          if (live && r == 0) s_tile[ti] = (uint16_t)nib;
         }
       }
       __syncwarp();
@@ -728,7 +761,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         }
       }
       if (p.packed) { /* np.packbits: 16 cells of a row -> 2 bytes, first cell in the most significant bit */
-        uint16_t* pk = reinterpret_cast<uint16_t*>(p.packed + (size_t)g * (cells >> 3));
+        uint16_t* pk = reinterpret_cast<uint16_t*>(p.packed + (size_t)gcur * (cells >> 3));
         for (int i = lane; i < (cells >> 4); i += 32) {
           uint32_t v = 0; /* nibbles of words 4i .. 4i+3 (row-major word index), word w = (oy, wx) -> tile (oy/4, wx), row oy%4 */
 #pragma unroll
@@ -742,7 +775,6 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
       }
       __syncwarp(); /* the staging area is reused by the next agent */
     }
-    g = __shfl_sync(FULL_MASK, gnext, 0);
   }
   if (!map_ready) g2_wait_map(bar); /* nobody leaves while the bulk copies into this CTA's shared memory are in flight */
   /* the last warp to run dry re-arms the work counters for the next launch */
