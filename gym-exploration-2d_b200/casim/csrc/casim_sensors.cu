@@ -471,11 +471,13 @@ struct Grid2Args {
   int E, A;
 };
 
-__device__ __forceinline__ uint32_t g2_cell(const uint32_t* __restrict__ sp, int fx, int fy) {
-  /* fx, fy: biased source coordinates in 1/1024 cell (OpenCV's X0 + adelta, before the >> 5) */
+__device__ __forceinline__ uint32_t g2_cell(uint32_t a_map, int fx, int fy) {
+  /* fx, fy: biased source coordinates in 1/1024 cell (OpenCV's X0 + adelta, before the >> 5); a_map: shared-space
+   * address of the staged planes */
   const int xi = fx >> 10, yi = fy >> 10;
   const int plane = ((fx & 0x3E0) ? CASIM_G2_PLANE_WORDS : 0) + ((fy & 0x3E0) ? 2 * CASIM_G2_PLANE_WORDS : 0);
-  const uint32_t w = sp[plane + yi * CASIM_G2_WORDS + (xi >> 5)];
+  uint32_t w;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(a_map + 4u * (uint32_t)(plane + yi * CASIM_G2_WORDS + (xi >> 5))));
   return (w >> (xi & 31)) & 1u;
 }
 
@@ -499,22 +501,32 @@ __device__ __forceinline__ uint32_t g2_row_lt(const int4 cc, int t) {
 }
 
 /* CTW, CTH: tile columns / rows as compile-time constants (15 x 15 = the reference's 60 x 60 submap), 0 = run time */
+/* Shared-memory accessors on explicit 32-bit shared-space addresses.  With ordinary pointers into the dynamic shared
+ * array the compiler rebuilt the CTA's shared-window base (S2UR SR_CgaCtaId / ULEA) in front of almost every access
+ * (9.5 % of the kernel's instructions, profiles/r2g); the addresses below are formed once. */
+__device__ __forceinline__ int g2_ld32(uint32_t a) { int v; asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t g2_ldu16(uint32_t a) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t g2_ldu8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ int2 g2_ld64(uint32_t a) { int2 v; asm volatile("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }
+__device__ __forceinline__ int4 g2_ld128(uint32_t a) {
+  int4 v;
+  asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void g2_st32(uint32_t a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void g2_st64(uint32_t a, int2 v) { asm volatile("st.shared.v2.s32 [%0], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory"); }
+__device__ __forceinline__ void g2_stu16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v) : "memory"); }
+
 template <int CTW, int CTH>
 __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constant__ CUtensorMap tmap, const Grid2Args p) {
   extern __shared__ __align__(128) uint8_t g2_smem[];
-  const uint32_t* s_map = reinterpret_cast<const uint32_t*>(g2_smem);
-  const uint8_t* s_cls = g2_smem + CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS * 4;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  uint8_t* wbase = g2_smem + CASIM_G2_BYTES + wid * G2_WARP_BYTES;
-  uint16_t* s_tile = reinterpret_cast<uint16_t*>(wbase);
-  int* s_rx = reinterpret_cast<int*>(wbase + 512);
-  int* s_ry = s_rx + 64;
-  int* s_cx = s_rx + 128;
-  int* s_cy = s_rx + 192;
-  int2* s_rmin = reinterpret_cast<int2*>(wbase + 512 + 1024);
-  int2* s_cmin = s_rmin + 16;
-  uint16_t* s_q = reinterpret_cast<uint16_t*>(wbase + 512 + 1024 + 256);
-  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(g2_smem + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES);
+  const uint32_t a_map = (uint32_t)__cvta_generic_to_shared(g2_smem); /* 4 footprint planes, then the classification bytes */
+  const uint32_t a_cls = a_map + CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS * 4;
+  const uint32_t a_w = a_map + CASIM_G2_BYTES + wid * G2_WARP_BYTES;    /* this warp's staging area */
+  const uint32_t a_tile = a_w, a_rx = a_w + 512, a_ry = a_rx + 256, a_cx = a_rx + 512, a_cy = a_rx + 768;
+  const uint32_t a_rmin = a_w + 512 + 1024, a_cmin = a_rmin + 128, a_q = a_rmin + 256;
+  const uint32_t bar = a_map + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES;
   unsigned* s_ticket = reinterpret_cast<unsigned*>(g2_smem + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES + 8);
 
   /* ---- stage the map: the loads do not depend on the preceding kernels, so they go out before the PDL wait ---- */
@@ -523,7 +535,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)CASIM_G2_BYTES) : "memory");
-    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(g2_smem);
+    const uint32_t dst = a_map;
 #pragma unroll 1
     for (int k = 0; k < CASIM_G2_BOXES; k++)
       asm volatile(
@@ -624,27 +636,27 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           cyd = rint(M3 * x * 1024);
         }
         ok = ok && fabs(rxd) < 5.0e8 && fabs(ryd) < 5.0e8 && fabs(cxd) < 5.0e8 && fabs(cyd) < 5.0e8;
-        s_rx[t] = (int)rxd + 16 + BIAS;
-        s_ry[t] = (int)ryd + 16 + BIAS;
-        s_cx[t] = (int)cxd;
-        s_cy[t] = (int)cyd;
+        g2_st32(a_rx + 4 * t, (int)rxd + 16 + BIAS);
+        g2_st32(a_ry + 4 * t, (int)ryd + 16 + BIAS);
+        g2_st32(a_cx + 4 * t, (int)cxd);
+        g2_st32(a_cy + 4 * t, (int)cyd);
       }
       __syncwarp();
       int spx = 0, spy = 0, cpx = 0, cpy = 0;
       if (lane < 4) { /* the four corner cells bound every source coordinate (monotone terms) */
         const int oy = (lane & 1) ? W - 1 : 0, ox = (lane & 2) ? H - 1 : 0;
-        const int xi = (s_rx[oy] + s_cx[ox]) >> 10, yi = (s_ry[oy] + s_cy[ox]) >> 10;
+        const int xi = (g2_ld32(a_rx + 4 * oy) + g2_ld32(a_cx + 4 * ox)) >> 10, yi = (g2_ld32(a_ry + 4 * oy) + g2_ld32(a_cy + 4 * ox)) >> 10;
         ok = ok && xi >= 2 && yi >= 2 && xi <= CASIM_G2_DIM - 12 && yi <= CASIM_G2_DIM - 12;
       }
       if (lane < TH) { /* per tile row: minima of the row terms, and how far a tile reaches along each axis */
-        const int ax = s_rx[4 * lane], bx = s_rx[4 * lane + 3], ay = s_ry[4 * lane], by = s_ry[4 * lane + 3];
-        s_rmin[lane] = make_int2(min(ax, bx), min(ay, by));
+        const int ax = g2_ld32(a_rx + 16 * lane), bx = g2_ld32(a_rx + 16 * lane + 12), ay = g2_ld32(a_ry + 16 * lane), by = g2_ld32(a_ry + 16 * lane + 12);
+        g2_st64(a_rmin + 8 * lane, make_int2(min(ax, bx), min(ay, by)));
         spx = abs(ax - bx);
         spy = abs(ay - by);
       }
       if (lane < TW) {
-        const int ax = s_cx[4 * lane], bx = s_cx[4 * lane + 3], ay = s_cy[4 * lane], by = s_cy[4 * lane + 3];
-        s_cmin[lane] = make_int2(min(ax, bx), min(ay, by));
+        const int ax = g2_ld32(a_cx + 16 * lane), bx = g2_ld32(a_cx + 16 * lane + 12), ay = g2_ld32(a_cy + 16 * lane), by = g2_ld32(a_cy + 16 * lane + 12);
+        g2_st64(a_cmin + 8 * lane, make_int2(min(ax, bx), min(ay, by)));
         cpx = abs(ax - bx);
         cpy = abs(ay - by);
       }
@@ -672,8 +684,8 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           uint32_t bits = 0;
           for (int k = 0; k < 16; k++) {
             const int oy = 4 * ty + (k >> 2), ox = 4 * tx + (k & 3);
-            long long Xl = ((long long)s_rx[oy] - BIAS + s_cx[ox]) >> 5;
-            long long Yl = ((long long)s_ry[oy] - BIAS + s_cy[ox]) >> 5;
+            long long Xl = ((long long)g2_ld32(a_rx + 4 * oy) - BIAS + g2_ld32(a_cx + 4 * ox)) >> 5;
+            long long Yl = ((long long)g2_ld32(a_ry + 4 * oy) - BIAS + g2_ld32(a_cy + 4 * ox)) >> 5;
             int X = (int)Xl, Y = (int)Yl;
             int sxi = X >> 5, syi = Y >> 5, fx = X & 31, fy = Y & 31;
             uint32_t v = S(syi, sxi);
@@ -682,7 +694,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
             if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
             bits |= v << k;
           }
-          s_tile[ti] = (uint16_t)bits;
+          g2_stu16(a_tile + 2 * ti, bits);
         }
       } else {
         /* ---- pass 1: one lane per 4x4 tile: uniform tiles are done, the others are queued with their code ---- */
@@ -693,14 +705,14 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           const int ty = ti / TW, tx = ti - ty * TW;
           uint32_t code = 1u;
           if (valid) {
-            const int2 rm = s_rmin[ty], cm = s_cmin[tx];
-            code = s_cls[((rm.y + cm.y) >> 11) * CASIM_G2_CLS_DIM + ((rm.x + cm.x) >> 11)]; /* even anchor / 2 */
+            const int2 rm = g2_ld64(a_rmin + 8 * ty), cm = g2_ld64(a_cmin + 8 * tx);
+            code = g2_ldu8(a_cls + ((rm.y + cm.y) >> 11) * CASIM_G2_CLS_DIM + ((rm.x + cm.x) >> 11)); /* even anchor / 2 */
           }
           const uint32_t kind = code & 7u;
           const bool queued = kind != 1u && kind != 2u;
-          if (valid && !queued) s_tile[ti] = kind == 2u ? (uint16_t)0xFFFF : (uint16_t)0;
+          if (valid && !queued) g2_stu16(a_tile + 2 * ti, kind == 2u ? 0xFFFFu : 0u);
           const unsigned bq = __ballot_sync(FULL_MASK, queued);
-          if (queued) s_q[nq + __popc(bq & ((1u << lane) - 1u))] = (uint16_t)(ti | (code << 8));
+          if (queued) g2_stu16(a_q + 2 * (nq + __popc(bq & ((1u << lane) - 1u))), ti | (code << 8));
           nq += __popc(bq);
         }
         __syncwarp();
@@ -709,29 +721,27 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         int no = 0; /* OTHER tiles: compacted in place to the front of the queue (slot no + rank <= the slot just read) */
         for (int m0 = 0; m0 < nq; m0 += 32) {
           const int m = m0 + lane;
-          const uint32_t en = m < nq ? s_q[m] : (1u << 8);
+          const uint32_t en = m < nq ? g2_ldu16(a_q + 2 * m) : (1u << 8);
           const int ti = (int)(en & 255u);
           const int ty = ti / TW, tx = ti - ty * TW;
           const uint32_t kind = (en >> 8) & 7u, pp = (en >> 11) & 7u;
           const bool other = kind == 0u;
           const unsigned bo = __ballot_sync(FULL_MASK, other);
-          if (other) s_q[no + __popc(bo & ((1u << lane) - 1u))] = (uint16_t)ti; /* the ballot orders every lane's read first */
+          if (other) g2_stu16(a_q + 2 * (no + __popc(bo & ((1u << lane) - 1u))), ti); /* the ballot orders every lane's read first */
           no += __popc(bo);
           if (kind >= 3u) {
-            const int4 rx = *reinterpret_cast<const int4*>(s_rx + 4 * ty), ry = *reinterpret_cast<const int4*>(s_ry + 4 * ty);
-            const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * tx), cy = *reinterpret_cast<const int4*>(s_cy + 4 * tx);
             uint32_t bits;
             const bool horiz = kind >= 5u, ge = (kind & 1u) != 0u; /* 3, 5: ">= p occupied"; 4, 6: "< p occupied" */
-            const int2 rm = s_rmin[ty], cmn = s_cmin[tx];
-            const int anc = ((horiz ? rm.y + cmn.y : rm.x + cmn.x) >> 11) << 1;
+            const int sel = horiz ? 4 : 0; /* .y halves of the (x, y) pairs */
+            const int anc = ((g2_ld32(a_rmin + 8 * ty + sel) + g2_ld32(a_cmin + 8 * tx + sel)) >> 11) << 1;
             /* ge: footprint max index = (v + 992) >> 10 >= anc + p  <=>  v >= (anc + p) * 1024 - 992
              * lt: footprint min index = v >> 10 < anc + p           <=>  v <  (anc + p) * 1024            */
             const int thr = ((anc + (int)pp) << 10) - (ge ? 992 : 0);
-            const int4 rr = horiz ? ry : rx, cc = horiz ? cy : cx;
+            const int4 rr = g2_ld128((horiz ? a_ry : a_rx) + 16 * ty), cc = g2_ld128((horiz ? a_cy : a_cx) + 16 * tx);
             bits = g2_row_lt(cc, thr - rr.x) | (g2_row_lt(cc, thr - rr.y) << 4) | (g2_row_lt(cc, thr - rr.z) << 8) |
                    (g2_row_lt(cc, thr - rr.w) << 12);
             if (ge) bits ^= 0xFFFFu;
-            s_tile[ti] = (uint16_t)bits;
+            g2_stu16(a_tile + 2 * ti, bits);
           }
         }
         __syncwarp();
@@ -740,18 +750,18 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         for (int m0 = 0; m0 < 4 * no; m0 += 32) {
           const int m = m0 + lane;
           const bool live = m < 4 * no;
-          const int ti = live ? (int)s_q[m >> 2] : 0;
+          const int ti = live ? (int)g2_ldu16(a_q + 2 * (m >> 2)) : 0;
           const int ty = ti / TW, tx = ti - ty * TW, r = m & 3;
-          const int rxx = s_rx[4 * ty + r], ryy = s_ry[4 * ty + r];
-          const int4 cx = *reinterpret_cast<const int4*>(s_cx + 4 * tx), cy = *reinterpret_cast<const int4*>(s_cy + 4 * tx);
-          uint32_t nib = g2_cell(s_map, rxx + cx.x, ryy + cy.x);
-          nib |= g2_cell(s_map, rxx + cx.y, ryy + cy.y) << 1;
-          nib |= g2_cell(s_map, rxx + cx.z, ryy + cy.z) << 2;
-          nib |= g2_cell(s_map, rxx + cx.w, ryy + cy.w) << 3;
+          const int rxx = g2_ld32(a_rx + 4 * (4 * ty + r)), ryy = g2_ld32(a_ry + 4 * (4 * ty + r));
+          const int4 cx = g2_ld128(a_cx + 16 * tx), cy = g2_ld128(a_cy + 16 * tx);
+          uint32_t nib = g2_cell(a_map, rxx + cx.x, ryy + cy.x);
+          nib |= g2_cell(a_map, rxx + cx.y, ryy + cy.y) << 1;
+          nib |= g2_cell(a_map, rxx + cx.z, ryy + cy.z) << 2;
+          nib |= g2_cell(a_map, rxx + cx.w, ryy + cy.w) << 3;
           nib <<= 4 * r;
           nib |= __shfl_xor_sync(FULL_MASK, nib, 1);
           nib |= __shfl_xor_sync(FULL_MASK, nib, 2);
-          if (live && r == 0) s_tile[ti] = (uint16_t)nib;
+          if (live && r == 0) g2_stu16(a_tile + 2 * ti, nib);
         }
       }
       __syncwarp();
@@ -761,7 +771,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         const int ti = t0 + lane;
         if (ti < NT) {
           const int ty = ti / TW, tx = ti - ty * TW;
-          const uint32_t q = s_tile[ti];
+          const uint32_t q = g2_ldu16(a_tile + 2 * ti);
           uint32_t* o = gout + (4 * ty) * TW + tx;
           o[0] = ((q & 0xFu) * 0x00204081u) & 0x01010101u;
           o[TW] = (((q >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
@@ -776,7 +786,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
 #pragma unroll
           for (int k = 0; k < 4; k++) {
             const int w = 4 * i + k, oy = w / TW, wx = w - oy * TW;
-            const uint32_t nib = ((uint32_t)s_tile[(oy >> 2) * TW + wx] >> (4 * (oy & 3))) & 0xFu;
+            const uint32_t nib = (g2_ldu16(a_tile + 2 * ((oy >> 2) * TW + wx)) >> (4 * (oy & 3))) & 0xFu;
             v |= (__brev(nib) >> 28) << (4 * (3 - k)); /* cell 0 of the nibble to its top bit; first word in the top nibble */
           }
           pk[i] = (uint16_t)(((v >> 8) & 0xFFu) | ((v & 0xFFu) << 8)); /* byte 0 = cells 0-7 */
