@@ -233,6 +233,13 @@ int casim_destroy(casim_handle* h) {
   cudaFree(h->ga3c_wb);
   cudaFree(h->ga3c_x);
   cudaFree(h->ga3c_xb);
+  if (h->pipe_stream) {
+    for (int k = 0; k < 2; k++) {
+      cudaEventDestroy(h->pipe_ev_kernels[k]);
+      cudaEventDestroy(h->pipe_ev_copied[k]);
+    }
+    cudaStreamDestroy(h->pipe_stream);
+  }
   free(h);
   return 0;
 }
@@ -406,11 +413,13 @@ static void* mapped_alias(const void* p) {
   return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
 }
 
-int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
-                    const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
-                    void* stream) {
-  REQUIRE(h && state && dev && host, "null argument");
-  cudaStream_t s = (cudaStream_t)stream;
+/* Shared body of the host-buffer steps: actions in (zero-copy read or H2D copy on `s`), the step with the small results
+ * stored straight into mapped host memory, and the list of (dst, src, bytes) D2H copies that remain to be issued. */
+struct HostPending { void* dst; const void* src; size_t bytes; };
+
+static int host_step_launch(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
+                            const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
+                            cudaStream_t s, HostPending* pend, int* n_pend) {
   size_t N = (size_t)h->E * h->A;
   static const int zc_on = casim_tuning_int("CASIM_ZEROCOPY", 1);
   /* Actions.  Pinned + mapped and small: the step kernel reads them from host memory itself (every lane, one
@@ -432,9 +441,8 @@ int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host
    * written by the kernels STRAIGHT into host memory over PCIe (posted, coalesced stores; the field's device
    * buffer is not touched by this call): no copy-engine hop and no extra stream operation per field, which is
    * what bounds a small step (C2: four D2H copies cost more than the step kernel).  Larger results (sensor
-   * planes) and pageable buffers go through cudaMemcpyAsync after the kernels.  CASIM_ZEROCOPY=0 disables. */
+   * planes) and pageable buffers go through cudaMemcpyAsync after the kernels. */
   casim_obs run = *dev;
-  struct Pending { void* dst; const void* src; size_t bytes; } pend[10];
   int np = 0;
 #define OUT(field, nbytes, zc_ok)                                                                \
   if (host->field) {                                                                             \
@@ -460,9 +468,72 @@ int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host
 #undef OUT
   int rc = casim_step(h, state, ext_src, policy_actions, dt, &run, s);
   h->ext_copy_dst = nullptr;
+  *n_pend = np;
+  return rc;
+}
+
+int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
+                    const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
+                    void* stream) {
+  REQUIRE(h && state && dev && host, "null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  HostPending pend[12];
+  int np = 0;
+  int rc = host_step_launch(h, state, ext_actions_host, ext_actions_dev, policy_actions, dt, dev, host, s, pend, &np);
   if (rc) return rc;
   for (int i = 0; i < np; i++) CK(cudaMemcpyAsync(pend[i].dst, pend[i].src, pend[i].bytes, cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+int casim_step_host_pipelined(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
+                              const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
+                              uint8_t* grid_packed_dev, uint8_t* grid_packed_host, void* stream) {
+  REQUIRE(h && state && dev && host, "null argument");
+  REQUIRE((grid_packed_dev == nullptr) == (grid_packed_host == nullptr), "packed grid: give both buffers or neither");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!h->pipe_stream) {
+    CK(cudaStreamCreateWithFlags(&h->pipe_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; k++) {
+      CK(cudaEventCreateWithFlags(&h->pipe_ev_kernels[k], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&h->pipe_ev_copied[k], cudaEventDisableTiming));
+    }
+  }
+  const int slot = (int)(h->pipe_steps & 1ull);
+  /* step t: kernels on the caller's stream; with a packed grid the dense local_grid stays on the device */
+  casim_obs host_run = *host;
+  uint8_t* keep_packed = h->grid_packed;
+  if (grid_packed_dev) {
+    REQUIRE(dev->local_grid, "packed grid delivery needs the device local_grid buffer");
+    h->grid_packed = grid_packed_dev;
+    host_run.local_grid = nullptr;
+  }
+  HostPending pend[12];
+  int np = 0;
+  int rc = host_step_launch(h, state, ext_actions_host, ext_actions_dev, policy_actions, dt, dev, &host_run, s, pend, &np);
+  h->grid_packed = keep_packed;
+  if (rc) return rc;
+  if (grid_packed_dev) {
+    pend[np].dst = grid_packed_host;
+    pend[np].src = grid_packed_dev;
+    pend[np].bytes = (size_t)h->E * h->A * (size_t)((h->dc.submap_w * h->dc.submap_h + 7) / 8);
+    np++;
+  }
+  CK(cudaEventRecord(h->pipe_ev_kernels[slot], s));
+  /* its D2H copies on the copy stream: they overlap the kernels of step t+1 */
+  CK(cudaStreamWaitEvent(h->pipe_stream, h->pipe_ev_kernels[slot], 0));
+  for (int i = 0; i < np; i++)
+    CK(cudaMemcpyAsync(pend[i].dst, pend[i].src, pend[i].bytes, cudaMemcpyDeviceToHost, h->pipe_stream));
+  CK(cudaEventRecord(h->pipe_ev_copied[slot], h->pipe_stream));
+  /* what the caller gets back now: step t-1, complete in ITS host buffers */
+  if (h->pipe_steps > 0) CK(cudaEventSynchronize(h->pipe_ev_copied[slot ^ 1]));
+  h->pipe_steps++;
+  return 0;
+}
+
+int casim_host_flush(casim_handle* h) {
+  REQUIRE(h, "null handle");
+  if (h->pipe_stream && h->pipe_steps > 0) CK(cudaEventSynchronize(h->pipe_ev_copied[(int)((h->pipe_steps - 1) & 1ull)]));
   return 0;
 }
 

@@ -113,6 +113,10 @@ struct casim_handle {
   int4* rvo_node;
   int rvo_n, rvo_root;
   float* ext_copy_dst;     /* set by casim_step_host around its casim_step call (see CoreArgs::ext_copy_dst) */
+  /* casim_step_host_pipelined: copy stream + per-slot events (kernels done / copies done), steps issued so far */
+  cudaStream_t pipe_stream;
+  cudaEvent_t pipe_ev_kernels[2], pipe_ev_copied[2];
+  unsigned long long pipe_steps;
   unsigned long long launches;
 };
 

@@ -504,18 +504,21 @@ __device__ __forceinline__ uint32_t g2_row_lt(const int4 cc, int t) {
 /* Shared-memory accessors on explicit 32-bit shared-space addresses.  With ordinary pointers into the dynamic shared
  * array the compiler rebuilt the CTA's shared-window base (S2UR SR_CgaCtaId / ULEA) in front of almost every access
  * (9.5 % of the kernel's instructions, profiles/r2g); the addresses below are formed once. */
-__device__ __forceinline__ int g2_ld32(uint32_t a) { int v; asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ uint32_t g2_ldu16(uint32_t a) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ uint32_t g2_ldu8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ int2 g2_ld64(uint32_t a) { int2 v; asm volatile("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }
-__device__ __forceinline__ int4 g2_ld128(uint32_t a) {
+/* OFF = byte offset folded into the instruction's immediate field (the per-warp arrays sit at fixed offsets from a_w) */
+template <int OFF = 0> __device__ __forceinline__ int g2_ld32(uint32_t a) { int v; asm volatile("ld.shared.s32 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(OFF)); return v; }
+template <int OFF = 0> __device__ __forceinline__ uint32_t g2_ldu16(uint32_t a) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(OFF)); return v; }
+template <int OFF = 0> __device__ __forceinline__ uint32_t g2_ldu8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(OFF)); return v; }
+template <int OFF = 0> __device__ __forceinline__ int2 g2_ld64(uint32_t a) { int2 v; asm volatile("ld.shared.v2.s32 {%0, %1}, [%2+%3];" : "=r"(v.x), "=r"(v.y) : "r"(a), "n"(OFF)); return v; }
+template <int OFF = 0> __device__ __forceinline__ int4 g2_ld128(uint32_t a) {
   int4 v;
-  asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4+%5];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a), "n"(OFF));
   return v;
 }
-__device__ __forceinline__ void g2_st32(uint32_t a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-__device__ __forceinline__ void g2_st64(uint32_t a, int2 v) { asm volatile("st.shared.v2.s32 [%0], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory"); }
-__device__ __forceinline__ void g2_stu16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v) : "memory"); }
+template <int OFF = 0> __device__ __forceinline__ void g2_st32(uint32_t a, int v) { asm volatile("st.shared.s32 [%0+%2], %1;" ::"r"(a), "r"(v), "n"(OFF) : "memory"); }
+template <int OFF = 0> __device__ __forceinline__ void g2_st64(uint32_t a, int2 v) { asm volatile("st.shared.v2.s32 [%0+%3], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y), "n"(OFF) : "memory"); }
+template <int OFF = 0> __device__ __forceinline__ void g2_stu16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0+%2], %1;" ::"r"(a), "h"((uint16_t)v), "n"(OFF) : "memory"); }
+/* byte offsets of the per-warp arrays from the warp's staging base a_w */
+enum { G2_TILE = 0, G2_RX = 512, G2_RY = 768, G2_CX = 1024, G2_CY = 1280, G2_RMIN = 1536, G2_CMIN = 1664, G2_Q = 1792 };
 
 template <int CTW, int CTH>
 __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constant__ CUtensorMap tmap, const Grid2Args p) {
@@ -524,8 +527,6 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
   const uint32_t a_map = (uint32_t)__cvta_generic_to_shared(g2_smem); /* 4 footprint planes, then the classification bytes */
   const uint32_t a_cls = a_map + CASIM_NUM_PLANES * CASIM_G2_PLANE_WORDS * 4;
   const uint32_t a_w = a_map + CASIM_G2_BYTES + wid * G2_WARP_BYTES;    /* this warp's staging area */
-  const uint32_t a_tile = a_w, a_rx = a_w + 512, a_ry = a_rx + 256, a_cx = a_rx + 512, a_cy = a_rx + 768;
-  const uint32_t a_rmin = a_w + 512 + 1024, a_cmin = a_rmin + 128, a_q = a_rmin + 256;
   const uint32_t bar = a_map + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES;
   unsigned* s_ticket = reinterpret_cast<unsigned*>(g2_smem + CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES + 8);
 
@@ -636,27 +637,27 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           cyd = rint(M3 * x * 1024);
         }
         ok = ok && fabs(rxd) < 5.0e8 && fabs(ryd) < 5.0e8 && fabs(cxd) < 5.0e8 && fabs(cyd) < 5.0e8;
-        g2_st32(a_rx + 4 * t, (int)rxd + 16 + BIAS);
-        g2_st32(a_ry + 4 * t, (int)ryd + 16 + BIAS);
-        g2_st32(a_cx + 4 * t, (int)cxd);
-        g2_st32(a_cy + 4 * t, (int)cyd);
+        g2_st32<G2_RX>(a_w + 4 * t, (int)rxd + 16 + BIAS);
+        g2_st32<G2_RY>(a_w + 4 * t, (int)ryd + 16 + BIAS);
+        g2_st32<G2_CX>(a_w + 4 * t, (int)cxd);
+        g2_st32<G2_CY>(a_w + 4 * t, (int)cyd);
       }
       __syncwarp();
       int spx = 0, spy = 0, cpx = 0, cpy = 0;
       if (lane < 4) { /* the four corner cells bound every source coordinate (monotone terms) */
         const int oy = (lane & 1) ? W - 1 : 0, ox = (lane & 2) ? H - 1 : 0;
-        const int xi = (g2_ld32(a_rx + 4 * oy) + g2_ld32(a_cx + 4 * ox)) >> 10, yi = (g2_ld32(a_ry + 4 * oy) + g2_ld32(a_cy + 4 * ox)) >> 10;
+        const int xi = (g2_ld32<G2_RX>(a_w + 4 * oy) + g2_ld32<G2_CX>(a_w + 4 * ox)) >> 10, yi = (g2_ld32<G2_RY>(a_w + 4 * oy) + g2_ld32<G2_CY>(a_w + 4 * ox)) >> 10;
         ok = ok && xi >= 2 && yi >= 2 && xi <= CASIM_G2_DIM - 12 && yi <= CASIM_G2_DIM - 12;
       }
       if (lane < TH) { /* per tile row: minima of the row terms, and how far a tile reaches along each axis */
-        const int ax = g2_ld32(a_rx + 16 * lane), bx = g2_ld32(a_rx + 16 * lane + 12), ay = g2_ld32(a_ry + 16 * lane), by = g2_ld32(a_ry + 16 * lane + 12);
-        g2_st64(a_rmin + 8 * lane, make_int2(min(ax, bx), min(ay, by)));
+        const int ax = g2_ld32<G2_RX>(a_w + 16 * lane), bx = g2_ld32<G2_RX>(a_w + 16 * lane + 12), ay = g2_ld32<G2_RY>(a_w + 16 * lane), by = g2_ld32<G2_RY>(a_w + 16 * lane + 12);
+        g2_st64<G2_RMIN>(a_w + 8 * lane, make_int2(min(ax, bx), min(ay, by)));
         spx = abs(ax - bx);
         spy = abs(ay - by);
       }
       if (lane < TW) {
-        const int ax = g2_ld32(a_cx + 16 * lane), bx = g2_ld32(a_cx + 16 * lane + 12), ay = g2_ld32(a_cy + 16 * lane), by = g2_ld32(a_cy + 16 * lane + 12);
-        g2_st64(a_cmin + 8 * lane, make_int2(min(ax, bx), min(ay, by)));
+        const int ax = g2_ld32<G2_CX>(a_w + 16 * lane), bx = g2_ld32<G2_CX>(a_w + 16 * lane + 12), ay = g2_ld32<G2_CY>(a_w + 16 * lane), by = g2_ld32<G2_CY>(a_w + 16 * lane + 12);
+        g2_st64<G2_CMIN>(a_w + 8 * lane, make_int2(min(ax, bx), min(ay, by)));
         cpx = abs(ax - bx);
         cpy = abs(ay - by);
       }
@@ -684,8 +685,8 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           uint32_t bits = 0;
           for (int k = 0; k < 16; k++) {
             const int oy = 4 * ty + (k >> 2), ox = 4 * tx + (k & 3);
-            long long Xl = ((long long)g2_ld32(a_rx + 4 * oy) - BIAS + g2_ld32(a_cx + 4 * ox)) >> 5;
-            long long Yl = ((long long)g2_ld32(a_ry + 4 * oy) - BIAS + g2_ld32(a_cy + 4 * ox)) >> 5;
+            long long Xl = ((long long)g2_ld32<G2_RX>(a_w + 4 * oy) - BIAS + g2_ld32<G2_CX>(a_w + 4 * ox)) >> 5;
+            long long Yl = ((long long)g2_ld32<G2_RY>(a_w + 4 * oy) - BIAS + g2_ld32<G2_CY>(a_w + 4 * ox)) >> 5;
             int X = (int)Xl, Y = (int)Yl;
             int sxi = X >> 5, syi = Y >> 5, fx = X & 31, fy = Y & 31;
             uint32_t v = S(syi, sxi);
@@ -694,7 +695,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
             if (fx > 0 && fy > 0) v |= S(syi + 1, sxi + 1);
             bits |= v << k;
           }
-          g2_stu16(a_tile + 2 * ti, bits);
+          g2_stu16<G2_TILE>(a_w + 2 * ti, bits);
         }
       } else {
         /* ---- pass 1: one lane per 4x4 tile: uniform tiles are done, the others are queued with their code ---- */
@@ -705,14 +706,14 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           const int ty = ti / TW, tx = ti - ty * TW;
           uint32_t code = 1u;
           if (valid) {
-            const int2 rm = g2_ld64(a_rmin + 8 * ty), cm = g2_ld64(a_cmin + 8 * tx);
+            const int2 rm = g2_ld64<G2_RMIN>(a_w + 8 * ty), cm = g2_ld64<G2_CMIN>(a_w + 8 * tx);
             code = g2_ldu8(a_cls + ((rm.y + cm.y) >> 11) * CASIM_G2_CLS_DIM + ((rm.x + cm.x) >> 11)); /* even anchor / 2 */
           }
           const uint32_t kind = code & 7u;
           const bool queued = kind != 1u && kind != 2u;
-          if (valid && !queued) g2_stu16(a_tile + 2 * ti, kind == 2u ? 0xFFFFu : 0u);
+          if (valid && !queued) g2_stu16<G2_TILE>(a_w + 2 * ti, kind == 2u ? 0xFFFFu : 0u);
           const unsigned bq = __ballot_sync(FULL_MASK, queued);
-          if (queued) g2_stu16(a_q + 2 * (nq + __popc(bq & ((1u << lane) - 1u))), ti | (code << 8));
+          if (queued) g2_stu16<G2_Q>(a_w + 2 * (nq + __popc(bq & ((1u << lane) - 1u))), ti | (code << 8));
           nq += __popc(bq);
         }
         __syncwarp();
@@ -721,27 +722,27 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         int no = 0; /* OTHER tiles: compacted in place to the front of the queue (slot no + rank <= the slot just read) */
         for (int m0 = 0; m0 < nq; m0 += 32) {
           const int m = m0 + lane;
-          const uint32_t en = m < nq ? g2_ldu16(a_q + 2 * m) : (1u << 8);
+          const uint32_t en = m < nq ? g2_ldu16<G2_Q>(a_w + 2 * m) : (1u << 8);
           const int ti = (int)(en & 255u);
           const int ty = ti / TW, tx = ti - ty * TW;
           const uint32_t kind = (en >> 8) & 7u, pp = (en >> 11) & 7u;
           const bool other = kind == 0u;
           const unsigned bo = __ballot_sync(FULL_MASK, other);
-          if (other) g2_stu16(a_q + 2 * (no + __popc(bo & ((1u << lane) - 1u))), ti); /* the ballot orders every lane's read first */
+          if (other) g2_stu16<G2_Q>(a_w + 2 * (no + __popc(bo & ((1u << lane) - 1u))), ti); /* the ballot orders every lane's read first */
           no += __popc(bo);
           if (kind >= 3u) {
             uint32_t bits;
             const bool horiz = kind >= 5u, ge = (kind & 1u) != 0u; /* 3, 5: ">= p occupied"; 4, 6: "< p occupied" */
             const int sel = horiz ? 4 : 0; /* .y halves of the (x, y) pairs */
-            const int anc = ((g2_ld32(a_rmin + 8 * ty + sel) + g2_ld32(a_cmin + 8 * tx + sel)) >> 11) << 1;
+            const int anc = ((g2_ld32<G2_RMIN>(a_w + 8 * ty + sel) + g2_ld32<G2_CMIN>(a_w + 8 * tx + sel)) >> 11) << 1;
             /* ge: footprint max index = (v + 992) >> 10 >= anc + p  <=>  v >= (anc + p) * 1024 - 992
              * lt: footprint min index = v >> 10 < anc + p           <=>  v <  (anc + p) * 1024            */
             const int thr = ((anc + (int)pp) << 10) - (ge ? 992 : 0);
-            const int4 rr = g2_ld128((horiz ? a_ry : a_rx) + 16 * ty), cc = g2_ld128((horiz ? a_cy : a_cx) + 16 * tx);
+            const int4 rr = g2_ld128<G2_RX>(a_w + (horiz ? G2_RY - G2_RX : 0) + 16 * ty), cc = g2_ld128<G2_CX>(a_w + (horiz ? G2_CY - G2_CX : 0) + 16 * tx);
             bits = g2_row_lt(cc, thr - rr.x) | (g2_row_lt(cc, thr - rr.y) << 4) | (g2_row_lt(cc, thr - rr.z) << 8) |
                    (g2_row_lt(cc, thr - rr.w) << 12);
             if (ge) bits ^= 0xFFFFu;
-            g2_stu16(a_tile + 2 * ti, bits);
+            g2_stu16<G2_TILE>(a_w + 2 * ti, bits);
           }
         }
         __syncwarp();
@@ -750,10 +751,10 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         for (int m0 = 0; m0 < 4 * no; m0 += 32) {
           const int m = m0 + lane;
           const bool live = m < 4 * no;
-          const int ti = live ? (int)g2_ldu16(a_q + 2 * (m >> 2)) : 0;
+          const int ti = live ? (int)g2_ldu16<G2_Q>(a_w + 2 * (m >> 2)) : 0;
           const int ty = ti / TW, tx = ti - ty * TW, r = m & 3;
-          const int rxx = g2_ld32(a_rx + 4 * (4 * ty + r)), ryy = g2_ld32(a_ry + 4 * (4 * ty + r));
-          const int4 cx = g2_ld128(a_cx + 16 * tx), cy = g2_ld128(a_cy + 16 * tx);
+          const int rxx = g2_ld32<G2_RX>(a_w + 4 * (4 * ty + r)), ryy = g2_ld32<G2_RY>(a_w + 4 * (4 * ty + r));
+          const int4 cx = g2_ld128<G2_CX>(a_w + 16 * tx), cy = g2_ld128<G2_CY>(a_w + 16 * tx);
           uint32_t nib = g2_cell(a_map, rxx + cx.x, ryy + cy.x);
           nib |= g2_cell(a_map, rxx + cx.y, ryy + cy.y) << 1;
           nib |= g2_cell(a_map, rxx + cx.z, ryy + cy.z) << 2;
@@ -761,7 +762,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           nib <<= 4 * r;
           nib |= __shfl_xor_sync(FULL_MASK, nib, 1);
           nib |= __shfl_xor_sync(FULL_MASK, nib, 2);
-          if (live && r == 0) g2_stu16(a_tile + 2 * ti, nib);
+          if (live && r == 0) g2_stu16<G2_TILE>(a_w + 2 * ti, nib);
         }
       }
       __syncwarp();
@@ -771,7 +772,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         const int ti = t0 + lane;
         if (ti < NT) {
           const int ty = ti / TW, tx = ti - ty * TW;
-          const uint32_t q = g2_ldu16(a_tile + 2 * ti);
+          const uint32_t q = g2_ldu16<G2_TILE>(a_w + 2 * ti);
           uint32_t* o = gout + (4 * ty) * TW + tx;
           o[0] = ((q & 0xFu) * 0x00204081u) & 0x01010101u;
           o[TW] = (((q >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
@@ -786,7 +787,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
 #pragma unroll
           for (int k = 0; k < 4; k++) {
             const int w = 4 * i + k, oy = w / TW, wx = w - oy * TW;
-            const uint32_t nib = (g2_ldu16(a_tile + 2 * ((oy >> 2) * TW + wx)) >> (4 * (oy & 3))) & 0xFu;
+            const uint32_t nib = (g2_ldu16<G2_TILE>(a_w + 2 * ((oy >> 2) * TW + wx)) >> (4 * (oy & 3))) & 0xFu;
             v |= (__brev(nib) >> 28) << (4 * (3 - k)); /* cell 0 of the nibble to its top bit; first word in the top nibble */
           }
           pk[i] = (uint16_t)(((v >> 8) & 0xFFu) | ((v & 0xFFu) << 8)); /* byte 0 = cells 0-7 */

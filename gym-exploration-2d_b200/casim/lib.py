@@ -56,6 +56,9 @@ SYMBOLS = {
     "casim_run_sensor": (c_int, [c_void_p, c_void_p, _POBS, c_int, c_void_p]),
     "casim_step_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_double, _POBS, _POBS,
                                 c_void_p]),
+    "casim_step_host_pipelined": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_double, _POBS, _POBS,
+                                          c_void_p, c_void_p, c_void_p]),
+    "casim_host_flush": (c_int, [c_void_p]),
     "casim_explore_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
     "casim_generate_scenario": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

@@ -275,6 +275,13 @@ class BatchedSim:
                 check(rc, "casim_step_host")
         return call
 
+    def host_pipeline(self, fields, packed_grid=True, ext_actions=False, stream=None):
+        """Pipelined host delivery (casim_step_host_pipelined): returns a ``HostPipeline`` whose ``step()`` enqueues one
+        env step and hands back the PREVIOUS step's results in pinned host tensors (one step of latency, D2H copies
+        overlapped with the next step's kernels).  ``fields``: names of the result / observation buffers wanted on the
+        host; with ``packed_grid`` the occupancy grid travels as numpy.packbits bytes (``'local_grid_packed'``)."""
+        return HostPipeline(self, fields, packed_grid, ext_actions, stream)
+
     # ------------------------------------------------------------------------------------------
     # exploration (ig_greedy) and GA3C-CADRL policies: both write into the shared ``policy_actions`` buffer
     def _policy_buffers(self):
@@ -450,6 +457,59 @@ class BatchedSim:
             iw[..., k] = state[..., k].astype(np.int32)
         packs = np.ascontiguousarray(w.reshape(E, A, W // 4, 4).transpose(2, 0, 1, 3))
         self.state.copy_(torch.from_numpy(packs).to(self.device))
+
+
+class HostPipeline:
+    """Two alternating sets of device observation buffers + pinned host buffers around casim_step_host_pipelined.
+    ``step()`` returns the dict of host tensors holding the previous step's results (None on the very first call);
+    ``flush()`` returns the last step's.  A returned dict is valid until the second ``step()`` after it."""
+
+    def __init__(self, sim, fields, packed_grid, ext_actions, stream):
+        self.sim = sim
+        fields = list(fields)
+        self.packed = bool(packed_grid and "local_grid" in fields)
+        if self.packed:
+            fields.remove("local_grid")
+        dev_sets = [dict(sim.buf), {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in sim.buf.items()}]
+        self.dev = [BatchedSim._obs_struct(d) for d in dev_sets]
+        self._dev_keep = dev_sets
+        self.host = []
+        self.host_structs = []
+        self.pk_dev, self.pk_host = [None, None], [None, None]
+        cells = sim.cfg.submap_w * sim.cfg.submap_h
+        for k in range(2):
+            hb = {f: torch.zeros(sim.buf[f].shape, dtype=sim.buf[f].dtype).pin_memory() for f in fields}
+            self.host_structs.append(BatchedSim._obs_struct(hb))
+            if self.packed:
+                self.pk_dev[k] = torch.zeros((sim.E, sim.A, cells // 8), dtype=torch.uint8, device=sim.device)
+                self.pk_host[k] = torch.zeros((sim.E, sim.A, cells // 8), dtype=torch.uint8).pin_memory()
+                hb = dict(hb, local_grid_packed=self.pk_host[k])
+            self.host.append(hb)
+        self.act_host = torch.zeros((sim.E, sim.A, 2), dtype=torch.float32).pin_memory() if ext_actions else None
+        self.act_dev = torch.zeros((sim.E, sim.A, 2), dtype=torch.float32, device=sim.device) if ext_actions else None
+        self.stream = torch.cuda.current_stream(sim.device) if stream is None else stream
+        self.t = 0
+        self.h2d_bytes = self.act_host.numel() * 4 if ext_actions else 0
+        self.d2h_bytes = sum(v.numel() * v.element_size() for v in self.host[0].values())
+        fn = sim.lib.casim_step_host_pipelined
+        self._calls = []
+        for k in range(2):
+            self._calls.append((fn, (sim.handle, _lib.ptr(sim.state), _lib.ptr(self.act_host), _lib.ptr(self.act_dev)),
+                                (ctypes.byref(self.dev[k]), ctypes.byref(self.host_structs[k]), _lib.ptr(self.pk_dev[k]),
+                                 _lib.ptr(self.pk_host[k]), ctypes.c_void_p(self.stream.cuda_stream))))
+
+    def step(self, policy_actions=None, dt=None):
+        k = self.t & 1
+        fn, head, tail = self._calls[k]
+        rc = fn(*head, _lib.ptr(policy_actions), float(dt) if dt is not None else 0.0, *tail)
+        if rc:
+            _lib.check(rc, "casim_step_host_pipelined")
+        self.t += 1
+        return self.host[k ^ 1] if self.t > 1 else None
+
+    def flush(self):
+        _lib.check(self.sim.lib.casim_host_flush(self.sim.handle), "casim_host_flush")
+        return self.host[(self.t - 1) & 1] if self.t > 0 else None
 
 
 def pack_cell_mask(mask):

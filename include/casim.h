@@ -255,6 +255,20 @@ int casim_step_host(casim_handle* h, float* state, const float* ext_actions_host
                     const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
                     void* stream);
 
+/* Pipelined host-buffer step for consumers that want the observations in host memory every step (the reference hands
+ * them out as numpy arrays, agent.py:244-248).  Same arguments as casim_step_host plus an optional bit-packed
+ * local_grid pair (see casim_set_grid_packed_output; when given, the dense local_grid stays on the device and only
+ * 1/8 of its bytes crosses PCIe).  Call t ENQUEUES step t (kernels on `stream`, then the D2H copies of its large results on
+ * an internal copy stream, where they overlap the kernels of step t+1) and returns as soon as step t-1 is complete in
+ * the host buffers that were passed to call t-1 -- ONE STEP OF LATENCY: the caller alternates between two sets of `dev`
+ * observation buffers / `host` buffers / packed buffers (set t & 1), reads set (t-1) & 1 after call t returns, and must be
+ * done with a set before passing it again.  `state` is single (stepped in place).  casim_host_flush waits for the last
+ * step issued.  Not to be mixed with casim_step_host on the same handle while steps are in flight. */
+int casim_step_host_pipelined(casim_handle* h, float* state, const float* ext_actions_host, float* ext_actions_dev,
+                              const float* policy_actions, double dt, const casim_obs* dev, const casim_obs* host,
+                              uint8_t* grid_packed_dev, uint8_t* grid_packed_host, void* stream);
+int casim_host_flush(casim_handle* h);
+
 /* Replaces ig_greedy.find_next_action for every ig_greedy agent (policies/ig_greedy.py:31-93,
  * information_models/targetMap.py:43-147, edfMap.py:14-47): detector emulation from other_agents_states,
  * target-map odds update over the visible cells, one-step greedy information-gain argmax over 9 candidate

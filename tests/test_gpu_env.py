@@ -148,3 +148,44 @@ def test_step_host_delivery_matches_device_step(pinned):
     assert host["done"].any() and host["stats"][6] == E * A
     for s in sims:
         s.close()
+
+
+def test_pipelined_host_step_equals_blocking_steps():
+    """casim_step_host_pipelined: the host buffers handed back by call t hold step t-1, bit for bit what a plain
+    casim_step sequence on a twin simulator produces; the packed grid equals numpy.packbits of the dense one."""
+    import torch
+    from casim import lib, scenarios as S
+    from casim.sim import BatchedSim
+    E, A = 256, 10
+    sens = ("other_agents_states", "laserscan", "local_grid")
+    init, types, n, rects = S.crossing(E, A, seed=11, sensors=L.SENSOR_OTHER_AGENTS | L.SENSOR_LASERSCAN | L.SENSOR_OCCUPANCY_GRID)
+    cfg = lib.default_config()
+    cfg.auto_reset = 1
+    sims = []
+    for _ in range(2):
+        sim = BatchedSim(E, A, cfg=cfg, sensors=sens, want_debug=False)
+        sim.set_obstacles(rects)
+        sim.reset(init, types, n)
+        sims.append(sim)
+    a, b = sims
+    pipe = a.host_pipeline(["rewards", "done", "game_over", "obs_misc", "other_agents_states", "laserscan", "local_grid"])
+    assert pipe.d2h_bytes < 1000 * E * A
+    T = 7
+    refs = []
+    for t in range(T):
+        got = pipe.step()
+        b.step()
+        torch.cuda.synchronize()
+        refs.append({k: v.cpu().clone() for k, v in b.buf.items() if isinstance(v, torch.Tensor)})
+        if t == 0:
+            assert got is None
+            continue
+        want = refs[t - 1]
+        for k in ("rewards", "done", "game_over", "obs_misc", "other_agents_states", "laserscan"):
+            assert torch.equal(got[k], want[k]), (t, k)
+        assert np.array_equal(got["local_grid_packed"].numpy(), np.packbits(want["local_grid"].numpy().reshape(E, A, -1), axis=-1)), t
+    got = pipe.flush()
+    assert torch.equal(got["other_agents_states"], refs[-1]["other_agents_states"])
+    assert np.array_equal(got["local_grid_packed"].numpy(), np.packbits(refs[-1]["local_grid"].numpy().reshape(E, A, -1), axis=-1))
+    for sim in sims:
+        sim.close()
