@@ -782,10 +782,16 @@ def main():
             line["cpu_baseline"] = cpu_baseline_obj(wl, v, threads, "%d steps of %d envs x %d agents, oracle/casim_oracle.c with %d POSIX threads"
                                                     % (n_steps, Es, A, threads))
         emit(line)
+    torch.cuda.synchronize()
+    if world > 1:
+        # Captured NCCL work keeps the communicator busy: destroy_process_group() / interpreter teardown with the graphs
+        # still alive was seen to hang after the line had been printed (r2j, 2 ranks).  Every collective of this run has
+        # completed (synchronize above, nothing follows the JSON line), so the ranks leave without the teardown.
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
     for s in sims:
         s.close()
-    if world > 1:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
