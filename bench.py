@@ -489,13 +489,20 @@ def main():
         sim.reset(init, types, n)
         sims.append(sim)
     torch.cuda.synchronize()
-    launches_per_step = 1 + (1 if "laserscan" in W["sensors"] else 0) + (1 if "local_grid" in W["sensors"] else 0)
-    launches_per_step += 1 if wl in ("c4", "rvo") else (2 if wl == "c5" else 0)
     use_tc = bool(args.ga3c_tc)
 
     stream = torch.cuda.Stream(device=dev)
-    side = torch.cuda.Stream(device=dev)
+    from casim.dist import StatsReducer
+    reducer = StatsReducer(device=dev)
+    side = reducer.stream
     collective = (not args.no_collective) and (not args.no_stats)
+    stats_events = []
+    if collective:                    # the statistics are final right after k_core: the library records this event there
+        for sm in sims:
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            sm.set_stats_event(ev)
+            stats_events.append(ev)
 
     def policy_step(sim):
         if wl == "c4":
@@ -516,16 +523,16 @@ def main():
             if not args.no_stats:
                 sim._obs.stats = row.data_ptr()
             sim.step(policy_actions=policy_step(sim))
-            if collective and reduce_stats:
-                side.wait_stream(stream)
-                with torch.cuda.stream(side):
-                    if world > 1:
-                        dist.all_reduce(row, op=dist.ReduceOp.SUM)
+            if collective and reduce_stats:            # NCCL all-reduce of this step's row, overlapping its sensor kernels
+                reducer.reduce_row(row, ready_event=stats_events[i % R])
         if collective and reduce_stats:
-            stream.wait_stream(side)
+            reducer.wait()
 
     with torch.cuda.stream(stream):
         run_steps(0, Wm)                                  # warm-up (also loads the kernels, creates the NCCL communicator)
+        n0 = sims[0].launch_count()                       # kernels per step: counted by the library, not assumed
+        run_steps(0, 1)
+        launches_per_step = sims[0].launch_count() - n0
     stream.synchronize()
     side.synchronize()
 
@@ -708,14 +715,21 @@ def main():
     kern = {}          # name -> (seconds per launch, algorithmic units per launch, how)
     NA = E * A
     t_sens = 0.0
-    if "laserscan" in W["sensors"]:
-        t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_LASERSCAN))
-        kern["k_laser"] = (t, BYTES_LASER * NA, "timed alone", MUST_LASER * NA + (MAP_PLANE_BYTES * E if per_env_maps else 0))
+    fused = "laserscan" in W["sensors"] and "local_grid" in W["sensors"] and not per_env_maps
+    if fused:
+        # shared map: ONE persistent kernel (k_grid_tma) stages the map in shared memory and produces both observations
+        t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_LASERSCAN | LY.SENSOR_OCCUPANCY_GRID))
+        kern["k_grid_tma(grid+laser)"] = (t, (BYTES_GRID + BYTES_LASER) * NA, "timed alone", (MUST_GRID + MUST_LASER) * NA)
         t_sens += t
-    if "local_grid" in W["sensors"]:
-        t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_OCCUPANCY_GRID))
-        kern["k_grid"] = (t, BYTES_GRID * NA, "timed alone", MUST_GRID * NA + (MAP_PLANE_BYTES * E if per_env_maps else 0))
-        t_sens += t
+    else:
+        if "laserscan" in W["sensors"]:
+            t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_LASERSCAN))
+            kern["k_laser"] = (t, BYTES_LASER * NA, "timed alone", MUST_LASER * NA + (MAP_PLANE_BYTES * E if per_env_maps else 0))
+            t_sens += t
+        if "local_grid" in W["sensors"]:
+            t = time_alone(lambda sm: sm.run_sensor(LY.SENSOR_OCCUPANCY_GRID))
+            kern["k_grid"] = (t, BYTES_GRID * NA, "timed alone", MUST_GRID * NA + (MAP_PLANE_BYTES * E if per_env_maps else 0))
+            t_sens += t
     explore_counts = None
     if wl == "c4":
         t = time_alone(lambda sm: sm.explore_step())

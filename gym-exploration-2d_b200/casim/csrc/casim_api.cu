@@ -316,6 +316,12 @@ int casim_set_map(casim_handle* h, const uint8_t* static_map, int n_maps, void* 
   return 0;
 }
 
+int casim_set_stats_event(casim_handle* h, void* cuda_event) {
+  REQUIRE(h, "null handle");
+  h->stats_event = (cudaEvent_t)cuda_event;
+  return 0;
+}
+
 int casim_set_grid_packed_output(casim_handle* h, uint8_t* packed) {
   REQUIRE(h, "null handle");
   REQUIRE((((uintptr_t)packed) & 1) == 0, "packed local_grid buffer must be 2-byte aligned");
@@ -338,6 +344,11 @@ static int check_obs(const casim_handle* h, const casim_obs* obs) {
 }
 
 static int run_sensors(casim_handle* h, const float* state, const casim_obs* obs, cudaStream_t s) {
+  /* both map sensors on a shared map: ONE persistent kernel stages the map once and produces both observations */
+  if (obs->laserscan && obs->local_grid && casim_grid_can_fuse_laser(h, obs->local_grid)) {
+    CK(casim_launch_grid(h, state, obs->local_grid, s, obs->laserscan));
+    return 0;
+  }
   if (obs->laserscan) CK(casim_launch_laser(h, state, obs->laserscan, s));
   if (obs->local_grid) CK(casim_launch_grid(h, state, obs->local_grid, s));
   return 0;
@@ -385,6 +396,7 @@ int casim_step(casim_handle* h, float* state, const float* ext_actions, const fl
   cudaStream_t s = (cudaStream_t)stream;
   double dtd = dt > 0 ? dt : h->cfg.dt;
   CK(casim_launch_core(h, CASIM_MODE_STEP, state, ext_actions, policy_actions, dtd, obs, s));
+  if (h->stats_event) CK(cudaEventRecord(h->stats_event, s)); /* rewards / done / game_over / stats are final from here */
   return run_sensors(h, state, obs, s);
 }
 
@@ -397,8 +409,11 @@ int casim_run_sensor(casim_handle* h, const float* state, const casim_obs* obs, 
   } else if (which == CASIM_SENSOR_OCCUPANCY_GRID) {
     REQUIRE(obs->local_grid, "local_grid buffer missing");
     CK(casim_launch_grid(h, state, obs->local_grid, s));
+  } else if (which == (CASIM_SENSOR_LASERSCAN | CASIM_SENSOR_OCCUPANCY_GRID)) {
+    REQUIRE(obs->local_grid && obs->laserscan, "sensor buffer missing");
+    return run_sensors(h, state, obs, s); /* what casim_step launches: fused when the map is shared */
   } else {
-    REQUIRE(false, "which must be CASIM_SENSOR_LASERSCAN or CASIM_SENSOR_OCCUPANCY_GRID");
+    REQUIRE(false, "which must be CASIM_SENSOR_LASERSCAN, CASIM_SENSOR_OCCUPANCY_GRID or both");
   }
   return 0;
 }

@@ -117,6 +117,7 @@ struct casim_handle {
   cudaStream_t pipe_stream;
   cudaEvent_t pipe_ev_kernels[2], pipe_ev_copied[2];
   unsigned long long pipe_steps;
+  cudaEvent_t stats_event; /* casim_set_stats_event: recorded right after the step kernel (the statistics are final then) */
   unsigned long long launches;
 };
 
@@ -127,7 +128,9 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
                               const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s,
                               const uint8_t* reset_mask = nullptr);
 cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laserscan, cudaStream_t s);
-cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s);
+cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s,
+                              float* fused_laser = nullptr);
+bool casim_grid_can_fuse_laser(const casim_handle* h, const uint8_t* local_grid);
 cudaError_t casim_launch_raster(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps,
                                 int max_rects, cudaStream_t s);
 cudaError_t casim_launch_pack_map(casim_handle* h, const uint8_t* static_map, int n_maps, cudaStream_t s);

@@ -458,7 +458,10 @@ __global__ void __launch_bounds__(32 * GRID_WARPS, GRID_MINB) k_grid_gather(cons
 /* per warp: tiles[256] uint16 (bit 4r+k = cell (row r, column k) of the 4x4 tile), s_rx, s_ry, s_cx, s_cy [64] int,
  * s_rmin[16] int2, s_cmin[16] int2, queue[256] uint16 */
 #define G2_WARP_BYTES (256 * 2 + 4 * 64 * 4 + 16 * 8 + 16 * 8 + 256 * 2)
-#define G2_SMEM_BYTES (CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES + 16) /* + mbarrier (8 B) + ticket counter (4 B) */
+/* + mbarrier (8 B) + ticket counter (4 B) + the laser tables: cos, sin of the beam angles, range samples (doubles),
+ * reported values (floats) */
+#define G2_LASER_OFF (CASIM_G2_BYTES + G2_WARPS * G2_WARP_BYTES + 16)
+#define G2_SMEM_BYTES (G2_LASER_OFF + 3 * CASIM_MAX_BEAMS * 8 + (CASIM_MAX_RANGES + 1) * 4 + 12)
 
 struct Grid2Args {
   DevCfg c;
@@ -468,6 +471,8 @@ struct Grid2Args {
   const uint32_t* map_planes; /* unpadded plane 0 (slow path) */
   uint8_t* out;
   uint8_t* packed;            /* optional np.packbits form, or NULL */
+  float* laser;               /* LaserScanSensor output [E*A][nb] when the laser rides in this kernel, else NULL */
+  int lg2P;                   /* laser: lanes per beam = 1 << lg2P */
   int E, A;
 };
 
@@ -545,10 +550,24 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           "l"(&tmap), "r"(0), "r"(k * CASIM_G2_BOX_ROWS), "r"(bar)
           : "memory");
   }
+  const DevCfg& c = p.c;
+  /* laser tables (lane-dependent indices: shared memory, not the constant bank) */
+  double* s_lcos = reinterpret_cast<double*>(g2_smem + G2_LASER_OFF);
+  double* s_lsin = s_lcos + CASIM_MAX_BEAMS;
+  double* s_lr = s_lsin + CASIM_MAX_BEAMS;
+  float* s_lout = reinterpret_cast<float*>(s_lr + CASIM_MAX_RANGES);
+  if (p.laser != nullptr) {
+    static_assert(CASIM_MAX_BEAMS == CASIM_MAX_RANGES, "one fill loop for both tables");
+    if (threadIdx.x < CASIM_MAX_BEAMS) {
+      s_lcos[threadIdx.x] = c.laser_cos[threadIdx.x];
+      s_lsin[threadIdx.x] = c.laser_sin[threadIdx.x];
+      s_lr[threadIdx.x] = c.laser_r[threadIdx.x];
+    }
+    if (threadIdx.x <= CASIM_MAX_RANGES) s_lout[threadIdx.x] = c.laser_out[threadIdx.x];
+  }
   casim_pdl_enter();
   __syncthreads(); /* the barrier word is initialised for everybody */
 
-  const DevCfg& c = p.c;
   const unsigned N = (unsigned)p.E * (unsigned)p.A;
   const int H = CTW ? 4 * CTW : c.submap_h, W = CTH ? 4 * CTH : c.submap_w; /* out[oy*H + ox]: W rows of H cells */
   const int TW = H >> 2, TH = W >> 2;                                       /* 4x4 tiles */
@@ -571,12 +590,14 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
   bool map_ready = false;
   /* an agent's inputs: loaded one agent ahead, so that their global-memory latency hides behind the previous agent */
   int in_type = 0, in_n = 0;
+  float in_radius = 0.f;
   double2 in_q0 = make_double2(0., 0.), in_q1 = make_double2(0., 0.);
   auto fetch = [&](unsigned ag) {
     if (ag < N) {
       const int ee = (int)(ag / (unsigned)p.A);
       in_n = p.n_agents ? min(p.n_agents[ee], p.A) : p.A;
       in_type = __float_as_int(p.state[5 * (size_t)N + ag].w);
+      if (p.laser != nullptr) in_radius = p.state[2 * (size_t)N + ag].z;
       in_q0 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)ag)[0];
       in_q1 = reinterpret_cast<const double2*>(p.pose64 + 4 * (size_t)ag)[1];
     }
@@ -589,6 +610,55 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
     const int type = in_type;
     const double2 q0 = in_q0, q1 = in_q1;
     const bool on = ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_OCCUPANCY_GRID);
+    if (p.laser != nullptr) {
+      /* ---- LaserScanSensor (LaserScanSensor.py:27-58) riding in this kernel: same arithmetic as k_laser above, the
+       * 256 lattice samples read plane 0 of the map staged in shared memory ---- */
+      const int nb = c.nb, nr = c.nr;
+      float* lout = p.laser + (size_t)g * nb;
+      if (!(ai < n && (((type >> 16) & 0xff) & CASIM_SENSOR_LASERSCAN))) {
+        for (int b = lane; b < nb; b += 32) lout[b] = 0.f;
+      } else {
+        if (!map_ready) {
+          g2_wait_map(bar);
+          map_ready = true;
+        }
+        const double px = q0.x, py = q0.y, ch = q1.x, sh = q1.y;
+        int r0, c0;
+        const bool ego_in = world_to_map_mul(c, px, py, r0, c0);
+        const double rc = (double)in_radius * c.inv_cell, rc2 = rc * rc;
+        const int disc_thr = ego_in ? (int)fmin(ceil(rc2), 2.0e9) - 1 : -1; /* d^2 < rc2 <=> d^2 <= ceil(rc2) - 1 */
+        const int P = 1 << p.lg2P;
+        const int b = lane >> p.lg2P, part = lane & (P - 1);
+        unsigned mask = 0;
+        if (b < nb) {
+          const double cs = s_lcos[b] * ch - s_lsin[b] * sh, sn = s_lsin[b] * ch + s_lcos[b] * sh;
+          const double u0 = c.map_oy + px * c.inv_cell, du = cs * c.inv_cell;
+          const double v0 = c.map_ox - py * c.inv_cell, dv = -(sn * c.inv_cell);
+          for (int k = part; k < nr; k += P) {
+            const double rk = s_lr[k];
+            const int col = __double2int_rd(fma(rk, du, u0)), row = __double2int_rd(fma(rk, dv, v0));
+            if ((unsigned)row < (unsigned)CASIM_MAP_DIM && (unsigned)col < (unsigned)CASIM_MAP_DIM) {
+              const int pc = col + CASIM_G2_PAD;
+              uint32_t w;
+              asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(a_map + 4u * (uint32_t)((row + CASIM_G2_PAD) * CASIM_G2_WORDS + (pc >> 5))));
+              if ((w >> (pc & 31)) & 1u) {
+                const int dr = row - r0, dc = col - c0;
+                if (dr * dr + dc * dc > disc_thr) mask |= 1u << k;
+              }
+            }
+          }
+        }
+        for (int o = 1; o < P; o <<= 1) mask |= __shfl_xor_sync(FULL_MASK, mask, o);
+        if (b < nb && part == 0) {
+          int idx = CASIM_MAX_RANGES; /* no hit: max range */
+          if (mask) {
+            const unsigned rest = mask & (mask - 1); /* drop the first hit */
+            idx = rest ? (__ffs(rest) - 2) : (nr - 1);
+          }
+          lout[b] = s_lout[idx];
+        }
+      }
+    }
     if (!on) {
       uint4* g4 = reinterpret_cast<uint4*>(gout);
       for (int i = lane; i < (cells >> 4); i += 32) g4[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -870,7 +940,14 @@ cudaError_t casim_grid2_encode_tmap(casim_handle* h) {
   return cudaSuccess;
 }
 
-cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s) {
+/* The shared-map occupancy-grid kernel can carry the LaserScanSensor too (both read the same staged map). */
+bool casim_grid_can_fuse_laser(const casim_handle* h, const uint8_t* local_grid) {
+  const int cells = h->dc.submap_w * h->dc.submap_h;
+  return h->n_maps == 1 && h->grid2_map != nullptr && (h->dc.submap_h & 3) == 0 && (h->dc.submap_w & 3) == 0 &&
+         (cells & 15) == 0 && (((uintptr_t)local_grid) & 15) == 0 && (long long)h->E * h->A < (1ll << 31);
+}
+
+cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s, float* fused_laser) {
   if (h->dc.submap_w > 64 || h->dc.submap_h > 64) return cudaErrorInvalidValue;
   GridArgs a;
   a.c = h->dc;
@@ -913,6 +990,13 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
     b.map_planes = h->map_planes;
     b.out = local_grid;
     b.packed = h->grid_packed;
+    b.laser = fused_laser;
+    {
+      int nbp = 1, lg = 5;
+      while (nbp < h->dc.nb) nbp <<= 1;
+      for (int t = nbp; t > 1; t >>= 1) lg--;
+      b.lg2P = lg;
+    }
     b.E = h->E;
     b.A = h->A;
     const long long want = (N + G2_WARPS - 1) / G2_WARPS;
@@ -929,6 +1013,7 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
     cfg.numAttrs = casim_pdl_enabled() ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, *reinterpret_cast<const CUtensorMap*>(h->grid2_tmap), b);
   }
+  if (fused_laser) return cudaErrorInvalidValue; /* the caller checks casim_grid_can_fuse_laser first */
   if (fast)
     err = casim_launch_pdl<GridArgs>(k_grid_gather, dim3((unsigned)((N + GRID_WARPS - 1) / GRID_WARPS)), dim3(32 * GRID_WARPS), 0, s, a);
   else

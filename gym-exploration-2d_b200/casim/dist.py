@@ -52,6 +52,24 @@ class StatsReducer:
                 dist.all_reduce(self.total, op=dist.ReduceOp.SUM)
         return self.total
 
+    def reduce_row(self, row, ready_event=None):
+        """In-place all_reduce(SUM) of one statistics row on the side stream, which first waits for ``ready_event`` (the
+        event casim_set_stats_event records after the step kernel) or, without one, for the current stream.  The row
+        must not be rewritten before ``wait()`` (bench.py gives every step of a CUDA graph its own row)."""
+        if self.stream is None:
+            if self.world > 1:
+                dist.all_reduce(row, op=dist.ReduceOp.SUM)
+            return row
+        if ready_event is not None:
+            self.stream.wait_event(ready_event)
+        else:
+            self.stream.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self.stream):
+            if self.world > 1:
+                dist.all_reduce(row, op=dist.ReduceOp.SUM)
+        self.total = row
+        return row
+
     def wait(self):
         if self.stream is not None:
             torch.cuda.current_stream(self.device).wait_stream(self.stream)

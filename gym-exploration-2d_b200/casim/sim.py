@@ -136,6 +136,13 @@ class BatchedSim:
         torch.cuda.current_stream().synchronize()
         self.has_map = True
 
+    def set_stats_event(self, event):
+        """casim_set_stats_event: ``event`` (a torch.cuda.Event that has been recorded at least once, or None) is recorded
+        by every ``step`` right after the fused step kernel, when the episode statistics are final."""
+        self._keep["stats_event"] = event
+        _lib.check(self.lib.casim_set_stats_event(self.handle, ctypes.c_void_p(event.cuda_event) if event is not None else None),
+                   "casim_set_stats_event")
+
     def enable_packed_grid(self, on=True):
         """Second delivery format of ``local_grid`` (casim_set_grid_packed_output): ``buf['local_grid_packed']``
         uint8 [E, A, w*h/8] = numpy.packbits of every agent's grid, written by every later step next to the dense form."""

@@ -198,6 +198,14 @@ int casim_set_obstacles(casim_handle* h, const float* rects, const int32_t* n_re
 /* Same, from a ready-made occupancy raster [n_maps,300,300] uint8 (Map.static_map). */
 int casim_set_map(casim_handle* h, const uint8_t* static_map, int n_maps, void* stream);
 
+/* Multi-GPU statistics hook (the per-step all-reduce of the [8] episode statistics, the design's only
+ * collective; the reference's counterpart is the rolling n_collisions / n_timeouts of collision_avoidance_env.py:147-148,
+ * 218-221).  When an event (cudaEvent_t passed as void*) is set, every casim_step records it on its stream right after
+ * the fused step kernel -- rewards, done, game_over and stats are final at that point, the sensor kernels that follow do
+ * not touch them -- so that a side stream can wait on it and start the collective while the sensors still run.
+ * NULL turns it off.  Works under stream capture. */
+int casim_set_stats_event(casim_handle* h, void* cuda_event);
+
 /* Optional second delivery format of the OccupancyGrid observation (OccupancyGridSensor.py:98 returns a bool array):
  * when `packed` is non-NULL every later casim_step / casim_reset / casim_observe ALSO writes each agent's grid bit-packed,
  * ceil(submap_w*submap_h/8) bytes per agent = numpy.packbits(local_grid[e,a].ravel()) (first cell in the most significant
@@ -240,7 +248,9 @@ int casim_step(casim_handle* h, float* state, const float* ext_actions, const fl
 
 /* Profiling / benchmark aid: launch ONE sensor kernel -- `which` = CASIM_SENSOR_LASERSCAN (LaserScanSensor.py:27-58)
  * or CASIM_SENSOR_OCCUPANCY_GRID (OccupancyGridSensor.py:70-98) -- on the post-move poses left by the last
- * casim_step / casim_reset / casim_observe of this handle, so that the kernel can be timed alone. */
+ * casim_step / casim_reset / casim_observe of this handle, so that the kernel can be timed alone; the OR of the two =
+ * the sensor launches of a step as casim_step issues them (with a map shared by all environments both observations
+ * come out of one kernel that stages the map in shared memory once). */
 int casim_run_sensor(casim_handle* h, const float* state, const casim_obs* obs, int which, void* stream);
 
 /* Host-buffer variant: ext_actions_host (pinned, may be NULL) is copied H2D, the step runs, and rewards, done and
