@@ -425,6 +425,8 @@ def main():
     ap.add_argument("--ga3c-tc", action="store_true", help="c5: bf16 tensor-core forward (default: the fp32 forward, whose "
                     "action index equals the reference network's on every decisive state)")
     ap.add_argument("--no-stats", action="store_true", help="diagnostics: do not compute the per-step episode statistics")
+    ap.add_argument("--steps-per-launch", type=int, default=1, help="c2 / c3 / full: casim_step_n, this many env steps per "
+                    "kernel launch with the state in registers (in-kernel policies); K must be a multiple of it")
     ap.add_argument("--ring", type=int, default=None, help="override the number of env batches in the ring (diagnostics)")
     args = ap.parse_args()
     guard_stdout()
@@ -491,6 +493,9 @@ def main():
     torch.cuda.synchronize()
     use_tc = bool(args.ga3c_tc)
 
+    spl = max(1, int(args.steps_per_launch))
+    if spl > 1:
+        assert wl in ("c2", "c3", "full") and K % spl == 0 and Wm % spl == 0, "--steps-per-launch: c2/c3/full, K and W multiples of it"
     stream = torch.cuda.Stream(device=dev)
     from casim.dist import StatsReducer
     reducer = StatsReducer(device=dev)
@@ -517,6 +522,15 @@ def main():
         """Steps k0 .. k0+k-1 on `stream` (current).  Step i writes its episode statistics into row i of `stats_rows`
         (one row per step of the graph, so nothing has to be cloned) and the row is all-reduced across the ranks on
         the side stream while the next step's kernels run."""
+        if spl > 1:                       # casim_step_n: spl steps per launch, each launch on the next ring batch
+            for j, i in enumerate(range(k0, k0 + k, spl)):
+                sim = sims[j % R]
+                ring = sim.step_n(spl)
+                if collective and reduce_stats:
+                    reducer.reduce_row(ring["stats"], ready_event=stats_events[j % R])
+            if collective and reduce_stats:
+                reducer.wait()
+            return
         for i in range(k0, k0 + k):
             sim = sims[i % R]
             row = stats_rows[i % stats_rows.shape[0]]
@@ -531,8 +545,8 @@ def main():
     with torch.cuda.stream(stream):
         run_steps(0, Wm)                                  # warm-up (also loads the kernels, creates the NCCL communicator)
         n0 = sims[0].launch_count()                       # kernels per step: counted by the library, not assumed
-        run_steps(0, 1)
-        launches_per_step = sims[0].launch_count() - n0
+        run_steps(0, spl)
+        launches_per_step = (sims[0].launch_count() - n0) / spl
     stream.synchronize()
     side.synchronize()
 
@@ -585,7 +599,7 @@ def main():
         ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
-    stats_last = stats_rows[:K].clone()
+    stats_last = stats_rows[:K].clone() if spl == 1 else torch.cat([sm._ring["stats"] for sm in sims[:max(1, min(R, K // spl))]])
     # keep the same workload running ~1.2 s so that nvidia-smi (50 ms period) sees the clocks under this load
     t_end = time.perf_counter() + 1.2
     with torch.cuda.stream(stream):
@@ -778,10 +792,11 @@ def main():
                     "collective_in_timed_region": ("all_reduce(SUM) of the [8] statistics row of every step, side stream, "
                                                    + ("NCCL over %d ranks" % world if world > 1 else "1 rank: stream fork/join only"))
                     if collective else "off (--no-collective / --no-stats)",
+                    "steps_per_launch": spl,
                     "ga3c_forward": ("bf16 tcgen05" if use_tc else "fp32") if wl == "c5" else None},
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": Ke, "call": e2e_call},
-            "gpu_launches": launches_per_step * K * reps,
+            "gpu_launches": int(round(launches_per_step * K * reps)),
             "roofline": roofline_obj(wl, kern, dominant, step_s,
                                      sum(v[1] for k, v in kern.items() if not k.startswith("k_ga3c")),
                                      sum(v[3] for k, v in kern.items() if not k.startswith("k_ga3c")), explore_counts),

@@ -199,11 +199,15 @@ int casim_create(const casim_config* cfg, int E, int A, casim_handle** out) {
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->prev_game_over, (size_t)E);
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->state0, N * 24 * sizeof(float));
   if (e == cudaSuccess) e = cudaMemset(h->state0, 0, N * 24 * sizeof(float));
-  if (e == cudaSuccess) e = cudaMalloc((void**)&h->partials, (size_t)(h->max_ctas > 32 ? h->max_ctas : 32) * CASIM_NUM_STATS * sizeof(double));
+  /* statistics accumulators: 8 words 64 B apart per step of a launch (casim_step_n: up to CASIM_STEP_N_MAX steps) */
+  const size_t partial_words = (size_t)(h->max_ctas > 32 ? h->max_ctas : 32) * CASIM_NUM_STATS > (size_t)CASIM_STEP_N_MAX * 64
+                                   ? (size_t)(h->max_ctas > 32 ? h->max_ctas : 32) * CASIM_NUM_STATS
+                                   : (size_t)CASIM_STEP_N_MAX * 64;
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->partials, partial_words * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc((void**)&h->ticket, sizeof(unsigned int));
   if (e == cudaSuccess) e = cudaMemset(h->prev_game_over, 0, (size_t)E);
   if (e == cudaSuccess) e = cudaMemset(h->ticket, 0, sizeof(unsigned int));
-  if (e == cudaSuccess) e = cudaMemset(h->partials, 0, (size_t)(h->max_ctas > 32 ? h->max_ctas : 32) * CASIM_NUM_STATS * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemset(h->partials, 0, partial_words * sizeof(double));
   if (e == cudaSuccess) e = cudaMemset(h->pose64, 0, N * 4 * sizeof(double));
   if (e != cudaSuccess) {
     casim_set_error("casim_create: %s", cudaGetErrorString(e));
@@ -397,6 +401,19 @@ int casim_step(casim_handle* h, float* state, const float* ext_actions, const fl
   double dtd = dt > 0 ? dt : h->cfg.dt;
   CK(casim_launch_core(h, CASIM_MODE_STEP, state, ext_actions, policy_actions, dtd, obs, s));
   if (h->stats_event) CK(cudaEventRecord(h->stats_event, s)); /* rewards / done / game_over / stats are final from here */
+  return run_sensors(h, state, obs, s);
+}
+
+int casim_step_n(casim_handle* h, float* state, const float* policy_actions, double dt, int n_steps, const casim_obs* obs,
+                 void* stream) {
+  REQUIRE(h && state, "null argument");
+  REQUIRE(n_steps >= 1 && n_steps <= CASIM_STEP_N_MAX, "casim_step_n: n_steps must be in 1..CASIM_STEP_N_MAX");
+  int rc = check_obs(h, obs);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  double dtd = dt > 0 ? dt : h->cfg.dt;
+  CK(casim_launch_core(h, CASIM_MODE_STEP, state, nullptr, policy_actions, dtd, obs, s, nullptr, n_steps));
+  if (h->stats_event) CK(cudaEventRecord(h->stats_event, s));
   return run_sensors(h, state, obs, s);
 }
 

@@ -122,11 +122,11 @@ struct casim_handle {
 };
 
 /* ---- launchers (host functions defined in the .cu files) ---- */
-enum { CASIM_MODE_STEP = 0, CASIM_MODE_RESET = 1, CASIM_MODE_OBSERVE = 2 };
+enum { CASIM_MODE_STEP = 0, CASIM_MODE_RESET = 1, CASIM_MODE_OBSERVE = 2, CASIM_MODE_STEP_N = 3 };
 
 cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const float* ext_actions,
                               const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s,
-                              const uint8_t* reset_mask = nullptr);
+                              const uint8_t* reset_mask = nullptr, int n_steps = 1);
 cudaError_t casim_launch_laser(casim_handle* h, const float* state, float* laserscan, cudaStream_t s);
 cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* local_grid, cudaStream_t s,
                               float* fused_laser = nullptr);

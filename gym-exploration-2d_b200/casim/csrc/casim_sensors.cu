@@ -634,18 +634,18 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
           const double cs = s_lcos[b] * ch - s_lsin[b] * sh, sn = s_lsin[b] * ch + s_lcos[b] * sh;
           const double u0 = c.map_oy + px * c.inv_cell, du = cs * c.inv_cell;
           const double v0 = c.map_ox - py * c.inv_cell, dv = -(sn * c.inv_cell);
+          /* branch-free: out-of-map samples read a clamped address and are masked out afterwards */
+#pragma unroll 4
           for (int k = part; k < nr; k += P) {
             const double rk = s_lr[k];
             const int col = __double2int_rd(fma(rk, du, u0)), row = __double2int_rd(fma(rk, dv, v0));
-            if ((unsigned)row < (unsigned)CASIM_MAP_DIM && (unsigned)col < (unsigned)CASIM_MAP_DIM) {
-              const int pc = col + CASIM_G2_PAD;
-              uint32_t w;
-              asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(a_map + 4u * (uint32_t)((row + CASIM_G2_PAD) * CASIM_G2_WORDS + (pc >> 5))));
-              if ((w >> (pc & 31)) & 1u) {
-                const int dr = row - r0, dc = col - c0;
-                if (dr * dr + dc * dc > disc_thr) mask |= 1u << k;
-              }
-            }
+            const bool in = (unsigned)row < (unsigned)CASIM_MAP_DIM && (unsigned)col < (unsigned)CASIM_MAP_DIM;
+            const int pr = min(max(row, 0), CASIM_MAP_DIM - 1) + CASIM_G2_PAD, pc = min(max(col, 0), CASIM_MAP_DIM - 1) + CASIM_G2_PAD;
+            uint32_t w;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(a_map + 4u * (uint32_t)(pr * CASIM_G2_WORDS + (pc >> 5))));
+            const int dr = row - r0, dc = col - c0;
+            const bool hit = in && ((w >> (pc & 31)) & 1u) && (dr * dr + dc * dc > disc_thr);
+            mask |= (hit ? 1u : 0u) << k;
           }
         }
         for (int o = 1; o < P; o <<= 1) mask |= __shfl_xor_sync(FULL_MASK, mask, o);

@@ -63,6 +63,7 @@ struct CoreArgs {
   casim_obs o;
   double dt;
   int E, A, T, n_maps, epw, write_pose, diag;
+  int n_steps; /* STEP mode: steps per launch (casim_step_n); rewards / done / game_over / stats are [n_steps, ...] rings */
 };
 
 struct Agent {
@@ -324,6 +325,9 @@ __device__ __forceinline__ void take_action(const DevCfg& c, Agent& a, float a0,
 template <int MODE, int AP>
 __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   extern __shared__ __align__(16) float s_stage[];
+  /* CASIM_MODE_STEP_N = the same step body run n_steps times per launch; its own instantiation, so that the loop-carried
+   * state does not cost the single-step kernel registers */
+  constexpr bool IS_STEP = MODE == CASIM_MODE_STEP || MODE == CASIM_MODE_STEP_N;
   casim_pdl_enter();
   const DevCfg& c = p.c;
   const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
@@ -344,15 +348,23 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   /* caller-supplied actions: one coalesced 8-byte read per lane.  In the host-buffer step the source is mapped host
    * memory (the read crosses PCIe while the state loads are in flight) and the device copy is refreshed here. */
   float2 ea = make_float2(0.f, 0.f);
-  const bool have_ext = MODE == CASIM_MODE_STEP && p.ext_actions != nullptr;
+  const bool have_ext = IS_STEP && p.ext_actions != nullptr;
   if (have_ext && slot) {
     ea = reinterpret_cast<const float2*>(p.ext_actions)[g];
     if (p.ext_copy_dst) p.ext_copy_dst[g] = ea;
   }
 
+  /* casim_step_n: the whole body below runs n_steps times per launch with the agent's state in registers (in-kernel
+   * policies only); per-step rewards / done / game_over / stats go to [n_steps, ...] rings, the observations and the
+   * state are those of the last step.  A single step is n_steps == 1. */
+  const int nsteps = MODE == CASIM_MODE_STEP_N ? p.n_steps : 1;
   Agent a;
-  int old_flags = 0;
   bool wrote_all = false;
+  int go_prev = 0; /* my environment's game_over of the previous step of this launch */
+#pragma unroll 1
+  for (int it = 0; it < nsteps; it++) {
+  const bool last = it == nsteps - 1;
+  int old_flags = 0;
   if (valid) {
     if (MODE == CASIM_MODE_RESET) {
       agent_init(c, p.init + g * 7, p.type0[g], a);
@@ -360,11 +372,12 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     } else {
       /* auto_reset (the env's reset() folded into the next step): the episode-start state is the one casim_reset
        * stored, i.e. exactly what reset() followed by step() would read */
-      const bool fresh = MODE == CASIM_MODE_STEP && c.auto_reset && p.init && p.prev_game_over[e];
-      load_agent(fresh ? p.state0 : p.state, plane, g, a);
-      wrote_all = fresh;
+      const bool fresh = IS_STEP && c.auto_reset && p.init && (it == 0 ? p.prev_game_over[e] != 0 : go_prev != 0);
+      if (it == 0 || fresh) load_agent(fresh ? p.state0 : p.state, plane, g, a);
+      a.have_cs = false;
+      wrote_all = wrote_all || fresh || it > 0;
     }
-  } else {
+  } else if (it == 0) {
     a.px = a.py = a.heading = a.turning = a.t = a.trem = a.cs = a.sn = 0;
     a.speed = a.vx = a.vy = a.dheading = a.gx = a.gy = a.radius = a.pref = a.dgoal = a.pdgoal = 0.f;
     a.a0v = a.a0w = a.a1v = a.a1w = a.hego = 0.f;
@@ -372,7 +385,7 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     a.have_cs = false;
   }
 
-  if (MODE == CASIM_MODE_STEP && valid) {
+  if (IS_STEP && valid) {
     old_flags = a.flags;
     float a0, a1;
     choose_action(c, a, have_ext, ea, p.policy_actions, g, a0, a1);
@@ -382,14 +395,14 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   /* ---- all pairs of my environment ---- */
   const bool me_static = (a.type & 0xff) == CASIM_POLICY_STATIC;
   const int sensors = (a.type >> 16) & 0xff;
-  const bool want_oas = p.o.other_agents_states != nullptr;
+  const bool want_oas = p.o.other_agents_states != nullptr && last;
   const double rme = (double)a.radius;
   float d32[AP];
   const bool need_dist = want_oas || p.o.nearest_dist != nullptr;
   const double close_band = c.close_range + 1e-3;
   bool coll_agent = false, amb = false;
   float nearest = INFINITY;
-  if (MODE == CASIM_MODE_STEP || want_oas) {
+  if (IS_STEP || want_oas) {
 #pragma unroll
     for (int j = 0; j < AP; j++) {
       int src = (base + j) & 31;
@@ -403,7 +416,7 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
         d = sqrtf((float)s);
         d32[j] = d;
       }
-      if (MODE == CASIM_MODE_STEP && valid && j < n && j != ai) {
+      if (IS_STEP && valid && j < n && j != ai) {
         /* pair (lo, hi): skipped when the HIGHER index is Static (collision_avoidance_env.py:643-644) */
         bool hi_static = j > ai ? (ostatic != 0) : me_static;
         if (!(hi_static && !c.coll_w_static)) {
@@ -428,7 +441,7 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     }
   }
   bool close = nearest <= (float)c.close_range;
-  if (MODE == CASIM_MODE_STEP) {
+  if (IS_STEP) {
     if (fabsf(nearest - (float)c.close_range) < 1e-5f) amb = true;
     if (__any_sync(FULL_MASK, amb)) {
       /* exact path: the reference's own fp64 formulas (collision_avoidance_env.py:640-655) */
@@ -462,7 +475,7 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   bool done = false;
   int st_new_coll = 0, st_new_goal = 0, st_new_to = 0, st_active = 0, st_agents = 0, st_go = 0;
   double st_rew = 0;
-  if (MODE == CASIM_MODE_STEP) {
+  if (IS_STEP) {
     if (valid && p.n_maps > 0) {
       /* :656-666 + Map.py:67-71: an occupied cell inside the disc (col-c0)^2+(row-r0)^2 < (r/cell)^2
        * <=> the exact squared distance from the agent's cell to the nearest occupied cell is < (r/cell)^2 */
@@ -530,15 +543,18 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
         go = (b_learn & envmask) == envmask;
       else
         go = n > 0 ? ((b_done >> base) & 1u) != 0 : true;
-      if (p.o.game_over) p.o.game_over[e] = (uint8_t)go;
-      p.prev_game_over[e] = (uint8_t)go;
+      if (p.o.game_over) p.o.game_over[(size_t)it * p.E + e] = (uint8_t)go;
+      if (last) p.prev_game_over[e] = (uint8_t)go;
       st_go = go;
     }
+    if (nsteps > 1) go_prev = __shfl_sync(FULL_MASK, st_go, base & 31); /* lane ai == 0 of my environment holds it */
     if (slot) {
-      if (p.o.rewards) p.o.rewards[g] = reward;
-      if (p.o.done) p.o.done[g] = (uint8_t)done;
-      if (p.o.collision_flags) p.o.collision_flags[g] = (uint8_t)((coll_agent ? 1 : 0) | (coll_wall ? 2 : 0));
-      if (p.o.nearest_dist) p.o.nearest_dist[g] = valid ? nearest : 0.f;
+      if (p.o.rewards) p.o.rewards[(size_t)it * plane + g] = reward;
+      if (p.o.done) p.o.done[(size_t)it * plane + g] = (uint8_t)done;
+      if (last) {
+        if (p.o.collision_flags) p.o.collision_flags[g] = (uint8_t)((coll_agent ? 1 : 0) | (coll_wall ? 2 : 0));
+        if (p.o.nearest_dist) p.o.nearest_dist[g] = valid ? nearest : 0.f;
+      }
     }
   } else if (MODE == CASIM_MODE_RESET) {
     if (slot && ai == 0) p.prev_game_over[e] = 0;
@@ -550,8 +566,9 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
    * complete total of that statistic in (returned value + its own contribution), writes the float and clears the
    * word for the next launch.  One L2 round trip on the critical path, no fence, no ticket, no second pass; integer
    * sums, so the result does not depend on the order of arrival (the reward sum is 2^-20 fixed point per CTA). ---- */
-  __shared__ long long s_stats[CASIM_CORE_MAX_WARPS][CASIM_NUM_STATS];
-  if (MODE == CASIM_MODE_STEP && p.o.stats != nullptr) {
+  __shared__ long long s_stats_buf[2][CASIM_CORE_MAX_WARPS][CASIM_NUM_STATS]; /* ping-pong over the steps of a launch */
+  long long (*s_stats)[CASIM_NUM_STATS] = s_stats_buf[it & 1];
+  if (IS_STEP && p.o.stats != nullptr) {
     long long v[CASIM_NUM_STATS];
     v[0] = __reduce_add_sync(FULL_MASK, st_new_coll);
     v[1] = __reduce_add_sync(FULL_MASK, st_new_goal);
@@ -572,26 +589,26 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
       if (lane == 4) t = (t + (1ll << 11)) >> 12; /* 2^-32 -> 2^-20 fixed point, rounded once per CTA */
       /* |t| < 2^31 for any CTA (<= 256 agents, |reward| <= 1): the bias keeps the 48-bit field non-negative */
       const unsigned long long mine = (1ull << 48) + (unsigned long long)(t + CASIM_STAT_BIAS);
-      unsigned long long* acc = reinterpret_cast<unsigned long long*>(p.partials) + lane * 8; /* 64 B apart */
+      unsigned long long* acc = reinterpret_cast<unsigned long long*>(p.partials) + (it * CASIM_NUM_STATS + lane) * 8; /* 64 B apart */
       const unsigned long long tot = atomicAdd(acc, mine) + mine;
       if ((unsigned)(tot >> 48) == gridDim.x) {
         *acc = 0ull;
         const long long sum = (long long)(tot & ((1ull << 48) - 1)) - (long long)gridDim.x * CASIM_STAT_BIAS;
-        p.o.stats[lane] = lane == 4 ? (float)((double)sum * (1.0 / 1048576.0)) : (float)sum;
+        p.o.stats[it * CASIM_NUM_STATS + lane] = lane == 4 ? (float)((double)sum * (1.0 / 1048576.0)) : (float)sum;
       }
     }
   }
 
   /* ---- state write-back ---- */
-  if (MODE == CASIM_MODE_STEP) {
-    if (valid) store_agent(p.state, plane, g, a, wrote_all);
+  if (IS_STEP) {
+    if (valid && last) store_agent(p.state, plane, g, a, wrote_all);
   } else if (MODE == CASIM_MODE_RESET) {
     if (slot) {
       store_agent(p.state, plane, g, a, true);
       store_agent(p.state0, plane, g, a, true);
     }
   }
-  if (p.write_pose && slot) { /* fp64 pose for the sensor kernels: px, py, cos(heading), sin(heading) */
+  if (p.write_pose && slot && last) { /* fp64 pose for the sensor kernels: px, py, cos(heading), sin(heading) */
     if (!a.have_cs) sincos(a.heading, &a.sn, &a.cs);
     double2* q = reinterpret_cast<double2*>(p.pose64 + 4 * g);
     q[0] = make_double2(a.px, a.py);
@@ -710,14 +727,14 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
       }
     }
   }
-  if (p.o.obs_misc && slot) { /* rel_goal (Dynamics.py:28), num_other_agents, use_ppo (config.py:208-213) */
+  if (p.o.obs_misc && slot && last) { /* rel_goal (Dynamics.py:28), num_other_agents, use_ppo (config.py:208-213) */
     float4 mo = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid)
       mo = make_float4((float)((double)a.gx - a.px), (float)((double)a.gy - a.py), (float)nobs,
                        (a.type & 0xff) == CASIM_POLICY_LEARNING ? 1.f : 0.f);
     reinterpret_cast<float4*>(p.o.obs_misc)[g] = mo;
   }
-
+  } /* steps of this launch */
 }
 
 template <int MODE>
@@ -752,9 +769,11 @@ cudaError_t launch_mode(const CoreArgs& a, int ap, dim3 grid, dim3 block, size_t
 
 cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const float* ext_actions,
                               const float* policy_actions, double dt, const casim_obs* obs, cudaStream_t s,
-                              const uint8_t* reset_mask) {
+                              const uint8_t* reset_mask, int n_steps) {
   CoreArgs a;
   a.reset_mask = mode == CASIM_MODE_RESET ? reset_mask : nullptr;
+  a.n_steps = mode == CASIM_MODE_STEP ? n_steps : 1;
+  if (mode == CASIM_MODE_STEP && n_steps > 1) mode = CASIM_MODE_STEP_N;
   a.c = h->dc;
   a.state = reinterpret_cast<float4*>(state);
   a.ext_actions = ext_actions;
@@ -809,6 +828,8 @@ cudaError_t casim_launch_core(casim_handle* h, int mode, float* state, const flo
   switch (mode) {
     case CASIM_MODE_STEP:
       return launch_mode<CASIM_MODE_STEP>(a, ap, grid, block, smem, s);
+    case CASIM_MODE_STEP_N:
+      return launch_mode<CASIM_MODE_STEP_N>(a, ap, grid, block, smem, s);
     case CASIM_MODE_RESET:
       return launch_mode<CASIM_MODE_RESET>(a, ap, grid, block, smem, s);
     default:

@@ -54,6 +54,7 @@ SYMBOLS = {
     "casim_reset_envs": (c_int, [c_void_p, c_void_p, c_void_p, _POBS, c_void_p]),
     "casim_observe": (c_int, [c_void_p, c_void_p, _POBS, c_void_p]),
     "casim_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_double, _POBS, c_void_p]),
+    "casim_step_n": (c_int, [c_void_p, c_void_p, c_void_p, c_double, c_int, _POBS, c_void_p]),
     "casim_run_sensor": (c_int, [c_void_p, c_void_p, _POBS, c_int, c_void_p]),
     "casim_step_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_double, _POBS, _POBS,
                                 c_void_p]),

@@ -239,6 +239,25 @@ class BatchedSim:
                                        _lib.ptr(policy_actions), float(dt) if dt is not None else 0.0,
                                        ctypes.byref(self._obs), _stream_ptr()), "casim_step")
 
+    def step_n(self, n_steps, policy_actions=None, dt=None):
+        """``n_steps`` env steps in ONE launch (casim_step_n; in-kernel policies only).  Returns the ring buffers
+        dict(rewards [n,E,A], done [n,E,A], game_over [n,E], stats [n,8]); ``buf`` / ``state`` hold the observations and
+        state after the last step (``buf['rewards']`` etc. are NOT updated by this call)."""
+        n_steps = int(n_steps)
+        ring = getattr(self, "_ring", None)
+        if ring is None or ring["rewards"].shape[0] != n_steps:
+            dev = self.device
+            ring = dict(rewards=torch.zeros((n_steps, self.E, self.A), dtype=torch.float32, device=dev),
+                        done=torch.zeros((n_steps, self.E, self.A), dtype=torch.uint8, device=dev),
+                        game_over=torch.zeros((n_steps, self.E), dtype=torch.uint8, device=dev),
+                        stats=torch.zeros((n_steps, NUM_STATS), dtype=torch.float32, device=dev) if self.buf["stats"] is not None else None)
+            self._ring = ring
+            self._ring_obs = self._obs_struct(dict(self.buf, **ring))
+        _lib.check(self.lib.casim_step_n(self.handle, _lib.ptr(self.state), _lib.ptr(policy_actions),
+                                         float(dt) if dt is not None else 0.0, n_steps, ctypes.byref(self._ring_obs),
+                                         _stream_ptr()), "casim_step_n")
+        return ring
+
     def run_sensor(self, which):
         """Launch one sensor kernel alone (profiling aid): which = layout.SENSOR_LASERSCAN / SENSOR_OCCUPANCY_GRID."""
         _lib.check(self.lib.casim_run_sensor(self.handle, _lib.ptr(self.state), ctypes.byref(self._obs), int(which),

@@ -246,6 +246,18 @@ int casim_observe(casim_handle* h, const float* state, const casim_obs* obs, voi
 int casim_step(casim_handle* h, float* state, const float* ext_actions, const float* policy_actions,
                double dt, const casim_obs* obs, void* stream);
 
+/* n_steps consecutive CollisionAvoidanceEnv.step calls in ONE launch, for batches whose every policy is evaluated inside
+ * the step kernel (Static, NonCooperative, PedestrianDataset; policy_actions, if given, is applied at every step): the
+ * agents' state stays in registers between the steps, which removes the per-step launch latency that bounds a small
+ * batch (collision_avoidance_env.py:162-232 called n_steps times with actions = {}).  Results: rewards [n_steps,E,A],
+ * done [n_steps,E,A], game_over [n_steps,E] and stats [n_steps,8] hold every step (the caller sizes these buffers of
+ * `obs` accordingly); the observations (obs_misc, other_agents_states, laserscan, local_grid, collision_flags,
+ * nearest_dist) and `state` are those after the last step.  auto_reset restarts finished environments between the
+ * steps of the launch exactly as between two casim_step calls.  Bit-identical to n_steps casim_step calls. */
+#define CASIM_STEP_N_MAX 64
+int casim_step_n(casim_handle* h, float* state, const float* policy_actions, double dt, int n_steps, const casim_obs* obs,
+                 void* stream);
+
 /* Profiling / benchmark aid: launch ONE sensor kernel -- `which` = CASIM_SENSOR_LASERSCAN (LaserScanSensor.py:27-58)
  * or CASIM_SENSOR_OCCUPANCY_GRID (OccupancyGridSensor.py:70-98) -- on the post-move poses left by the last
  * casim_step / casim_reset / casim_observe of this handle, so that the kernel can be timed alone; the OR of the two =

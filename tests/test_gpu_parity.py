@@ -421,3 +421,46 @@ def test_occupancy_grid_packed_output_per_env_maps(oracle_lib, torch_mod):
     assert g.any()
     assert np.array_equal(packed.cpu().numpy(), np.packbits(g.reshape(E, A, -1), axis=-1))
     sim.close()
+
+
+@pytest.mark.parametrize("A,sensors", [(10, ("other_agents_states",)), (6, ()), (20, ("other_agents_states", "laserscan", "local_grid"))])
+def test_step_n_equals_n_single_steps(oracle_lib, torch_mod, A, sensors):
+    """casim_step_n: n steps in one launch (state in registers, auto-reset between the steps) == n casim_step calls,
+    bit for bit: the per-step rewards / done / game_over / statistics rings, the final state and the last observation."""
+    torch = torch_mod
+    rng = np.random.default_rng(41 + A)
+    E = 333
+    b = H.random_batch(rng, E, A, sensor_choices=(7,) if sensors else (0,),
+                       policies=[L.POLICY_NONCOOPERATIVE] * 3 + [L.POLICY_STATIC, L.POLICY_PEDESTRIAN],
+                       dynamics=[L.DYN_UNICYCLE, L.DYN_FIRST_ORDER, L.DYN_UNICYCLE_MAX_ACC], spread=3.0)
+    maps, rects = H.unpack_maps()
+    cfg = gcfg(1, auto_reset=1)
+    sims = []
+    for _ in range(2):
+        sim = make_sim(E, A, cfg, sensors=sensors)
+        if "laserscan" in sensors:
+            sim.set_obstacles(rects[1].astype(np.float32))
+        sim.set_trajectories(b["traj"])
+        sim.reset(b["init"], b["types"], b["n_agents"])
+        sims.append(sim)
+    one, many = sims
+    for K in (1, 7, 24):
+        ring = many.step_n(K)
+        rews, dones, gos, stats = [], [], [], []
+        for _ in range(K):
+            one.step()
+            rews.append(one.buf["rewards"].clone())
+            dones.append(one.buf["done"].clone())
+            gos.append(one.buf["game_over"].clone())
+            stats.append(one.buf["stats"].clone())
+        torch.cuda.synchronize()
+        assert torch.equal(ring["rewards"], torch.stack(rews)), K
+        assert torch.equal(ring["done"], torch.stack(dones)), K
+        assert torch.equal(ring["game_over"], torch.stack(gos)), K
+        assert torch.equal(ring["stats"], torch.stack(stats)), K
+        assert torch.equal(many.state, one.state), K
+        for k in ("obs_misc", "collision_flags", "nearest_dist") + tuple(sensors):
+            assert torch.equal(many.buf[k], one.buf[k]), (K, k)
+        assert int(torch.stack(gos).sum()) > 0           # restarts did happen inside the launch
+    for sim in sims:
+        sim.close()
