@@ -734,6 +734,16 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
                        (a.type & 0xff) == CASIM_POLICY_LEARNING ? 1.f : 0.f);
     reinterpret_cast<float4*>(p.o.obs_misc)[g] = mo;
   }
+  if (MODE == CASIM_MODE_STEP_N && !last) {
+    /* the state between two steps is the STORED state: fp32 words (casim.h).  Round the fp64 working copies exactly as
+     * a store + load would, so that n steps in one launch equal n launches bit for bit. */
+    a.px = (double)(float)a.px;
+    a.py = (double)(float)a.py;
+    a.heading = (double)(float)a.heading;
+    a.turning = (double)(float)a.turning;
+    a.t = (double)(float)a.t;
+    a.trem = (double)(float)a.trem;
+  }
   } /* steps of this launch */
 }
 
