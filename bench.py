@@ -66,7 +66,9 @@ WORKLOADS = {
     "rvo": dict(E=4096, A=10, sensors=(),
                 desc="4096 envs x 10 agents, all RVOPolicy (ORCA, reciprocal), collision + reward step (SURVEY 8(f) rank 1)"),
 }
-GA3C_FLOP_PER_AGENT = 666112      # 2*[10*71*256 + 68*256 + 256*256 + 256*256 + 256*11]
+# 2*[T*71*256 + 68*256 + 256*256 + 256*256 + 256*11] with T = LSTM steps actually run: Config.MAX_NUM_OTHER_AGENTS_OBSERVED = 9
+# (SURVEY.md 8(d) counts the network's 10 slots: 666 112; the 10th slot is never filled)
+GA3C_FLOP_PER_AGENT = 2 * (9 * 71 * 256 + 68 * 256 + 256 * 256 + 256 * 256 + 256 * 11)
 
 
 def algorithmic_bytes(wl):
@@ -134,7 +136,8 @@ def roofline_obj(wl, kern, dominant, step_s, step_bytes, step_must, explore_coun
     out["traffic"] = traffic_for(wl, dominant)
     out["kernels"] = {k: {"duration_us": v[0] * 1e6, "share_of_step": v[0] / step_s, "how": v[2],
                           "frac": (v[1] / v[0] / 1e9 / peak) if not k.startswith("k_ga3c") else None,
-                          "frac_must_move": (v[3] / v[0] / 1e9 / peak) if not k.startswith("k_ga3c") else None}
+                          "frac_must_move": (v[3] / v[0] / 1e9 / peak) if not k.startswith("k_ga3c") else None,
+                          "tensor_frac": (v[1] / v[0] / 1e12 / tensor_peak()[0]) if k in ("k_ga3c_tc", "k_ga3c_fwd") else None}
                       for k, v in kern.items()}
     out["whole_step"] = {"duration_us": step_s * 1e6, "algorithmic_bytes": step_bytes,
                          "achieved_GBps": step_bytes / step_s / 1e9, "frac_of_hbm_peak": step_bytes / step_s / 1e9 / peak,
@@ -422,8 +425,9 @@ def main():
     ap.add_argument("--no-collective", action="store_true", help="diagnostics: leave the per-step statistics all-reduce out")
     ap.add_argument("--min-timed-ms", type=float, default=50.0, help="replay the K-step graph until the timed region is this long")
     ap.add_argument("--e2e-steps", type=int, default=200)
-    ap.add_argument("--ga3c-tc", action="store_true", help="c5: bf16 tensor-core forward (default: the fp32 forward, whose "
-                    "action index equals the reference network's on every decisive state)")
+    ap.add_argument("--ga3c", default="tc-exact", choices=["tc-exact", "tc", "fp32"],
+                    help="c5 forward: bf16 tensor cores + fp32 re-evaluation of the agents bf16 cannot call (default: actions equal "
+                         "the fp32 forward's), bare bf16 tensor cores, or the fp32 SIMT kernel")
     ap.add_argument("--no-stats", action="store_true", help="diagnostics: do not compute the per-step episode statistics")
     ap.add_argument("--steps-per-launch", type=int, default=1, help="c2 / c3 / full: casim_step_n, this many env steps per "
                     "kernel launch with the state in registers (in-kernel policies); K must be a multiple of it")
@@ -491,7 +495,8 @@ def main():
         sim.reset(init, types, n)
         sims.append(sim)
     torch.cuda.synchronize()
-    use_tc = bool(args.ga3c_tc)
+    use_tc = args.ga3c != "fp32"
+    ga3c_exact = args.ga3c == "tc-exact"
 
     spl = max(1, int(args.steps_per_launch))
     if spl > 1:
@@ -513,7 +518,7 @@ def main():
         if wl == "c4":
             return sim.explore_step()
         if wl == "c5":
-            return sim.ga3c_forward(use_tensor_cores=use_tc)
+            return sim.ga3c_forward(use_tensor_cores=use_tc, exact=ga3c_exact)
         if wl == "rvo":
             return sim.rvo_step()
         return None
@@ -766,13 +771,17 @@ def main():
         kern["k_rvo"] = (t, (48 + 8) * NA, "timed alone", (48 + 8) * NA)
         t_sens += t
     if wl == "c5":
-        t_both = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc))
+        t_both = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc, exact=ga3c_exact))
         t_fwd = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc, forward_only=True))
         fwd_name = "k_ga3c_tc" if use_tc else "k_ga3c_fwd"
         kern[fwd_name] = (t_fwd, GA3C_FLOP_PER_AGENT * NA, "timed alone (forward kernel on the previous state vectors)", 0)
         # state-vector kernel: reads 4 state planes of the agent + 3 of each other agent (L1/L2-resident within the
         # env), writes the 76-float row + 11 bf16 chunks: counted as 64 + 304 + 176 B per agent
-        kern["k_ga3c_state"] = (max(t_both - t_fwd, 1e-9), (64 + 304 + 176) * NA, "state+forward timed alone minus the forward alone", (64 + 304 + 176) * NA)
+        t_plain = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc)) if ga3c_exact else t_both
+        kern["k_ga3c_state"] = (max(t_plain - t_fwd, 1e-9), (64 + 304 + 176) * NA, "state+forward timed alone minus the forward alone", (64 + 304 + 176) * NA)
+        if ga3c_exact:
+            kern["k_ga3c_fwd(fix-up)"] = (max(t_both - t_plain, 1e-9), 0, "exact mode minus the bare bf16 forward: fp32 re-evaluation of the "
+                                          "agents whose top-2 margin is below the bf16 error bound", 0)
         t_sens += t_both
     core_units = (BYTES_CORE + (BYTES_OAS if "other_agents_states" in W["sensors"] else 0)
                   + (BYTES_WALL if "laserscan" in W["sensors"] or "local_grid" in W["sensors"] else 0)) * NA
@@ -793,7 +802,7 @@ def main():
                                                    + ("NCCL over %d ranks" % world if world > 1 else "1 rank: stream fork/join only"))
                     if collective else "off (--no-collective / --no-stats)",
                     "steps_per_launch": spl,
-                    "ga3c_forward": ("bf16 tcgen05" if use_tc else "fp32") if wl == "c5" else None},
+                    "ga3c_forward": args.ga3c if wl == "c5" else None},
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": Ke, "call": e2e_call},
             "gpu_launches": int(round(launches_per_step * K * reps)),

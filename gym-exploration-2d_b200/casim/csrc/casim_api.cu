@@ -237,6 +237,7 @@ int casim_destroy(casim_handle* h) {
   cudaFree(h->ga3c_wb);
   cudaFree(h->ga3c_x);
   cudaFree(h->ga3c_xb);
+  cudaFree(h->ga3c_fix);
   if (h->pipe_stream) {
     for (int k = 0; k < 2; k++) {
       cudaEventDestroy(h->pipe_ev_kernels[k]);

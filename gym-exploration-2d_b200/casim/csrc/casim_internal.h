@@ -106,6 +106,7 @@ struct casim_handle {
   float* ga3c_w;           /* fp32 parameter blob on the device */
   void* ga3c_wb;           /* bf16 tiles for the tensor-core path */
   float* ga3c_x;           /* [E*A][76] network input scratch */
+  int32_t* ga3c_fix;       /* [1 + E*A] counter + list of the agents the fp32 kernel re-evaluates after the bf16 forward */
   void* ga3c_xb;           /* [tiles][10][128] x 16 B: bf16 LSTM input chunks for the tensor-core path */
   /* RVO obstacle set (casim_rvo_set_obstacles): processed vertices + obstacle tree, see casim_rvo.cu */
   float2 *rvo_point, *rvo_unitdir;

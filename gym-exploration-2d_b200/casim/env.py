@@ -90,9 +90,11 @@ class BatchedCollisionAvoidanceEnv:
         self.episode_step_number = 0
         self._host_state = None
         self._generator = None
-        # GA3C-CADRL forward: the fp32 kernel is the default because the action index it returns equals the fp32
-        # restatement of the reference network on every decisive state; the bf16 tensor-core kernel is opt-in
-        self.ga3c_use_tensor_cores = False
+        # GA3C-CADRL forward: bf16 tensor cores with the fp32 fix-up of the agents bf16 cannot call ("exact"): the action
+        # index equals the fp32 forward's for every agent.  ga3c_exact = False gives the bare bf16 forward,
+        # ga3c_use_tensor_cores = False the fp32 forward.
+        self.ga3c_use_tensor_cores = True
+        self.ga3c_exact = True
 
     # ---- scenario injection (the reference's reset() ignores set_agents(): SURVEY.md 3.2) ----
     def set_agents(self, agents):
@@ -311,7 +313,7 @@ class BatchedCollisionAvoidanceEnv:
         elif self._has_ig:
             pol = sim.explore_step()
         if self._has_ga3c:
-            pol = sim.ga3c_forward(use_tensor_cores=self.ga3c_use_tensor_cores)
+            pol = sim.ga3c_forward(use_tensor_cores=self.ga3c_use_tensor_cores, exact=self.ga3c_exact)
         if self._has_rvo:
             pol = sim.rvo_step(coop=self._rvo_coop, params=self._rvo_params)
         sim.step(ext_actions=ext, policy_actions=pol, dt=dt)

@@ -410,12 +410,15 @@ class BatchedSim:
         self.buf["probs"] = torch.zeros((self.E, self.A, 11), dtype=torch.float32, device=dev) if want_debug else None
         self.buf["nn_input"] = torch.zeros((self.E, self.A, 75), dtype=torch.float32, device=dev) if want_debug else None
 
-    def ga3c_forward(self, use_tensor_cores=False, forward_only=False):
+    def ga3c_forward(self, use_tensor_cores=False, forward_only=False, exact=False):
         """GA3CCADRLPolicy.find_next_action for every GA3C agent -> ``buf['policy_actions']``.
+        ``use_tensor_cores``: bf16 tcgen05 forward; with ``exact`` the agents it cannot call (top-2 margin below the bf16
+        error bound) are re-evaluated in fp32 in the same call, so the actions equal the fp32 forward's.
         ``forward_only`` (profiling aid) skips the state-vector kernel and reuses the previous call's vectors."""
         _lib.check(self.lib.casim_ga3c_forward(self.handle, _lib.ptr(self.state), _lib.ptr(self.buf["policy_actions"]),
                                                _lib.ptr(self.buf.get("action_idx")), _lib.ptr(self.buf.get("probs")),
-                                               _lib.ptr(self.buf.get("nn_input")), int(bool(use_tensor_cores)) | (2 if forward_only else 0),
+                                               _lib.ptr(self.buf.get("nn_input")),
+                                               int(bool(use_tensor_cores)) | (2 if forward_only else 0) | (4 if (exact and use_tensor_cores) else 0),
                                                _stream_ptr()), "casim_ga3c_forward")
         return self.buf["policy_actions"]
 

@@ -10,9 +10,9 @@ from casim import layout as L
 pytestmark = pytest.mark.gpu
 
 # tensor-core forward vs the float64 graph value with the trained checkpoint (see casim_ga3c.cu "precision")
-TC_PROB_TOL = 6e-2
-TC_MIN_MARGIN = 0.24
-TC_MIN_AGREE = 0.93
+TC_PROB_TOL = 5e-2         # measured 0.039 over 163 044 agent-steps (profiles/r2_ga3c_agreement.json)
+TC_MIN_MARGIN = 0.10       # an argmax can only flip when the top-2 margin is below 2 x the probability error
+TC_MIN_AGREE = 0.99
 
 
 def _cfg(**kw):
@@ -141,5 +141,49 @@ def test_ga3c_forward_vs_oracle(oracle_lib, use_tc, trained):
             m = same
             H.assert_close(ga[e, :k][act][m], o["policy_actions"][e, :k][act][m], "action t=%d env %d" % (t, e), rtol=1e-6, atol=1e-7)
         sim.step(policy_actions=sim.buf["policy_actions"])
-    assert total > 5000 and agree / total > ((0.93 if trained else 0.97) if use_tc else 0.999)
+    assert total > 5000 and agree / total > ((0.99 if trained else 0.97) if use_tc else 0.999)
+    sim.close()
+
+
+@pytest.mark.parametrize("trained", [False, True])
+def test_ga3c_tensor_cores_exact_mode_equals_fp32_actions(oracle_lib, trained):
+    """the default GA3C path must not take different discrete actions than the fp32 network.  In
+    "exact" mode the bf16 tensor-core forward queues every agent whose top-2 margin is below the bf16 error bound and the
+    fp32 kernel re-evaluates them in the same call: action_idx / policy_actions equal the fp32 forward's for EVERY agent,
+    and the re-evaluated agents' probabilities are the fp32 kernel's bit for bit."""
+    import torch
+    from casim import scenarios as S
+    from casim.sim import BatchedSim
+    E, A = 512, 20
+    init, types, n = S.formations(E, A, seed=23)
+    n = n.copy()
+    n[::9] = 11
+    cfg = _cfg(near_goal_threshold=0.2)
+    w = H.load("ga3c_iros18.npz")["weights"] if trained else oracle_lib.ga3c_random_weights(4)
+    sim = BatchedSim(E, A, cfg=cfg, sensors=("other_agents_states",))
+    sim.reset(init, types, n)
+    sim.ga3c_set_weights(w)
+    n_fixed = n_live = 0
+    for t in range(6):
+        sim.ga3c_forward(use_tensor_cores=False)
+        torch.cuda.synchronize()
+        p32, i32, a32 = sim.buf["probs"].clone(), sim.buf["action_idx"].clone(), sim.buf["policy_actions"].clone()
+        sim.ga3c_forward(use_tensor_cores=True)
+        torch.cuda.synchronize()
+        ptc = sim.buf["probs"].clone()
+        sim.ga3c_forward(use_tensor_cores=True, exact=True)
+        torch.cuda.synchronize()
+        pex, iex, aex = sim.buf["probs"], sim.buf["action_idx"], sim.buf["policy_actions"]
+        assert torch.equal(iex, i32), (t, int((iex != i32).sum()))
+        assert torch.equal(aex, a32), t
+        live = i32 >= 0
+        fixed = live & (pex != ptc).any(-1)                  # rows the fp32 kernel rewrote
+        assert torch.equal(pex[fixed], p32[fixed])
+        srt = torch.sort(ptc[live], dim=-1).values
+        close = (srt[:, -1] - srt[:, -2]) < 0.12
+        assert int(fixed.sum()) <= int(close.sum())           # only close calls are re-evaluated ...
+        n_fixed += int(fixed.sum())
+        n_live += int(live.sum())
+        sim.step(policy_actions=aex)
+    assert 0 < n_fixed < 0.6 * n_live                         # ... and the tensor cores keep the bulk
     sim.close()
