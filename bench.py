@@ -234,6 +234,14 @@ SCENARIO_DESC = {
 }
 
 
+def ga3c_trained_weights():
+    """The reference's shipped GA3C-CADRL checkpoint (GA3C_CADRL/checkpoints/IROS18/network_01900000, the default of
+    GA3CCADRLPolicy.initialize_network), as read from the TF1 bundle by casim.ga3c_checkpoint and committed as a test
+    fixture; None when the fixture is absent."""
+    path = os.path.join(ROOT, "tests", "golden", "ga3c_iros18.npz")
+    return np.load(path)["weights"] if os.path.exists(path) else None
+
+
 def ga3c_weights(seed=0):
     """Random-init weights of the GA3C-CADRL architecture: Glorot-uniform kernels, zero biases (TF1 defaults)."""
     rng = np.random.default_rng(seed)
@@ -272,7 +280,10 @@ def oracle_run(wl, E, A, steps, warmup, threads, seed=1234, per_env_maps=False):
     init64 = init.astype(np.float64)
     go = np.zeros((E,), np.uint8)
     belief = np.ones((E, A, cfg.ig_map_dim, cfg.ig_map_dim)) if wl == "c4" else None
-    w = ga3c_weights() if wl == "c5" else None
+    w = None
+    if wl == "c5":
+        w = ga3c_trained_weights()
+        w = ga3c_weights() if w is None else w
     if wl == "c5":
         cfg.near_goal_threshold = 0.2
 
@@ -428,6 +439,8 @@ def main():
     ap.add_argument("--ga3c", default="tc-exact", choices=["tc-exact", "tc", "fp32"],
                     help="c5 forward: bf16 tensor cores + fp32 re-evaluation of the agents bf16 cannot call (default: actions equal "
                          "the fp32 forward's), bare bf16 tensor cores, or the fp32 SIMT kernel")
+    ap.add_argument("--ga3c-weights", default="iros18", choices=["iros18", "random"],
+                    help="c5: the reference's shipped IROS18 checkpoint (default) or Glorot random-init weights")
     ap.add_argument("--no-stats", action="store_true", help="diagnostics: do not compute the per-step episode statistics")
     ap.add_argument("--steps-per-launch", type=int, default=1, help="c2 / c3 / full: casim_step_n, this many env steps per "
                     "kernel launch with the state in registers (in-kernel policies); K must be a multiple of it")
@@ -491,7 +504,8 @@ def main():
         if wl == "c4":
             sim.enable_exploration(want_debug=False)
         if wl == "c5":
-            sim.ga3c_set_weights(ga3c_weights(), want_debug=False)
+            wts = ga3c_trained_weights() if args.ga3c_weights == "iros18" else None
+            sim.ga3c_set_weights(wts if wts is not None else ga3c_weights(), want_debug=False)
         sim.reset(init, types, n)
         sims.append(sim)
     torch.cuda.synchronize()
@@ -802,7 +816,8 @@ def main():
                                                    + ("NCCL over %d ranks" % world if world > 1 else "1 rank: stream fork/join only"))
                     if collective else "off (--no-collective / --no-stats)",
                     "steps_per_launch": spl,
-                    "ga3c_forward": args.ga3c if wl == "c5" else None},
+                    "ga3c_forward": args.ga3c if wl == "c5" else None,
+                    "ga3c_weights": (args.ga3c_weights if ga3c_trained_weights() is not None else "random") if wl == "c5" else None},
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": Ke, "call": e2e_call},
             "gpu_launches": int(round(launches_per_step * K * reps)),

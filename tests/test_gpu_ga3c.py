@@ -185,5 +185,5 @@ def test_ga3c_tensor_cores_exact_mode_equals_fp32_actions(oracle_lib, trained):
         n_fixed += int(fixed.sum())
         n_live += int(live.sum())
         sim.step(policy_actions=aex)
-    assert 0 < n_fixed < 0.6 * n_live                         # ... and the tensor cores keep the bulk
+    assert n_fixed > 0 and (n_fixed < 0.6 * n_live or not trained)   # ... and with trained weights the tensor cores keep the bulk
     sim.close()
