@@ -92,7 +92,7 @@ __device__ __forceinline__ const float4* ga3c_src(const Ga3cArgs& p, size_t g) {
  * disagreement of the argmax had an fp32 top-2 margin < 0.024), so an argmax can only flip when that margin is below
  * ~0.08.  Agents whose bf16 margin is below G_FIX_MARGIN are queued and re-evaluated by the fp32 kernel, which then
  * overwrites their action / probabilities: the action index equals the fp32 forward's for every agent. */
-#define G_FIX_MARGIN 0.12f
+#define G_FIX_MARGIN 0.10f
 
 #define U_NA 144 /* agents per CTA of the tensor-core path */
 #define U_XB_SLOTS 11
@@ -288,9 +288,10 @@ __device__ __forceinline__ float sigmoid_f(float v) { return 1.0f / (1.0f + expf
 /* acc[a][o] += sum_k act[k][ag0 + a] * W[k][col(o)] for this thread's 8 agents x 8 columns.
  * LSTM = true : columns {g*64 + tx*2 + {0,1}}: all four gates of units tx*2, tx*2+1 (row length 256);
  * LSTM = false: columns tx*8 .. tx*8+7. */
-template <bool LSTM>
+template <bool LSTM, int AG>
 __device__ __forceinline__ void gemm_tile(const float* __restrict__ W, const float* __restrict__ bias, int K,
-                                          const float* act /* smem [K][G_TILE] */, int tx, int ty, float acc[8][8]) {
+                                          const float* act /* smem [K][8 * AG] */, int tx, int ty, float acc[AG][8]) {
+  constexpr int TILE = 8 * AG;
   float b[8];
   if (LSTM) {
 #pragma unroll
@@ -304,7 +305,7 @@ __device__ __forceinline__ void gemm_tile(const float* __restrict__ W, const flo
     b[0] = v0.x; b[1] = v0.y; b[2] = v0.z; b[3] = v0.w; b[4] = v1.x; b[5] = v1.y; b[6] = v1.z; b[7] = v1.w;
   }
 #pragma unroll
-  for (int a = 0; a < 8; a++)
+  for (int a = 0; a < AG; a++)
 #pragma unroll
     for (int o = 0; o < 8; o++) acc[a][o] = 0.f;
 #pragma unroll 4
@@ -322,27 +323,38 @@ __device__ __forceinline__ void gemm_tile(const float* __restrict__ W, const flo
       float4 v0 = __ldg(reinterpret_cast<const float4*>(wr + tx * 8)), v1 = __ldg(reinterpret_cast<const float4*>(wr + tx * 8 + 4));
       w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
     }
-    const float4 a0 = *reinterpret_cast<const float4*>(act + k * G_TILE + ty * 8);
-    const float4 a1 = *reinterpret_cast<const float4*>(act + k * G_TILE + ty * 8 + 4);
-    const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    float av[AG];
+    if (AG == 8) {
+      const float4 a0 = *reinterpret_cast<const float4*>(act + k * TILE + ty * 8);
+      const float4 a1 = *reinterpret_cast<const float4*>(act + k * TILE + ty * 8 + 4);
+      av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w;
+      av[AG - 4] = a1.x; av[AG - 3] = a1.y; av[AG - 2] = a1.z; av[AG - 1] = a1.w;
+    } else {
 #pragma unroll
-    for (int a = 0; a < 8; a++)
+      for (int a = 0; a < AG; a++) av[a] = act[k * TILE + ty * AG + a];
+    }
+#pragma unroll
+    for (int a = 0; a < AG; a++)
 #pragma unroll
       for (int o = 0; o < 8; o++) acc[a][o] = fmaf(av[a], w[o], acc[a][o]);
   }
 #pragma unroll
-  for (int a = 0; a < 8; a++)
+  for (int a = 0; a < AG; a++)
 #pragma unroll
     for (int o = 0; o < 8; o++) acc[a][o] += b[o];
 }
 
-/* fp32 forward: CTA = 64 agents, 256 threads (tx = lane: output columns, ty = warp: 8 agents) */
+/* fp32 forward: CTA = 8 * AG agents, 256 threads (tx = lane: output columns, ty = warp: AG agents).  AG = 8 for the full
+ * batch; AG = 2 for the fix-up of a short list (4x the CTAs, a quarter of the serial work per thread: the list is short, so
+ * its cost is one CTA's latency).  An agent's result does not depend on AG (same k order per output). */
+template <int AG>
 __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
-  extern __shared__ __align__(16) float s_act[]; /* [256][G_TILE] transposed activations */
-  __shared__ float s_logit[G_TILE][12];
-  __shared__ int s_len[G_TILE];
+  constexpr int TILE = 8 * AG;
+  extern __shared__ __align__(16) float s_act[]; /* [256][TILE] transposed activations */
+  __shared__ float s_logit[TILE][12];
+  __shared__ int s_len[TILE];
   const size_t N = (size_t)p.E * p.A;
-  const size_t g0 = (size_t)blockIdx.x * G_TILE;
+  const size_t g0 = (size_t)blockIdx.x * TILE;
   const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
   const float* w = p.w;
   /* fix-up mode: slot a of this CTA is the agent fix_list[g0 + a] (N = empty slot); whole CTAs beyond the list leave */
@@ -354,14 +366,14 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
   };
 
   /* sequence length per agent (x[0], un-normalised: network.py:85); -1 = slot without a GA3C agent */
-  if (tid < G_TILE) {
+  if (tid < TILE) {
     size_t g = agent_of(tid);
     float x0 = g < N ? p.x[g * G_XS] : -1.f;
     s_len[tid] = (int)x0;
   }
   /* rows 0..6 = x_t (first step), rows 7..70 = h = 0 */
-  for (int idx = tid; idx < (G_OTHER + G_H) * G_TILE; idx += G_THREADS) {
-    int k = idx / G_TILE, a = idx - k * G_TILE;
+  for (int idx = tid; idx < (G_OTHER + G_H) * TILE; idx += G_THREADS) {
+    int k = idx / TILE, a = idx - k * TILE;
     float v = 0.f;
     size_t g = agent_of(a);
     if (k < G_OTHER && g < N) v = (p.x[g * G_XS + 1 + G_HOST + k] - c_oth_avg[k]) / c_oth_std[k];
@@ -369,33 +381,33 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
   }
   __syncthreads();
   int maxlen = 0;
-  for (int a = 0; a < G_TILE; a++) maxlen = max(maxlen, s_len[a]);
+  for (int a = 0; a < TILE; a++) maxlen = max(maxlen, s_len[a]);
   maxlen = min(maxlen, G_SLOTS);
 
-  float acc[8][8];
-  float cst[8][2]; /* LSTM cell state of my 8 agents x 2 units */
+  float acc[AG][8];
+  float cst[AG][2]; /* LSTM cell state of my 8 agents x 2 units */
 #pragma unroll
-  for (int a = 0; a < 8; a++) cst[a][0] = cst[a][1] = 0.f;
+  for (int a = 0; a < AG; a++) cst[a][0] = cst[a][1] = 0.f;
   for (int t = 0; t < maxlen; t++) {
-    gemm_tile<true>(w + W_LSTM_K, w + W_LSTM_B, G_OTHER + G_H, s_act, tx, ty, acc);
+    gemm_tile<true, AG>(w + W_LSTM_K, w + W_LSTM_B, G_OTHER + G_H, s_act, tx, ty, acc);
     __syncthreads(); /* everyone has read x_t and h */
 #pragma unroll
-    for (int a = 0; a < 8; a++) {
-      const int ag = ty * 8 + a;
+    for (int a = 0; a < AG; a++) {
+      const int ag = ty * AG + a;
       if (t < s_len[ag]) { /* dynamic_rnn(sequence_length): state copied through beyond the last valid step */
 #pragma unroll
         for (int u = 0; u < 2; u++) { /* TF1 LSTMCell: i, j, f, o; forget_bias 1.0 */
           float gi = acc[a][u], gj = acc[a][2 + u], gf = acc[a][4 + u], go = acc[a][6 + u];
           float cn = sigmoid_f(gf + 1.0f) * cst[a][u] + sigmoid_f(gi) * tanhf(gj);
           cst[a][u] = cn;
-          s_act[(G_OTHER + tx * 2 + u) * G_TILE + ag] = sigmoid_f(go) * tanhf(cn);
+          s_act[(G_OTHER + tx * 2 + u) * TILE + ag] = sigmoid_f(go) * tanhf(cn);
         }
       }
     }
     /* next step's inputs */
     if (t + 1 < maxlen)
-      for (int idx = tid; idx < G_OTHER * G_TILE; idx += G_THREADS) {
-        int k = idx / G_TILE, a = idx - k * G_TILE;
+      for (int idx = tid; idx < G_OTHER * TILE; idx += G_THREADS) {
+        int k = idx / TILE, a = idx - k * TILE;
         size_t g = agent_of(a);
         float v = 0.f;
         if (g < N && t + 1 < s_len[a]) v = (p.x[g * G_XS + 1 + G_HOST + G_OTHER * (t + 1) + k] - c_oth_avg[k]) / c_oth_std[k];
@@ -404,10 +416,10 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
     __syncthreads();
   }
   /* layer1 input = concat(host4, h64): host goes to rows 3..6, h already sits in rows 7..70 */
-  if (tid < G_HOST * G_TILE) {
-    int k = tid / G_TILE, a = tid - k * G_TILE;
+  if (tid < G_HOST * TILE) {
+    int k = tid / TILE, a = tid - k * TILE;
     size_t g = agent_of(a);
-    s_act[(3 + k) * G_TILE + a] = g < N ? (p.x[g * G_XS + 1 + k] - c_host_avg[k]) / c_host_std[k] : 0.f;
+    s_act[(3 + k) * TILE + a] = g < N ? (p.x[g * G_XS + 1 + k] - c_host_avg[k]) / c_host_std[k] : 0.f;
   }
   __syncthreads();
   const float* Wk[3] = {w + W_L1_K, w + W_L2_K, w + W_FC_K};
@@ -415,22 +427,22 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
 #pragma unroll 1
   for (int layer = 0; layer < 3; layer++) {
     if (layer == 0)
-      gemm_tile<false>(Wk[0], Wb[0], G_HOST + G_H, s_act + 3 * G_TILE, tx, ty, acc);
+      gemm_tile<false, AG>(Wk[0], Wb[0], G_HOST + G_H, s_act + 3 * TILE, tx, ty, acc);
     else
-      gemm_tile<false>(Wk[layer], Wb[layer], G_FC, s_act, tx, ty, acc);
+      gemm_tile<false, AG>(Wk[layer], Wb[layer], G_FC, s_act, tx, ty, acc);
     __syncthreads();
 #pragma unroll
-    for (int a = 0; a < 8; a++)
+    for (int a = 0; a < AG; a++)
 #pragma unroll
-      for (int o = 0; o < 8; o++) s_act[(tx * 8 + o) * G_TILE + ty * 8 + a] = fmaxf(acc[a][o], 0.f);
+      for (int o = 0; o < 8; o++) s_act[(tx * 8 + o) * TILE + ty * AG + a] = fmaxf(acc[a][o], 0.f);
     __syncthreads();
   }
-  /* logits_p: 64 agents x 11 outputs, K = 256 */
-  {
+  /* logits_p: TILE agents x 11 outputs, K = 256 */
+  if (tid < 4 * TILE) {
     const int a = tid >> 2, q = tid & 3;
     float l[3] = {0.f, 0.f, 0.f};
     for (int k = 0; k < G_FC; k++) {
-      float v = s_act[k * G_TILE + a];
+      float v = s_act[k * TILE + a];
 #pragma unroll
       for (int mm = 0; mm < 3; mm++) {
         int o = q + 4 * mm;
@@ -444,7 +456,7 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
     }
   }
   __syncthreads();
-  if (tid < G_TILE) {
+  if (tid < TILE) {
     const size_t g = agent_of(tid);
     if (g < N && s_len[tid] >= 0) {
       const int flags = __float_as_int(ga3c_src(p, g)[5 * N + g].z);
@@ -1034,7 +1046,7 @@ cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_
     e = cudaMalloc((void**)&h->ga3c_x, (size_t)h->E * h->A * G_XS * sizeof(float));
     if (e != cudaSuccess) return e;
   }
-  e = cudaFuncSetAttribute(k_ga3c_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)G_FC * G_TILE * sizeof(float)));
+  e = cudaFuncSetAttribute(k_ga3c_fwd<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)G_FC * G_TILE * sizeof(float)));
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_ga3c_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)U_DYN_SMEM);
   if (e != cudaSuccess) return e;
@@ -1116,9 +1128,9 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
     if (skip_state) return cudaErrorInvalidValue; /* the state kernel zeroes the fix-up counter */
     h->launches++;
     a.fix_mode = 1;
-    k_ga3c_fwd<<<(unsigned)((N + G_TILE - 1) / G_TILE), G_THREADS, (size_t)G_FC * G_TILE * sizeof(float), s>>>(a);
+    k_ga3c_fwd<2><<<(unsigned)((N + 15) / 16), G_THREADS, (size_t)G_FC * 16 * sizeof(float), s>>>(a);
     return cudaGetLastError();
   } else
-    k_ga3c_fwd<<<(unsigned)((N + G_TILE - 1) / G_TILE), G_THREADS, (size_t)G_FC * G_TILE * sizeof(float), s>>>(a);
+    k_ga3c_fwd<8><<<(unsigned)((N + G_TILE - 1) / G_TILE), G_THREADS, (size_t)G_FC * G_TILE * sizeof(float), s>>>(a);
   return cudaGetLastError();
 }
