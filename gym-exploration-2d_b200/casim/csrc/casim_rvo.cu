@@ -362,6 +362,49 @@ __device__ int obstacle_lines(const RvoObst& O, const int* no, int nn, float2 po
   return nl;
 }
 
+/* Agent.cpp:298-364: the ORCA half-plane one neighbour induces on the ego agent's velocity (o0 = px, py, ..; o1 = vx, vy,
+ * ..; o2 = .., .., radius, ..).  Binary32, the library's operation order. */
+__device__ __forceinline__ Line agent_orca_line(float2 position, float2 velocity, float radius_, float4 o0, float4 o1, float4 o2,
+                                                double radius_scale, float invTimeHorizon, float time_step, float collab) {
+  const float2 relativePosition = sub(V(o0.x, o0.y), position);
+  const float2 relativeVelocity = sub(velocity, V(o1.x, o1.y));
+  const float distSq = absSq(relativePosition);
+  const float combinedRadius = radius_ + (float)(radius_scale * (double)o2.z);
+  const float combinedRadiusSq = sqr(combinedRadius);
+  Line line;
+  float2 u;
+  if (distSq > combinedRadiusSq) {
+    const float2 w = sub(relativeVelocity, mulsv(invTimeHorizon, relativePosition));
+    const float wLengthSq = absSq(w);
+    const float dotProduct1 = dot(w, relativePosition);
+    if (dotProduct1 < 0.0f && sqr(dotProduct1) > combinedRadiusSq * wLengthSq) {
+      const float wLength = sqrtf(wLengthSq);
+      const float2 unitW = divs(w, wLength);
+      line.direction = V(unitW.y, -unitW.x);
+      u = mulsv(combinedRadius * invTimeHorizon - wLength, unitW);
+    } else {
+      const float leg = sqrtf(distSq - combinedRadiusSq);
+      if (det(relativePosition, w) > 0.0f)
+        line.direction = divs(V(relativePosition.x * leg - relativePosition.y * combinedRadius,
+                                relativePosition.x * combinedRadius + relativePosition.y * leg), distSq);
+      else
+        line.direction = divs(neg(V(relativePosition.x * leg + relativePosition.y * combinedRadius,
+                                    -relativePosition.x * combinedRadius + relativePosition.y * leg)), distSq);
+      const float dotProduct2 = dot(relativeVelocity, line.direction);
+      u = sub(mulsv(dotProduct2, line.direction), relativeVelocity);
+    }
+  } else {
+    const float invTimeStep = 1.0f / time_step;
+    const float2 w = sub(relativeVelocity, mulsv(invTimeStep, relativePosition));
+    const float wLength = sqrtf(dot(w, w));
+    const float2 unitW = divs(w, wLength);
+    line.direction = V(unitW.y, -unitW.x);
+    u = mulsv(combinedRadius * invTimeStep - wLength, unitW);
+  }
+  line.point = add(velocity, mulsv(collab, u)); /* Agent.cpp:361 */
+  return line;
+}
+
 #ifndef RVO_THREADS
 #define RVO_THREADS 128
 #endif
@@ -436,44 +479,8 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
   } else if (collab > 0.0f) {
     for (int k = 0; k < nn; k++) { /* Agent.cpp:298-364 */
       const int o = nidx[k];
-      const float4 o0 = s0[o], o1 = s1[o], o2 = s2[o];
-      const float2 relativePosition = sub(V(o0.x, o0.y), position);
-      const float2 relativeVelocity = sub(velocity, V(o1.x, o1.y));
-      const float distSq = absSq(relativePosition);
-      const float combinedRadius = radius_ + (float)(p.radius_scale * (double)o2.z);
-      const float combinedRadiusSq = sqr(combinedRadius);
-      Line line;
-      float2 u;
-      if (distSq > combinedRadiusSq) {
-        const float2 w = sub(relativeVelocity, mulsv(invTimeHorizon, relativePosition));
-        const float wLengthSq = absSq(w);
-        const float dotProduct1 = dot(w, relativePosition);
-        if (dotProduct1 < 0.0f && sqr(dotProduct1) > combinedRadiusSq * wLengthSq) {
-          const float wLength = sqrtf(wLengthSq);
-          const float2 unitW = divs(w, wLength);
-          line.direction = V(unitW.y, -unitW.x);
-          u = mulsv(combinedRadius * invTimeHorizon - wLength, unitW);
-        } else {
-          const float leg = sqrtf(distSq - combinedRadiusSq);
-          if (det(relativePosition, w) > 0.0f)
-            line.direction = divs(V(relativePosition.x * leg - relativePosition.y * combinedRadius,
-                                    relativePosition.x * combinedRadius + relativePosition.y * leg), distSq);
-          else
-            line.direction = divs(neg(V(relativePosition.x * leg + relativePosition.y * combinedRadius,
-                                        -relativePosition.x * combinedRadius + relativePosition.y * leg)), distSq);
-          const float dotProduct2 = dot(relativeVelocity, line.direction);
-          u = sub(mulsv(dotProduct2, line.direction), relativeVelocity);
-        }
-      } else {
-        const float invTimeStep = 1.0f / p.time_step;
-        const float2 w = sub(relativeVelocity, mulsv(invTimeStep, relativePosition));
-        const float wLength = sqrtf(dot(w, w));
-        const float2 unitW = divs(w, wLength);
-        line.direction = V(unitW.y, -unitW.x);
-        u = mulsv(combinedRadius * invTimeStep - wLength, unitW);
-      }
-      line.point = add(velocity, mulsv(collab, u)); /* Agent.cpp:361 */
-      lines[nl++] = line;
+      lines[nl++] = agent_orca_line(position, velocity, radius_, s0[o], s1[o], s2[o], p.radius_scale, invTimeHorizon,
+                                    p.time_step, collab);
     }
   } else if (nn > 0) { /* Agent.cpp:367-416 */
     float minDistSq = INFINITY;
@@ -508,6 +515,295 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
   float2 newVel = V(0.f, 0.f);
   const int lineFail = lp2(lines, nl, maxSpeed, prefVel, false, newVel);
   if (lineFail < nl) lp3(lines, nl, numObstLines, lineFail, maxSpeed, newVel, proj);
+  const float2 newPos = add(position, mulvs(newVel, p.time_step)); /* Agent.cpp:516-521 */
+
+  /* RVOPolicy.py:91-110 (fp64) */
+  const double ddx = (double)newPos.x - (double)me0.x, ddy = (double)newPos.y - (double)me0.y;
+  const double ang1 = atan2(ddy, ddx);
+  double new_heading = fmod(ang1, CASIM_2PI); /* np.mod(ang1 - 0, 2 pi) */
+  if (new_heading != 0.0 && new_heading < 0.0) new_heading += CASIM_2PI;
+  double delta_heading = wrap_pi(new_heading - (double)me0.z);
+  double pref_speed = 1 / p.dt * sqrt(ddx * ddx + ddy * ddy);
+  if (fabs(delta_heading) > p.max_delta_heading) {
+    delta_heading = (delta_heading > 0 ? 1.0 : (delta_heading < 0 ? -1.0 : 0.0)) * p.max_delta_heading;
+    pref_speed = 0.;
+  }
+  reinterpret_cast<float2*>(p.policy_actions)[g] = make_float2((float)pref_speed, (float)delta_heading);
+}
+
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * k_rvo4 -- the agents-only case (no static obstacles) mapped onto the GPU: FOUR LANES PER EGO AGENT, 8 agents per warp.
+ * One thread per agent leaves the machine with ~9 warps per SM and a serial chain of a few thousand dependent fp32
+ * operations per thread (52.9 us for 40 960 agents).  Here the chain is cut in four and there are four times as many
+ * warps:
+ *   neighbours   lane q evaluates the candidates j = q, q+4, ..; the reference's "sorted insertion with the range
+ *                shrinking to the farthest kept neighbour" (Agent.cpp:449-473) is a stable rank by (distSq, index)
+ *                cut at maxNeighbors, so each lane RANKS its candidates by counting -- no serial sort;
+ *   ORCA lines   built by the lane that owns the candidate (agent_orca_line), stored at slot = rank in shared memory;
+ *   LP 2         "the next violated line at or after i" is a 4-lane min over per-lane scans (the result only changes
+ *                at a repair); LP 1's scan over the earlier lines only tightens tLeft (max) / tRight (min) and fails
+ *                on an infeasible parallel line, so each lane scans a quarter of them and the group combines with
+ *                min / max / or -- exact, order-free (tLeft never decreases and tRight never increases, hence "some
+ *                prefix has tLeft > tRight" == "the final one has");
+ *   LP 3         the projected lines of one violated line are built four at a time and compacted in order with a
+ *                group ballot, then LP 2 runs on them.
+ * All lanes of a group carry the same scalars (result, tLeft, ...), computed redundantly from the same inputs, so every
+ * branch on them is uniform in the group; groups of one warp run independently (group masks on every shuffle).
+ * The arithmetic per (line, line) pair is the library's binary32 sequence: new velocities are bit-identical to it. */
+#define R4_MAXL 32 /* ORCA lines per agent (A - 1 <= 31) */
+#define R4_THREADS 128
+#define R4_GROUPS (R4_THREADS / 4)
+
+struct R4Group {
+  unsigned mask; /* the four lanes of my group */
+  int q;         /* my lane inside the group */
+  __device__ __forceinline__ float gminf(float v) const {
+    float t = __shfl_xor_sync(mask, v, 1);
+    v = (t < v) ? t : v;
+    t = __shfl_xor_sync(mask, v, 2);
+    return (t < v) ? t : v;
+  }
+  __device__ __forceinline__ float gmaxf(float v) const {
+    float t = __shfl_xor_sync(mask, v, 1);
+    v = (v < t) ? t : v;
+    t = __shfl_xor_sync(mask, v, 2);
+    return (v < t) ? t : v;
+  }
+  __device__ __forceinline__ int gmini(int v) const {
+    v = min(v, __shfl_xor_sync(mask, v, 1));
+    return min(v, __shfl_xor_sync(mask, v, 2));
+  }
+  __device__ __forceinline__ int gsumi(int v) const {
+    v += __shfl_xor_sync(mask, v, 1);
+    return v + __shfl_xor_sync(mask, v, 2);
+  }
+  __device__ __forceinline__ unsigned gballot(bool b, int lane) const { return (__ballot_sync(mask, b) >> (lane & ~3)) & 0xFu; }
+  __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+};
+
+__device__ __forceinline__ Line r4_load(const float4* L, int i) {
+  const float4 v = L[i];
+  Line l;
+  l.point = V(v.x, v.y);
+  l.direction = V(v.z, v.w);
+  return l;
+}
+
+/* Agent.cpp:477-546 with the scan over the earlier lines split over the four lanes */
+__device__ bool r4_lp1(const R4Group& G, const float4* lines, int lineNo, float radius, float2 opt, bool dirOpt, float2& result) {
+  const Line L = r4_load(lines, lineNo);
+  const float dotProduct = dot(L.point, L.direction);
+  const float discriminant = sqr(dotProduct) + sqr(radius) - absSq(L.point);
+  if (discriminant < 0.0f) return false;
+  const float sq = sqrtf(discriminant);
+  float tLeft = -dotProduct - sq;
+  float tRight = -dotProduct + sq;
+  bool infeasible = false;
+  for (int i = G.q; i < lineNo; i += 4) {
+    const Line Li = r4_load(lines, i);
+    const float denominator = det(L.direction, Li.direction);
+    const float numerator = det(Li.direction, sub(L.point, Li.point));
+    if (fabsf(denominator) <= RVO_EPS) {
+      if (numerator < 0.0f) infeasible = true;
+      continue;
+    }
+    const float t = numerator / denominator;
+    if (denominator >= 0.0f)
+      tRight = (t < tRight) ? t : tRight;
+    else
+      tLeft = (tLeft < t) ? t : tLeft;
+  }
+  tRight = G.gminf(tRight);
+  tLeft = G.gmaxf(tLeft);
+  if (__any_sync(G.mask, infeasible) || tLeft > tRight) return false;
+  if (dirOpt) {
+    if (dot(opt, L.direction) > 0.0f)
+      result = add(L.point, mulsv(tRight, L.direction));
+    else
+      result = add(L.point, mulsv(tLeft, L.direction));
+  } else {
+    const float t = dot(L.direction, sub(opt, L.point));
+    if (t < tLeft)
+      result = add(L.point, mulsv(tLeft, L.direction));
+    else if (t > tRight)
+      result = add(L.point, mulsv(tRight, L.direction));
+    else
+      result = add(L.point, mulsv(t, L.direction));
+  }
+  return true;
+}
+
+/* Agent.cpp:548-578 */
+__device__ int r4_lp2(const R4Group& G, const float4* lines, int nl, float radius, float2 opt, bool dirOpt, float2& result) {
+  if (dirOpt)
+    result = mulvs(opt, radius);
+  else if (absSq(opt) > sqr(radius))
+    result = mulvs(normalize(opt), radius);
+  else
+    result = opt;
+  int i = 0;
+  while (i < nl) {
+    /* the first violated line at or after i: each lane scans its own lines (k = q mod 4) */
+    int k = i + ((G.q - i) & 3);
+    for (; k < nl; k += 4) {
+      const Line Lk = r4_load(lines, k);
+      if (det(Lk.direction, sub(Lk.point, result)) > 0.0f) break;
+    }
+    const int v = G.gmini(k);
+    if (v >= nl) break;
+    const float2 temp = result;
+    if (!r4_lp1(G, lines, v, radius, opt, dirOpt, result)) {
+      result = temp;
+      return v;
+    }
+    i = v + 1;
+  }
+  return nl;
+}
+
+/* Agent.cpp:580-630 (no obstacle lines in this kernel: numObstLines = 0) */
+__device__ void r4_lp3(const R4Group& G, int lane, const float4* lines, int nl, int beginLine, float radius, float2& result,
+                       float4* proj) {
+  float distance = 0.0f;
+  for (int i = beginLine; i < nl; i++) {
+    const Line Li = r4_load(lines, i);
+    if (det(Li.direction, sub(Li.point, result)) > distance) {
+      int np = 0;
+      for (int j0 = 0; j0 < i; j0 += 4) { /* four projected lines per round, compacted in order */
+        const int j = j0 + G.q;
+        bool keep = false;
+        Line l;
+        l.point = V(0.f, 0.f);
+        l.direction = V(0.f, 0.f);
+        if (j < i) {
+          const Line Lj = r4_load(lines, j);
+          const float determinant = det(Li.direction, Lj.direction);
+          keep = true;
+          if (fabsf(determinant) <= RVO_EPS) {
+            if (dot(Li.direction, Lj.direction) > 0.0f)
+              keep = false;
+            else
+              l.point = mulsv(0.5f, add(Li.point, Lj.point));
+          } else {
+            l.point = add(Li.point, mulsv(det(Lj.direction, sub(Li.point, Lj.point)) / determinant, Li.direction));
+          }
+          if (keep) l.direction = normalize(sub(Lj.direction, Li.direction));
+        }
+        const unsigned b = G.gballot(keep, lane);
+        if (keep) proj[np + __popc(b & ((1u << G.q) - 1u))] = make_float4(l.point.x, l.point.y, l.direction.x, l.direction.y);
+        np += __popc(b);
+      }
+      G.sync();
+      const float2 temp = result;
+      if (r4_lp2(G, proj, np, radius, V(-Li.direction.y, Li.direction.x), true, result) < np) result = temp;
+      distance = det(Li.direction, sub(Li.point, result));
+      G.sync(); /* proj is rebuilt for the next violated line */
+    }
+  }
+}
+
+
+__global__ void __launch_bounds__(R4_THREADS) k_rvo4(const RvoArgs p) {
+  __shared__ __align__(16) float4 s_line[R4_GROUPS][R4_MAXL];
+  __shared__ __align__(16) float4 s_proj[R4_GROUPS][R4_MAXL];
+  __shared__ float s_cd[R4_GROUPS][R4_MAXL];
+  casim_pdl_enter();
+  const size_t N = (size_t)p.E * p.A;
+  const int lane = threadIdx.x & 31, grp = threadIdx.x >> 2;
+  const size_t g = (size_t)blockIdx.x * R4_GROUPS + grp;
+  if (g >= N) return; /* whole groups leave together */
+  R4Group G;
+  G.q = lane & 3;
+  G.mask = 0xFu << (lane & ~3);
+  const int A = p.A;
+  const int e = (int)(g / A), ego = (int)(g - (size_t)e * A);
+  const int n = p.n_agents ? min(p.n_agents[e], A) : A;
+  if (ego >= n) return;
+  const float4* s0 = ((p.prev_game_over && p.prev_game_over[e]) ? p.state0 : p.state) + (size_t)e * A; /* px, py, heading, speed */
+  const float4* s1 = s0 + N;                                                                              /* vx, vy, ... */
+  const float4* s2 = s1 + N;                                                                              /* gx, gy, radius, pref_speed */
+  const float4* s5 = s2 + 3 * N;
+  if ((__float_as_int(s5[ego].w) & 0xff) != CASIM_POLICY_RVO) return;
+  float4* lines = s_line[grp];
+  float* cd = s_cd[grp];
+
+  const float4 me0 = s0[ego], me1 = s1[ego], me2 = s2[ego];
+  const float2 position = V(me0.x, me0.y), velocity = V(me1.x, me1.y);
+  const float radius_ = (float)(p.radius_scale * (double)me2.z); /* RVOPolicy.py:78 + rvo2.pyx:218 */
+  const float maxSpeed = me2.w;                                  /* :77 */
+  const float collab = p.coop ? p.coop[g] : 1.0f;
+  float2 prefVel;
+  { /* RVOPolicy.py:73-74 in fp64, then the binding's float conversion */
+    double dx = (double)me2.x - (double)me0.x, dy = (double)me2.y - (double)me0.y;
+    double k = (double)me2.w / sqrt(dx * dx + dy * dy);
+    prefVel = V((float)(k * dx), (float)(k * dy));
+  }
+
+  /* ---- neighbours (Agent.cpp:43-56, 449-473): squared distances, then a stable rank by counting ---- */
+  const float rangeSq = sqr(p.neighbor_dist);
+  int mine = 0;
+  for (int j = G.q; j < n; j += 4) {
+    float d = INFINITY;
+    if (j != ego && p.max_neighbors > 0) {
+      const float4 o0 = s0[j];
+      const float distSq = absSq(sub(position, V(o0.x, o0.y)));
+      if (distSq < rangeSq) {
+        d = distSq;
+        mine++;
+      }
+    }
+    cd[j] = d;
+  }
+  const int nn = min(G.gsumi(mine), p.max_neighbors);
+  G.sync();
+  const float invTimeHorizon = 1.0f / p.time_horizon;
+  int nl = 0;
+  int j_closest = INT_MAX; /* the candidate of rank 0 */
+  for (int j = G.q; j < n; j += 4) {
+    const float d = cd[j];
+    if (!(d < INFINITY)) continue;
+    int rank = 0;
+    for (int k = 0; k < n; k++) {
+      const float dk = cd[k];
+      rank += (dk < d || (dk == d && k < j)) ? 1 : 0;
+    }
+    if (rank == 0) j_closest = j;
+    if (rank < nn && collab > 0.0f) { /* Agent.cpp:298-364, slot = position in the sorted neighbour list */
+      const Line l = agent_orca_line(position, velocity, radius_, s0[j], s1[j], s2[j], p.radius_scale, invTimeHorizon, p.time_step,
+                                     collab);
+      lines[rank] = make_float4(l.point.x, l.point.y, l.direction.x, l.direction.y);
+    }
+  }
+  if (collab > 0.0f) nl = nn;
+  j_closest = G.gmini(j_closest);
+  if (collab < 0.0f && nn > 0) { /* Agent.cpp:367-416: two lines around the closest neighbour (every lane the same values) */
+    const int o = j_closest;
+    const float4 o0 = s0[o], o1 = s1[o], o2 = s2[o];
+    const float2 relativePosition = sub(V(o0.x, o0.y), position);
+    const float2 ovel = V(o1.x, o1.y);
+    const float distSq = absSq(relativePosition);
+    const float combinedRadius = radius_ + (float)(p.radius_scale * (double)o2.z);
+    const float combinedRadiusSq = sqr(combinedRadius);
+    const float leg = sqrtf(distSq - combinedRadiusSq);
+    const float2 d1 = divs(neg(V(relativePosition.x * leg - relativePosition.y * combinedRadius,
+                                 relativePosition.x * combinedRadius + relativePosition.y * leg)), distSq);
+    const float2 d2 = divs(V(relativePosition.x * leg + relativePosition.y * combinedRadius,
+                             -relativePosition.x * combinedRadius + relativePosition.y * leg), distSq);
+    const float2 pt = add(ovel, relativePosition);
+    if (G.q == 0) {
+      lines[0] = make_float4(pt.x, pt.y, d1.x, d1.y);
+      lines[1] = make_float4(pt.x, pt.y, d2.x, d2.y);
+    }
+    nl = 2;
+    prefVel = add(ovel, mulsv(-collab, normalize(relativePosition)));
+  }
+  G.sync();
+
+  float2 newVel = V(0.f, 0.f);
+  const int lineFail = r4_lp2(G, lines, nl, maxSpeed, prefVel, false, newVel);
+  if (lineFail < nl) r4_lp3(G, lane, lines, nl, lineFail, maxSpeed, newVel, s_proj[grp]);
+  if (G.q != 0) return;
   const float2 newPos = add(position, mulvs(newVel, p.time_step)); /* Agent.cpp:516-521 */
 
   /* RVOPolicy.py:91-110 (fp64) */
@@ -702,5 +998,8 @@ cudaError_t casim_launch_rvo(casim_handle* h, const float* state, const float* c
   h->launches++;
   const dim3 grid((unsigned)((N + RVO_THREADS - 1) / RVO_THREADS)), block(RVO_THREADS);
   if (a.ob.root >= 0) return casim_launch_pdl<RvoArgs>(k_rvo<true>, grid, block, 0, s, a);
-  return casim_launch_pdl<RvoArgs>(k_rvo<false>, grid, block, 0, s, a);
+  static const int one_thread = casim_tuning_int("CASIM_RVO_THREAD_PER_AGENT", 0);
+  if (one_thread) return casim_launch_pdl<RvoArgs>(k_rvo<false>, grid, block, 0, s, a);
+  /* agents only: four lanes per ego agent */
+  return casim_launch_pdl<RvoArgs>(k_rvo4, dim3((unsigned)((N + R4_GROUPS - 1) / R4_GROUPS)), dim3(R4_THREADS), 0, s, a);
 }
