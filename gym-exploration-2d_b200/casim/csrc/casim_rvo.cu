@@ -533,9 +533,9 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
 
 
 /* ------------------------------------------------------------------------------------------------------------------
- * k_rvo4 -- the agents-only case (no static obstacles) mapped onto the GPU: FOUR LANES PER EGO AGENT, 8 agents per warp.
+ * k_rvo4 -- the agents-only case (no static obstacles) mapped onto the GPU: R4_LPA (8) LANES PER EGO AGENT, several agents per warp.
  * One thread per agent leaves the machine with ~9 warps per SM and a serial chain of a few thousand dependent fp32
- * operations per thread (52.9 us for 40 960 agents).  Here the chain is cut in four and there are four times as many
+ * operations per thread (52.9 us for 40 960 agents).  Here the chain is cut in R4_LPA pieces and there are that many times as many
  * warps:
  *   neighbours   lane q evaluates the candidates j = q, q+4, ..; the reference's "sorted insertion with the range
  *                shrinking to the farthest kept neighbour" (Agent.cpp:449-473) is a stable rank by (distSq, index)
@@ -553,32 +553,43 @@ __global__ void __launch_bounds__(RVO_THREADS) k_rvo(const RvoArgs p) {
  * The arithmetic per (line, line) pair is the library's binary32 sequence: new velocities are bit-identical to it. */
 #define R4_MAXL 32 /* ORCA lines per agent (A - 1 <= 31) */
 #define R4_THREADS 128
-#define R4_GROUPS (R4_THREADS / 4)
+#ifndef R4_LPA
+#define R4_LPA 8 /* lanes per ego agent (power of two <= 32).  Measured at 4096 x 10 (profiles/sweep_rvo_lanes.sh): 4 lanes 38.7 us, 8 lanes 36.6 us, 16 lanes 46.1 us; one thread per agent 52.9 us */
+#endif
+#define R4_GROUPS (R4_THREADS / R4_LPA)
 
 struct R4Group {
-  unsigned mask; /* the four lanes of my group */
+  unsigned mask; /* the lanes of my group */
   int q;         /* my lane inside the group */
   __device__ __forceinline__ float gminf(float v) const {
-    float t = __shfl_xor_sync(mask, v, 1);
-    v = (t < v) ? t : v;
-    t = __shfl_xor_sync(mask, v, 2);
-    return (t < v) ? t : v;
+#pragma unroll
+    for (int o = 1; o < R4_LPA; o <<= 1) {
+      const float t = __shfl_xor_sync(mask, v, o);
+      v = (t < v) ? t : v;
+    }
+    return v;
   }
   __device__ __forceinline__ float gmaxf(float v) const {
-    float t = __shfl_xor_sync(mask, v, 1);
-    v = (v < t) ? t : v;
-    t = __shfl_xor_sync(mask, v, 2);
-    return (v < t) ? t : v;
+#pragma unroll
+    for (int o = 1; o < R4_LPA; o <<= 1) {
+      const float t = __shfl_xor_sync(mask, v, o);
+      v = (v < t) ? t : v;
+    }
+    return v;
   }
   __device__ __forceinline__ int gmini(int v) const {
-    v = min(v, __shfl_xor_sync(mask, v, 1));
-    return min(v, __shfl_xor_sync(mask, v, 2));
+#pragma unroll
+    for (int o = 1; o < R4_LPA; o <<= 1) v = min(v, __shfl_xor_sync(mask, v, o));
+    return v;
   }
   __device__ __forceinline__ int gsumi(int v) const {
-    v += __shfl_xor_sync(mask, v, 1);
-    return v + __shfl_xor_sync(mask, v, 2);
+#pragma unroll
+    for (int o = 1; o < R4_LPA; o <<= 1) v += __shfl_xor_sync(mask, v, o);
+    return v;
   }
-  __device__ __forceinline__ unsigned gballot(bool b, int lane) const { return (__ballot_sync(mask, b) >> (lane & ~3)) & 0xFu; }
+  __device__ __forceinline__ unsigned gballot(bool b, int lane) const {
+    return (__ballot_sync(mask, b) >> (lane & ~(R4_LPA - 1))) & (R4_LPA == 32 ? 0xFFFFFFFFu : ((1u << R4_LPA) - 1u));
+  }
   __device__ __forceinline__ void sync() const { __syncwarp(mask); }
 };
 
@@ -600,7 +611,7 @@ __device__ bool r4_lp1(const R4Group& G, const float4* lines, int lineNo, float 
   float tLeft = -dotProduct - sq;
   float tRight = -dotProduct + sq;
   bool infeasible = false;
-  for (int i = G.q; i < lineNo; i += 4) {
+  for (int i = G.q; i < lineNo; i += R4_LPA) {
     const Line Li = r4_load(lines, i);
     const float denominator = det(L.direction, Li.direction);
     const float numerator = det(Li.direction, sub(L.point, Li.point));
@@ -645,8 +656,8 @@ __device__ int r4_lp2(const R4Group& G, const float4* lines, int nl, float radiu
   int i = 0;
   while (i < nl) {
     /* the first violated line at or after i: each lane scans its own lines (k = q mod 4) */
-    int k = i + ((G.q - i) & 3);
-    for (; k < nl; k += 4) {
+    int k = i + ((G.q - i) & (R4_LPA - 1));
+    for (; k < nl; k += R4_LPA) {
       const Line Lk = r4_load(lines, k);
       if (det(Lk.direction, sub(Lk.point, result)) > 0.0f) break;
     }
@@ -670,7 +681,7 @@ __device__ void r4_lp3(const R4Group& G, int lane, const float4* lines, int nl, 
     const Line Li = r4_load(lines, i);
     if (det(Li.direction, sub(Li.point, result)) > distance) {
       int np = 0;
-      for (int j0 = 0; j0 < i; j0 += 4) { /* four projected lines per round, compacted in order */
+      for (int j0 = 0; j0 < i; j0 += R4_LPA) { /* one projected line per lane and round, compacted in order */
         const int j = j0 + G.q;
         bool keep = false;
         Line l;
@@ -710,12 +721,12 @@ __global__ void __launch_bounds__(R4_THREADS) k_rvo4(const RvoArgs p) {
   __shared__ float s_cd[R4_GROUPS][R4_MAXL];
   casim_pdl_enter();
   const size_t N = (size_t)p.E * p.A;
-  const int lane = threadIdx.x & 31, grp = threadIdx.x >> 2;
+  const int lane = threadIdx.x & 31, grp = threadIdx.x / R4_LPA;
   const size_t g = (size_t)blockIdx.x * R4_GROUPS + grp;
   if (g >= N) return; /* whole groups leave together */
   R4Group G;
-  G.q = lane & 3;
-  G.mask = 0xFu << (lane & ~3);
+  G.q = lane & (R4_LPA - 1);
+  G.mask = (R4_LPA == 32 ? 0xFFFFFFFFu : ((1u << R4_LPA) - 1u)) << (lane & ~(R4_LPA - 1));
   const int A = p.A;
   const int e = (int)(g / A), ego = (int)(g - (size_t)e * A);
   const int n = p.n_agents ? min(p.n_agents[e], A) : A;
@@ -743,7 +754,7 @@ __global__ void __launch_bounds__(R4_THREADS) k_rvo4(const RvoArgs p) {
   /* ---- neighbours (Agent.cpp:43-56, 449-473): squared distances, then a stable rank by counting ---- */
   const float rangeSq = sqr(p.neighbor_dist);
   int mine = 0;
-  for (int j = G.q; j < n; j += 4) {
+  for (int j = G.q; j < n; j += R4_LPA) {
     float d = INFINITY;
     if (j != ego && p.max_neighbors > 0) {
       const float4 o0 = s0[j];
@@ -760,7 +771,7 @@ __global__ void __launch_bounds__(R4_THREADS) k_rvo4(const RvoArgs p) {
   const float invTimeHorizon = 1.0f / p.time_horizon;
   int nl = 0;
   int j_closest = INT_MAX; /* the candidate of rank 0 */
-  for (int j = G.q; j < n; j += 4) {
+  for (int j = G.q; j < n; j += R4_LPA) {
     const float d = cd[j];
     if (!(d < INFINITY)) continue;
     int rank = 0;
