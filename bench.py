@@ -148,10 +148,14 @@ def roofline_obj(wl, kern, dominant, step_s, step_bytes, step_must, explore_coun
 
 
 def traffic_for(wl, kernel=None):
+    """dram bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/traffic.json)."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             d = json.load(f).get(wl)
-            return d.get(kernel) if isinstance(d, dict) else d
+        if not isinstance(d, dict):
+            return d
+        key = (kernel or "").split("(")[0]                 # "k_grid_tma(grid+laser)" -> "k_grid_tma"
+        return d.get(key, d.get({"k_rvo": "k_rvo4"}.get(key, key)))
     except Exception:
         return None
 

@@ -6,9 +6,9 @@
 #      RESET one that runs once per ring batch at set-up).
 # Outputs land in gpurun_out/; profiles/summarize_ncu.py + profiles/make_traffic.py turn them into the tracked
 # summaries and profiles/traffic.json.   Usage: bash profiles/capture.sh <tag> [workloads...]
-TAG=${1:-r1g}; shift
+TAG=${1:-r2}; shift
 WLS=${@:-"c2 c3 full c4 c5 rvo"}
-declare -A KERN=( [c2]="k_core<\(int\)0" [c3]="k_laser" [full]="k_grid" [c4]="k_explore" [c5]="k_ga3c_tc" [rvo]="k_rvo" )
+declare -A KERN=( [c2]="k_core<\(int\)0" [c3]="k_laser" [full]="k_grid_tma" [c4]="k_explore" [c5]="k_ga3c_tc" [rvo]="k_rvo4" )
 mkdir -p gpurun_out
 for wl in $WLS; do
   python bench.py --workload $wl > gpurun_out/${TAG}_bench_$wl.json 2> gpurun_out/${TAG}_bench_$wl.err; echo "bench $wl rc=$?"

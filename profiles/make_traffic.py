@@ -11,7 +11,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-SHORT = ("k_core", "k_laser", "k_grid", "k_explore", "k_ga3c_tc", "k_ga3c_state", "k_rvo", "k_flatten")
+SHORT = ("k_core", "k_laser", "k_grid_tma", "k_grid_gather", "k_grid", "k_explore", "k_ga3c_tc", "k_ga3c_state", "k_ga3c_fwd",
+         "k_rvo4", "k_rvo", "k_flatten")
 
 
 def main(tag):

@@ -21,6 +21,10 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio",
         "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_tensor.sum",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor_subpipe_hmma.sum", "sm__inst_executed_pipe_uniform.sum", "sm__inst_executed_pipe_tmem.sum",
+        "smsp__inst_executed_pipe_tensor.sum", "sm__pipe_shared_cycles_active.avg.pct_of_peak_sustained_active",
         "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
@@ -40,6 +44,9 @@ def main(path):
         for w in WANT:
             if w in col:
                 print(w, r[col[w]], units[col[w]])
+        for h in hdr:                                  # every tensor-pipe / tcgen05 counter the report holds
+            if ("tensor" in h or "tmem" in h or "utc" in h.lower()) and h not in WANT and r[col[h]] not in ("", "0", "n/a"):
+                print(h, r[col[h]], units[col[h]])
 
 
 if __name__ == "__main__":
