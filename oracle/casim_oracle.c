@@ -9,10 +9,11 @@
  * Parity status: PINNED for rows a1-a22 of SURVEY.md section 8(a) against outputs of the
  * reference itself executed in the build container (oracle/gen_golden.py ->
  * tests/golden/ (npz files); tests/test_oracle_golden.py) and against the known answers of
- * SURVEY.md Appendix B.  The GA3C-CADRL network numerics (a24) are "parity unpinned":
- * TensorFlow 1.15 is not installable here and the reference holds no test vectors for it;
- * that part restates GA3C_CADRL/network.py:45-98 + TF1 LSTMCell semantics and is
- * cross-checked against torch.nn.LSTMCell only.
+ * SURVEY.md Appendix B.  The GA3C-CADRL network numerics (a24): TensorFlow 1.15 is not
+ * installable here and the reference holds no test vectors for it; casim_oracle_ga3c.c restates
+ * GA3C_CADRL/network.py:45-98 + TF1 LSTMCell semantics and is pinned (round 2) against an independent
+ * numpy float64 evaluation of the TF graph on the reference's shipped IROS18 weights
+ * (oracle/gen_golden_ga3c_probs.py -> tests/golden/ga3c_probs.npz) -- not against TensorFlow itself.
  *
  * Arithmetic: the reference is float64 numpy with the chosen actions rounded to float32
  * (collision_avoidance_env.py:289).  This file follows that (numpy-1.x promotion rules; the

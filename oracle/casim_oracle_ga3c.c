@@ -11,9 +11,12 @@
  *   GA3C_CADRL/network.py:101-151 Config (sizes, normalisation vectors)
  *
  * Parity status: the STATE VECTOR (a23) is PINNED against the reference function executed in the build
- * container (oracle/gen_golden_ga3c.py -> tests/golden/ga3c_state.npz).  The NETWORK NUMERICS (a24) are
- * "PARITY UNPINNED": tensorflow==1.15.0 (requirements.txt:1) is not installable here and the reference holds no
- * test vectors; this file restates the graph and TF1 tf.contrib.rnn.LSTMCell semantics (one kernel [7+64, 256],
+ * container (oracle/gen_golden_ga3c.py -> tests/golden/ga3c_state.npz).  The NETWORK NUMERICS (a24) cannot be pinned to
+ * TensorFlow: tensorflow==1.15.0 (requirements.txt:1) is not installable here and the reference holds no test vectors.
+ * They are pinned instead (round 2) to an independent numpy evaluation of the TF graph, float64 and float32, on the
+ * reference's shipped IROS18 weights and 1574 reference-generated state vectors (oracle/gen_golden_ga3c_probs.py ->
+ * tests/golden/ga3c_probs.npz; test_ga3c_network_vs_tf_graph_golden: |dp| <= 5e-6, argmax identical).  What stays
+ * unpinned is TensorFlow's own float32 rounding.  This file restates the graph and TF1 tf.contrib.rnn.LSTMCell semantics (one kernel [7+64, 256],
  * gate order i, j, f, o, forget_bias 1.0, zero initial state, dynamic_rnn(sequence_length) returning the state
  * at the last valid step) in fp32 and is cross-checked against torch.nn.LSTMCell / torch.nn.functional in
  * tests/test_oracle_golden.py.

@@ -1,6 +1,7 @@
 """GPU parity of the GA3C-CADRL policy (casim_ga3c_forward): the state vector against golden vectors recorded
 from the reference's agents_to_ga3c_cadrl_state (slot order exact), the network forward against the fp32 CPU
-oracle (network numerics are "parity unpinned" w.r.t. TensorFlow, see oracle/casim_oracle_ga3c.c)."""
+oracle and the float64 evaluation of the TF graph on the shipped weights (tests/golden/ga3c_probs.npz; TensorFlow itself
+is not installable here, see oracle/casim_oracle_ga3c.c)."""
 import numpy as np
 import pytest
 
