@@ -12,6 +12,8 @@
  */
 #include "casim_device.cuh"
 
+#include <mutex>
+
 namespace {
 
 __global__ void k_raster(DevCfg c, const float* rects, const int32_t* n_rects, int n_maps, int max_rects,
@@ -295,4 +297,91 @@ cudaError_t casim_launch_map_derive(casim_handle* h, int n_maps, uint8_t* map_ou
   k_edt_cols<<<(n_maps * CASIM_MAP_DIM + 127) / 128, 128, 0, s>>>(n_maps, h->map_planes, gdist);
   k_edt_rows<<<n_maps * CASIM_MAP_DIM, 128, 0, s>>>(n_maps, gdist, h->edf_d2, h->edf, h->dc.cell);
   return cudaGetLastError();
+}
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * casim_rasterize_noalloc -- the allocation-free variant of the map build (include/casim.h).  Same kernels as
+ * casim_set_obstacles (k_raster -> k_derive -> k_edt_cols -> k_edt_rows), but every intermediate lives in ONE file-scope
+ * device array instead of the handle's cudaMalloc'ed buffers:
+ *
+ *   per map (CASIM_NOALLOC_MAX_MAPS of them):  4 bit planes [4][300][10] u32 | column distances [300][300] i32 |
+ *                                              squared distances [300][300] i32          = 768 000 B
+ *
+ * The array is held by every GPU that loads the library until the process exits.  Every word the kernels read is
+ * written earlier in the same call (k_raster writes all of plane 0, k_derive all of planes 1-3, k_edt_cols every column
+ * distance, k_edt_rows every squared distance), so nothing has to start at zero and the previous call's contents are
+ * simply overwritten; two calls that overlap on the GPU (different streams) race on it. */
+namespace {
+
+constexpr size_t NA_PLANE_WORDS = (size_t)CASIM_NUM_PLANES * CASIM_PLANE_WORDS;        /* 12 000 */
+constexpr size_t NA_CELLS = (size_t)CASIM_MAP_DIM * CASIM_MAP_DIM;                      /* 90 000 */
+constexpr size_t NA_WORDS = CASIM_NOALLOC_MAX_MAPS * (NA_PLANE_WORDS + 2 * NA_CELLS);   /* 768 000 words = 3 072 000 B */
+
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NA_WORDS];
+
+constexpr int NA_MAX_DEVICES = 64;
+uint32_t* g_noalloc_ptr[NA_MAX_DEVICES]; /* device address of g_noalloc_scratch on each device (the symbol itself is a
+                                            host-side stand-in and must never be handed to a kernel) */
+std::mutex g_noalloc_mu;
+
+/* once per device, with that device current */
+cudaError_t noalloc_scratch(uint32_t** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= NA_MAX_DEVICES) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    uint32_t* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    if (!p) return cudaErrorInvalidSymbol;
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" int casim_rasterize_noalloc(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps,
+                                       int max_rects, uint8_t* map_out, double* edf_out, void* stream) {
+  if (!h || !rects || !n_rects || (!map_out && !edf_out)) {
+    casim_set_error("casim: casim_rasterize_noalloc: null argument (handle, rects, n_rects and one of map_out / edf_out)");
+    return CASIM_EINVAL;
+  }
+  if (n_maps < 1 || n_maps > CASIM_NOALLOC_MAX_MAPS) {
+    casim_set_error("casim: casim_rasterize_noalloc: n_maps = %d outside 1..CASIM_NOALLOC_MAX_MAPS (%d): the static "
+                    "scratch holds no more; use casim_set_obstacles for larger batches", n_maps, CASIM_NOALLOC_MAX_MAPS);
+    return CASIM_EINVAL;
+  }
+  if (max_rects < 0 || max_rects > CASIM_NOALLOC_MAX_RECTS) {
+    casim_set_error("casim: casim_rasterize_noalloc: max_rects = %d outside 0..CASIM_NOALLOC_MAX_RECTS (%d)", max_rects,
+                    CASIM_NOALLOC_MAX_RECTS);
+    return CASIM_EINVAL;
+  }
+  uint32_t* scratch = nullptr;
+  cudaError_t e = noalloc_scratch(&scratch);
+  if (e != cudaSuccess) {
+    casim_set_error("casim_rasterize_noalloc: cudaGetSymbolAddress(g_noalloc_scratch) failed: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  uint32_t* planes = scratch;                                                    /* [n_maps][4][3000] */
+  int* gdist = reinterpret_cast<int*>(scratch + CASIM_NOALLOC_MAX_MAPS * NA_PLANE_WORDS);   /* [n_maps][300][300] */
+  int32_t* d2 = gdist + CASIM_NOALLOC_MAX_MAPS * NA_CELLS;                       /* [n_maps][300][300] */
+  const int total = n_maps * CASIM_PLANE_WORDS;
+  k_raster<<<(total + 255) / 256, 256, 0, s>>>(h->dc, rects, n_rects, n_maps, max_rects, planes);
+  k_derive<<<(total + 255) / 256, 256, 0, s>>>(n_maps, planes, map_out);
+  if (edf_out) {
+    k_edt_cols<<<(n_maps * CASIM_MAP_DIM + 127) / 128, 128, 0, s>>>(n_maps, planes, gdist);
+    k_edt_rows<<<n_maps * CASIM_MAP_DIM, 128, 0, s>>>(n_maps, gdist, d2, edf_out, h->dc.cell);
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    casim_set_error("casim_rasterize_noalloc: launch failed: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  h->launches += edf_out ? 4 : 2;
+  return 0;
 }

@@ -47,6 +47,7 @@ SYMBOLS = {
     "casim_set_config": (c_int, [c_void_p, _PCFG]),
     "casim_set_obstacles": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "casim_set_map": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "casim_rasterize_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "casim_set_stats_event": (c_int, [c_void_p, c_void_p]),
     "casim_set_grid_packed_output": (c_int, [c_void_p, c_void_p]),
     "casim_set_trajectories": (c_int, [c_void_p, c_void_p, c_int]),

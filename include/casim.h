@@ -198,6 +198,24 @@ int casim_set_obstacles(casim_handle* h, const float* rects, const int32_t* n_re
 /* Same, from a ready-made occupancy raster [n_maps,300,300] uint8 (Map.static_map). */
 int casim_set_map(casim_handle* h, const uint8_t* static_map, int n_maps, void* stream);
 
+/* Allocation-free map build.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same
+ * kernels as casim_set_obstacles, but with every intermediate (bit planes, column distances, squared distances) in one
+ * file-scope `static __device__` array of the library (3 072 000 B, held by every GPU that loads the library until the
+ * process exits) instead of the handle's buffers; the call itself allocates nothing and leaves the handle's own map
+ * untouched (the handle supplies the Map geometry of its config only).  All pointers are DEVICE pointers.
+ *   rects [n_maps,max_rects,4], n_rects [n_maps]: as casim_set_obstacles;
+ *   map_out  (optional) [n_maps,300,300] uint8  = what casim_set_obstacles writes to its map_out, bit for bit;
+ *   edf_out  (optional) [n_maps,300,300] double = edfMap.map, sqrt(squared distance) * cell (information_models/edfMap.py:11-12).
+ * Limits: 1 <= n_maps <= CASIM_NOALLOC_MAX_MAPS and max_rects <= CASIM_NOALLOC_MAX_RECTS, anything beyond is refused with
+ * CASIM_EINVAL and a casim_last_error() message.  Every call shares the one array and overwrites the previous call's
+ * contents (every word read is written earlier in the same call, nothing needs clearing); calls that overlap on the GPU
+ * -- different streams, or different handles on one device -- race on it: serialise them. */
+#define CASIM_NOALLOC_MAX_MAPS 4
+#define CASIM_NOALLOC_MAX_RECTS 256
+int casim_rasterize_noalloc(casim_handle* h, const float* rects, const int32_t* n_rects, int n_maps, int max_rects,
+                            uint8_t* map_out, double* edf_out, void* stream);
+
 /* Multi-GPU statistics hook (the per-step all-reduce of the [8] episode statistics, the design's only
  * collective; the reference's counterpart is the rolling n_collisions / n_timeouts of collision_avoidance_env.py:147-148,
  * 218-221).  When an event (cudaEvent_t passed as void*) is set, every casim_step records it on its stream right after
