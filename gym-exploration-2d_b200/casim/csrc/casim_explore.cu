@@ -185,8 +185,9 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
 
   __shared__ PoseBox s_pose[X_NPOSE];
   __shared__ double s_det[CASIM_MAX_AGENTS][2];
-  __shared__ int s_ndet, s_qn;
-  __shared__ unsigned int s_queue[XQ_CAP];
+  __shared__ int s_ndet;
+  __shared__ int s_off[X_NPOSE + 1];                 /* prefix of the box sizes: cells of pose k are [s_off[k], s_off[k+1]) */
+  __shared__ unsigned int s_wq[X_THREADS / 32][64];  /* per-warp queue of wedge survivors: (pose << 12) | (j << 6) | i */
   __shared__ unsigned long long s_mi[X_NPOSE];
   __shared__ unsigned int s_vis[64 * 64]; /* per target-map cell: bit k = visible from candidate pose k (this batch) */
   __shared__ unsigned int s_cnt[4];
@@ -199,7 +200,6 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
 
   if (tid == 0) {
     s_ndet = 0;
-    s_qn = 0;
     double x, y, h, rad;
     if (restart) { /* agent.py:21-33 with the initial condition kept by casim_reset */
       const float* in = p.init + (size_t)g * 7;
@@ -258,125 +258,138 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
     if (tid == 0) s_ndet = __popc(m);
   }
   /* ---- the ten poses: 0 = current, 1..9 = get_next_pose(action a) (ig_greedy.py:81-93) ---- */
-  if (tid >= 32 && tid < 32 + X_NPOSE) {
-    int k = tid - 32;
-    double x = px, y = py, h = ph;
-    int feasible = 1;
-    if (k > 0) {
-      int a = k - 1;
-      double v = 2.0 * (double)(a / 3), w = (a % 3 == 0) ? -CASIM_PI : ((a % 3 == 2) ? CASIM_PI : 0.0);
-      double sn, cs;
-      sincos(ph, &sn, &cs);
-      double vx = cs * v + (-sn) * 0.0, vy = sn * v + cs * 0.0;
-      x = px + vx * c.ig_dt;
-      y = py + vy * c.ig_dt;
-      h = ph + w * c.ig_dt;
-      unsigned cl = 0;
-      feasible = edf_value(c, d2, x, y, cl) > prad + 0.1;
-      cnt_samples++;
-      cnt_clamped += cl;
+  if ((tid >> 5) == 1) { /* warp 1, lanes 0..9 */
+    const int k = tid - 32;
+    int cells = 0;
+    if (k < X_NPOSE) {
+      double x = px, y = py, h = ph;
+      int feasible = 1;
+      if (k > 0) {
+        int a = k - 1;
+        double v = 2.0 * (double)(a / 3), w = (a % 3 == 0) ? -CASIM_PI : ((a % 3 == 2) ? CASIM_PI : 0.0);
+        double sn, cs;
+        sincos(ph, &sn, &cs);
+        double vx = cs * v + (-sn) * 0.0, vy = sn * v + cs * 0.0;
+        x = px + vx * c.ig_dt;
+        y = py + vy * c.ig_dt;
+        h = ph + w * c.ig_dt;
+        unsigned cl = 0;
+        feasible = edf_value(c, d2, x, y, cl) > prad + 0.1;
+        cnt_samples++;
+        cnt_clamped += cl;
+      }
+      PoseBox b;
+      pose_box(c, x, y, h, b, cnt_clamped);
+      b.feasible = feasible;
+      if (!feasible) b.w = b.h = 0;
+      s_pose[k] = b;
+      cells = b.w * b.h;
     }
-    PoseBox b;
-    pose_box(c, x, y, h, b, cnt_clamped);
-    b.feasible = feasible;
-    if (!feasible) b.w = b.h = 0;
-    s_pose[k] = b;
+    int incl = cells; /* inclusive prefix over the warp */
+#pragma unroll
+    for (int d = 1; d < 16; d <<= 1) {
+      const int up = __shfl_up_sync(FULL_MASK, incl, d);
+      if (k >= d) incl += up;
+    }
+    if (k < X_NPOSE) s_off[k + 1] = incl;
+    if (k == 0) s_off[0] = 0;
   }
   __syncthreads();
 
   const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
   const int ndet = s_ndet;
-  int pstart = 0;
-  while (pstart < X_NPOSE) {
-    /* pose 0 (the update) runs alone; the candidate poses are batched while their boxes fit the queue */
-    int pend = pstart + 1;
-    int total = s_pose[pstart].w * s_pose[pstart].h;
-    if (pstart > 0)
-      while (pend < X_NPOSE && total + s_pose[pend].w * s_pose[pend].h <= XQ_CAP) {
-        total += s_pose[pend].w * s_pose[pend].h;
-        pend++;
-      }
-    /* ---- phase 1: range / FOV wedge test of every box cell (targetMap.py:73-79) ---- */
-    int k = pstart, base = 0, cnt = s_pose[pstart].w * s_pose[pstart].h; /* idx only grows: the pose cursor never rewinds */
-    for (int idx = tid; idx < total; idx += X_THREADS) {
-      while (idx - base >= cnt) {
-        base += cnt;
-        k++;
-        cnt = s_pose[k].w * s_pose[k].h;
-      }
-      const int off = idx - base;
-      const PoseBox& b = s_pose[k];
-      int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
-      int i = b.x0 + ii, j = b.y0 + jj;
-      double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
-      double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy; /* R = ((c, s), (-s, c)) */
-      cnt_tested++;
-      if (in_wedge(c, r0, r1)) {
-        int q = atomicAdd(&s_qn, 1);
-        s_queue[q] = ((unsigned)k << 12) | ((unsigned)j << 6) | (unsigned)i;
-      }
-    }
-    __syncthreads();
-    const int qn = s_qn;
-    /* ---- phase 2: line of sight, then odds update (pose 0) or mutual information (candidates) ---- */
-    for (int q = tid; q < qn; q += X_THREADS) {
-      unsigned en = s_queue[q];
-      int k = (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
-      const PoseBox& b = s_pose[k];
-      double gx = cell_centre(c, i, c.map_hw), gy = cell_centre(c, j, c.map_hh);
-      if (!line_of_sight(c, d2, b.x, b.y, gx, gy, cnt_samples, cnt_clamped)) continue;
-      cnt_visible++;
+  const int lane = tid & 31, wid = tid >> 5;
+  unsigned int* wq = s_wq[wid];
+
+  /* line of sight of one queued (pose, cell), then the odds update (pose 0) or the visibility bit (candidates) */
+  auto trace = [&](unsigned en) {
+    const int k = (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
+    const PoseBox& b = s_pose[k];
+    const double gx = cell_centre(c, i, c.map_hw), gy = cell_centre(c, j, c.map_hh);
+    if (!line_of_sight(c, d2, b.x, b.y, gx, gy, cnt_samples, cnt_clamped)) return;
+    cnt_visible++;
+    if (k == 0) { /* targetMap.py:104-126; every cell of pose 0's box is queued at most once: no race on the belief */
       float* cellp = belief + j * dim + i;
-      if (k == 0) { /* targetMap.py:104-126 */
-        double rs = c.ig_remp;
-        if (ndet > 0) {
-          double dx = gx - b.x, dy = gy - b.y;
-          double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
-          for (int t = 0; t < ndet; t++) {
-            double ex = s_det[t][0] - r0, ey = s_det[t][1] - r1;
-            if (sqrt(ex * ex + ey * ey) < c.ig_det_thresh) {
-              rs = c.ig_rocc;
-              break;
-            }
+      double rs = c.ig_remp;
+      if (ndet > 0) {
+        double dx = gx - b.x, dy = gy - b.y;
+        double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy;
+        for (int t = 0; t < ndet; t++) {
+          double ex = s_det[t][0] - r0, ey = s_det[t][1] - r1;
+          if (sqrt(ex * ex + ey * ey) < c.ig_det_thresh) {
+            rs = c.ig_rocc;
+            break;
           }
         }
-        *cellp = fminf((float)((double)*cellp * rs), FLT_MAX);
-      } else {
-        /* The candidate poses' wedges overlap heavily and a cell's mutual information depends on the cell alone:
-         * record who sees it, evaluate the two fp64 logs once per cell below (not once per pose and cell). */
-        atomicOr(&s_vis[j * 64 + i], 1u << k);
       }
+      *cellp = fminf((float)((double)*cellp * rs), FLT_MAX);
+    } else {
+      /* The candidate poses' wedges overlap heavily and a cell's mutual information depends on the cell alone:
+       * record who sees it, evaluate the two fp64 logs once per cell below (not once per pose and cell). */
+      atomicOr(&s_vis[j * 64 + i], 1u << k);
     }
-    __syncthreads();
-    if (pstart > 0) { /* targetMap.py:130-143 over the union box of this batch's poses */
-      int ux0 = INT_MAX, uy0 = INT_MAX, ux1 = INT_MIN, uy1 = INT_MIN;
-      for (int k = pstart; k < pend; k++) {
-        const PoseBox& b = s_pose[k];
-        if (b.w <= 0 || b.h <= 0) continue;
-        ux0 = min(ux0, b.x0); uy0 = min(uy0, b.y0);
-        ux1 = max(ux1, b.x0 + b.w); uy1 = max(uy1, b.y0 + b.h);
-      }
-      const int uw = ux1 > ux0 ? ux1 - ux0 : 0, uh = uy1 > uy0 ? uy1 - uy0 : 0; /* (all boxes empty: nothing to do) */
-      for (int idx = tid; idx < uw * uh; idx += X_THREADS) {
-        const int ii = idx / uh, jj = idx - ii * uh;
-        const int i = ux0 + ii, j = uy0 + jj;
-        unsigned m = s_vis[j * 64 + i];
-        if (m == 0u) continue;
-        s_vis[j * 64 + i] = 0u;
-        const double mi = cell_mi(c, (double)belief[j * dim + i], log_rocc, log_remp);
-        const unsigned long long fx = (unsigned long long)__double2ll_rn(mi * X_MI_SCALE);
-        while (m) { /* integer (fixed-point) sums: independent of the order of arrival */
-          const int k = __ffs(m) - 1;
-          m &= m - 1;
-          atomicAdd(&s_mi[k], fx);
-        }
-      }
+  };
+
+  /* ---- ONE sweep over the cells of all ten boxes, no CTA barrier inside: each warp tests 32 consecutive box cells
+   * against the range / FOV wedge (targetMap.py:73-79), appends the survivors to ITS OWN queue (ballot-compacted) and
+   * traces a full warp's worth of lines of sight as soon as 32 are waiting, so that wedge tests and traces of different
+   * warps overlap instead of meeting at a barrier per phase and per pose batch. ---- */
+  const int total = s_off[X_NPOSE];
+  int k = 0, wqn = 0;
+  for (int base = wid * 32; base < total; base += X_THREADS) { /* warp-uniform trip count */
+    const int idx = base + lane;
+    bool keep = false;
+    unsigned en = 0u;
+    if (idx < total) {
+      while (idx >= s_off[k + 1]) k++; /* idx only grows: the pose cursor never rewinds */
+      const int off = idx - s_off[k];
+      const PoseBox& b = s_pose[k];
+      const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
+      const int i = b.x0 + ii, j = b.y0 + jj;
+      const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
+      const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy; /* R = ((c, s), (-s, c)) */
+      cnt_tested++;
+      keep = in_wedge(c, r0, r1);
+      en = ((unsigned)k << 12) | ((unsigned)j << 6) | (unsigned)i;
     }
-    __syncthreads();
-    if (tid == 0) s_qn = 0;
-    __syncthreads();
-    pstart = pend;
+    const unsigned m = __ballot_sync(FULL_MASK, keep);
+    if (keep) wq[wqn + __popc(m & ((1u << lane) - 1u))] = en;
+    wqn += __popc(m);
+    __syncwarp();
+    if (wqn >= 32) {
+      wqn -= 32;
+      const unsigned e2 = wq[wqn + lane];
+      __syncwarp();
+      trace(e2);
+    }
   }
+  if (lane < wqn) trace(wq[lane]);
+  __syncthreads(); /* pose 0's odds update and every visibility bit are in place */
+
+  { /* targetMap.py:130-143 over the union box of the candidate poses, on the UPDATED belief */
+    int ux0 = INT_MAX, uy0 = INT_MAX, ux1 = INT_MIN, uy1 = INT_MIN;
+    for (int kk = 1; kk < X_NPOSE; kk++) {
+      const PoseBox& b = s_pose[kk];
+      if (b.w <= 0 || b.h <= 0) continue;
+      ux0 = min(ux0, b.x0); uy0 = min(uy0, b.y0);
+      ux1 = max(ux1, b.x0 + b.w); uy1 = max(uy1, b.y0 + b.h);
+    }
+    const int uw = ux1 > ux0 ? ux1 - ux0 : 0, uh = uy1 > uy0 ? uy1 - uy0 : 0; /* (all boxes empty: nothing to do) */
+    for (int idx = tid; idx < uw * uh; idx += X_THREADS) {
+      const int ii = idx / uh, jj = idx - ii * uh;
+      const int i = ux0 + ii, j = uy0 + jj;
+      unsigned m = s_vis[j * 64 + i];
+      if (m == 0u) continue;
+      const double mi = cell_mi(c, (double)belief[j * dim + i], log_rocc, log_remp);
+      const unsigned long long fx = (unsigned long long)__double2ll_rn(mi * X_MI_SCALE);
+      while (m) { /* integer (fixed-point) sums: independent of the order of arrival */
+        const int kk = __ffs(m) - 1;
+        m &= m - 1;
+        atomicAdd(&s_mi[kk], fx);
+      }
+    }
+  }
+  __syncthreads();
 
   /* ---- greedy argmax, strict '>' in action order, starting from -1 (ig_greedy.py:64-78) ---- */
   if (tid == 0) {
