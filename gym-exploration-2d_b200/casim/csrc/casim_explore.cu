@@ -161,7 +161,10 @@ __device__ __forceinline__ void pose_box(const DevCfg& c, double x, double y, do
   b.inv_h = b.h > 0 ? ((1 << 18) + b.h - 1) / b.h : 0;
 }
 
-__global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
+/* One CTA per explorer.  COUNT: instrumentation counters (cells tested / EDF samples / visible cells / clamped indices)
+ * compiled in only when the caller passes a counters buffer. */
+template <bool COUNT>
+__global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
   const DevCfg& c = p.c;
   const int g = blockIdx.x;
   const int e = g / p.A, ai = g - e * p.A;
@@ -171,7 +174,7 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
   const float4 p5 = p.state[5 * N + g];
   const int type = __float_as_int(p5.w), flags = __float_as_int(p5.z);
   if ((type & 0xff) != CASIM_POLICY_IG_GREEDY) return;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const bool restart = c.auto_reset && p.prev_game_over && p.init && p.prev_game_over[e];
   if (!restart && (flags & CASIM_F_IS_DONE)) { /* collision_avoidance_env.py:298-300: no policy query */
     if (tid == 0) {
@@ -185,42 +188,37 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
 
   __shared__ PoseBox s_pose[X_NPOSE];
   __shared__ double s_det[CASIM_MAX_AGENTS][2];
-  __shared__ int s_ndet;
+  __shared__ double s_log[2];                        /* log(ig_rocc), log(ig_remp) */
+  __shared__ int s_ndet, s_ticket;
   __shared__ int s_off[X_NPOSE + 1];                 /* prefix of the box sizes: cells of pose k are [s_off[k], s_off[k+1]) */
-  __shared__ unsigned int s_wq[X_THREADS / 32][64];  /* per-warp queue of wedge survivors: (pose << 12) | (j << 6) | i */
-  __shared__ unsigned long long s_mi[X_NPOSE];
-  __shared__ unsigned int s_vis[64 * 64]; /* per target-map cell: bit k = visible from candidate pose k (this batch) */
+  __shared__ unsigned int s_wq[X_THREADS / 32][64];  /* per-warp queue: wedge survivors (pose << 12) | (j << 6) | i, then seen cells */
+  __shared__ long long s_miw[X_THREADS / 32][X_NPOSE]; /* per-warp fixed-point mutual-information sums */
+  __shared__ unsigned int s_vis[64 * 64];            /* per target-map cell: bit k = visible from candidate pose k */
   __shared__ unsigned int s_cnt[4];
-  __shared__ double s_pose0[4]; /* x, y, heading, radius */
 
   const int dim = c.ig_dim;
   float* belief = p.belief + (size_t)g * dim * dim;
   const double* d2 = p.edf + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
   unsigned cnt_tested = 0, cnt_samples = 0, cnt_visible = 0, cnt_clamped = 0;
 
-  if (tid == 0) {
-    s_ndet = 0;
-    double x, y, h, rad;
-    if (restart) { /* agent.py:21-33 with the initial condition kept by casim_reset */
-      const float* in = p.init + (size_t)g * 7;
-      x = in[0]; y = in[1]; rad = in[4];
-      h = isnan(in[6]) ? atan2((double)in[3] - (double)in[1], (double)in[2] - (double)in[0]) : (double)in[6];
-    } else {
-      const float4 p0 = p.state[g], p2 = p.state[2 * N + g];
-      x = p0.x; y = p0.y; h = p0.z; rad = p2.z;
-    }
-    s_pose0[0] = x; s_pose0[1] = y; s_pose0[2] = h; s_pose0[3] = rad;
+  /* the explorer's pose: every thread reads it itself (uniform loads), nobody waits for a broadcast through shared memory */
+  double px, py, ph, prad;
+  if (restart) { /* agent.py:21-33 with the initial condition kept by casim_reset */
+    const float* in = p.init + (size_t)g * 7;
+    px = in[0]; py = in[1]; prad = in[4];
+    ph = isnan(in[6]) ? atan2((double)in[3] - (double)in[1], (double)in[2] - (double)in[0]) : (double)in[6];
+  } else {
+    const float4 p0 = p.state[g], p2 = p.state[2 * N + g];
+    px = p0.x; py = p0.y; ph = p0.z; prad = p2.z;
   }
-  if (tid < X_NPOSE) s_mi[tid] = 0ull;
   for (int k = tid; k < 64 * 64; k += X_THREADS) s_vis[k] = 0u;
-  if (tid < 4) s_cnt[tid] = 0u;
+  if (COUNT && tid < 4) s_cnt[tid] = 0u;
+  if (tid == 0) s_ticket = 0;
   if (restart)
     for (int k = tid; k < dim * dim; k += X_THREADS) belief[k] = (float)c.ig_prior;
-  __syncthreads();
-  const double px = s_pose0[0], py = s_pose0[1], ph = s_pose0[2], prad = s_pose0[3];
 
-  /* ---- detector emulation (ig_greedy.py:45-62) + ego-frame detections (targetMap.py:91-103) ---- */
-  if (tid < 32) {
+  if (wid == 0) {
+    /* ---- detector emulation (ig_greedy.py:45-62) + ego-frame detections (targetMap.py:91-103) ---- */
     double rx = 0, ry = 0;
     bool hit = false;
     if (restart) {
@@ -256,10 +254,9 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
       s_det[k][1] = -sn * dx + cs * dy;
     }
     if (tid == 0) s_ndet = __popc(m);
-  }
-  /* ---- the ten poses: 0 = current, 1..9 = get_next_pose(action a) (ig_greedy.py:81-93) ---- */
-  if ((tid >> 5) == 1) { /* warp 1, lanes 0..9 */
-    const int k = tid - 32;
+  } else if (wid == 1) {
+    /* ---- the ten poses: 0 = current, 1..9 = get_next_pose(action a) (ig_greedy.py:81-93), lanes 0..9 ---- */
+    const int k = lane;
     int cells = 0;
     if (k < X_NPOSE) {
       double x = px, y = py, h = ph;
@@ -293,12 +290,14 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
     }
     if (k < X_NPOSE) s_off[k + 1] = incl;
     if (k == 0) s_off[0] = 0;
+  } else if (tid == 64) {
+    s_log[0] = log(c.ig_rocc);
+  } else if (tid == 65) {
+    s_log[1] = log(c.ig_remp);
   }
   __syncthreads();
 
-  const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
   const int ndet = s_ndet;
-  const int lane = tid & 31, wid = tid >> 5;
   unsigned int* wq = s_wq[wid];
 
   /* line of sight of one queued (pose, cell), then the odds update (pose 0) or the visibility bit (candidates) */
@@ -330,18 +329,22 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
     }
   };
 
-  /* ---- ONE sweep over the cells of all ten boxes, no CTA barrier inside: each warp tests 32 consecutive box cells
-   * against the range / FOV wedge (targetMap.py:73-79), appends the survivors to ITS OWN queue (ballot-compacted) and
-   * traces a full warp's worth of lines of sight as soon as 32 are waiting, so that wedge tests and traces of different
-   * warps overlap instead of meeting at a barrier per phase and per pose batch. ---- */
+  /* ---- ONE sweep over the cells of all ten boxes, no CTA barrier inside: a warp draws 32 consecutive box cells from a
+   * shared ticket, tests them against the range / FOV wedge (targetMap.py:73-79), appends the survivors to ITS OWN
+   * queue (ballot-compacted) and traces a full warp's worth of lines of sight as soon as 32 are waiting, so that wedge
+   * tests and traces of different warps overlap and a warp that drew long rays simply draws fewer tickets. ---- */
   const int total = s_off[X_NPOSE];
   int k = 0, wqn = 0;
-  for (int base = wid * 32; base < total; base += X_THREADS) { /* warp-uniform trip count */
+  for (;;) {
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&s_ticket, 32);
+    base = __shfl_sync(FULL_MASK, base, 0);
+    if (base >= total) break;
     const int idx = base + lane;
     bool keep = false;
     unsigned en = 0u;
     if (idx < total) {
-      while (idx >= s_off[k + 1]) k++; /* idx only grows: the pose cursor never rewinds */
+      while (idx >= s_off[k + 1]) k++; /* tickets only grow: the pose cursor never rewinds */
       const int off = idx - s_off[k];
       const PoseBox& b = s_pose[k];
       const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
@@ -366,7 +369,35 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
   if (lane < wqn) trace(wq[lane]);
   __syncthreads(); /* pose 0's odds update and every visibility bit are in place */
 
-  { /* targetMap.py:130-143 over the union box of the candidate poses, on the UPDATED belief */
+  /* ---- targetMap.py:130-143 over the union box of the candidate poses, on the UPDATED belief.  Seen cells are
+   * compacted into the warp's queue first so that the two fp64 logs per cell run on full warps; the per-pose sums are
+   * integer (fixed point, 2^-44): independent of the order of arrival, accumulated with warp reductions on three
+   * 22-bit pieces (lane k of every warp carries pose k's sum), no shared-memory atomics. ---- */
+  {
+    const double log_rocc = s_log[0], log_remp = s_log[1];
+    long long acc = 0;
+    auto score = [&](bool valid, unsigned cell) {
+      unsigned m = 0u;
+      long long v = 0;
+      if (valid) {
+        const int j = (int)(cell >> 6), i = (int)(cell & 63u);
+        m = s_vis[j * 64 + i];
+        v = __double2ll_rn(cell_mi(c, (double)belief[j * dim + i], log_rocc, log_remp) * X_MI_SCALE);
+      }
+      const unsigned lo = (unsigned)(v & 0x3fffffll), mid = (unsigned)((v >> 22) & 0x3fffffll);
+      const int hi = (int)(v >> 44); /* arithmetic shift: v == (hi << 44) + (mid << 22) + lo for negative v too */
+      unsigned um = __reduce_or_sync(FULL_MASK, m);
+      while (um) {
+        const int kk = __ffs(um) - 1;
+        um &= um - 1;
+        const bool on = (m >> kk) & 1u;
+        const unsigned a = __reduce_add_sync(FULL_MASK, on ? lo : 0u), b2 = __reduce_add_sync(FULL_MASK, on ? mid : 0u);
+        const int c2 = __reduce_add_sync(FULL_MASK, on ? hi : 0);
+        if (lane == kk)
+          acc = (long long)((unsigned long long)acc + (unsigned long long)a + ((unsigned long long)b2 << 22) +
+                            ((unsigned long long)(long long)c2 << 44));
+      }
+    };
     int ux0 = INT_MAX, uy0 = INT_MAX, ux1 = INT_MIN, uy1 = INT_MIN;
     for (int kk = 1; kk < X_NPOSE; kk++) {
       const PoseBox& b = s_pose[kk];
@@ -375,19 +406,31 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
       ux1 = max(ux1, b.x0 + b.w); uy1 = max(uy1, b.y0 + b.h);
     }
     const int uw = ux1 > ux0 ? ux1 - ux0 : 0, uh = uy1 > uy0 ? uy1 - uy0 : 0; /* (all boxes empty: nothing to do) */
-    for (int idx = tid; idx < uw * uh; idx += X_THREADS) {
-      const int ii = idx / uh, jj = idx - ii * uh;
-      const int i = ux0 + ii, j = uy0 + jj;
-      unsigned m = s_vis[j * 64 + i];
-      if (m == 0u) continue;
-      const double mi = cell_mi(c, (double)belief[j * dim + i], log_rocc, log_remp);
-      const unsigned long long fx = (unsigned long long)__double2ll_rn(mi * X_MI_SCALE);
-      while (m) { /* integer (fixed-point) sums: independent of the order of arrival */
-        const int kk = __ffs(m) - 1;
-        m &= m - 1;
-        atomicAdd(&s_mi[kk], fx);
+    const int ncell = uw * uh;
+    int qn = 0;
+    for (int base = wid * 32; base < ncell; base += X_THREADS) { /* warp-uniform trip count */
+      const int idx = base + lane;
+      bool seen = false;
+      unsigned cell = 0u;
+      if (idx < ncell) {
+        const int ii = idx / uh, jj = idx - ii * uh;
+        const int i = ux0 + ii, j = uy0 + jj;
+        seen = s_vis[j * 64 + i] != 0u;
+        cell = ((unsigned)j << 6) | (unsigned)i;
+      }
+      const unsigned m = __ballot_sync(FULL_MASK, seen);
+      if (seen) wq[qn + __popc(m & ((1u << lane) - 1u))] = cell;
+      qn += __popc(m);
+      __syncwarp();
+      if (qn >= 32) {
+        qn -= 32;
+        const unsigned c2 = wq[qn + lane];
+        __syncwarp();
+        score(true, c2);
       }
     }
+    if (qn > 0) score(lane < qn, lane < qn ? wq[lane] : 0u);
+    if (lane < X_NPOSE) s_miw[wid][lane] = acc;
   }
   __syncthreads();
 
@@ -398,7 +441,9 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
     for (int a = 0; a < 9; a++) {
       double mi = -1.0;
       if (s_pose[a + 1].feasible) {
-        mi = (double)(long long)s_mi[a + 1] / X_MI_SCALE;
+        unsigned long long sum = 0ull;
+        for (int w = 0; w < X_THREADS / 32; w++) sum += (unsigned long long)s_miw[w][a + 1];
+        mi = (double)(long long)sum / X_MI_SCALE;
         if (mi > max_mi) {
           max_mi = mi;
           a0 = 2.0f * (float)(a / 3);
@@ -411,7 +456,7 @@ __global__ void __launch_bounds__(X_THREADS) k_explore(const ExploreArgs p) {
     p.policy_actions[2 * g + 1] = a1;
     if (p.best_mi) p.best_mi[g] = (float)max_mi;
   }
-  if (p.counters) { /* instrumentation only: per-CTA totals, one global atomic per counter */
+  if (COUNT) { /* instrumentation only: per-CTA totals, one global atomic per counter */
     unsigned v0 = __reduce_add_sync(FULL_MASK, cnt_tested), v1 = __reduce_add_sync(FULL_MASK, cnt_samples);
     unsigned v2 = __reduce_add_sync(FULL_MASK, cnt_visible), v3 = __reduce_add_sync(FULL_MASK, cnt_clamped);
     if ((tid & 31) == 0) {
@@ -814,7 +859,8 @@ cudaError_t casim_launch_explore(casim_handle* h, const float* state, const floa
     if (e != cudaSuccess) return e;
   }
   h->launches++;
-  k_explore<<<(unsigned)((size_t)h->E * h->A), X_THREADS, 0, s>>>(a);
+  if (counters) k_explore<true><<<(unsigned)((size_t)h->E * h->A), X_THREADS, 0, s>>>(a);
+  else k_explore<false><<<(unsigned)((size_t)h->E * h->A), X_THREADS, 0, s>>>(a);
   return cudaGetLastError();
 }
 
