@@ -189,11 +189,11 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
   __shared__ PoseBox s_pose[X_NPOSE];
   __shared__ double s_det[CASIM_MAX_AGENTS][2];
   __shared__ double s_log[2];                        /* log(ig_rocc), log(ig_remp) */
-  __shared__ int s_ndet, s_ticket;
-  __shared__ int s_off[X_NPOSE + 1];                 /* prefix of the box sizes: cells of pose k are [s_off[k], s_off[k+1]) */
+  __shared__ int s_ndet;
+  __shared__ int s_off[X_NPOSE + 1];                 /* prefix of the box sizes: cells of pose k are [s_off[k], s_off[k+1]); pose 2: none */
   __shared__ unsigned int s_wq[X_THREADS / 32][64];  /* per-warp queue: wedge survivors (pose << 12) | (j << 6) | i, then seen cells */
   __shared__ long long s_miw[X_THREADS / 32][X_NPOSE]; /* per-warp fixed-point mutual-information sums */
-  __shared__ unsigned int s_vis[64 * 64];            /* per target-map cell: bit k = visible from candidate pose k */
+  __shared__ unsigned int s_vis[64 * 64];            /* per target-map cell: bit 16+k = inside pose k's wedge, bit k = visible from candidate pose k */
   __shared__ unsigned int s_cnt[4];
 
   const int dim = c.ig_dim;
@@ -213,7 +213,6 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
   }
   for (int k = tid; k < 64 * 64; k += X_THREADS) s_vis[k] = 0u;
   if (COUNT && tid < 4) s_cnt[tid] = 0u;
-  if (tid == 0) s_ticket = 0;
   if (restart)
     for (int k = tid; k < dim * dim; k += X_THREADS) belief[k] = (float)c.ig_prior;
 
@@ -280,7 +279,7 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
       b.feasible = feasible;
       if (!feasible) b.w = b.h = 0;
       s_pose[k] = b;
-      cells = b.w * b.h;
+      cells = k == 2 ? 0 : b.w * b.h; /* pose 2 rides on pose 0 (phase 1) */
     }
     int incl = cells; /* inclusive prefix over the warp */
 #pragma unroll
@@ -300,14 +299,53 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
   const int ndet = s_ndet;
   unsigned int* wq = s_wq[wid];
 
-  /* line of sight of one queued (pose, cell), then the odds update (pose 0) or the visibility bit (candidates) */
+  /* ---- phase 1: range / FOV wedge test (targetMap.py:73-79) of every cell of every pose's box, one dense sweep over the
+   * concatenated boxes; a survivor sets bit 16+k of its cell's word.  Pose 2 (action v = 0, w = 0) IS pose 0 -- same
+   * position, heading and box, bit for bit -- so its tests are not repeated: its bit is set with pose 0's. ---- */
+  {
+    const int total = s_off[X_NPOSE];
+    const unsigned twin = s_pose[2].feasible ? (1u << 18) : 0u;
+    int k = 0;
+    for (int idx = tid; idx < total; idx += X_THREADS) {
+      while (idx >= s_off[k + 1]) k++; /* idx only grows: the pose cursor never rewinds */
+      const int off = idx - s_off[k];
+      const PoseBox& b = s_pose[k];
+      const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
+      const int i = b.x0 + ii, j = b.y0 + jj;
+      const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
+      const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy; /* R = ((c, s), (-s, c)) */
+      cnt_tested += (k == 0 && twin) ? 2u : 1u;
+      if (in_wedge(c, r0, r1)) atomicOr(&s_vis[j * 64 + i], (1u << (16 + k)) | (k == 0 ? twin : 0u));
+    }
+  }
+  __syncthreads();
+
+  /* ---- phase 2: lines of sight.  The ten poses have only THREE distinct positions (speed 0 / 2 / 4 along the
+   * heading; the turn rate changes the heading alone: ig_greedy.py:81-93) and edfMap.checkVisibility depends on the two
+   * end points only, so one ray per (position, cell) serves every pose of that position whose wedge holds the cell:
+   * groups {0,1,2,3}, {4,5,6}, {7,8,9}.  Cells are compacted into the warp's queue and traced 32 at a time. ---- */
+  int ux0 = INT_MAX, uy0 = INT_MAX, ux1 = INT_MIN, uy1 = INT_MIN; /* union box of all poses */
+  for (int kk = 0; kk < X_NPOSE; kk++) {
+    const PoseBox& b = s_pose[kk];
+    if (b.w <= 0 || b.h <= 0) continue;
+    ux0 = min(ux0, b.x0); uy0 = min(uy0, b.y0);
+    ux1 = max(ux1, b.x0 + b.w); uy1 = max(uy1, b.y0 + b.h);
+  }
+  const int uw = ux1 > ux0 ? ux1 - ux0 : 0, uh = uy1 > uy0 ? uy1 - uy0 : 0; /* (all boxes empty: nothing to do) */
+  const int ncell = uw * uh;
+
   auto trace = [&](unsigned en) {
-    const int k = (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
-    const PoseBox& b = s_pose[k];
+    const int grp = (int)(en >> 12), j = (int)((en >> 6) & 63u), i = (int)(en & 63u);
+    const unsigned gmask = grp == 0 ? 0x00fu : (grp == 1 ? 0x070u : 0x380u);
+    const PoseBox& b = s_pose[grp == 0 ? 0 : (grp == 1 ? 4 : 7)];
+    const unsigned bits = (s_vis[j * 64 + i] >> 16) & gmask; /* the upper half is final since the barrier above */
     const double gx = cell_centre(c, i, c.map_hw), gy = cell_centre(c, j, c.map_hh);
-    if (!line_of_sight(c, d2, b.x, b.y, gx, gy, cnt_samples, cnt_clamped)) return;
-    cnt_visible++;
-    if (k == 0) { /* targetMap.py:104-126; every cell of pose 0's box is queued at most once: no race on the belief */
+    unsigned ns = 0;
+    const bool vis = line_of_sight(c, d2, b.x, b.y, gx, gy, ns, cnt_clamped);
+    if (COUNT) cnt_samples += ns * __popc(bits); /* counters report what the reference does: one ray per (pose, cell) */
+    if (!vis) return;
+    if (COUNT) cnt_visible += __popc(bits);
+    if (bits & 1u) { /* targetMap.py:104-126; pose 0's cell is traced exactly once: no race on the belief */
       float* cellp = belief + j * dim + i;
       double rs = c.ig_remp;
       if (ndet > 0) {
@@ -322,54 +360,44 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
         }
       }
       *cellp = fminf((float)((double)*cellp * rs), FLT_MAX);
-    } else {
-      /* The candidate poses' wedges overlap heavily and a cell's mutual information depends on the cell alone:
-       * record who sees it, evaluate the two fp64 logs once per cell below (not once per pose and cell). */
-      atomicOr(&s_vis[j * 64 + i], 1u << k);
     }
+    /* The candidate poses' wedges overlap heavily and a cell's mutual information depends on the cell alone:
+     * record who sees it, evaluate the two fp64 logs once per cell below (not once per pose and cell). */
+    if (bits & ~1u) atomicOr(&s_vis[j * 64 + i], bits & ~1u);
   };
-
-  /* ---- ONE sweep over the cells of all ten boxes, no CTA barrier inside: a warp draws 32 consecutive box cells from a
-   * shared ticket, tests them against the range / FOV wedge (targetMap.py:73-79), appends the survivors to ITS OWN
-   * queue (ballot-compacted) and traces a full warp's worth of lines of sight as soon as 32 are waiting, so that wedge
-   * tests and traces of different warps overlap and a warp that drew long rays simply draws fewer tickets. ---- */
-  const int total = s_off[X_NPOSE];
-  int k = 0, wqn = 0;
-  for (;;) {
-    int base = 0;
-    if (lane == 0) base = atomicAdd(&s_ticket, 32);
-    base = __shfl_sync(FULL_MASK, base, 0);
-    if (base >= total) break;
-    const int idx = base + lane;
-    bool keep = false;
-    unsigned en = 0u;
-    if (idx < total) {
-      while (idx >= s_off[k + 1]) k++; /* tickets only grow: the pose cursor never rewinds */
-      const int off = idx - s_off[k];
-      const PoseBox& b = s_pose[k];
-      const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
-      const int i = b.x0 + ii, j = b.y0 + jj;
-      const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
-      const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy; /* R = ((c, s), (-s, c)) */
-      cnt_tested++;
-      keep = in_wedge(c, r0, r1);
-      en = ((unsigned)k << 12) | ((unsigned)j << 6) | (unsigned)i;
+  {
+    int wqn = 0;
+    for (int base = wid * 32; base < ncell; base += X_THREADS) { /* warp-uniform trip count */
+      const int idx = base + lane;
+      unsigned w = 0u, cell = 0u;
+      if (idx < ncell) {
+        const int ii = idx / uh, jj = idx - ii * uh;
+        const int i = ux0 + ii, j = uy0 + jj;
+        w = s_vis[j * 64 + i] >> 16;
+        cell = ((unsigned)j << 6) | (unsigned)i;
+      }
+      if (__ballot_sync(FULL_MASK, w != 0u) == 0u) continue;
+#pragma unroll
+      for (int grp = 0; grp < 3; grp++) {
+        const bool has = (w & (grp == 0 ? 0x00fu : (grp == 1 ? 0x070u : 0x380u))) != 0u;
+        const unsigned m = __ballot_sync(FULL_MASK, has);
+        if (m == 0u) continue;
+        if (has) wq[wqn + __popc(m & ((1u << lane) - 1u))] = ((unsigned)grp << 12) | cell;
+        wqn += __popc(m);
+        __syncwarp();
+        if (wqn >= 32) {
+          wqn -= 32;
+          const unsigned e2 = wq[wqn + lane];
+          __syncwarp();
+          trace(e2);
+        }
+      }
     }
-    const unsigned m = __ballot_sync(FULL_MASK, keep);
-    if (keep) wq[wqn + __popc(m & ((1u << lane) - 1u))] = en;
-    wqn += __popc(m);
-    __syncwarp();
-    if (wqn >= 32) {
-      wqn -= 32;
-      const unsigned e2 = wq[wqn + lane];
-      __syncwarp();
-      trace(e2);
-    }
+    if (lane < wqn) trace(wq[lane]);
   }
-  if (lane < wqn) trace(wq[lane]);
   __syncthreads(); /* pose 0's odds update and every visibility bit are in place */
 
-  /* ---- targetMap.py:130-143 over the union box of the candidate poses, on the UPDATED belief.  Seen cells are
+  /* ---- phase 3: targetMap.py:130-143 over the union box, on the UPDATED belief.  Seen cells are
    * compacted into the warp's queue first so that the two fp64 logs per cell run on full warps; the per-pose sums are
    * integer (fixed point, 2^-44): independent of the order of arrival, accumulated with warp reductions on three
    * 22-bit pieces (lane k of every warp carries pose k's sum), no shared-memory atomics. ---- */
@@ -381,7 +409,7 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
       long long v = 0;
       if (valid) {
         const int j = (int)(cell >> 6), i = (int)(cell & 63u);
-        m = s_vis[j * 64 + i];
+        m = s_vis[j * 64 + i] & 0x3feu;
         v = __double2ll_rn(cell_mi(c, (double)belief[j * dim + i], log_rocc, log_remp) * X_MI_SCALE);
       }
       const unsigned lo = (unsigned)(v & 0x3fffffll), mid = (unsigned)((v >> 22) & 0x3fffffll);
@@ -398,15 +426,6 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
                             ((unsigned long long)(long long)c2 << 44));
       }
     };
-    int ux0 = INT_MAX, uy0 = INT_MAX, ux1 = INT_MIN, uy1 = INT_MIN;
-    for (int kk = 1; kk < X_NPOSE; kk++) {
-      const PoseBox& b = s_pose[kk];
-      if (b.w <= 0 || b.h <= 0) continue;
-      ux0 = min(ux0, b.x0); uy0 = min(uy0, b.y0);
-      ux1 = max(ux1, b.x0 + b.w); uy1 = max(uy1, b.y0 + b.h);
-    }
-    const int uw = ux1 > ux0 ? ux1 - ux0 : 0, uh = uy1 > uy0 ? uy1 - uy0 : 0; /* (all boxes empty: nothing to do) */
-    const int ncell = uw * uh;
     int qn = 0;
     for (int base = wid * 32; base < ncell; base += X_THREADS) { /* warp-uniform trip count */
       const int idx = base + lane;
@@ -415,7 +434,7 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
       if (idx < ncell) {
         const int ii = idx / uh, jj = idx - ii * uh;
         const int i = ux0 + ii, j = uy0 + jj;
-        seen = s_vis[j * 64 + i] != 0u;
+        seen = (s_vis[j * 64 + i] & 0x3feu) != 0u;
         cell = ((unsigned)j << 6) | (unsigned)i;
       }
       const unsigned m = __ballot_sync(FULL_MASK, seen);
