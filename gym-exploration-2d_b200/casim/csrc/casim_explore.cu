@@ -32,10 +32,13 @@ namespace {
 
 #define XQ_CAP 4096        /* queue entries: >= ig_dim^2 (ig_dim <= 64), so one pose always fits */
 #ifndef X_THREADS
-#define X_THREADS 192 /* C4 sweep (profiles/r1k_sweep_explore.txt): 64: 170 us, 128: 118, 192: 115, 256: 120, 512: 309; the maximum
-                        * shared-memory carve-out costs 3 us (the EDF samples live in L1) */
+#define X_THREADS 128 /* C4 sweep of the three-phase kernel (profiles/r2e_sweep_explore_threads.txt): 96: 83.9 us, 128: 69.8,
+                        * 192: 83.1 (spills at 64 registers), 256: 90.0.  k_team_update shares the value. */
 #endif
 #define X_NPOSE 10
+#ifndef X_MIN_CTAS
+#define X_MIN_CTAS (1024 / X_THREADS) /* 64 registers per thread */
+#endif
 #define X_MI_SCALE 17592186044416.0 /* 2^44 */
 
 struct ExploreArgs {
@@ -68,13 +71,13 @@ __device__ __forceinline__ double edf_value(const DevCfg& c, const double* __res
    * quotient's unless it lands within 1e-9 of an integer; only then is the division itself evaluated */
   double tx = (px + c.map_hw) * c.inv_cell, ty = (py + c.map_hh) * c.inv_cell;
   double fx = floor(tx), fy = floor(ty);
-  if (!(tx - fx > 1e-9 && fx + 1.0 - tx > 1e-9)) fx = floor((px + c.map_hw) / c.cell);
-  if (!(ty - fy > 1e-9 && fy + 1.0 - ty > 1e-9)) fy = floor((py + c.map_hh) / c.cell);
-  if (!(fx >= 0.0)) { fx = 0.0; clamped++; }
-  if (fx > (double)(CASIM_MAP_DIM - 1)) { fx = (double)(CASIM_MAP_DIM - 1); clamped++; }
-  if (!(fy >= 0.0)) { fy = 0.0; clamped++; }
-  if (fy > (double)(CASIM_MAP_DIM - 1)) { fy = (double)(CASIM_MAP_DIM - 1); clamped++; }
-  int xi = (int)fx, yi = (int)fy;
+  const double rx = tx - fx, ry = ty - fy; /* exact (tx and its floor are within a factor of two, or the result is < 1) */
+  if (!(rx > 1e-9 && rx < 1.0 - 1e-9)) fx = floor((px + c.map_hw) / c.cell);
+  if (!(ry > 1e-9 && ry < 1.0 - 1e-9)) fy = floor((py + c.map_hh) / c.cell);
+  /* double -> int saturates and maps NaN to 0: the clamp of edfMap.py:16-19 in two integer min/max per axis */
+  const int xr = __double2int_rz(fx), yr = __double2int_rz(fy);
+  const int xi = min(max(xr, 0), CASIM_MAP_DIM - 1), yi = min(max(yr, 0), CASIM_MAP_DIM - 1);
+  clamped += (unsigned)(xi != xr) + (unsigned)(yi != yr);
   return __ldg(d2 + yi * CASIM_MAP_DIM + xi);
 }
 
@@ -164,7 +167,7 @@ __device__ __forceinline__ void pose_box(const DevCfg& c, double x, double y, do
 /* One CTA per explorer.  COUNT: instrumentation counters (cells tested / EDF samples / visible cells / clamped indices)
  * compiled in only when the caller passes a counters buffer. */
 template <bool COUNT>
-__global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
+__global__ void __launch_bounds__(X_THREADS, X_MIN_CTAS) k_explore(const ExploreArgs p) {
   const DevCfg& c = p.c;
   const int g = blockIdx.x;
   const int e = g / p.A, ai = g - e * p.A;
@@ -189,6 +192,7 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
   __shared__ PoseBox s_pose[X_NPOSE];
   __shared__ double s_det[CASIM_MAX_AGENTS][2];
   __shared__ double s_log[2];                        /* log(ig_rocc), log(ig_remp) */
+  __shared__ double s_cc[2][64];                     /* getPoseFromCell per axis (targetMap.py:33-36): x of column i, y of row j */
   __shared__ int s_ndet;
   __shared__ int s_off[X_NPOSE + 1];                 /* prefix of the box sizes: cells of pose k are [s_off[k], s_off[k+1]); pose 2: none */
   __shared__ unsigned int s_wq[X_THREADS / 32][64];  /* per-warp queue: wedge survivors (pose << 12) | (j << 6) | i, then seen cells */
@@ -212,6 +216,7 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
     px = p0.x; py = p0.y; ph = p0.z; prad = p2.z;
   }
   for (int k = tid; k < 64 * 64; k += X_THREADS) s_vis[k] = 0u;
+  for (int k = tid; k < 128; k += X_THREADS) s_cc[k >> 6][k & 63] = cell_centre(c, k & 63, (k >> 6) ? c.map_hh : c.map_hw);
   if (COUNT && tid < 4) s_cnt[tid] = 0u;
   if (restart)
     for (int k = tid; k < dim * dim; k += X_THREADS) belief[k] = (float)c.ig_prior;
@@ -289,11 +294,9 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
     }
     if (k < X_NPOSE) s_off[k + 1] = incl;
     if (k == 0) s_off[0] = 0;
-  } else if (tid == 64) {
-    s_log[0] = log(c.ig_rocc);
-  } else if (tid == 65) {
-    s_log[1] = log(c.ig_remp);
   }
+  if (tid == X_THREADS - 1) s_log[0] = log(c.ig_rocc);
+  if (tid == X_THREADS - 2) s_log[1] = log(c.ig_remp);
   __syncthreads();
 
   const int ndet = s_ndet;
@@ -312,7 +315,7 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
       const PoseBox& b = s_pose[k];
       const int ii = (off * b.inv_h) >> 18, jj = off - ii * b.h;
       const int i = b.x0 + ii, j = b.y0 + jj;
-      const double dx = cell_centre(c, i, c.map_hw) - b.x, dy = cell_centre(c, j, c.map_hh) - b.y;
+      const double dx = s_cc[0][i] - b.x, dy = s_cc[1][j] - b.y;
       const double r0 = b.cs * dx + b.sn * dy, r1 = -b.sn * dx + b.cs * dy; /* R = ((c, s), (-s, c)) */
       cnt_tested += (k == 0 && twin) ? 2u : 1u;
       if (in_wedge(c, r0, r1)) atomicOr(&s_vis[j * 64 + i], (1u << (16 + k)) | (k == 0 ? twin : 0u));
@@ -339,7 +342,7 @@ __global__ void __launch_bounds__(X_THREADS, 5) k_explore(const ExploreArgs p) {
     const unsigned gmask = grp == 0 ? 0x00fu : (grp == 1 ? 0x070u : 0x380u);
     const PoseBox& b = s_pose[grp == 0 ? 0 : (grp == 1 ? 4 : 7)];
     const unsigned bits = (s_vis[j * 64 + i] >> 16) & gmask; /* the upper half is final since the barrier above */
-    const double gx = cell_centre(c, i, c.map_hw), gy = cell_centre(c, j, c.map_hh);
+    const double gx = s_cc[0][i], gy = s_cc[1][j];
     unsigned ns = 0;
     const bool vis = line_of_sight(c, d2, b.x, b.y, gx, gy, ns, cnt_clamped);
     if (COUNT) cnt_samples += ns * __popc(bits); /* counters report what the reference does: one ray per (pose, cell) */
