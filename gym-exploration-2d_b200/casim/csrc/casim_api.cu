@@ -616,6 +616,38 @@ int casim_explore_rollouts(casim_handle* h, const float* state, const float* bel
   return 0;
 }
 
+static int mcts_check(const casim_handle* h, const casim_mcts_trees* t) {
+  REQUIRE(h && t, "null argument");
+  REQUIRE(t->T >= 1 && t->M >= 1 && t->H >= 1 && t->H <= CASIM_ROLLOUT_MAX_H && t->nsims >= 0, "mcts: bad tree dimensions");
+  REQUIRE(t->slot && t->n_nodes && t->node && t->parent && t->child && t->nchild && t->stage && t->has_rollout && t->mu &&
+              t->N && t->best_reward && t->path && t->best_seq && t->overflow, "mcts: null tree array");
+  REQUIRE(t->n_comms == 0 || (t->comm_q && t->comm_masks && t->comm_valid && t->comm_n >= 1), "mcts: null communication array");
+  return 0;
+}
+
+int casim_mcts_select(casim_handle* h, const casim_mcts_trees* trees, const uint8_t* draws, uint64_t draw_seed,
+                      int iteration, const double* comm_u, uint8_t* actions, uint32_t* exclude, int root_only, void* stream) {
+  int rc = mcts_check(h, trees);
+  if (rc) return rc;
+  REQUIRE(actions, "mcts: null action buffer");
+  REQUIRE(iteration >= 0, "mcts: negative iteration");
+  REQUIRE(!exclude || trees->n_comms == 0 || comm_u, "mcts: communication needs comm_u");
+  CK(casim_launch_mcts_select(h, trees, draws, (unsigned long long)draw_seed, iteration, comm_u, actions, exclude, root_only,
+                              (cudaStream_t)stream));
+  return 0;
+}
+
+int casim_mcts_update(casim_handle* h, const casim_mcts_trees* trees, const uint8_t* actions, const float* rewards,
+                      const int32_t* n_feasible, double* avg_out, int expand_only, void* stream) {
+  int rc = mcts_check(h, trees);
+  if (rc) return rc;
+  REQUIRE(actions && rewards && n_feasible, "mcts: null rollout result");
+  REQUIRE(expand_only || trees->nsims >= 1, "mcts: statistics need at least one simulation");
+  CK(casim_launch_mcts_update(h, trees, actions, rewards, n_feasible, avg_out, expand_only, trees->overflow,
+                              (cudaStream_t)stream));
+  return 0;
+}
+
 int casim_ga3c_set_weights(casim_handle* h, const float* weights_host, int n_params, void* stream) {
   REQUIRE(h && weights_host, "null argument");
   REQUIRE(n_params == CASIM_GA3C_NUM_PARAMS, "GA3C-CADRL parameter blob must hold 170764 floats");

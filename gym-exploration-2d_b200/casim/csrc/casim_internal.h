@@ -160,6 +160,12 @@ cudaError_t casim_launch_flatten(casim_handle* h, const float* state, const casi
 int casim_flat_row_size_impl(const casim_handle* h, const int32_t* keys, int n_keys);
 cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_params, cudaStream_t s);
 
+cudaError_t casim_launch_mcts_select(casim_handle* h, const casim_mcts_trees* t, const uint8_t* draws,
+                                     unsigned long long draw_seed, int iteration, const double* comm_u, uint8_t* actions,
+                                     uint32_t* exclude, int root_only, cudaStream_t s);
+cudaError_t casim_launch_mcts_update(casim_handle* h, const casim_mcts_trees* t, const uint8_t* actions, const float* rewards,
+                                     const int32_t* n_feasible, double* avg_out, int expand_only, int* overflow,
+                                     cudaStream_t s);
 void casim_set_error(const char* fmt, ...);
 
 /* Tuning knobs (launch shapes, zero-copy, PDL, trace dumps) are read from the environment ONLY in a -DCASIM_TUNING

@@ -35,6 +35,16 @@ class RvoParams(ctypes.Structure):
                 ("max_delta_heading", c_double), ("max_neighbors", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
 
 
+class MctsTrees(ctypes.Structure):
+    """``struct casim_mcts_trees``: dimensions, constants and DEVICE pointers of T Dec-MCTS trees (include/casim.h)."""
+    _fields_ = [("T", ctypes.c_int32), ("M", ctypes.c_int32), ("H", ctypes.c_int32), ("nsims", ctypes.c_int32),
+                ("n_comms", ctypes.c_int32), ("comm_n", ctypes.c_int32), ("c_p", c_double), ("gamma", c_double),
+                ("slot", c_void_p), ("n_nodes", c_void_p), ("node", c_void_p), ("parent", c_void_p), ("child", c_void_p),
+                ("nchild", c_void_p), ("stage", c_void_p), ("has_rollout", c_void_p), ("mu", c_void_p), ("N", c_void_p),
+                ("best_reward", c_void_p), ("path", c_void_p), ("best_seq", c_void_p), ("comm_q", c_void_p),
+                ("comm_masks", c_void_p), ("comm_valid", c_void_p), ("overflow", c_void_p)]
+
+
 # every symbol include/casim.h declares: name -> (restype, argtypes)
 _PCFG = ctypes.POINTER(SimConfig)
 _POBS = ctypes.POINTER(Obs)
@@ -69,6 +79,9 @@ SYMBOLS = {
     "casim_explore_team_update": (c_int, [c_void_p] * 11),
     "casim_explore_rollouts": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "casim_mcts_select": (c_int, [c_void_p, ctypes.POINTER(MctsTrees), c_void_p, ctypes.c_uint64, c_int, c_void_p, c_void_p,
+                          c_void_p, c_int, c_void_p]),
+    "casim_mcts_update": (c_int, [c_void_p, ctypes.POINTER(MctsTrees), c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "casim_ga3c_set_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "casim_ga3c_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "casim_rvo_default_params": (None, [ctypes.POINTER(RvoParams)]),

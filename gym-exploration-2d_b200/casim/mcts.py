@@ -25,6 +25,25 @@ def action_value(idx):
     return np.stack([np.take(VEL_LIST, idx // 3), np.take(DPHI_LIST, idx % 3)], -1)
 
 
+def draw_seed(seed):
+    """any numpy seed (int / tuple) -> the 64-bit seed of the counter-based draws"""
+    return int(np.random.SeedSequence(seed).generate_state(1, np.uint64)[0])
+
+
+def hash_draws(seed64, iteration, T, nsims, H):
+    """The draws casim_mcts_select makes itself when it is given none (csrc/casim_mcts.cu:mcts_draw): splitmix64 of
+    (seed, global draw index), top 32 bits scaled to 0..8.  -> uint8 [T,nsims,H]"""
+    with np.errstate(over="ignore"):
+        idx = np.uint64(iteration) * np.uint64(T * nsims * H) + np.arange(T * nsims * H, dtype=np.uint64)
+        x = np.uint64(seed64) + np.uint64(0x9E3779B97F4A7C15) * (idx + np.uint64(1))
+        x ^= x >> np.uint64(30)
+        x *= np.uint64(0xBF58476D1CE4E5B9)
+        x ^= x >> np.uint64(27)
+        x *= np.uint64(0x94D049BB133111EB)
+        x ^= x >> np.uint64(31)
+        return (((x >> np.uint64(32)) * np.uint64(9)) >> np.uint64(32)).astype(np.uint8).reshape(T, nsims, H)
+
+
 class ActionDistribution:
     """DecMCTS.py:21-59 for every tree: ``seqs`` [T,n,H] uint8 best rollouts of the top-n nodes (END padded), ``q`` [T,n]
     normalised weights (0 = slot unused), ``masks`` [T,n,128] int32 observed-cell masks of those rollouts."""
@@ -45,9 +64,11 @@ class BatchedDecMCTS:
     rollout evaluator (``sim_evaluator`` below wraps casim_explore_rollouts).  T trees, all rooted at their agent's
     current pose."""
 
-    def __init__(self, n_trees, evaluate, horizon=10, c_p=1.0, comm_n=5, seed=0, reference_order=False):
+    def __init__(self, n_trees, evaluate, horizon=10, c_p=1.0, comm_n=5, seed=0, reference_order=False, hashed_draws=False):
         self.T, self.H, self.c_p, self.comm_n = int(n_trees), int(horizon), float(c_p), int(comm_n)
         self.evaluate = evaluate
+        self.hashed_draws = draw_seed(seed) if hashed_draws else None   # draw like DeviceDecMCTS(device_draws=True)
+        self.iteration = 0
         self.reference_order = bool(reference_order)       # draw from np.random exactly like the reference (tests)
         self.rng = np.random.default_rng(seed)
         self.comms = []                                    # list of (ActionDistribution, valid [T] bool)
@@ -96,8 +117,11 @@ class BatchedDecMCTS:
                     for i in range(nsims):
                         for d in range(stage[t], H):
                             draws[t, i, d] = np.random.choice(N_ACTIONS)
+            elif self.hashed_draws is not None:
+                draws = hash_draws(self.hashed_draws, self.iteration, T, nsims, H)
+                self.iteration += 1
             else:
-                draws = self.rng.integers(0, N_ACTIONS, (T, nsims, H)).astype(np.uint8)
+                draws = self.rng.integers(0, N_ACTIONS, (T, nsims, H), dtype=np.uint8)
             tail = np.arange(H)[None, None, :] >= stage[:, None, None]
             seqs[:, N_ACTIONS:] = np.where(tail, draws, seqs[:, N_ACTIONS:])
         rewards, n_feasible = self.evaluate(seqs, exclude)
@@ -219,18 +243,25 @@ class BatchedDecMCTS:
         returning observed-cell masks for [T,n,H] sequences (needed only when the distribution is communicated)."""
         T, n = self.T, self.comm_n
         r = self._rows()
-        mu = np.where(np.arange(self.M)[None, :] < self.n_nodes[:, None], self.mu, -np.inf)
-        mu[:, 0] = -np.inf
-        top = np.argsort(-mu, axis=1, kind="stable")[:, :n]                   # [T,n]
-        ok = np.isfinite(mu[r[:, None], top]) & self.has_rollout[r[:, None], top]
-        seqs = np.where(ok[:, :, None], self.best_seq[r[:, None], top], END).astype(np.uint8)
-        q = np.where(ok, self.mu[r[:, None], top] ** 2, 0.0)
+        top, mu_top, has_top, seq_top = self._top_nodes(n)
+        ok = np.isfinite(mu_top) & has_top
+        seqs = np.where(ok[:, :, None], seq_top, END).astype(np.uint8)
+        q = np.where(ok, mu_top ** 2, 0.0)
         # compact the kept entries to the front (the reference builds X, q from the kept nodes only)
         order = np.argsort(~ok, axis=1, kind="stable")
         seqs, q, top = seqs[r[:, None], order], q[r[:, None], order], top[r[:, None], order]
         d = ActionDistribution(seqs, q, with_masks(seqs) if with_masks is not None else None)
         d.nodes = np.where(np.take_along_axis(ok, order, 1), top, -1)
         return d
+
+    def _top_nodes(self, n):
+        """-> (node ids [T,n], their mu (-inf = no such node), has_rollout, best_seq [T,n,H]): highest mu first, ties by
+        lowest node id, the root excluded."""
+        r = self._rows()
+        mu = np.where(np.arange(self.M)[None, :] < self.n_nodes[:, None], self.mu, -np.inf)
+        mu[:, 0] = -np.inf
+        top = np.argsort(-mu, axis=1, kind="stable")[:, :n]                   # [T,n]
+        return top, mu[r[:, None], top], self.has_rollout[r[:, None], top], self.best_seq[r[:, None], top]
 
     def best_action_index(self):
         """ig_mcts.find_next_action's result (ig_mcts.py:106-109): the first action of the best rollout of the
@@ -248,6 +279,193 @@ class BatchedDecMCTS:
         valid = np.ones(self.T, bool) if valid is None else np.asarray(valid, bool)
         draw = np.zeros(self.T, bool) if draw_only is None else np.asarray(draw_only, bool)
         self.comms.append((dist, valid & (dist.n > 0), draw & (dist.n > 0)))
+
+
+class DeviceDecMCTS(BatchedDecMCTS):
+    """The same planner with the node arrays resident on the GPU: one grow iteration = casim_mcts_select ->
+    casim_explore_rollouts -> casim_mcts_update on the current stream, no host round trip (csrc/casim_mcts.cu).  The random
+    draws (simulation actions, one uniform per communicating robot) are generated on the host in the host planner's
+    order and uploaded once per ``grow_n`` call, so a tree grown here equals the tree ``BatchedDecMCTS`` grows from the
+    same seed, node for node.  ``select`` [E,A] bool marks the agents that plan (one tree each, (env, agent) order)."""
+
+    ARRAYS = ("parent", "stage", "mu", "N", "best_reward", "child", "nchild", "path", "has_rollout", "best_seq")
+
+    def __init__(self, sim, select, horizon=10, c_p=1.0, comm_n=5, seed=0, xdt=1, nsims=10, n_grows=100, device_draws=True):
+        import torch
+        from . import lib as _lib
+        self._torch, self._lib = torch, _lib
+        self.sim, self.xdt, self.nsims = sim, int(xdt), int(nsims)
+        te, ta = np.nonzero(np.asarray(select, bool))
+        self.te, self.ta = te, ta
+        self.T, self.H, self.c_p, self.comm_n = len(te), int(horizon), float(c_p), int(comm_n)
+        if self.T == 0:
+            raise _lib.CasimError("DeviceDecMCTS: no agent selected")
+        if getattr(sim, "belief", None) is None:
+            raise _lib.CasimError("DeviceDecMCTS needs sim.enable_exploration() first")
+        self.reference_order = False
+        self.rng = np.random.default_rng(seed)
+        # simulation actions: drawn inside casim_mcts_select (counter-based hash, = hash_draws) or, for a tree that must
+        # equal the host planner's default stream, on the host with self.rng and uploaded
+        self.device_draws = bool(device_draws)
+        self.seed64, self.iteration = draw_seed(seed), 0
+        self.comms = []
+        self.launches = 0
+        self.K = N_ACTIONS + self.nsims
+        dev, T, H, K = sim.device, self.T, self.H, self.K
+        self.M = 0
+        self.d = dict(slot=torch.as_tensor(te * sim.A + ta, dtype=torch.int32, device=dev),
+                      n_nodes=torch.ones(T, dtype=torch.int32, device=dev),
+                      node=torch.zeros(T, dtype=torch.int32, device=dev),
+                      overflow=torch.zeros(1, dtype=torch.int32, device=dev))
+        self._alloc(1 + N_ACTIONS * (int(n_grows) + 1))
+        self.actions = torch.full((sim.E, sim.A, K, H), END, dtype=torch.uint8, device=dev)
+        self.rewards = torch.zeros((sim.E, sim.A, K), dtype=torch.float32, device=dev)
+        self.n_feasible = torch.zeros((sim.E, sim.A, K), dtype=torch.int32, device=dev)
+        self.exclude = None
+        self.avg = torch.zeros(T, dtype=torch.float64, device=dev)
+        self._comm_dev = None
+        self._host_valid = False
+        # root (Tree.__init__, :120-133): _expansion(root) from the feasibility of its 9 one-step extensions
+        self._iteration(None, None, 0.0, root_only=True)
+
+    # ---------------------------------------------------------------- storage
+    def _alloc(self, M):
+        torch, dev, T, H = self._torch, self.sim.device, self.T, self.H
+        spec = dict(parent=((T, M), torch.int32, -1), child=((T, M, N_ACTIONS), torch.int32, -1),
+                    nchild=((T, M), torch.uint8, 0), stage=((T, M), torch.uint8, 0), has_rollout=((T, M), torch.uint8, 0),
+                    mu=((T, M), torch.float64, 0), N=((T, M), torch.float64, 0), best_reward=((T, M), torch.float64, 0),
+                    path=((T, M, H), torch.uint8, END), best_seq=((T, M, H), torch.uint8, END))
+        for k, (shape, dt, fill) in spec.items():
+            new = torch.full(shape, fill, dtype=dt, device=dev)
+            if self.M:
+                new[:, :self.M] = self.d[k]
+            self.d[k] = new
+        self.M = M
+
+    def reserve(self, n_grows):
+        self._torch.cuda.current_stream().synchronize()
+        need = int(self.d["n_nodes"].max().item()) + N_ACTIONS * int(n_grows)
+        if need > self.M:
+            self._alloc(need)
+
+    def _struct(self, gamma):
+        L, d = self._lib, self.d
+        s = L.MctsTrees()
+        s.T, s.M, s.H, s.nsims, s.comm_n = self.T, self.M, self.H, self.nsims, self.comm_n
+        s.c_p, s.gamma = self.c_p, float(gamma)
+        for k in ("slot", "n_nodes", "node", "overflow") + self.ARRAYS:
+            setattr(s, k, d[k].data_ptr())
+        if self._comm_dev is not None:
+            q, masks, valid = self._comm_dev
+            s.n_comms, s.comm_q, s.comm_masks, s.comm_valid = q.shape[0], q.data_ptr(), masks.data_ptr(), valid.data_ptr()
+        return s
+
+    def _upload_comms(self):
+        """receive_comms entries -> [C,T,n] weights, [C,T,n,128] masks, [C,T] valid on the device"""
+        torch, dev = self._torch, self.sim.device
+        if not self.comms:
+            self._comm_dev, self.exclude = None, None
+            return
+        for dist, _, _ in self.comms:
+            if dist.q.shape != (self.T, self.comm_n) or dist.masks is None:
+                raise self._lib.CasimError("DeviceDecMCTS: a received distribution needs [T, comm_n] weights and masks")
+        q = np.stack([np.ascontiguousarray(dist.q, np.float64) for dist, _, _ in self.comms])
+        masks = np.stack([np.ascontiguousarray(dist.masks, np.int32) for dist, _, _ in self.comms])
+        valid = np.stack([np.asarray(v, np.uint8) for _, v, _ in self.comms])
+        self._comm_dev = (torch.from_numpy(q).to(dev), torch.from_numpy(masks).to(dev), torch.from_numpy(valid).to(dev))
+        if self.exclude is None:
+            self.exclude = torch.zeros((self.sim.E, self.sim.A, 128), dtype=torch.int32, device=dev)
+
+    # ---------------------------------------------------------------- one iteration, all on the device
+    def _iteration(self, draws, comm_u, gamma, root_only=False):
+        L, sim = self._lib, self.sim
+        stream = ctypes_stream(self._torch)
+        s = self._struct(gamma)
+        ex = None if (root_only or self.exclude is None) else self.exclude
+        L.check(sim.lib.casim_mcts_select(sim.handle, ctypes_byref(s), L.ptr(draws), self.seed64, self.iteration,
+                                          L.ptr(comm_u), L.ptr(self.actions), L.ptr(ex), int(root_only), stream),
+                "casim_mcts_select")
+        if not root_only and draws is None:
+            self.iteration += 1
+        L.check(sim.lib.casim_explore_rollouts(sim.handle, L.ptr(sim.state), L.ptr(sim.belief), L.ptr(self.actions), self.K,
+                                               self.H, self.xdt, L.ptr(ex), 0, L.ptr(self.rewards), None, None,
+                                               L.ptr(self.n_feasible), stream), "casim_explore_rollouts")
+        L.check(sim.lib.casim_mcts_update(sim.handle, ctypes_byref(s), L.ptr(self.actions), L.ptr(self.rewards),
+                                          L.ptr(self.n_feasible), L.ptr(self.avg), int(root_only), stream), "casim_mcts_update")
+        self.launches += 1
+        self._host_valid = False
+
+    def grow_n(self, n, nsims=None, gamma=0.9):
+        """``n`` iterations of Tree.grow (:273-360) for every tree, without touching the host in between."""
+        torch, dev, T = self._torch, self.sim.device, self.T
+        if nsims is not None and int(nsims) != self.nsims:
+            raise self._lib.CasimError("DeviceDecMCTS was built for nsims = %d" % self.nsims)
+        self._upload_comms()
+        C = len(self.comms)
+        us = np.zeros((n, max(C, 1), T))
+        draws = None if self.device_draws else np.empty((n, T, self.nsims, self.H), np.uint8)
+        for it in range(n):                              # the host planner's order: _system_exclude, then _rollouts
+            for c in range(C):
+                us[it, c] = self.rng.random(T)
+            if draws is not None:
+                draws[it] = self.rng.integers(0, N_ACTIONS, (T, self.nsims, self.H), dtype=np.uint8)
+        d_us = torch.from_numpy(us).to(dev) if C else None
+        d_draws = None if draws is None else torch.from_numpy(draws).to(dev)
+        for it in range(n):
+            self._iteration(None if d_draws is None else d_draws[it], d_us[it] if C else None, gamma)
+        self._keep = (d_us, d_draws)                     # alive until the stream has consumed them
+
+    def grow(self, nsims=10, gamma=0.9):
+        self.grow_n(1, nsims, gamma)
+        self._torch.cuda.current_stream().synchronize()
+        return self.avg.cpu().numpy()
+
+    # ---------------------------------------------------------------- results
+    def sync_host(self):
+        """Node arrays -> the numpy attributes of the host planner (distribution / best_action_index read them)."""
+        if self._host_valid:
+            return
+        self._torch.cuda.current_stream().synchronize()
+        if int(self.d["overflow"].item()):
+            raise self._lib.CasimError("DeviceDecMCTS: node arrays full (M = %d); reserve() more iterations" % self.M)
+        self.n_nodes = self.d["n_nodes"].cpu().numpy().astype(np.int64)
+        used = int(self.n_nodes.max())
+        for k in self.ARRAYS:
+            a = self.d[k][:, :used].cpu().numpy()
+            if k in ("parent", "child", "stage", "nchild"):
+                a = a.astype(np.int64)
+            elif k == "has_rollout":
+                a = a.astype(bool)
+            setattr(self, k, a)
+        self.last_node = self.d["node"].cpu().numpy().astype(np.int64)
+        self._host_valid = True
+
+    def _top_nodes(self, n):
+        """The same ranking with a stable sort on the device; only the n winners per tree come back."""
+        torch, d = self._torch, self.d
+        used = int(d["n_nodes"].max().item())                                 # (synchronises the stream)
+        if int(d["overflow"].item()):
+            raise self._lib.CasimError("DeviceDecMCTS: node arrays full (M = %d); reserve() more iterations" % self.M)
+        ids = torch.arange(used, device=self.sim.device)[None, :]
+        mu = torch.where(ids < d["n_nodes"][:, None], d["mu"][:, :used], float("-inf"))
+        mu[:, 0] = float("-inf")
+        top = torch.argsort(-mu, dim=1, stable=True)[:, :n]
+        if top.shape[1] < n:                                                  # fewer nodes than entries: pad with the root
+            top = torch.cat([top, torch.zeros((self.T, n - top.shape[1]), dtype=top.dtype, device=top.device)], 1)
+        mu_top = torch.gather(mu, 1, top)
+        has = torch.gather(d["has_rollout"][:, :used], 1, top) != 0
+        seq = torch.gather(d["best_seq"][:, :used], 1, top[:, :, None].expand(-1, -1, self.H))
+        return top.cpu().numpy(), mu_top.cpu().numpy(), has.cpu().numpy(), seq.cpu().numpy()
+
+
+def ctypes_stream(torch):
+    import ctypes
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ctypes_byref(s):
+    import ctypes
+    return ctypes.byref(s)
 
 
 def sim_evaluator(sim, xdt=1, select=None):
@@ -331,10 +549,15 @@ class TeamPlanner:
                     continue
                 T, ev, masks_of, (te, ta) = sim_evaluator(sim, p.xDT, select=sel)
                 if cycle == 0:
-                    tree = BatchedDecMCTS(T, ev, horizon=p.mcts_horizon, c_p=p.mcts_cp, comm_n=5,
-                                          seed=(p.seed, self.steps, r),
-                                          reference_order=getattr(p, "reference_order", False))
-                    tree.reserve(p.Ntree * p.Ncycles)
+                    ref_order = getattr(p, "reference_order", False)
+                    if getattr(p, "device_trees", True) and not ref_order:
+                        tree = DeviceDecMCTS(sim, sel, horizon=p.mcts_horizon, c_p=p.mcts_cp, comm_n=5,
+                                             seed=(p.seed, self.steps, r), xdt=p.xDT, nsims=p.Nsims,
+                                             n_grows=p.Ntree * p.Ncycles)
+                    else:
+                        tree = BatchedDecMCTS(T, ev, horizon=p.mcts_horizon, c_p=p.mcts_cp, comm_n=5,
+                                              seed=(p.seed, self.steps, r), reference_order=ref_order)
+                        tree.reserve(p.Ntree * p.Ncycles)
                     self.trees[r] = (tree, te)
                 else:
                     tree, te_old = self.trees[r]
@@ -348,8 +571,11 @@ class TeamPlanner:
                         tree.receive_comms(dist, valid=np.zeros(T, bool), draw_only=listed)
                     else:
                         tree.receive_comms(dist, valid=listed)
-                for _ in range(p.Ntree):
-                    tree.grow(nsims=p.Nsims, gamma=p.mcts_gamma)
+                if isinstance(tree, DeviceDecMCTS):
+                    tree.grow_n(p.Ntree, nsims=p.Nsims, gamma=p.mcts_gamma)
+                else:
+                    for _ in range(p.Ntree):
+                        tree.grow(nsims=p.Nsims, gamma=p.mcts_gamma)
                 d = tree.distribution(with_masks=masks_of)
                 self.best[r]["seqs"][te], self.best[r]["q"][te], self.best[r]["masks"][te] = d.seqs, d.q, d.masks
                 a = tree.best_action_index()

@@ -369,6 +369,49 @@ int casim_explore_rollouts(casim_handle* h, const float* state, const float* bel
                            int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
                            float* end_pose, uint32_t* obsvd, int32_t* n_feasible, void* stream);
 
+/* Dec-MCTS tree bookkeeping on the device.  Replaces, for T trees grown in lock-step,
+ * the parts of pydecmcts `Tree.grow` (policies/pydecmcts/DecMCTS.py:273-360) around the simulations:
+ * casim_mcts_select = _get_system_state (:182-194) + _select / _UCT (:140-153, :14-18) + the action sequences of the
+ * selected node's 9 one-step extensions and `nsims` random completions (_expansion :201-231, _simulate :233-269), written
+ * into the action buffer of casim_explore_rollouts (K = 9 + nsims rollouts per tree, at the tree's agent slot);
+ * casim_mcts_update = _expansion (a child per feasible action, in action order) + the node's statistics (:323-339) +
+ * the discounted back-propagation (:341-357), from casim_explore_rollouts' rewards / n_feasible.
+ * All arrays are DEVICE memory owned by the caller; node 0 is the root (parent -1, stage 0, everything else zero, path
+ * and best_seq filled with 255); nodes are numbered in creation order like the reference's graph.
+ *   draws  [T,nsims,H] uint8: the random action (0..8) of every simulation step (ig_mcts.py:257; only d >= stage is used);
+ *          NULL = drawn in the kernel: splitmix64(draw_seed, ((iteration * T + tree) * nsims + sim) * H + d) scaled to 0..8;
+ *   comm_u [n_comms,T] double in [0,1): one draw per communicating robot (np.random.choice(n, p=q), DecMCTS.py:190);
+ *   actions [E,A,K,H] uint8 / exclude [E,A,128] (or NULL: no communication): only the trees' slots are written;
+ *   root_only = 1: no descent, no simulations (Tree.__init__'s _expansion of the root, :133); expand_only likewise.
+ * A tree whose node array is full sets *overflow = 1 and is left unchanged. */
+#define CASIM_MCTS_ACTIONS 9
+typedef struct casim_mcts_trees {
+  int32_t T, M, H, nsims;      /* trees, node capacity per tree, horizon (<= CASIM_ROLLOUT_MAX_H), simulations per grow */
+  int32_t n_comms, comm_n;     /* communicating robots, entries per action distribution (DecMCTS.py:21-59) */
+  double c_p, gamma;           /* exploration constant (:14-18), back-propagation discount (:341) */
+  const int32_t* slot;         /* [T] agent slot e * A + a of each tree */
+  int32_t* n_nodes;            /* [T] */
+  int32_t* node;               /* [T] the node casim_mcts_select chose, consumed by casim_mcts_update */
+  int32_t* parent;             /* [T,M] */
+  int32_t* child;              /* [T,M,9] children in creation order, -1 = none */
+  uint8_t* nchild;             /* [T,M] */
+  uint8_t* stage;              /* [T,M] depth = length of the node's path */
+  uint8_t* has_rollout;        /* [T,M] best_seq is set */
+  double* mu;                  /* [T,M] */
+  double* N;                   /* [T,M] discounted visit count */
+  double* best_reward;         /* [T,M] */
+  uint8_t* path;               /* [T,M,H] action sequence from the root, 255 padded */
+  uint8_t* best_seq;           /* [T,M,H] best rollout through the node (requested actions, full length) */
+  const double* comm_q;        /* [n_comms,T,comm_n] normalised weights */
+  const uint32_t* comm_masks;  /* [n_comms,T,comm_n,128] observed-cell masks of the distributions' rollouts */
+  const uint8_t* comm_valid;   /* [n_comms,T] */
+  int32_t* overflow;           /* [1] */
+} casim_mcts_trees;
+int casim_mcts_select(casim_handle* h, const casim_mcts_trees* trees, const uint8_t* draws, uint64_t draw_seed,
+                      int iteration, const double* comm_u, uint8_t* actions, uint32_t* exclude, int root_only, void* stream);
+int casim_mcts_update(casim_handle* h, const casim_mcts_trees* trees, const uint8_t* actions, const float* rewards,
+                      const int32_t* n_feasible, double* avg_out, int expand_only, void* stream);
+
 /* Replaces GA3CCADRLPolicy.find_next_action for every GA3C agent (policies/GA3CCADRLPolicy.py:34-106,
  * GA3C_CADRL/network.py:45-98).  weights: fp32 parameter blob, order kernel/bias of lstm [71,256],[256];
  * layer1 [68,256],[256]; layer2 [256,256],[256]; fullyconnected1 [256,256],[256]; logits_p [256,11],[11]

@@ -107,6 +107,76 @@ def test_mcts_c4_planning_step():
     sim.close()
 
 
+def test_device_trees_equal_host_trees_node_for_node():
+    """DeviceDecMCTS (casim_mcts_select / casim_mcts_update: selection, expansion, statistics, back-propagation and the
+    sampling of the other robots' claimed cells on the GPU) against BatchedDecMCTS (the host planner the golden test
+    pins to the reference's trees) from the same seed: every node array identical, with and without communication,
+    discount < 1, a tree that reaches the horizon, and a re-allocation of the node arrays on the way."""
+    from casim import scenarios as S
+    from casim.mcts import ActionDistribution, BatchedDecMCTS, DeviceDecMCTS, sim_evaluator
+    E = 96
+    init, types, n, rects = S.exploration(E, seed=11)
+    cfg = _cfg()
+    sim = _sim(E, 4, cfg)
+    sim.set_obstacles(rects)
+    sim.reset(init, types, n)
+    for _ in range(3):
+        sim.explore_step()
+        sim.step(policy_actions=sim.buf["policy_actions"])
+    T, ev, masks_of, (te, ta) = sim_evaluator(sim)
+    sel = np.zeros((E, 4), bool)
+    sel[te, ta] = True
+    partner = np.arange(T) ^ 1
+
+    def same(dev, host, what):
+        dev.sync_host()
+        assert np.array_equal(dev.n_nodes, host.n_nodes), what
+        nmax = int(host.n_nodes.max())
+        live = np.arange(nmax)[None, :] < host.n_nodes[:, None]
+        for k in ("parent", "stage", "nchild", "has_rollout", "mu", "N", "best_reward"):
+            assert np.array_equal(getattr(dev, k)[:, :nmax][live], getattr(host, k)[:, :nmax][live]), (what, k)
+        for k in ("child", "path", "best_seq"):
+            assert np.array_equal(getattr(dev, k)[:, :nmax][live], getattr(host, k)[:, :nmax][live]), (what, k)
+        assert np.array_equal(dev.last_node, host.last_node), what
+
+    # horizon 2: leaves at stage == H are re-simulated; hashed: the simulation actions drawn inside casim_mcts_select
+    for Hn, gamma, nsims, hashed in ((10, 0.9, 10, False), (2, 1.0, 4, False), (10, 0.95, 10, True)):
+        host = BatchedDecMCTS(T, ev, horizon=Hn, c_p=1.0, seed=7, hashed_draws=hashed)
+        dev = DeviceDecMCTS(sim, sel, horizon=Hn, c_p=1.0, seed=7, nsims=nsims, n_grows=4,    # too small on purpose
+                            device_draws=hashed)
+        for _ in range(12):
+            host.grow(nsims=nsims, gamma=gamma)
+        dev.reserve(12)
+        dev.grow_n(12, nsims=nsims, gamma=gamma)
+        same(dev, host, "H=%d no comms" % Hn)
+        dh, dd = host.distribution(with_masks=masks_of), dev.distribution(with_masks=masks_of)
+        assert np.array_equal(dh.seqs, dd.seqs) and np.array_equal(dh.q, dd.q) and np.array_equal(dh.masks, dd.masks)
+        assert np.array_equal(host.best_action_index(), dev.best_action_index())
+        # communication: every tree receives its partner's distribution; a third of the trees have no partner entry
+        valid = (np.arange(T) % 3) != 0
+        for tr, dist in ((host, dh), (dev, dd)):
+            tr.receive_comms(ActionDistribution(dist.seqs[partner], dist.q[partner], dist.masks[partner]), valid=valid)
+            tr.receive_comms(ActionDistribution(dist.seqs, dist.q, dist.masks), valid=np.zeros(T, bool), draw_only=valid)
+        avg_h = None
+        for _ in range(9):
+            avg_h = host.grow(nsims=nsims, gamma=gamma)
+        dev.reserve(9)
+        dev.grow_n(8, nsims=nsims, gamma=gamma)
+        avg_d = dev.grow(nsims=nsims, gamma=gamma)
+        same(dev, host, "H=%d comms" % Hn)
+        assert np.array_equal(avg_h, avg_d)
+        assert dev.launches == host.launches == 22
+        assert (host.n_nodes > 12).all()
+        if Hn == 2:
+            assert (host.stage[np.arange(T), host.last_node] == 2).any()
+    # an under-sized node array is refused, not overrun
+    small = DeviceDecMCTS(sim, sel, horizon=10, seed=1, nsims=4, n_grows=1)
+    small.grow_n(6, gamma=1.0)
+    with pytest.raises(Exception, match="node arrays full"):
+        small.sync_host()
+    sim.close()
+
+
 def test_env_runs_ig_mcts_policy():
     """ig_mcts agents driven by the env itself: team belief update + Dec-MCTS planning inside step(); two explorers
     and two static targets per environment, explorers first (the reference's layout)."""

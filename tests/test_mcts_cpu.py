@@ -81,8 +81,8 @@ def test_mcts_batch_is_independent_trees(oracle_lib):
         def __init__(self, seeds):
             self.g = [np.random.default_rng(s) for s in seeds]
 
-        def integers(self, lo, hi, shape):
-            return np.stack([g.integers(lo, hi, shape[1:]) for g in self.g])
+        def integers(self, lo, hi, shape, dtype=np.int64):
+            return np.stack([g.integers(lo, hi, shape[1:], dtype=dtype) for g in self.g])
 
         def random(self, n):
             return np.array([g.random() for g in self.g])
