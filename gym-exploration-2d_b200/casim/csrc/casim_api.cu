@@ -144,6 +144,9 @@ static int derive(const casim_config* c, DevCfg* d) {
     d->laser_sin[i] = sin(c->laser_angles[i]);
   }
   for (int i = 0; i < d->nr; i++) d->laser_r[i] = c->laser_ranges[i];
+  d->laser_sorted = 1;
+  for (int i = 1; i < d->nr; i++)
+    if (!(c->laser_ranges[i] > c->laser_ranges[i - 1])) d->laser_sorted = 0;
   /* LaserScanSensor.py:58 `1 - ranges / max_range`, fp64 then stored fp32: one IEEE division per table entry, here instead of per CTA */
   for (int i = 0; i < CASIM_MAX_RANGES; i++) d->laser_out[i] = i < d->nr ? (float)(1.0 - d->laser_r[i] / d->laser_norm) : 0.f;
   d->laser_out[CASIM_MAX_RANGES] = (float)(1.0 - d->laser_max_range / d->laser_norm);

@@ -66,6 +66,7 @@ struct DevCfg {
   double map_hw, map_hh; /* map_width/2, map_height/2 (metres) */
   int nb, nr;
   int coll_w_static, max_obs, rows, submap_w, submap_h, game_over_mode, auto_reset, ig_dim;
+  int laser_sorted; /* laser_r strictly increasing (np.arange): the ego-disc test is confined to a prefix of the samples */
 };
 
 struct casim_handle {

@@ -629,24 +629,38 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
         const int disc_thr = ego_in ? (int)fmin(ceil(rc2), 2.0e9) - 1 : -1; /* d^2 < rc2 <=> d^2 <= ceil(rc2) - 1 */
         const int P = 1 << p.lg2P;
         const int b = lane >> p.lg2P, part = lane & (P - 1);
+        /* kd = samples that may fall into the ego disc: r_k / cell < rc + 1.5; a prefix when the r_k increase
+         * (np.arange, LaserScanSensor.py:18-20), every sample otherwise */
+        const int kd = !c.laser_sorted ? nr
+                                       : __popc(__ballot_sync(FULL_MASK, lane < nr && disc_thr >= 0 &&
+                                                                             s_lr[min(lane, CASIM_MAX_RANGES - 1)] * c.inv_cell < rc + 1.5));
         unsigned mask = 0;
         if (b < nb) {
           const double cs = s_lcos[b] * ch - s_lsin[b] * sh, sn = s_lsin[b] * ch + s_lcos[b] * sh;
           const double u0 = c.map_oy + px * c.inv_cell, du = cs * c.inv_cell;
           const double v0 = c.map_ox - py * c.inv_cell, dv = -(sn * c.inv_cell);
-          /* branch-free: out-of-map samples read a clamped address and are masked out afterwards */
-#pragma unroll 4
-          for (int k = part; k < nr; k += P) {
+          /* Branch-free.  The staged plane is padded with free cells on every side, so an out-of-map sample needs no
+           * bounds test: its (unsigned-)clamped address lands on a free padding cell.  The ego-disc exclusion (Map.py:73-79)
+           * can only remove samples within rc + sqrt(2) cells of the agent (a cell index is within one cell of the point
+           * it holds): only the first kd samples of a beam carry the test. */
+          auto sample = [&](int k) -> uint32_t {
             const double rk = s_lr[k];
             const int col = __double2int_rd(fma(rk, du, u0)), row = __double2int_rd(fma(rk, dv, v0));
-            const bool in = (unsigned)row < (unsigned)CASIM_MAP_DIM && (unsigned)col < (unsigned)CASIM_MAP_DIM;
-            const int pr = min(max(row, 0), CASIM_MAP_DIM - 1) + CASIM_G2_PAD, pc = min(max(col, 0), CASIM_MAP_DIM - 1) + CASIM_G2_PAD;
+            const uint32_t pr = min((uint32_t)row + (uint32_t)CASIM_G2_PAD, (uint32_t)(CASIM_G2_DIM - 1));
+            const uint32_t pc = min((uint32_t)col + (uint32_t)CASIM_G2_PAD, (uint32_t)(CASIM_G2_DIM - 1));
             uint32_t w;
-            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(a_map + 4u * (uint32_t)(pr * CASIM_G2_WORDS + (pc >> 5))));
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(a_map + 4u * (pr * CASIM_G2_WORDS + (pc >> 5))));
+            return (w >> (pc & 31u)) & 1u;
+          };
+          int k = part;
+          for (; k < kd; k += P) { /* near the agent: with the disc test */
+            const double rk = s_lr[k];
+            const int col = __double2int_rd(fma(rk, du, u0)), row = __double2int_rd(fma(rk, dv, v0));
             const int dr = row - r0, dc = col - c0;
-            const bool hit = in && ((w >> (pc & 31)) & 1u) && (dr * dr + dc * dc > disc_thr);
-            mask |= (hit ? 1u : 0u) << k;
+            mask |= ((dr * dr + dc * dc > disc_thr) ? sample(k) : 0u) << k;
           }
+#pragma unroll 4
+          for (; k < nr; k += P) mask |= sample(k) << k;
         }
         for (int o = 1; o < P; o <<= 1) mask |= __shfl_xor_sync(FULL_MASK, mask, o);
         if (b < nb && part == 0) {
