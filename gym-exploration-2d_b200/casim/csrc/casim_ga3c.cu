@@ -92,6 +92,9 @@ __device__ __forceinline__ const float4* ga3c_src(const Ga3cArgs& p, size_t g) {
  * disagreement of the argmax had an fp32 top-2 margin < 0.024), so an argmax can only flip when that margin is below
  * ~0.08.  Agents whose bf16 margin is below G_FIX_MARGIN are queued and re-evaluated by the fp32 kernel, which then
  * overwrites their action / probabilities: the action index equals the fp32 forward's for every agent. */
+#ifndef G_FIX_AG
+#define G_FIX_AG 2 /* agents per warp of the fix-up tile: 8 * G_FIX_AG agents per CTA (4: same kernel time, slower step) */
+#endif
 #define G_FIX_MARGIN 0.10f
 
 #define U_NA 144 /* agents per CTA of the tensor-core path */
@@ -285,43 +288,43 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
 
 __device__ __forceinline__ float sigmoid_f(float v) { return 1.0f / (1.0f + expf(-v)); }
 
-/* acc[a][o] += sum_k act[k][ag0 + a] * W[k][col(o)] for this thread's 8 agents x 8 columns.
- * LSTM = true : columns {g*64 + tx*2 + {0,1}}: all four gates of units tx*2, tx*2+1 (row length 256);
- * LSTM = false: columns tx*8 .. tx*8+7. */
-template <bool LSTM, int AG>
-__device__ __forceinline__ void gemm_tile(const float* __restrict__ W, const float* __restrict__ bias, int K,
+/* ---- weights staged through shared memory (cp.async), so that a tile's serial k loop never waits on L2 ---- */
+#define G_WKC 32                               /* rows per streamed chunk of a dense layer */
+#define G_WBUF ((G_OTHER + G_H) * G_FC)        /* floats: the whole LSTM kernel (71 x 256), or two dense chunks (2 x 32 x 256) */
+
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+/* rows x 256 floats, global -> shared, all G_THREADS threads; the caller commits / waits */
+__device__ __forceinline__ void stage_rows(float* dst, const float* src, int rows, int tid) {
+  for (int i = tid; i < rows * (G_FC / 4); i += G_THREADS) cp_async16(dst + 4 * i, src + 4 * i);
+}
+
+/* acc[a][o] = bias + sum_k act[k][ty * AG + a] * W[k][col(o)] for this thread's AG agents x 8 columns, k ascending (an
+ * agent's result does not depend on AG or on the staging).
+ * LSTM step: columns {g*64 + tx*2 + {0,1}}: all four gates of units tx*2, tx*2+1; W = the kernel resident in shared memory. */
+template <int AG>
+__device__ __forceinline__ void lstm_tile(const float* sw /* smem [71][256] */, const float* __restrict__ bias,
                                           const float* act /* smem [K][8 * AG] */, int tx, int ty, float acc[AG][8]) {
   constexpr int TILE = 8 * AG;
-  float b[8];
-  if (LSTM) {
-#pragma unroll
-    for (int g = 0; g < 4; g++) {
-      float2 v = __ldg(reinterpret_cast<const float2*>(bias + g * G_H + tx * 2));
-      b[2 * g] = v.x;
-      b[2 * g + 1] = v.y;
-    }
-  } else {
-    float4 v0 = __ldg(reinterpret_cast<const float4*>(bias + tx * 8)), v1 = __ldg(reinterpret_cast<const float4*>(bias + tx * 8 + 4));
-    b[0] = v0.x; b[1] = v0.y; b[2] = v0.z; b[3] = v0.w; b[4] = v1.x; b[5] = v1.y; b[6] = v1.z; b[7] = v1.w;
-  }
 #pragma unroll
   for (int a = 0; a < AG; a++)
 #pragma unroll
     for (int o = 0; o < 8; o++) acc[a][o] = 0.f;
 #pragma unroll 4
-  for (int k = 0; k < K; k++) {
+  for (int k = 0; k < G_OTHER + G_H; k++) {
     float w[8];
-    const float* wr = W + (size_t)k * G_FC;
-    if (LSTM) {
 #pragma unroll
-      for (int g = 0; g < 4; g++) {
-        float2 v = __ldg(reinterpret_cast<const float2*>(wr + g * G_H + tx * 2));
-        w[2 * g] = v.x;
-        w[2 * g + 1] = v.y;
-      }
-    } else {
-      float4 v0 = __ldg(reinterpret_cast<const float4*>(wr + tx * 8)), v1 = __ldg(reinterpret_cast<const float4*>(wr + tx * 8 + 4));
-      w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
+    for (int g = 0; g < 4; g++) {
+      const float2 v = *reinterpret_cast<const float2*>(sw + k * G_FC + g * G_H + tx * 2);
+      w[2 * g] = v.x;
+      w[2 * g + 1] = v.y;
     }
     float av[AG];
     if (AG == 8) {
@@ -329,6 +332,9 @@ __device__ __forceinline__ void gemm_tile(const float* __restrict__ W, const flo
       const float4 a1 = *reinterpret_cast<const float4*>(act + k * TILE + ty * 8 + 4);
       av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w;
       av[AG - 4] = a1.x; av[AG - 3] = a1.y; av[AG - 2] = a1.z; av[AG - 1] = a1.w;
+    } else if (AG == 4) {
+      const float4 a0 = *reinterpret_cast<const float4*>(act + k * TILE + ty * 4);
+      av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[AG - 1] = a0.w;
     } else {
 #pragma unroll
       for (int a = 0; a < AG; a++) av[a] = act[k * TILE + ty * AG + a];
@@ -339,18 +345,88 @@ __device__ __forceinline__ void gemm_tile(const float* __restrict__ W, const flo
       for (int o = 0; o < 8; o++) acc[a][o] = fmaf(av[a], w[o], acc[a][o]);
   }
 #pragma unroll
+  for (int g = 0; g < 4; g++) {
+    const float2 v = __ldg(reinterpret_cast<const float2*>(bias + g * G_H + tx * 2));
+#pragma unroll
+    for (int a = 0; a < AG; a++) {
+      acc[a][2 * g] += v.x;
+      acc[a][2 * g + 1] += v.y;
+    }
+  }
+}
+
+/* Dense layer: column of output o = (o < 4 ? tx*4 + o : 128 + tx*4 + o - 4) (two conflict-free LDS.128 per k row);
+ * W [K][256] streams from global memory through a two-chunk ring in shared memory.  Every thread of the CTA must call. */
+__device__ __forceinline__ int dense_col(int tx, int o) { return o < 4 ? tx * 4 + o : G_FC / 2 + tx * 4 + o - 4; }
+
+template <int AG>
+__device__ __forceinline__ void dense_tile(const float* __restrict__ W, const float* __restrict__ bias, int K,
+                                           const float* act /* smem [K][8 * AG] */, float* sw /* smem [2][G_WKC][256] */,
+                                           int tid, int tx, int ty, float acc[AG][8]) {
+  constexpr int TILE = 8 * AG;
+#pragma unroll
   for (int a = 0; a < AG; a++)
 #pragma unroll
-    for (int o = 0; o < 8; o++) acc[a][o] += b[o];
+    for (int o = 0; o < 8; o++) acc[a][o] = 0.f;
+  const int nchunks = (K + G_WKC - 1) / G_WKC;
+  stage_rows(sw, W, min(G_WKC, K), tid);
+  cp_async_commit();
+  for (int ch = 0; ch < nchunks; ch++) {
+    const int k0 = ch * G_WKC, rows = min(G_WKC, K - k0);
+    if (ch + 1 < nchunks) {
+      stage_rows(sw + ((ch + 1) & 1) * G_WKC * G_FC, W + (size_t)(k0 + G_WKC) * G_FC, min(G_WKC, K - k0 - G_WKC), tid);
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads(); /* chunk ch has landed for everyone */
+    const float* wc = sw + (ch & 1) * G_WKC * G_FC;
+#pragma unroll 4
+    for (int kk = 0; kk < rows; kk++) {
+      const float4 v0 = *reinterpret_cast<const float4*>(wc + kk * G_FC + tx * 4);
+      const float4 v1 = *reinterpret_cast<const float4*>(wc + kk * G_FC + G_FC / 2 + tx * 4);
+      const float w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+      const int k = k0 + kk;
+      float av[AG];
+      if (AG == 8) {
+        const float4 a0 = *reinterpret_cast<const float4*>(act + k * TILE + ty * 8);
+        const float4 a1 = *reinterpret_cast<const float4*>(act + k * TILE + ty * 8 + 4);
+        av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w;
+        av[AG - 4] = a1.x; av[AG - 3] = a1.y; av[AG - 2] = a1.z; av[AG - 1] = a1.w;
+      } else if (AG == 4) {
+        const float4 a0 = *reinterpret_cast<const float4*>(act + k * TILE + ty * 4);
+        av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[AG - 1] = a0.w;
+      } else {
+#pragma unroll
+        for (int a = 0; a < AG; a++) av[a] = act[k * TILE + ty * AG + a];
+      }
+#pragma unroll
+      for (int a = 0; a < AG; a++)
+#pragma unroll
+        for (int o = 0; o < 8; o++) acc[a][o] = fmaf(av[a], w[o], acc[a][o]);
+    }
+    __syncthreads(); /* everyone is done with this buffer before chunk ch + 2 overwrites it */
+  }
+  const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + tx * 4));
+  const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + G_FC / 2 + tx * 4));
+  const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+  for (int a = 0; a < AG; a++)
+#pragma unroll
+    for (int o = 0; o < 8; o++) acc[a][o] += bb[o];
 }
 
 /* fp32 forward: CTA = 8 * AG agents, 256 threads (tx = lane: output columns, ty = warp: AG agents).  AG = 8 for the full
- * batch; AG = 2 for the fix-up of a short list (4x the CTAs, a quarter of the serial work per thread: the list is short, so
- * its cost is one CTA's latency).  An agent's result does not depend on AG (same k order per output). */
+ * batch; AG = G_FIX_AG = 2 for the fix-up of a short list (4x the CTAs, a quarter of the serial work per thread: the list is
+ * short, so its cost is one CTA's latency).  The LSTM kernel is staged into shared memory once and stays for the ten steps;
+ * the dense layers' weights stream through a two-chunk cp.async ring: 238.8 -> 141.0 us for the fix-up of the C5 bench
+ * (20 % of the agents), 680 -> 550 us for the full-batch fp32 forward.  An agent's result does not depend on AG (same k order per output). */
 template <int AG>
 __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
   constexpr int TILE = 8 * AG;
-  extern __shared__ __align__(16) float s_act[]; /* [256][TILE] transposed activations */
+  extern __shared__ __align__(16) float s_act[]; /* [256][TILE] transposed activations, then G_WBUF floats of weights */
+  float* s_w = s_act + G_FC * TILE;
   __shared__ float s_logit[TILE][12];
   __shared__ int s_len[TILE];
   const size_t N = (size_t)p.E * p.A;
@@ -365,6 +441,8 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
     return g0 + a < (size_t)nfix ? (size_t)p.fix_list[g0 + a] : N;
   };
 
+  stage_rows(s_w, w + W_LSTM_K, G_OTHER + G_H, tid); /* the LSTM kernel stays in shared memory for all the steps */
+  cp_async_commit();
   /* sequence length per agent (x[0], un-normalised: network.py:85); -1 = slot without a GA3C agent */
   if (tid < TILE) {
     size_t g = agent_of(tid);
@@ -379,6 +457,7 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
     if (k < G_OTHER && g < N) v = (p.x[g * G_XS + 1 + G_HOST + k] - c_oth_avg[k]) / c_oth_std[k];
     s_act[idx] = v;
   }
+  cp_async_wait<0>();
   __syncthreads();
   int maxlen = 0;
   for (int a = 0; a < TILE; a++) maxlen = max(maxlen, s_len[a]);
@@ -389,7 +468,7 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
 #pragma unroll
   for (int a = 0; a < AG; a++) cst[a][0] = cst[a][1] = 0.f;
   for (int t = 0; t < maxlen; t++) {
-    gemm_tile<true, AG>(w + W_LSTM_K, w + W_LSTM_B, G_OTHER + G_H, s_act, tx, ty, acc);
+    lstm_tile<AG>(s_w, w + W_LSTM_B, s_act, tx, ty, acc);
     __syncthreads(); /* everyone has read x_t and h */
 #pragma unroll
     for (int a = 0; a < AG; a++) {
@@ -427,14 +506,14 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
 #pragma unroll 1
   for (int layer = 0; layer < 3; layer++) {
     if (layer == 0)
-      gemm_tile<false, AG>(Wk[0], Wb[0], G_HOST + G_H, s_act + 3 * TILE, tx, ty, acc);
+      dense_tile<AG>(Wk[0], Wb[0], G_HOST + G_H, s_act + 3 * TILE, s_w, tid, tx, ty, acc);
     else
-      gemm_tile<false, AG>(Wk[layer], Wb[layer], G_FC, s_act, tx, ty, acc);
-    __syncthreads();
+      dense_tile<AG>(Wk[layer], Wb[layer], G_FC, s_act, s_w, tid, tx, ty, acc);
+    /* (dense_tile ends on a barrier: everyone has read the layer's input) */
 #pragma unroll
     for (int a = 0; a < AG; a++)
 #pragma unroll
-      for (int o = 0; o < 8; o++) s_act[(tx * 8 + o) * TILE + ty * AG + a] = fmaxf(acc[a][o], 0.f);
+      for (int o = 0; o < 8; o++) s_act[dense_col(tx, o) * TILE + ty * AG + a] = fmaxf(acc[a][o], 0.f);
     __syncthreads();
   }
   /* logits_p: TILE agents x 11 outputs, K = 256 */
@@ -1046,7 +1125,9 @@ cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_
     e = cudaMalloc((void**)&h->ga3c_x, (size_t)h->E * h->A * G_XS * sizeof(float));
     if (e != cudaSuccess) return e;
   }
-  e = cudaFuncSetAttribute(k_ga3c_fwd<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)G_FC * G_TILE * sizeof(float)));
+  e = cudaFuncSetAttribute(k_ga3c_fwd<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((size_t)G_FC * G_TILE + G_WBUF) * sizeof(float)));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k_ga3c_fwd<G_FIX_AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((size_t)G_FC * 8 * G_FIX_AG + G_WBUF) * sizeof(float)));
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_ga3c_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)U_DYN_SMEM);
   if (e != cudaSuccess) return e;
@@ -1128,9 +1209,10 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
     if (skip_state) return cudaErrorInvalidValue; /* the state kernel zeroes the fix-up counter */
     h->launches++;
     a.fix_mode = 1;
-    k_ga3c_fwd<2><<<(unsigned)((N + 15) / 16), G_THREADS, (size_t)G_FC * 16 * sizeof(float), s>>>(a);
+    k_ga3c_fwd<G_FIX_AG><<<(unsigned)((N + 8 * G_FIX_AG - 1) / (8 * G_FIX_AG)), G_THREADS,
+                           ((size_t)G_FC * 8 * G_FIX_AG + G_WBUF) * sizeof(float), s>>>(a);
     return cudaGetLastError();
   } else
-    k_ga3c_fwd<8><<<(unsigned)((N + G_TILE - 1) / G_TILE), G_THREADS, (size_t)G_FC * G_TILE * sizeof(float), s>>>(a);
+    k_ga3c_fwd<8><<<(unsigned)((N + G_TILE - 1) / G_TILE), G_THREADS, ((size_t)G_FC * G_TILE + G_WBUF) * sizeof(float), s>>>(a);
   return cudaGetLastError();
 }

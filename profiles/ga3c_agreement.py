@@ -28,6 +28,7 @@ sim.ga3c_set_weights(w)
 tot = same = 0
 maxdp = 0.0
 hist = []
+low = {0.02: 0, 0.05: 0, 0.10: 0}
 for t in range(8):
     sim.ga3c_forward(use_tensor_cores=False)
     torch.cuda.synchronize()
@@ -42,9 +43,13 @@ for t in range(8):
     maxdp = max(maxdp, float((ptc[live] - p32[live]).abs().max()))
     srt = torch.sort(p32[live], dim=-1).values
     margin = srt[:, -1] - srt[:, -2]
+    srt_tc = torch.sort(ptc[live], dim=-1).values
+    for thr in low:                                   # what the exact mode would re-evaluate at this margin threshold
+        low[thr] += int(((srt_tc[:, -1] - srt_tc[:, -2]) < thr).sum())
     bad = itc[live] != i32[live]
     hist.append(float(margin[bad].max()) if bool(bad.any()) else 0.0)
     sim.step(policy_actions=a32)
 print(json.dumps({"set": "formations 1024x20, 8 steps", "agents": tot, "agreement": same / tot, "max_abs_dprob": maxdp,
-                  "largest_margin_of_a_disagreement": max(hist)}))
+                  "largest_margin_of_a_disagreement": max(hist),
+                  "fraction_with_bf16_margin_below": {str(k): v / tot for k, v in low.items()}}))
 sim.close()
