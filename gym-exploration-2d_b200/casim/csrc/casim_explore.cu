@@ -551,7 +551,7 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   __shared__ unsigned short s_queue[XR_QCAP];
   __shared__ unsigned int s_seen[XR_MASK_WORDS];
   __shared__ unsigned long long s_sum;
-  __shared__ int s_qn, s_nposes;
+  __shared__ int s_qn, s_nposes, s_probe;
 
   const int dim = c.ig_dim;
   const double* d2 = p.edf + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
@@ -565,9 +565,13 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
     const double rad = p2.z;
     const uint8_t* seq = p.actions + (size_t)gk * p.H;
     int np_ = 0;
+    s_probe = 0;
     for (int t = 0; t < p.H; t++) {
       const int a = seq[t];
-      if (a > 8) break;
+      if (a > 8) { /* end of the sequence; CASIM_ROLLOUT_PROBE: the caller only wants n_feasible (an expansion probe) */
+        s_probe = a == CASIM_ROLLOUT_PROBE;
+        break;
+      }
       const double v = 2.0 * (double)(a / 3);
       const double w = (a % 3 == 0) ? -0.5 * CASIM_PI : ((a % 3 == 2) ? 0.5 * CASIM_PI : 0.0);
       double nx = x, ny = y, nh = h;
@@ -596,6 +600,12 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
     }
   }
   __syncthreads();
+  if (s_probe) { /* feasibility only: no visibility, no reward */
+    if (tid == 0) p.rewards[gk] = 0.f;
+    if (p.obsvd)
+      for (int w = tid; w < XR_MASK_WORDS; w += XR_THREADS) p.obsvd[(size_t)gk * XR_MASK_WORDS + w] = 0u;
+    return;
+  }
   const int nposes = s_nposes;
   if (tid < nposes) { /* the boxes (three fp64 sincos each) do not depend on one another: one thread per pose */
     PoseBox b;

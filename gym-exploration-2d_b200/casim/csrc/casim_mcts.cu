@@ -109,8 +109,10 @@ __global__ void __launch_bounds__(32 * MC_WARPS)
   for (int idx = lane; idx < K * H; idx += 32) {
     const int k = idx / H, d = idx - k * H;
     int v = path[d];
-    if (k < MC_ACT) {
-      if (stage < H && d == stage) v = k;
+    if (k < MC_ACT) { /* expansion probe: path + action k, feasibility only; nothing to probe at the horizon */
+      if (stage >= H) v = MC_END;
+      else if (d == stage) v = k;
+      else if (d == stage + 1) v = CASIM_ROLLOUT_PROBE;
     } else if (root_only) {
       v = MC_END;
     } else if (d >= stage) {

@@ -364,6 +364,9 @@ int casim_explore_team_update(casim_handle* h, const float* state, const float* 
  * the sequence were applied; == the sequence length iff mcts_state_storer would accept every step, :200-221) are
  * optional. */
 #define CASIM_ROLLOUT_MAX_H 32
+#define CASIM_ROLLOUT_PROBE 254 /* action value that ends a sequence like any value > 8 and marks it as an expansion probe: only
+                                   n_feasible is wanted (DecMCTS.py:201-231 asks whether path + action is feasible, not what it
+                                   sees), so the visibility / reward part is skipped: rewards = 0, obsvd = 0 */
 #define CASIM_CELL_MASK_WORDS 128
 int casim_explore_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                            int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
