@@ -606,6 +606,18 @@ int casim_explore_team_update(casim_handle* h, const float* state, const float* 
   return 0;
 }
 
+int casim_explore_mi_table(casim_handle* h, const float* state, const float* belief, int64_t* table, void* stream) {
+  REQUIRE(h && state && belief && table, "null argument");
+  CK(casim_launch_mi_table(h, state, belief, reinterpret_cast<long long*>(table), (cudaStream_t)stream));
+  return 0;
+}
+
+int casim_explore_set_mi_table(casim_handle* h, const int64_t* table) {
+  REQUIRE(h, "null handle");
+  h->mi_table = reinterpret_cast<const long long*>(table);
+  return 0;
+}
+
 int casim_explore_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                            int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
                            float* end_pose, uint32_t* obsvd, int32_t* n_feasible, void* stream) {

@@ -519,6 +519,7 @@ struct RolloutArgs {
   int32_t* n_feasible;        /* [E*A][K] or NULL: steps of the sequence that were applied */
   const int32_t* n_agents;
   const double* edf;
+  const long long* mi_table;  /* [E*A][dim][dim] fixed-point cell_mi of the belief (casim_explore_mi_table) or NULL */
   int E, A, n_maps, K, H, xdt, exclude_per_rollout, qcap;
 };
 
@@ -660,7 +661,23 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   }
 
   /* ---- mcts_reward: MI over obsvd_cells minus the other robots' cells (targetMap.py:130-143) ---- */
-  {
+  if (p.mi_table) {
+    /* The belief does not change while a planner grows its trees, so a cell's (fixed-point) mutual information is a
+     * constant of the planning step: the caller tabulates it once (casim_explore_mi_table) and a rollout's reward is an
+     * integer sum over its cells -- the same integers as below, no logarithms.  One mask word per warp pass, lane = bit. */
+    const long long* tab = p.mi_table + (size_t)g * dim * dim;
+    const int lane = tid & 31;
+    long long part = 0;
+    for (int w = tid >> 5; w < XR_MASK_WORDS; w += XR_THREADS / 32) {
+      const unsigned int seen = s_seen[w];
+      if (p.obsvd && lane == 0) p.obsvd[(size_t)gk * XR_MASK_WORDS + w] = seen;
+      unsigned int m = seen;
+      if (m && p.exclude) m &= ~p.exclude[((size_t)(p.exclude_per_rollout ? gk : g)) * XR_MASK_WORDS + w];
+      if ((m >> lane) & 1u) part += tab[(w >> 1) * dim + (w & 1) * 32 + lane];
+    }
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL_MASK, part, o);
+    if (lane == 0 && part) atomicAdd(&s_sum, (unsigned long long)part);
+  } else {
     const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
     const float* belief = p.belief + (size_t)g * dim * dim;
     long long part = 0;
@@ -897,6 +914,27 @@ cudaError_t casim_launch_explore(casim_handle* h, const float* state, const floa
 }
 
 
+namespace {
+/* cell_mi of every target-map cell of every explorer, in the 2^-44 fixed point the rollout rewards are summed in */
+__global__ void k_mi_table(DevCfg c, const float4* state, const float* belief, long long* table, int E, int A) {
+  const size_t N = (size_t)E * A;
+  const int cells = c.ig_dim * c.ig_dim;
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * cells) return;
+  const size_t g = idx / cells;
+  if ((__float_as_int(state[5 * N + g].w) & 0xff) != CASIM_POLICY_IG_GREEDY) return;
+  const double log_rocc = log(c.ig_rocc), log_remp = log(c.ig_remp);
+  table[idx] = __double2ll_rn(cell_mi(c, (double)belief[idx], log_rocc, log_remp) * X_MI_SCALE);
+}
+}  // namespace
+
+cudaError_t casim_launch_mi_table(casim_handle* h, const float* state, const float* belief, long long* table, cudaStream_t s) {
+  const size_t total = (size_t)h->E * h->A * h->dc.ig_dim * h->dc.ig_dim;
+  h->launches++;
+  k_mi_table<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(h->dc, reinterpret_cast<const float4*>(state), belief, table, h->E, h->A);
+  return cudaGetLastError();
+}
+
 cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                                   int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
                                   float* end_pose, uint32_t* obsvd, int32_t* n_feasible, cudaStream_t s) {
@@ -912,6 +950,7 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   a.n_feasible = n_feasible;
   a.n_agents = h->n_agents;
   a.edf = h->edf;
+  a.mi_table = h->mi_table;
   a.E = h->E;
   a.A = h->A;
   a.n_maps = h->n_maps;

@@ -89,6 +89,7 @@ struct casim_handle {
   int grid2_ready;         /* tensor map encoded for the current grid2_map */
   unsigned int* grid_work; /* [2] self-resetting work counter + finished-warp counter of the persistent k_grid_tma */
   uint8_t* grid_packed;    /* caller's optional bit-packed local_grid buffer (casim_set_grid_packed_output) or NULL */
+  const long long* mi_table; /* caller's optional tabulated cell_mi of the belief (casim_explore_set_mi_table) or NULL */
   /* borrowed from the caller (casim_reset / casim_set_trajectories) */
   const float* init;
   const int32_t* type0;
@@ -147,6 +148,7 @@ cudaError_t casim_launch_scenario(casim_handle* h, int kind, int number_of_agent
 cudaError_t casim_launch_team_update(casim_handle* h, const float* state, const float* oas, float* belief,
                                      const double* targets_prev, const int32_t* n_prev, double* targets_new,
                                      int32_t* n_new, uint32_t* team_mask, float* team_reward, cudaStream_t s);
+cudaError_t casim_launch_mi_table(casim_handle* h, const float* state, const float* belief, long long* table, cudaStream_t s);
 cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                                   int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
                                   float* end_pose, uint32_t* obsvd, int32_t* n_feasible, cudaStream_t s);

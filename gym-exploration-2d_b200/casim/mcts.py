@@ -323,6 +323,9 @@ class DeviceDecMCTS(BatchedDecMCTS):
         self.n_feasible = torch.zeros((sim.E, sim.A, K), dtype=torch.int32, device=dev)
         self.exclude = None
         self.avg = torch.zeros(T, dtype=torch.float64, device=dev)
+        # mcts_reward's per-cell term on the (fixed) belief, tabulated once per grow_n: casim_explore_mi_table
+        self.mi_table = torch.zeros(tuple(sim.belief.shape), dtype=torch.int64, device=dev)
+        self._table_ready = False
         self._comm_dev = None
         self._host_valid = False
         # root (Tree.__init__, :120-133): _expansion(root) from the feasibility of its 9 one-step extensions
@@ -387,9 +390,16 @@ class DeviceDecMCTS(BatchedDecMCTS):
                 "casim_mcts_select")
         if not root_only and draws is None:
             self.iteration += 1
-        L.check(sim.lib.casim_explore_rollouts(sim.handle, L.ptr(sim.state), L.ptr(sim.belief), L.ptr(self.actions), self.K,
-                                               self.H, self.xdt, L.ptr(ex), 0, L.ptr(self.rewards), None, None,
-                                               L.ptr(self.n_feasible), stream), "casim_explore_rollouts")
+        use_table = self._table_ready and not root_only
+        if use_table:
+            L.check(sim.lib.casim_explore_set_mi_table(sim.handle, L.ptr(self.mi_table)), "casim_explore_set_mi_table")
+        try:
+            L.check(sim.lib.casim_explore_rollouts(sim.handle, L.ptr(sim.state), L.ptr(sim.belief), L.ptr(self.actions), self.K,
+                                                   self.H, self.xdt, L.ptr(ex), 0, L.ptr(self.rewards), None, None,
+                                                   L.ptr(self.n_feasible), stream), "casim_explore_rollouts")
+        finally:
+            if use_table:                        # the launch has taken the pointer: no other caller ever sees a stale table
+                L.check(sim.lib.casim_explore_set_mi_table(sim.handle, None), "casim_explore_set_mi_table")
         L.check(sim.lib.casim_mcts_update(sim.handle, ctypes_byref(s), L.ptr(self.actions), L.ptr(self.rewards),
                                           L.ptr(self.n_feasible), L.ptr(self.avg), int(root_only), stream), "casim_mcts_update")
         self.launches += 1
@@ -401,6 +411,10 @@ class DeviceDecMCTS(BatchedDecMCTS):
         if nsims is not None and int(nsims) != self.nsims:
             raise self._lib.CasimError("DeviceDecMCTS was built for nsims = %d" % self.nsims)
         self._upload_comms()
+        self._lib.check(self.sim.lib.casim_explore_mi_table(self.sim.handle, self._lib.ptr(self.sim.state),
+                                                            self._lib.ptr(self.sim.belief), self._lib.ptr(self.mi_table),
+                                                            ctypes_stream(torch)), "casim_explore_mi_table")
+        self._table_ready = True
         C = len(self.comms)
         us = np.zeros((n, max(C, 1), T))
         draws = None if self.device_draws else np.empty((n, T, self.nsims, self.H), np.uint8)

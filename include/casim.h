@@ -363,6 +363,15 @@ int casim_explore_team_update(casim_handle* h, const float* state, const float* 
  * as a mask, BEFORE the difference -- what a robot communicates) and n_feasible [E,A,K] (int32: how many steps of
  * the sequence were applied; == the sequence length iff mcts_state_storer would accept every step, :200-221) are
  * optional. */
+/* Tabulated mutual information for the rollouts.  A planner evaluates thousands of rollouts per agent on ONE belief
+ * (ig_mcts.find_next_action grows its tree between two belief updates, ig_mcts.py:79-109), and mcts_reward's per-cell term
+ * (targetMap.py:130-143) depends on the cell's belief alone.  casim_explore_mi_table writes that term for every cell of
+ * every ig_* agent, in the 2^-44 fixed point the rewards are summed in, to table [E,A,dim,dim] int64 (device);
+ * casim_explore_set_mi_table(h, table) makes casim_explore_rollouts read it instead of taking two logarithms per observed
+ * cell (same integers, same rewards); NULL switches back.  The table belongs to the caller and must match the belief
+ * passed to casim_explore_rollouts. */
+int casim_explore_mi_table(casim_handle* h, const float* state, const float* belief, int64_t* table, void* stream);
+int casim_explore_set_mi_table(casim_handle* h, const int64_t* table);
 #define CASIM_ROLLOUT_MAX_H 32
 #define CASIM_ROLLOUT_PROBE 254 /* action value that ends a sequence like any value > 8 and marks it as an expansion probe: only
                                    n_feasible is wanted (DecMCTS.py:201-231 asks whether path + action is feasible, not what it

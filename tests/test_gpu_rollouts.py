@@ -154,6 +154,28 @@ def test_rollouts_full_size_properties():
     c = s2.explore_rollouts(actions[lo:hi])
     assert torch.equal(c["rewards"], a["rewards"][lo:hi]) and torch.equal(c["end_pose"], a["end_pose"][lo:hi])
     s2.close()
+    # tabulated mutual information (casim_explore_mi_table / casim_explore_set_mi_table): the same rewards, bit for bit,
+    # with and without the other robots' claimed cells; and the probe marker gives n_feasible without a reward
+    from casim import lib as _lib
+    table = torch.zeros(tuple(sim.belief.shape), dtype=torch.int64, device=sim.belief.device)
+    _lib.check(sim.lib.casim_explore_mi_table(sim.handle, _lib.ptr(sim.state), _lib.ptr(sim.belief), _lib.ptr(table), None),
+               "casim_explore_mi_table")
+    ex = rng.integers(-2**31, 2**31, (E, 4, 128)).astype(np.int32)
+    plain_ex = sim.explore_rollouts(actions, exclude=ex)
+    _lib.check(sim.lib.casim_explore_set_mi_table(sim.handle, _lib.ptr(table)), "casim_explore_set_mi_table")
+    t0, t1 = sim.explore_rollouts(actions), sim.explore_rollouts(actions, exclude=ex)
+    _lib.check(sim.lib.casim_explore_set_mi_table(sim.handle, None), "casim_explore_set_mi_table")
+    assert torch.equal(t0["rewards"], a["rewards"]) and torch.equal(t0["obsvd"], a["obsvd"])
+    assert torch.equal(t1["rewards"], plain_ex["rewards"]) and torch.equal(t1["n_feasible"], a["n_feasible"])
+    assert float((plain_ex["rewards"] - a["rewards"]).abs().max()) > 0.1
+    probe = actions.copy()
+    probe[..., 4] = 254                                # CASIM_ROLLOUT_PROBE after four steps
+    pr = sim.explore_rollouts(probe)
+    four = actions.copy()
+    four[..., 4:] = 255
+    f4 = sim.explore_rollouts(four)
+    assert torch.equal(pr["n_feasible"], f4["n_feasible"]) and float(pr["rewards"].abs().max()) == 0.0
+    assert float(f4["rewards"].max()) > 0.1 and int(pr["obsvd"].abs().max()) == 0
     still = np.full((E, 4, 1, Hn), 1, np.uint8)      # v = 0, dphi = 0: the pose never changes
     st = sim.explore_rollouts(still)
     end = st["end_pose"][:, :, 0]
