@@ -558,7 +558,75 @@ __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   const double* d2 = p.edf + (size_t)(p.n_maps == 1 ? 0 : e) * CASIM_MAP_DIM * CASIM_MAP_DIM;
   unsigned cnt_samples = 0, cnt_clamped = 0;
   for (int w = tid; w < XR_MASK_WORDS; w += XR_THREADS) s_seen[w] = 0u;
-  if (tid == 0) {
+  if (p.xdt == 1 && tid < 32) {
+    /* ---- the replay on one warp, lane t = step t.  The only serial dependence is feasibility (an infeasible step keeps
+     * pose and heading), so the warp SPECULATES that every remaining step is feasible: headings and positions are the same
+     * running sums the serial loop forms (each lane accumulates its own prefix in step order: identical operations,
+     * identical bits), the fp64 sincos and the clearance look-ups of all steps run side by side, and the first infeasible
+     * step ends the pass -- the steps before it are final, the walk resumes behind it from the last good pose.  One pass
+     * per infeasible step instead of one sincos + one dependent EDF load per step. ---- */
+    const int lane = tid;
+    if (lane == 0) {
+      s_qn = 0;
+      s_sum = 0ull;
+    }
+    const float4 p0 = p.state[g], p2 = p.state[2 * N + g];
+    double x = p0.x, y = p0.y, h = p0.z;
+    const double rad = p2.z;
+    const int a = lane < p.H ? (int)p.actions[(size_t)gk * p.H + lane] : 255;
+    const unsigned endm = __ballot_sync(FULL_MASK, a > 8);
+    const int len = endm ? __ffs(endm) - 1 : 32;
+    const int a_end = __shfl_sync(FULL_MASK, a, min(len, 31));
+    const double v = a <= 8 ? 2.0 * (double)(a / 3) : 0.0;
+    const double w = a <= 8 ? ((a % 3 == 0) ? -0.5 * CASIM_PI : ((a % 3 == 2) ? 0.5 * CASIM_PI : 0.0)) : 0.0;
+    int t0 = 0, np_ = 0;
+    while (t0 < len) {
+      double hh = h, xx = x, yy = y; /* the state before step `lane` if steps t0 .. lane-1 are all feasible */
+      for (int k = t0; k < len; k++) {
+        const double wk = __shfl_sync(FULL_MASK, w, k);
+        if (k < lane) hh = hh + wk * c.ig_dt;
+      }
+      double sn, cs;
+      sincos(hh, &sn, &cs);
+      const double vx = cs * v + (-sn) * 0.0, vy = sn * v + cs * 0.0;
+      for (int k = t0; k < len; k++) {
+        const double vxk = __shfl_sync(FULL_MASK, vx, k), vyk = __shfl_sync(FULL_MASK, vy, k);
+        if (k < lane) {
+          xx = xx + vxk * c.ig_dt;
+          yy = yy + vyk * c.ig_dt;
+        }
+      }
+      const double nx = xx + vx * c.ig_dt, ny = yy + vy * c.ig_dt, nh = hh + w * c.ig_dt;
+      const bool mine = lane >= t0 && lane < len;
+      bool ok = true;
+      if (mine && v != 0.0) {
+        const bool in_map = c.map_hw > nx && c.map_hh > ny && nx > -c.map_hw && ny > -c.map_hh;
+        ok = in_map && edf_value(c, d2, nx, ny, cnt_clamped) > rad + 0.1;
+      }
+      const unsigned bad = __ballot_sync(FULL_MASK, mine && !ok);
+      const int f = bad ? __ffs(bad) - 1 : len; /* ig_mcts.py:237-243: at step f the pose stays, nothing is observed */
+      if (lane >= t0 && lane < f) {
+        PoseBox& q = s_pose[np_ + lane - t0];
+        q.x = nx; q.y = ny; q.cs = nh; /* heading parked in .cs until the boxes are built */
+      }
+      if (f > t0) {
+        x = __shfl_sync(FULL_MASK, nx, f - 1);
+        y = __shfl_sync(FULL_MASK, ny, f - 1);
+        h = __shfl_sync(FULL_MASK, nh, f - 1);
+      }
+      np_ += f - t0;
+      t0 = f + 1;
+    }
+    if (lane == 0) {
+      s_probe = len < p.H && a_end == CASIM_ROLLOUT_PROBE;
+      s_nposes = np_;
+      if (p.n_feasible) p.n_feasible[gk] = np_;
+      if (p.end_pose) {
+        p.end_pose[3 * (size_t)gk] = (float)x; p.end_pose[3 * (size_t)gk + 1] = (float)y;
+        p.end_pose[3 * (size_t)gk + 2] = (float)h;
+      }
+    }
+  } else if (p.xdt != 1 && tid == 0) { /* sub-stepped actions (xDT > 1): the plain serial replay */
     s_qn = 0;
     s_sum = 0ull;
     const float4 p0 = p.state[g], p2 = p.state[2 * N + g];
