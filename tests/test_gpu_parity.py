@@ -234,6 +234,38 @@ def test_random_batch_sensors_vs_oracle(oracle_lib, torch_mod, per_env_maps):
     sim.close()
 
 
+@pytest.mark.parametrize("A", [3, 12, 16, 24, 32])
+def test_agent_count_instantiations_vs_oracle(oracle_lib, torch_mod, A):
+    """Every k_core<., AP> instantiation the other tests do not reach (AP = 4 via an odd count, 12, 16, 24 and the
+    CASIM_MAX_AGENTS = 32 maximum): ragged n_agents, all sensors, observe + 6 lock-step steps on a shared map."""
+    torch = torch_mod
+    oracle = oracle_lib
+    rng = np.random.default_rng(100 + A)
+    E = 24
+    b = H.random_batch(rng, E, A, sensor_choices=(0, 1, 3, 7, 7), spread=9.0)
+    b["n_agents"][0] = A                       # the full width at least once, a ragged rest
+    assert int(b["n_agents"].min()) < A
+    maps, rects = H.unpack_maps()
+    cfg = gcfg(0)
+    sim = make_sim(E, A, cfg)
+    sim.set_obstacles(rects[1].astype(np.float32))
+    sim.bind(types=b["types"], n_agents=b["n_agents"])
+    sim.set_trajectories(b["traj"])
+    sim.load_state_numpy(b["state"])
+    ext = torch.as_tensor(b["ext"], dtype=torch.float32).cuda()
+    sim.observe()
+    torch.cuda.synchronize()
+    oobs = oracle.observe(cfg, b["state"], n_agents=b["n_agents"], maps=maps[1])
+    H.compare_obs("observe A=%d" % A, b["n_agents"], bufs_numpy(sim), oobs)
+    for t in range(6):
+        ostate = sim.state_numpy()
+        oobs = oracle.step(cfg, ostate, ext_actions=b["ext"], n_agents=b["n_agents"], traj=b["traj"], maps=maps[1])
+        sim.step(ext_actions=ext)
+        torch.cuda.synchronize()
+        H.compare_step("A=%d t=%d" % (A, t), b["n_agents"], sim.state_numpy(), bufs_numpy(sim), ostate, oobs)
+    sim.close()
+
+
 def test_auto_reset_and_multi_step_vs_oracle(oracle_lib, torch_mod):
     """30 lock-step steps with auto-reset: a game-over environment restarts from its initial condition."""
     oracle = oracle_lib
