@@ -151,3 +151,49 @@ def test_explore_c4_full_size_properties(oracle_lib):
     H.assert_close(sim.belief.cpu().numpy()[sel][ig], belief[ig], "C4 belief", rtol=1e-6, atol=0)
     H.assert_close(sim.buf["cand_mi"].cpu().numpy()[sel][ig], o["cand_mi"][ig], "C4 cand_mi", rtol=1e-5, atol=1e-9)
     sim.close()
+
+
+def test_explore_and_rollouts_per_env_maps():
+    """n_maps == E: every environment samples ITS OWN distance field (the `n_maps == 1 ? 0 : e` indexing of k_explore,
+    k_rollouts and k_team_update).  Environments alternate between two different maps; each must behave exactly like the
+    same environment in a batch that shares its map."""
+    import torch
+    from casim import scenarios as S
+    E = 16
+    init, types, n, rects = S.exploration(E, seed=77)
+    z = H.load("explore.npz")
+    maps, _ = H.explore_maps(z)
+    cfg = _cfg()
+    which = np.arange(E) % 2                                       # map 0 / map 1 of the exploration fixtures
+    rng = np.random.default_rng(2)
+    actions = rng.integers(0, 9, (E, 4, 6, 8)).astype(np.uint8)
+
+    def run(map_arg, lo=0, hi=E, idx=None):
+        idx = np.arange(lo, hi) if idx is None else idx
+        sim = _sim(len(idx), 4, cfg)
+        sim.set_map(map_arg)
+        sim.reset(init[idx], types[idx], n[idx])
+        outs = []
+        for _ in range(3):
+            sim.explore_step()
+            outs.append(sim.buf["policy_actions"].clone())
+            sim.step(policy_actions=sim.buf["policy_actions"])
+        r = sim.explore_rollouts(actions[idx])
+        torch.cuda.synchronize()
+        res = (sim.belief.clone(), sim.state.clone(), torch.stack(outs), r["rewards"].clone(), r["n_feasible"].clone(), r["obsvd"].clone())
+        sim.close()
+        return res
+
+    per_env = run(np.stack([maps[int(w)] for w in which]))
+    differ = False
+    for m in (0, 1):
+        idx = np.nonzero(which == m)[0]
+        shared = run(maps[m], idx=idx)
+        ti = torch.from_numpy(idx).cuda()
+        assert torch.equal(per_env[0][ti], shared[0]) and torch.equal(per_env[1][:, ti], shared[1])
+        assert torch.equal(per_env[2][:, ti], shared[2])
+        for k in (3, 4, 5):
+            assert torch.equal(per_env[k][ti], shared[k]), k
+        other = run(maps[1 - m], idx=idx)                          # the wrong map does change the outcome
+        differ |= not torch.equal(other[0], shared[0]) or not torch.equal(other[3], shared[3])
+    assert differ

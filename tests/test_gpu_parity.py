@@ -266,6 +266,39 @@ def test_agent_count_instantiations_vs_oracle(oracle_lib, torch_mod, A):
     sim.close()
 
 
+def test_empty_and_single_agent_environments_vs_oracle(oracle_lib, torch_mod):
+    """Ragged down to nothing: environments with 0 agents (game_over at once, all(...) of an empty list,
+    collision_avoidance_env.py:700-717) and with 1 agent (no pairs, no OtherAgentsStates rows) next to full ones."""
+    torch = torch_mod
+    oracle = oracle_lib
+    rng = np.random.default_rng(5)
+    E, A = 40, 6
+    b = H.random_batch(rng, E, A, sensor_choices=(0, 1, 3, 7, 7), spread=9.0, n_min=0)
+    b["n_agents"][:6] = [0, 1, 0, 1, 2, A]
+    maps, rects = H.unpack_maps()
+    cfg = gcfg(0)
+    sim = make_sim(E, A, cfg)
+    sim.set_obstacles(rects[1].astype(np.float32))
+    sim.bind(types=b["types"], n_agents=b["n_agents"])
+    sim.set_trajectories(b["traj"])
+    sim.load_state_numpy(b["state"])
+    ext = torch.as_tensor(b["ext"], dtype=torch.float32).cuda()
+    sim.observe()
+    torch.cuda.synchronize()
+    oobs = oracle.observe(cfg, b["state"], n_agents=b["n_agents"], maps=maps[1])
+    H.compare_obs("observe", b["n_agents"], bufs_numpy(sim), oobs)
+    for t in range(4):
+        ostate = sim.state_numpy()
+        oobs = oracle.step(cfg, ostate, ext_actions=b["ext"], n_agents=b["n_agents"], traj=b["traj"], maps=maps[1])
+        sim.step(ext_actions=ext)
+        torch.cuda.synchronize()
+        H.compare_step("t=%d" % t, b["n_agents"], sim.state_numpy(), bufs_numpy(sim), ostate, oobs)
+        g = bufs_numpy(sim)
+        empty = b["n_agents"] == 0
+        assert g["game_over"][empty].all() and np.array_equal(g["game_over"], oobs.game_over)
+    sim.close()
+
+
 def test_auto_reset_and_multi_step_vs_oracle(oracle_lib, torch_mod):
     """30 lock-step steps with auto-reset: a game-over environment restarts from its initial condition."""
     oracle = oracle_lib
