@@ -135,6 +135,8 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
   __shared__ double s_po[GS_AG][CASIM_MAX_AGENTS];
   __shared__ int s_kr[GS_AG][CASIM_MAX_AGENTS];
   __shared__ int s_m[GS_AG], s_n[GS_AG], s_ok[GS_AG];
+  __shared__ const float4* s_src[GS_AG];            /* the state this agent's ENVIRONMENT is read from (ga3c_src: state, or the
+                                                       episode-start state when the environment restarts inside the coming step) */
   __shared__ __align__(16) float s_row[GS_AG][G_XS];
   const DevCfg& c = p.c;
   const size_t N = (size_t)p.E * p.A;
@@ -150,10 +152,12 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
       const size_t g = gb + a;
       const int e = (int)(g / A), i = (int)(g - (size_t)e * A);
       n = p.n_agents ? min(p.n_agents[e], A) : A;
-      const int type = __float_as_int(ga3c_src(p, g)[5 * N + g].w);
+      const float4* src = ga3c_src(p, g);
+      s_src[a] = src;
+      const int type = __float_as_int(src[5 * N + g].w);
       ok = (i < n && (type & 0xff) == CASIM_POLICY_GA3C_CADRL) ? 1 : 0;
       if (ok) {
-        const float4 h0 = ga3c_src(p, g)[g], h2 = ga3c_src(p, g)[2 * N + g];
+        const float4 h0 = src[g], h2 = src[2 * N + g];
         const double px = h0.x, py = h0.y;
         /* agent.py:250-269 get_ref */
         double gx = (double)h2.x - px, gy = (double)h2.y - py;
@@ -184,7 +188,8 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
       const int e = (int)(g / A), i = (int)(g - (size_t)e * A);
       if (j < s_n[a] && j != i) {
         const size_t o = (size_t)e * A + j;
-        const float4 o0 = ga3c_src(p, o)[o], o2 = ga3c_src(p, o)[2 * N + o];
+        const float4* src = s_src[a]; /* o is an agent of the same environment */
+        const float4 o0 = src[o], o2 = src[2 * N + o];
         const double rx = (double)o0.x - s_fr[a][0], ry = (double)o0.y - s_fr[a][1];
         const double dc = sqrt(rx * rx + ry * ry);
         if (!(dc > c.sensing_horizon)) {
@@ -219,7 +224,8 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
     if (slot < 0) continue;
     const size_t g = gb + a;
     const size_t o = (g / A) * A + j;
-    const float4 o0 = ga3c_src(p, o)[o], o1 = ga3c_src(p, o)[N + o], o2 = ga3c_src(p, o)[2 * N + o];
+    const float4* src = s_src[a];
+    const float4 o0 = src[o], o1 = src[N + o], o2 = src[2 * N + o];
     const double prx = s_fr[a][2], pry = s_fr[a][3], rh = s_fr[a][4];
     const double rx = (double)o0.x - s_fr[a][0], ry = (double)o0.y - s_fr[a][1];
     const double vx = o1.x, vy = o1.y;
@@ -236,7 +242,8 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
     const int a = tid;
     if (s_ok[a]) {
       const size_t g = gb + a;
-      const float4 h2 = ga3c_src(p, g)[2 * N + g], h3 = ga3c_src(p, g)[3 * N + g], h5 = ga3c_src(p, g)[5 * N + g];
+      const float4* src = s_src[a];
+      const float4 h2 = src[2 * N + g], h3 = src[3 * N + g], h5 = src[5 * N + g];
       s_row[a][0] = (float)min(min(s_m[a], c.max_obs), G_SLOTS);
       s_row[a][1] = h3.z; /* dist_to_goal */
       s_row[a][2] = h5.x; /* heading_ego_frame */
