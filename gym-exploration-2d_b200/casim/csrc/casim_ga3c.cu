@@ -324,7 +324,7 @@ __device__ __forceinline__ void lstm_tile(const float* sw /* smem [71][256] */, 
   for (int a = 0; a < AG; a++)
 #pragma unroll
     for (int o = 0; o < 8; o++) acc[a][o] = 0.f;
-#pragma unroll 4
+#pragma unroll(AG == 8 ? 4 : 8)
   for (int k = 0; k < G_OTHER + G_H; k++) {
     float w[8];
 #pragma unroll
@@ -389,7 +389,7 @@ __device__ __forceinline__ void dense_tile(const float* __restrict__ W, const fl
     }
     __syncthreads(); /* chunk ch has landed for everyone */
     const float* wc = sw + (ch & 1) * G_WKC * G_FC;
-#pragma unroll 4
+#pragma unroll(AG == 8 ? 4 : 8)
     for (int kk = 0; kk < rows; kk++) {
       const float4 v0 = *reinterpret_cast<const float4*>(wc + kk * G_FC + tx * 4);
       const float4 v1 = *reinterpret_cast<const float4*>(wc + kk * G_FC + G_FC / 2 + tx * 4);
