@@ -121,10 +121,10 @@ def roofline_obj(wl, kern, dominant, step_s, step_bytes, step_must, explore_coun
     peak, peak_src = peaks()
     t, units, how, must = kern[dominant]
     if dominant == "k_ga3c_fwd(fix-up)":
-        # exact mode: the network's algorithmic flops are produced by the bf16 tensor-core forward PLUS the fp32
+        # exact mode: the network's algorithmic flops are produced by the fp16-operand tensor-core forward PLUS the fp32
         # re-evaluation of the agents it cannot call; the roofline line is the pair, on the flops of ONE forward per agent
         t_tc, units, _, _ = kern["k_ga3c_tc"]
-        t, how, dominant = t + t_tc, "k_ga3c_tc timed alone + (exact mode minus the bare bf16 forward)", "k_ga3c_tc + k_ga3c_fwd(fix-up)"
+        t, how, dominant = t + t_tc, "k_ga3c_tc timed alone + (exact mode minus the bare tensor-core forward)", "k_ga3c_tc + k_ga3c_fwd(fix-up)"
     tensor = dominant.startswith(("k_ga3c_tc", "k_ga3c_fwd"))
     if tensor:
         tpeak, tsrc = tensor_peak()
@@ -446,8 +446,8 @@ def main():
     ap.add_argument("--min-timed-ms", type=float, default=50.0, help="replay the K-step graph until the timed region is this long")
     ap.add_argument("--e2e-steps", type=int, default=200)
     ap.add_argument("--ga3c", default="tc-exact", choices=["tc-exact", "tc", "fp32"],
-                    help="c5 forward: bf16 tensor cores + fp32 re-evaluation of the agents bf16 cannot call (default: actions equal "
-                         "the fp32 forward's), bare bf16 tensor cores, or the fp32 SIMT kernel")
+                    help="c5 forward: tensor cores (fp16 operands, fp32 accumulate) + fp32 re-evaluation of the agents they cannot call (default: actions equal "
+                         "the fp32 forward's), bare tensor cores, or the fp32 SIMT kernel")
     ap.add_argument("--ga3c-weights", default="iros18", choices=["iros18", "random"],
                     help="c5: the reference's shipped IROS18 checkpoint (default) or Glorot random-init weights")
     ap.add_argument("--no-stats", action="store_true", help="diagnostics: do not compute the per-step episode statistics")
@@ -799,12 +799,12 @@ def main():
         fwd_name = "k_ga3c_tc" if use_tc else "k_ga3c_fwd"
         kern[fwd_name] = (t_fwd, GA3C_FLOP_PER_AGENT * NA, "timed alone (forward kernel on the previous state vectors)", 0)
         # state-vector kernel: reads 4 state planes of the agent + 3 of each other agent (L1/L2-resident within the
-        # env), writes the 76-float row + 11 bf16 chunks: counted as 64 + 304 + 176 B per agent
+        # env), writes the 76-float row + 11 fp16 chunks: counted as 64 + 304 + 176 B per agent
         t_plain = time_alone(lambda sm: sm.ga3c_forward(use_tensor_cores=use_tc)) if ga3c_exact else t_both
         kern["k_ga3c_state"] = (max(t_plain - t_fwd, 1e-9), (64 + 304 + 176) * NA, "state+forward timed alone minus the forward alone", (64 + 304 + 176) * NA)
         if ga3c_exact:
-            kern["k_ga3c_fwd(fix-up)"] = (max(t_both - t_plain, 1e-9), 0, "exact mode minus the bare bf16 forward: fp32 re-evaluation of the "
-                                          "agents whose top-2 margin is below the bf16 error bound", 0)
+            kern["k_ga3c_fwd(fix-up)"] = (max(t_both - t_plain, 1e-9), 0, "exact mode minus the bare tensor-core forward: fp32 re-evaluation of the "
+                                          "agents whose top-2 margin is below the fp16-operand error bound", 0)
         t_sens += t_both
     core_units = (BYTES_CORE + (BYTES_OAS if "other_agents_states" in W["sensors"] else 0)
                   + (BYTES_WALL if "laserscan" in W["sensors"] or "local_grid" in W["sensors"] else 0)) * NA

@@ -17,6 +17,7 @@
  * k_ga3c_tc: bf16 tcgen05 forward, fp32 accumulate in TMEM (see the block comment above the kernel).
  */
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <cstdio>
 #include <cstdlib>
@@ -87,21 +88,38 @@ __device__ __forceinline__ const float4* ga3c_src(const Ga3cArgs& p, size_t g) {
   return p.state;
 }
 
-/* "tensor cores, exact decisions": the bf16 forward's probabilities were measured within 0.04 of the fp32 forward's
- * (trained IROS18 weights, 163 044 agent-steps of the formation scenario, profiles/r2_ga3c_agreement.json; every
- * disagreement of the argmax had an fp32 top-2 margin < 0.024), so an argmax can only flip when that margin is below
- * ~0.08.  Agents whose bf16 margin is below G_FIX_MARGIN are queued and re-evaluated by the fp32 kernel, which then
- * overwrites their action / probabilities: the action index equals the fp32 forward's for every agent. */
+/* "tensor cores, exact decisions": the tensor-core forward's probabilities were measured within 0.0055 of the fp32 forward's
+ * with fp16 operands (0.039 with bf16; trained IROS18 weights, 163 044 agent-steps of the formation scenario,
+ * profiles/r2z_ga3c_agreement_fp16.json; every disagreement of the argmax had an fp32 top-2 margin < 0.005), so an argmax
+ * can only flip when that margin is below ~0.011.  Agents whose margin is below G_FIX_MARGIN (0.02 for fp16 operands, 0.10
+ * for bf16: ~3.6 x / 2.5 x the measured error) are queued and re-evaluated by the fp32 kernel, which then overwrites their
+ * action / probabilities: the action index equals the fp32 forward's for every agent. */
 #ifndef G_FIX_AG
 #define G_FIX_AG 2 /* agents per warp of the fix-up tile: 8 * G_FIX_AG agents per CTA (4: same kernel time, slower step) */
 #endif
-#define G_FIX_MARGIN 0.10f
+#ifndef U_FP16
+#define U_FP16 1
+#endif
+#define G_FIX_MARGIN (U_FP16 ? 0.02f : 0.10f)
 
 #define U_NA 144 /* agents per CTA of the tensor-core path */
 #define U_XB_SLOTS 11
 
+/* Operand format of the tensor-core forward.  tcgen05 kind::f16 takes fp16 or bf16 operands at the same rate; every operand
+ * of this network is far inside fp16's range (normalised inputs, |h| < 1, ReLU activations of a few units, weights < 10), so
+ * the three extra mantissa bits of fp16 are free accuracy: max |dp| against the fp32 forward 0.039 (bf16) -> see DESIGN.md 4.6.
+ * U_FP16 = 0 restores bf16 operands.  (The helper names keep their round-1 "bf16" suffix.) */
+#ifndef U_FP16
+#define U_FP16 1
+#endif
+#define U_ONE16 (U_FP16 ? 0x3c00u : 0x3f80u) /* 1.0 in the operand format */
+#define U_MAX16 65504.0f                       /* largest finite fp16: activations are clamped, never overflow to inf */
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+#if U_FP16
+  __half2 v = __floats2half2_rn(fminf(fmaxf(lo, -U_MAX16), U_MAX16), fminf(fmaxf(hi, -U_MAX16), U_MAX16)); /* .x = lo (low half) */
+#else
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi); /* .x = lo (low half) */
+#endif
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
@@ -285,7 +303,7 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
           float hv[4];
 #pragma unroll
           for (int k = 0; k < G_HOST; k++) hv[k] = (s_row[a][1 + k] - c_host_avg[k]) / c_host_std[k];
-          q = make_uint4(pack_bf16(hv[0], hv[1]), pack_bf16(hv[2], hv[3]), 0x3f803f80u, (uint32_t)(int)s_row[a][0]);
+          q = make_uint4(pack_bf16(hv[0], hv[1]), pack_bf16(hv[2], hv[3]), U_ONE16 | (U_ONE16 << 16), (uint32_t)(int)s_row[a][0]);
         }
       }
       p.xb[(size_t)sl * npad + gb + a] = q;
@@ -296,8 +314,9 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
 __device__ __forceinline__ float sigmoid_f(float v) { return 1.0f / (1.0f + expf(-v)); }
 
 /* ---- weights staged through shared memory (cp.async), so that a tile's serial k loop never waits on L2 ---- */
-#define G_WKC 32                               /* rows per streamed chunk of a dense layer */
-#define G_WBUF ((G_OTHER + G_H) * G_FC)        /* floats: the whole LSTM kernel (71 x 256), or two dense chunks (2 x 32 x 256) */
+#define G_WKC 16                               /* rows per streamed chunk of a dense layer */
+#define G_WST 4                                /* chunks in the ring: three in flight behind the one in use */
+#define G_WBUF ((G_OTHER + G_H) * G_FC)        /* floats: the whole LSTM kernel (71 x 256), or the dense ring (4 x 16 x 256) */
 
 __device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
@@ -368,7 +387,7 @@ __device__ __forceinline__ int dense_col(int tx, int o) { return o < 4 ? tx * 4 
 
 template <int AG>
 __device__ __forceinline__ void dense_tile(const float* __restrict__ W, const float* __restrict__ bias, int K,
-                                           const float* act /* smem [K][8 * AG] */, float* sw /* smem [2][G_WKC][256] */,
+                                           const float* act /* smem [K][8 * AG] */, float* sw /* smem [G_WST][G_WKC][256] */,
                                            int tid, int tx, int ty, float acc[AG][8]) {
   constexpr int TILE = 8 * AG;
 #pragma unroll
@@ -376,19 +395,24 @@ __device__ __forceinline__ void dense_tile(const float* __restrict__ W, const fl
 #pragma unroll
     for (int o = 0; o < 8; o++) acc[a][o] = 0.f;
   const int nchunks = (K + G_WKC - 1) / G_WKC;
-  stage_rows(sw, W, min(G_WKC, K), tid);
-  cp_async_commit();
+  /* G_WST-deep ring: chunks ch+1 .. ch+G_WST-1 are in flight while chunk ch is used (one commit group per iteration, empty
+   * past the end, so that "all but the newest G_WST-1 groups have landed" always means "chunk ch has landed") */
+#pragma unroll
+  for (int pre = 0; pre < G_WST - 1; pre++) {
+    if (pre < nchunks) stage_rows(sw + pre * G_WKC * G_FC, W + (size_t)pre * G_WKC * G_FC, min(G_WKC, K - pre * G_WKC), tid);
+    cp_async_commit();
+  }
   for (int ch = 0; ch < nchunks; ch++) {
     const int k0 = ch * G_WKC, rows = min(G_WKC, K - k0);
-    if (ch + 1 < nchunks) {
-      stage_rows(sw + ((ch + 1) & 1) * G_WKC * G_FC, W + (size_t)(k0 + G_WKC) * G_FC, min(G_WKC, K - k0 - G_WKC), tid);
+    {
+      const int nx = ch + G_WST - 1;
+      if (nx < nchunks)
+        stage_rows(sw + (nx % G_WST) * G_WKC * G_FC, W + (size_t)nx * G_WKC * G_FC, min(G_WKC, K - nx * G_WKC), tid);
       cp_async_commit();
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
+      cp_async_wait<G_WST - 1>();
     }
     __syncthreads(); /* chunk ch has landed for everyone */
-    const float* wc = sw + (ch & 1) * G_WKC * G_FC;
+    const float* wc = sw + (ch % G_WST) * G_WKC * G_FC;
 #pragma unroll(AG == 8 ? 4 : 8)
     for (int kk = 0; kk < rows; kk++) {
       const float4 v0 = *reinterpret_cast<const float4*>(wc + kk * G_FC + tx * 4);
@@ -413,7 +437,7 @@ __device__ __forceinline__ void dense_tile(const float* __restrict__ W, const fl
 #pragma unroll
         for (int o = 0; o < 8; o++) acc[a][o] = fmaf(av[a], w[o], acc[a][o]);
     }
-    __syncthreads(); /* everyone is done with this buffer before chunk ch + 2 overwrites it */
+    __syncthreads(); /* everyone is done with this buffer before chunk ch + G_WST overwrites it */
   }
   const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + tx * 4));
   const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + G_FC / 2 + tx * 4));
@@ -689,7 +713,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint
 /* instruction descriptor (cute::UMMA::InstrDescriptor): D fp32 [4,6) = 1, A bf16 [7,10) = 1, B bf16 [10,13) = 1,
  * both K-major (bits 15, 16 = 0), N >> 3 in [17,23), M >> 4 in [24,29) */
 __device__ __forceinline__ uint32_t umma_idesc(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+  return (1u << 4) | (U_FP16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24); /* A / B format: 0 = fp16, 1 = bf16 */
 }
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
@@ -726,7 +750,11 @@ __device__ __forceinline__ void sts16(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ void sts_bf16(uint32_t addr, float v) {
+#if U_FP16
+  const __half b = __float2half_rn(fminf(fmaxf(v, -U_MAX16), U_MAX16));
+#else
   const __nv_bfloat16 b = __float2bfloat16_rn(v);
+#endif
   asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(*reinterpret_cast<const unsigned short*>(&b)) : "memory");
 }
 
@@ -870,7 +898,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
     if (tid < U_NA) {
       if (maxlen > 0) {
         sts16(xrow + 8 * U_XCH, p.xb[g0 + tid]);
-        sts16(xrow + 9 * U_XCH, make_uint4(0x3f80u, 0u, 0u, 0u));
+        sts16(xrow + 9 * U_XCH, make_uint4(U_ONE16, 0u, 0u, 0u));
       } else {
         sts16(xrow + 8 * U_XCH, host_chunk);
       }
@@ -1043,7 +1071,13 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
 
 }  // namespace
 
-static uint16_t f32_to_bf16(float f) { /* round to nearest even, like cvt.rn.bf16.f32 */
+static uint16_t f32_to_bf16(float f) { /* round to nearest even, like cvt.rn.bf16.f32 / cvt.rn.f16.f32 */
+#if U_FP16
+  const __half hv = __float2half_rn(f);
+  uint16_t r;
+  memcpy(&r, &hv, 2);
+  return r;
+#endif
   uint32_t u;
   memcpy(&u, &f, 4);
   if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
@@ -1051,6 +1085,11 @@ static uint16_t f32_to_bf16(float f) { /* round to nearest even, like cvt.rn.bf1
   return (uint16_t)(u >> 16);
 }
 static float bf16_to_f32(uint16_t b) {
+#if U_FP16
+  __half hv;
+  memcpy(&hv, &b, 2);
+  return __half2float(hv);
+#endif
   uint32_t u = (uint32_t)b << 16;
   float f;
   memcpy(&f, &u, 4);

@@ -90,8 +90,8 @@ class BatchedCollisionAvoidanceEnv:
         self.episode_step_number = 0
         self._host_state = None
         self._generator = None
-        # GA3C-CADRL forward: bf16 tensor cores with the fp32 fix-up of the agents bf16 cannot call ("exact"): the action
-        # index equals the fp32 forward's for every agent.  ga3c_exact = False gives the bare bf16 forward,
+        # GA3C-CADRL forward: tensor cores (fp16 operands) with the fp32 fix-up of the agents they cannot call ("exact"): the action
+        # index equals the fp32 forward's for every agent.  ga3c_exact = False gives the bare tensor-core forward,
         # ga3c_use_tensor_cores = False the fp32 forward.
         self.ga3c_use_tensor_cores = True
         self.ga3c_exact = True

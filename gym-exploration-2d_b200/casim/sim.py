@@ -412,7 +412,7 @@ class BatchedSim:
 
     def ga3c_forward(self, use_tensor_cores=False, forward_only=False, exact=False):
         """GA3CCADRLPolicy.find_next_action for every GA3C agent -> ``buf['policy_actions']``.
-        ``use_tensor_cores``: bf16 tcgen05 forward; with ``exact`` the agents it cannot call (top-2 margin below the bf16
+        ``use_tensor_cores``: tcgen05 forward (fp16 operands, fp32 accumulate); with ``exact`` the agents it cannot call (top-2 margin below the fp16
         error bound) are re-evaluated in fp32 in the same call, so the actions equal the fp32 forward's.
         ``forward_only`` (profiling aid) skips the state-vector kernel and reuses the previous call's vectors."""
         _lib.check(self.lib.casim_ga3c_forward(self.handle, _lib.ptr(self.state), _lib.ptr(self.buf["policy_actions"]),

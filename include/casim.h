@@ -429,9 +429,9 @@ int casim_mcts_update(casim_handle* h, const casim_mcts_trees* trees, const uint
  * layer1 [68,256],[256]; layer2 [256,256],[256]; fullyconnected1 [256,256],[256]; logits_p [256,11],[11]
  * (row-major [in,out] like TF).  Writes policy_actions [E,A,2]; optionally action_idx [E,A] (int32, -1 for
  * non-GA3C agents), probs [E,A,11] and nn_input [E,A,75].
- * use_tensor_cores: bit 0 = bf16 tcgen05 forward (else the fp32 SIMT forward); bit 1 = profiling aid, skip the
+ * use_tensor_cores: bit 0 = tcgen05 forward with fp16 operands and fp32 accumulation (else the fp32 SIMT forward); bit 1 = profiling aid, skip the
  * state-vector kernel and run the forward on the state vectors of the previous call; bit 2 (with bit 0) = "tensor cores,
- * exact decisions": every agent whose bf16 top-2 probability margin is too small to call is re-evaluated by the fp32
+ * exact decisions": every agent whose tensor-core top-2 probability margin is too small to call is re-evaluated by the fp32
  * forward in the same call, so that action_idx / policy_actions equal the fp32 forward's for every agent (the reference
  * runs this network in fp32, GA3C_CADRL/network.py:45-98). */
 int casim_ga3c_set_weights(casim_handle* h, const float* weights_host, int n_params, void* stream);
