@@ -11,9 +11,10 @@ from casim import layout as L
 pytestmark = pytest.mark.gpu
 
 # tensor-core forward vs the float64 graph value with the trained checkpoint (see casim_ga3c.cu "precision")
-TC_PROB_TOL = 5e-2         # measured 0.039 over 163 044 agent-steps (profiles/r2_ga3c_agreement.json)
-TC_MIN_MARGIN = 0.10       # an argmax can only flip when the top-2 margin is below 2 x the probability error
-TC_MIN_AGREE = 0.99
+# (fp16 operands: profiles/r2z_ga3c_agreement_fp16.json; the bf16 build of round 1 needed 5e-2 / 0.10 / 0.99)
+TC_PROB_TOL = 1e-2         # measured 0.0055 over 163 044 agent-steps
+TC_MIN_MARGIN = 0.02       # an argmax can only flip when the top-2 margin is below 2 x the probability error
+TC_MIN_AGREE = 0.998
 
 
 def _cfg(**kw):
