@@ -14,7 +14,7 @@
  * k_ga3c_fwd<false>: fp32 SIMT forward, one CTA per tile of 64 agents, register-tiled (8 agents x 8 outputs per
  * thread), activations transposed in shared memory, weights streamed through L1/L2 (170 k parameters, shared by
  * every CTA).  This is the path compared against the fp32 oracle (1e-5).
- * k_ga3c_tc: bf16 tcgen05 forward, fp32 accumulate in TMEM (see the block comment above the kernel).
+ * k_ga3c_tc: tcgen05 forward on 16-bit operands (fp16; bf16 with -DU_FP16=0), fp32 accumulate in TMEM (see the block comment above the kernel).
  */
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -59,12 +59,12 @@ struct Ga3cArgs {
   const int32_t* n_agents;
   const float* w;          /* fp32 parameter blob */
   float* x;                /* [N][G_XS] scratch: the 75-float network input, fp32 */
-  uint4* xb;               /* [tiles][10 slots][128 rows] 16 B: 7 normalised bf16 inputs + bf16 1.0, or NULL */
-  const uint8_t* wimg;     /* bf16 weight image in UMMA smem order (tensor-core path) */
+  uint4* xb;               /* [tiles][10 slots][128 rows] 16 B: 7 normalised 16-bit inputs + 1.0, or NULL */
+  const uint8_t* wimg;     /* 16-bit weight image in UMMA smem order (tensor-core path) */
   unsigned long long* trace; /* tuning aid (CASIM_GA3C_TRACE): [CTA][2 roles][64] globaltimer stamps, else NULL */
   float* policy_actions;   /* [N][2] */
   int32_t* action_idx;     /* [N] or NULL */
-  int32_t* fix_list;       /* [N] agents whose bf16 result is too close to call (top-2 margin < G_FIX_MARGIN), or NULL */
+  int32_t* fix_list;       /* [N] agents whose tensor-core result is too close to call (top-2 margin < G_FIX_MARGIN), or NULL */
   int32_t* fix_count;      /* [1] length of fix_list: zeroed by k_ga3c_state, appended by k_ga3c_tc, read by the fp32 fix-up */
   int fix_mode;            /* k_ga3c_fwd: 1 = re-evaluate the agents of fix_list instead of all agents */
   float* probs;            /* [N][11] or NULL */
@@ -108,13 +108,13 @@ __device__ __forceinline__ const float4* ga3c_src(const Ga3cArgs& p, size_t g) {
 /* Operand format of the tensor-core forward.  tcgen05 kind::f16 takes fp16 or bf16 operands at the same rate; every operand
  * of this network is far inside fp16's range (normalised inputs, |h| < 1, ReLU activations of a few units, weights < 10), so
  * the three extra mantissa bits of fp16 are free accuracy: max |dp| against the fp32 forward 0.039 (bf16) -> see DESIGN.md 4.6.
- * U_FP16 = 0 restores bf16 operands.  (The helper names keep their round-1 "bf16" suffix.) */
+ * U_FP16 = 0 restores bf16 operands ("op16" in the helper names = whichever 16-bit format is selected). */
 #ifndef U_FP16
 #define U_FP16 1
 #endif
 #define U_ONE16 (U_FP16 ? 0x3c00u : 0x3f80u) /* 1.0 in the operand format */
 #define U_MAX16 65504.0f                       /* largest finite fp16: activations are clamped, never overflow to inf */
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+__device__ __forceinline__ uint32_t pack_op16(float lo, float hi) {
 #if U_FP16
   __half2 v = __floats2half2_rn(fminf(fmaxf(lo, -U_MAX16), U_MAX16), fminf(fmaxf(hi, -U_MAX16), U_MAX16)); /* .x = lo (low half) */
 #else
@@ -143,7 +143,7 @@ __device__ __forceinline__ long long py_round2_hundredths(double x) {
  * (nearly) all lanes useful: phase A = one lane per agent (reference frame), phase B = one lane per (agent, other)
  * pair (distance, rounded key, p_orthog), phase C = stable rank of sorted(key = (-round(dist, 2), p_orthog)) per pair
  * (integer compares, fp64 only on key ties), then the 76-float rows are assembled in shared memory and leave the
- * CTA as contiguous stores (x, nn_input) and 16-byte bf16 chunks (xb). */
+ * CTA as contiguous stores (x, nn_input) and 16-byte chunks of 16-bit operands (xb). */
 #define GS_AG 32
 #ifndef GS_THREADS
 #define GS_THREADS 256 /* C5 sweep: 64: 108.6 us per step, 128: 98.5, 192: 97.7, 256: 96.8 (profiles/r1k_sweep_gs.txt) */
@@ -298,12 +298,12 @@ __global__ void __launch_bounds__(GS_THREADS) k_ga3c_state(const Ga3cArgs p) {
 #pragma unroll
           for (int k = 0; k < G_OTHER; k++) nv[k] = (v[k] - c_oth_avg[k]) / c_oth_std[k];
           nv[7] = 1.0f;
-          q = make_uint4(pack_bf16(nv[0], nv[1]), pack_bf16(nv[2], nv[3]), pack_bf16(nv[4], nv[5]), pack_bf16(nv[6], nv[7]));
+          q = make_uint4(pack_op16(nv[0], nv[1]), pack_op16(nv[2], nv[3]), pack_op16(nv[4], nv[5]), pack_op16(nv[6], nv[7]));
         } else {
           float hv[4];
 #pragma unroll
           for (int k = 0; k < G_HOST; k++) hv[k] = (s_row[a][1 + k] - c_host_avg[k]) / c_host_std[k];
-          q = make_uint4(pack_bf16(hv[0], hv[1]), pack_bf16(hv[2], hv[3]), U_ONE16 | (U_ONE16 << 16), (uint32_t)(int)s_row[a][0]);
+          q = make_uint4(pack_op16(hv[0], hv[1]), pack_op16(hv[2], hv[3]), U_ONE16 | (U_ONE16 << 16), (uint32_t)(int)s_row[a][0]);
         }
       }
       p.xb[(size_t)sl * npad + gb + a] = q;
@@ -601,7 +601,7 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
 }
 
 /* ------------------------------------------------------------------------------------------------------------
- * k_ga3c_tc: the same network on the 5th-generation tensor cores (tcgen05.mma, kind::f16, bf16 x bf16 -> fp32),
+ * k_ga3c_tc: the same network on the 5th-generation tensor cores (tcgen05.mma, kind::f16, 16-bit operands -> fp32),
  * TRANSPOSED: D^T[outputs x agents] = W^T[outputs x K] * X^T[K x agents].  Weights are the A operand (M = 128 output
  * rows <-> the 128 TMEM lanes), agents are the N dimension (TMEM columns).  Why: the epilogue is MUFU-bound (5 tanh
  * per LSTM unit per agent per step), MUFU cost is per warp instruction, and a thread can only read its own TMEM
@@ -614,7 +614,7 @@ __global__ void __launch_bounds__(G_THREADS) k_ga3c_fwd(const Ga3cArgs p) {
  * its own lane.  The group split rides on K: gate g's A tile is [W_g ; 0] for K-slabs 0..4 (which multiply agents
  * 0..79) and [0 ; W_g] for K-slabs 5..9 (agents 72..151), both cut out of one shared-memory image laid out
  * [0 | W_i | 0 | W_j | 0 | W_f | 0 | W_o | 0] (64-row blocks) by moving the descriptor start.  K = 80 per group =
- * [h(64) | x_t(7) | 1 | 1 | 0..]; the two "1" columns carry the bias as a bf16 hi + lo pair.
+ * [h(64) | x_t(7) | 1 | 1 | 0..]; the two "1" columns carry the bias as a 16-bit hi + lo pair.
  * layer1 / layer2 / fullyconnected1: two M = 128 blocks x N = 144; logits_p: one block (11 of 128 rows used).
  * Operands sit in shared memory in the canonical K-major SWIZZLE_NONE layout (8-row x 16-byte core matrices): element
  * (r, k) at (k/8)*LBO + r*16 + (k%8)*2, SBO = 128.  The activation tile X[agent][k] uses LBO = 153*16 bytes: the odd
@@ -710,12 +710,12 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint
   return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) |
          (1ull << 46);
 }
-/* instruction descriptor (cute::UMMA::InstrDescriptor): D fp32 [4,6) = 1, A bf16 [7,10) = 1, B bf16 [10,13) = 1,
+/* instruction descriptor (cute::UMMA::InstrDescriptor): D fp32 [4,6) = 1, A / B format [7,10) / [10,13): 0 = fp16, 1 = bf16,
  * both K-major (bits 15, 16 = 0), N >> 3 in [17,23), M >> 4 in [24,29) */
 __device__ __forceinline__ uint32_t umma_idesc(int M, int N) {
   return (1u << 4) | (U_FP16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24); /* A / B format: 0 = fp16, 1 = bf16 */
 }
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
@@ -749,7 +749,7 @@ __device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_
 __device__ __forceinline__ void sts16(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
-__device__ __forceinline__ void sts_bf16(uint32_t addr, float v) {
+__device__ __forceinline__ void sts_op16(uint32_t addr, float v) {
 #if U_FP16
   const __half b = __float2half_rn(fminf(fmaxf(v, -U_MAX16), U_MAX16));
 #else
@@ -847,7 +847,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
 #pragma unroll
           for (int s = 0; s < 10; s++) {
             const int grp = s / 5, sc = s % 5;
-            umma_bf16(tmem + g * 80, umma_desc(sL + (2 * sc) * U_LCH + (2 * g + 1 - grp) * U_LBLK, U_LCH, 128),
+            umma_f16(tmem + g * 80, umma_desc(sL + (2 * sc) * U_LCH + (2 * g + 1 - grp) * U_LBLK, U_LCH, 128),
                       umma_desc(sX + (2 * sc) * U_XCH + grp * U_G * 16, U_XCH, 128), id80, s > 0);
           }
         if (t == maxlen - 1) tc_commit(bar_ldone);
@@ -866,8 +866,8 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
           tc_fence_after();
           const int ks = rot_slab(q, blockIdx.x) - (q - s); /* which K slab of this layer sits in the slot */
           const uint64_t bd = umma_desc(sX + (2 * ks) * U_XCH, U_XCH, 128);
-          umma_bf16(tmem, umma_desc(slot_addr(slot), 4096, 128), bd, id144, s > 0);
-          umma_bf16(tmem + U_NA, umma_desc(slot_addr(slot) + 2048, 4096, 128), bd, id144, s > 0);
+          umma_f16(tmem, umma_desc(slot_addr(slot), 4096, 128), bd, id144, s > 0);
+          umma_f16(tmem + U_NA, umma_desc(slot_addr(slot) + 2048, 4096, 128), bd, id144, s > 0);
           tc_commit(bar_empty + 8 * slot);
         }
         tc_commit(bar_d);
@@ -880,7 +880,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
         mbar_wait(bar_full + 8 * slot, (q / U_RING) & 1);
         tc_fence_after();
         for (int s = 0; s < G_FC / 16; s++)
-          umma_bf16(tmem, umma_desc(slot_addr(slot) + s * 512, 256, 128), umma_desc(sX + (2 * s) * U_XCH, U_XCH, 128), id144,
+          umma_f16(tmem, umma_desc(slot_addr(slot) + s * 512, 256, 128), umma_desc(sX + (2 * s) * U_XCH, U_XCH, 128), id144,
                     s > 0);
         tc_commit(bar_d);
       }
@@ -938,7 +938,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
             const float hn = sigmoid_fast(go[k]) * tanh_fast(cn);
             if (t < lenp[cc + k]) { /* dynamic_rnn(sequence_length): state copied through beyond the last valid step */
               cst[cc + k] = cn;
-              sts_bf16(hdst + (cc + k) * 16, hn);
+              sts_op16(hdst + (cc + k) * 16, hn);
             }
           }
         }
@@ -956,7 +956,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
         if (tid == 0) TRACE(0, ti++);
       }
     }
-    /* layer1, layer2, fullyconnected1: ReLU(D + bias) -> bf16 -> X (in place: the MMAs that read X have completed
+    /* layer1, layer2, fullyconnected1: ReLU(D + bias) -> 16-bit -> X (in place: the MMAs that read X have completed
      * when bar_d fires); output row o = mb*128 + l is K index o of the next GEMM */
     const float* biasg = reinterpret_cast<const float*>(p.wimg + U_IMG_BYTES);
     for (int layer = 0; layer < 3; layer++) {
@@ -980,7 +980,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
           tmem_ld8(trow + mb * U_NA + hw * U_G + cc, v);
           tc_wait_ld();
 #pragma unroll
-          for (int k = 0; k < 8; k++) sts_bf16(dst + (cc + k) * 16, fmaxf(v[k] + b, 0.f));
+          for (int k = 0; k < 8; k++) sts_op16(dst + (cc + k) * 16, fmaxf(v[k] + b, 0.f));
         }
       }
       fence_async_smem();
@@ -1045,7 +1045,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
               psecond = fmaxf(psecond, pr[k]);
             }
           }
-          if (p.fix_list != nullptr && pbest - psecond < G_FIX_MARGIN) /* too close to call in bf16: fp32 decides */
+          if (p.fix_list != nullptr && pbest - psecond < G_FIX_MARGIN) /* too close to call on the tensor cores: fp32 decides */
             p.fix_list[atomicAdd(p.fix_count, 1)] = (int32_t)g;
           if (p.probs) {
 #pragma unroll
@@ -1071,7 +1071,7 @@ __global__ void __launch_bounds__(U_THREADS, 1) k_ga3c_tc(const Ga3cArgs p) {
 
 }  // namespace
 
-static uint16_t f32_to_bf16(float f) { /* round to nearest even, like cvt.rn.bf16.f32 / cvt.rn.f16.f32 */
+static uint16_t f32_to_op16(float f) { /* round to nearest even, like cvt.rn.bf16.f32 / cvt.rn.f16.f32 */
 #if U_FP16
   const __half hv = __float2half_rn(f);
   uint16_t r;
@@ -1084,7 +1084,7 @@ static uint16_t f32_to_bf16(float f) { /* round to nearest even, like cvt.rn.bf1
   u += 0x7fffu + ((u >> 16) & 1u);
   return (uint16_t)(u >> 16);
 }
-static float bf16_to_f32(uint16_t b) {
+static float op16_to_f32(uint16_t b) {
 #if U_FP16
   __half hv;
   memcpy(&hv, &b, 2);
@@ -1113,17 +1113,17 @@ cudaError_t casim_ga3c_upload(casim_handle* h, const float* weights_host, int n_
   for (int k = 0; k < 3; k++, r++) { table[r][0] = 0.0f; table[r][1] = (float)(-PI / 6 + k * (PI / 6)); }
   e = cudaMemcpyToSymbolAsync(c_actions, table, sizeof(table), 0, cudaMemcpyHostToDevice, s);
   if (e != cudaSuccess) return e;
-  /* tensor-core path: bf16 image of every layer in the shared-memory order k_ga3c_tc feeds to tcgen05.mma as the
+  /* tensor-core path: 16-bit image of every layer in the shared-memory order k_ga3c_tc feeds to tcgen05.mma as the
    * A operand (K-major, SWIZZLE_NONE: element (row, k) of a layer at (k/8)*LBO + row*16 + (k%8)*2) */
   std::vector<uint8_t> img(U_IMG_BYTES + U_NBIAS * sizeof(float), 0);
   auto put = [&](size_t layer_off, size_t lbo, int k, int row, float v) {
-    uint16_t b = f32_to_bf16(v);
+    uint16_t b = f32_to_op16(v);
     memcpy(&img[layer_off + (size_t)(k / 8) * lbo + (size_t)row * 16 + (k % 8) * 2], &b, 2);
   };
-  auto put_bias = [&](size_t layer_off, size_t lbo, int k, int row, float v) { /* bf16 hi + lo pair against two "1" columns */
-    uint16_t hi = f32_to_bf16(v);
+  auto put_bias = [&](size_t layer_off, size_t lbo, int k, int row, float v) { /* 16-bit hi + lo pair against two "1" columns */
+    uint16_t hi = f32_to_op16(v);
     put(layer_off, lbo, k, row, v);
-    put(layer_off, lbo, k + 1, row, v - bf16_to_f32(hi));
+    put(layer_off, lbo, k + 1, row, v - op16_to_f32(hi));
   };
   const float* w = weights_host;
   /* LSTM: per K chunk nine 64-row blocks [0 | W_i | 0 | W_j | 0 | W_f | 0 | W_o | 0]; K order [h(64) | x(7) | 1 | 1];
@@ -1206,7 +1206,7 @@ cudaError_t casim_launch_ga3c(casim_handle* h, const float* state, float* policy
   a.fix_list = nullptr;
   a.fix_count = nullptr;
   a.fix_mode = 0;
-  const bool exact = (use_tc & 1) && (use_tc & 4); /* bit 2: fp32 re-evaluation of the agents bf16 cannot call */
+  const bool exact = (use_tc & 1) && (use_tc & 4); /* bit 2: fp32 re-evaluation of the agents the tensor-core forward cannot call */
   if (exact) {
     if (!h->ga3c_fix) {
       cudaError_t e = cudaMalloc((void**)&h->ga3c_fix, (N + 1) * sizeof(int32_t));
