@@ -618,6 +618,14 @@ int casim_explore_set_mi_table(casim_handle* h, const int64_t* table) {
   return 0;
 }
 
+int casim_explore_set_rollout_slots(casim_handle* h, const int32_t* slots, int n_slots) {
+  REQUIRE(h, "null handle");
+  REQUIRE(slots == nullptr || (n_slots >= 1 && (size_t)n_slots <= (size_t)h->E * h->A), "rollout slots: 1 <= n_slots <= E * A");
+  h->rollout_slots = slots;
+  h->n_rollout_slots = slots ? n_slots : 0;
+  return 0;
+}
+
 int casim_explore_rollouts(casim_handle* h, const float* state, const float* belief, const uint8_t* actions, int K,
                            int H, int xdt, const uint32_t* exclude, int exclude_per_rollout, float* rewards,
                            float* end_pose, uint32_t* obsvd, int32_t* n_feasible, void* stream) {

@@ -520,14 +520,17 @@ struct RolloutArgs {
   const int32_t* n_agents;
   const double* edf;
   const long long* mi_table;  /* [E*A][dim][dim] fixed-point cell_mi of the belief (casim_explore_mi_table) or NULL */
+  const int32_t* slots;       /* [n_slots] agent slots to evaluate (casim_explore_set_rollout_slots) or NULL = every slot */
   int E, A, n_maps, K, H, xdt, exclude_per_rollout, qcap;
 };
 
 template <int XR_THREADS>
 __global__ void __launch_bounds__(XR_THREADS) k_rollouts(const RolloutArgs p) {
   const DevCfg& c = p.c;
-  const int gk = blockIdx.x;
-  const int g = gk / p.K;
+  /* one CTA per (agent slot, rollout); with a slot list only the listed slots get CTAs, results stay at [slot][k] */
+  const int si = blockIdx.x / p.K;
+  const int g = p.slots ? p.slots[si] : si;
+  const int gk = g * p.K + (blockIdx.x - si * p.K);
   const int e = g / p.A, ai = g - e * p.A;
   const int n = p.n_agents ? min(p.n_agents[e], p.A) : p.A;
   const size_t N = (size_t)p.E * p.A;
@@ -1019,6 +1022,7 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   a.n_agents = h->n_agents;
   a.edf = h->edf;
   a.mi_table = h->mi_table;
+  a.slots = h->rollout_slots;
   a.E = h->E;
   a.A = h->A;
   a.n_maps = h->n_maps;
@@ -1030,7 +1034,7 @@ cudaError_t casim_launch_rollouts(casim_handle* h, const float* state, const flo
   static const int threads = casim_tuning_int("CASIM_XR_THREADS", 64);
   static const int qcap = [] { int q = casim_tuning_int("CASIM_XR_QCAP", 1024); return q < 1 ? 1 : (q > XR_QCAP ? XR_QCAP : q); }();
   a.qcap = qcap;
-  const unsigned grid = (unsigned)((size_t)h->E * h->A * K);
+  const unsigned grid = (unsigned)((h->rollout_slots ? (size_t)h->n_rollout_slots : (size_t)h->E * h->A) * K);
   if (threads == 32) k_rollouts<32><<<grid, 32, 0, s>>>(a);
   else if (threads == 128) k_rollouts<128><<<grid, 128, 0, s>>>(a);
   else k_rollouts<64><<<grid, 64, 0, s>>>(a);

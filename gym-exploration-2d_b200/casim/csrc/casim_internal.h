@@ -90,6 +90,8 @@ struct casim_handle {
   unsigned int* grid_work; /* [2] self-resetting work counter + finished-warp counter of the persistent k_grid_tma */
   uint8_t* grid_packed;    /* caller's optional bit-packed local_grid buffer (casim_set_grid_packed_output) or NULL */
   const long long* mi_table; /* caller's optional tabulated cell_mi of the belief (casim_explore_set_mi_table) or NULL */
+  const int32_t* rollout_slots; /* caller's optional list of agent slots for casim_explore_rollouts (device) or NULL */
+  int n_rollout_slots;
   /* borrowed from the caller (casim_reset / casim_set_trajectories) */
   const float* init;
   const int32_t* type0;

@@ -81,6 +81,7 @@ SYMBOLS = {
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "casim_explore_mi_table": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "casim_explore_set_mi_table": (c_int, [c_void_p, c_void_p]),
+    "casim_explore_set_rollout_slots": (c_int, [c_void_p, c_void_p, c_int]),
     "casim_mcts_select": (c_int, [c_void_p, ctypes.POINTER(MctsTrees), c_void_p, ctypes.c_uint64, c_int, c_void_p, c_void_p,
                           c_void_p, c_int, c_void_p]),
     "casim_mcts_update": (c_int, [c_void_p, ctypes.POINTER(MctsTrees), c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

@@ -393,12 +393,15 @@ class DeviceDecMCTS(BatchedDecMCTS):
         use_table = self._table_ready and not root_only
         if use_table:
             L.check(sim.lib.casim_explore_set_mi_table(sim.handle, L.ptr(self.mi_table)), "casim_explore_set_mi_table")
+        # only the trees' agent slots get rollout CTAs (the other explorers of an environment plan in their own batch)
+        L.check(sim.lib.casim_explore_set_rollout_slots(sim.handle, L.ptr(self.d["slot"]), self.T), "casim_explore_set_rollout_slots")
         try:
             L.check(sim.lib.casim_explore_rollouts(sim.handle, L.ptr(sim.state), L.ptr(sim.belief), L.ptr(self.actions), self.K,
                                                    self.H, self.xdt, L.ptr(ex), 0, L.ptr(self.rewards), None, None,
                                                    L.ptr(self.n_feasible), stream), "casim_explore_rollouts")
-        finally:
-            if use_table:                        # the launch has taken the pointer: no other caller ever sees a stale table
+        finally:                                 # the launch has taken the pointers: no other caller sees a stale table / list
+            L.check(sim.lib.casim_explore_set_rollout_slots(sim.handle, None, 0), "casim_explore_set_rollout_slots")
+            if use_table:
                 L.check(sim.lib.casim_explore_set_mi_table(sim.handle, None), "casim_explore_set_mi_table")
         L.check(sim.lib.casim_mcts_update(sim.handle, ctypes_byref(s), L.ptr(self.actions), L.ptr(self.rewards),
                                           L.ptr(self.n_feasible), L.ptr(self.avg), int(root_only), stream), "casim_mcts_update")

@@ -372,6 +372,11 @@ int casim_explore_team_update(casim_handle* h, const float* state, const float* 
  * passed to casim_explore_rollouts. */
 int casim_explore_mi_table(casim_handle* h, const float* state, const float* belief, int64_t* table, void* stream);
 int casim_explore_set_mi_table(casim_handle* h, const int64_t* table);
+/* Restrict casim_explore_rollouts to a list of agent slots (e * A + a, int32, DEVICE memory, each a valid slot, no
+ * duplicates): only those slots get CTAs and only their [slot][k] results are written -- a planner that grows the trees of
+ * one explorer per environment (collision_avoidance_env.py:341-379 plans the robots one after the other) does not launch the
+ * other three quarters of the batch.  NULL = every slot again.  The list belongs to the caller. */
+int casim_explore_set_rollout_slots(casim_handle* h, const int32_t* slots, int n_slots);
 #define CASIM_ROLLOUT_MAX_H 32
 #define CASIM_ROLLOUT_PROBE 254 /* action value that ends a sequence like any value > 8 and marks it as an expansion probe: only
                                    n_feasible is wanted (DecMCTS.py:201-231 asks whether path + action is feasible, not what it

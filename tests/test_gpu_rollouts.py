@@ -168,6 +168,16 @@ def test_rollouts_full_size_properties():
     assert torch.equal(t0["rewards"], a["rewards"]) and torch.equal(t0["obsvd"], a["obsvd"])
     assert torch.equal(t1["rewards"], plain_ex["rewards"]) and torch.equal(t1["n_feasible"], a["n_feasible"])
     assert float((plain_ex["rewards"] - a["rewards"]).abs().max()) > 0.1
+    # slot list (casim_explore_set_rollout_slots): only the listed agents are evaluated, at their own [slot][k] positions
+    ig_slots = np.nonzero(((types & 0xff) == L.POLICY_IG_GREEDY).ravel())[0]
+    pick = torch.from_numpy(ig_slots[::3].astype(np.int32)).to(sim.belief.device)
+    _lib.check(sim.lib.casim_explore_set_rollout_slots(sim.handle, _lib.ptr(pick), len(pick)), "casim_explore_set_rollout_slots")
+    part = sim.explore_rollouts(actions)              # (fresh torch.empty outputs: the unlisted slots hold whatever was there)
+    _lib.check(sim.lib.casim_explore_set_rollout_slots(sim.handle, None, 0), "casim_explore_set_rollout_slots")
+    pl = pick.long()
+    for k in ("rewards", "n_feasible", "obsvd", "end_pose"):
+        assert torch.equal(part[k].flatten(0, 1)[pl], a[k].flatten(0, 1)[pl]), k
+    assert sim.lib.casim_explore_set_rollout_slots(sim.handle, _lib.ptr(pick), E * 4 + 1) == 10001
     probe = actions.copy()
     probe[..., 4] = 254                                # CASIM_ROLLOUT_PROBE after four steps
     pr = sim.explore_rollouts(probe)
