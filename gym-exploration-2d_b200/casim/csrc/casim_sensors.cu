@@ -499,6 +499,7 @@ struct Grid2Args {
   float* laser;               /* LaserScanSensor output [E*A][nb] when the laser rides in this kernel, else NULL */
   int lg2P;                   /* laser: lanes per beam = 1 << lg2P */
   int E, A;
+  unsigned inv_A;             /* floor(2^32 / A) + 1 when E * A < 2^32 / A (then umulhi(g, inv_A) == g / A for every agent), else 0 */
 };
 
 __device__ __forceinline__ uint32_t g2_cell(uint32_t a_map, int fx, int fy) {
@@ -614,12 +615,14 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
   unsigned g = ticket();
   bool map_ready = false;
   /* an agent's inputs: loaded one agent ahead, so that their global-memory latency hides behind the previous agent */
-  int in_type = 0, in_n = 0;
+  int in_type = 0, in_n = 0, in_ai = 0;
   float in_radius = 0.f;
   double2 in_q0 = make_double2(0., 0.), in_q1 = make_double2(0., 0.);
   auto fetch = [&](unsigned ag) {
     if (ag < N) {
-      const int ee = (int)(ag / (unsigned)p.A);
+      /* environment of the agent: one multiply-high instead of a division when the launcher could prove it exact */
+      const int ee = p.inv_A ? (int)__umulhi(ag, p.inv_A) : (int)(ag / (unsigned)p.A);
+      in_ai = (int)(ag - (unsigned)ee * (unsigned)p.A);
       in_n = p.n_agents ? min(p.n_agents[ee], p.A) : p.A;
       in_type = __float_as_int(p.state[5 * (size_t)N + ag].w);
       if (p.laser != nullptr) in_radius = p.state[2 * (size_t)N + ag].z;
@@ -629,7 +632,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) k_grid_tma(const __grid_constan
   };
   fetch(g);
   while (g < N) {
-    const int e = (int)(g / (unsigned)p.A), ai = (int)(g - (unsigned)e * (unsigned)p.A);
+    const int ai = in_ai;
     const int n = in_n;
     uint32_t* gout = reinterpret_cast<uint32_t*>(p.out + (size_t)g * cells);
     const int type = in_type;
@@ -1040,6 +1043,7 @@ cudaError_t casim_launch_grid(casim_handle* h, const float* state, uint8_t* loca
     }
     b.E = h->E;
     b.A = h->A;
+    b.inv_A = (h->A >= 2 && (unsigned long long)N * (unsigned long long)h->A < (1ull << 32)) ? (unsigned)((1ull << 32) / (unsigned)h->A) + 1u : 0u;
     const long long want = (N + G2_WARPS - 1) / G2_WARPS;
     const int sms = h->num_sms > 0 ? h->num_sms : CASIM_NUM_SMS_FALLBACK;
     cudaLaunchConfig_t cfg = {};
