@@ -361,6 +361,14 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
   Agent a;
   bool wrote_all = false;
   int go_prev = 0; /* my environment's game_over of the previous step of this launch */
+  /* The kernel is a latency chain on few warps, so its first global loads are issued together instead of one behind the other:
+   * the state planes are read for every lane of the [E,A] range before n_agents (-> valid) and the restart flag have
+   * arrived; a restarting environment re-reads the episode-start state below. */
+  int pgo0 = 0;
+  if (MODE != CASIM_MODE_RESET && slot) {
+    if (IS_STEP && c.auto_reset && p.init) pgo0 = p.prev_game_over[e];
+    load_agent(p.state, plane, g, a);
+  }
 #pragma unroll 1
   for (int it = 0; it < nsteps; it++) {
   const bool last = it == nsteps - 1;
@@ -372,8 +380,8 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
     } else {
       /* auto_reset (the env's reset() folded into the next step): the episode-start state is the one casim_reset
        * stored, i.e. exactly what reset() followed by step() would read */
-      const bool fresh = IS_STEP && c.auto_reset && p.init && (it == 0 ? p.prev_game_over[e] != 0 : go_prev != 0);
-      if (it == 0 || fresh) load_agent(fresh ? p.state0 : p.state, plane, g, a);
+      const bool fresh = IS_STEP && c.auto_reset && p.init && (it == 0 ? pgo0 != 0 : go_prev != 0);
+      if (fresh) load_agent(p.state0, plane, g, a);
       a.have_cs = false;
       wrote_all = wrote_all || fresh || it > 0;
     }
