@@ -102,3 +102,32 @@ def test_mcts_batch_is_independent_trees(oracle_lib):
         for name in ("parent", "stage", "path", "mu", "N", "best_reward", "best_seq", "has_rollout"):
             assert np.array_equal(getattr(both, name)[t, :n], getattr(one, name)[0, :n]), name
     assert both.launches == 9          # one evaluator call per iteration (+ the root expansion)
+
+
+def test_hash_draws_known_answers_and_uniformity():
+    """casim.mcts.hash_draws (the numpy twin of csrc/casim_mcts.cu:mcts_draw, the in-kernel stand-in for
+    np.random.choice(9)) against a plain-integer splitmix64, plus a uniformity check."""
+    from casim.mcts import draw_seed, hash_draws
+    M = (1 << 64) - 1
+
+    def ref(seed, index):
+        x = (seed + 0x9E3779B97F4A7C15 * (index + 1)) & M
+        x ^= x >> 30
+        x = (x * 0xBF58476D1CE4E5B9) & M
+        x ^= x >> 27
+        x = (x * 0x94D049BB133111EB) & M
+        x ^= x >> 31
+        return ((x >> 32) * 9) >> 32
+
+    seed = draw_seed((3, 1, 4))
+    assert seed == draw_seed((3, 1, 4)) and seed != draw_seed((3, 1, 5)) and 0 <= seed < (1 << 64)
+    T, nsims, H = 5, 3, 7
+    for it in (0, 1, 17):
+        d = hash_draws(seed, it, T, nsims, H)
+        assert d.shape == (T, nsims, H) and d.dtype == np.uint8
+        flat = d.ravel()
+        for i in (0, 1, 2, 50, T * nsims * H - 1):
+            assert int(flat[i]) == ref(seed, it * T * nsims * H + i), (it, i)
+    big = hash_draws(seed, 2, 2048, 10, 10)
+    freq = np.bincount(big.ravel(), minlength=9) / big.size
+    assert big.max() == 8 and np.abs(freq - 1 / 9).max() < 0.005
