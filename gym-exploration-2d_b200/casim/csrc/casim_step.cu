@@ -729,7 +729,16 @@ __global__ void __launch_bounds__(CASIM_CORE_THREADS) k_core(const CoreArgs p) {
       if ((((uintptr_t)dst) & 15) == 0 && (total & 3) == 0) {
         const float4* s4 = reinterpret_cast<const float4*>(stage);
         float4* d4 = reinterpret_cast<float4*>(dst);
-        for (int i = lane; i < (total >> 2); i += 32) d4[i] = s4[i];
+        const int n4 = total >> 2;
+        int i = lane;
+        for (; i + 96 < n4; i += 128) { /* four independent 16-byte copies in flight per lane */
+          const float4 v0 = s4[i], v1 = s4[i + 32], v2 = s4[i + 64], v3 = s4[i + 96];
+          d4[i] = v0;
+          d4[i + 32] = v1;
+          d4[i + 64] = v2;
+          d4[i + 96] = v3;
+        }
+        for (; i < n4; i += 32) d4[i] = s4[i];
       } else {
         for (int i = lane; i < total; i += 32) dst[i] = stage[i];
       }
