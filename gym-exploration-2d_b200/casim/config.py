@@ -36,6 +36,7 @@ class Config:
     COLLISION_AV_W_STATIC_AGENT = False
     # envs/config.py:15-16,46
     EVALUATE_MODE = False
+    SCENARIOS_FOR_TRAINING = ["IG_agent_crossing"]   # config.py:91 of the fork (casim.test_cases holds the fixed ones)
     TRAIN_SINGLE_AGENT = True
     HOMOGENEOUS_TESTING = False
     # envs/config.py:55-72

@@ -155,7 +155,18 @@ class BatchedCollisionAvoidanceEnv:
         if self._tensors is not None:
             return self._tensors
         if self.agents is None:
-            raise RuntimeError("call set_agents() or set_scenario_tensors() before reset()")
+            # collision_avoidance_env.py:403-445 _init_agents: tc.<Config.SCENARIOS_FOR_TRAINING[...]>(); the fork's list
+            # is ["IG_agent_crossing"] (config.py:91), a fixed scenario -> every environment of the batch starts it
+            from . import test_cases as tc
+            names = getattr(self.config, "SCENARIOS_FOR_TRAINING", None) or []
+            made = tc.default_scenario(names[0]) if names else None
+            if made is None:
+                raise RuntimeError("call set_agents(), set_scenario_tensors() or set_scenario_generator() before reset() "
+                                   "(Config.SCENARIOS_FOR_TRAINING names no fixed scenario)")
+            if len(made[0]) > self.A:
+                raise RuntimeError("scenario %s has %d agents, max_agents is %d" % (names[0], len(made[0]), self.A))
+            self.set_agents([tc.default_scenario(names[0])[0] for _ in range(self.E)])
+            self.set_static_map(made[1])
         init = np.zeros((self.E, self.A, 7), np.float32)
         types = np.zeros((self.E, self.A), np.int32)
         n = np.zeros((self.E,), np.int32)

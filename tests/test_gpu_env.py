@@ -189,3 +189,31 @@ def test_pipelined_host_step_equals_blocking_steps():
     assert np.array_equal(got["local_grid_packed"].numpy(), np.packbits(refs[-1]["local_grid"].numpy().reshape(E, A, -1), axis=-1))
     for sim in sims:
         sim.close()
+
+
+def test_reset_without_a_scenario_starts_the_forks_default():
+    """Config.SCENARIOS_FOR_TRAINING = ["IG_agent_crossing"] (envs/config.py:91 of the fork): reset() without set_agents /
+    set_scenario_tensors / set_scenario_generator builds that fixed scenario (test_cases.py:3209-3237) in every
+    environment, map included -- what _init_agents does (collision_avoidance_env.py:403-445)."""
+    import torch
+    from casim import test_cases as tc
+    from casim.env import BatchedCollisionAvoidanceEnv
+    env = BatchedCollisionAvoidanceEnv(num_envs=3, max_agents=6)
+    env.reset()
+    torch.cuda.synchronize()
+    st = env.sim.state_numpy()
+    assert np.array_equal(env.sim._keep["n_agents"].cpu().numpy(), [5, 5, 5])
+    assert np.allclose(st[:, :5, L.PX], [[-5, 0, 5, 6, -6]] * 3) and np.allclose(st[:, :5, L.PY], [[0, 0, 0, 12, -12]] * 3)
+    pol = st[:, :5, L.TYPE].astype(np.int64) & 0xff
+    assert (pol[:, :3] == L.POLICY_IG_GREEDY).all() and (pol[:, 3:] == L.POLICY_STATIC).all()
+    assert env.sim.has_map and env._mcts is not None                 # crossing map set, Dec-MCTS planner armed
+    agents, obstacles = tc.IG_agent_crossing()
+    assert len(agents) == 5 and obstacles == tc.CROSSING_OBSTACLES
+    env.close()
+    small = BatchedCollisionAvoidanceEnv(num_envs=1, max_agents=4)   # the scenario does not fit: said so, loudly
+    with pytest.raises(RuntimeError, match="max_agents"):
+        small.reset()
+    small.close()
+    assert [a.policy.policy_id for a in tc.get_testcase_two_agents()] == [L.POLICY_LEARNING, L.POLICY_GA3C_CADRL]
+    assert tc.get_testcase_two_agents_external_rvo()[1].policy.policy_id == L.POLICY_RVO
+    assert all(a.sensors[0].bit == L.SENSOR_LASERSCAN for a in tc.get_testcase_two_agents_laserscanners())
